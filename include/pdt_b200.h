@@ -1,0 +1,145 @@
+/* pdt_b200.h — C ABI of libpdt_b200.so (hand-written sm_100a kernels).
+ *
+ * Conventions
+ *   - every function returns 0 on success, else a cudaError_t value (or a
+ *     negative PDT_E* code), and only ENQUEUES work on `stream`;
+ *   - pointers are device pointers unless stated otherwise;
+ *   - activations are NHWC ("channels_last"), dtype codes PDT_BF16/FP16/FP32;
+ *   - nothing here allocates device memory: callers own every buffer
+ *     (torch tensors on the Python side).
+ * Each declaration cites what it replaces in the reference call graph
+ * (/root/reference/*.py and the torch internals those reach).
+ */
+#ifndef PDT_B200_H_
+#define PDT_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+#include <cuda_runtime_api.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PDT_MAX_RANKS 8
+#define PDT_BF16 0
+#define PDT_FP16 1
+#define PDT_FP32 2
+
+#define PDT_E_UNSUPPORTED (-2)   /* shape/dtype outside what the kernel was written for */
+#define PDT_E_TOO_LARGE (-3)     /* size beyond a documented fixed limit */
+
+/* ---- fabric pad layout (one pad per rank, peer-mapped) ------------------- */
+#define PDT_COMM_CHANNELS 4            /* 0: gradient stream, 1: main stream, 2-3: spare */
+#define PDT_COMM_MAX_BLOCKS 256
+#define PDT_SCRATCH_FLOATS 8192        /* per (channel, source rank) */
+#define PDT_PAD_INF_OFFSET_WORDS (PDT_COMM_CHANNELS * PDT_COMM_MAX_BLOCKS * PDT_MAX_RANKS)
+#define PDT_PAD_SCRATCH_OFFSET_WORDS (PDT_PAD_INF_OFFSET_WORDS + PDT_COMM_MAX_BLOCKS * PDT_MAX_RANKS)
+#define PDT_PAD_BYTES ((size_t)4 * (PDT_PAD_SCRATCH_OFFSET_WORDS + PDT_COMM_CHANNELS * PDT_MAX_RANKS * PDT_SCRATCH_FLOATS))
+
+#ifndef PDT_PEERS_DEFINED
+#define PDT_PEERS_DEFINED
+typedef struct PdtPeers { void* p[PDT_MAX_RANKS]; } PdtPeers;   /* same VA range seen from this rank, one per rank */
+#endif
+
+typedef struct PdtCommDesc {
+  int rank, world;
+  void* pad[PDT_MAX_RANKS];   /* PDT_PAD_BYTES each, zero-initialised once */
+} PdtCommDesc;
+
+size_t pdt_comm_pad_bytes(void);
+
+/* amp_state: 8 x 32-bit words on the device:
+ *   [0] loss scale (f32)  [1] growth tracker (i32)  [2] found_inf, this rank (i32)
+ *   [3] skipped steps (i32)  [4] found_inf consensus (i32)
+ * hyper: 4 floats on the device: lr, momentum, weight_decay, amp_enabled(0/1).   */
+
+/* Gradient bucket all-reduce, first half (c10d Reducer + ncclAllReduce at
+ * distributed.py:262) fused with 1/world, AMP unscale and inf check
+ * (_amp_foreach_non_finite_check_and_unscale_, distributed_syncBN_amp.py:276). */
+int pdt_reduce_scatter_f32(const PdtCommDesc* comm, const PdtPeers* grads, size_t seg_off, size_t seg_len,
+                           float* amp_state, int use_flags, int blocks, cudaStream_t stream);
+
+/* Second half: inf consensus + momentum SGD (torch/optim/sgd.py:343-380) on the
+ * owned shard + store of fp32 weights and low-precision shadow to every rank
+ * (optimizer.step() at distributed.py:263; autocast weight casts). */
+int pdt_sgd_allgather(const PdtCommDesc* comm, const PdtPeers* grads, const PdtPeers* params, const PdtPeers* shadow,
+                      int shadow_dtype, float* momentum, size_t seg_off, size_t seg_len, const float* hyper,
+                      float* amp_state, int use_flags, int blocks, cudaStream_t stream);
+
+/* In-place two-shot all-reduce (dist.all_reduce, distributed.py:80). */
+int pdt_allreduce_f32(const PdtCommDesc* comm, const PdtPeers* bufs, size_t off, size_t len, float post_scale,
+                      int blocks, cudaStream_t stream);
+
+/* One-shot all-reduce of <= PDT_SCRATCH_FLOATS floats: reduce_mean(loss),
+ * reduce_mean(acc1) and the barrier before them (distributed.py:253-255). */
+int pdt_allreduce_small_f32(const PdtCommDesc* comm, const float* in, float* out, int n, float post_scale,
+                            int channel, cudaStream_t stream);
+
+/* Pull [off, off+len) of the root's arena into every rank's arena (DDP
+ * constructor _sync_module_states and per-forward _sync_buffers,
+ * torch/nn/parallel/distributed.py:879-890, 2214-2257). */
+int pdt_bcast_pull(const PdtCommDesc* comm, const PdtPeers* bufs, size_t off_bytes, size_t len_bytes, int root,
+                   int channel, int blocks, cudaStream_t stream);
+
+/* dist.barrier() as a device-side rendezvous (distributed.py:253). */
+int pdt_barrier(const PdtCommDesc* comm, int channel, cudaStream_t stream);
+
+/* GradScaler.update() (_amp_update_scale_, distributed_syncBN_amp.py:277). */
+int pdt_scale_update(float* amp_state, float growth, float backoff, int interval, cudaStream_t stream);
+
+/* foreach momentum SGD on one flat arena (torch/optim/sgd.py:383-477). */
+int pdt_sgd_flat(float* p, const float* g, float* m, void* shadow, int shadow_dtype, size_t n, const float* hyper,
+                 float* amp_state, cudaStream_t stream);
+
+/* ---- BatchNorm / SyncBatchNorm on NHWC activations ------------------------
+ * x, y, dy, dx, res: [M][C] in `dtype`; statistics and affine parameters fp32.
+ * scratch: pdt_bn_scratch_bytes(C) bytes, first word zero before the first
+ * call (self-resetting afterwards); do not share one scratch between kernels
+ * that may overlap.  comm == NULL or world == 1: plain BatchNorm (cuDNN/ATen
+ * batch_norm, 20 layers of torchvision resnet18).  world > 1: SyncBatchNorm
+ * with the cross-rank exchange inside the kernel (replaces
+ * torch/nn/modules/_functions.py:39-209; distributed_syncBN_amp.py:143-145). */
+#define PDT_BN_MAX_BLOCKS 592
+size_t pdt_bn_scratch_bytes(int C);
+int pdt_bn_fwd_stats(const void* x, long M, int C, int dtype, void* scratch, const PdtCommDesc* comm,
+                     float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
+                     float* save_invstd, cudaStream_t stream);
+int pdt_bn_fwd_apply(const void* x, const void* res, void* y, long M, int C, int dtype, const float* mean,
+                     const float* stat2, const float* gamma, const float* beta, int relu, int eval, float eps,
+                     cudaStream_t stream);
+int pdt_bn_bwd_reduce(const void* dy, const void* y, const void* x, long M, int C, int dtype, const float* mean,
+                      const float* invstd, int relu, void* scratch, const PdtCommDesc* comm, float* dgamma,
+                      float* dbeta, float* out_k, cudaStream_t stream);
+int pdt_bn_bwd_apply(const void* dy, const void* y, const void* x, void* dx, void* dres, long M, int C, int dtype,
+                     const float* mean, const float* invstd, const float* gamma, const float* k, int relu,
+                     cudaStream_t stream);
+
+/* ---- loss / pooling / layout ----------------------------------------------
+ * pdt_ce_fwd: nn.CrossEntropyLoss (mean) + utils.accuracy top-1 in one pass
+ * (distributed.py:247,250; utils.py:105-111).  out = {loss, hit fraction};
+ * dlogits_unit = d loss / d logits in fp32.  scratch: pdt_ce_scratch_bytes(B),
+ * first word zero before the first call. */
+size_t pdt_ce_scratch_bytes(int B);
+int pdt_ce_fwd(const void* logits, int dtype, const long long* target, int B, int K, float* dlogits_unit, void* scratch,
+               float* out, cudaStream_t stream);
+/* out = in * (*scale) cast to dtype (loss-scaled dlogits; GradScaler.scale, distributed_syncBN_amp.py:275). */
+int pdt_scale_cast(const float* in, const float* scale, void* out, int dtype, size_t n, cudaStream_t stream);
+/* nn.MaxPool2d / nn.AdaptiveAvgPool2d(1) of torchvision ResNet (ATen max_pool2d_with_indices, mean). */
+int pdt_maxpool_fwd(const void* x, void* y, int8_t* idx, int dtype, int N, int H, int W, int C, int ks, int st, int pd,
+                    cudaStream_t stream);
+int pdt_maxpool_bwd(const void* dy, const int8_t* idx, void* dx, int dtype, int N, int H, int W, int C, int ks, int st,
+                    int pd, cudaStream_t stream);
+int pdt_avgpool_fwd(const void* x, void* y, int dtype, int N, int HW, int C, cudaStream_t stream);
+int pdt_avgpool_bwd(const void* dy, void* dx, int dtype, int N, int HW, int C, cudaStream_t stream);
+/* autocast input cast + channels_last conversion with channel padding (autocast_mode.cpp casts). */
+int pdt_nchw_to_nhwc(const float* x, void* y, int dtype, int N, int Cin, int H, int W, int Cpad, cudaStream_t stream);
+
+/* Destination-side pull of `nbytes` from a peer-mapped pointer (DataParallel scatter / gather /
+ * buffer broadcast; torch.cuda.comm.scatter/gather/broadcast_coalesced, dataparallel.py:119). */
+int pdt_peer_copy(const void* src, void* dst, size_t nbytes, cudaStream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PDT_B200_H_ */

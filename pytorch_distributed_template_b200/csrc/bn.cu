@@ -1,0 +1,402 @@
+// BatchNorm / SyncBatchNorm training kernels on NHWC activations (SURVEY §2.2 N5, N7;
+// §2.4 X7, X8).
+//
+// Forward  = k_bn_fwd_stats  (per-channel sum, sum of squares -> mean, invstd,
+//                             running-stat update; with world > 1 the raw moments
+//                             are exchanged with every peer INSIDE the kernel, over
+//                             NVLink peer stores into the peers' scratch slots)
+//          + k_bn_fwd_apply  (normalise, affine, optional residual add, optional ReLU).
+// Backward = k_bn_bwd_reduce (ReLU mask, sum dy, sum dy*(x-mean); local dgamma/dbeta;
+//                             cross-rank sum of the two vectors in-kernel)
+//          + k_bn_bwd_apply  (dx and the residual branch's gradient).
+//
+// This replaces, for the reference's SyncBN mode (distributed_syncBN_amp.py:143-145),
+// ATen batch_norm_stats + all_gather_into_tensor + batch_norm_gather_stats_with_counts
+// + batch_norm_elemt and batch_norm_backward_reduce + all_reduce +
+// batch_norm_backward_elemt (torch/nn/modules/_functions.py:39-209): 2 collectives, 1
+// host sync and ~8 launches per layer become 0 / 0 / 2.  Equal per-rank counts make the
+// raw-moment sum algebraically identical to the reference's (mean, invstd, count) merge.
+//
+// Reduction scheme: every block reduces a slab of rows to one row of `partial`
+// (scratch, [blocks][2C] floats); the block that takes the last ticket of `counter`
+// (scratch, one word, self-resetting) folds the rows in a fixed order in fp64, so the
+// result is deterministic for a given grid.
+#include "fabric.cuh"
+
+namespace {
+
+using namespace pdt;
+
+constexpr int kThreads = 512;
+constexpr int kSmemFloats = 10240;  // 40 KB staging, reused as double[5120] in the finalise step
+
+template <typename T> struct Vec { static constexpr int N = 16 / sizeof(T); };
+
+template <typename T>
+__device__ __forceinline__ void load_vec(const T* p, float (&f)[Vec<T>::N]) {
+  const uint4 u = *reinterpret_cast<const uint4*>(p);
+  if constexpr (sizeof(T) == 4) {
+    f[0] = __uint_as_float(u.x); f[1] = __uint_as_float(u.y); f[2] = __uint_as_float(u.z); f[3] = __uint_as_float(u.w);
+  } else {
+    unpack8<T>(u, f);
+  }
+}
+template <typename T>
+__device__ __forceinline__ void store_vec(T* p, const float (&f)[Vec<T>::N]) {
+  uint4 u;
+  if constexpr (sizeof(T) == 4) {
+    u.x = __float_as_uint(f[0]); u.y = __float_as_uint(f[1]); u.z = __float_as_uint(f[2]); u.w = __float_as_uint(f[3]);
+  } else {
+    u = pack8<T>(f);
+  }
+  *reinterpret_cast<uint4*>(p) = u;
+}
+
+// Block-level: fold per-thread accumulators (V channels x 2 quantities) into partial[blockIdx][2C].
+template <int V>
+__device__ __forceinline__ void block_fold(float* smem, const float (&a)[V], const float (&b)[V], int C, int cg, int rpi,
+                                           float* __restrict__ partial) {
+  const int tid = threadIdx.x, cgi = tid % cg, r = tid / cg, n2 = 2 * C;
+  if (r < rpi) {
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      smem[r * n2 + cgi * V + j] = a[j];
+      smem[r * n2 + C + cgi * V + j] = b[j];
+    }
+  }
+  __syncthreads();
+  for (int i = tid; i < n2; i += blockDim.x) {
+    float s = 0.f;
+    for (int rr = 0; rr < rpi; ++rr) s += smem[rr * n2 + i];
+    partial[(size_t)blockIdx.x * n2 + i] = s;
+  }
+}
+
+// Returns true in exactly one block per launch: the one that arrives last.
+__device__ __forceinline__ bool take_last_ticket(unsigned* counter) {
+  __shared__ int s_last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = (atomicAdd(counter, 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (s_last) __threadfence();
+  return s_last != 0;
+}
+
+// Last block: tot[i] = sum_b partial[b][i] in fp64, left in smem as double[n2].
+__device__ __forceinline__ void fold_partials(double* tot, const float* __restrict__ partial, int nb, int n2) {
+  const int tid = threadIdx.x;
+  __syncthreads();
+  if (n2 >= (int)blockDim.x) {
+    for (int i = tid; i < n2; i += blockDim.x) {
+      double s = 0.0;
+#pragma unroll 8
+      for (int b = 0; b < nb; ++b) s += (double)__ldcg(partial + (size_t)b * n2 + i);
+      tot[i] = s;
+    }
+    __syncthreads();
+  } else {
+    const int rg = blockDim.x / n2, col = tid % n2, g = tid / n2;
+    double s = 0.0;
+    if (g < rg) {
+#pragma unroll 8
+      for (int b = g; b < nb; b += rg) s += (double)__ldcg(partial + (size_t)b * n2 + col);
+    }
+    // stage [rg][n2] doubles: rg*n2 <= blockDim.x = 512 doubles
+    double* stage = tot + n2;
+    if (g < rg) stage[g * n2 + col] = s;
+    __syncthreads();
+    if (tid < n2) {
+      double t = 0.0;
+      for (int gg = 0; gg < rg; ++gg) t += stage[gg * n2 + tid];
+      tot[tid] = t;
+    }
+    __syncthreads();
+  }
+}
+
+// Cross-rank sum of tot[0..n) (+ the count) through the peers' scratch slots; one block per rank.
+__device__ __forceinline__ void exchange_sum(const Comm& c, double* tot, int n, double* count) {
+  const int ch = 1;
+  for (int i = threadIdx.x; i <= n; i += blockDim.x) {
+    const float v = (i < n) ? (float)tot[i] : (float)*count;
+    for (int q = 0; q < c.world; ++q) scratch_addr(c.pad[q], ch, c.rank)[i] = v;
+  }
+  __threadfence_system();
+  block_barrier(c, ch, 0);
+  for (int i = threadIdx.x; i <= n; i += blockDim.x) {
+    double a = 0.0;
+    for (int p = 0; p < c.world; ++p) a += (double)*reinterpret_cast<volatile float*>(scratch_addr(c.pad[c.rank], ch, p) + i);
+    if (i < n) tot[i] = a; else *count = a;
+  }
+  block_barrier(c, ch, 0);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads) k_bn_fwd_stats(const T* __restrict__ x, long M, int C, float* __restrict__ partial,
+                                                          unsigned* counter, Comm comm, float* running_mean,
+                                                          float* running_var, float momentum, float eps,
+                                                          float* __restrict__ save_mean, float* __restrict__ save_invstd) {
+  constexpr int V = Vec<T>::N;
+  __shared__ __align__(16) float smem[kSmemFloats];
+  __shared__ double s_count;
+  const int tid = threadIdx.x, cg = C / V, rpi = kThreads / cg, cgi = tid % cg, r = tid / cg;
+  const long chunk = (M + gridDim.x - 1) / gridDim.x;
+  const long row0 = (long)blockIdx.x * chunk, row1 = min(M, row0 + chunk);
+  float s[V], q[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) s[j] = q[j] = 0.f;
+  if (r < rpi) {
+#pragma unroll 4
+    for (long row = row0 + r; row < row1; row += rpi) {
+      float f[V];
+      load_vec<T>(x + row * C + cgi * V, f);
+#pragma unroll
+      for (int j = 0; j < V; ++j) { s[j] += f[j]; q[j] = fmaf(f[j], f[j], q[j]); }
+    }
+  }
+  block_fold<V>(smem, s, q, C, cg, rpi, partial);
+  if (!take_last_ticket(counter)) return;
+
+  double* tot = reinterpret_cast<double*>(smem);
+  fold_partials(tot, partial, gridDim.x, 2 * C);
+  if (tid == 0) { s_count = (double)M; *counter = 0; }
+  __syncthreads();
+  if (comm.world > 1) exchange_sum(comm, tot, 2 * C, &s_count);
+  __syncthreads();
+  const double N = s_count;
+  for (int c = tid; c < C; c += blockDim.x) {
+    const double mean = tot[c] / N;
+    double var = tot[C + c] / N - mean * mean;
+    var = var > 0.0 ? var : 0.0;
+    save_mean[c] = (float)mean;
+    save_invstd[c] = (float)(1.0 / sqrt(var + (double)eps));
+    if (running_mean) {
+      const double unbiased = N > 1.0 ? var * N / (N - 1.0) : var;
+      running_mean[c] = (float)((1.0 - momentum) * running_mean[c] + momentum * mean);
+      running_var[c] = (float)((1.0 - momentum) * running_var[c] + momentum * unbiased);
+    }
+  }
+}
+
+// stat2 is invstd (training) or running_var (eval, eps applied here).
+template <typename T>
+__global__ void __launch_bounds__(kThreads) k_bn_fwd_apply(const T* __restrict__ x, const T* __restrict__ res, T* __restrict__ y,
+                                                          long nvec, int C, const float* __restrict__ mean,
+                                                          const float* __restrict__ stat2, const float* __restrict__ gamma,
+                                                          const float* __restrict__ beta, int relu, int eval, float eps) {
+  constexpr int V = Vec<T>::N;
+  extern __shared__ float sm[];
+  float* scale = sm;
+  float* shift = sm + C;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const float inv = eval ? rsqrtf(stat2[c] + eps) : stat2[c];
+    const float sc = gamma[c] * inv;
+    scale[c] = sc;
+    shift[c] = beta[c] - mean[c] * sc;
+  }
+  __syncthreads();
+  const int cg = C / V;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long)gridDim.x * blockDim.x) {
+    const int c0 = (int)(i % cg) * V;
+    float f[V];
+    load_vec<T>(x + i * V, f);
+#pragma unroll
+    for (int j = 0; j < V; ++j) f[j] = fmaf(f[j], scale[c0 + j], shift[c0 + j]);
+    if (res) {
+      float g[V];
+      load_vec<T>(res + i * V, g);
+#pragma unroll
+      for (int j = 0; j < V; ++j) f[j] += g[j];
+    }
+    if (relu) {
+#pragma unroll
+      for (int j = 0; j < V; ++j) f[j] = fmaxf(f[j], 0.f);
+    }
+    store_vec<T>(y + i * V, f);
+  }
+}
+
+// out_k: [2C] floats consumed by k_bn_bwd_apply: k1 = sum_dy / N, k2 = sum_dy_xmu * invstd^2 / N (N global)
+template <typename T>
+__global__ void __launch_bounds__(kThreads) k_bn_bwd_reduce(const T* __restrict__ dy, const T* __restrict__ y,
+                                                           const T* __restrict__ x, long M, int C,
+                                                           const float* __restrict__ mean, const float* __restrict__ invstd,
+                                                           int relu, float* __restrict__ partial, unsigned* counter, Comm comm,
+                                                           float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                                           float* __restrict__ out_k) {
+  constexpr int V = Vec<T>::N;
+  __shared__ __align__(16) float smem[kSmemFloats];
+  __shared__ double s_count;
+  const int tid = threadIdx.x, cg = C / V, rpi = kThreads / cg, cgi = tid % cg, r = tid / cg;
+  const long chunk = (M + gridDim.x - 1) / gridDim.x;
+  const long row0 = (long)blockIdx.x * chunk, row1 = min(M, row0 + chunk);
+  float s[V], q[V], mu[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) { s[j] = q[j] = 0.f; mu[j] = (r < rpi) ? mean[cgi * V + j] : 0.f; }
+  if (r < rpi) {
+#pragma unroll 2
+    for (long row = row0 + r; row < row1; row += rpi) {
+      const long o = row * C + cgi * V;
+      float g[V], xv[V];
+      load_vec<T>(dy + o, g);
+      load_vec<T>(x + o, xv);
+      if (relu) {
+        float yv[V];
+        load_vec<T>(y + o, yv);
+#pragma unroll
+        for (int j = 0; j < V; ++j) g[j] = yv[j] > 0.f ? g[j] : 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < V; ++j) { s[j] += g[j]; q[j] = fmaf(g[j], xv[j] - mu[j], q[j]); }
+    }
+  }
+  block_fold<V>(smem, s, q, C, cg, rpi, partial);
+  if (!take_last_ticket(counter)) return;
+
+  double* tot = reinterpret_cast<double*>(smem);
+  fold_partials(tot, partial, gridDim.x, 2 * C);
+  if (tid == 0) { s_count = (double)M; *counter = 0; }
+  __syncthreads();
+  for (int c = tid; c < C; c += blockDim.x) {   // parameter grads stay local: DDP averages them
+    dbeta[c] = (float)tot[c];
+    dgamma[c] = (float)(tot[C + c] * (double)invstd[c]);
+  }
+  __syncthreads();
+  if (comm.world > 1) exchange_sum(comm, tot, 2 * C, &s_count);
+  __syncthreads();
+  const double N = s_count;
+  for (int c = tid; c < C; c += blockDim.x) {
+    const double is = (double)invstd[c];
+    out_k[c] = (float)(tot[c] / N);
+    out_k[C + c] = (float)(tot[C + c] * is * is / N);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads) k_bn_bwd_apply(const T* __restrict__ dy, const T* __restrict__ y,
+                                                          const T* __restrict__ x, T* __restrict__ dx, T* __restrict__ dres,
+                                                          long nvec, int C, const float* __restrict__ mean,
+                                                          const float* __restrict__ invstd, const float* __restrict__ gamma,
+                                                          const float* __restrict__ k, int relu) {
+  constexpr int V = Vec<T>::N;
+  extern __shared__ float sm[];
+  float* a = sm;            // invstd*gamma
+  float* k1 = sm + C;
+  float* k2 = sm + 2 * C;
+  float* mu = sm + 3 * C;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    a[c] = invstd[c] * gamma[c];
+    k1[c] = k[c];
+    k2[c] = k[C + c];
+    mu[c] = mean[c];
+  }
+  __syncthreads();
+  const int cg = C / V;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long)gridDim.x * blockDim.x) {
+    const int c0 = (int)(i % cg) * V;
+    float g[V], xv[V];
+    load_vec<T>(dy + i * V, g);
+    load_vec<T>(x + i * V, xv);
+    if (relu) {
+      float yv[V];
+      load_vec<T>(y + i * V, yv);
+#pragma unroll
+      for (int j = 0; j < V; ++j) g[j] = yv[j] > 0.f ? g[j] : 0.f;
+    }
+    if (dres) store_vec<T>(dres + i * V, g);
+#pragma unroll
+    for (int j = 0; j < V; ++j) g[j] = (g[j] - k1[c0 + j] - (xv[j] - mu[c0 + j]) * k2[c0 + j]) * a[c0 + j];
+    store_vec<T>(dx + i * V, g);
+  }
+}
+
+template <typename T> bool shape_ok(int C) {
+  const int V = Vec<T>::N;
+  if (C % V) return false;
+  const int cg = C / V;
+  return cg >= 1 && cg <= kThreads && (cg & (cg - 1)) == 0 && 2 * C <= PDT_SCRATCH_FLOATS - 1 && 2 * C <= kSmemFloats / 2 - kThreads;
+}
+
+int stats_blocks(long M, int C, int V) {
+  const int rpi = kThreads / (C / V);
+  long nb = M / ((long)rpi * 8);             // at least 8 rows per thread
+  if (nb < 1) nb = 1;
+  if (nb > PDT_BN_MAX_BLOCKS) nb = PDT_BN_MAX_BLOCKS;
+  return (int)nb;
+}
+
+int apply_blocks(long nvec) {
+  long nb = (nvec + kThreads * 4 - 1) / (kThreads * 4);
+  if (nb < 1) nb = 1;
+  if (nb > 148 * 8) nb = 148 * 8;
+  return (int)nb;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t pdt_bn_scratch_bytes(int C) { return (size_t)PDT_BN_MAX_BLOCKS * 2 * C * sizeof(float) + 256; }
+
+#define BN_DISPATCH(dtype, ...)                                                      \
+  if (dtype == PDT_BF16) { using T = __nv_bfloat16; __VA_ARGS__; }                   \
+  else if (dtype == PDT_FP16) { using T = __half; __VA_ARGS__; }                     \
+  else if (dtype == PDT_FP32) { using T = float; __VA_ARGS__; }                      \
+  else return PDT_E_UNSUPPORTED;
+
+int pdt_bn_fwd_stats(const void* x, long M, int C, int dtype, void* scratch, const PdtCommDesc* comm,
+                     float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
+                     float* save_invstd, cudaStream_t stream) {
+  unsigned* counter = reinterpret_cast<unsigned*>(scratch);
+  float* partial = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + 256);
+  BN_DISPATCH(dtype, {
+    if (!shape_ok<T>(C)) return PDT_E_UNSUPPORTED;
+    k_bn_fwd_stats<T><<<stats_blocks(M, C, Vec<T>::N), kThreads, 0, stream>>>(
+        reinterpret_cast<const T*>(x), M, C, partial, counter, make_comm(comm), running_mean, running_var, momentum, eps,
+        save_mean, save_invstd);
+  });
+  return (int)cudaGetLastError();
+}
+
+int pdt_bn_fwd_apply(const void* x, const void* res, void* y, long M, int C, int dtype, const float* mean,
+                     const float* stat2, const float* gamma, const float* beta, int relu, int eval, float eps,
+                     cudaStream_t stream) {
+  BN_DISPATCH(dtype, {
+    if (C % Vec<T>::N) return PDT_E_UNSUPPORTED;
+    const long nvec = M * C / Vec<T>::N;
+    k_bn_fwd_apply<T><<<apply_blocks(nvec), kThreads, 2 * C * sizeof(float), stream>>>(
+        reinterpret_cast<const T*>(x), reinterpret_cast<const T*>(res), reinterpret_cast<T*>(y), nvec, C, mean, stat2,
+        gamma, beta, relu, eval, eps);
+  });
+  return (int)cudaGetLastError();
+}
+
+int pdt_bn_bwd_reduce(const void* dy, const void* y, const void* x, long M, int C, int dtype, const float* mean,
+                      const float* invstd, int relu, void* scratch, const PdtCommDesc* comm, float* dgamma,
+                      float* dbeta, float* out_k, cudaStream_t stream) {
+  unsigned* counter = reinterpret_cast<unsigned*>(scratch);
+  float* partial = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + 256);
+  BN_DISPATCH(dtype, {
+    if (!shape_ok<T>(C)) return PDT_E_UNSUPPORTED;
+    k_bn_bwd_reduce<T><<<stats_blocks(M, C, Vec<T>::N), kThreads, 0, stream>>>(
+        reinterpret_cast<const T*>(dy), reinterpret_cast<const T*>(y), reinterpret_cast<const T*>(x), M, C, mean, invstd,
+        relu, partial, counter, make_comm(comm), dgamma, dbeta, out_k);
+  });
+  return (int)cudaGetLastError();
+}
+
+int pdt_bn_bwd_apply(const void* dy, const void* y, const void* x, void* dx, void* dres, long M, int C, int dtype,
+                     const float* mean, const float* invstd, const float* gamma, const float* k, int relu,
+                     cudaStream_t stream) {
+  BN_DISPATCH(dtype, {
+    if (C % Vec<T>::N) return PDT_E_UNSUPPORTED;
+    const long nvec = M * C / Vec<T>::N;
+    k_bn_bwd_apply<T><<<apply_blocks(nvec), kThreads, 4 * C * sizeof(float), stream>>>(
+        reinterpret_cast<const T*>(dy), reinterpret_cast<const T*>(y), reinterpret_cast<const T*>(x),
+        reinterpret_cast<T*>(dx), reinterpret_cast<T*>(dres), nvec, C, mean, invstd, gamma, k, relu);
+  });
+  return (int)cudaGetLastError();
+}
+
+}  // extern "C"

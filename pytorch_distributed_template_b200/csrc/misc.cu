@@ -1,0 +1,355 @@
+// Loss, pooling and layout/cast kernels on NHWC activations (§2.4(a)).
+//
+//   k_ce_fwd        CrossEntropyLoss(mean) + unit dlogits + top-1 hit fraction in ONE pass
+//                   over the logits (replaces _log_softmax + nll_loss_forward + their
+//                   backward pair + topk/eq/sum of utils.accuracy; reference call sites
+//                   distributed.py:247,250 and utils.py:105-111).
+//   k_scale_cast    dlogits = unit_dlogits * grad_output (a device scalar, e.g. the AMP
+//                   loss scale) cast to the activation dtype.
+//   k_maxpool_*     MaxPool2d(3,2,1) forward (saves the arg-max tap as int8) / backward
+//                   (gather form, no atomics).
+//   k_avgpool_*     AdaptiveAvgPool2d(1) forward / backward.
+//   k_nchw_to_nhwc  fp32 NCHW image batch -> low-precision NHWC with the channel dimension
+//                   zero-padded (the autocast input cast + channels_last conversion).
+#include "common.cuh"
+#include "../../include/pdt_b200.h"
+
+namespace {
+
+using namespace pdt;
+
+// ---- fused cross entropy ---------------------------------------------------------------
+// One block (128 threads) per row.  row_out[b] = {loss_b, hit_b}; the block that takes the
+// last ticket folds the rows in index order (deterministic) into out = {mean loss, hit fraction}.
+template <typename T>
+__global__ void __launch_bounds__(128) k_ce_fwd(const T* __restrict__ logits, const long long* __restrict__ target, int B, int K,
+                                               float* __restrict__ dlogits_unit, float2* __restrict__ row_out,
+                                               unsigned* counter, float* __restrict__ out) {
+  __shared__ float s_red[4];
+  __shared__ int s_idx[4];
+  __shared__ int s_last;
+  const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const T* row = logits + (size_t)b * K;
+  const int tgt = (int)target[b];
+
+  float mx = -INFINITY;
+  int arg = 0x7fffffff;
+  for (int i = tid; i < K; i += 128) {
+    const float v = Cvt<T>::to_f(row[i]);
+    if (v > mx) { mx = v; arg = i; }
+  }
+  // arg-max with lowest-index tie break
+  for (int o = 16; o > 0; o >>= 1) {
+    const float om = __shfl_xor_sync(0xffffffffu, mx, o);
+    const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+    if (om > mx || (om == mx && oa < arg)) { mx = om; arg = oa; }
+  }
+  if (lane == 0) { s_red[wid] = mx; s_idx[wid] = arg; }
+  __syncthreads();
+  mx = s_red[0]; arg = s_idx[0];
+  for (int w = 1; w < 4; ++w)
+    if (s_red[w] > mx || (s_red[w] == mx && s_idx[w] < arg)) { mx = s_red[w]; arg = s_idx[w]; }
+  __syncthreads();
+
+  float se = 0.f;
+  for (int i = tid; i < K; i += 128) se += __expf(Cvt<T>::to_f(row[i]) - mx);
+  se = warp_sum(se);
+  if (lane == 0) s_red[wid] = se;
+  __syncthreads();
+  se = s_red[0] + s_red[1] + s_red[2] + s_red[3];
+  const float lse = mx + __logf(se);
+  const float inv = 1.f / se, invB = 1.f / (float)B;
+  float* drow = dlogits_unit + (size_t)b * K;
+  for (int i = tid; i < K; i += 128) {
+    const float p = __expf(Cvt<T>::to_f(row[i]) - mx) * inv;
+    drow[i] = (p - (i == tgt ? 1.f : 0.f)) * invB;
+  }
+  if (tid == 0) row_out[b] = make_float2(lse - Cvt<T>::to_f(row[tgt]), arg == tgt ? 1.f : 0.f);
+
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) s_last = (atomicAdd(counter, 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  // fixed-order fold: thread t sums rows t, t+128, ... then a fixed tree
+  double l = 0.0, h = 0.0;
+  for (int i = tid; i < B; i += 128) {
+    const float2 v = __ldcg(row_out + i);
+    l += v.x; h += v.y;
+  }
+  __shared__ double s_l[128], s_h[128];
+  s_l[tid] = l; s_h[tid] = h;
+  __syncthreads();
+  for (int o = 64; o > 0; o >>= 1) {
+    if (tid < o) { s_l[tid] += s_l[tid + o]; s_h[tid] += s_h[tid + o]; }
+    __syncthreads();
+  }
+  if (tid == 0) {
+    out[0] = (float)(s_l[0] / B);
+    out[1] = (float)(s_h[0] / B);
+    *counter = 0;
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) k_scale_cast(const float* __restrict__ in, const float* __restrict__ scale, T* __restrict__ out,
+                                                   size_t n) {
+  const float s = *scale;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    out[i] = Cvt<T>::from_f(in[i] * s);
+}
+
+// ---- pooling ---------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) k_maxpool_fwd(const T* __restrict__ x, T* __restrict__ y, int8_t* __restrict__ idx, int N, int H,
+                                                    int W, int C, int Ho, int Wo, int ks, int st, int pd) {
+  const int cg = C / 8;
+  const long total = (long)N * Ho * Wo * cg;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int c8 = (int)(i % cg);
+    long r = i / cg;
+    const int wo = (int)(r % Wo); r /= Wo;
+    const int ho = (int)(r % Ho);
+    const int n = (int)(r / Ho);
+    float best[8];
+    int bi[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { best[j] = -INFINITY; bi[j] = 0; }
+    for (int kh = 0; kh < ks; ++kh) {
+      const int hi = ho * st - pd + kh;
+      if (hi < 0 || hi >= H) continue;
+      for (int kw = 0; kw < ks; ++kw) {
+        const int wi = wo * st - pd + kw;
+        if (wi < 0 || wi >= W) continue;
+        float f[8];
+        unpack8<T>(*reinterpret_cast<const uint4*>(x + (((long)n * H + hi) * W + wi) * C + c8 * 8), f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (f[j] > best[j]) { best[j] = f[j]; bi[j] = kh * ks + kw; }
+      }
+    }
+    const long o = (((long)n * Ho + ho) * Wo + wo) * C + c8 * 8;
+    *reinterpret_cast<uint4*>(y + o) = pack8<T>(best);
+    uint2 pk;
+    pk.x = (bi[0] & 0xff) | ((bi[1] & 0xff) << 8) | ((bi[2] & 0xff) << 16) | ((bi[3] & 0xff) << 24);
+    pk.y = (bi[4] & 0xff) | ((bi[5] & 0xff) << 8) | ((bi[6] & 0xff) << 16) | ((bi[7] & 0xff) << 24);
+    *reinterpret_cast<uint2*>(idx + o) = pk;
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) k_maxpool_bwd(const T* __restrict__ dy, const int8_t* __restrict__ idx, T* __restrict__ dx, int N,
+                                                    int H, int W, int C, int Ho, int Wo, int ks, int st, int pd) {
+  const int cg = C / 8;
+  const long total = (long)N * H * W * cg;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int c8 = (int)(i % cg);
+    long r = i / cg;
+    const int wi = (int)(r % W); r /= W;
+    const int hi = (int)(r % H);
+    const int n = (int)(r / H);
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    // outputs (ho, wo) whose window covers (hi, wi): ho*st - pd + kh == hi
+    for (int kh = 0; kh < ks; ++kh) {
+      const int t = hi + pd - kh;
+      if (t < 0 || t % st) continue;
+      const int ho = t / st;
+      if (ho >= Ho) continue;
+      for (int kw = 0; kw < ks; ++kw) {
+        const int u = wi + pd - kw;
+        if (u < 0 || u % st) continue;
+        const int wo = u / st;
+        if (wo >= Wo) continue;
+        const long o = (((long)n * Ho + ho) * Wo + wo) * C + c8 * 8;
+        const uint2 pk = *reinterpret_cast<const uint2*>(idx + o);
+        float g[8];
+        unpack8<T>(*reinterpret_cast<const uint4*>(dy + o), g);
+        const int tap = kh * ks + kw;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int sel = ((j < 4 ? pk.x : pk.y) >> ((j & 3) * 8)) & 0xff;
+          if (sel == tap) acc[j] += g[j];
+        }
+      }
+    }
+    *reinterpret_cast<uint4*>(dx + (((long)n * H + hi) * W + wi) * C + c8 * 8) = pack8<T>(acc);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) k_avgpool_fwd(const T* __restrict__ x, T* __restrict__ y, int N, int HW, int C) {
+  const int cg = C / 8;
+  const long total = (long)N * cg;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int c8 = (int)(i % cg);
+    const long n = i / cg;
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    for (int p = 0; p < HW; ++p) {
+      float f[8];
+      unpack8<T>(*reinterpret_cast<const uint4*>(x + (n * HW + p) * C + c8 * 8), f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += f[j];
+    }
+    const float inv = 1.f / (float)HW;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] *= inv;
+    *reinterpret_cast<uint4*>(y + n * C + c8 * 8) = pack8<T>(acc);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) k_avgpool_bwd(const T* __restrict__ dy, T* __restrict__ dx, int N, int HW, int C) {
+  const int cg = C / 8;
+  const long total = (long)N * HW * cg;
+  const float inv = 1.f / (float)HW;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int c8 = (int)(i % cg);
+    const long n = i / cg / HW;
+    float f[8];
+    unpack8<T>(*reinterpret_cast<const uint4*>(dy + n * C + c8 * 8), f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] *= inv;
+    *reinterpret_cast<uint4*>(dx + i * 8) = pack8<T>(f);
+  }
+}
+
+// x: [N][Cin][H][W] fp32 -> y: [N][H][W][Cpad] T, channels >= Cin zero.  Cpad in {4, 8}.
+template <typename T, int CP>
+__global__ void __launch_bounds__(256) k_nchw_to_nhwc(const float* __restrict__ x, T* __restrict__ y, int N, int Cin, long HW) {
+  const long total = (long)N * HW;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const long n = i / HW, p = i % HW;
+    float f[CP];
+#pragma unroll
+    for (int c = 0; c < CP; ++c) f[c] = (c < Cin) ? x[(n * Cin + c) * HW + p] : 0.f;
+    if constexpr (CP == 8) {
+      float g[8];
+#pragma unroll
+      for (int c = 0; c < 8; ++c) g[c] = f[c];
+      *reinterpret_cast<uint4*>(y + i * 8) = pack8<T>(g);
+    } else {
+      uint2 u;
+      u.x = Cvt<T>::pack2(f[0], f[1]);
+      u.y = Cvt<T>::pack2(f[2], f[3]);
+      *reinterpret_cast<uint2*>(y + i * 4) = u;
+    }
+  }
+}
+
+int grid_for(long total, int threads) {
+  long nb = (total + threads - 1) / threads;
+  if (nb < 1) nb = 1;
+  if (nb > 148 * 16) nb = 148 * 16;
+  return (int)nb;
+}
+
+}  // namespace
+
+extern "C" {
+
+#define LP_DISPATCH(dtype, ...)                                      \
+  if (dtype == PDT_BF16) { using T = __nv_bfloat16; __VA_ARGS__; }   \
+  else if (dtype == PDT_FP16) { using T = __half; __VA_ARGS__; }     \
+  else return PDT_E_UNSUPPORTED;
+
+size_t pdt_ce_scratch_bytes(int B) { return 256 + (size_t)B * sizeof(float2); }
+
+int pdt_ce_fwd(const void* logits, int dtype, const long long* target, int B, int K, float* dlogits_unit, void* scratch,
+               float* out, cudaStream_t stream) {
+  unsigned* counter = reinterpret_cast<unsigned*>(scratch);
+  float2* rows = reinterpret_cast<float2*>(reinterpret_cast<char*>(scratch) + 256);
+  if (dtype == PDT_FP32)
+    k_ce_fwd<float><<<B, 128, 0, stream>>>(reinterpret_cast<const float*>(logits), target, B, K, dlogits_unit, rows, counter, out);
+  else
+    LP_DISPATCH(dtype, k_ce_fwd<T><<<B, 128, 0, stream>>>(reinterpret_cast<const T*>(logits), target, B, K, dlogits_unit, rows, counter, out));
+  return (int)cudaGetLastError();
+}
+
+int pdt_scale_cast(const float* in, const float* scale, void* out, int dtype, size_t n, cudaStream_t stream) {
+  const int nb = grid_for((long)n, 256 * 4);
+  if (dtype == PDT_FP32)
+    k_scale_cast<float><<<nb, 256, 0, stream>>>(in, scale, reinterpret_cast<float*>(out), n);
+  else
+    LP_DISPATCH(dtype, k_scale_cast<T><<<nb, 256, 0, stream>>>(in, scale, reinterpret_cast<T*>(out), n));
+  return (int)cudaGetLastError();
+}
+
+int pdt_maxpool_fwd(const void* x, void* y, int8_t* idx, int dtype, int N, int H, int W, int C, int ks, int st, int pd,
+                    cudaStream_t stream) {
+  if (C % 8 || ks * ks > 127) return PDT_E_UNSUPPORTED;
+  const int Ho = (H + 2 * pd - ks) / st + 1, Wo = (W + 2 * pd - ks) / st + 1;
+  LP_DISPATCH(dtype, k_maxpool_fwd<T><<<grid_for((long)N * Ho * Wo * (C / 8), 256), 256, 0, stream>>>(
+      reinterpret_cast<const T*>(x), reinterpret_cast<T*>(y), idx, N, H, W, C, Ho, Wo, ks, st, pd));
+  return (int)cudaGetLastError();
+}
+
+int pdt_maxpool_bwd(const void* dy, const int8_t* idx, void* dx, int dtype, int N, int H, int W, int C, int ks, int st,
+                    int pd, cudaStream_t stream) {
+  if (C % 8) return PDT_E_UNSUPPORTED;
+  const int Ho = (H + 2 * pd - ks) / st + 1, Wo = (W + 2 * pd - ks) / st + 1;
+  LP_DISPATCH(dtype, k_maxpool_bwd<T><<<grid_for((long)N * H * W * (C / 8), 256), 256, 0, stream>>>(
+      reinterpret_cast<const T*>(dy), idx, reinterpret_cast<T*>(dx), N, H, W, C, Ho, Wo, ks, st, pd));
+  return (int)cudaGetLastError();
+}
+
+int pdt_avgpool_fwd(const void* x, void* y, int dtype, int N, int HW, int C, cudaStream_t stream) {
+  if (C % 8) return PDT_E_UNSUPPORTED;
+  LP_DISPATCH(dtype, k_avgpool_fwd<T><<<grid_for((long)N * (C / 8), 256), 256, 0, stream>>>(
+      reinterpret_cast<const T*>(x), reinterpret_cast<T*>(y), N, HW, C));
+  return (int)cudaGetLastError();
+}
+
+int pdt_avgpool_bwd(const void* dy, void* dx, int dtype, int N, int HW, int C, cudaStream_t stream) {
+  if (C % 8) return PDT_E_UNSUPPORTED;
+  LP_DISPATCH(dtype, k_avgpool_bwd<T><<<grid_for((long)N * HW * (C / 8), 256), 256, 0, stream>>>(
+      reinterpret_cast<const T*>(dy), reinterpret_cast<T*>(dx), N, HW, C));
+  return (int)cudaGetLastError();
+}
+
+int pdt_nchw_to_nhwc(const float* x, void* y, int dtype, int N, int Cin, int H, int W, int Cpad, cudaStream_t stream) {
+  if (Cin > Cpad || (Cpad != 4 && Cpad != 8)) return PDT_E_UNSUPPORTED;
+  const long HW = (long)H * W;
+  const int nb = grid_for((long)N * HW, 256);
+  if (Cpad == 8) {
+    LP_DISPATCH(dtype, k_nchw_to_nhwc<T, 8><<<nb, 256, 0, stream>>>(x, reinterpret_cast<T*>(y), N, Cin, HW));
+  } else {
+    LP_DISPATCH(dtype, k_nchw_to_nhwc<T, 4><<<nb, 256, 0, stream>>>(x, reinterpret_cast<T*>(y), N, Cin, HW));
+  }
+  return (int)cudaGetLastError();
+}
+
+}  // extern "C"
+
+// ---- peer copy (DataParallel scatter / gather / buffer broadcast) ------------------------------
+// Runs on the DESTINATION device and pulls from a peer-mapped source pointer over NVLink
+// (replaces torch.cuda.comm.scatter / gather / broadcast_coalesced, torch/nn/parallel/comm.py).
+namespace {
+__global__ void __launch_bounds__(512) k_peer_copy(const uint4* __restrict__ src, uint4* __restrict__ dst, size_t n16,
+                                                  const unsigned char* __restrict__ src_tail, unsigned char* __restrict__ dst_tail,
+                                                  int tail) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (size_t)gridDim.x * blockDim.x) {
+    uint4 v;
+    asm volatile("ld.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(src + i) : "memory");
+    dst[i] = v;
+  }
+  if (blockIdx.x == 0 && (int)threadIdx.x < tail) dst_tail[threadIdx.x] = src_tail[threadIdx.x];
+}
+}  // namespace
+
+extern "C" int pdt_peer_copy(const void* src, void* dst, size_t nbytes, cudaStream_t stream) {
+  if ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) return PDT_E_UNSUPPORTED;
+  const size_t n16 = nbytes / 16;
+  const int tail = (int)(nbytes % 16);
+  long nb = (long)((n16 + 512 * 4 - 1) / (512 * 4));
+  if (nb < 1) nb = 1;
+  if (nb > 148 * 4) nb = 148 * 4;
+  k_peer_copy<<<(int)nb, 512, 0, stream>>>(reinterpret_cast<const uint4*>(src), reinterpret_cast<uint4*>(dst), n16,
+                                           reinterpret_cast<const unsigned char*>(src) + n16 * 16,
+                                           reinterpret_cast<unsigned char*>(dst) + n16 * 16, tail);
+  return (int)cudaGetLastError();
+}

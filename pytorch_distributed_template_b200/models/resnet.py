@@ -1,0 +1,124 @@
+"""ResNet family with torchvision's parameter names and initialisation, built from fused ops.
+
+``state_dict()`` keys, shapes and the random init match
+``torchvision.models.resnet{18,34,50,101,152}`` (what the reference trains,
+/root/reference/distributed.py:134-137), so checkpoints interchange in both
+directions.  The forward differs: activations are channels_last, every
+conv -> BN -> (+identity) -> ReLU chain is ``ops.conv2d`` followed by ONE fused
+``ops.bn_act`` (statistics + normalise + residual + ReLU), pooling and the
+classifier use the package's kernels, and under ``amp.autocast`` activations
+are born in bf16/fp16 from shadow weights.
+"""
+import torch
+import torch.nn as nn
+
+from .. import ops
+from ..parallel.syncbn import fused_bn
+
+
+def conv3x3(cin, cout, stride=1):
+    return nn.Conv2d(cin, cout, 3, stride, 1, bias=False)
+
+
+def conv1x1(cin, cout, stride=1):
+    return nn.Conv2d(cin, cout, 1, stride, 0, bias=False)
+
+
+class BasicBlock(nn.Module):
+    expansion = 1
+
+    def __init__(self, inplanes, planes, stride=1, downsample=None):
+        super().__init__()
+        self.conv1 = conv3x3(inplanes, planes, stride)
+        self.bn1 = nn.BatchNorm2d(planes)
+        self.relu = nn.ReLU(inplace=True)
+        self.conv2 = conv3x3(planes, planes)
+        self.bn2 = nn.BatchNorm2d(planes)
+        self.downsample = downsample
+        self.stride = stride
+
+    def forward(self, x):
+        identity = x
+        out = fused_bn(self.bn1, ops.conv2d(x, self.conv1), relu=True)
+        if self.downsample is not None:
+            identity = fused_bn(self.downsample[1], ops.conv2d(x, self.downsample[0]))
+        return fused_bn(self.bn2, ops.conv2d(out, self.conv2), residual=identity, relu=True)
+
+
+class Bottleneck(nn.Module):
+    expansion = 4
+
+    def __init__(self, inplanes, planes, stride=1, downsample=None):
+        super().__init__()
+        self.conv1 = conv1x1(inplanes, planes)
+        self.bn1 = nn.BatchNorm2d(planes)
+        self.conv2 = conv3x3(planes, planes, stride)
+        self.bn2 = nn.BatchNorm2d(planes)
+        self.conv3 = conv1x1(planes, planes * self.expansion)
+        self.bn3 = nn.BatchNorm2d(planes * self.expansion)
+        self.relu = nn.ReLU(inplace=True)
+        self.downsample = downsample
+        self.stride = stride
+
+    def forward(self, x):
+        identity = x
+        out = fused_bn(self.bn1, ops.conv2d(x, self.conv1), relu=True)
+        out = fused_bn(self.bn2, ops.conv2d(out, self.conv2), relu=True)
+        if self.downsample is not None:
+            identity = fused_bn(self.downsample[1], ops.conv2d(x, self.downsample[0]))
+        return fused_bn(self.bn3, ops.conv2d(out, self.conv3), residual=identity, relu=True)
+
+
+class ResNet(nn.Module):
+    def __init__(self, block, layers, num_classes=1000):
+        super().__init__()
+        self.inplanes = 64
+        self.conv1 = nn.Conv2d(3, 64, 7, 2, 3, bias=False)
+        self.bn1 = nn.BatchNorm2d(64)
+        self.relu = nn.ReLU(inplace=True)
+        self.maxpool = nn.MaxPool2d(3, 2, 1)
+        self.layer1 = self._make_layer(block, 64, layers[0])
+        self.layer2 = self._make_layer(block, 128, layers[1], stride=2)
+        self.layer3 = self._make_layer(block, 256, layers[2], stride=2)
+        self.layer4 = self._make_layer(block, 512, layers[3], stride=2)
+        self.avgpool = nn.AdaptiveAvgPool2d((1, 1))
+        self.fc = nn.Linear(512 * block.expansion, num_classes)
+        for m in self.modules():   # torchvision/models/resnet.py init
+            if isinstance(m, nn.Conv2d):
+                nn.init.kaiming_normal_(m.weight, mode="fan_out", nonlinearity="relu")
+            elif isinstance(m, nn.BatchNorm2d):
+                nn.init.constant_(m.weight, 1)
+                nn.init.constant_(m.bias, 0)
+
+    def _make_layer(self, block, planes, blocks, stride=1):
+        downsample = None
+        if stride != 1 or self.inplanes != planes * block.expansion:
+            downsample = nn.Sequential(conv1x1(self.inplanes, planes * block.expansion, stride),
+                                       nn.BatchNorm2d(planes * block.expansion))
+        layers = [block(self.inplanes, planes, stride, downsample)]
+        self.inplanes = planes * block.expansion
+        layers += [block(self.inplanes, planes) for _ in range(1, blocks)]
+        return nn.Sequential(*layers)
+
+    def forward(self, x):
+        if x.dim() == 4 and not x.is_contiguous(memory_format=torch.channels_last):
+            x = x.contiguous(memory_format=torch.channels_last)
+        x = fused_bn(self.bn1, ops.conv2d(x, self.conv1), relu=True)
+        x = ops.max_pool2d(x, 3, 2, 1)
+        x = self.layer4(self.layer3(self.layer2(self.layer1(x))))
+        x = ops.global_avg_pool(x)
+        return ops.linear(x, self.fc)
+
+
+_CFG = {"resnet18": (BasicBlock, [2, 2, 2, 2]), "resnet34": (BasicBlock, [3, 4, 6, 3]),
+        "resnet50": (Bottleneck, [3, 4, 6, 3]), "resnet101": (Bottleneck, [3, 4, 23, 3]),
+        "resnet152": (Bottleneck, [3, 8, 36, 3])}
+
+
+def native_archs():
+    return sorted(_CFG)
+
+
+def build_resnet(arch, num_classes=1000):
+    block, layers = _CFG[arch]
+    return ResNet(block, layers, num_classes)

@@ -1,0 +1,8 @@
+"""Functional ops: autograd.Functions over the sm_100a kernels, with torch oracles."""
+from .bn import bn_act
+from .conv import conv2d, linear
+from .loss import CrossEntropyLoss, cross_entropy_with_accuracy
+from .pool import global_avg_pool, max_pool2d
+
+__all__ = ["bn_act", "conv2d", "linear", "CrossEntropyLoss", "cross_entropy_with_accuracy",
+           "global_avg_pool", "max_pool2d"]

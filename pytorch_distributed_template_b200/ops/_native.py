@@ -1,0 +1,146 @@
+"""ctypes binding of ``lib/libpdt_b200.so`` (C ABI in ``include/pdt_b200.h``).
+
+The library is plain CUDA with no torch dependency; tensors cross the boundary
+as raw device pointers plus the current torch stream.  On a machine with a GPU
+a missing library is an error, not a reason to fall back silently: call
+``require()`` from every native code path.
+"""
+import ctypes
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libpdt_b200.so")
+
+MAX_RANKS = 8
+BF16, FP16, FP32 = 0, 1, 2
+_DTYPE_CODE = {torch.bfloat16: BF16, torch.float16: FP16, torch.float32: FP32}
+
+_lib = None
+_load_error = None
+launch_count = 0   # kernels launched through this binding (bench.py reports it)
+
+
+class Peers(ctypes.Structure):
+    _fields_ = [("p", ctypes.c_void_p * MAX_RANKS)]
+
+
+class CommDesc(ctypes.Structure):
+    _fields_ = [("rank", ctypes.c_int), ("world", ctypes.c_int), ("pad", ctypes.c_void_p * MAX_RANKS)]
+
+
+def dtype_code(dtype):
+    return _DTYPE_CODE[dtype]
+
+
+def make_peers(ptrs):
+    s = Peers()
+    for i in range(MAX_RANKS):
+        s.p[i] = int(ptrs[i]) if i < len(ptrs) and ptrs[i] else None
+    return s
+
+
+def make_comm(rank, world, pad_ptrs):
+    d = CommDesc()
+    d.rank, d.world = rank, world
+    for i in range(MAX_RANKS):
+        d.pad[i] = int(pad_ptrs[i]) if i < len(pad_ptrs) and pad_ptrs[i] else None
+    return d
+
+
+_vp, _i, _l, _f, _sz = ctypes.c_void_p, ctypes.c_int, ctypes.c_long, ctypes.c_float, ctypes.c_size_t
+_PC, _PP = ctypes.POINTER(CommDesc), ctypes.POINTER(Peers)
+
+_SIGNATURES = {
+    "pdt_comm_pad_bytes": ([], _sz),
+    "pdt_reduce_scatter_f32": ([_PC, _PP, _sz, _sz, _vp, _i, _i, _vp], _i),
+    "pdt_sgd_allgather": ([_PC, _PP, _PP, _PP, _i, _vp, _sz, _sz, _vp, _vp, _i, _i, _vp], _i),
+    "pdt_allreduce_f32": ([_PC, _PP, _sz, _sz, _f, _i, _vp], _i),
+    "pdt_allreduce_small_f32": ([_PC, _vp, _vp, _i, _f, _i, _vp], _i),
+    "pdt_bcast_pull": ([_PC, _PP, _sz, _sz, _i, _i, _i, _vp], _i),
+    "pdt_barrier": ([_PC, _i, _vp], _i),
+    "pdt_scale_update": ([_vp, _f, _f, _i, _vp], _i),
+    "pdt_sgd_flat": ([_vp, _vp, _vp, _vp, _i, _sz, _vp, _vp, _vp], _i),
+    "pdt_bn_scratch_bytes": ([_i], _sz),
+    "pdt_bn_fwd_stats": ([_vp, _l, _i, _i, _vp, _PC, _vp, _vp, _f, _f, _vp, _vp, _vp], _i),
+    "pdt_bn_fwd_apply": ([_vp, _vp, _vp, _l, _i, _i, _vp, _vp, _vp, _vp, _i, _i, _f, _vp], _i),
+    "pdt_bn_bwd_reduce": ([_vp, _vp, _vp, _l, _i, _i, _vp, _vp, _i, _vp, _PC, _vp, _vp, _vp, _vp], _i),
+    "pdt_bn_bwd_apply": ([_vp, _vp, _vp, _vp, _vp, _l, _i, _i, _vp, _vp, _vp, _vp, _i, _vp], _i),
+    "pdt_ce_scratch_bytes": ([_i], _sz),
+    "pdt_ce_fwd": ([_vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp], _i),
+    "pdt_scale_cast": ([_vp, _vp, _vp, _i, _sz, _vp], _i),
+    "pdt_maxpool_fwd": ([_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp], _i),
+    "pdt_maxpool_bwd": ([_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp], _i),
+    "pdt_avgpool_fwd": ([_vp, _vp, _i, _i, _i, _i, _vp], _i),
+    "pdt_avgpool_bwd": ([_vp, _vp, _i, _i, _i, _i, _vp], _i),
+    "pdt_peer_copy": ([_vp, _vp, _sz, _vp], _i),
+    "pdt_nchw_to_nhwc": ([_vp, _vp, _i, _i, _i, _i, _i, _i, _vp], _i),
+}
+
+
+def _load():
+    global _lib, _load_error
+    if _lib is not None or _load_error is not None:
+        return _lib
+    try:
+        lib = ctypes.CDLL(LIB_PATH)
+        for name, (argtypes, restype) in _SIGNATURES.items():
+            fn = getattr(lib, name, None)
+            if fn is None:
+                continue
+            fn.argtypes, fn.restype = argtypes, restype
+        _lib = lib
+    except OSError as e:  # not built
+        _load_error = e
+    return _lib
+
+
+def register(name, argtypes, restype=_i):
+    """Used by the other ops modules to add signatures (conv/gemm)."""
+    _SIGNATURES[name] = (argtypes, restype)
+    if _lib is not None and hasattr(_lib, name):
+        fn = getattr(_lib, name)
+        fn.argtypes, fn.restype = argtypes, restype
+
+
+def available():
+    """True when the library is built AND a CUDA device is usable."""
+    return torch.cuda.is_available() and _load() is not None
+
+
+def require():
+    lib = _load()
+    if lib is None:
+        raise RuntimeError(
+            "libpdt_b200.so is not built ({}); run `python -m pytorch_distributed_template_b200.build` "
+            "or `python -c 'import __graft_entry__ as g; g.build()'`".format(_load_error))
+    return lib
+
+
+def lib():
+    return require()
+
+
+def stream_ptr(device=None):
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def check(code, what):
+    global launch_count
+    launch_count += 1
+    if code != 0:
+        if code > 0:
+            raise RuntimeError("{}: CUDA error {} ({})".format(what, code, _cuda_error_name(code)))
+        raise RuntimeError("{}: unsupported arguments (code {})".format(what, code))
+
+
+def _cuda_error_name(code):
+    try:
+        return torch.cuda.cudart().cudaGetErrorString(code) if hasattr(torch.cuda.cudart(), "cudaGetErrorString") else str(code)
+    except Exception:
+        return str(code)

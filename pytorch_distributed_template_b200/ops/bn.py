@@ -1,0 +1,153 @@
+"""Fused BatchNorm(+residual)(+ReLU) on channels_last activations.
+
+Native path: ``csrc/bn.cu`` (two kernels forward, two backward; the SyncBN
+cross-rank exchange happens inside the statistics kernels).  Oracle / CPU path:
+``F.batch_norm`` + add + relu, and for SyncBN an all-reduce of raw moments.
+Reference semantics: eps 1e-5, momentum 0.1, unbiased running variance
+(SURVEY §2.4 "Math that the fused kernels must match").
+"""
+import torch
+import torch.distributed as dist
+import torch.nn.functional as F
+
+from . import _native
+
+_scratch = {}
+
+
+def _bn_scratch(device, C):
+    """One scratch per (device, stream): kernels on a stream never overlap."""
+    key = (device, torch.cuda.current_stream(device).cuda_stream)
+    need = _native.lib().pdt_bn_scratch_bytes(max(C, 512))
+    buf = _scratch.get(key)
+    if buf is None or buf.numel() < need:
+        buf = torch.zeros(need, dtype=torch.uint8, device=device)
+        _scratch[key] = buf
+    return buf
+
+
+def _native_ok(x, C):
+    if not (x.is_cuda and x.dim() == 4 and _native.available()):
+        return False
+    if x.dtype not in (torch.bfloat16, torch.float16, torch.float32):
+        return False
+    v = 4 if x.dtype == torch.float32 else 8
+    cg = C // v
+    return C % v == 0 and cg >= 1 and (cg & (cg - 1)) == 0 and cg <= 512 and 2 * C <= 4608
+
+
+class _BNActNative(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, res, weight, bias, running_mean, running_var, momentum, eps, relu, comm):
+        N, C, H, W = x.shape
+        M = N * H * W
+        x = x.contiguous(memory_format=torch.channels_last)
+        if res is not None:
+            res = res.contiguous(memory_format=torch.channels_last)
+        lib, s, dt = _native.lib(), _native.stream_ptr(x.device), _native.dtype_code(x.dtype)
+        mean = torch.empty(C, dtype=torch.float32, device=x.device)
+        invstd = torch.empty_like(mean)
+        scratch = _bn_scratch(x.device, C)
+        _native.check(lib.pdt_bn_fwd_stats(x.data_ptr(), M, C, dt, scratch.data_ptr(), comm,
+                                           _native.ptr(running_mean), _native.ptr(running_var), momentum, eps,
+                                           mean.data_ptr(), invstd.data_ptr(), s), "pdt_bn_fwd_stats")
+        y = torch.empty_like(x)
+        _native.check(lib.pdt_bn_fwd_apply(x.data_ptr(), _native.ptr(res), y.data_ptr(), M, C, dt, mean.data_ptr(),
+                                           invstd.data_ptr(), weight.data_ptr(), bias.data_ptr(), int(relu), 0, eps, s),
+                      "pdt_bn_fwd_apply")
+        ctx.save_for_backward(x, y if relu else None, weight, mean, invstd)
+        ctx.relu, ctx.has_res, ctx.comm = relu, res is not None, comm
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, y, weight, mean, invstd = ctx.saved_tensors
+        N, C, H, W = x.shape
+        M = N * H * W
+        dy = dy.contiguous(memory_format=torch.channels_last)
+        lib, s, dt = _native.lib(), _native.stream_ptr(x.device), _native.dtype_code(x.dtype)
+        dgamma = torch.empty(C, dtype=torch.float32, device=x.device)
+        dbeta = torch.empty_like(dgamma)
+        k = torch.empty(2 * C, dtype=torch.float32, device=x.device)
+        scratch = _bn_scratch(x.device, C)
+        _native.check(lib.pdt_bn_bwd_reduce(dy.data_ptr(), _native.ptr(y), x.data_ptr(), M, C, dt, mean.data_ptr(),
+                                            invstd.data_ptr(), int(ctx.relu), scratch.data_ptr(), ctx.comm,
+                                            dgamma.data_ptr(), dbeta.data_ptr(), k.data_ptr(), s), "pdt_bn_bwd_reduce")
+        dx = torch.empty_like(x)
+        dres = torch.empty_like(x) if ctx.has_res else None
+        _native.check(lib.pdt_bn_bwd_apply(dy.data_ptr(), _native.ptr(y), x.data_ptr(), dx.data_ptr(), _native.ptr(dres),
+                                           M, C, dt, mean.data_ptr(), invstd.data_ptr(), weight.data_ptr(), k.data_ptr(),
+                                           int(ctx.relu), s), "pdt_bn_bwd_apply")
+        return dx, dres, dgamma, dbeta, None, None, None, None, None, None
+
+
+class _SyncStatsTorch(torch.autograd.Function):
+    """CPU/oracle SyncBN: all-reduce of raw moments forward, of (sum dy, sum dy*xhat) backward."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, running_mean, running_var, momentum, eps, group):
+        C = x.shape[1]
+        xf = x.float()
+        dims = [0, 2, 3]
+        n = torch.tensor([float(x.numel() // C)], device=x.device)
+        stats = torch.cat([xf.sum(dims), (xf * xf).sum(dims), n])
+        dist.all_reduce(stats, group=group)
+        Ntot = stats[-1]
+        mean = stats[:C] / Ntot
+        var = (stats[C:2 * C] / Ntot - mean * mean).clamp_min(0)
+        invstd = torch.rsqrt(var + eps)
+        if running_mean is not None:
+            running_mean.mul_(1 - momentum).add_(mean, alpha=momentum)
+            running_var.mul_(1 - momentum).add_(var * Ntot / (Ntot - 1), alpha=momentum)
+        xhat = (xf - mean.view(1, C, 1, 1)) * invstd.view(1, C, 1, 1)
+        ctx.save_for_backward(xhat, weight, invstd, Ntot)
+        ctx.group = group
+        return (xhat * weight.view(1, C, 1, 1) + bias.view(1, C, 1, 1)).to(x.dtype)
+
+    @staticmethod
+    def backward(ctx, dy):
+        xhat, weight, invstd, Ntot = ctx.saved_tensors
+        C = xhat.shape[1]
+        dyf = dy.float()
+        dims = [0, 2, 3]
+        sum_dy, sum_dy_xhat = dyf.sum(dims), (dyf * xhat).sum(dims)
+        dgamma, dbeta = sum_dy_xhat.clone(), sum_dy.clone()
+        red = torch.cat([sum_dy, sum_dy_xhat])
+        dist.all_reduce(red, group=ctx.group)
+        k1 = (red[:C] / Ntot).view(1, C, 1, 1)
+        k2 = (red[C:] / Ntot).view(1, C, 1, 1)
+        dx = (dyf - k1 - xhat * k2) * (invstd * weight).view(1, C, 1, 1)
+        return dx.to(dy.dtype), dgamma, dbeta, None, None, None, None, None
+
+
+def bn_act(x, bn, residual=None, relu=False, comm=None, group=None):
+    """``relu?(bn(x) + residual?)`` for an ``nn.BatchNorm2d``-like module ``bn``.
+
+    ``comm`` (native CommDesc) or ``group`` (process group) turn it into SyncBatchNorm.
+    """
+    C = x.shape[1]
+    training = bn.training or bn.running_mean is None
+    sync = training and (comm is not None or group is not None)
+    if training and bn.track_running_stats and bn.num_batches_tracked is not None:
+        bn.num_batches_tracked.add_(1)
+    momentum = 0.1 if bn.momentum is None else bn.momentum
+    if training and _native_ok(x, C) and torch.is_grad_enabled() and (not sync or comm is not None):
+        return _BNActNative.apply(x, residual, bn.weight, bn.bias, bn.running_mean, bn.running_var, momentum, bn.eps,
+                                  relu, comm if sync else None)
+    if not training and _native_ok(x, C) and x.dtype != torch.float32 and not torch.is_grad_enabled():
+        xc = x.contiguous(memory_format=torch.channels_last)
+        rc = residual.contiguous(memory_format=torch.channels_last) if residual is not None else None
+        y = torch.empty_like(xc)
+        N, _, H, W = x.shape
+        _native.check(_native.lib().pdt_bn_fwd_apply(
+            xc.data_ptr(), _native.ptr(rc), y.data_ptr(), N * H * W, C, _native.dtype_code(x.dtype),
+            bn.running_mean.data_ptr(), bn.running_var.data_ptr(), bn.weight.data_ptr(), bn.bias.data_ptr(),
+            int(relu), 1, bn.eps, _native.stream_ptr(x.device)), "pdt_bn_fwd_apply(eval)")
+        return y
+    if sync and group is not None and dist.is_initialized() and dist.get_world_size(group) > 1:
+        y = _SyncStatsTorch.apply(x, bn.weight, bn.bias, bn.running_mean, bn.running_var, momentum, bn.eps, group)
+    else:
+        y = F.batch_norm(x, bn.running_mean, bn.running_var, bn.weight, bn.bias, training, momentum, bn.eps)
+    if residual is not None:
+        y = y + residual
+    return F.relu(y) if relu else y

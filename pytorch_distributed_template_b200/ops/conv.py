@@ -1,0 +1,90 @@
+"""Convolution and linear layers on channels_last low-precision activations.
+
+``conv2d`` / ``linear`` take the module (for its fp32 master weight and
+geometry).  Inside an ``amp.autocast`` region on a GPU they run in bf16/fp16
+from the optimizer-maintained *shadow* weights (no per-forward weight cast,
+SURVEY N11) and produce fp32 weight gradients; the implicit-GEMM tcgen05
+kernels of ``csrc/conv.cu`` serve the shapes they support, every other shape
+goes through ``aten::convolution`` with the same dtypes and layouts.
+Outside autocast (fp32 training, validation — the reference validates without
+autocast) they are ``F.conv2d`` / ``F.linear``.
+"""
+import torch
+import torch.nn.functional as F
+
+from .. import amp
+from . import _native
+
+_conv_native = None   # set by ops.conv_native when the tcgen05 kernels are importable
+
+
+def shadow_of(p, dtype):
+    arena = getattr(p, "_pdt_arena", None)
+    if arena is not None and arena.shadow_dtype == dtype:
+        return arena.shadow_view(p)
+    return None
+
+
+class _ConvLPTorch(torch.autograd.Function):
+    """Low-precision conv through aten (cuDNN) with an fp32 weight gradient."""
+
+    @staticmethod
+    def forward(ctx, x, weight, w_lp, stride, padding):
+        ctx.save_for_backward(x, w_lp)
+        ctx.geom = (stride, padding)
+        return torch.ops.aten.convolution(x, w_lp, None, stride, padding, (1, 1), False, (0, 0), 1)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w_lp = ctx.saved_tensors
+        stride, padding = ctx.geom
+        dy = dy.contiguous(memory_format=torch.channels_last)
+        dx, dw, _ = torch.ops.aten.convolution_backward(
+            dy, x, w_lp, None, stride, padding, (1, 1), False, (0, 0), 1,
+            (ctx.needs_input_grad[0], True, False))
+        return dx, dw.float(), None, None, None
+
+
+def conv2d(x, conv):
+    lp = amp.active_dtype()
+    if lp is None or not x.is_cuda or conv.groups != 1 or conv.dilation != (1, 1) or conv.bias is not None \
+            or conv.padding_mode != "zeros" or isinstance(conv.padding, str):
+        return conv._conv_forward(x, conv.weight, conv.bias)
+    if x.dtype != lp or not x.is_contiguous(memory_format=torch.channels_last):
+        x = x.to(dtype=lp, memory_format=torch.channels_last)
+    w_lp = shadow_of(conv.weight, lp)
+    if w_lp is None:
+        w_lp = conv.weight.detach().to(dtype=lp, memory_format=torch.channels_last)
+    if _conv_native is not None and _native.available():
+        y = _conv_native(x, conv.weight, w_lp, conv.stride, conv.padding)
+        if y is not None:
+            return y
+    return _ConvLPTorch.apply(x, conv.weight, w_lp, conv.stride, conv.padding)
+
+
+class _LinearLP(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, w_lp):
+        ctx.save_for_backward(x, w_lp)
+        ctx.has_bias = bias is not None
+        return F.linear(x, w_lp, bias.to(x.dtype) if bias is not None else None)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w_lp = ctx.saved_tensors
+        dx = dy @ w_lp if ctx.needs_input_grad[0] else None
+        dw = (dy.t() @ x).float()
+        db = dy.float().sum(0) if ctx.has_bias else None
+        return dx, dw, db, None
+
+
+def linear(x, fc):
+    lp = amp.active_dtype()
+    if lp is None or not x.is_cuda:
+        return F.linear(x, fc.weight, fc.bias)
+    if x.dtype != lp:
+        x = x.to(lp)
+    w_lp = shadow_of(fc.weight, lp)
+    if w_lp is None:
+        w_lp = fc.weight.detach().to(lp)
+    return _LinearLP.apply(x, fc.weight, fc.bias, w_lp)

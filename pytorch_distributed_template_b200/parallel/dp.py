@@ -1,0 +1,289 @@
+"""Single-process multi-GPU DataParallel.
+
+User contract of ``nn.DataParallel`` as the reference uses it
+(``nn.DataParallel(model).cuda()``, /root/reference/dataparallel.py:119): the
+whole batch arrives on GPU 0, ``forward`` returns logits for the whole batch on
+GPU 0, ``.module`` is the real network whose parameters the optimizer owns.
+
+What is different underneath:
+* replicas are PERSISTENT (built once) instead of re-broadcast every forward
+  (D3: 46.8 MB x 7 per step in the reference);
+* scatter (D2), gather (D5), the gradient-of-gather (D7a) and the BN-buffer
+  broadcast are destination-side pull kernels over NVLink peer mappings
+  (``pdt_peer_copy``), not NCCL / cudaMemcpyPeer calls;
+* the gradient reduce-to-GPU-0 + SGD-on-GPU-0 + next-forward broadcast
+  (D7, D8, D3) is ONE pair of kernels per device: device d sums shard d of
+  every replica's gradient arena through peer loads, applies momentum SGD to
+  that shard and stores the new weights (and bf16/fp16 shadow) into every
+  replica's arena through peer stores — the optimizer work is spread over all
+  GPUs and no parameter ever travels as a separate broadcast.
+* replica forwards are driven from one persistent thread per device; backward
+  uses autograd's own per-device threads (N4).
+
+Without CUDA the wrapper is transparent (like torch's with no GPUs).
+"""
+import copy
+import threading
+
+import torch
+import torch.nn as nn
+
+from ..ops import _native
+from .arena import ParamArena
+from .ddp import BufferArena
+from .fabric import Fabric
+
+
+def _peer_copy(src, dst):
+    """dst (on the current device) <- src (possibly on a peer); both contiguous, same nbytes."""
+    nbytes = dst.numel() * dst.element_size()
+    if _native.available() and src.data_ptr() % 16 == 0 and dst.data_ptr() % 16 == 0:
+        _native.check(_native.lib().pdt_peer_copy(src.data_ptr(), dst.data_ptr(), nbytes,
+                                                  _native.stream_ptr(dst.device)), "pdt_peer_copy")
+    else:
+        dst.copy_(src, non_blocking=True)
+
+
+class _Scatter(torch.autograd.Function):
+    """Chunk a GPU-0 tensor along dim 0 onto the devices; each device pulls its slice."""
+
+    @staticmethod
+    def forward(ctx, dp, x):
+        chunks = x.chunk(len(dp.device_ids), 0)
+        outs = []
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(x.device))
+        for dev, c in zip(dp.devices, chunks):
+            if dev == x.device:
+                outs.append(c)
+                continue
+            with torch.cuda.device(dev):
+                torch.cuda.current_stream(dev).wait_event(ev)
+                o = torch.empty(c.shape, dtype=c.dtype, device=dev)
+                _peer_copy(c.contiguous(), o)
+                outs.append(o)
+        return tuple(outs)
+
+    @staticmethod
+    def backward(ctx, *grads):
+        return None, None
+
+
+class _Gather(torch.autograd.Function):
+    """Concatenate per-device outputs on GPU 0 (pull), and scatter the gradient back (pull)."""
+
+    @staticmethod
+    def forward(ctx, dp, *outs):
+        ctx.dp = dp
+        ctx.sizes = [o.shape[0] for o in outs]
+        dev0 = dp.devices[0]
+        full = torch.empty((sum(ctx.sizes),) + tuple(outs[0].shape[1:]), dtype=outs[0].dtype, device=dev0)
+        pos = 0
+        with torch.cuda.device(dev0):
+            s0 = torch.cuda.current_stream(dev0)
+            for o in outs:
+                if o.device != dev0:
+                    ev = torch.cuda.Event()
+                    ev.record(torch.cuda.current_stream(o.device))
+                    s0.wait_event(ev)
+                _peer_copy(o.contiguous(), full[pos:pos + o.shape[0]])
+                pos += o.shape[0]
+        return full
+
+    @staticmethod
+    def backward(ctx, g):
+        dp = ctx.dp
+        g = g.contiguous()
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(g.device))
+        outs, pos = [], 0
+        for dev, n in zip(dp.devices, ctx.sizes):
+            piece = g[pos:pos + n]
+            pos += n
+            if dev == g.device:
+                outs.append(piece)
+                continue
+            with torch.cuda.device(dev):
+                torch.cuda.current_stream(dev).wait_event(ev)
+                o = torch.empty(piece.shape, dtype=piece.dtype, device=dev)
+                _peer_copy(piece, o)
+                outs.append(o)
+        return (None,) + tuple(outs)
+
+
+class _Worker(threading.Thread):
+    """One persistent launch thread per device (the reference spawns W threads per forward)."""
+
+    def __init__(self, device):
+        super().__init__(daemon=True)
+        self.device = device
+        self.job = None
+        self.result = None
+        self.cv = threading.Condition()
+        self.start()
+
+    def run(self):
+        torch.cuda.set_device(self.device)
+        while True:
+            with self.cv:
+                while self.job is None:
+                    self.cv.wait()
+                fn, args = self.job
+            try:
+                res = (True, fn(*args))
+            except BaseException as e:  # propagate to the caller
+                res = (False, e)
+            with self.cv:
+                self.job, self.result = None, res
+                self.cv.notify_all()
+
+    def submit(self, fn, *args):
+        with self.cv:
+            self.result = None
+            self.job = (fn, args)
+            self.cv.notify_all()
+
+    def wait(self):
+        with self.cv:
+            while self.result is None:
+                self.cv.wait()
+            ok, val = self.result
+        if not ok:
+            raise val
+        return val
+
+
+class DataParallel(nn.Module):
+    def __init__(self, module, device_ids=None, output_device=None, dim=0, shadow_dtype=None):
+        super().__init__()
+        if dim != 0:
+            raise ValueError("only dim=0 is supported (what the reference uses)")
+        self.module = module
+        self.dim = 0
+        if device_ids is None:
+            device_ids = list(range(torch.cuda.device_count())) if torch.cuda.is_available() else []
+        self.device_ids = [d if isinstance(d, int) else torch.device(d).index for d in device_ids]
+        self.devices = [torch.device("cuda", d) for d in self.device_ids]
+        self.output_device = self.device_ids[0] if self.device_ids else None
+        self.shadow_dtype = shadow_dtype
+        self.optimizer = None
+        self._built = False
+        self.replicas, self.arenas, self.buffer_arenas, self._workers = [], [], [], []
+        self._state = []
+
+    # ------------------------------------------------------------------ lazy construction
+    def _build(self):
+        """Called at the first forward: by then ``.cuda()`` has moved the module to GPU 0."""
+        dev0 = self.devices[0]
+        if next(self.module.parameters()).device != dev0:
+            self.module.to(dev0)
+        for a in self.devices:       # map every pair once (torch enables peer access on first copy)
+            for b in self.devices:
+                if a != b:
+                    if not torch.cuda.can_device_access_peer(a.index, b.index):
+                        raise RuntimeError("DataParallel needs peer access between GPU {} and {}".format(a, b))
+                    torch.zeros(1, device=a).to(b)
+        self.replicas = [self.module] + [copy.deepcopy(self.module).to(d) for d in self.devices[1:]]
+        for rep, dev in zip(self.replicas, self.devices):
+            with torch.cuda.device(dev):
+                fab = Fabric(dev, group="solo")
+                arena = ParamArena(rep.parameters(), fab, shadow_dtype=self.shadow_dtype)
+                arena.owner = self
+                self.arenas.append(arena)
+                self.buffer_arenas.append(BufferArena(rep, fab))
+                st = torch.zeros(8, dtype=torch.float32, device=dev)
+                st[0] = 1.0 / len(self.devices)      # k_reduce_scatter multiplies by 1/(W*scale): DP grads are sums
+                self._state.append(st)
+        self._workers = [None] + [_Worker(d) for d in self.devices[1:]]
+        W = len(self.devices)
+        self._grads = _native.make_peers([a.grad_buf.ptrs[0] for a in self.arenas])
+        self._params = _native.make_peers([a.param_buf.ptrs[0] for a in self.arenas])
+        self._shadow = _native.make_peers([a.shadow_buf.ptrs[0] for a in self.arenas]) if self.shadow_dtype else None
+        self._comms = [_native.make_comm(r, W, []) for r in range(W)]
+        self._hypers = [torch.zeros(4, dtype=torch.float32, device=d) for d in self.devices]
+        for d in self.devices:
+            torch.cuda.synchronize(d)
+        self._built = True
+
+    @property
+    def arena(self):
+        return self.arenas[0] if self.arenas else None
+
+    def _bcast_buffers(self):
+        ba0 = self.buffer_arenas[0]
+        if ba0.used == 0:
+            return
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.devices[0]))
+        for dev, ba in zip(self.devices[1:], self.buffer_arenas[1:]):
+            with torch.cuda.device(dev):
+                torch.cuda.current_stream(dev).wait_event(ev)
+                _peer_copy(ba0.flat, ba.flat)
+
+    # ------------------------------------------------------------------ forward
+    def forward(self, *inputs, **kwargs):
+        if len(self.device_ids) <= 1 or not torch.cuda.is_available():
+            return self.module(*inputs, **kwargs)
+        if not self._built:
+            self._build()
+        x = inputs[0]
+        if x.shape[0] < len(self.devices):
+            return self.module(*inputs, **kwargs)
+        for rep in self.replicas[1:]:
+            rep.train(self.module.training)
+        self._bcast_buffers()
+        xs = _Scatter.apply(self, x)
+        grad_on = torch.is_grad_enabled()
+        from .. import amp
+        lp = amp.active_dtype()
+
+        def run(rep, xi):
+            with torch.set_grad_enabled(grad_on), amp.autocast(enabled=lp is not None, dtype=lp):
+                return rep(xi)
+
+        for w, rep, xi in zip(self._workers[1:], self.replicas[1:], xs[1:]):
+            w.submit(run, rep, xi)
+        outs = [run(self.replicas[0], xs[0])] + [w.wait() for w in self._workers[1:]]
+        return _Gather.apply(self, *outs)
+
+    # ------------------------------------------------------------------ fused optimizer step
+    def fused_step(self, opt):
+        """D7 + D8 + D3 in one pair of kernels per device (see module docstring)."""
+        W = len(self.devices)
+        lib = _native.lib()
+        g = opt.param_groups[0]
+        host = torch.tensor([g["lr"], g["momentum"], g["weight_decay"], 0.0], dtype=torch.float32)
+        done = []
+        for dev in self.devices:      # every replica's backward must be complete before anyone reads it
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(dev))
+            done.append(ev)
+        sh_dtype = _native.dtype_code(self.shadow_dtype) if self.shadow_dtype is not None else _native.BF16
+        after = []
+        for r, dev in enumerate(self.devices):
+            a = self.arenas[r]
+            with torch.cuda.device(dev):
+                s = torch.cuda.current_stream(dev)
+                for ev in done:
+                    s.wait_event(ev)
+                a.gather_grads(drop=(r != 0))
+                self._hypers[r].copy_(host, non_blocking=True)
+                _native.check(lib.pdt_reduce_scatter_f32(self._comms[r], self._grads, 0, a.total,
+                                                        self._state[r].data_ptr(), 0, 64, s.cuda_stream),
+                              "pdt_reduce_scatter_f32(dp)")
+                _native.check(lib.pdt_sgd_allgather(self._comms[r], self._grads, self._params, self._shadow, sh_dtype,
+                                                   a.momentum.data_ptr(), 0, a.total, self._hypers[r].data_ptr(),
+                                                   self._state[r].data_ptr(), 0, 64, s.cuda_stream),
+                              "pdt_sgd_allgather(dp)")
+                ev = torch.cuda.Event()
+                ev.record(s)
+                after.append(ev)
+        for dev in self.devices:      # new weights were written by peers: everybody waits for everybody
+            s = torch.cuda.current_stream(dev)
+            for ev in after:
+                s.wait_event(ev)
+
+    def zero_replica_grads(self):
+        for rep in self.replicas[1:]:
+            for p in rep.parameters():
+                p.grad = None
