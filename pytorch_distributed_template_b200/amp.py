@@ -81,7 +81,9 @@ class GradScaler:
 
     def bind(self, optimizer):
         self._optimizer = optimizer
-        device = optimizer.arena.device if hasattr(optimizer, "arena") else self._device
+        arena = getattr(optimizer, "arena", None)
+        device = arena.device if arena is not None else (
+            self._device or optimizer.param_groups[0]["params"][0].device)
         self._ensure_state(device)
         if hasattr(optimizer, "attach_scaler"):
             optimizer.attach_scaler(self)

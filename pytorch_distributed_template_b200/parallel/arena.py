@@ -94,7 +94,10 @@ class ParamArena:
                 view = self._view(self.flat_params, p)
                 view.copy_(p.data)
                 p.data = view
-                p.grad = None
+                if p.grad is not None:      # built after a backward (lazy optimizer binding): keep it
+                    gv = self._view(self.flat_grads, p)
+                    gv.copy_(p.grad)
+                    p.grad = gv
                 p._pdt_arena = self
         self.refresh_shadow()
 

@@ -1,0 +1,99 @@
+"""Worker for test_ddp_gloo.py: 2 ranks on CPU/gloo (or N ranks on GPUs/NCCL with --cuda).
+Compares our DistributedDataParallel + fused SGD against torch DDP + torch SGD, same seeds."""
+import copy
+import json
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from pytorch_distributed_template_b200 import amp, env, optim  # noqa: E402
+from pytorch_distributed_template_b200.models import create_model  # noqa: E402
+from pytorch_distributed_template_b200.parallel import DistributedDataParallel, SyncBatchNorm  # noqa: E402
+
+
+def main():
+    cuda = "--cuda" in sys.argv
+    syncbn = "--syncbn" in sys.argv
+    if not cuda:
+        os.environ["PDT_DEVICE"] = "cpu"
+    rank = int(os.environ["RANK"])
+    device = env.init_distributed(int(os.environ["LOCAL_RANK"]))
+    world = dist.get_world_size()
+    torch.manual_seed(100 + rank)                       # different init per rank: ctor must sync from rank 0
+    net = create_model("resnet18", num_classes=10)
+    if syncbn:
+        net = SyncBatchNorm.convert_sync_batchnorm(net)
+    net = net.to(device)
+    ref_net = copy.deepcopy(net)
+    if syncbn:
+        ref_net = copy.deepcopy(create_model("resnet18", num_classes=10))
+        ref_net.load_state_dict(net.state_dict())
+        ref_net = torch.nn.SyncBatchNorm.convert_sync_batchnorm(ref_net).to(device) if cuda else None
+
+    ours = DistributedDataParallel(net, device_ids=[device.index] if cuda else None)
+    out = {"rank": rank, "world": world, "segments": len(ours.arena.segments), "fabric": ours.fabric.describe()}
+    # 1. constructor broadcast: every rank equals rank 0
+    flat = ours.arena.flat_params.detach().clone()
+    ref0 = flat.clone()
+    dist.broadcast(ref0, src=0)
+    out["init_synced"] = bool(torch.equal(flat, ref0))
+    out["prefix_ok"] = all(k.startswith("module.") for k in ours.state_dict()) and \
+        "conv1.weight" in ours.module.state_dict()
+
+    res = {}
+    if ref_net is not None:
+        ref_net.load_state_dict(ours.module.state_dict())
+        theirs = torch.nn.parallel.DistributedDataParallel(ref_net, device_ids=[device.index] if cuda else None)
+        o_ours = optim.SGD(ours.parameters(), 0.01, momentum=0.9, weight_decay=1e-4)
+        o_ref = torch.optim.SGD(theirs.parameters(), 0.01, momentum=0.9, weight_decay=1e-4)
+        g = torch.Generator().manual_seed(7 + rank)
+        worst_grad = worst_param = 0.0
+        worst_name = None
+        for it in range(3):
+            x = torch.randn(8, 3, 64, 64, generator=g).to(device)
+            y = torch.randint(0, 10, (8,), generator=g).to(device)
+            for model, opt in ((ours, o_ours), (theirs, o_ref)):
+                model.train()
+                opt.zero_grad()
+                loss = torch.nn.functional.cross_entropy(model(x), y)
+                loss.backward()
+                if model is theirs or cuda is False:
+                    pass
+                opt.step()
+            if it == 0 and not cuda:
+                # torch backend leaves the averaged gradient in p.grad: compare directly
+                for p, q in zip(ours.module.parameters(), theirs.module.parameters()):
+                    d = (p.grad - q.grad).abs().max().item() / (q.grad.abs().max().item() + 1e-12)
+                    worst_grad = max(worst_grad, d)
+            for (k, p), q in zip(ours.module.named_parameters(), theirs.module.parameters()):
+                d = (p.detach() - q.detach()).abs().max().item() / (q.detach().abs().max().item() + 1e-12)
+                if d > worst_param:
+                    worst_param, worst_name = d, (it, k)
+            if it == 0:
+                first_param = worst_param
+        res = {"worst_grad_rel": worst_grad, "worst_param_rel": worst_param, "worst_name": str(worst_name), "first_param_rel": first_param}
+        # ranks agree with each other bit-for-bit
+        mine = ours.arena.flat_params.detach().clone()
+        other = mine.clone()
+        dist.broadcast(other, src=0)
+        res["ranks_identical"] = bool(torch.equal(mine, other))
+        # running stats: rank 0's are broadcast before each forward (broadcast_buffers=True)
+        rm = ours.module.bn1.running_mean.detach().clone()
+        rm_ref = theirs.module.bn1.running_mean.detach().clone()
+        res["bn_buffer_rel"] = ((rm - rm_ref).abs().max() / (rm_ref.abs().max() + 1e-12)).item()
+    out.update(res)
+    # scalar metric reduction
+    t = torch.tensor([float(rank + 1), 2.0 * (rank + 1)], device=device)
+    ours.fabric.allreduce_small_(t, mean=True)
+    out["reduce_mean"] = t.tolist()
+    print("RESULT " + json.dumps(out), flush=True)
+    env.shutdown_distributed()
+
+
+if __name__ == "__main__":
+    main()

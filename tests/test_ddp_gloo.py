@@ -1,0 +1,59 @@
+"""T1: distributed plumbing on CPU — 2 ranks, gloo, ResNet-18, tiny synthetic batches
+(BASELINE.json config #1).  Oracle: torch.nn.parallel.DistributedDataParallel + torch SGD."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def _launch(extra, nproc=2, port=29621, timeout=600):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(nproc),
+           "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(HERE, "_ddp_worker.py")] + extra
+    env = dict(os.environ, OMP_NUM_THREADS="2")
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env=env)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    outs = [json.loads(l[len("RESULT "):]) for l in r.stdout.splitlines() if l.startswith("RESULT ")]
+    assert len(outs) == nproc, r.stdout[-2000:]
+    return outs
+
+
+def test_ddp_two_ranks_matches_torch_ddp():
+    outs = _launch([])
+    for o in outs:
+        assert o["world"] == 2 and o["init_synced"] and o["prefix_ok"]
+        assert o["segments"] == 3                       # 1 MiB + 25 MiB caps on 46.8 MB of gradients
+        assert o["ranks_identical"]
+        assert o["worst_grad_rel"] < 1e-4, o      # KRSC weight strides pick different CPU conv kernels
+        assert o["first_param_rel"] < 1e-5, o           # one step: update arithmetic is exact
+        assert o["worst_param_rel"] < 2e-2, o           # three steps: fp32 reassociation amplified by small-batch BN
+        assert o["bn_buffer_rel"] < 1e-4, o
+        assert o["reduce_mean"] == pytest.approx([1.5, 3.0])
+
+
+def test_training_script_two_ranks(tmp_path):
+    """distributed_syncBN_amp.py end to end on 2 CPU ranks: logs, settings, checkpoint keys, rank-0-only IO."""
+    env = dict(os.environ, PDT_SYNTHETIC="1", PDT_SYNTH_TRAIN_SIZE="16", PDT_SYNTH_VAL_SIZE="8", PDT_IMAGE_SIZE="32",
+               PDT_NUM_CLASSES="10", PDT_MAX_STEPS="2", PDT_DEVICE="cpu", OMP_NUM_THREADS="2")
+    root = os.path.dirname(HERE)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", "29631", os.path.join(root, "distributed_syncBN_amp.py"), "--epochs", "2",
+           "-b", "8", "-j", "0", "--outpath", str(tmp_path / "o"), "--sync_batchnorm", "1", "--step", "1"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env, cwd=root)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    out = tmp_path / "o_resnet18"
+    assert sorted(p.name for p in out.iterdir() if not p.name.startswith("events")) == \
+        ["checkpoint.pth.tar", "experiment.log", "model_best.pth.tar", "settings.log"]
+    log = (out / "experiment.log").read_text()
+    for needle in ("=> creating model: resnet18", "=> using sync BN", "lr_scheduler: SGD MultiStepLR !!!",
+                   "Train epoch: [0/2][0/", "||==> Train epoch: [1/2]\tlr=0.010000", "||==> Val epoch: [1/2]",
+                   "||==> Epoch=[1/2]\tbest_acc1=", "||==> total_time_cost="):
+        assert needle in log, needle
+    import torch
+    ck = torch.load(out / "checkpoint.pth.tar", map_location="cpu", weights_only=False)
+    assert set(ck) == {"epoch", "arch", "state_dict", "best_acc1"} and ck["epoch"] == 2 and ck["arch"] == "resnet18"
+    assert len(ck["state_dict"]) == 122 and "conv1.weight" in ck["state_dict"]
+    assert "batch_size: 4" in (out / "settings.log").read_text() or "batch_size: 8" in (out / "settings.log").read_text()

@@ -1,0 +1,246 @@
+"""T2: every native kernel against a plain PyTorch fp32 reference of the same op."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+CUDA = torch.cuda.is_available()
+
+
+def _dev():
+    return torch.device("cuda", 0)
+
+
+def _nhwc(*shape, dtype=torch.bfloat16, scale=1.0, shift=0.0):
+    x = (torch.randn(*shape, device=_dev()) * scale + shift).to(dtype)
+    return x.contiguous(memory_format=torch.channels_last)
+
+
+TOL = {torch.bfloat16: 2e-2, torch.float16: 4e-3, torch.float32: 2e-4}
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
+@pytest.mark.parametrize("shape,relu,res", [((6, 64, 56, 56), True, False), ((6, 128, 28, 28), True, True),
+                                            ((5, 256, 14, 14), False, False), ((9, 512, 7, 7), True, True),
+                                            ((3, 64, 112, 112), True, False)])
+def test_bn_act_forward_backward(native_lib, dtype, shape, relu, res):
+    from pytorch_distributed_template_b200 import ops
+    from pytorch_distributed_template_b200.ops import _native
+    torch.manual_seed(0)
+    C = shape[1]
+    x = _nhwc(*shape, dtype=dtype, scale=1.5, shift=0.3).requires_grad_(True)
+    r = _nhwc(*shape, dtype=dtype).requires_grad_(True) if res else None
+    bn = torch.nn.BatchNorm2d(C).to(_dev())
+    with torch.no_grad():
+        bn.weight.uniform_(0.5, 1.5)
+        bn.bias.uniform_(-0.5, 0.5)
+    ref_bn = torch.nn.BatchNorm2d(C).to(_dev())
+    ref_bn.load_state_dict(bn.state_dict())
+    n0 = _native.launch_count
+    y = ops.bn_act(x, bn, r, relu)
+    assert _native.launch_count - n0 == 2, "native BN path not taken"
+    dy = _nhwc(*shape, dtype=dtype)
+    y.backward(dy)
+    assert _native.launch_count - n0 == 4
+
+    xf = x.detach().float().requires_grad_(True)
+    rf = r.detach().float().requires_grad_(True) if res else None
+    yf = ref_bn(xf)
+    if res:
+        yf = yf + rf
+    if relu:
+        yf = F.relu(yf)
+    yf.backward(dy.float())
+    tol = TOL[dtype]
+    assert y.dtype == dtype and y.is_contiguous(memory_format=torch.channels_last)
+    assert torch.allclose(y.float(), yf, rtol=tol, atol=tol)
+    gscale = xf.grad.abs().max().item()
+    assert (x.grad.float() - xf.grad).abs().max().item() <= tol * max(1.0, gscale) * 2
+    if res:
+        assert torch.allclose(r.grad.float(), rf.grad, rtol=tol, atol=tol)
+    wscale = ref_bn.weight.grad.abs().max().item()
+    assert (bn.weight.grad - ref_bn.weight.grad).abs().max().item() <= tol * max(1.0, wscale)
+    assert (bn.bias.grad - ref_bn.bias.grad).abs().max().item() <= tol * max(1.0, ref_bn.bias.grad.abs().max().item())
+    assert torch.allclose(bn.running_mean, ref_bn.running_mean, rtol=1e-3, atol=1e-4)
+    assert torch.allclose(bn.running_var, ref_bn.running_var, rtol=1e-3, atol=1e-4)
+    assert int(bn.num_batches_tracked) == 1
+
+
+def test_bn_eval_apply(native_lib):
+    from pytorch_distributed_template_b200 import ops
+    x = _nhwc(4, 64, 20, 20)
+    bn = torch.nn.BatchNorm2d(64).to(_dev()).eval()
+    with torch.no_grad():
+        bn.running_mean.normal_(); bn.running_var.uniform_(0.5, 2.0); bn.weight.uniform_(0.5, 1.5); bn.bias.normal_()
+        y = ops.bn_act(x, bn, None, True)
+        ref = F.relu(bn(x.float()))
+    assert torch.allclose(y.float(), ref, rtol=2e-2, atol=2e-2)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("B,K", [(150, 1000), (37, 10), (1200, 1000)])
+def test_cross_entropy_fused(native_lib, dtype, B, K):
+    from pytorch_distributed_template_b200.ops import cross_entropy_with_accuracy
+    torch.manual_seed(1)
+    logits = (torch.randn(B, K, device=_dev()) * 3).to(dtype).requires_grad_(True)
+    tgt = torch.randint(0, K, (B,), device=_dev())
+    with torch.no_grad():                                  # make ~half the rows correct
+        logits[torch.arange(0, B, 2), tgt[::2]] += 20
+    loss, acc = cross_entropy_with_accuracy(logits, tgt)
+    scale = torch.tensor(1024.0, device=_dev())
+    (loss * scale).backward()
+    lf = logits.detach().float().requires_grad_(True)
+    ref = F.cross_entropy(lf, tgt)
+    (ref * 1024.0).backward()
+    assert loss.item() == pytest.approx(ref.item(), rel=1e-4, abs=1e-5)
+    assert acc.item() == pytest.approx((lf.argmax(1) == tgt).float().mean().item(), abs=1e-6)
+    tol = {torch.float32: 1e-5, torch.bfloat16: 1e-2, torch.float16: 2e-3}[dtype]
+    assert logits.grad.dtype == dtype
+    assert (logits.grad.float() - lf.grad).abs().max().item() <= tol * lf.grad.abs().max().item() + 1e-7
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_pools(native_lib, dtype):
+    from pytorch_distributed_template_b200 import ops
+    x = _nhwc(5, 64, 112, 112, dtype=dtype).requires_grad_(True)
+    y = ops.max_pool2d(x, 3, 2, 1)
+    xf = x.detach().float().requires_grad_(True)
+    yf = F.max_pool2d(xf, 3, 2, 1)
+    assert torch.equal(y.float(), yf)
+    dy = _nhwc(5, 64, 56, 56, dtype=dtype)
+    y.backward(dy); yf.backward(dy.float())
+    assert torch.allclose(x.grad.float(), xf.grad, rtol=1e-2, atol=1e-2)
+    z = _nhwc(7, 512, 7, 7, dtype=dtype).requires_grad_(True)
+    a = ops.global_avg_pool(z)
+    zf = z.detach().float().requires_grad_(True)
+    af = torch.flatten(F.adaptive_avg_pool2d(zf, 1), 1)
+    assert a.shape == (7, 512) and torch.allclose(a.float(), af, rtol=1e-2, atol=1e-2)
+    da = torch.randn(7, 512, device=_dev()).to(dtype)
+    a.backward(da); af.backward(da.float())
+    assert torch.allclose(z.grad.float(), zf.grad, rtol=1e-2, atol=1e-3)
+
+
+def test_layout_cast_and_peer_copy(native_lib):
+    from pytorch_distributed_template_b200.ops import _native
+    x = torch.randn(3, 3, 17, 19, device=_dev())
+    for cp in (4, 8):
+        y = torch.empty(3, 17, 19, cp, dtype=torch.bfloat16, device=_dev())
+        _native.check(native_lib.pdt_nchw_to_nhwc(x.data_ptr(), y.data_ptr(), _native.BF16, 3, 3, 17, 19, cp,
+                                                  _native.stream_ptr()), "nchw_to_nhwc")
+        assert torch.equal(y[..., :3].float(), x.permute(0, 2, 3, 1).bfloat16().float()) and y[..., 3:].abs().sum() == 0
+    src = torch.randn(1000003, device=_dev())
+    dst = torch.zeros_like(src)
+    _native.check(native_lib.pdt_peer_copy(src.data_ptr(), dst.data_ptr(), src.numel() * 4, _native.stream_ptr()), "peer_copy")
+    assert torch.equal(src, dst)
+
+
+@pytest.mark.parametrize("amp_on,inject_inf", [(False, False), (True, False), (True, True)])
+def test_fused_gradient_path_world1(native_lib, amp_on, inject_inf):
+    """reduce_scatter (unscale + inf check) -> sgd_allgather (SGD + shadow) -> scale_update on one rank,
+    through DistributedDataParallel + optim.SGD + amp.GradScaler, against torch SGD on fp32 copies."""
+    import copy
+    import os
+    import torch.distributed as dist
+    from pytorch_distributed_template_b200 import amp, env, optim
+    from pytorch_distributed_template_b200.parallel import DistributedDataParallel
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT="29651", RANK="0", WORLD_SIZE="1", LOCAL_RANK="0")
+    env.init_distributed(0)
+    try:
+        torch.manual_seed(3)
+        net = torch.nn.Sequential(torch.nn.Linear(64, 300), torch.nn.ReLU(), torch.nn.Linear(300, 10)).to(_dev())
+        ref = copy.deepcopy(net)
+        ddp = DistributedDataParallel(net, device_ids=[0], shadow_dtype=torch.bfloat16)
+        opt = optim.SGD(ddp.parameters(), 0.1, momentum=0.9, weight_decay=1e-2)
+        ropt = torch.optim.SGD(ref.parameters(), 0.1, momentum=0.9, weight_decay=1e-2)
+        scaler = amp.GradScaler(init_scale=256.0, growth_interval=2, enabled=amp_on, device=_dev())
+        if amp_on:
+            scaler.bind(opt)
+        x = torch.randn(32, 64, device=_dev())
+        y = torch.randint(0, 10, (32,), device=_dev())
+        for it in range(3):
+            bad = inject_inf and it == 1
+            opt.zero_grad(); ropt.zero_grad()
+            loss = F.cross_entropy(ddp(x), y)
+            if bad:
+                loss = loss * float("inf")
+            scaler.scale(loss).backward()
+            scaler.step(opt)
+            scaler.update()
+            if not bad:
+                F.cross_entropy(ref(x), y).backward()
+                ropt.step()
+        torch.cuda.synchronize()
+        for p, q in zip(net.parameters(), ref.parameters()):
+            assert torch.allclose(p, q, rtol=1e-4, atol=1e-5)
+            sh = p._pdt_arena.shadow_view(p)
+            assert torch.equal(sh, p.detach().bfloat16())
+        if amp_on:
+            assert scaler.skipped_steps() == (1 if inject_inf else 0)
+            # clean: x2 after the 2nd clean step.  inf at step 1: halved, tracker restarts
+            assert scaler.get_scale() == (128.0 if inject_inf else 512.0)
+    finally:
+        env.shutdown_distributed()
+
+
+def test_standalone_sgd_flat(native_lib):
+    import copy
+    from pytorch_distributed_template_b200 import optim
+    torch.manual_seed(5)
+    net = torch.nn.Linear(100, 50).to(_dev())
+    ref = copy.deepcopy(net)
+    opt = optim.SGD(net.parameters(), 0.05, momentum=0.9, weight_decay=1e-3)
+    ropt = torch.optim.SGD(ref.parameters(), 0.05, momentum=0.9, weight_decay=1e-3)
+    x = torch.randn(16, 100, device=_dev())
+    for _ in range(3):
+        for m, o in ((net, opt), (ref, ropt)):
+            o.zero_grad()
+            m(x).square().mean().backward()
+            o.step()
+    for p, q in zip(net.parameters(), ref.parameters()):
+        assert torch.allclose(p, q, rtol=1e-5, atol=1e-6)
+
+
+def test_resnet18_amp_step_matches_torch_autocast(native_lib):
+    """Whole flagship step (native BN/pool/CE kernels, shadow weights, fused SGD) vs torchvision + torch.autocast."""
+    import copy
+    import os
+    import torchvision
+    from pytorch_distributed_template_b200 import amp, env, optim
+    from pytorch_distributed_template_b200.models import create_model
+    from pytorch_distributed_template_b200.ops import CrossEntropyLoss
+    from pytorch_distributed_template_b200.parallel import DistributedDataParallel
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT="29652", RANK="0", WORLD_SIZE="1", LOCAL_RANK="0")
+    env.init_distributed(0)
+    try:
+        torch.manual_seed(11)
+        net = create_model("resnet18").to(_dev())
+        tv = torchvision.models.resnet18().to(_dev())
+        tv.load_state_dict(net.state_dict())
+        init = torch.cat([q.detach().float().reshape(-1) for q in tv.parameters()])
+        ddp = DistributedDataParallel(net, device_ids=[0], shadow_dtype=torch.bfloat16)
+        crit = CrossEntropyLoss()
+        opt = optim.SGD(ddp.parameters(), 0.01, momentum=0.9, weight_decay=1e-4)
+        scaler = amp.GradScaler(enabled=True, device=_dev(), optimizer=opt)
+        ropt = torch.optim.SGD(tv.parameters(), 0.01, momentum=0.9, weight_decay=1e-4)
+        x = torch.randn(16, 3, 224, 224, device=_dev())
+        y = torch.randint(0, 1000, (16,), device=_dev())
+        ddp.train(); tv.train()
+        with amp.autocast(True, torch.bfloat16):
+            loss = crit(ddp(x), y)
+        opt.zero_grad()
+        scaler.scale(loss).backward()
+        scaler.step(opt); scaler.update()
+        with torch.autocast("cuda", torch.bfloat16):
+            rloss = F.cross_entropy(tv(x), y)
+        ropt.zero_grad(); rloss.backward(); ropt.step()
+        torch.cuda.synchronize()
+        assert loss.item() == pytest.approx(rloss.item(), rel=3e-2)
+        ours = torch.cat([p.detach().float().reshape(-1) for p in net.parameters()])
+        theirs = torch.cat([q.detach().float().reshape(-1) for q in tv.parameters()])
+        assert torch.isfinite(ours).all()
+        # the UPDATE must agree, not just the weights: error relative to the size of the step
+        assert (ours - theirs).norm().item() <= 0.2 * (theirs - init).norm().item()
+        assert scaler.skipped_steps() == 0
+    finally:
+        env.shutdown_distributed()
