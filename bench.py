@@ -235,6 +235,11 @@ def run_ours(args, world):
         world_for_batch = world
     _native.require()
     per_rank = args.batch // world_for_batch
+    # Everything — construction, warm-up, capture, replay — runs on ONE non-default stream:
+    # autograd's AccumulateGrad nodes remember the stream they were created on, and a
+    # capture that has to synchronise with the legacy default stream is invalid.
+    work_stream = torch.cuda.Stream(device)
+    torch.cuda.set_stream(work_stream)
     model, step, lp = build_ours(args, device, world)
 
     g = torch.Generator().manual_seed(1234 + rank)
@@ -262,16 +267,9 @@ def run_ours(args, world):
     use_graph = (not args.no_graph) and args.mode != "dp" and os.environ.get("PDT_BENCH_GRAPH", "1") == "1"
     if use_graph:
         try:
-            side = torch.cuda.Stream(device)
-            side.wait_stream(torch.cuda.current_stream(device))
-            with torch.cuda.stream(side):
-                for _ in range(2):
-                    step(static_img, static_tgt)
-            torch.cuda.current_stream(device).wait_stream(side)
-            fence()
             graph = torch.cuda.CUDAGraph()
             n0 = _native.launch_count
-            with torch.cuda.graph(graph):
+            with torch.cuda.graph(graph, stream=work_stream):
                 static_loss = step(static_img, static_tgt)
             launches_per_step = _native.launch_count - n0
             fence()

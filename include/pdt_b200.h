@@ -139,6 +139,15 @@ int pdt_nchw_to_nhwc(const float* x, void* y, int dtype, int N, int Cin, int H, 
  * buffer broadcast; torch.cuda.comm.scatter/gather/broadcast_coalesced, dataparallel.py:119). */
 int pdt_peer_copy(const void* src, void* dst, size_t nbytes, cudaStream_t stream);
 
+/* ---- implicit-GEMM convolution on tcgen05 / TMEM / TMA --------------------
+ * x: [N][H][W][C], w: [K][R][S][C] (KRSC), y: [N][P][Q][K], all bf16 or fp16; C % 64 == 0,
+ * K % 8 == 0, 16-byte aligned pointers.  Forward convolution of nn.Conv2d (cuDNN
+ * cudnnConvolutionForward; every conv of torchvision resnet18, distributed.py:137,246) and,
+ * with dy as x and the flipped/transposed filter as w (pad' = R-1-pad), the data gradient of
+ * stride-1 convolutions (cudnnConvolutionBackwardData, distributed.py:262). */
+int pdt_conv_fprop(const void* x, const void* w, void* y, int dtype, int N, int H, int W, int C, int K, int R, int S,
+                   int stride, int pad, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

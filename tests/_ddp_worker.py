@@ -30,8 +30,9 @@ def main():
         net = SyncBatchNorm.convert_sync_batchnorm(net)
     net = net.to(device)
     ref_net = copy.deepcopy(net)
-    if syncbn:
-        ref_net = copy.deepcopy(create_model("resnet18", num_classes=10))
+    if syncbn:     # oracle: torchvision's ResNet with torch's own SyncBatchNorm (CUDA only)
+        import torchvision
+        ref_net = torchvision.models.resnet18(num_classes=10)
         ref_net.load_state_dict(net.state_dict())
         ref_net = torch.nn.SyncBatchNorm.convert_sync_batchnorm(ref_net).to(device) if cuda else None
 

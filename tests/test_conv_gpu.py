@@ -1,0 +1,53 @@
+"""T2: tcgen05 implicit-GEMM convolution vs F.conv2d (fp32, TF32 off) on every ResNet-18 conv shape
+the kernel serves, forward and stride-1 data gradient."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+# (Cin, Cout, H, k, stride, pad) — SURVEY §2.4(a)
+SHAPES = [(64, 64, 56, 3, 1, 1), (64, 128, 56, 3, 2, 1), (128, 128, 28, 3, 1, 1), (64, 128, 56, 1, 2, 0),
+          (128, 256, 28, 3, 2, 1), (256, 256, 14, 3, 1, 1), (128, 256, 28, 1, 2, 0), (256, 512, 14, 3, 2, 1),
+          (512, 512, 7, 3, 1, 1), (256, 512, 14, 1, 2, 0)]
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("cin,cout,hw,k,stride,pad", SHAPES)
+@pytest.mark.parametrize("batch", [3, 10])
+def test_conv_fprop_matches_conv2d(native_lib, dtype, cin, cout, hw, k, stride, pad, batch):
+    from pytorch_distributed_template_b200.ops import conv_native
+    torch.backends.cudnn.allow_tf32 = False
+    torch.manual_seed(0)
+    dev = torch.device("cuda", 0)
+    x = torch.randn(batch, cin, hw, hw, device=dev).to(dtype).contiguous(memory_format=torch.channels_last)
+    w = (torch.randn(cout, cin, k, k, device=dev) / (cin * k * k) ** 0.5).to(dtype).contiguous(memory_format=torch.channels_last)
+    y = conv_native.fprop(x, w, stride, pad)
+    ref = F.conv2d(x.float(), w.float(), None, stride, pad)
+    assert y.shape == ref.shape and y.is_contiguous(memory_format=torch.channels_last)
+    tol = 2e-2 if dtype == torch.bfloat16 else 3e-3
+    err = (y.float() - ref).abs().max().item()
+    assert err <= tol * max(1.0, ref.abs().max().item()), (err, ref.abs().max().item())
+
+
+@pytest.mark.parametrize("cin,cout,hw,k,stride,pad", [s for s in SHAPES if s[4] == 1] + [(64, 64, 56, 3, 2, 1)])
+def test_conv_autograd_matches_torch(native_lib, cin, cout, hw, k, stride, pad):
+    from pytorch_distributed_template_b200.ops import conv_native
+    torch.backends.cudnn.allow_tf32 = False
+    torch.manual_seed(1)
+    dev = torch.device("cuda", 0)
+    dtype = torch.bfloat16
+    x = torch.randn(4, cin, hw, hw, device=dev).to(dtype).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    wm = (torch.randn(cout, cin, k, k, device=dev) / (cin * k * k) ** 0.5).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    w_lp = wm.detach().to(dtype)
+    y = conv_native.conv_native(x, wm, w_lp, (stride, stride), (pad, pad))
+    assert y is not None
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    xf = x.detach().float().requires_grad_(True)
+    wf = w_lp.float().requires_grad_(True)
+    yf = F.conv2d(xf, wf, None, stride, pad)
+    yf.backward(dy.float())
+    assert (x.grad.float() - xf.grad).abs().max().item() <= 2e-2 * max(1.0, xf.grad.abs().max().item())
+    assert wm.grad.dtype == torch.float32
+    assert (wm.grad - wf.grad).abs().max().item() <= 3e-2 * max(1.0, wf.grad.abs().max().item())
