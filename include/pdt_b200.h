@@ -147,6 +147,10 @@ int pdt_peer_copy(const void* src, void* dst, size_t nbytes, cudaStream_t stream
  * stride-1 convolutions (cudnnConvolutionBackwardData, distributed.py:262). */
 int pdt_conv_fprop(const void* x, const void* w, void* y, int dtype, int N, int H, int W, int C, int K, int R, int S,
                    int stride, int pad, cudaStream_t stream);
+/* Weight gradient (cudnnConvolutionBackwardFilter): dw [K][R][S][C] fp32 += sum over pixels; split-K over
+ * the pixel dimension with red.global.add, so zero dw first.  C % 64 == 0, K % 64 == 0. */
+int pdt_conv_wgrad(const void* x, const void* dy, float* dw, int dtype, int N, int H, int W, int C, int K, int R, int S,
+                   int stride, int pad, cudaStream_t stream);
 
 #ifdef __cplusplus
 }

@@ -34,9 +34,16 @@ struct ConvGeom {
   int N, H, W, C;              // input  (NHWC)
   int K, R, S;                 // filter (KRSC)
   int P, Q;                    // output spatial
-  int stride, pad;
+  int stride;
+  int pad_h, pad_w;            // lower (top/left) padding
+  int pad_hi_h, pad_hi_w;      // upper (bottom/right) padding
   int M;                       // N*P*Q
   int m_tiles, n_tiles;
+  // where output pixel (n,p,q) lands: ((n*OH + p*os + oa)*OW + q*os + ob)*K.  Dense NHWC: OH=P, OW=Q, os=1.
+  int OH, OW, os, oa, ob;
+  // activation tensor as TMA sees it: Cx channels per pixel, byte strides of w / h / n
+  int Cx;
+  long long x_sw, x_sh, x_sn;
 };
 
 template <int BN> struct Cfg {
@@ -51,7 +58,7 @@ template <int BN> struct Cfg {
 template <int BN, typename T>
 __global__ void __launch_bounds__(kThreads, 1)
 k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, T* __restrict__ out,
-             const ConvGeom g) {
+             const float* __restrict__ bias, const ConvGeom g) {
   using C = Cfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -66,7 +73,7 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int num_tiles = g.m_tiles * g.n_tiles;
-  const int c_chunks = g.C / BK;
+  const int c_chunks = (g.C + BK - 1) / BK;
   const int k_blocks = g.R * g.S * c_chunks;
 
   if (warp == 0 && lane == 0) {
@@ -95,7 +102,7 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         const int img = m0 / (g.P * g.Q);
         const int rem = m0 - img * (g.P * g.Q);
         const int p0 = rem / g.Q, q0 = rem - p0 * g.Q;
-        const int cw = q0 * g.stride - g.pad, ch = p0 * g.stride - g.pad;
+        const int cw = q0 * g.stride - g.pad_w, ch = p0 * g.stride - g.pad_h;
         for (int r = 0; r < g.R; ++r)
           for (int s = 0; s < g.S; ++s)
             for (int cc = 0; cc < c_chunks; ++cc) {
@@ -146,7 +153,15 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
       tc_fence_after();
       const long row = (long)mt * BM + quarter * 32 + lane;
       const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(quarter * 32) << 16);
-      T* orow = out + row * g.K + (long)nt * BN;
+      long opix = row;
+      if (g.os != 1 || g.OH != g.P || g.OW != g.Q) {       // strided / offset placement (parity classes of a strided dgrad)
+        const int pq = g.P * g.Q;
+        const long n = row / pq;
+        const int rem = (int)(row - n * pq);
+        const int p = rem / g.Q, q = rem - p * g.Q;
+        opix = (n * g.OH + (long)p * g.os + g.oa) * g.OW + (long)q * g.os + g.ob;
+      }
+      T* orow = out + opix * g.K + (long)nt * BN;
 #pragma unroll 1
       for (int c0 = 0; c0 < BN; c0 += 32) {
         uint32_t v[32];
@@ -156,13 +171,195 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
 #pragma unroll
           for (int j = 0; j < 32; j += 8) {
             if (nt * BN + c0 + j < g.K) {
+              float f[8];
+#pragma unroll
+              for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(v[j + e]);
+              if (bias != nullptr) {
+                const float4 b0 = *reinterpret_cast<const float4*>(bias + nt * BN + c0 + j);
+                const float4 b1 = *reinterpret_cast<const float4*>(bias + nt * BN + c0 + j + 4);
+                f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w;
+                f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
+              }
               uint4 o;
-              o.x = Cvt<T>::pack2(__uint_as_float(v[j + 0]), __uint_as_float(v[j + 1]));
-              o.y = Cvt<T>::pack2(__uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
-              o.z = Cvt<T>::pack2(__uint_as_float(v[j + 4]), __uint_as_float(v[j + 5]));
-              o.w = Cvt<T>::pack2(__uint_as_float(v[j + 6]), __uint_as_float(v[j + 7]));
+              o.x = Cvt<T>::pack2(f[0], f[1]);
+              o.y = Cvt<T>::pack2(f[2], f[3]);
+              o.z = Cvt<T>::pack2(f[4], f[5]);
+              o.w = Cvt<T>::pack2(f[6], f[7]);
               *reinterpret_cast<uint4*>(orow + c0 + j) = o;
             }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[acc]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, C::kTmemCols);
+  }
+}
+
+// ---- weight gradient --------------------------------------------------------------------------------------
+// dW[k][r][s][c] = sum_{n,p,q} dy[n,p,q,k] * x[n, p*stride - pad + r, q*stride - pad + s, c]
+// as a GEMM over the PIXEL dimension:  D[(r,s,c), k] = sum_pix X_im2col[pix, (r,s,c)] * dY[pix, k].
+// Both operands are "MN-major" for the tensor core (the reduction index is the row index in
+// memory), which tcgen05 reads directly from 128B-swizzled [pixel][64 channel] tiles:
+//   A: two 64-channel blocks (each one filter tap x 64 input channels) via IM2COL TMA, 64 pixels deep;
+//   B: BN/64 blocks of 64 output channels via tiled TMA on dy viewed as [pixels][Cout].
+// The pixel range is split across CTAs (split-K); partial tiles are accumulated into the fp32
+// gradient with red.global.add (the caller zeroes dW first).  TMEM lane = (tap, c) row, so a warp's
+// 32 lanes hit 32 consecutive floats of dW for a fixed k: coalesced reductions.
+// Replaces cudnnConvolutionBackwardFilter (distributed.py:262).
+struct WgradGeom {
+  ConvGeom c;
+  int rsc;                     // R*S*C
+  int m_tiles, n_tiles;        // over (r,s,c) in 128s, over Cout in BN
+  int k_steps;                 // ceil(M / 64)
+  int splits, steps_per_split;
+};
+
+constexpr int BKP = 64;        // pixels per k-step
+constexpr int kBlkBytes = BKP * 128;   // one [64 pixel][64 x 16 bit] block
+
+template <int BN> struct WCfg {
+  static constexpr int kStageBytesA = 2 * kBlkBytes;
+  static constexpr int kStageBytesB = (BN / 64) * kBlkBytes;
+  static constexpr int kStageBytes = kStageBytesA + kStageBytesB;
+  static constexpr int kStages = (BN >= 256) ? 4 : (BN >= 128 ? 6 : 8);
+  static constexpr int kTmemCols = 2 * BN;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256;
+};
+
+template <int BN, typename T>
+__global__ void __launch_bounds__(kThreads, 1)
+k_conv_wgrad(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmDY, float* __restrict__ dw,
+             const WgradGeom wg) {
+  using C = WCfg<BN>;
+  const ConvGeom& g = wg.c;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smA = smem;
+  uint8_t* smB = smem + C::kStages * C::kStageBytesA;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + C::kStages;
+  uint64_t* tfull = bars + 2 * C::kStages;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int items = wg.m_tiles * wg.n_tiles * wg.splits;
+  const int c_chunks = g.C / 64;
+  const int m_blocks = wg.rsc / 64;   // wgrad needs C % 64 == 0: an (r,s,c) block never straddles two taps
+
+  if (warp == 0 && lane == 0) { prefetch_tmap(&tmX); prefetch_tmap(&tmDY); }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < C::kStages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 4); }
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, C::kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int item = blockIdx.x; item < items; item += gridDim.x) {
+        const int sp = item % wg.splits;
+        const int tile = item / wg.splits;
+        const int mt = tile / wg.n_tiles, nt = tile % wg.n_tiles;
+        const int ks0 = sp * wg.steps_per_split;
+        const int ks1 = min(wg.k_steps, ks0 + wg.steps_per_split);
+        const int nA = min(2, m_blocks - mt * 2);
+        const int nB = min(BN / 64, (g.K - nt * BN + 63) / 64);
+        int tapr[2], taps[2], cc[2];
+        for (int b = 0; b < 2; ++b) {
+          const int gb = min(mt * 2 + b, m_blocks - 1);
+          const int tap = gb / c_chunks;
+          cc[b] = gb - tap * c_chunks;
+          tapr[b] = tap / g.S;
+          taps[b] = tap - tapr[b] * g.S;
+        }
+        for (int ks = ks0; ks < ks1; ++ks) {
+          const int m0 = ks * BKP;
+          const int img = m0 / (g.P * g.Q);
+          const int rem = m0 - img * (g.P * g.Q);
+          const int p0 = rem / g.Q, q0 = rem - p0 * g.Q;
+          const int cw = q0 * g.stride - g.pad_w, ch = p0 * g.stride - g.pad_h;
+          mbar_wait(&empty[stage], phase ^ 1);
+          mbar_expect_tx(&full[stage], (uint32_t)(nA + nB) * kBlkBytes);
+          for (int b = 0; b < nA; ++b)
+            tma_load_im2col_4d(smA + stage * C::kStageBytesA + b * kBlkBytes, &tmX, &full[stage], cc[b] * 64, cw, ch, img,
+                               (uint16_t)taps[b], (uint16_t)tapr[b]);
+          for (int j = 0; j < nB; ++j)
+            tma_load_2d(smB + stage * C::kStageBytesB + j * kBlkBytes, &tmDY, &full[stage], nt * BN + j * 64, m0);
+          if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(128, BN, std::is_same<T, __nv_bfloat16>::value ? 1 : 0, 1, 1);
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int item = blockIdx.x; item < items; item += gridDim.x, ++it) {
+        const int sp = item % wg.splits;
+        const int ks0 = sp * wg.steps_per_split;
+        const int ks1 = min(wg.k_steps, ks0 + wg.steps_per_split);
+        const int acc = it & 1;
+        const uint32_t acc_phase = (it >> 1) & 1;
+        mbar_wait(&tempty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + acc * BN;
+        for (int ks = ks0; ks < ks1; ++ks) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          // MN-major, 128B swizzle: 8-pixel groups 1024 B apart (SBO), 64-channel blocks kBlkBytes apart (LBO)
+          const uint64_t da = make_sw128_desc(smem_u32(smA + stage * C::kStageBytesA), 1024, kBlkBytes);
+          const uint64_t db = make_sw128_desc(smem_u32(smB + stage * C::kStageBytesB), 1024, kBlkBytes);
+#pragma unroll
+          for (int k = 0; k < BKP / 16; ++k)   // 16 pixels = 2048 bytes per UMMA_K step: +128 in the (addr >> 4) field
+            umma_f16(tmem_d, da + 128 * k, db + 128 * k, idesc, (ks > ks0 || k > 0) ? 1u : 0u);
+          umma_commit(&empty[stage]);
+          if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&tfull[acc]);
+      }
+    }
+  } else if (warp >= 4) {
+    const int quarter = warp & 3;
+    int it = 0;
+    for (int item = blockIdx.x; item < items; item += gridDim.x, ++it) {
+      const int tile = item / wg.splits;
+      const int mt = tile / wg.n_tiles, nt = tile % wg.n_tiles;
+      const int sp = item % wg.splits;
+      const bool nonempty = sp * wg.steps_per_split < wg.k_steps;
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1;
+      mbar_wait(&tfull[acc], acc_phase);
+      tc_fence_after();
+      const int m = mt * 128 + quarter * 32 + lane;           // (tap, c) index == column of dW's [Cout][R*S*C] view
+      const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(quarter * 32) << 16);
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld32(taddr + c0, v);
+        tmem_ld_wait();
+        if (m < wg.rsc && nonempty) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const int k = nt * BN + c0 + j;
+            if (k < g.K) atomicAdd(dw + (size_t)k * wg.rsc + m, __uint_as_float(v[j]));
           }
         }
       }
@@ -208,14 +405,14 @@ int load_driver_fns() {
 CUtensorMapDataType tm_dtype(int dtype) { return dtype == PDT_FP16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16; }
 
 template <int BN>
-int launch_fprop(const void* x, const void* w, void* y, int dtype, const ConvGeom& g, cudaStream_t stream) {
+int launch_fprop(const void* x, const void* w, void* y, const float* bias, int dtype, const ConvGeom& g, cudaStream_t stream) {
   using C = Cfg<BN>;
   CUtensorMap tmA, tmB;
   {
-    cuuint64_t dims[4] = {(cuuint64_t)g.C, (cuuint64_t)g.W, (cuuint64_t)g.H, (cuuint64_t)g.N};
-    cuuint64_t strides[3] = {(cuuint64_t)g.C * 2, (cuuint64_t)g.W * g.C * 2, (cuuint64_t)g.H * g.W * g.C * 2};
-    int lower[2] = {-g.pad, -g.pad};
-    int upper[2] = {g.pad - (g.S - 1), g.pad - (g.R - 1)};
+    cuuint64_t dims[4] = {(cuuint64_t)g.Cx, (cuuint64_t)g.W, (cuuint64_t)g.H, (cuuint64_t)g.N};
+    cuuint64_t strides[3] = {(cuuint64_t)g.x_sw, (cuuint64_t)g.x_sh, (cuuint64_t)g.x_sn};
+    int lower[2] = {-g.pad_w, -g.pad_h};
+    int upper[2] = {g.pad_hi_w - (g.S - 1), g.pad_hi_h - (g.R - 1)};
     cuuint32_t estr[4] = {1, (cuuint32_t)g.stride, (cuuint32_t)g.stride, 1};
     CUresult r = g_encode_im2col(&tmA, tm_dtype(dtype), 4, const_cast<void*>(x), dims, strides, lower, upper, BK, BM, estr,
                                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
@@ -225,7 +422,7 @@ int launch_fprop(const void* x, const void* w, void* y, int dtype, const ConvGeo
     // second descriptor word (the same fix-up CUTLASS applies in copy_traits_sm90_im2col.hpp).
     int drv = 0;
     cudaDriverGetVersion(&drv);
-    if (drv <= 13010 && (size_t)g.N * g.H * g.W * g.C * 2 < 131072)
+    if (drv <= 13010 && (size_t)g.N * (size_t)g.x_sn < 131072)
       reinterpret_cast<uint64_t*>(&tmA)[1] &= ~(1ull << 21);
   }
   {
@@ -246,38 +443,149 @@ int launch_fprop(const void* x, const void* w, void* y, int dtype, const ConvGeo
   if (dtype == PDT_FP16) {
     auto kern = k_conv_igemm<BN, __half>;
     PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
-    kern<<<grid, kThreads, C::kSmemBytes, stream>>>(tmA, tmB, reinterpret_cast<__half*>(y), g);
+    kern<<<grid, kThreads, C::kSmemBytes, stream>>>(tmA, tmB, reinterpret_cast<__half*>(y), bias, g);
   } else {
     auto kern = k_conv_igemm<BN, __nv_bfloat16>;
     PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
-    kern<<<grid, kThreads, C::kSmemBytes, stream>>>(tmA, tmB, reinterpret_cast<__nv_bfloat16*>(y), g);
+    kern<<<grid, kThreads, C::kSmemBytes, stream>>>(tmA, tmB, reinterpret_cast<__nv_bfloat16*>(y), bias, g);
   }
   return (int)cudaGetLastError();
+}
+
+template <int BN>
+int launch_wgrad(const void* x, const void* dy, float* dw, int dtype, WgradGeom& wg, cudaStream_t stream) {
+  using C = WCfg<BN>;
+  const ConvGeom& g = wg.c;
+  CUtensorMap tmX, tmDY;
+  {
+    cuuint64_t dims[4] = {(cuuint64_t)g.Cx, (cuuint64_t)g.W, (cuuint64_t)g.H, (cuuint64_t)g.N};
+    cuuint64_t strides[3] = {(cuuint64_t)g.x_sw, (cuuint64_t)g.x_sh, (cuuint64_t)g.x_sn};
+    int lower[2] = {-g.pad_w, -g.pad_h};
+    int upper[2] = {g.pad_hi_w - (g.S - 1), g.pad_hi_h - (g.R - 1)};
+    cuuint32_t estr[4] = {1, (cuuint32_t)g.stride, (cuuint32_t)g.stride, 1};
+    CUresult r = g_encode_im2col(&tmX, tm_dtype(dtype), 4, const_cast<void*>(x), dims, strides, lower, upper, 64, BKP, estr,
+                                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                                 CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return 10000 + (int)r;
+    int drv = 0;
+    cudaDriverGetVersion(&drv);
+    if (drv <= 13010 && (size_t)g.N * (size_t)g.x_sn < 131072)
+      reinterpret_cast<uint64_t*>(&tmX)[1] &= ~(1ull << 21);
+  }
+  {
+    cuuint64_t dims[2] = {(cuuint64_t)g.K, (cuuint64_t)g.M};
+    cuuint64_t strides[1] = {(cuuint64_t)g.K * 2};
+    cuuint32_t box[2] = {64, BKP};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = g_encode_tiled(&tmDY, tm_dtype(dtype), 2, const_cast<void*>(dy), dims, strides, box, estr,
+                                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return 20000 + (int)r;
+  }
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int tiles = wg.m_tiles * wg.n_tiles;
+  int splits = sms / tiles;                                   // one wave: never more work items than SMs
+  if (splits > wg.k_steps) splits = wg.k_steps;
+  if (splits < 1) splits = 1;
+  wg.steps_per_split = (wg.k_steps + splits - 1) / splits;
+  wg.splits = (wg.k_steps + wg.steps_per_split - 1) / wg.steps_per_split;
+  const int items = tiles * wg.splits;
+  const int grid = items < sms ? items : sms;
+  if (dtype == PDT_FP16) {
+    auto kern = k_conv_wgrad<BN, __half>;
+    PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+    kern<<<grid, kThreads, C::kSmemBytes, stream>>>(tmX, tmDY, dw, wg);
+  } else {
+    auto kern = k_conv_wgrad<BN, __nv_bfloat16>;
+    PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+    kern<<<grid, kThreads, C::kSmemBytes, stream>>>(tmX, tmDY, dw, wg);
+  }
+  return (int)cudaGetLastError();
+}
+
+void fill_dense(ConvGeom& g, int N, int H, int W, int C, int K, int R, int S, int stride, int pad) {
+  g.N = N; g.H = H; g.W = W; g.C = C; g.K = K; g.R = R; g.S = S; g.stride = stride;
+  g.pad_h = g.pad_w = g.pad_hi_h = g.pad_hi_w = pad;
+  g.P = (H + 2 * pad - R) / stride + 1;
+  g.Q = (W + 2 * pad - S) / stride + 1;
+  g.M = N * g.P * g.Q;
+  g.m_tiles = (g.M + BM - 1) / BM;
+  g.n_tiles = 0;
+  g.OH = g.P; g.OW = g.Q; g.os = 1; g.oa = g.ob = 0;
+  g.Cx = C;
+  g.x_sw = (long long)C * 2; g.x_sh = (long long)W * C * 2; g.x_sn = (long long)H * W * C * 2;
+}
+
+int dispatch_fprop(const void* x, const void* w, void* y, const float* bias, int dtype, ConvGeom& g, cudaStream_t stream) {
+  if (g.K <= 64) { g.n_tiles = 1; return launch_fprop<64>(x, w, y, bias, dtype, g, stream); }
+  if (g.K <= 128) { g.n_tiles = 1; return launch_fprop<128>(x, w, y, bias, dtype, g, stream); }
+  g.n_tiles = (g.K + 255) / 256;
+  return launch_fprop<256>(x, w, y, bias, dtype, g, stream);
 }
 
 }  // namespace
 
 extern "C" {
 
-// x: [N][H][W][C], w: [K][R][S][C], y: [N][P][Q][K]; C % 64 == 0, K % 8 == 0, square filter/stride/pad.
+// x: [N][H][W][C], dy: [N][P][Q][K] (bf16/fp16), dw: [K][R][S][C] fp32, ACCUMULATED into (zero it first).
+int pdt_conv_wgrad(const void* x, const void* dy, float* dw, int dtype, int N, int H, int W, int C, int K, int R, int S,
+                   int stride, int pad, cudaStream_t stream) {
+  if (dtype != PDT_BF16 && dtype != PDT_FP16) return PDT_E_UNSUPPORTED;
+  if (C % 64 || K % 8 || R < 1 || S < 1 || stride < 1 || pad < 0) return PDT_E_UNSUPPORTED;
+  if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(dw)) & 15) return PDT_E_UNSUPPORTED;
+  int e = load_driver_fns();
+  if (e) return e;
+  WgradGeom wg;
+  fill_dense(wg.c, N, H, W, C, K, R, S, stride, pad);
+  if (wg.c.P < 1 || wg.c.Q < 1) return PDT_E_UNSUPPORTED;
+  wg.rsc = R * S * C;
+  wg.m_tiles = (wg.rsc + 127) / 128;
+  wg.k_steps = (wg.c.M + BKP - 1) / BKP;
+  if (K <= 64) { wg.n_tiles = 1; return launch_wgrad<64>(x, dy, dw, dtype, wg, stream); }
+  if (K <= 128) { wg.n_tiles = 1; return launch_wgrad<128>(x, dy, dw, dtype, wg, stream); }
+  wg.n_tiles = (K + 255) / 256;
+  return launch_wgrad<256>(x, dy, dw, dtype, wg, stream);
+}
+
+// x: [N][H][W][C], w: [K][R][S][C], y: [N][P][Q][K]; C % 8 == 0, K % 8 == 0, square stride/pad.
 int pdt_conv_fprop(const void* x, const void* w, void* y, int dtype, int N, int H, int W, int C, int K, int R, int S,
                    int stride, int pad, cudaStream_t stream) {
   if (dtype != PDT_BF16 && dtype != PDT_FP16) return PDT_E_UNSUPPORTED;
-  if (C % BK || K % 8 || R < 1 || S < 1 || stride < 1 || pad < 0) return PDT_E_UNSUPPORTED;
+  if (C % 8 || K % 8 || R < 1 || S < 1 || stride < 1 || pad < 0) return PDT_E_UNSUPPORTED;
   if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(w) | reinterpret_cast<uintptr_t>(y)) & 15) return PDT_E_UNSUPPORTED;
   int e = load_driver_fns();
   if (e) return e;
   ConvGeom g;
-  g.N = N; g.H = H; g.W = W; g.C = C; g.K = K; g.R = R; g.S = S; g.stride = stride; g.pad = pad;
-  g.P = (H + 2 * pad - R) / stride + 1;
-  g.Q = (W + 2 * pad - S) / stride + 1;
+  fill_dense(g, N, H, W, C, K, R, S, stride, pad);
   if (g.P < 1 || g.Q < 1) return PDT_E_UNSUPPORTED;
-  g.M = N * g.P * g.Q;
+  return dispatch_fprop(x, w, y, nullptr, dtype, g, stream);
+}
+
+// General form.  Adds: an fp32 bias [K] in the epilogue (nn.Linear as a 1x1 convolution); separate
+// lower/upper padding and an explicit output size P x Q; placement of output pixel (p,q) at
+// (p*os + oa, q*os + ob) of an OH x OW image (one parity class of a strided data gradient);
+// explicit byte strides and per-pixel channel count of the activation as TMA should see it
+// (overlapping "pixels" let a space-to-depth stem read 4 neighbouring pixels as one 64-channel row).
+int pdt_conv_fprop_ex(const void* x, const void* w, void* y, const float* bias, int dtype, int N, int H, int W, int C,
+                      int Cx, long long x_sw, long long x_sh, long long x_sn, int K, int R, int S, int stride,
+                      int pad_lo_h, int pad_lo_w, int pad_hi_h, int pad_hi_w, int P, int Q, int OH, int OW, int os,
+                      int oa, int ob, cudaStream_t stream) {
+  if (dtype != PDT_BF16 && dtype != PDT_FP16) return PDT_E_UNSUPPORTED;
+  if (K % 8 || R < 1 || S < 1 || stride < 1 || P < 1 || Q < 1 || (x_sw | x_sh | x_sn) % 16) return PDT_E_UNSUPPORTED;
+  if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(w) | reinterpret_cast<uintptr_t>(y)) & 15) return PDT_E_UNSUPPORTED;
+  int e = load_driver_fns();
+  if (e) return e;
+  ConvGeom g;
+  g.N = N; g.H = H; g.W = W; g.C = C; g.K = K; g.R = R; g.S = S; g.stride = stride;
+  g.pad_h = pad_lo_h; g.pad_w = pad_lo_w; g.pad_hi_h = pad_hi_h; g.pad_hi_w = pad_hi_w;
+  g.P = P; g.Q = Q;
+  g.M = N * P * Q;
   g.m_tiles = (g.M + BM - 1) / BM;
-  if (K <= 64) { g.n_tiles = 1; return launch_fprop<64>(x, w, y, dtype, g, stream); }
-  if (K <= 128) { g.n_tiles = 1; return launch_fprop<128>(x, w, y, dtype, g, stream); }
-  g.n_tiles = (K + 255) / 256;
-  return launch_fprop<256>(x, w, y, dtype, g, stream);
+  g.OH = OH; g.OW = OW; g.os = os; g.oa = oa; g.ob = ob;
+  g.Cx = Cx; g.x_sw = x_sw; g.x_sh = x_sh; g.x_sn = x_sn;
+  return dispatch_fprop(x, w, y, bias, dtype, g, stream);
 }
 
 }  // extern "C"

@@ -14,6 +14,7 @@ from . import conv as _conv
 
 _vp, _i = _native._vp, _native._i
 _native.register("pdt_conv_fprop", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp])
+_native.register("pdt_conv_wgrad", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp])
 
 
 def supported(x, weight, stride, padding):
@@ -33,6 +34,23 @@ def fprop(x, w_lp, stride, pad):
                                                N, H, W, C, K, R, S, stride, pad, _native.stream_ptr(x.device)),
                   "pdt_conv_fprop")
     return y
+
+
+def wgrad(x, dy, weight_shape, stride, pad, out=None):
+    """fp32 dW [K,C,R,S] (channels_last, i.e. KRSC) from x [N,C,H,W] and dy [N,K,P,Q], both channels_last."""
+    N, C, H, W = x.shape
+    K, _, R, S = weight_shape
+    if out is None:
+        out = torch.empty((K, C, R, S), dtype=torch.float32, device=x.device, memory_format=torch.channels_last)
+    out.zero_()
+    _native.check(_native.lib().pdt_conv_wgrad(x.data_ptr(), dy.data_ptr(), out.data_ptr(), _native.dtype_code(x.dtype),
+                                               N, H, W, C, K, R, S, stride, pad, _native.stream_ptr(x.device)),
+                  "pdt_conv_wgrad")
+    return out
+
+
+def wgrad_supported(C, K):
+    return C % 64 == 0 and K % 64 == 0 and os.environ.get("PDT_WGRAD", "native") == "native"
 
 
 class _ConvNative(torch.autograd.Function):
@@ -55,9 +73,17 @@ class _ConvNative(torch.autograd.Function):
             # dx = conv(dy, flip(w)^T, pad' = R-1-pad): the same kernel with the roles of C and K swapped
             w_t = w_lp.flip(2, 3).transpose(0, 1).contiguous(memory_format=torch.channels_last)
             dx = fprop(dy, w_t, 1, R - 1 - padding[0])
-        dx2, dw, _ = torch.ops.aten.convolution_backward(
-            dy, x, w_lp, None, stride, padding, (1, 1), False, (0, 0), 1, (need_dx and not native_dx, True, False))
-        return (dx if native_dx else dx2), dw.float(), None, None, None
+        native_dw = wgrad_supported(C, K)
+        dw = wgrad(x, dy, w_lp.shape, stride[0], padding[0]) if native_dw else None
+        if (need_dx and not native_dx) or not native_dw:
+            dx2, dw2, _ = torch.ops.aten.convolution_backward(
+                dy, x, w_lp, None, stride, padding, (1, 1), False, (0, 0), 1,
+                (need_dx and not native_dx, not native_dw, False))
+            if not native_dx:
+                dx = dx2
+            if not native_dw:
+                dw = dw2.float()
+        return dx, dw, None, None, None
 
 
 def conv_native(x, weight, w_lp, stride, padding):

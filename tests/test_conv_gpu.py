@@ -51,3 +51,22 @@ def test_conv_autograd_matches_torch(native_lib, cin, cout, hw, k, stride, pad):
     assert (x.grad.float() - xf.grad).abs().max().item() <= 2e-2 * max(1.0, xf.grad.abs().max().item())
     assert wm.grad.dtype == torch.float32
     assert (wm.grad - wf.grad).abs().max().item() <= 3e-2 * max(1.0, wf.grad.abs().max().item())
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("cin,cout,hw,k,stride,pad", SHAPES)
+@pytest.mark.parametrize("batch", [2, 9])
+def test_conv_wgrad_matches_autograd(native_lib, dtype, cin, cout, hw, k, stride, pad, batch):
+    from pytorch_distributed_template_b200.ops import conv_native
+    torch.backends.cudnn.allow_tf32 = False
+    torch.manual_seed(2)
+    dev = torch.device("cuda", 0)
+    x = torch.randn(batch, cin, hw, hw, device=dev).to(dtype).contiguous(memory_format=torch.channels_last)
+    P = (hw + 2 * pad - k) // stride + 1
+    dy = (torch.randn(batch, cout, P, P, device=dev) / 8).to(dtype).contiguous(memory_format=torch.channels_last)
+    dw = conv_native.wgrad(x, dy, (cout, cin, k, k), stride, pad)
+    wf = torch.zeros(cout, cin, k, k, device=dev, requires_grad=True)
+    F.conv2d(x.float(), wf, None, stride, pad).backward(dy.float())
+    assert dw.dtype == torch.float32 and dw.shape == wf.grad.shape
+    err = (dw - wf.grad).abs().max().item()
+    assert err <= 2e-3 * max(1.0, wf.grad.abs().max().item()), (err, wf.grad.abs().max().item())
