@@ -151,6 +151,20 @@ int pdt_conv_fprop(const void* x, const void* w, void* y, int dtype, int N, int 
  * the pixel dimension with red.global.add, so zero dw first.  C % 64 == 0, K % 64 == 0. */
 int pdt_conv_wgrad(const void* x, const void* dy, float* dw, int dtype, int N, int H, int W, int C, int K, int R, int S,
                    int stride, int pad, cudaStream_t stream);
+/* General forms: fp32 bias [K] in the epilogue (nn.Linear as a 1x1 convolution, cuBLASLt GEMM + bias);
+ * separate lower/upper padding with an explicit output size; placement of output pixel (p,q) at
+ * (p*os + oa, q*os + ob) of an OH x OW image (one parity class of a strided data gradient, cuDNN strided
+ * dgrad); explicit byte strides / channels-per-pixel of the activation as TMA sees it (space-to-depth stem). */
+int pdt_conv_fprop_ex(const void* x, const void* w, void* y, const float* bias, int dtype, int N, int H, int W, int C,
+                      int Cx, long long x_sw, long long x_sh, long long x_sn, int K, int R, int S, int stride,
+                      int pad_lo_h, int pad_lo_w, int pad_hi_h, int pad_hi_w, int P, int Q, int OH, int OW, int os,
+                      int oa, int ob, cudaStream_t stream);
+int pdt_conv_wgrad_ex(const void* x, const void* dy, float* dw, int dtype, int N, int H, int W, int C, int Cx,
+                      long long x_sw, long long x_sh, long long x_sn, int K, int R, int S, int stride, int pad_lo_h,
+                      int pad_lo_w, int pad_hi_h, int pad_hi_w, int P, int Q, cudaStream_t stream);
+/* Stem input transform: NCHW fp32 -> 2x2 space-to-depth NHWC(16) low precision, zero padded by `pad`
+ * (autocast input cast + layout change for the 7x7 stride-2 stem of torchvision resnet). */
+int pdt_stem_s2d(const float* x, void* y, int dtype, int N, int H, int W, int pad, cudaStream_t stream);
 
 #ifdef __cplusplus
 }

@@ -549,6 +549,34 @@ int pdt_conv_wgrad(const void* x, const void* dy, float* dw, int dtype, int N, i
   return launch_wgrad<256>(x, dy, dw, dtype, wg, stream);
 }
 
+// General form of the weight gradient: explicit activation strides / per-pixel channel count, separate
+// lower/upper padding and output size (the space-to-depth stem, see pdt_conv_fprop_ex).
+int pdt_conv_wgrad_ex(const void* x, const void* dy, float* dw, int dtype, int N, int H, int W, int C, int Cx,
+                      long long x_sw, long long x_sh, long long x_sn, int K, int R, int S, int stride, int pad_lo_h,
+                      int pad_lo_w, int pad_hi_h, int pad_hi_w, int P, int Q, cudaStream_t stream) {
+  if (dtype != PDT_BF16 && dtype != PDT_FP16) return PDT_E_UNSUPPORTED;
+  if (C % 64 || K % 8 || R < 1 || S < 1 || stride < 1 || P < 1 || Q < 1 || (x_sw | x_sh | x_sn) % 16) return PDT_E_UNSUPPORTED;
+  if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(dw)) & 15) return PDT_E_UNSUPPORTED;
+  int e = load_driver_fns();
+  if (e) return e;
+  WgradGeom wg;
+  ConvGeom& g = wg.c;
+  g.N = N; g.H = H; g.W = W; g.C = C; g.K = K; g.R = R; g.S = S; g.stride = stride;
+  g.pad_h = pad_lo_h; g.pad_w = pad_lo_w; g.pad_hi_h = pad_hi_h; g.pad_hi_w = pad_hi_w;
+  g.P = P; g.Q = Q;
+  g.M = N * P * Q;
+  g.m_tiles = g.n_tiles = 0;
+  g.OH = P; g.OW = Q; g.os = 1; g.oa = g.ob = 0;
+  g.Cx = Cx; g.x_sw = x_sw; g.x_sh = x_sh; g.x_sn = x_sn;
+  wg.rsc = R * S * C;
+  wg.m_tiles = (wg.rsc + 127) / 128;
+  wg.k_steps = (g.M + BKP - 1) / BKP;
+  if (K <= 64) { wg.n_tiles = 1; return launch_wgrad<64>(x, dy, dw, dtype, wg, stream); }
+  if (K <= 128) { wg.n_tiles = 1; return launch_wgrad<128>(x, dy, dw, dtype, wg, stream); }
+  wg.n_tiles = (K + 255) / 256;
+  return launch_wgrad<256>(x, dy, dw, dtype, wg, stream);
+}
+
 // x: [N][H][W][C], w: [K][R][S][C], y: [N][P][Q][K]; C % 8 == 0, K % 8 == 0, square stride/pad.
 int pdt_conv_fprop(const void* x, const void* w, void* y, int dtype, int N, int H, int W, int C, int K, int R, int S,
                    int stride, int pad, cudaStream_t stream) {

@@ -152,17 +152,14 @@ __global__ void __launch_bounds__(256) k_maxpool_bwd(const T* __restrict__ dy, c
     float acc[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[j] = 0.f;
-    // outputs (ho, wo) whose window covers (hi, wi): ho*st - pd + kh == hi
-    for (int kh = 0; kh < ks; ++kh) {
-      const int t = hi + pd - kh;
-      if (t < 0 || t % st) continue;
-      const int ho = t / st;
-      if (ho >= Ho) continue;
-      for (int kw = 0; kw < ks; ++kw) {
-        const int u = wi + pd - kw;
-        if (u < 0 || u % st) continue;
-        const int wo = u / st;
-        if (wo >= Wo) continue;
+    // outputs (ho, wo) whose window covers (hi, wi): ho*st - pd + kh == hi with 0 <= kh < ks,
+    // i.e. ho in [ceil((hi + pd - ks + 1) / st), floor((hi + pd) / st)] — at most 2 x 2 for (3, 2, 1)
+    const int ho_lo = max(0, (hi + pd - ks + st) / st), ho_hi = min(Ho - 1, (hi + pd) / st);
+    const int wo_lo = max(0, (wi + pd - ks + st) / st), wo_hi = min(Wo - 1, (wi + pd) / st);
+    for (int ho = ho_lo; ho <= ho_hi; ++ho) {
+      const int kh = hi + pd - ho * st;
+      for (int wo = wo_lo; wo <= wo_hi; ++wo) {
+        const int kw = wi + pd - wo * st;
         const long o = (((long)n * Ho + ho) * Wo + wo) * C + c8 * 8;
         const uint2 pk = *reinterpret_cast<const uint2*>(idx + o);
         float g[8];
@@ -241,6 +238,44 @@ __global__ void __launch_bounds__(256) k_nchw_to_nhwc(const float* __restrict__ 
   }
 }
 
+// Stem input transform: x [N][3][H][W] fp32 (NCHW) -> y [N][HP][WP][16] low precision with
+//   y[n][i][j][(dy*2+dx)*3 + c] = xpad[n][c][2i+dy][2j+dx],  xpad = x zero-padded by `pad` on every side,
+// channels 12..15 zero (2x2 space-to-depth).  A 7x7 stride-2 pad-3 convolution over x becomes a
+// 4x4 stride-1 convolution over y whose four horizontal taps x 16 channels are 64 CONTIGUOUS
+// elements — exactly one 128-byte tensor-core K row (see ops/stem.py).
+template <typename T>
+__global__ void __launch_bounds__(256) k_stem_s2d(const float* __restrict__ x, T* __restrict__ y, int N, int H, int W, int HP, int WP,
+                                                 int pad) {
+  const long total = (long)N * HP * WP;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int j = (int)(i % WP);
+    long r = i / WP;
+    const int ii = (int)(r % HP);
+    const long n = r / HP;
+    float f[16];
+#pragma unroll
+    for (int e = 0; e < 16; ++e) f[e] = 0.f;
+#pragma unroll
+    for (int dy = 0; dy < 2; ++dy) {
+      const int yy = 2 * ii + dy - pad;
+#pragma unroll
+      for (int dx = 0; dx < 2; ++dx) {
+        const int xx = 2 * j + dx - pad;
+        if (yy >= 0 && yy < H && xx >= 0 && xx < W) {
+#pragma unroll
+          for (int c = 0; c < 3; ++c) f[(dy * 2 + dx) * 3 + c] = __ldg(x + ((n * 3 + c) * H + yy) * (long)W + xx);
+        }
+      }
+    }
+    float a[8], b[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) { a[e] = f[e]; b[e] = f[8 + e]; }
+    uint4* dst = reinterpret_cast<uint4*>(y + i * 16);
+    dst[0] = pack8<T>(a);
+    dst[1] = pack8<T>(b);
+  }
+}
+
 int grid_for(long total, int threads) {
   long nb = (total + threads - 1) / threads;
   if (nb < 1) nb = 1;
@@ -308,6 +343,13 @@ int pdt_avgpool_bwd(const void* dy, void* dx, int dtype, int N, int HW, int C, c
   if (C % 8) return PDT_E_UNSUPPORTED;
   LP_DISPATCH(dtype, k_avgpool_bwd<T><<<grid_for((long)N * HW * (C / 8), 256), 256, 0, stream>>>(
       reinterpret_cast<const T*>(dy), reinterpret_cast<T*>(dx), N, HW, C));
+  return (int)cudaGetLastError();
+}
+
+int pdt_stem_s2d(const float* x, void* y, int dtype, int N, int H, int W, int pad, cudaStream_t stream) {
+  const int HP = (H + 2 * pad + 1) / 2, WP = (W + 2 * pad + 1) / 2;
+  const int nb = grid_for((long)N * HP * WP, 256);
+  LP_DISPATCH(dtype, k_stem_s2d<T><<<nb, 256, 0, stream>>>(x, reinterpret_cast<T*>(y), N, H, W, HP, WP, pad));
   return (int)cudaGetLastError();
 }
 

@@ -16,6 +16,8 @@ from .. import amp
 from . import _native
 
 _conv_native = None   # set by ops.conv_native when the tcgen05 kernels are importable
+_stem_native = None   # (supported(x, conv), run(x, conv, w_lp))
+_linear_native = None
 
 
 def shadow_of(p, dtype):
@@ -50,11 +52,13 @@ def conv2d(x, conv):
     if lp is None or not x.is_cuda or conv.groups != 1 or conv.dilation != (1, 1) or conv.bias is not None \
             or conv.padding_mode != "zeros" or isinstance(conv.padding, str):
         return conv._conv_forward(x, conv.weight, conv.bias)
-    if x.dtype != lp or not x.is_contiguous(memory_format=torch.channels_last):
-        x = x.to(dtype=lp, memory_format=torch.channels_last)
     w_lp = shadow_of(conv.weight, lp)
     if w_lp is None:
         w_lp = conv.weight.detach().to(dtype=lp, memory_format=torch.channels_last)
+    if _stem_native is not None and _native.available() and _stem_native[0](x, conv):
+        return _stem_native[1](x, conv, w_lp)      # fp32 NCHW images: cast + layout change happen in the stem kernel
+    if x.dtype != lp or not x.is_contiguous(memory_format=torch.channels_last):
+        x = x.to(dtype=lp, memory_format=torch.channels_last)
     if _conv_native is not None and _native.available():
         y = _conv_native(x, conv.weight, w_lp, conv.stride, conv.padding)
         if y is not None:
@@ -87,4 +91,6 @@ def linear(x, fc):
     w_lp = shadow_of(fc.weight, lp)
     if w_lp is None:
         w_lp = fc.weight.detach().to(lp)
+    if _linear_native is not None and _native.available() and _linear_native[0](x, fc):
+        return _linear_native[1](x, fc, w_lp)
     return _LinearLP.apply(x, fc.weight, fc.bias, w_lp)

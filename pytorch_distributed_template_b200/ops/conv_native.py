@@ -1,38 +1,63 @@
-"""tcgen05 implicit-GEMM convolution (``csrc/conv.cu``) behind ``ops.conv2d``.
+"""tcgen05 implicit-GEMM convolution (``csrc/conv.cu``) behind ``ops.conv2d`` / ``ops.linear``.
 
-Forward and the stride-1 data gradient run on the native kernel; shapes it does not cover
-(the 3-channel stem, strided data gradients, and for now the weight gradient) go through
-``aten::convolution_backward`` with the same low-precision operands.  ``PDT_CONV=torch``
-disables the native path (A/B measurements, debugging).
+Native on the training path:
+  * forward of every conv with C_in % 64 == 0 (IM2COL-TMA fprop kernel);
+  * data gradient: stride 1 = the fprop kernel on dy with the flipped/transposed filter;
+    stride 2 = one fprop launch per output parity class (sub-filters of <= 2x2 taps), each
+    writing its own interleaved positions of dx;
+  * weight gradient: split-K kernel over the pixel dimension, fp32 result;
+  * the 7x7/2 stem (C_in = 3) through a 2x2 space-to-depth transform (``stem_*`` below);
+  * nn.Linear as a 1x1 convolution with a bias epilogue.
+``PDT_CONV=torch`` sends everything through ``aten::convolution*`` instead (A/B runs, debugging).
 """
 import os
 
 import torch
+import torch.nn.functional as F
 
 from . import _native
 from . import conv as _conv
 
-_vp, _i = _native._vp, _native._i
+_vp, _i, _ll = _native._vp, _native._i, _native.ctypes.c_longlong
 _native.register("pdt_conv_fprop", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp])
 _native.register("pdt_conv_wgrad", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp])
+_native.register("pdt_conv_fprop_ex", [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _ll, _ll, _ll, _i, _i, _i, _i,
+                                       _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp])
+_native.register("pdt_conv_wgrad_ex", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _ll, _ll, _ll, _i, _i, _i, _i,
+                                       _i, _i, _i, _i, _i, _i, _vp])
+_native.register("pdt_stem_s2d", [_vp, _vp, _i, _i, _i, _i, _i, _vp])
+
+CL = torch.channels_last
+
+
+def enabled():
+    return os.environ.get("PDT_CONV", "native") == "native"
 
 
 def supported(x, weight, stride, padding):
     K, C, R, S = weight.shape
     return (x.is_cuda and x.dtype in (torch.bfloat16, torch.float16) and C % 64 == 0 and K % 8 == 0
-            and stride[0] == stride[1] and padding[0] == padding[1] and R == S
-            and os.environ.get("PDT_CONV", "native") == "native")
+            and stride[0] == stride[1] and padding[0] == padding[1] and R == S and enabled())
 
 
+# ------------------------------------------------------------------------------------------ kernels
 def fprop(x, w_lp, stride, pad):
     """x: [N,C,H,W] channels_last, w_lp: [K,C,R,S] channels_last -> y [N,K,P,Q] channels_last."""
     N, C, H, W = x.shape
     K, _, R, S = w_lp.shape
     P, Q = (H + 2 * pad - R) // stride + 1, (W + 2 * pad - S) // stride + 1
-    y = torch.empty((N, K, P, Q), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
+    y = torch.empty((N, K, P, Q), dtype=x.dtype, device=x.device, memory_format=CL)
     _native.check(_native.lib().pdt_conv_fprop(x.data_ptr(), w_lp.data_ptr(), y.data_ptr(), _native.dtype_code(x.dtype),
                                                N, H, W, C, K, R, S, stride, pad, _native.stream_ptr(x.device)),
                   "pdt_conv_fprop")
+    return y
+
+
+def fprop_ex(x_ptr, w, y, bias, dtype, N, H, W, C, Cx, sw, sh, sn, K, R, S, stride, pads, P, Q, OH, OW, os_, oa, ob, device):
+    _native.check(_native.lib().pdt_conv_fprop_ex(
+        x_ptr, w.data_ptr(), y.data_ptr(), _native.ptr(bias), _native.dtype_code(dtype), N, H, W, C, Cx, sw, sh, sn,
+        K, R, S, stride, pads[0], pads[1], pads[2], pads[3], P, Q, OH, OW, os_, oa, ob, _native.stream_ptr(device)),
+        "pdt_conv_fprop_ex")
     return y
 
 
@@ -41,7 +66,7 @@ def wgrad(x, dy, weight_shape, stride, pad, out=None):
     N, C, H, W = x.shape
     K, _, R, S = weight_shape
     if out is None:
-        out = torch.empty((K, C, R, S), dtype=torch.float32, device=x.device, memory_format=torch.channels_last)
+        out = torch.empty((K, C, R, S), dtype=torch.float32, device=x.device, memory_format=CL)
     out.zero_()
     _native.check(_native.lib().pdt_conv_wgrad(x.data_ptr(), dy.data_ptr(), out.data_ptr(), _native.dtype_code(x.dtype),
                                                N, H, W, C, K, R, S, stride, pad, _native.stream_ptr(x.device)),
@@ -50,9 +75,56 @@ def wgrad(x, dy, weight_shape, stride, pad, out=None):
 
 
 def wgrad_supported(C, K):
-    return C % 64 == 0 and K % 64 == 0 and os.environ.get("PDT_WGRAD", "native") == "native"
+    return C % 64 == 0 and K % 8 == 0 and os.environ.get("PDT_WGRAD", "native") == "native"
 
 
+def _parity_taps(size_in, ksize, pad, a):
+    """Taps of the stride-2 data gradient that reach input rows h = 2i + a.
+    Returns (filter rows in increasing dy-offset order, lowest dy offset)."""
+    rs = [r for r in range(ksize) if (a + pad - r) % 2 == 0]
+    if not rs:
+        return [], 0
+    rs = sorted(rs, reverse=True)                 # decreasing r == increasing offset into dy
+    return rs, (a + pad - rs[0]) // 2
+
+
+def dgrad_stride2(dy, w_lp, x_shape, pad):
+    """dx for a stride-2 convolution: one fprop launch per parity class of the input grid."""
+    N, C, H, W = x_shape
+    K, _, R, S = w_lp.shape
+    _, _, P, Q = dy.shape
+    plan = []
+    for a in (0, 1):
+        rs, dh = _parity_taps(H, R, pad, a)
+        for b in (0, 1):
+            ss, dw_ = _parity_taps(W, S, pad, b)
+            if rs and ss and (dh > 0 or dw_ > 0):
+                return None                        # would need negative padding: not produced by ResNet shapes
+            plan.append((a, b, rs, ss, dh, dw_))
+    full = all(p[2] and p[3] for p in plan)
+    dx = torch.empty((N, C, H, W), dtype=dy.dtype, device=dy.device, memory_format=CL)
+    if not full:
+        dx.zero_()
+    sw, sh, sn = K * 2, Q * K * 2, P * Q * K * 2
+    for a, b, rs, ss, dh, dw_ in plan:
+        if not rs or not ss:
+            continue
+        Hs, Ws = (H - a + 1) // 2, (W - b + 1) // 2
+        if Hs <= 0 or Ws <= 0:
+            continue
+        idx_r = torch.tensor(rs, device=dy.device)
+        idx_s = torch.tensor(ss, device=dy.device)
+        w_sub = w_lp.index_select(2, idx_r).index_select(3, idx_s).transpose(0, 1).contiguous(memory_format=CL)
+        Th, Tw = len(rs), len(ss)
+        pads = (-dh, -dw_, Hs + dh + Th - 1 - P, Ws + dw_ + Tw - 1 - Q)
+        if pads[2] < 0 or pads[3] < 0:
+            return None
+        fprop_ex(dy.data_ptr(), w_sub, dx, None, dy.dtype, N, P, Q, K, K, sw, sh, sn, C, Th, Tw, 1, pads, Hs, Ws,
+                 H, W, 2, a, b, dy.device)
+    return dx
+
+
+# ------------------------------------------------------------------------------------------ autograd
 class _ConvNative(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, w_lp, stride, padding):
@@ -64,15 +136,18 @@ class _ConvNative(torch.autograd.Function):
     def backward(ctx, dy):
         x, w_lp = ctx.saved_tensors
         stride, padding = ctx.geom
-        dy = dy.contiguous(memory_format=torch.channels_last)
+        dy = dy.contiguous(memory_format=CL)
         K, C, R, S = w_lp.shape
         need_dx = ctx.needs_input_grad[0]
         dx = None
-        native_dx = need_dx and stride[0] == 1 and K % 64 == 0 and C % 8 == 0 and R - 1 - padding[0] >= 0
-        if native_dx:
-            # dx = conv(dy, flip(w)^T, pad' = R-1-pad): the same kernel with the roles of C and K swapped
-            w_t = w_lp.flip(2, 3).transpose(0, 1).contiguous(memory_format=torch.channels_last)
-            dx = fprop(dy, w_t, 1, R - 1 - padding[0])
+        if need_dx and K % 8 == 0 and C % 8 == 0:
+            if stride[0] == 1 and R - 1 - padding[0] >= 0:
+                # dx = conv(dy, flip(w)^T, pad' = R-1-pad): the same kernel with the roles of C and K swapped
+                w_t = w_lp.flip(2, 3).transpose(0, 1).contiguous(memory_format=CL)
+                dx = fprop(dy, w_t, 1, R - 1 - padding[0])
+            elif stride[0] == 2:
+                dx = dgrad_stride2(dy, w_lp, x.shape, padding[0])
+        native_dx = dx is not None
         native_dw = wgrad_supported(C, K)
         dw = wgrad(x, dy, w_lp.shape, stride[0], padding[0]) if native_dw else None
         if (need_dx and not native_dx) or not native_dw:
@@ -89,9 +164,118 @@ class _ConvNative(torch.autograd.Function):
 def conv_native(x, weight, w_lp, stride, padding):
     if not supported(x, weight, stride, padding):
         return None
-    if not w_lp.is_contiguous(memory_format=torch.channels_last):
-        w_lp = w_lp.contiguous(memory_format=torch.channels_last)
+    if not w_lp.is_contiguous(memory_format=CL):
+        w_lp = w_lp.contiguous(memory_format=CL)
     return _ConvNative.apply(x, weight, w_lp, tuple(stride), tuple(padding))
 
 
+# ------------------------------------------------------------------------------------------ stem (7x7/2, C_in = 3)
+def stem_weight_s2d(w_lp):
+    """[K,3,7,7] -> [K,4,4,16] (k, r', s', (dy,dx,c) padded to 16): filter of the equivalent 4x4/1 conv."""
+    K = w_lp.shape[0]
+    wp = F.pad(w_lp, (0, 1, 0, 1))                                   # 8x8, zero last row/col
+    wp = wp.reshape(K, 3, 4, 2, 4, 2).permute(0, 2, 4, 3, 5, 1)       # k, r', s', dy, dx, c
+    wp = wp.reshape(K, 4, 4, 12)
+    return F.pad(wp, (0, 4)).contiguous()
+
+
+def stem_weight_grad_from_s2d(dwp, K):
+    """inverse of stem_weight_s2d for the fp32 gradient: [K,4,4,16] -> [K,3,7,7]."""
+    g = dwp.reshape(K, 4, 4, 16)[..., :12].reshape(K, 4, 4, 2, 2, 3).permute(0, 5, 1, 3, 2, 4)   # k,c,r',dy,s',dx
+    return g.reshape(K, 3, 8, 8)[:, :, :7, :7]
+
+
+def stem_supported(x, conv):
+    return (enabled() and x.is_cuda and x.dtype == torch.float32 and x.dim() == 4 and x.shape[1] == 3
+            and conv.kernel_size == (7, 7) and conv.stride == (2, 2) and conv.padding == (3, 3)
+            and conv.out_channels % 8 == 0 and x.shape[2] % 2 == 0 and x.shape[3] % 2 == 0
+            and os.environ.get("PDT_STEM", "native") == "native")
+
+
+class _StemNative(torch.autograd.Function):
+    """conv1 of torchvision ResNet on fp32 NCHW images: space-to-depth + 4x4/1 implicit GEMM."""
+
+    @staticmethod
+    def forward(ctx, x, weight, w_lp):
+        N, _, H, W = x.shape
+        K = weight.shape[0]
+        lp = w_lp.dtype
+        HP, WP = (H + 6) // 2, (W + 6) // 2
+        P, Q = HP - 3, WP - 3
+        xs = torch.empty((N, HP, WP, 16), dtype=lp, device=x.device)
+        x = x.contiguous()
+        _native.check(_native.lib().pdt_stem_s2d(x.data_ptr(), xs.data_ptr(), _native.dtype_code(lp), N, H, W, 3,
+                                                 _native.stream_ptr(x.device)), "pdt_stem_s2d")
+        wp = stem_weight_s2d(w_lp)
+        y = torch.empty((N, K, P, Q), dtype=lp, device=x.device, memory_format=CL)
+        # TMA view of xs: "pixel" q = 64 contiguous elements starting at column q (4 neighbours x 16 ch)
+        sw, sh, sn = 32, WP * 32, HP * WP * 32
+        fprop_ex(xs.data_ptr(), wp, y, None, lp, N, HP, Q, 64, 64, sw, sh, sn, K, 4, 1, 1, (0, 0, 0, 0), P, Q, P, Q, 1, 0, 0,
+                 x.device)
+        ctx.save_for_backward(xs)
+        ctx.geom = (N, HP, WP, P, Q, K)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (xs,) = ctx.saved_tensors
+        N, HP, WP, P, Q, K = ctx.geom
+        dy = dy.contiguous(memory_format=CL)
+        dwp = torch.zeros((K, 256), dtype=torch.float32, device=dy.device)
+        sw, sh, sn = 32, WP * 32, HP * WP * 32
+        _native.check(_native.lib().pdt_conv_wgrad_ex(
+            xs.data_ptr(), dy.data_ptr(), dwp.data_ptr(), _native.dtype_code(dy.dtype), N, HP, Q, 64, 64, sw, sh, sn,
+            K, 4, 1, 1, 0, 0, 0, 0, P, Q, _native.stream_ptr(dy.device)), "pdt_conv_wgrad_ex")
+        return None, stem_weight_grad_from_s2d(dwp, K), None
+
+
+def stem_native(x, conv, w_lp):
+    return _StemNative.apply(x, conv.weight, w_lp)
+
+
+# ------------------------------------------------------------------------------------------ linear
+class _LinearNative(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, w_lp):
+        B, C = x.shape
+        K = w_lp.shape[0]
+        x = x.contiguous()
+        y = torch.empty((B, K), dtype=x.dtype, device=x.device)
+        bias32 = bias.detach().float().contiguous() if bias is not None else None
+        fprop_ex(x.data_ptr(), w_lp, y, bias32, x.dtype, B, 1, 1, C, C, C * 2, C * 2, C * 2, K, 1, 1, 1, (0, 0, 0, 0),
+                 1, 1, 1, 1, 1, 0, 0, x.device)
+        ctx.save_for_backward(x, w_lp)
+        ctx.has_bias = bias is not None
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w_lp = ctx.saved_tensors
+        B, C = x.shape
+        K = w_lp.shape[0]
+        dy = dy.contiguous()
+        dx = None
+        if ctx.needs_input_grad[0]:
+            w_t = w_lp.t().contiguous()                      # [C][K]: "filter" of the transposed product
+            dx = torch.empty((B, C), dtype=dy.dtype, device=dy.device)
+            fprop_ex(dy.data_ptr(), w_t, dx, None, dy.dtype, B, 1, 1, K, K, K * 2, K * 2, K * 2, C, 1, 1, 1, (0, 0, 0, 0),
+                     1, 1, 1, 1, 1, 0, 0, dy.device)
+        dw = torch.zeros((K, C), dtype=torch.float32, device=dy.device)
+        _native.check(_native.lib().pdt_conv_wgrad(x.data_ptr(), dy.data_ptr(), dw.data_ptr(), _native.dtype_code(dy.dtype),
+                                                   B, 1, 1, C, K, 1, 1, 1, 0, _native.stream_ptr(dy.device)), "pdt_conv_wgrad(fc)")
+        db = dy.float().sum(0) if ctx.has_bias else None
+        return dx, dw, db, None
+
+
+def linear_supported(x, fc):
+    return (enabled() and x.is_cuda and x.dim() == 2 and x.dtype in (torch.bfloat16, torch.float16)
+            and fc.in_features % 64 == 0 and fc.out_features % 8 == 0)
+
+
+def linear_native(x, fc, w_lp):
+    return _LinearNative.apply(x, fc.weight, fc.bias, w_lp.contiguous())
+
+
 _conv._conv_native = conv_native
+_conv._stem_native = (stem_supported, stem_native)
+_conv._linear_native = (linear_supported, linear_native)

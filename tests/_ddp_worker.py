@@ -92,6 +92,10 @@ def main():
     t = torch.tensor([float(rank + 1), 2.0 * (rank + 1)], device=device)
     ours.fabric.allreduce_small_(t, mean=True)
     out["reduce_mean"] = t.tolist()
+    res_dir = os.environ.get("PDT_RESULT_DIR")
+    if res_dir:       # one file per rank: stdout lines of concurrent ranks can interleave
+        with open(os.path.join(res_dir, "rank{}.json".format(rank)), "w") as f:
+            json.dump(out, f)
     print("RESULT " + json.dumps(out), flush=True)
     env.shutdown_distributed()
 

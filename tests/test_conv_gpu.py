@@ -70,3 +70,68 @@ def test_conv_wgrad_matches_autograd(native_lib, dtype, cin, cout, hw, k, stride
     assert dw.dtype == torch.float32 and dw.shape == wf.grad.shape
     err = (dw - wf.grad).abs().max().item()
     assert err <= 2e-3 * max(1.0, wf.grad.abs().max().item()), (err, wf.grad.abs().max().item())
+
+
+@pytest.mark.parametrize("cin,cout,hw,k,stride,pad", [s for s in SHAPES if s[4] == 2])
+def test_strided_dgrad_native(native_lib, cin, cout, hw, k, stride, pad):
+    from pytorch_distributed_template_b200.ops import conv_native
+    torch.backends.cudnn.allow_tf32 = False
+    torch.manual_seed(4)
+    dev = torch.device("cuda", 0)
+    dtype = torch.bfloat16
+    w = (torch.randn(cout, cin, k, k, device=dev) / (cin * k * k) ** 0.5).to(dtype).contiguous(memory_format=torch.channels_last)
+    P = (hw + 2 * pad - k) // stride + 1
+    dy = torch.randn(3, cout, P, P, device=dev).to(dtype).contiguous(memory_format=torch.channels_last)
+    dx = conv_native.dgrad_stride2(dy, w, (3, cin, hw, hw), pad)
+    assert dx is not None
+    xf = torch.zeros(3, cin, hw, hw, device=dev, requires_grad=True)
+    F.conv2d(xf, w.float(), None, stride, pad).backward(dy.float())
+    assert (dx.float() - xf.grad).abs().max().item() <= 2e-2 * max(1.0, xf.grad.abs().max().item())
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("batch,hw", [(4, 224), (3, 64)])
+def test_stem_space_to_depth(native_lib, dtype, batch, hw):
+    from pytorch_distributed_template_b200.ops import conv_native
+    torch.backends.cudnn.allow_tf32 = False
+    torch.manual_seed(5)
+    dev = torch.device("cuda", 0)
+    conv = torch.nn.Conv2d(3, 64, 7, 2, 3, bias=False).to(dev)
+    x = torch.randn(batch, 3, hw, hw, device=dev)
+    assert conv_native.stem_supported(x, conv)
+    w_lp = conv.weight.detach().to(dtype)
+    y = conv_native.stem_native(x, conv, w_lp)
+    ref = F.conv2d(x.to(dtype).float(), w_lp.float(), None, 2, 3)
+    tol = 2e-2 if dtype == torch.bfloat16 else 3e-3
+    assert y.shape == ref.shape
+    assert (y.float() - ref).abs().max().item() <= tol * max(1.0, ref.abs().max().item())
+    dy = (torch.randn_like(ref) / 16).to(dtype).contiguous(memory_format=torch.channels_last)
+    y.backward(dy)
+    wf = w_lp.float().requires_grad_(True)
+    F.conv2d(x.to(dtype).float(), wf, None, 2, 3).backward(dy.float())
+    assert conv.weight.grad.shape == (64, 3, 7, 7)
+    assert (conv.weight.grad - wf.grad).abs().max().item() <= 3e-3 * max(1.0, wf.grad.abs().max().item())
+
+
+@pytest.mark.parametrize("B", [150, 37])
+def test_linear_native(native_lib, B):
+    from pytorch_distributed_template_b200.ops import conv_native
+    torch.manual_seed(6)
+    dev = torch.device("cuda", 0)
+    dtype = torch.bfloat16
+    fc = torch.nn.Linear(512, 1000).to(dev)
+    x = torch.randn(B, 512, device=dev).to(dtype).requires_grad_(True)
+    assert conv_native.linear_supported(x, fc)
+    w_lp = fc.weight.detach().to(dtype)
+    y = conv_native.linear_native(x, fc, w_lp)
+    xf = x.detach().float().requires_grad_(True)
+    wf = w_lp.float().requires_grad_(True)
+    bf = fc.bias.detach().clone().requires_grad_(True)
+    ref = F.linear(xf, wf, bf)
+    assert (y.float() - ref).abs().max().item() <= 2e-2 * max(1.0, ref.abs().max().item())
+    dy = (torch.randn(B, 1000, device=dev) / 8).to(dtype)
+    y.backward(dy)
+    ref.backward(dy.float())
+    assert (x.grad.float() - xf.grad).abs().max().item() <= 2e-2 * max(1.0, xf.grad.abs().max().item())
+    assert (fc.weight.grad - wf.grad).abs().max().item() <= 3e-3 * max(1.0, wf.grad.abs().max().item())
+    assert torch.allclose(fc.bias.grad, bf.grad, rtol=1e-3, atol=1e-3)

@@ -13,11 +13,12 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 def _launch(extra, nproc=2, port=29621, timeout=600):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(nproc),
            "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(HERE, "_ddp_worker.py")] + extra
-    env = dict(os.environ, OMP_NUM_THREADS="2")
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env=env)
-    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
-    outs = [json.loads(l[len("RESULT "):]) for l in r.stdout.splitlines() if l.startswith("RESULT ")]
-    assert len(outs) == nproc, r.stdout[-2000:]
+    import tempfile
+    with tempfile.TemporaryDirectory() as d:
+        env = dict(os.environ, OMP_NUM_THREADS="2", PDT_RESULT_DIR=d)
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env=env)
+        assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+        outs = [json.load(open(os.path.join(d, "rank{}.json".format(i)))) for i in range(nproc)]
     return outs
 
 

@@ -19,9 +19,11 @@ def _ngpu():
 def _launch(extra, nproc, port):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(nproc),
            "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(HERE, "_ddp_worker.py"), "--cuda"] + extra
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
-    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
-    return [json.loads(l[len("RESULT "):]) for l in r.stdout.splitlines() if l.startswith("RESULT ")]
+    import tempfile
+    with tempfile.TemporaryDirectory() as d:
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, env=dict(os.environ, PDT_RESULT_DIR=d))
+        assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+        return [json.load(open(os.path.join(d, "rank{}.json".format(i)))) for i in range(nproc)]
 
 
 @pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
