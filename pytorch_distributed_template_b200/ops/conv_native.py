@@ -88,6 +88,19 @@ def _parity_taps(size_in, ksize, pad, a):
     return rs, (a + pad - rs[0]) // 2
 
 
+_index_cache = {}
+
+
+def _index_tensor(values, device):
+    """Small index tensors are created once (an H2D copy is not allowed inside a graph capture)."""
+    key = (tuple(values), device)
+    t = _index_cache.get(key)
+    if t is None:
+        t = torch.tensor(list(values), device=device)
+        _index_cache[key] = t
+    return t
+
+
 def dgrad_stride2(dy, w_lp, x_shape, pad):
     """dx for a stride-2 convolution: one fprop launch per parity class of the input grid."""
     N, C, H, W = x_shape
@@ -112,8 +125,8 @@ def dgrad_stride2(dy, w_lp, x_shape, pad):
         Hs, Ws = (H - a + 1) // 2, (W - b + 1) // 2
         if Hs <= 0 or Ws <= 0:
             continue
-        idx_r = torch.tensor(rs, device=dy.device)
-        idx_s = torch.tensor(ss, device=dy.device)
+        idx_r = _index_tensor(rs, dy.device)
+        idx_s = _index_tensor(ss, dy.device)
         w_sub = w_lp.index_select(2, idx_r).index_select(3, idx_s).transpose(0, 1).contiguous(memory_format=CL)
         Th, Tw = len(rs), len(ss)
         pads = (-dh, -dw_, Hs + dh + Th - 1 - P, Ws + dw_ + Tw - 1 - Q)

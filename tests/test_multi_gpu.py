@@ -46,3 +46,51 @@ def test_syncbn_native_matches_torch_syncbn(native_lib):
         assert o["ranks_identical"], o
         assert o["first_param_rel"] < 1e-3, o
         assert o["bn_buffer_rel"] < 1e-3, o
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
+def test_dataparallel_matches_torch_dataparallel(native_lib):
+    """Single-process DataParallel: peer-copy scatter/gather, per-device reduce + SGD + weight push."""
+    import copy
+    import torch.nn.functional as F
+    import torchvision
+    from pytorch_distributed_template_b200 import optim
+    from pytorch_distributed_template_b200.models import create_model
+    from pytorch_distributed_template_b200.parallel import DataParallel
+    n = 2
+    torch.manual_seed(21)
+    net = create_model("resnet18", num_classes=10)
+    tv = torchvision.models.resnet18(num_classes=10)
+    tv.load_state_dict(net.state_dict())
+    ours = DataParallel(net, device_ids=list(range(n))).cuda()
+    theirs = torch.nn.DataParallel(tv, device_ids=list(range(n))).cuda()
+    o1 = optim.SGD(ours.parameters(), 0.01, momentum=0.9, weight_decay=1e-4)
+    o2 = torch.optim.SGD(theirs.parameters(), 0.01, momentum=0.9, weight_decay=1e-4)
+    g = torch.Generator().manual_seed(3)
+    first = None
+    for it in range(3):
+        x = torch.randn(8 * n, 3, 64, 64, generator=g).cuda()
+        y = torch.randint(0, 10, (8 * n,), generator=g).cuda()
+        for model, opt in ((ours, o1), (theirs, o2)):
+            model.train()
+            out = model(x)
+            assert out.shape == (8 * n, 10) and out.device.index == 0
+            loss = F.cross_entropy(out, y)
+            opt.zero_grad()
+            loss.backward()
+            opt.step()
+        for d in range(n):
+            torch.cuda.synchronize(d)
+        worst = max(((p.detach() - q.detach()).abs().max() / (q.detach().abs().max() + 1e-12)).item()
+                    for p, q in zip(ours.module.parameters(), theirs.module.parameters()))
+        first = worst if first is None else first
+    assert first < 1e-4, first
+    assert worst < 5e-2, worst
+    # replicas hold the same weights as the module (the optimizer kernel pushed them)
+    for rep in ours.replicas[1:]:
+        for p, q in zip(rep.parameters(), ours.module.parameters()):
+            assert torch.equal(p.detach().cpu(), q.detach().cpu())
+    assert all(k.startswith("module.") for k in ours.state_dict())
+    ours.eval()
+    with torch.no_grad():
+        assert ours(torch.randn(4 * n, 3, 64, 64).cuda()).shape == (4 * n, 10)
