@@ -105,6 +105,20 @@ size_t pdt_bn_scratch_bytes(int C);
 int pdt_bn_fwd_stats(const void* x, long M, int C, int dtype, void* scratch, const PdtCommDesc* comm,
                      float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
                      float* save_invstd, cudaStream_t stream);
+/* Allocation-free BatchNorm statistics (no counterpart in the reference: it exists for callers of THIS
+ * library that cannot allocate the scratch buffer pdt_bn_fwd_stats needs — code inside latency-critical
+ * or graph-replayed loops where cudaMalloc is off limits because it synchronises the device, plugins
+ * that must not grow a host framework's memory pool, C callers without an allocator).  Same result as
+ * pdt_bn_fwd_stats with comm == NULL; the scratch is a fixed array inside the library.
+ *   limit   : C <= PDT_BN_STATIC_MAX_C, else PDT_E_TOO_LARGE; each GPU that loads the library keeps
+ *             PDT_BN_STATIC_SCRATCH_BYTES resident until exit;
+ *   sharing : all calls on a device use the same array; calls that may overlap on the GPU race;
+ *   set-up  : the first call on each device looks the array's address up — do it before any stream capture.
+ * Calls no cudaMalloc / cudaFree / allocating routine. */
+#define PDT_BN_STATIC_MAX_C 512
+#define PDT_BN_STATIC_SCRATCH_BYTES (256 + PDT_BN_MAX_BLOCKS * 2 * PDT_BN_STATIC_MAX_C * 4)
+int pdt_bn_fwd_stats_noalloc(const void* x, long M, int C, int dtype, float* running_mean, float* running_var,
+                             float momentum, float eps, float* save_mean, float* save_invstd, cudaStream_t stream);
 int pdt_bn_fwd_apply(const void* x, const void* res, void* y, long M, int C, int dtype, const float* mean,
                      const float* stat2, const float* gamma, const float* beta, int relu, int eval, float eps,
                      cudaStream_t stream);

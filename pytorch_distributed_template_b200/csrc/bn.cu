@@ -359,6 +359,57 @@ int pdt_bn_fwd_stats(const void* x, long M, int C, int dtype, void* scratch, con
   return (int)cudaGetLastError();
 }
 
+// ---- allocation-free variant of pdt_bn_fwd_stats ---------------------------------------------------
+// Some callers cannot hand us a scratch buffer because they cannot allocate one at the point of the
+// call: code running inside a CUDA-graph-replayed region or a real-time inference/training loop that
+// forbids cudaMalloc (it synchronises the device), plugins living under a foreign framework's memory
+// pool that must not be grown, and plain C callers with no allocator of their own.  For them the
+// scratch (ticket counter + per-block partial sums) lives in this file-scope device array instead.
+//   * fixed size: channels <= PDT_BN_STATIC_MAX_C; larger C is refused with PDT_E_TOO_LARGE;
+//   * every GPU that loads the library holds these ~2.3 MiB until the process exits;
+//   * the array is SHARED by all calls on a device and keeps the last call's contents: the words that
+//     must start at zero (the ticket counter block) are cleared on the caller's stream before every
+//     launch, and two calls whose kernels can overlap on one GPU (different streams) race;
+//   * the first call on a device resolves the array's device address (cudaGetSymbolAddress) — make
+//     that first call outside any stream capture.
+// Nothing here calls cudaMalloc, cudaFree or any allocating routine.
+static __device__ __align__(256) unsigned char g_bn_static_scratch[PDT_BN_STATIC_SCRATCH_BYTES];
+
+static void* g_bn_static_ptr[64];        // per device; filled once, with that device current
+static bool g_bn_static_ready[64];
+
+static int bn_static_scratch_for_current_device(void** out) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= 64) return (int)cudaErrorInvalidDevice;
+  if (!g_bn_static_ready[dev]) {
+    // In host code the array's name is only a handle for the runtime, not a device address.
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_bn_static_scratch);
+    if (e != cudaSuccess) return (int)e;
+    if (p == nullptr) return (int)cudaErrorInvalidSymbol;
+    g_bn_static_ptr[dev] = p;
+    g_bn_static_ready[dev] = true;
+  }
+  *out = g_bn_static_ptr[dev];
+  return 0;
+}
+
+int pdt_bn_fwd_stats_noalloc(const void* x, long M, int C, int dtype, float* running_mean, float* running_var,
+                             float momentum, float eps, float* save_mean, float* save_invstd, cudaStream_t stream) {
+  if (C > PDT_BN_STATIC_MAX_C) return PDT_E_TOO_LARGE;
+  if (pdt_bn_scratch_bytes(C) > (size_t)PDT_BN_STATIC_SCRATCH_BYTES) return PDT_E_TOO_LARGE;
+  void* scratch = nullptr;
+  int rc = bn_static_scratch_for_current_device(&scratch);
+  if (rc != 0) return rc;
+  // the ticket counter must read zero when the kernel starts, whatever an earlier call left behind
+  cudaError_t e = cudaMemsetAsync(scratch, 0, 256, stream);
+  if (e != cudaSuccess) return (int)e;
+  return pdt_bn_fwd_stats(x, M, C, dtype, scratch, nullptr, running_mean, running_var, momentum, eps, save_mean,
+                          save_invstd, stream);
+}
+
 int pdt_bn_fwd_apply(const void* x, const void* res, void* y, long M, int C, int dtype, const float* mean,
                      const float* stat2, const float* gamma, const float* beta, int relu, int eval, float eps,
                      cudaStream_t stream) {
