@@ -122,12 +122,27 @@ int pdt_bn_fwd_stats_noalloc(const void* x, long M, int C, int dtype, float* run
 int pdt_bn_fwd_apply(const void* x, const void* res, void* y, long M, int C, int dtype, const float* mean,
                      const float* stat2, const float* gamma, const float* beta, int relu, int eval, float eps,
                      cudaStream_t stream);
+/* y may be NULL when relu != 0 and no residual entered the ReLU: the mask is then recomputed from x. */
 int pdt_bn_bwd_reduce(const void* dy, const void* y, const void* x, long M, int C, int dtype, const float* mean,
-                      const float* invstd, int relu, void* scratch, const PdtCommDesc* comm, float* dgamma,
-                      float* dbeta, float* out_k, cudaStream_t stream);
+                      const float* invstd, const float* gamma, const float* beta, int relu, void* scratch,
+                      const PdtCommDesc* comm, float* dgamma, float* dbeta, float* out_k, cudaStream_t stream);
 int pdt_bn_bwd_apply(const void* dy, const void* y, const void* x, void* dx, void* dres, long M, int C, int dtype,
-                     const float* mean, const float* invstd, const float* gamma, const float* k, int relu,
-                     cudaStream_t stream);
+                     const float* mean, const float* invstd, const float* gamma, const float* beta, const float* k,
+                     int relu, cudaStream_t stream);
+
+/* BatchNorm + ReLU + MaxPool fused (ResNet stem tail: batch_norm + relu_ + max_pool2d_with_indices and
+ * their backward kernels).  The normalised tensor is never written: forward pools relu(bn(x)) straight
+ * from the conv output x; backward gathers the pooled gradient through the saved arg-max taps and
+ * recomputes the ReLU mask from x.  Statistics come from pdt_bn_fwd_stats on x. */
+int pdt_bn_pool_fwd(const void* x, void* y, int8_t* idx, int dtype, int N, int H, int W, int C, int ks, int st, int pd,
+                    const float* mean, const float* invstd, const float* gamma, const float* beta, cudaStream_t stream);
+int pdt_bn_pool_bwd_reduce(const void* dpool, const int8_t* idx, const void* x, int dtype, int N, int H, int W, int C,
+                           int ks, int st, int pd, const float* mean, const float* invstd, const float* gamma,
+                           const float* beta, void* scratch, const PdtCommDesc* comm, float* dgamma, float* dbeta,
+                           float* out_k, cudaStream_t stream);
+int pdt_bn_pool_bwd_apply(const void* dpool, const int8_t* idx, const void* x, void* dx, int dtype, int N, int H, int W,
+                          int C, int ks, int st, int pd, const float* mean, const float* invstd, const float* gamma,
+                          const float* beta, const float* k, cudaStream_t stream);
 
 /* ---- loss / pooling / layout ----------------------------------------------
  * pdt_ce_fwd: nn.CrossEntropyLoss (mean) + utils.accuracy top-1 in one pass
@@ -154,13 +169,21 @@ int pdt_nchw_to_nhwc(const float* x, void* y, int dtype, int N, int Cin, int H, 
 int pdt_peer_copy(const void* src, void* dst, size_t nbytes, cudaStream_t stream);
 
 /* ---- implicit-GEMM convolution on tcgen05 / TMEM / TMA --------------------
- * x: [N][H][W][C], w: [K][R][S][C] (KRSC), y: [N][P][Q][K], all bf16 or fp16; C % 64 == 0,
- * K % 8 == 0, 16-byte aligned pointers.  Forward convolution of nn.Conv2d (cuDNN
+ * x: [N][H][W][C], w: [K][R][S][C] (KRSC), y: [N][P][Q][K], all bf16, fp16 (kind::f16) or fp32
+ * (kind::tf32: operands read as TF32, fp32 accumulate, like cuDNN with allow_tf32); K % 8 == 0,
+ * channel rows 16-byte aligned, 16-byte aligned pointers.  Forward convolution of nn.Conv2d (cuDNN
  * cudnnConvolutionForward; every conv of torchvision resnet18, distributed.py:137,246) and,
  * with dy as x and the flipped/transposed filter as w (pad' = R-1-pad), the data gradient of
  * stride-1 convolutions (cudnnConvolutionBackwardData, distributed.py:262). */
 int pdt_conv_fprop(const void* x, const void* w, void* y, int dtype, int N, int H, int W, int C, int K, int R, int S,
                    int stride, int pad, cudaStream_t stream);
+/* Convolution + BatchNorm batch statistics in one kernel: the epilogue also produces the per-channel
+ * mean / invstd of y (and updates the running statistics), so BatchNorm needs no statistics pass of its
+ * own (cudnnConvolutionForward + batch_norm statistics kernel).  Dense NHWC output, K <= 512.
+ * scratch: pdt_bn_scratch_bytes(K) bytes, first word zero before the first call. */
+int pdt_conv_fprop_bnstats(const void* x, const void* w, void* y, int dtype, int N, int H, int W, int C, int K, int R, int S,
+                           int stride, int pad, void* scratch, float* running_mean, float* running_var, float momentum,
+                           float eps, float* save_mean, float* save_invstd, cudaStream_t stream);
 /* Weight gradient (cudnnConvolutionBackwardFilter): dw [K][R][S][C] fp32 += sum over pixels; split-K over
  * the pixel dimension with red.global.add, so zero dw first.  C % 64 == 0, K % 64 == 0. */
 int pdt_conv_wgrad(const void* x, const void* dy, float* dw, int dtype, int N, int H, int W, int C, int K, int R, int S,
@@ -172,10 +195,10 @@ int pdt_conv_wgrad(const void* x, const void* dy, float* dw, int dtype, int N, i
 int pdt_conv_fprop_ex(const void* x, const void* w, void* y, const float* bias, int dtype, int N, int H, int W, int C,
                       int Cx, long long x_sw, long long x_sh, long long x_sn, int K, int R, int S, int stride,
                       int pad_lo_h, int pad_lo_w, int pad_hi_h, int pad_hi_w, int P, int Q, int OH, int OW, int os,
-                      int oa, int ob, cudaStream_t stream);
+                      int oa, int ob, int dil_w, cudaStream_t stream);
 int pdt_conv_wgrad_ex(const void* x, const void* dy, float* dw, int dtype, int N, int H, int W, int C, int Cx,
                       long long x_sw, long long x_sh, long long x_sn, int K, int R, int S, int stride, int pad_lo_h,
-                      int pad_lo_w, int pad_hi_h, int pad_hi_w, int P, int Q, cudaStream_t stream);
+                      int pad_lo_w, int pad_hi_h, int pad_hi_w, int P, int Q, int dil_w, cudaStream_t stream);
 /* Stem input transform: NCHW fp32 -> 2x2 space-to-depth NHWC(16) low precision, zero padded by `pad`
  * (autocast input cast + layout change for the 7x7 stride-2 stem of torchvision resnet). */
 int pdt_stem_s2d(const float* x, void* y, int dtype, int N, int H, int W, int pad, cudaStream_t stream);

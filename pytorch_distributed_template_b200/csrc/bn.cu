@@ -222,6 +222,7 @@ template <typename T>
 __global__ void __launch_bounds__(kThreads) k_bn_bwd_reduce(const T* __restrict__ dy, const T* __restrict__ y,
                                                            const T* __restrict__ x, long M, int C,
                                                            const float* __restrict__ mean, const float* __restrict__ invstd,
+                                                           const float* __restrict__ gamma, const float* __restrict__ beta,
                                                            int relu, float* __restrict__ partial, unsigned* counter, Comm comm,
                                                            float* __restrict__ dgamma, float* __restrict__ dbeta,
                                                            float* __restrict__ out_k) {
@@ -231,9 +232,18 @@ __global__ void __launch_bounds__(kThreads) k_bn_bwd_reduce(const T* __restrict_
   const int tid = threadIdx.x, cg = C / V, rpi = kThreads / cg, cgi = tid % cg, r = tid / cg;
   const long chunk = (M + gridDim.x - 1) / gridDim.x;
   const long row0 = (long)blockIdx.x * chunk, row1 = min(M, row0 + chunk);
-  float s[V], q[V], mu[V];
+  // y == nullptr with relu: no residual entered the ReLU, so its mask is recomputed from x with the
+  // forward's own scale/shift instead of reading the output tensor (one pass of traffic less)
+  const bool remask = relu && y == nullptr;
+  float s[V], q[V], mu[V], sc[V], sh[V];
 #pragma unroll
-  for (int j = 0; j < V; ++j) { s[j] = q[j] = 0.f; mu[j] = (r < rpi) ? mean[cgi * V + j] : 0.f; }
+  for (int j = 0; j < V; ++j) {
+    s[j] = q[j] = 0.f;
+    const int c = cgi * V + j;
+    mu[j] = (r < rpi) ? mean[c] : 0.f;
+    sc[j] = (r < rpi && remask) ? gamma[c] * invstd[c] : 0.f;
+    sh[j] = (r < rpi && remask) ? beta[c] - mean[c] * sc[j] : 0.f;
+  }
   if (r < rpi) {
 #pragma unroll 2
     for (long row = row0 + r; row < row1; row += rpi) {
@@ -241,7 +251,10 @@ __global__ void __launch_bounds__(kThreads) k_bn_bwd_reduce(const T* __restrict_
       float g[V], xv[V];
       load_vec<T>(dy + o, g);
       load_vec<T>(x + o, xv);
-      if (relu) {
+      if (remask) {
+#pragma unroll
+        for (int j = 0; j < V; ++j) g[j] = fmaf(xv[j], sc[j], sh[j]) > 0.f ? g[j] : 0.f;
+      } else if (relu) {
         float yv[V];
         load_vec<T>(y + o, yv);
 #pragma unroll
@@ -278,18 +291,21 @@ __global__ void __launch_bounds__(kThreads) k_bn_bwd_apply(const T* __restrict__
                                                           const T* __restrict__ x, T* __restrict__ dx, T* __restrict__ dres,
                                                           long nvec, int C, const float* __restrict__ mean,
                                                           const float* __restrict__ invstd, const float* __restrict__ gamma,
-                                                          const float* __restrict__ k, int relu) {
+                                                          const float* __restrict__ beta, const float* __restrict__ k, int relu) {
   constexpr int V = Vec<T>::N;
   extern __shared__ float sm[];
-  float* a = sm;            // invstd*gamma
+  float* a = sm;            // invstd*gamma (also the forward scale)
   float* k1 = sm + C;
   float* k2 = sm + 2 * C;
   float* mu = sm + 3 * C;
+  float* sh = sm + 4 * C;   // forward shift
+  const bool remask = relu && y == nullptr;
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    a[c] = invstd[c] * gamma[c];
+    a[c] = gamma[c] * invstd[c];
     k1[c] = k[c];
     k2[c] = k[C + c];
     mu[c] = mean[c];
+    sh[c] = beta[c] - mean[c] * a[c];
   }
   __syncthreads();
   const int cg = C / V;
@@ -298,7 +314,10 @@ __global__ void __launch_bounds__(kThreads) k_bn_bwd_apply(const T* __restrict__
     float g[V], xv[V];
     load_vec<T>(dy + i * V, g);
     load_vec<T>(x + i * V, xv);
-    if (relu) {
+    if (remask) {
+#pragma unroll
+      for (int j = 0; j < V; ++j) g[j] = fmaf(xv[j], a[c0 + j], sh[c0 + j]) > 0.f ? g[j] : 0.f;
+    } else if (relu) {
       float yv[V];
       load_vec<T>(y + i * V, yv);
 #pragma unroll
@@ -308,6 +327,194 @@ __global__ void __launch_bounds__(kThreads) k_bn_bwd_apply(const T* __restrict__
 #pragma unroll
     for (int j = 0; j < V; ++j) g[j] = (g[j] - k1[c0 + j] - (xv[j] - mu[c0 + j]) * k2[c0 + j]) * a[c0 + j];
     store_vec<T>(dx + i * V, g);
+  }
+}
+
+// ---- BatchNorm + ReLU + MaxPool fused (the ResNet stem tail) -----------------------------------------
+// The stem's BN output is the largest activation of the network (112 x 112 x 64 per image) and exists
+// only to be max-pooled.  These kernels never materialise it:
+//   forward : pooled = maxpool(relu(bn(x))) straight from the conv output x, arg-max tap saved as int8;
+//   backward: the gradient w.r.t. the (virtual) BN output at (h, w) is gathered from the <= 4 pooled
+//             outputs whose arg-max is (h, w), masked by relu'(bn(x)) recomputed from x; the BN
+//             reduction and the dx pass consume it on the fly.
+// Replaces batch_norm + relu_ + max_pool2d_with_indices and their three backward kernels.
+struct PoolGeom { int N, H, W, C, Ho, Wo, ks, st, pd; };
+
+template <typename T>
+__device__ __forceinline__ void gather_pool_grad(const T* __restrict__ dpool, const int8_t* __restrict__ idx, const PoolGeom& g,
+                                                 int n, int h, int w, int c0, float (&acc)[8]) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  const int ho_lo = max(0, (h + g.pd - g.ks + g.st) / g.st), ho_hi = min(g.Ho - 1, (h + g.pd) / g.st);
+  const int wo_lo = max(0, (w + g.pd - g.ks + g.st) / g.st), wo_hi = min(g.Wo - 1, (w + g.pd) / g.st);
+  for (int ho = ho_lo; ho <= ho_hi; ++ho) {
+    const int kh = h + g.pd - ho * g.st;
+    for (int wo = wo_lo; wo <= wo_hi; ++wo) {
+      const int tap = kh * g.ks + (w + g.pd - wo * g.st);
+      const size_t o = (((size_t)n * g.Ho + ho) * g.Wo + wo) * g.C + c0;
+      const uint2 pk = *reinterpret_cast<const uint2*>(idx + o);
+      float d[8];
+      unpack8<T>(*reinterpret_cast<const uint4*>(dpool + o), d);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int sel = ((j < 4 ? pk.x : pk.y) >> ((j & 3) * 8)) & 0xff;
+        if (sel == tap) acc[j] += d[j];
+      }
+    }
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) k_bn_pool_fwd(const T* __restrict__ x, T* __restrict__ y, int8_t* __restrict__ idx, PoolGeom g,
+                                                    const float* __restrict__ mean, const float* __restrict__ invstd,
+                                                    const float* __restrict__ gamma, const float* __restrict__ beta) {
+  extern __shared__ float sm[];
+  float* scale = sm;
+  float* shift = sm + g.C;
+  for (int c = threadIdx.x; c < g.C; c += blockDim.x) {
+    const float sc = gamma[c] * invstd[c];
+    scale[c] = sc;
+    shift[c] = beta[c] - mean[c] * sc;
+  }
+  __syncthreads();
+  const int cg = g.C / 8;
+  const unsigned total = (unsigned)g.N * g.Ho * g.Wo * cg;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int c0 = (int)(i % cg) * 8;
+    unsigned r = i / cg;
+    const int wo = (int)(r % g.Wo); r /= g.Wo;
+    const int ho = (int)(r % g.Ho);
+    const int n = (int)(r / g.Ho);
+    float best[8];
+    int bi[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { best[j] = -INFINITY; bi[j] = 0; }
+    for (int kh = 0; kh < g.ks; ++kh) {
+      const int h = ho * g.st - g.pd + kh;
+      if (h < 0 || h >= g.H) continue;
+      for (int kw = 0; kw < g.ks; ++kw) {
+        const int w = wo * g.st - g.pd + kw;
+        if (w < 0 || w >= g.W) continue;
+        float f[8];
+        unpack8<T>(*reinterpret_cast<const uint4*>(x + (((size_t)n * g.H + h) * g.W + w) * g.C + c0), f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float v = fmaxf(fmaf(f[j], scale[c0 + j], shift[c0 + j]), 0.f);
+          if (v > best[j]) { best[j] = v; bi[j] = kh * g.ks + kw; }
+        }
+      }
+    }
+    const size_t o = (((size_t)n * g.Ho + ho) * g.Wo + wo) * g.C + c0;
+    *reinterpret_cast<uint4*>(y + o) = pack8<T>(best);
+    uint2 pk;
+    pk.x = (bi[0] & 0xff) | ((bi[1] & 0xff) << 8) | ((bi[2] & 0xff) << 16) | ((bi[3] & 0xff) << 24);
+    pk.y = (bi[4] & 0xff) | ((bi[5] & 0xff) << 8) | ((bi[6] & 0xff) << 16) | ((bi[7] & 0xff) << 24);
+    *reinterpret_cast<uint2*>(idx + o) = pk;
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads) k_bn_pool_bwd_reduce(const T* __restrict__ dpool, const int8_t* __restrict__ idx,
+                                                                const T* __restrict__ x, PoolGeom g,
+                                                                const float* __restrict__ mean, const float* __restrict__ invstd,
+                                                                const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                                float* __restrict__ partial, unsigned* counter, Comm comm,
+                                                                float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                                                float* __restrict__ out_k) {
+  constexpr int V = 8;
+  __shared__ __align__(16) float smem[kSmemFloats];
+  __shared__ double s_count;
+  const int C = g.C;
+  const long M = (long)g.N * g.H * g.W;
+  const int tid = threadIdx.x, cg = C / V, rpi = kThreads / cg, cgi = tid % cg, r = tid / cg;
+  const long chunk = (M + gridDim.x - 1) / gridDim.x;
+  const long row0 = (long)blockIdx.x * chunk, row1 = min(M, row0 + chunk);
+  float s[V], q[V], mu[V], sc[V], sh[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) {
+    s[j] = q[j] = 0.f;
+    const int c = cgi * V + j;
+    mu[j] = (r < rpi) ? mean[c] : 0.f;
+    sc[j] = (r < rpi) ? gamma[c] * invstd[c] : 0.f;
+    sh[j] = (r < rpi) ? beta[c] - mean[c] * sc[j] : 0.f;
+  }
+  if (r < rpi) {
+    const int hw = g.H * g.W;
+    for (long row = row0 + r; row < row1; row += rpi) {
+      const int n = (int)(row / hw);
+      const int rem = (int)(row - (long)n * hw);
+      const int h = rem / g.W, w = rem - h * g.W;
+      float gy[V], xv[V];
+      gather_pool_grad<T>(dpool, idx, g, n, h, w, cgi * V, gy);
+      load_vec<T>(x + row * C + cgi * V, xv);
+#pragma unroll
+      for (int j = 0; j < V; ++j) {
+        const float gg = fmaf(xv[j], sc[j], sh[j]) > 0.f ? gy[j] : 0.f;
+        s[j] += gg;
+        q[j] = fmaf(gg, xv[j] - mu[j], q[j]);
+      }
+    }
+  }
+  block_fold<V>(smem, s, q, C, cg, rpi, partial);
+  if (!take_last_ticket(counter)) return;
+
+  double* tot = reinterpret_cast<double*>(smem);
+  fold_partials(tot, partial, gridDim.x, 2 * C);
+  if (tid == 0) { s_count = (double)M; *counter = 0; }
+  __syncthreads();
+  for (int c = tid; c < C; c += blockDim.x) {
+    dbeta[c] = (float)tot[c];
+    dgamma[c] = (float)(tot[C + c] * (double)invstd[c]);
+  }
+  __syncthreads();
+  if (comm.world > 1) exchange_sum(comm, tot, 2 * C, &s_count);
+  __syncthreads();
+  const double Nn = s_count;
+  for (int c = tid; c < C; c += blockDim.x) {
+    const double is = (double)invstd[c];
+    out_k[c] = (float)(tot[c] / Nn);
+    out_k[C + c] = (float)(tot[C + c] * is * is / Nn);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) k_bn_pool_bwd_apply(const T* __restrict__ dpool, const int8_t* __restrict__ idx,
+                                                          const T* __restrict__ x, T* __restrict__ dx, PoolGeom g,
+                                                          const float* __restrict__ mean, const float* __restrict__ invstd,
+                                                          const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                          const float* __restrict__ k) {
+  extern __shared__ float sm[];
+  const int C = g.C;
+  float* a = sm;            // invstd*gamma  (also the forward scale)
+  float* sh = sm + C;       // forward shift
+  float* k1 = sm + 2 * C;
+  float* k2 = sm + 3 * C;
+  float* mu = sm + 4 * C;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    a[c] = invstd[c] * gamma[c];
+    sh[c] = beta[c] - mean[c] * a[c];
+    k1[c] = k[c];
+    k2[c] = k[C + c];
+    mu[c] = mean[c];
+  }
+  __syncthreads();
+  const int cg = C / 8;
+  const unsigned total = (unsigned)g.N * g.H * g.W * cg;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int c0 = (int)(i % cg) * 8;
+    unsigned r = i / cg;
+    const int w = (int)(r % g.W); r /= g.W;
+    const int h = (int)(r % g.H);
+    const int n = (int)(r / g.H);
+    float gy[8], xv[8];
+    gather_pool_grad<T>(dpool, idx, g, n, h, w, c0, gy);
+    unpack8<T>(*reinterpret_cast<const uint4*>(x + (size_t)i * 8), xv);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float gg = fmaf(xv[j], a[c0 + j], sh[c0 + j]) > 0.f ? gy[j] : 0.f;
+      gy[j] = (gg - k1[c0 + j] - (xv[j] - mu[c0 + j]) * k2[c0 + j]) * a[c0 + j];
+    }
+    *reinterpret_cast<uint4*>(dx + (size_t)i * 8) = pack8<T>(gy);
   }
 }
 
@@ -338,6 +545,61 @@ int apply_blocks(long nvec) {
 extern "C" {
 
 size_t pdt_bn_scratch_bytes(int C) { return (size_t)PDT_BN_MAX_BLOCKS * 2 * C * sizeof(float) + 256; }
+
+#define BNP_DISPATCH(dtype, ...)                                      \
+  if (dtype == PDT_BF16) { using T = __nv_bfloat16; __VA_ARGS__; }    \
+  else if (dtype == PDT_FP16) { using T = __half; __VA_ARGS__; }      \
+  else return PDT_E_UNSUPPORTED;
+
+static bool pool_geom(PoolGeom& g, int N, int H, int W, int C, int ks, int st, int pd) {
+  g.N = N; g.H = H; g.W = W; g.C = C; g.ks = ks; g.st = st; g.pd = pd;
+  g.Ho = (H + 2 * pd - ks) / st + 1;
+  g.Wo = (W + 2 * pd - ks) / st + 1;
+  return C % 8 == 0 && ks * ks <= 127 && g.Ho > 0 && g.Wo > 0 && (double)N * H * W * (C / 8) < 4.0e9;
+}
+
+int pdt_bn_pool_fwd(const void* x, void* y, int8_t* idx, int dtype, int N, int H, int W, int C, int ks, int st, int pd,
+                    const float* mean, const float* invstd, const float* gamma, const float* beta, cudaStream_t stream) {
+  PoolGeom g;
+  if (!pool_geom(g, N, H, W, C, ks, st, pd)) return PDT_E_UNSUPPORTED;
+  const long total = (long)N * g.Ho * g.Wo * (C / 8);
+  long nb = (total + 255) / 256;
+  if (nb > 148 * 16) nb = 148 * 16;
+  BNP_DISPATCH(dtype, k_bn_pool_fwd<T><<<(int)nb, 256, 2 * C * sizeof(float), stream>>>(
+      reinterpret_cast<const T*>(x), reinterpret_cast<T*>(y), idx, g, mean, invstd, gamma, beta));
+  return (int)cudaGetLastError();
+}
+
+int pdt_bn_pool_bwd_reduce(const void* dpool, const int8_t* idx, const void* x, int dtype, int N, int H, int W, int C,
+                           int ks, int st, int pd, const float* mean, const float* invstd, const float* gamma,
+                           const float* beta, void* scratch, const PdtCommDesc* comm, float* dgamma, float* dbeta,
+                           float* out_k, cudaStream_t stream) {
+  PoolGeom g;
+  if (!pool_geom(g, N, H, W, C, ks, st, pd)) return PDT_E_UNSUPPORTED;
+  unsigned* counter = reinterpret_cast<unsigned*>(scratch);
+  float* partial = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + 256);
+  BNP_DISPATCH(dtype, {
+    if (!shape_ok<T>(C)) return PDT_E_UNSUPPORTED;
+    k_bn_pool_bwd_reduce<T><<<stats_blocks((long)N * H * W, C, 8), kThreads, 0, stream>>>(
+        reinterpret_cast<const T*>(dpool), idx, reinterpret_cast<const T*>(x), g, mean, invstd, gamma, beta, partial,
+        counter, make_comm(comm), dgamma, dbeta, out_k);
+  });
+  return (int)cudaGetLastError();
+}
+
+int pdt_bn_pool_bwd_apply(const void* dpool, const int8_t* idx, const void* x, void* dx, int dtype, int N, int H, int W,
+                          int C, int ks, int st, int pd, const float* mean, const float* invstd, const float* gamma,
+                          const float* beta, const float* k, cudaStream_t stream) {
+  PoolGeom g;
+  if (!pool_geom(g, N, H, W, C, ks, st, pd)) return PDT_E_UNSUPPORTED;
+  const long total = (long)N * H * W * (C / 8);
+  long nb = (total + 255) / 256;
+  if (nb > 148 * 16) nb = 148 * 16;
+  BNP_DISPATCH(dtype, k_bn_pool_bwd_apply<T><<<(int)nb, 256, 5 * C * sizeof(float), stream>>>(
+      reinterpret_cast<const T*>(dpool), idx, reinterpret_cast<const T*>(x), reinterpret_cast<T*>(dx), g, mean, invstd,
+      gamma, beta, k));
+  return (int)cudaGetLastError();
+}
 
 #define BN_DISPATCH(dtype, ...)                                                      \
   if (dtype == PDT_BF16) { using T = __nv_bfloat16; __VA_ARGS__; }                   \
@@ -424,28 +686,28 @@ int pdt_bn_fwd_apply(const void* x, const void* res, void* y, long M, int C, int
 }
 
 int pdt_bn_bwd_reduce(const void* dy, const void* y, const void* x, long M, int C, int dtype, const float* mean,
-                      const float* invstd, int relu, void* scratch, const PdtCommDesc* comm, float* dgamma,
-                      float* dbeta, float* out_k, cudaStream_t stream) {
+                      const float* invstd, const float* gamma, const float* beta, int relu, void* scratch,
+                      const PdtCommDesc* comm, float* dgamma, float* dbeta, float* out_k, cudaStream_t stream) {
   unsigned* counter = reinterpret_cast<unsigned*>(scratch);
   float* partial = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + 256);
   BN_DISPATCH(dtype, {
     if (!shape_ok<T>(C)) return PDT_E_UNSUPPORTED;
     k_bn_bwd_reduce<T><<<stats_blocks(M, C, Vec<T>::N), kThreads, 0, stream>>>(
         reinterpret_cast<const T*>(dy), reinterpret_cast<const T*>(y), reinterpret_cast<const T*>(x), M, C, mean, invstd,
-        relu, partial, counter, make_comm(comm), dgamma, dbeta, out_k);
+        gamma, beta, relu, partial, counter, make_comm(comm), dgamma, dbeta, out_k);
   });
   return (int)cudaGetLastError();
 }
 
 int pdt_bn_bwd_apply(const void* dy, const void* y, const void* x, void* dx, void* dres, long M, int C, int dtype,
-                     const float* mean, const float* invstd, const float* gamma, const float* k, int relu,
-                     cudaStream_t stream) {
+                     const float* mean, const float* invstd, const float* gamma, const float* beta, const float* k,
+                     int relu, cudaStream_t stream) {
   BN_DISPATCH(dtype, {
     if (C % Vec<T>::N) return PDT_E_UNSUPPORTED;
     const long nvec = M * C / Vec<T>::N;
-    k_bn_bwd_apply<T><<<apply_blocks(nvec), kThreads, 4 * C * sizeof(float), stream>>>(
+    k_bn_bwd_apply<T><<<apply_blocks(nvec), kThreads, 5 * C * sizeof(float), stream>>>(
         reinterpret_cast<const T*>(dy), reinterpret_cast<const T*>(y), reinterpret_cast<const T*>(x),
-        reinterpret_cast<T*>(dx), reinterpret_cast<T*>(dres), nvec, C, mean, invstd, gamma, k, relu);
+        reinterpret_cast<T*>(dx), reinterpret_cast<T*>(dres), nvec, C, mean, invstd, gamma, beta, k, relu);
   });
   return (int)cudaGetLastError();
 }

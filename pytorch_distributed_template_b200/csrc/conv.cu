@@ -27,7 +27,18 @@ using namespace pdt;
 using namespace pdt::tc;
 
 constexpr int BM = 128;        // output pixels per tile (= TMEM lanes)
-constexpr int BK = 64;         // channels per k-block: 64 x 16 bit = one 128 B swizzle row
+// Element-type traits: one k-block is always one 128-byte swizzle row, i.e. 64 bf16/fp16 or 32 tf32
+// channels; one tcgen05.mma consumes 32 bytes of it along K (UMMA_K = 16 or 8).
+template <typename T> struct Elem {
+  static constexpr int kRow = 128 / (int)sizeof(T);
+  static constexpr int kUK = 32 / (int)sizeof(T);
+  static constexpr int kFmt = std::is_same<T, __nv_bfloat16>::value ? 1 : (std::is_same<T, __half>::value ? 0 : 2);
+};
+template <typename T>
+__device__ __forceinline__ void umma(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t acc) {
+  if constexpr (sizeof(T) == 4) umma_tf32(tmem_d, da, db, idesc, acc);
+  else umma_f16(tmem_d, da, db, idesc, acc);
+}
 constexpr int kThreads = 256;
 
 struct ConvGeom {
@@ -35,6 +46,7 @@ struct ConvGeom {
   int K, R, S;                 // filter (KRSC)
   int P, Q;                    // output spatial
   int stride;
+  int dil_w;                   // horizontal distance (in TMA pixels) between filter taps, normally 1
   int pad_h, pad_w;            // lower (top/left) padding
   int pad_hi_h, pad_hi_w;      // upper (bottom/right) padding
   int M;                       // N*P*Q
@@ -46,19 +58,52 @@ struct ConvGeom {
   long long x_sw, x_sh, x_sn;
 };
 
+// Optional epilogue fusion: per-channel sum / sum of squares of the convolution output (the BatchNorm
+// batch statistics), so the following BatchNorm needs no pass of its own over the activation.
+// Every CTA accumulates its tiles' column sums in shared memory, writes one row of `partial`, and the
+// CTA that takes the last ticket folds the rows in fp64 and finalises mean / invstd / running stats.
+constexpr int kStatMaxK = 512;
+struct BnStats {
+  int enabled;
+  float* partial;          // [gridDim][2*K] scratch
+  unsigned* counter;       // ticket, zero before the launch, reset by the kernel
+  float* running_mean;     // may be null
+  float* running_var;
+  float* save_mean;
+  float* save_invstd;
+  float momentum, eps;
+};
+
 template <int BN> struct Cfg {
-  static constexpr int kStageBytesA = BM * BK * 2;
-  static constexpr int kStageBytesB = BN * BK * 2;
+  static constexpr int kStageBytesA = BM * 128;
+  static constexpr int kStageBytesB = BN * 128;
   static constexpr int kStageBytes = kStageBytesA + kStageBytesB;
   static constexpr int kStages = (BN >= 256) ? 4 : (BN >= 128 ? 6 : 8);
   static constexpr int kTmemCols = 2 * BN;     // double-buffered accumulator (power of two >= 32 for BN in {64,128,256})
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*alignment slack*/ + 256 /*barriers*/;
+  static constexpr int kStatBytes = 4 * 2 * kStatMaxK * 4;   // [4 epilogue warps][sum, sumsq][K] floats
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*alignment slack*/ + 256 /*barriers*/ + kStatBytes;
 };
+
+// Column sums over the 32 lanes of a warp for 32 values per lane: after the call lane L holds
+// sum over lanes of a[L] in a[0].  31 shuffles (butterfly that halves the live values each step).
+__device__ __forceinline__ void warp_transpose_reduce(float (&a)[32], int lane) {
+#pragma unroll
+  for (int s = 16; s >= 1; s >>= 1) {
+    const bool up = (lane & s) != 0;
+#pragma unroll
+    for (int i = 0; i < s; ++i) {
+      const float keep = up ? a[i + s] : a[i];
+      const float send = up ? a[i] : a[i + s];
+      a[i] = keep + __shfl_xor_sync(0xffffffffu, send, s);
+    }
+  }
+}
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 
 template <int BN, typename T>
 __global__ void __launch_bounds__(kThreads, 1)
 k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, T* __restrict__ out,
-             const float* __restrict__ bias, const ConvGeom g) {
+             const float* __restrict__ bias, const ConvGeom g, const BnStats bs) {
   using C = Cfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -70,9 +115,11 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   uint64_t* tfull = bars + 2 * C::kStages;
   uint64_t* tempty = tfull + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  float* s_stat = reinterpret_cast<float*>(smem + C::kStages * C::kStageBytes + 256);   // [4][2][kStatMaxK]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int num_tiles = g.m_tiles * g.n_tiles;
+  constexpr int BK = Elem<T>::kRow;
   const int c_chunks = (g.C + BK - 1) / BK;
   const int k_blocks = g.R * g.S * c_chunks;
 
@@ -108,7 +155,7 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
             for (int cc = 0; cc < c_chunks; ++cc) {
               mbar_wait(&empty[stage], phase ^ 1);
               mbar_expect_tx(&full[stage], C::kStageBytes);
-              tma_load_im2col_4d(smA + stage * C::kStageBytesA, &tmA, &full[stage], cc * BK, cw, ch, img, (uint16_t)s, (uint16_t)r);
+              tma_load_im2col_4d(smA + stage * C::kStageBytesA, &tmA, &full[stage], cc * BK, cw, ch, img, (uint16_t)(s * g.dil_w), (uint16_t)r);
               tma_load_2d(smB + stage * C::kStageBytesB, &tmB, &full[stage], (r * g.S + s) * g.C + cc * BK, nt * BN);
               if (++stage == C::kStages) { stage = 0; phase ^= 1; }
             }
@@ -117,7 +164,7 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   } else if (warp == 1) {
     // ================= MMA issuer =================
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc(BM, BN, sizeof(T) == 2 && std::is_same<T, __nv_bfloat16>::value ? 1 : 0, 0, 0);
+      constexpr uint32_t idesc = make_idesc(BM, BN, Elem<T>::kFmt, 0, 0);
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
@@ -133,8 +180,8 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
           const uint64_t da = make_sw128_desc(smem_u32(smA + stage * C::kStageBytesA), 1024, 16);
           const uint64_t db = make_sw128_desc(smem_u32(smB + stage * C::kStageBytesB), 1024, 16);
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k)   // +32 bytes along K per UMMA_K=16 step: +2 in the (addr >> 4) field
-            umma_f16(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+          for (int k = 0; k < 4; ++k)   // +32 bytes along K per UMMA_K step: +2 in the (addr >> 4) field
+            umma<T>(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
           umma_commit(&empty[stage]);
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
         }
@@ -144,6 +191,11 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   } else if (warp >= 4) {
     // ================= epilogue: TMEM -> registers -> global =================
     const int quarter = warp & 3;                 // TMEM lanes [32*quarter, +32) are the ones this warp may read
+    float* my_stat = s_stat + quarter * 2 * kStatMaxK;
+    if (bs.enabled) {
+      for (int i = lane; i < 2 * kStatMaxK; i += 32) my_stat[i] = 0.f;
+      __syncwarp();
+    }
     int it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
       const int mt = tile / g.n_tiles, nt = tile % g.n_tiles;
@@ -167,6 +219,22 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         uint32_t v[32];
         tmem_ld32(taddr + c0, v);
         tmem_ld_wait();
+        if (bs.enabled) {
+          // rows past M come from zero-filled (out-of-bounds) pixels: their accumulators are exactly 0
+          float a[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) a[j] = __uint_as_float(v[j]);
+          warp_transpose_reduce(a, lane);
+          const float colsum = a[0];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) { const float t = __uint_as_float(v[j]); a[j] = t * t; }
+          warp_transpose_reduce(a, lane);
+          const int col = nt * BN + c0 + lane;
+          if (col < g.K) {
+            my_stat[col] += colsum;
+            my_stat[kStatMaxK + col] += a[0];
+          }
+        }
         if (row < g.M) {
 #pragma unroll
           for (int j = 0; j < 32; j += 8) {
@@ -180,12 +248,17 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                 f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w;
                 f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
               }
-              uint4 o;
-              o.x = Cvt<T>::pack2(f[0], f[1]);
-              o.y = Cvt<T>::pack2(f[2], f[3]);
-              o.z = Cvt<T>::pack2(f[4], f[5]);
-              o.w = Cvt<T>::pack2(f[6], f[7]);
-              *reinterpret_cast<uint4*>(orow + c0 + j) = o;
+              if constexpr (sizeof(T) == 4) {
+                *reinterpret_cast<float4*>(orow + c0 + j) = make_float4(f[0], f[1], f[2], f[3]);
+                *reinterpret_cast<float4*>(orow + c0 + j + 4) = make_float4(f[4], f[5], f[6], f[7]);
+              } else {
+                uint4 o;
+                o.x = Cvt<T>::pack2(f[0], f[1]);
+                o.y = Cvt<T>::pack2(f[2], f[3]);
+                o.z = Cvt<T>::pack2(f[4], f[5]);
+                o.w = Cvt<T>::pack2(f[6], f[7]);
+                *reinterpret_cast<uint4*>(orow + c0 + j) = o;
+              }
             }
           }
         }
@@ -193,6 +266,50 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty[acc]);
+    }
+    if (bs.enabled) {
+      // ---- fold the 4 warps' column sums, publish this CTA's row, last CTA finalises ----
+      __shared__ int s_last;
+      const int te = threadIdx.x - 128;           // 0..127 among the epilogue threads
+      const int K = g.K;
+      epi_bar_sync();
+      for (int i = te; i < 2 * K; i += 128) {
+        const int which = i / K, c = i - which * K;
+        float t = 0.f;
+#pragma unroll
+        for (int q4 = 0; q4 < 4; ++q4) t += s_stat[(q4 * 2 + which) * kStatMaxK + c];
+        bs.partial[(size_t)blockIdx.x * 2 * K + i] = t;
+      }
+      __threadfence();
+      epi_bar_sync();
+      if (te == 0) s_last = (atomicAdd(bs.counter, 1u) == gridDim.x - 1);
+      epi_bar_sync();
+      if (s_last) {
+        __threadfence();
+        double* tot = reinterpret_cast<double*>(s_stat);      // 2K doubles <= 8 KB of the 16 KB region
+        epi_bar_sync();
+        for (int i = te; i < 2 * K; i += 128) {
+          double t = 0.0;
+#pragma unroll 4
+          for (int b = 0; b < (int)gridDim.x; ++b) t += (double)__ldcg(bs.partial + (size_t)b * 2 * K + i);
+          tot[i] = t;
+        }
+        epi_bar_sync();
+        const double n = (double)g.M;
+        for (int c = te; c < K; c += 128) {
+          const double mean = tot[c] / n;
+          double var = tot[K + c] / n - mean * mean;
+          var = var > 0.0 ? var : 0.0;
+          bs.save_mean[c] = (float)mean;
+          bs.save_invstd[c] = (float)(1.0 / sqrt(var + (double)bs.eps));
+          if (bs.running_mean != nullptr) {
+            const double unbiased = n > 1.0 ? var * n / (n - 1.0) : var;
+            bs.running_mean[c] = (float)((1.0 - bs.momentum) * bs.running_mean[c] + bs.momentum * mean);
+            bs.running_var[c] = (float)((1.0 - bs.momentum) * bs.running_var[c] + bs.momentum * unbiased);
+          }
+        }
+        if (te == 0) *bs.counter = 0;
+      }
     }
   }
 
@@ -223,12 +340,14 @@ struct WgradGeom {
   int splits, steps_per_split;
 };
 
-constexpr int BKP = 64;        // pixels per k-step
-constexpr int kBlkBytes = BKP * 128;   // one [64 pixel][64 x 16 bit] block
-
-template <int BN> struct WCfg {
-  static constexpr int kStageBytesA = 2 * kBlkBytes;
-  static constexpr int kStageBytesB = (BN / 64) * kBlkBytes;
+template <int BN, typename T> struct WCfg {
+  static constexpr int kRow = Elem<T>::kRow;             // channels per 128-byte block row: 64 (16 bit) / 32 (tf32)
+  static constexpr int kPix = 4 * Elem<T>::kUK;          // pixels per k-step (4 MMAs): 64 / 32
+  static constexpr int kBlkBytes = kPix * 128;           // one [kPix pixel][128 byte] block
+  static constexpr int kABlocks = 128 / kRow;            // blocks forming the M = 128 side
+  static constexpr int kBBlocks = BN / kRow;
+  static constexpr int kStageBytesA = kABlocks * kBlkBytes;
+  static constexpr int kStageBytesB = kBBlocks * kBlkBytes;
   static constexpr int kStageBytes = kStageBytesA + kStageBytesB;
   static constexpr int kStages = (BN >= 256) ? 4 : (BN >= 128 ? 6 : 8);
   static constexpr int kTmemCols = 2 * BN;
@@ -239,7 +358,8 @@ template <int BN, typename T>
 __global__ void __launch_bounds__(kThreads, 1)
 k_conv_wgrad(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmDY, float* __restrict__ dw,
              const WgradGeom wg) {
-  using C = WCfg<BN>;
+  using C = WCfg<BN, T>;
+  constexpr int kRow = C::kRow, BKP = C::kPix, kBlkBytes = C::kBlkBytes, kAB = C::kABlocks;
   const ConvGeom& g = wg.c;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -254,8 +374,8 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int items = wg.m_tiles * wg.n_tiles * wg.splits;
-  const int c_chunks = g.C / 64;
-  const int m_blocks = wg.rsc / 64;   // wgrad needs C % 64 == 0: an (r,s,c) block never straddles two taps
+  const int c_chunks = g.C / kRow;
+  const int m_blocks = wg.rsc / kRow;   // wgrad needs C % kRow == 0: an (r,s,c) block never straddles two taps
 
   if (warp == 0 && lane == 0) { prefetch_tmap(&tmX); prefetch_tmap(&tmDY); }
   if (warp == 1 && lane == 0) {
@@ -279,11 +399,11 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
         const int mt = tile / wg.n_tiles, nt = tile % wg.n_tiles;
         const int ks0 = sp * wg.steps_per_split;
         const int ks1 = min(wg.k_steps, ks0 + wg.steps_per_split);
-        const int nA = min(2, m_blocks - mt * 2);
-        const int nB = min(BN / 64, (g.K - nt * BN + 63) / 64);
-        int tapr[2], taps[2], cc[2];
-        for (int b = 0; b < 2; ++b) {
-          const int gb = min(mt * 2 + b, m_blocks - 1);
+        const int nA = min(kAB, m_blocks - mt * kAB);
+        const int nB = min(C::kBBlocks, (g.K - nt * BN + kRow - 1) / kRow);
+        int tapr[kAB], taps[kAB], cc[kAB];
+        for (int b = 0; b < kAB; ++b) {
+          const int gb = min(mt * kAB + b, m_blocks - 1);
           const int tap = gb / c_chunks;
           cc[b] = gb - tap * c_chunks;
           tapr[b] = tap / g.S;
@@ -298,17 +418,17 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
           mbar_wait(&empty[stage], phase ^ 1);
           mbar_expect_tx(&full[stage], (uint32_t)(nA + nB) * kBlkBytes);
           for (int b = 0; b < nA; ++b)
-            tma_load_im2col_4d(smA + stage * C::kStageBytesA + b * kBlkBytes, &tmX, &full[stage], cc[b] * 64, cw, ch, img,
-                               (uint16_t)taps[b], (uint16_t)tapr[b]);
+            tma_load_im2col_4d(smA + stage * C::kStageBytesA + b * kBlkBytes, &tmX, &full[stage], cc[b] * kRow, cw, ch, img,
+                               (uint16_t)(taps[b] * g.dil_w), (uint16_t)tapr[b]);
           for (int j = 0; j < nB; ++j)
-            tma_load_2d(smB + stage * C::kStageBytesB + j * kBlkBytes, &tmDY, &full[stage], nt * BN + j * 64, m0);
+            tma_load_2d(smB + stage * C::kStageBytesB + j * kBlkBytes, &tmDY, &full[stage], nt * BN + j * kRow, m0);
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc(128, BN, std::is_same<T, __nv_bfloat16>::value ? 1 : 0, 1, 1);
+      constexpr uint32_t idesc = make_idesc(128, BN, Elem<T>::kFmt, 1, 1);
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
@@ -328,8 +448,8 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
           const uint64_t da = make_sw128_desc(smem_u32(smA + stage * C::kStageBytesA), 1024, kBlkBytes);
           const uint64_t db = make_sw128_desc(smem_u32(smB + stage * C::kStageBytesB), 1024, kBlkBytes);
 #pragma unroll
-          for (int k = 0; k < BKP / 16; ++k)   // 16 pixels = 2048 bytes per UMMA_K step: +128 in the (addr >> 4) field
-            umma_f16(tmem_d, da + 128 * k, db + 128 * k, idesc, (ks > ks0 || k > 0) ? 1u : 0u);
+          for (int k = 0; k < 4; ++k)   // UMMA_K pixels = kUK * 128 bytes per step, in (addr >> 4) units
+            umma<T>(tmem_d, da + (Elem<T>::kUK * 8) * k, db + (Elem<T>::kUK * 8) * k, idesc, (ks > ks0 || k > 0) ? 1u : 0u);
           umma_commit(&empty[stage]);
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
         }
@@ -402,18 +522,24 @@ int load_driver_fns() {
   return 0;
 }
 
-CUtensorMapDataType tm_dtype(int dtype) { return dtype == PDT_FP16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16; }
+CUtensorMapDataType tm_dtype(int dtype) {
+  return dtype == PDT_FP16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16
+                           : (dtype == PDT_FP32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16);
+}
+int esize_of(int dtype) { return dtype == PDT_FP32 ? 4 : 2; }
 
 template <int BN>
-int launch_fprop(const void* x, const void* w, void* y, const float* bias, int dtype, const ConvGeom& g, cudaStream_t stream) {
+int launch_fprop(const void* x, const void* w, void* y, const float* bias, int dtype, const ConvGeom& g, const BnStats& bs,
+                 cudaStream_t stream) {
   using C = Cfg<BN>;
   CUtensorMap tmA, tmB;
   {
     cuuint64_t dims[4] = {(cuuint64_t)g.Cx, (cuuint64_t)g.W, (cuuint64_t)g.H, (cuuint64_t)g.N};
     cuuint64_t strides[3] = {(cuuint64_t)g.x_sw, (cuuint64_t)g.x_sh, (cuuint64_t)g.x_sn};
     int lower[2] = {-g.pad_w, -g.pad_h};
-    int upper[2] = {g.pad_hi_w - (g.S - 1), g.pad_hi_h - (g.R - 1)};
+    int upper[2] = {g.pad_hi_w - (g.S - 1) * g.dil_w, g.pad_hi_h - (g.R - 1)};
     cuuint32_t estr[4] = {1, (cuuint32_t)g.stride, (cuuint32_t)g.stride, 1};
+    const int BK = 128 / esize_of(dtype);
     CUresult r = g_encode_im2col(&tmA, tm_dtype(dtype), 4, const_cast<void*>(x), dims, strides, lower, upper, BK, BM, estr,
                                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -427,8 +553,8 @@ int launch_fprop(const void* x, const void* w, void* y, const float* bias, int d
   }
   {
     cuuint64_t dims[2] = {(cuuint64_t)g.R * g.S * g.C, (cuuint64_t)g.K};
-    cuuint64_t strides[1] = {(cuuint64_t)g.R * g.S * g.C * 2};
-    cuuint32_t box[2] = {BK, (cuuint32_t)BN};
+    cuuint64_t strides[1] = {(cuuint64_t)g.R * g.S * g.C * esize_of(dtype)};
+    cuuint32_t box[2] = {(cuuint32_t)(128 / esize_of(dtype)), (cuuint32_t)BN};
     cuuint32_t estr[2] = {1, 1};
     CUresult r = g_encode_tiled(&tmB, tm_dtype(dtype), 2, const_cast<void*>(w), dims, strides, box, estr,
                                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -443,27 +569,33 @@ int launch_fprop(const void* x, const void* w, void* y, const float* bias, int d
   if (dtype == PDT_FP16) {
     auto kern = k_conv_igemm<BN, __half>;
     PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
-    kern<<<grid, kThreads, C::kSmemBytes, stream>>>(tmA, tmB, reinterpret_cast<__half*>(y), bias, g);
+    kern<<<grid, kThreads, C::kSmemBytes, stream>>>(tmA, tmB, reinterpret_cast<__half*>(y), bias, g, bs);
+  } else if (dtype == PDT_FP32) {
+    auto kern = k_conv_igemm<BN, float>;
+    PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+    kern<<<grid, kThreads, C::kSmemBytes, stream>>>(tmA, tmB, reinterpret_cast<float*>(y), bias, g, bs);
   } else {
     auto kern = k_conv_igemm<BN, __nv_bfloat16>;
     PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
-    kern<<<grid, kThreads, C::kSmemBytes, stream>>>(tmA, tmB, reinterpret_cast<__nv_bfloat16*>(y), bias, g);
+    kern<<<grid, kThreads, C::kSmemBytes, stream>>>(tmA, tmB, reinterpret_cast<__nv_bfloat16*>(y), bias, g, bs);
   }
   return (int)cudaGetLastError();
 }
 
 template <int BN>
 int launch_wgrad(const void* x, const void* dy, float* dw, int dtype, WgradGeom& wg, cudaStream_t stream) {
-  using C = WCfg<BN>;
   const ConvGeom& g = wg.c;
+  const int es = esize_of(dtype);
+  const int kRow = 128 / es, BKP = 4 * (32 / es);
+  const int smem_bytes = (dtype == PDT_FP32) ? WCfg<BN, float>::kSmemBytes : WCfg<BN, __half>::kSmemBytes;
   CUtensorMap tmX, tmDY;
   {
     cuuint64_t dims[4] = {(cuuint64_t)g.Cx, (cuuint64_t)g.W, (cuuint64_t)g.H, (cuuint64_t)g.N};
     cuuint64_t strides[3] = {(cuuint64_t)g.x_sw, (cuuint64_t)g.x_sh, (cuuint64_t)g.x_sn};
     int lower[2] = {-g.pad_w, -g.pad_h};
-    int upper[2] = {g.pad_hi_w - (g.S - 1), g.pad_hi_h - (g.R - 1)};
+    int upper[2] = {g.pad_hi_w - (g.S - 1) * g.dil_w, g.pad_hi_h - (g.R - 1)};
     cuuint32_t estr[4] = {1, (cuuint32_t)g.stride, (cuuint32_t)g.stride, 1};
-    CUresult r = g_encode_im2col(&tmX, tm_dtype(dtype), 4, const_cast<void*>(x), dims, strides, lower, upper, 64, BKP, estr,
+    CUresult r = g_encode_im2col(&tmX, tm_dtype(dtype), 4, const_cast<void*>(x), dims, strides, lower, upper, kRow, BKP, estr,
                                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return 10000 + (int)r;
@@ -474,8 +606,8 @@ int launch_wgrad(const void* x, const void* dy, float* dw, int dtype, WgradGeom&
   }
   {
     cuuint64_t dims[2] = {(cuuint64_t)g.K, (cuuint64_t)g.M};
-    cuuint64_t strides[1] = {(cuuint64_t)g.K * 2};
-    cuuint32_t box[2] = {64, BKP};
+    cuuint64_t strides[1] = {(cuuint64_t)g.K * es};
+    cuuint32_t box[2] = {(cuuint32_t)kRow, (cuuint32_t)BKP};
     cuuint32_t estr[2] = {1, 1};
     CUresult r = g_encode_tiled(&tmDY, tm_dtype(dtype), 2, const_cast<void*>(dy), dims, strides, box, estr,
                                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
@@ -495,18 +627,22 @@ int launch_wgrad(const void* x, const void* dy, float* dw, int dtype, WgradGeom&
   const int grid = items < sms ? items : sms;
   if (dtype == PDT_FP16) {
     auto kern = k_conv_wgrad<BN, __half>;
-    PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
-    kern<<<grid, kThreads, C::kSmemBytes, stream>>>(tmX, tmDY, dw, wg);
+    PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+    kern<<<grid, kThreads, smem_bytes, stream>>>(tmX, tmDY, dw, wg);
+  } else if (dtype == PDT_FP32) {
+    auto kern = k_conv_wgrad<BN, float>;
+    PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+    kern<<<grid, kThreads, smem_bytes, stream>>>(tmX, tmDY, dw, wg);
   } else {
     auto kern = k_conv_wgrad<BN, __nv_bfloat16>;
-    PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
-    kern<<<grid, kThreads, C::kSmemBytes, stream>>>(tmX, tmDY, dw, wg);
+    PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+    kern<<<grid, kThreads, smem_bytes, stream>>>(tmX, tmDY, dw, wg);
   }
   return (int)cudaGetLastError();
 }
 
-void fill_dense(ConvGeom& g, int N, int H, int W, int C, int K, int R, int S, int stride, int pad) {
-  g.N = N; g.H = H; g.W = W; g.C = C; g.K = K; g.R = R; g.S = S; g.stride = stride;
+void fill_dense(ConvGeom& g, int N, int H, int W, int C, int K, int R, int S, int stride, int pad, int es) {
+  g.N = N; g.H = H; g.W = W; g.C = C; g.K = K; g.R = R; g.S = S; g.stride = stride; g.dil_w = 1;
   g.pad_h = g.pad_w = g.pad_hi_h = g.pad_hi_w = pad;
   g.P = (H + 2 * pad - R) / stride + 1;
   g.Q = (W + 2 * pad - S) / stride + 1;
@@ -515,14 +651,17 @@ void fill_dense(ConvGeom& g, int N, int H, int W, int C, int K, int R, int S, in
   g.n_tiles = 0;
   g.OH = g.P; g.OW = g.Q; g.os = 1; g.oa = g.ob = 0;
   g.Cx = C;
-  g.x_sw = (long long)C * 2; g.x_sh = (long long)W * C * 2; g.x_sn = (long long)H * W * C * 2;
+  g.x_sw = (long long)C * es; g.x_sh = (long long)W * C * es; g.x_sn = (long long)H * W * C * es;
 }
 
-int dispatch_fprop(const void* x, const void* w, void* y, const float* bias, int dtype, ConvGeom& g, cudaStream_t stream) {
-  if (g.K <= 64) { g.n_tiles = 1; return launch_fprop<64>(x, w, y, bias, dtype, g, stream); }
-  if (g.K <= 128) { g.n_tiles = 1; return launch_fprop<128>(x, w, y, bias, dtype, g, stream); }
+int dispatch_fprop(const void* x, const void* w, void* y, const float* bias, int dtype, ConvGeom& g, cudaStream_t stream,
+                   const BnStats* stats = nullptr) {
+  BnStats bs;
+  if (stats != nullptr) bs = *stats; else { bs = BnStats(); bs.enabled = 0; }
+  if (g.K <= 64) { g.n_tiles = 1; return launch_fprop<64>(x, w, y, bias, dtype, g, bs, stream); }
+  if (g.K <= 128) { g.n_tiles = 1; return launch_fprop<128>(x, w, y, bias, dtype, g, bs, stream); }
   g.n_tiles = (g.K + 255) / 256;
-  return launch_fprop<256>(x, w, y, bias, dtype, g, stream);
+  return launch_fprop<256>(x, w, y, bias, dtype, g, bs, stream);
 }
 
 }  // namespace
@@ -532,13 +671,14 @@ extern "C" {
 // x: [N][H][W][C], dy: [N][P][Q][K] (bf16/fp16), dw: [K][R][S][C] fp32, ACCUMULATED into (zero it first).
 int pdt_conv_wgrad(const void* x, const void* dy, float* dw, int dtype, int N, int H, int W, int C, int K, int R, int S,
                    int stride, int pad, cudaStream_t stream) {
-  if (dtype != PDT_BF16 && dtype != PDT_FP16) return PDT_E_UNSUPPORTED;
-  if (C % 64 || K % 8 || R < 1 || S < 1 || stride < 1 || pad < 0) return PDT_E_UNSUPPORTED;
+  if (dtype != PDT_BF16 && dtype != PDT_FP16 && dtype != PDT_FP32) return PDT_E_UNSUPPORTED;
+  const int es = esize_of(dtype), BKP = 4 * (32 / es);
+  if (C % (128 / es) || K % 8 || R < 1 || S < 1 || stride < 1 || pad < 0) return PDT_E_UNSUPPORTED;
   if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(dw)) & 15) return PDT_E_UNSUPPORTED;
   int e = load_driver_fns();
   if (e) return e;
   WgradGeom wg;
-  fill_dense(wg.c, N, H, W, C, K, R, S, stride, pad);
+  fill_dense(wg.c, N, H, W, C, K, R, S, stride, pad, es);
   if (wg.c.P < 1 || wg.c.Q < 1) return PDT_E_UNSUPPORTED;
   wg.rsc = R * S * C;
   wg.m_tiles = (wg.rsc + 127) / 128;
@@ -553,15 +693,16 @@ int pdt_conv_wgrad(const void* x, const void* dy, float* dw, int dtype, int N, i
 // lower/upper padding and output size (the space-to-depth stem, see pdt_conv_fprop_ex).
 int pdt_conv_wgrad_ex(const void* x, const void* dy, float* dw, int dtype, int N, int H, int W, int C, int Cx,
                       long long x_sw, long long x_sh, long long x_sn, int K, int R, int S, int stride, int pad_lo_h,
-                      int pad_lo_w, int pad_hi_h, int pad_hi_w, int P, int Q, cudaStream_t stream) {
-  if (dtype != PDT_BF16 && dtype != PDT_FP16) return PDT_E_UNSUPPORTED;
-  if (C % 64 || K % 8 || R < 1 || S < 1 || stride < 1 || P < 1 || Q < 1 || (x_sw | x_sh | x_sn) % 16) return PDT_E_UNSUPPORTED;
+                      int pad_lo_w, int pad_hi_h, int pad_hi_w, int P, int Q, int dil_w, cudaStream_t stream) {
+  if (dtype != PDT_BF16 && dtype != PDT_FP16 && dtype != PDT_FP32) return PDT_E_UNSUPPORTED;
+  const int es = esize_of(dtype), BKP = 4 * (32 / es);
+  if (C % (128 / es) || K % 8 || R < 1 || S < 1 || stride < 1 || P < 1 || Q < 1 || dil_w < 1 || (x_sw | x_sh | x_sn) % 16) return PDT_E_UNSUPPORTED;
   if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(dw)) & 15) return PDT_E_UNSUPPORTED;
   int e = load_driver_fns();
   if (e) return e;
   WgradGeom wg;
   ConvGeom& g = wg.c;
-  g.N = N; g.H = H; g.W = W; g.C = C; g.K = K; g.R = R; g.S = S; g.stride = stride;
+  g.N = N; g.H = H; g.W = W; g.C = C; g.K = K; g.R = R; g.S = S; g.stride = stride; g.dil_w = dil_w;
   g.pad_h = pad_lo_h; g.pad_w = pad_lo_w; g.pad_hi_h = pad_hi_h; g.pad_hi_w = pad_hi_w;
   g.P = P; g.Q = Q;
   g.M = N * P * Q;
@@ -580,15 +721,40 @@ int pdt_conv_wgrad_ex(const void* x, const void* dy, float* dw, int dtype, int N
 // x: [N][H][W][C], w: [K][R][S][C], y: [N][P][Q][K]; C % 8 == 0, K % 8 == 0, square stride/pad.
 int pdt_conv_fprop(const void* x, const void* w, void* y, int dtype, int N, int H, int W, int C, int K, int R, int S,
                    int stride, int pad, cudaStream_t stream) {
-  if (dtype != PDT_BF16 && dtype != PDT_FP16) return PDT_E_UNSUPPORTED;
-  if (C % 8 || K % 8 || R < 1 || S < 1 || stride < 1 || pad < 0) return PDT_E_UNSUPPORTED;
+  if (dtype != PDT_BF16 && dtype != PDT_FP16 && dtype != PDT_FP32) return PDT_E_UNSUPPORTED;
+  const int es = esize_of(dtype);
+  if (C % (16 / es) || K % 8 || R < 1 || S < 1 || stride < 1 || pad < 0) return PDT_E_UNSUPPORTED;
   if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(w) | reinterpret_cast<uintptr_t>(y)) & 15) return PDT_E_UNSUPPORTED;
   int e = load_driver_fns();
   if (e) return e;
   ConvGeom g;
-  fill_dense(g, N, H, W, C, K, R, S, stride, pad);
+  fill_dense(g, N, H, W, C, K, R, S, stride, pad, es);
   if (g.P < 1 || g.Q < 1) return PDT_E_UNSUPPORTED;
   return dispatch_fprop(x, w, y, nullptr, dtype, g, stream);
+}
+
+// Convolution + BatchNorm batch statistics in one kernel (dense NHWC output, K <= 512).  scratch: at
+// least 256 + 148 * 2 * K * 4 bytes, first word zero before the first call (pdt_bn_scratch_bytes fits).
+int pdt_conv_fprop_bnstats(const void* x, const void* w, void* y, int dtype, int N, int H, int W, int C, int K, int R, int S,
+                           int stride, int pad, void* scratch, float* running_mean, float* running_var, float momentum,
+                           float eps, float* save_mean, float* save_invstd, cudaStream_t stream) {
+  if (dtype != PDT_BF16 && dtype != PDT_FP16 && dtype != PDT_FP32) return PDT_E_UNSUPPORTED;
+  const int es = esize_of(dtype);
+  if (C % (16 / es) || K % 8 || K > kStatMaxK || R < 1 || S < 1 || stride < 1 || pad < 0) return PDT_E_UNSUPPORTED;
+  if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(w) | reinterpret_cast<uintptr_t>(y)) & 15) return PDT_E_UNSUPPORTED;
+  int e = load_driver_fns();
+  if (e) return e;
+  ConvGeom g;
+  fill_dense(g, N, H, W, C, K, R, S, stride, pad, es);
+  if (g.P < 1 || g.Q < 1) return PDT_E_UNSUPPORTED;
+  BnStats bs;
+  bs.enabled = 1;
+  bs.counter = reinterpret_cast<unsigned*>(scratch);
+  bs.partial = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + 256);
+  bs.running_mean = running_mean; bs.running_var = running_var;
+  bs.save_mean = save_mean; bs.save_invstd = save_invstd;
+  bs.momentum = momentum; bs.eps = eps;
+  return dispatch_fprop(x, w, y, nullptr, dtype, g, stream, &bs);
 }
 
 // General form.  Adds: an fp32 bias [K] in the epilogue (nn.Linear as a 1x1 convolution); separate
@@ -599,14 +765,14 @@ int pdt_conv_fprop(const void* x, const void* w, void* y, int dtype, int N, int 
 int pdt_conv_fprop_ex(const void* x, const void* w, void* y, const float* bias, int dtype, int N, int H, int W, int C,
                       int Cx, long long x_sw, long long x_sh, long long x_sn, int K, int R, int S, int stride,
                       int pad_lo_h, int pad_lo_w, int pad_hi_h, int pad_hi_w, int P, int Q, int OH, int OW, int os,
-                      int oa, int ob, cudaStream_t stream) {
-  if (dtype != PDT_BF16 && dtype != PDT_FP16) return PDT_E_UNSUPPORTED;
-  if (K % 8 || R < 1 || S < 1 || stride < 1 || P < 1 || Q < 1 || (x_sw | x_sh | x_sn) % 16) return PDT_E_UNSUPPORTED;
+                      int oa, int ob, int dil_w, cudaStream_t stream) {
+  if (dtype != PDT_BF16 && dtype != PDT_FP16 && dtype != PDT_FP32) return PDT_E_UNSUPPORTED;
+  if (K % 8 || R < 1 || S < 1 || stride < 1 || P < 1 || Q < 1 || dil_w < 1 || (x_sw | x_sh | x_sn) % 16) return PDT_E_UNSUPPORTED;
   if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(w) | reinterpret_cast<uintptr_t>(y)) & 15) return PDT_E_UNSUPPORTED;
   int e = load_driver_fns();
   if (e) return e;
   ConvGeom g;
-  g.N = N; g.H = H; g.W = W; g.C = C; g.K = K; g.R = R; g.S = S; g.stride = stride;
+  g.N = N; g.H = H; g.W = W; g.C = C; g.K = K; g.R = R; g.S = S; g.stride = stride; g.dil_w = dil_w;
   g.pad_h = pad_lo_h; g.pad_w = pad_lo_w; g.pad_hi_h = pad_hi_h; g.pad_hi_w = pad_hi_w;
   g.P = P; g.Q = Q;
   g.M = N * P * Q;

@@ -267,12 +267,18 @@ __global__ void __launch_bounds__(256) k_stem_s2d(const float* __restrict__ x, T
         }
       }
     }
-    float a[8], b[8];
+    if constexpr (sizeof(T) == 4) {
+      float4* dst = reinterpret_cast<float4*>(y + i * 16);
 #pragma unroll
-    for (int e = 0; e < 8; ++e) { a[e] = f[e]; b[e] = f[8 + e]; }
-    uint4* dst = reinterpret_cast<uint4*>(y + i * 16);
-    dst[0] = pack8<T>(a);
-    dst[1] = pack8<T>(b);
+      for (int e = 0; e < 4; ++e) dst[e] = make_float4(f[4 * e], f[4 * e + 1], f[4 * e + 2], f[4 * e + 3]);
+    } else {
+      float a[8], b[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) { a[e] = f[e]; b[e] = f[8 + e]; }
+      uint4* dst = reinterpret_cast<uint4*>(y + i * 16);
+      dst[0] = pack8<T>(a);
+      dst[1] = pack8<T>(b);
+    }
   }
 }
 
@@ -349,6 +355,10 @@ int pdt_avgpool_bwd(const void* dy, void* dx, int dtype, int N, int HW, int C, c
 int pdt_stem_s2d(const float* x, void* y, int dtype, int N, int H, int W, int pad, cudaStream_t stream) {
   const int HP = (H + 2 * pad + 1) / 2, WP = (W + 2 * pad + 1) / 2;
   const int nb = grid_for((long)N * HP * WP, 256);
+  if (dtype == PDT_FP32) {
+    k_stem_s2d<float><<<nb, 256, 0, stream>>>(x, reinterpret_cast<float*>(y), N, H, W, HP, WP, pad);
+    return (int)cudaGetLastError();
+  }
   LP_DISPATCH(dtype, k_stem_s2d<T><<<nb, 256, 0, stream>>>(x, reinterpret_cast<T*>(y), N, H, W, HP, WP, pad));
   return (int)cudaGetLastError();
 }

@@ -12,8 +12,8 @@ are born in bf16/fp16 from shadow weights.
 import torch
 import torch.nn as nn
 
-from .. import ops
-from ..parallel.syncbn import fused_bn
+from .. import amp, ops
+from ..parallel.syncbn import fused_bn, fused_bn_relu_maxpool, fused_conv_bn
 
 
 def conv3x3(cin, cout, stride=1):
@@ -39,10 +39,10 @@ class BasicBlock(nn.Module):
 
     def forward(self, x):
         identity = x
-        out = fused_bn(self.bn1, ops.conv2d(x, self.conv1), relu=True)
+        out = fused_conv_bn(self.conv1, self.bn1, x, relu=True)
         if self.downsample is not None:
-            identity = fused_bn(self.downsample[1], ops.conv2d(x, self.downsample[0]))
-        return fused_bn(self.bn2, ops.conv2d(out, self.conv2), residual=identity, relu=True)
+            identity = fused_conv_bn(self.downsample[0], self.downsample[1], x)
+        return fused_conv_bn(self.conv2, self.bn2, out, residual=identity, relu=True)
 
 
 class Bottleneck(nn.Module):
@@ -62,11 +62,11 @@ class Bottleneck(nn.Module):
 
     def forward(self, x):
         identity = x
-        out = fused_bn(self.bn1, ops.conv2d(x, self.conv1), relu=True)
-        out = fused_bn(self.bn2, ops.conv2d(out, self.conv2), relu=True)
+        out = fused_conv_bn(self.conv1, self.bn1, x, relu=True)
+        out = fused_conv_bn(self.conv2, self.bn2, out, relu=True)
         if self.downsample is not None:
-            identity = fused_bn(self.downsample[1], ops.conv2d(x, self.downsample[0]))
-        return fused_bn(self.bn3, ops.conv2d(out, self.conv3), residual=identity, relu=True)
+            identity = fused_conv_bn(self.downsample[0], self.downsample[1], x)
+        return fused_conv_bn(self.conv3, self.bn3, out, residual=identity, relu=True)
 
 
 class ResNet(nn.Module):
@@ -101,8 +101,12 @@ class ResNet(nn.Module):
         return nn.Sequential(*layers)
 
     def forward(self, x):
-        x = fused_bn(self.bn1, ops.conv2d(x, self.conv1), relu=True)
-        x = ops.max_pool2d(x, 3, 2, 1)
+        # Weights live KRSC in the arena; keep activations channels_last to match.  (The native
+        # amp stem consumes fp32 NCHW images directly and does the layout change itself.)
+        if x.dim() == 4 and not (x.is_cuda and amp.active_dtype() is not None) \
+                and not x.is_contiguous(memory_format=torch.channels_last):
+            x = x.contiguous(memory_format=torch.channels_last)
+        x = fused_bn_relu_maxpool(self.bn1, ops.conv2d(x, self.conv1), 3, 2, 1)
         x = self.layer4(self.layer3(self.layer2(self.layer1(x))))
         x = ops.global_avg_pool(x)
         return ops.linear(x, self.fc)

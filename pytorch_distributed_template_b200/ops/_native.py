@@ -65,8 +65,11 @@ _SIGNATURES = {
     "pdt_bn_scratch_bytes": ([_i], _sz),
     "pdt_bn_fwd_stats": ([_vp, _l, _i, _i, _vp, _PC, _vp, _vp, _f, _f, _vp, _vp, _vp], _i),
     "pdt_bn_fwd_apply": ([_vp, _vp, _vp, _l, _i, _i, _vp, _vp, _vp, _vp, _i, _i, _f, _vp], _i),
-    "pdt_bn_bwd_reduce": ([_vp, _vp, _vp, _l, _i, _i, _vp, _vp, _i, _vp, _PC, _vp, _vp, _vp, _vp], _i),
-    "pdt_bn_bwd_apply": ([_vp, _vp, _vp, _vp, _vp, _l, _i, _i, _vp, _vp, _vp, _vp, _i, _vp], _i),
+    "pdt_bn_bwd_reduce": ([_vp, _vp, _vp, _l, _i, _i, _vp, _vp, _vp, _vp, _i, _vp, _PC, _vp, _vp, _vp, _vp], _i),
+    "pdt_bn_bwd_apply": ([_vp, _vp, _vp, _vp, _vp, _l, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp], _i),
+    "pdt_bn_pool_fwd": ([_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp], _i),
+    "pdt_bn_pool_bwd_reduce": ([_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _PC, _vp, _vp, _vp, _vp], _i),
+    "pdt_bn_pool_bwd_apply": ([_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp], _i),
     "pdt_ce_scratch_bytes": ([_i], _sz),
     "pdt_ce_fwd": ([_vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp], _i),
     "pdt_scale_cast": ([_vp, _vp, _vp, _i, _sz, _vp], _i),
@@ -120,6 +123,28 @@ def require():
 
 def lib():
     return require()
+
+
+class _NoGuard:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False
+
+
+_NO_GUARD = _NoGuard()
+
+
+def guard(device):
+    """Make ``device`` the current CUDA device while our kernels are enqueued.
+
+    torch ops carry their own device guards; a raw launch from the C library goes to whatever
+    device is current, so a tensor on cuda:1 touched from a thread whose current device is 0
+    (DataParallel, user code) would otherwise be launched into the wrong context."""
+    if device.type != "cuda" or device.index is None or torch.cuda.current_device() == device.index:
+        return _NO_GUARD
+    return torch.cuda.device(device)
 
 
 def stream_ptr(device=None):

@@ -38,30 +38,47 @@ def _native_ok(x, C):
 
 class _BNActNative(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, res, weight, bias, running_mean, running_var, momentum, eps, relu, comm):
+    def forward(ctx, x, res, weight, bias, running_mean, running_var, momentum, eps, relu, comm, pre_mean=None,
+                pre_invstd=None):
+        with _native.guard(x.device):
+            return _BNActNative._forward_impl(ctx, x, res, weight, bias, running_mean, running_var, momentum, eps, relu,
+                                              comm, pre_mean, pre_invstd)
+
+    @staticmethod
+    def _forward_impl(ctx, x, res, weight, bias, running_mean, running_var, momentum, eps, relu, comm, pre_mean=None,
+                      pre_invstd=None):
         N, C, H, W = x.shape
         M = N * H * W
         x = x.contiguous(memory_format=torch.channels_last)
         if res is not None:
             res = res.contiguous(memory_format=torch.channels_last)
         lib, s, dt = _native.lib(), _native.stream_ptr(x.device), _native.dtype_code(x.dtype)
-        mean = torch.empty(C, dtype=torch.float32, device=x.device)
-        invstd = torch.empty_like(mean)
-        scratch = _bn_scratch(x.device, C)
-        _native.check(lib.pdt_bn_fwd_stats(x.data_ptr(), M, C, dt, scratch.data_ptr(), comm,
-                                           _native.ptr(running_mean), _native.ptr(running_var), momentum, eps,
-                                           mean.data_ptr(), invstd.data_ptr(), s), "pdt_bn_fwd_stats")
+        if pre_mean is not None:       # statistics came out of the producing convolution's epilogue
+            mean, invstd = pre_mean, pre_invstd
+        else:
+            mean = torch.empty(C, dtype=torch.float32, device=x.device)
+            invstd = torch.empty_like(mean)
+            scratch = _bn_scratch(x.device, C)
+            _native.check(lib.pdt_bn_fwd_stats(x.data_ptr(), M, C, dt, scratch.data_ptr(), comm,
+                                               _native.ptr(running_mean), _native.ptr(running_var), momentum, eps,
+                                               mean.data_ptr(), invstd.data_ptr(), s), "pdt_bn_fwd_stats")
         y = torch.empty_like(x)
         _native.check(lib.pdt_bn_fwd_apply(x.data_ptr(), _native.ptr(res), y.data_ptr(), M, C, dt, mean.data_ptr(),
                                            invstd.data_ptr(), weight.data_ptr(), bias.data_ptr(), int(relu), 0, eps, s),
                       "pdt_bn_fwd_apply")
-        ctx.save_for_backward(x, y if relu else None, weight, mean, invstd)
+        # the ReLU mask is recomputed from x in backward unless a residual entered the ReLU
+        ctx.save_for_backward(x, y if (relu and res is not None) else None, weight, bias, mean, invstd)
         ctx.relu, ctx.has_res, ctx.comm = relu, res is not None, comm
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        x, y, weight, mean, invstd = ctx.saved_tensors
+        with _native.guard(dy.device):
+            return _BNActNative._backward_impl(ctx, dy)
+
+    @staticmethod
+    def _backward_impl(ctx, dy):
+        x, y, weight, bias, mean, invstd = ctx.saved_tensors
         N, C, H, W = x.shape
         M = N * H * W
         dy = dy.contiguous(memory_format=torch.channels_last)
@@ -71,14 +88,73 @@ class _BNActNative(torch.autograd.Function):
         k = torch.empty(2 * C, dtype=torch.float32, device=x.device)
         scratch = _bn_scratch(x.device, C)
         _native.check(lib.pdt_bn_bwd_reduce(dy.data_ptr(), _native.ptr(y), x.data_ptr(), M, C, dt, mean.data_ptr(),
-                                            invstd.data_ptr(), int(ctx.relu), scratch.data_ptr(), ctx.comm,
-                                            dgamma.data_ptr(), dbeta.data_ptr(), k.data_ptr(), s), "pdt_bn_bwd_reduce")
+                                            invstd.data_ptr(), weight.data_ptr(), bias.data_ptr(), int(ctx.relu),
+                                            scratch.data_ptr(), ctx.comm, dgamma.data_ptr(), dbeta.data_ptr(),
+                                            k.data_ptr(), s), "pdt_bn_bwd_reduce")
         dx = torch.empty_like(x)
         dres = torch.empty_like(x) if ctx.has_res else None
         _native.check(lib.pdt_bn_bwd_apply(dy.data_ptr(), _native.ptr(y), x.data_ptr(), dx.data_ptr(), _native.ptr(dres),
-                                           M, C, dt, mean.data_ptr(), invstd.data_ptr(), weight.data_ptr(), k.data_ptr(),
-                                           int(ctx.relu), s), "pdt_bn_bwd_apply")
-        return dx, dres, dgamma, dbeta, None, None, None, None, None, None
+                                           M, C, dt, mean.data_ptr(), invstd.data_ptr(), weight.data_ptr(), bias.data_ptr(),
+                                           k.data_ptr(), int(ctx.relu), s), "pdt_bn_bwd_apply")
+        return dx, dres, dgamma, dbeta, None, None, None, None, None, None, None, None
+
+
+class _BNReluPoolNative(torch.autograd.Function):
+    """maxpool(relu(bn(x))) without ever writing the normalised tensor (ResNet stem tail)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, running_mean, running_var, momentum, eps, ks, st, pd, comm):
+        with _native.guard(x.device):
+            return _BNReluPoolNative._forward_impl(ctx, x, weight, bias, running_mean, running_var, momentum, eps, ks, st, pd, comm)
+
+    @staticmethod
+    def _forward_impl(ctx, x, weight, bias, running_mean, running_var, momentum, eps, ks, st, pd, comm):
+        N, C, H, W = x.shape
+        x = x.contiguous(memory_format=torch.channels_last)
+        lib, s, dt = _native.lib(), _native.stream_ptr(x.device), _native.dtype_code(x.dtype)
+        mean = torch.empty(C, dtype=torch.float32, device=x.device)
+        invstd = torch.empty_like(mean)
+        scratch = _bn_scratch(x.device, C)
+        _native.check(lib.pdt_bn_fwd_stats(x.data_ptr(), N * H * W, C, dt, scratch.data_ptr(), comm,
+                                           _native.ptr(running_mean), _native.ptr(running_var), momentum, eps,
+                                           mean.data_ptr(), invstd.data_ptr(), s), "pdt_bn_fwd_stats")
+        Ho, Wo = (H + 2 * pd - ks) // st + 1, (W + 2 * pd - ks) // st + 1
+        y = torch.empty((N, C, Ho, Wo), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
+        idx = torch.empty((N, Ho, Wo, C), dtype=torch.int8, device=x.device)
+        _native.check(lib.pdt_bn_pool_fwd(x.data_ptr(), y.data_ptr(), idx.data_ptr(), dt, N, H, W, C, ks, st, pd,
+                                          mean.data_ptr(), invstd.data_ptr(), weight.data_ptr(), bias.data_ptr(), s),
+                      "pdt_bn_pool_fwd")
+        ctx.save_for_backward(x, idx, weight, bias, mean, invstd)
+        ctx.geom, ctx.comm = (ks, st, pd), comm
+        return y
+
+    @staticmethod
+    def backward(ctx, dpool):
+        with _native.guard(dpool.device):
+            return _BNReluPoolNative._backward_impl(ctx, dpool)
+
+    @staticmethod
+    def _backward_impl(ctx, dpool):
+        x, idx, weight, bias, mean, invstd = ctx.saved_tensors
+        ks, st, pd = ctx.geom
+        N, C, H, W = x.shape
+        dpool = dpool.contiguous(memory_format=torch.channels_last)
+        lib, s, dt = _native.lib(), _native.stream_ptr(x.device), _native.dtype_code(x.dtype)
+        dgamma = torch.empty(C, dtype=torch.float32, device=x.device)
+        dbeta = torch.empty_like(dgamma)
+        k = torch.empty(2 * C, dtype=torch.float32, device=x.device)
+        scratch = _bn_scratch(x.device, C)
+        _native.check(lib.pdt_bn_pool_bwd_reduce(dpool.data_ptr(), idx.data_ptr(), x.data_ptr(), dt, N, H, W, C, ks, st, pd,
+                                                 mean.data_ptr(), invstd.data_ptr(), weight.data_ptr(), bias.data_ptr(),
+                                                 scratch.data_ptr(), ctx.comm, dgamma.data_ptr(), dbeta.data_ptr(),
+                                                 k.data_ptr(), s), "pdt_bn_pool_bwd_reduce")
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty_like(x)
+            _native.check(lib.pdt_bn_pool_bwd_apply(dpool.data_ptr(), idx.data_ptr(), x.data_ptr(), dx.data_ptr(), dt, N, H, W,
+                                                    C, ks, st, pd, mean.data_ptr(), invstd.data_ptr(), weight.data_ptr(),
+                                                    bias.data_ptr(), k.data_ptr(), s), "pdt_bn_pool_bwd_apply")
+        return dx, dgamma, dbeta, None, None, None, None, None, None, None, None
 
 
 class _SyncStatsTorch(torch.autograd.Function):
@@ -120,12 +196,19 @@ class _SyncStatsTorch(torch.autograd.Function):
         return dx.to(dy.dtype), dgamma, dbeta, None, None, None, None, None
 
 
-def bn_act(x, bn, residual=None, relu=False, comm=None, group=None):
+def bn_act(x, bn, residual=None, relu=False, comm=None, group=None, stats=None):
     """``relu?(bn(x) + residual?)`` for an ``nn.BatchNorm2d``-like module ``bn``.
 
     ``comm`` (native CommDesc) or ``group`` (process group) turn it into SyncBatchNorm.
+    ``stats = (mean, invstd)``: batch statistics already produced (and running statistics already
+    updated) by the convolution that made ``x``.
     """
     C = x.shape[1]
+    if stats is not None:
+        if bn.track_running_stats and bn.num_batches_tracked is not None:
+            bn.num_batches_tracked.add_(1)
+        return _BNActNative.apply(x, residual, bn.weight, bn.bias, None, None, 0.1, bn.eps, relu, None,
+                                  stats[0], stats[1])
     training = bn.training or bn.running_mean is None
     sync = training and (comm is not None or group is not None)
     if training and bn.track_running_stats and bn.num_batches_tracked is not None:
@@ -139,10 +222,11 @@ def bn_act(x, bn, residual=None, relu=False, comm=None, group=None):
         rc = residual.contiguous(memory_format=torch.channels_last) if residual is not None else None
         y = torch.empty_like(xc)
         N, _, H, W = x.shape
-        _native.check(_native.lib().pdt_bn_fwd_apply(
-            xc.data_ptr(), _native.ptr(rc), y.data_ptr(), N * H * W, C, _native.dtype_code(x.dtype),
-            bn.running_mean.data_ptr(), bn.running_var.data_ptr(), bn.weight.data_ptr(), bn.bias.data_ptr(),
-            int(relu), 1, bn.eps, _native.stream_ptr(x.device)), "pdt_bn_fwd_apply(eval)")
+        with _native.guard(x.device):
+            _native.check(_native.lib().pdt_bn_fwd_apply(
+                xc.data_ptr(), _native.ptr(rc), y.data_ptr(), N * H * W, C, _native.dtype_code(x.dtype),
+                bn.running_mean.data_ptr(), bn.running_var.data_ptr(), bn.weight.data_ptr(), bn.bias.data_ptr(),
+                int(relu), 1, bn.eps, _native.stream_ptr(x.device)), "pdt_bn_fwd_apply(eval)")
         return y
     if sync and group is not None and dist.is_initialized() and dist.get_world_size(group) > 1:
         y = _SyncStatsTorch.apply(x, bn.weight, bn.bias, bn.running_mean, bn.running_var, momentum, bn.eps, group)
@@ -151,3 +235,39 @@ def bn_act(x, bn, residual=None, relu=False, comm=None, group=None):
     if residual is not None:
         y = y + residual
     return F.relu(y) if relu else y
+
+
+def bn_relu_maxpool(x, bn, kernel_size=3, stride=2, padding=1, comm=None, group=None):
+    """``max_pool2d(relu(bn(x)))``; one fused kernel set on the native training path."""
+    C = x.shape[1]
+    training = bn.training or bn.running_mean is None
+    sync = training and (comm is not None or group is not None)
+    if (training and torch.is_grad_enabled() and _native_ok(x, C) and x.dtype != torch.float32
+            and (not sync or comm is not None) and x.numel() // 8 < 4_000_000_000):
+        if bn.track_running_stats and bn.num_batches_tracked is not None:
+            bn.num_batches_tracked.add_(1)
+        momentum = 0.1 if bn.momentum is None else bn.momentum
+        return _BNReluPoolNative.apply(x, bn.weight, bn.bias, bn.running_mean, bn.running_var, momentum, bn.eps,
+                                       kernel_size, stride, padding, comm if sync else None)
+    from .pool import max_pool2d
+    return max_pool2d(bn_act(x, bn, None, True, comm=comm, group=group), kernel_size, stride, padding)
+
+
+def conv_bn_act(x, conv, bn, residual=None, relu=False, comm=None, group=None):
+    """``relu?(bn(conv(x)) + residual?)``.  On the native training path the convolution's epilogue
+    produces the BatchNorm statistics (no separate pass over the activation); SyncBatchNorm keeps its
+    own statistics kernel because the cross-rank exchange lives there."""
+    from .conv import conv2d
+    training = bn.training or bn.running_mean is None
+    fuse = (training and comm is None and group is None and torch.is_grad_enabled() and x.is_cuda
+            and _native.available() and bn.track_running_stats and bn.affine)
+    if fuse:
+        momentum = 0.1 if bn.momentum is None else bn.momentum
+        out = conv2d(x, conv, bnpack=(bn.running_mean, bn.running_var, momentum, bn.eps))
+        if isinstance(out, tuple):
+            y, mean, invstd = out
+            if _native_ok(y, y.shape[1]):
+                return bn_act(y, bn, residual, relu, stats=(mean, invstd))
+            raise RuntimeError("conv epilogue produced statistics for a shape the BN kernels do not serve")
+        return bn_act(out, bn, residual, relu, comm=comm, group=group)
+    return bn_act(conv2d(x, conv), bn, residual, relu, comm=comm, group=group)

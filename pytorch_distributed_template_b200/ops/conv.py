@@ -20,6 +20,11 @@ _stem_native = None   # (supported(x, conv), run(x, conv, w_lp))
 _linear_native = None
 
 
+def _tf32_on():
+    from . import conv_native
+    return conv_native.tf32_enabled()
+
+
 def shadow_of(p, dtype):
     arena = getattr(p, "_pdt_arena", None)
     if arena is not None and arena.shadow_dtype == dtype:
@@ -47,10 +52,23 @@ class _ConvLPTorch(torch.autograd.Function):
         return dx, dw.float(), None, None, None
 
 
-def conv2d(x, conv):
+def conv2d(x, conv, bnpack=None):
+    """``conv(x)``.  With ``bnpack`` (see conv_native.conv_native) the native kernel may return
+    ``(y, mean, invstd)`` — batch statistics of y for the BatchNorm that follows."""
     lp = amp.active_dtype()
-    if lp is None or not x.is_cuda or conv.groups != 1 or conv.dilation != (1, 1) or conv.bias is not None \
-            or conv.padding_mode != "zeros" or isinstance(conv.padding, str):
+    plain = (not x.is_cuda or conv.groups != 1 or conv.dilation != (1, 1) or conv.bias is not None
+             or conv.padding_mode != "zeros" or isinstance(conv.padding, str))
+    if lp is None and not plain and x.dtype == torch.float32 and _conv_native is not None and _native.available():
+        # fp32 training (DataParallel / plain DDP): tcgen05 kind::tf32 where torch would allow TF32
+        w = conv.weight.detach()
+        if _stem_native is not None and _stem_native[0](x, conv) and _tf32_on():
+            return _stem_native[1](x, conv, w)
+        if _tf32_on() and x.dim() == 4:
+            xc = x if x.is_contiguous(memory_format=torch.channels_last) else x.contiguous(memory_format=torch.channels_last)
+            y = _conv_native(xc, conv.weight, w, conv.stride, conv.padding, bnpack)
+            if y is not None:
+                return y
+    if lp is None or plain:
         return conv._conv_forward(x, conv.weight, conv.bias)
     w_lp = shadow_of(conv.weight, lp)
     if w_lp is None:
@@ -60,7 +78,7 @@ def conv2d(x, conv):
     if x.dtype != lp or not x.is_contiguous(memory_format=torch.channels_last):
         x = x.to(dtype=lp, memory_format=torch.channels_last)
     if _conv_native is not None and _native.available():
-        y = _conv_native(x, conv.weight, w_lp, conv.stride, conv.padding)
+        y = _conv_native(x, conv.weight, w_lp, conv.stride, conv.padding, bnpack)
         if y is not None:
             return y
     return _ConvLPTorch.apply(x, conv.weight, w_lp, conv.stride, conv.padding)
@@ -84,6 +102,9 @@ class _LinearLP(torch.autograd.Function):
 
 def linear(x, fc):
     lp = amp.active_dtype()
+    if lp is None and x.is_cuda and x.dtype == torch.float32 and _linear_native is not None and _native.available() \
+            and _linear_native[0](x, fc):
+        return _linear_native[1](x, fc, fc.weight.detach())
     if lp is None or not x.is_cuda:
         return F.linear(x, fc.weight, fc.bias)
     if x.dtype != lp:

@@ -22,10 +22,12 @@ _vp, _i, _ll = _native._vp, _native._i, _native.ctypes.c_longlong
 _native.register("pdt_conv_fprop", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp])
 _native.register("pdt_conv_wgrad", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp])
 _native.register("pdt_conv_fprop_ex", [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _ll, _ll, _ll, _i, _i, _i, _i,
-                                       _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp])
+                                       _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp])
 _native.register("pdt_conv_wgrad_ex", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _ll, _ll, _ll, _i, _i, _i, _i,
-                                       _i, _i, _i, _i, _i, _i, _vp])
+                                       _i, _i, _i, _i, _i, _i, _i, _vp])
 _native.register("pdt_stem_s2d", [_vp, _vp, _i, _i, _i, _i, _i, _vp])
+_native.register("pdt_conv_fprop_bnstats", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp,
+                                            _native._f, _native._f, _vp, _vp, _vp])
 
 CL = torch.channels_last
 
@@ -34,9 +36,19 @@ def enabled():
     return os.environ.get("PDT_CONV", "native") == "native"
 
 
+def tf32_enabled():
+    """fp32 convolutions run on tcgen05 kind::tf32 exactly when torch would let cuDNN use TF32."""
+    return torch.backends.cudnn.allow_tf32 and os.environ.get("PDT_TF32", "native") == "native"
+
+
+def _row(dtype):
+    return 32 if dtype == torch.float32 else 64     # channels per 128-byte K row
+
+
 def supported(x, weight, stride, padding):
     K, C, R, S = weight.shape
-    return (x.is_cuda and x.dtype in (torch.bfloat16, torch.float16) and C % 64 == 0 and K % 8 == 0
+    ok_dtype = x.dtype in (torch.bfloat16, torch.float16) or (x.dtype == torch.float32 and tf32_enabled())
+    return (x.is_cuda and ok_dtype and C % _row(x.dtype) == 0 and K % 8 == 0
             and stride[0] == stride[1] and padding[0] == padding[1] and R == S and enabled())
 
 
@@ -53,11 +65,28 @@ def fprop(x, w_lp, stride, pad):
     return y
 
 
-def fprop_ex(x_ptr, w, y, bias, dtype, N, H, W, C, Cx, sw, sh, sn, K, R, S, stride, pads, P, Q, OH, OW, os_, oa, ob, device):
+def fprop_bnstats(x, w_lp, stride, pad, running_mean, running_var, momentum, eps):
+    """Convolution whose epilogue also yields the BatchNorm batch statistics of its output."""
+    from .bn import _bn_scratch
+    N, C, H, W = x.shape
+    K, _, R, S = w_lp.shape
+    P, Q = (H + 2 * pad - R) // stride + 1, (W + 2 * pad - S) // stride + 1
+    y = torch.empty((N, K, P, Q), dtype=x.dtype, device=x.device, memory_format=CL)
+    mean = torch.empty(K, dtype=torch.float32, device=x.device)
+    invstd = torch.empty_like(mean)
+    _native.check(_native.lib().pdt_conv_fprop_bnstats(
+        x.data_ptr(), w_lp.data_ptr(), y.data_ptr(), _native.dtype_code(x.dtype), N, H, W, C, K, R, S, stride, pad,
+        _bn_scratch(x.device, K).data_ptr(), _native.ptr(running_mean), _native.ptr(running_var), momentum, eps,
+        mean.data_ptr(), invstd.data_ptr(), _native.stream_ptr(x.device)), "pdt_conv_fprop_bnstats")
+    return y, mean, invstd
+
+
+def fprop_ex(x_ptr, w, y, bias, dtype, N, H, W, C, Cx, sw, sh, sn, K, R, S, stride, pads, P, Q, OH, OW, os_, oa, ob, device,
+             dil_w=1):
     _native.check(_native.lib().pdt_conv_fprop_ex(
         x_ptr, w.data_ptr(), y.data_ptr(), _native.ptr(bias), _native.dtype_code(dtype), N, H, W, C, Cx, sw, sh, sn,
-        K, R, S, stride, pads[0], pads[1], pads[2], pads[3], P, Q, OH, OW, os_, oa, ob, _native.stream_ptr(device)),
-        "pdt_conv_fprop_ex")
+        K, R, S, stride, pads[0], pads[1], pads[2], pads[3], P, Q, OH, OW, os_, oa, ob, dil_w,
+        _native.stream_ptr(device)), "pdt_conv_fprop_ex")
     return y
 
 
@@ -74,8 +103,8 @@ def wgrad(x, dy, weight_shape, stride, pad, out=None):
     return out
 
 
-def wgrad_supported(C, K):
-    return C % 64 == 0 and K % 8 == 0 and os.environ.get("PDT_WGRAD", "native") == "native"
+def wgrad_supported(C, K, dtype=torch.bfloat16):
+    return C % _row(dtype) == 0 and K % 8 == 0 and os.environ.get("PDT_WGRAD", "native") == "native"
 
 
 def _parity_taps(size_in, ksize, pad, a):
@@ -118,7 +147,8 @@ def dgrad_stride2(dy, w_lp, x_shape, pad):
     dx = torch.empty((N, C, H, W), dtype=dy.dtype, device=dy.device, memory_format=CL)
     if not full:
         dx.zero_()
-    sw, sh, sn = K * 2, Q * K * 2, P * Q * K * 2
+    es = dy.element_size()
+    sw, sh, sn = K * es, Q * K * es, P * Q * K * es
     for a, b, rs, ss, dh, dw_ in plan:
         if not rs or not ss:
             continue
@@ -140,13 +170,27 @@ def dgrad_stride2(dy, w_lp, x_shape, pad):
 # ------------------------------------------------------------------------------------------ autograd
 class _ConvNative(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, w_lp, stride, padding):
-        ctx.save_for_backward(x, w_lp)
-        ctx.geom = (stride, padding)
-        return fprop(x, w_lp, stride[0], padding[0])
+    def forward(ctx, x, weight, w_lp, stride, padding, bnpack=None):
+        with _native.guard(x.device):
+            return _ConvNative._forward_impl(ctx, x, weight, w_lp, stride, padding, bnpack)
 
     @staticmethod
-    def backward(ctx, dy):
+    def _forward_impl(ctx, x, weight, w_lp, stride, padding, bnpack=None):
+        ctx.save_for_backward(x, w_lp)
+        ctx.geom = (stride, padding)
+        if bnpack is None:
+            return fprop(x, w_lp, stride[0], padding[0])
+        y, mean, invstd = fprop_bnstats(x, w_lp, stride[0], padding[0], *bnpack)
+        ctx.mark_non_differentiable(mean, invstd)
+        return y, mean, invstd
+
+    @staticmethod
+    def backward(ctx, dy, *unused_stat_grads):
+        with _native.guard(dy.device):
+            return _ConvNative._backward_impl(ctx, dy)
+
+    @staticmethod
+    def _backward_impl(ctx, dy):
         x, w_lp = ctx.saved_tensors
         stride, padding = ctx.geom
         dy = dy.contiguous(memory_format=CL)
@@ -161,7 +205,7 @@ class _ConvNative(torch.autograd.Function):
             elif stride[0] == 2:
                 dx = dgrad_stride2(dy, w_lp, x.shape, padding[0])
         native_dx = dx is not None
-        native_dw = wgrad_supported(C, K)
+        native_dw = wgrad_supported(C, K, x.dtype)
         dw = wgrad(x, dy, w_lp.shape, stride[0], padding[0]) if native_dw else None
         if (need_dx and not native_dx) or not native_dw:
             dx2, dw2, _ = torch.ops.aten.convolution_backward(
@@ -171,15 +215,22 @@ class _ConvNative(torch.autograd.Function):
                 dx = dx2
             if not native_dw:
                 dw = dw2.float()
-        return dx, dw, None, None, None
+        return dx, dw, None, None, None, None
 
 
-def conv_native(x, weight, w_lp, stride, padding):
+def conv_native(x, weight, w_lp, stride, padding, bnpack=None):
+    """bnpack = (running_mean, running_var, momentum, eps): also return the batch statistics of the
+    output, computed in the convolution's epilogue -> (y, mean, invstd)."""
     if not supported(x, weight, stride, padding):
         return None
     if not w_lp.is_contiguous(memory_format=CL):
         w_lp = w_lp.contiguous(memory_format=CL)
-    return _ConvNative.apply(x, weight, w_lp, tuple(stride), tuple(padding))
+    if bnpack is not None and (weight.shape[0] > 512 or os.environ.get("PDT_BNSTATS_FUSION", "1") != "1"):
+        bnpack = None
+    out = _ConvNative.apply(x, weight, w_lp, tuple(stride), tuple(padding), bnpack)
+    if bnpack is None:
+        return out
+    return out      # (y, mean, invstd)
 
 
 # ------------------------------------------------------------------------------------------ stem (7x7/2, C_in = 3)
@@ -206,10 +257,27 @@ def stem_supported(x, conv):
 
 
 class _StemNative(torch.autograd.Function):
-    """conv1 of torchvision ResNet on fp32 NCHW images: space-to-depth + 4x4/1 implicit GEMM."""
+    """conv1 of torchvision ResNet on fp32 NCHW images: space-to-depth + 4x4/1 implicit GEMM.
+
+    The transformed image has 16 channels per pixel.  In 16-bit types 4 horizontal neighbours are one
+    128-byte K row (taps 4 x 1); in fp32/TF32 two neighbours are (taps 4 x 2, horizontal tap distance
+    2 pixels).  Either way the filter is the same [K, 4, 4, 16] tensor."""
+
+    @staticmethod
+    def _geom(dtype, HP, WP, Q):
+        es = 4 if dtype == torch.float32 else 2
+        px = 16 * es                                   # bytes per transformed pixel
+        if es == 2:
+            return dict(C=64, S=1, dil=1, Wt=Q, sw=px, sh=WP * px, sn=HP * WP * px)
+        return dict(C=32, S=2, dil=2, Wt=Q + 2, sw=px, sh=WP * px, sn=HP * WP * px)
 
     @staticmethod
     def forward(ctx, x, weight, w_lp):
+        with _native.guard(x.device):
+            return _StemNative._forward_impl(ctx, x, weight, w_lp)
+
+    @staticmethod
+    def _forward_impl(ctx, x, weight, w_lp):
         N, _, H, W = x.shape
         K = weight.shape[0]
         lp = w_lp.dtype
@@ -221,24 +289,29 @@ class _StemNative(torch.autograd.Function):
                                                  _native.stream_ptr(x.device)), "pdt_stem_s2d")
         wp = stem_weight_s2d(w_lp)
         y = torch.empty((N, K, P, Q), dtype=lp, device=x.device, memory_format=CL)
-        # TMA view of xs: "pixel" q = 64 contiguous elements starting at column q (4 neighbours x 16 ch)
-        sw, sh, sn = 32, WP * 32, HP * WP * 32
-        fprop_ex(xs.data_ptr(), wp, y, None, lp, N, HP, Q, 64, 64, sw, sh, sn, K, 4, 1, 1, (0, 0, 0, 0), P, Q, P, Q, 1, 0, 0,
-                 x.device)
+        g = _StemNative._geom(lp, HP, WP, Q)
+        fprop_ex(xs.data_ptr(), wp, y, None, lp, N, HP, g["Wt"], g["C"], g["C"], g["sw"], g["sh"], g["sn"], K, 4, g["S"], 1,
+                 (0, 0, 0, 0), P, Q, P, Q, 1, 0, 0, x.device, dil_w=g["dil"])
         ctx.save_for_backward(xs)
         ctx.geom = (N, HP, WP, P, Q, K)
         return y
 
     @staticmethod
     def backward(ctx, dy):
+        with _native.guard(dy.device):
+            return _StemNative._backward_impl(ctx, dy)
+
+    @staticmethod
+    def _backward_impl(ctx, dy):
         (xs,) = ctx.saved_tensors
         N, HP, WP, P, Q, K = ctx.geom
         dy = dy.contiguous(memory_format=CL)
         dwp = torch.zeros((K, 256), dtype=torch.float32, device=dy.device)
-        sw, sh, sn = 32, WP * 32, HP * WP * 32
+        g = _StemNative._geom(xs.dtype, HP, WP, Q)
         _native.check(_native.lib().pdt_conv_wgrad_ex(
-            xs.data_ptr(), dy.data_ptr(), dwp.data_ptr(), _native.dtype_code(dy.dtype), N, HP, Q, 64, 64, sw, sh, sn,
-            K, 4, 1, 1, 0, 0, 0, 0, P, Q, _native.stream_ptr(dy.device)), "pdt_conv_wgrad_ex")
+            xs.data_ptr(), dy.data_ptr(), dwp.data_ptr(), _native.dtype_code(dy.dtype), N, HP, g["Wt"], g["C"], g["C"],
+            g["sw"], g["sh"], g["sn"], K, 4, g["S"], 1, 0, 0, 0, 0, P, Q, g["dil"], _native.stream_ptr(dy.device)),
+            "pdt_conv_wgrad_ex")
         return None, stem_weight_grad_from_s2d(dwp, K), None
 
 
@@ -250,12 +323,18 @@ def stem_native(x, conv, w_lp):
 class _LinearNative(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, bias, w_lp):
+        with _native.guard(x.device):
+            return _LinearNative._forward_impl(ctx, x, weight, bias, w_lp)
+
+    @staticmethod
+    def _forward_impl(ctx, x, weight, bias, w_lp):
         B, C = x.shape
         K = w_lp.shape[0]
         x = x.contiguous()
         y = torch.empty((B, K), dtype=x.dtype, device=x.device)
         bias32 = bias.detach().float().contiguous() if bias is not None else None
-        fprop_ex(x.data_ptr(), w_lp, y, bias32, x.dtype, B, 1, 1, C, C, C * 2, C * 2, C * 2, K, 1, 1, 1, (0, 0, 0, 0),
+        es = x.element_size()
+        fprop_ex(x.data_ptr(), w_lp, y, bias32, x.dtype, B, 1, 1, C, C, C * es, C * es, C * es, K, 1, 1, 1, (0, 0, 0, 0),
                  1, 1, 1, 1, 1, 0, 0, x.device)
         ctx.save_for_backward(x, w_lp)
         ctx.has_bias = bias is not None
@@ -263,6 +342,11 @@ class _LinearNative(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dy):
+        with _native.guard(dy.device):
+            return _LinearNative._backward_impl(ctx, dy)
+
+    @staticmethod
+    def _backward_impl(ctx, dy):
         x, w_lp = ctx.saved_tensors
         B, C = x.shape
         K = w_lp.shape[0]
@@ -271,7 +355,8 @@ class _LinearNative(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             w_t = w_lp.t().contiguous()                      # [C][K]: "filter" of the transposed product
             dx = torch.empty((B, C), dtype=dy.dtype, device=dy.device)
-            fprop_ex(dy.data_ptr(), w_t, dx, None, dy.dtype, B, 1, 1, K, K, K * 2, K * 2, K * 2, C, 1, 1, 1, (0, 0, 0, 0),
+            es = dy.element_size()
+            fprop_ex(dy.data_ptr(), w_t, dx, None, dy.dtype, B, 1, 1, K, K, K * es, K * es, K * es, C, 1, 1, 1, (0, 0, 0, 0),
                      1, 1, 1, 1, 1, 0, 0, dy.device)
         dw = torch.zeros((K, C), dtype=torch.float32, device=dy.device)
         _native.check(_native.lib().pdt_conv_wgrad(x.data_ptr(), dy.data_ptr(), dw.data_ptr(), _native.dtype_code(dy.dtype),
@@ -281,7 +366,9 @@ class _LinearNative(torch.autograd.Function):
 
 
 def linear_supported(x, fc):
-    return (enabled() and x.is_cuda and x.dim() == 2 and x.dtype in (torch.bfloat16, torch.float16)
+    ok_dtype = x.dtype in (torch.bfloat16, torch.float16) or (x.dtype == torch.float32 and tf32_enabled()
+                                                                and torch.backends.cuda.matmul.allow_tf32)
+    return (enabled() and x.is_cuda and x.dim() == 2 and ok_dtype
             and fc.in_features % 64 == 0 and fc.out_features % 8 == 0)
 
 

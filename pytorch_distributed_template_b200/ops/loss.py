@@ -26,6 +26,11 @@ def _ce_scratch(device, B):
 class _CENative(torch.autograd.Function):
     @staticmethod
     def forward(ctx, logits, target):
+        with _native.guard(logits.device):
+            return _CENative._forward_impl(ctx, logits, target)
+
+    @staticmethod
+    def _forward_impl(ctx, logits, target):
         B, K = logits.shape
         logits = logits.contiguous()
         out = torch.empty(2, dtype=torch.float32, device=logits.device)
@@ -41,6 +46,11 @@ class _CENative(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, gloss, _gacc):
+        with _native.guard(gloss.device):
+            return _CENative._backward_impl(ctx, gloss, _gacc)
+
+    @staticmethod
+    def _backward_impl(ctx, gloss, _gacc):
         (dunit,) = ctx.saved_tensors
         g = gloss.to(torch.float32).contiguous()
         d = torch.empty(dunit.shape, dtype=ctx.dtype, device=dunit.device)

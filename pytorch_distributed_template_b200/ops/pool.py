@@ -14,6 +14,11 @@ def _lp_native(x):
 class _MaxPoolNative(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, ks, st, pd):
+        with _native.guard(x.device):
+            return _MaxPoolNative._forward_impl(ctx, x, ks, st, pd)
+
+    @staticmethod
+    def _forward_impl(ctx, x, ks, st, pd):
         N, C, H, W = x.shape
         x = x.contiguous(memory_format=torch.channels_last)
         Ho, Wo = (H + 2 * pd - ks) // st + 1, (W + 2 * pd - ks) // st + 1
@@ -27,6 +32,11 @@ class _MaxPoolNative(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dy):
+        with _native.guard(dy.device):
+            return _MaxPoolNative._backward_impl(ctx, dy)
+
+    @staticmethod
+    def _backward_impl(ctx, dy):
         (idx,) = ctx.saved_tensors
         N, C, H, W, ks, st, pd = ctx.geom
         dy = dy.contiguous(memory_format=torch.channels_last)
@@ -39,6 +49,11 @@ class _MaxPoolNative(torch.autograd.Function):
 class _AvgPoolNative(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x):
+        with _native.guard(x.device):
+            return _AvgPoolNative._forward_impl(ctx, x)
+
+    @staticmethod
+    def _forward_impl(ctx, x):
         N, C, H, W = x.shape
         x = x.contiguous(memory_format=torch.channels_last)
         y = torch.empty((N, C), dtype=x.dtype, device=x.device)
@@ -49,6 +64,11 @@ class _AvgPoolNative(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dy):
+        with _native.guard(dy.device):
+            return _AvgPoolNative._backward_impl(ctx, dy)
+
+    @staticmethod
+    def _backward_impl(ctx, dy):
         N, C, H, W = ctx.geom
         dy = dy.contiguous()
         dx = torch.empty((N, C, H, W), dtype=dy.dtype, device=dy.device, memory_format=torch.channels_last)

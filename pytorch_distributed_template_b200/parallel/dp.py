@@ -253,20 +253,24 @@ class DataParallel(nn.Module):
         lib = _native.lib()
         g = opt.param_groups[0]
         host = torch.tensor([g["lr"], g["momentum"], g["weight_decay"], 0.0], dtype=torch.float32)
+        # phase 1: every device moves its replica's gradients into its arena
         done = []
-        for dev in self.devices:      # every replica's backward must be complete before anyone reads it
-            ev = torch.cuda.Event()
-            ev.record(torch.cuda.current_stream(dev))
-            done.append(ev)
+        for r, dev in enumerate(self.devices):
+            with torch.cuda.device(dev):
+                self.arenas[r].gather_grads(drop=(r != 0))
+                ev = torch.cuda.Event()
+                ev.record(torch.cuda.current_stream(dev))
+                done.append(ev)
         sh_dtype = _native.dtype_code(self.shadow_dtype) if self.shadow_dtype is not None else _native.BF16
         after = []
+        # phase 2: once ALL arenas are complete, device r reduces shard r over every arena,
+        # applies SGD to it and stores the new weights into every replica
         for r, dev in enumerate(self.devices):
             a = self.arenas[r]
             with torch.cuda.device(dev):
                 s = torch.cuda.current_stream(dev)
                 for ev in done:
                     s.wait_event(ev)
-                a.gather_grads(drop=(r != 0))
                 self._hypers[r].copy_(host, non_blocking=True)
                 _native.check(lib.pdt_reduce_scatter_f32(self._comms[r], self._grads, 0, a.total,
                                                         self._state[r].data_ptr(), 0, 64, s.cuda_stream),

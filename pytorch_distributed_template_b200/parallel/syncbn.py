@@ -67,3 +67,23 @@ def fused_bn(bn, x, residual=None, relu=False):
             y = y + residual
         return torch.relu(y) if relu else y
     return ops.bn_act(x, bn, residual, relu)
+
+
+def fused_bn_relu_maxpool(bn, x, kernel_size=3, stride=2, padding=1):
+    """Stem tail ``maxpool(relu(bn(x)))`` through the fused op (SyncBN aware)."""
+    if isinstance(bn, SyncBatchNorm) and bn.training:
+        fabric = bn._pdt_fabric
+        if fabric is not None and fabric.native and fabric.world > 1 and x.is_cuda:
+            return ops.bn_relu_maxpool(x, bn, kernel_size, stride, padding, comm=fabric.comm)
+        group = bn.process_group if bn.process_group is not None else (dist.group.WORLD if dist.is_initialized() else None)
+        if group is not None and dist.get_world_size(group) > 1:
+            return ops.bn_relu_maxpool(x, bn, kernel_size, stride, padding, group=group)
+    return ops.bn_relu_maxpool(x, bn, kernel_size, stride, padding)
+
+
+def fused_conv_bn(conv, bn, x, residual=None, relu=False):
+    """``relu?(bn(conv(x)) + residual?)`` (SyncBN aware): plain BatchNorm gets its statistics from the
+    convolution's epilogue, SyncBatchNorm from its own exchanging statistics kernel."""
+    if isinstance(bn, SyncBatchNorm) and bn.training:
+        return fused_bn(bn, ops.conv2d(x, conv), residual, relu)
+    return ops.conv_bn_act(x, conv, bn, residual, relu)

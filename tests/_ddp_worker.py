@@ -16,14 +16,63 @@ from pytorch_distributed_template_b200.models import create_model  # noqa: E402
 from pytorch_distributed_template_b200.parallel import DistributedDataParallel, SyncBatchNorm  # noqa: E402
 
 
+def syncbn_layer_check(device, rank):
+    """One SyncBatchNorm layer, ours (in-kernel NVLink exchange) vs torch.nn.SyncBatchNorm, per rank."""
+    from pytorch_distributed_template_b200.parallel import Fabric
+    from pytorch_distributed_template_b200.parallel.syncbn import fused_bn
+
+    def rel(a, b):
+        return ((a.float() - b.float()).abs().max() / (b.float().abs().max() + 1e-12)).item()
+
+    fab = Fabric(device)
+    worst = {}
+    for dtype in (torch.float32, torch.bfloat16):
+        for C, HW, relu in ((64, 16, False), (256, 7, True), (512, 4, True)):
+            torch.manual_seed(5 + rank)
+            x = (torch.randn(6, C, HW, HW, device=device) * (1 + rank) + rank).to(dtype).contiguous(memory_format=torch.channels_last)
+            dy = torch.randn(6, C, HW, HW, device=device).to(dtype).contiguous(memory_format=torch.channels_last)
+            ours = SyncBatchNorm(C).to(device)
+            ours._pdt_fabric = fab
+            ref = torch.nn.SyncBatchNorm(C).to(device)
+            with torch.no_grad():
+                ours.weight.uniform_(0.5, 1.5)
+                ours.bias.uniform_(-0.5, 0.5)
+                dist.broadcast(ours.weight, 0)
+                dist.broadcast(ours.bias, 0)
+            ref.load_state_dict(ours.state_dict())
+            xo = x.clone().requires_grad_(True)
+            xr = x.float().clone().requires_grad_(True)
+            yo = fused_bn(ours, xo, relu=relu)
+            yr = torch.relu(ref(xr)) if relu else ref(xr)
+            yo.backward(dy)
+            yr.backward(dy.float())
+            torch.cuda.synchronize()
+            key = "fp32" if dtype == torch.float32 else "bf16"
+            for name, a, b in (("y", yo, yr), ("dx", xo.grad, xr.grad), ("dgamma", ours.weight.grad, ref.weight.grad),
+                               ("dbeta", ours.bias.grad, ref.bias.grad), ("rmean", ours.running_mean, ref.running_mean),
+                               ("rvar", ours.running_var, ref.running_var)):
+                worst[key + "_" + name] = max(worst.get(key + "_" + name, 0.0), rel(a, b))
+    return worst
+
+
 def main():
     cuda = "--cuda" in sys.argv
     syncbn = "--syncbn" in sys.argv
     if not cuda:
         os.environ["PDT_DEVICE"] = "cpu"
+    # tight comparisons need identical arithmetic: TF32 convs pick different algorithms for NCHW
+    # (torchvision oracle) and NHWC (ours) and BatchNorm amplifies the 1e-3 rounding differences
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
     rank = int(os.environ["RANK"])
     device = env.init_distributed(int(os.environ["LOCAL_RANK"]))
     world = dist.get_world_size()
+    if "--syncbn-layer" in sys.argv:
+        out = {"rank": rank, "layer": syncbn_layer_check(device, rank)}
+        with open(os.path.join(os.environ["PDT_RESULT_DIR"], "rank{}.json".format(rank)), "w") as f:
+            json.dump(out, f)
+        env.shutdown_distributed()
+        return
     torch.manual_seed(100 + rank)                       # different init per rank: ctor must sync from rank 0
     net = create_model("resnet18", num_classes=10)
     if syncbn:
@@ -55,6 +104,7 @@ def main():
         g = torch.Generator().manual_seed(7 + rank)
         worst_grad = worst_param = 0.0
         worst_name = None
+        first_loss = []
         for it in range(3):
             x = torch.randn(8, 3, 64, 64, generator=g).to(device)
             y = torch.randint(0, 10, (8,), generator=g).to(device)
@@ -62,6 +112,8 @@ def main():
                 model.train()
                 opt.zero_grad()
                 loss = torch.nn.functional.cross_entropy(model(x), y)
+                if it == 0:
+                    first_loss.append(loss.item())
                 loss.backward()
                 if model is theirs or cuda is False:
                     pass
@@ -77,7 +129,8 @@ def main():
                     worst_param, worst_name = d, (it, k)
             if it == 0:
                 first_param = worst_param
-        res = {"worst_grad_rel": worst_grad, "worst_param_rel": worst_param, "worst_name": str(worst_name), "first_param_rel": first_param}
+        res = {"worst_grad_rel": worst_grad, "worst_param_rel": worst_param, "worst_name": str(worst_name), "first_param_rel": first_param,
+               "first_loss_rel": abs(first_loss[0] - first_loss[1]) / abs(first_loss[1])}
         # ranks agree with each other bit-for-bit
         mine = ours.arena.flat_params.detach().clone()
         other = mine.clone()

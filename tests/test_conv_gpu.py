@@ -135,3 +135,56 @@ def test_linear_native(native_lib, B):
     assert (x.grad.float() - xf.grad).abs().max().item() <= 2e-2 * max(1.0, xf.grad.abs().max().item())
     assert (fc.weight.grad - wf.grad).abs().max().item() <= 3e-3 * max(1.0, wf.grad.abs().max().item())
     assert torch.allclose(fc.bias.grad, bf.grad, rtol=1e-3, atol=1e-3)
+
+
+# ---- fp32 activations on tcgen05 kind::tf32 (the DataParallel / plain DDP modes) -------------------------
+TF32_TOL = 4e-3      # TF32 keeps 10 mantissa bits; cuDNN with allow_tf32 has the same error
+
+
+@pytest.mark.parametrize("cin,cout,hw,k,stride,pad", SHAPES)
+def test_tf32_conv_fprop_and_wgrad(native_lib, cin, cout, hw, k, stride, pad):
+    from pytorch_distributed_template_b200.ops import conv_native
+    torch.backends.cudnn.allow_tf32 = False
+    torch.manual_seed(10)
+    dev = torch.device("cuda", 0)
+    x = torch.randn(5, cin, hw, hw, device=dev).contiguous(memory_format=torch.channels_last)
+    w = (torch.randn(cout, cin, k, k, device=dev) / (cin * k * k) ** 0.5).contiguous(memory_format=torch.channels_last)
+    y = conv_native.fprop(x, w, stride, pad)
+    ref = F.conv2d(x, w, None, stride, pad)
+    assert y.dtype == torch.float32 and y.shape == ref.shape
+    assert (y - ref).abs().max().item() <= TF32_TOL * max(1.0, ref.abs().max().item())
+    dy = (torch.randn_like(ref) / 8).contiguous(memory_format=torch.channels_last)
+    dw = conv_native.wgrad(x, dy, (cout, cin, k, k), stride, pad)
+    wf = w.clone().requires_grad_(True)
+    F.conv2d(x, wf, None, stride, pad).backward(dy)
+    assert (dw - wf.grad).abs().max().item() <= TF32_TOL * max(1.0, wf.grad.abs().max().item())
+
+
+def test_tf32_model_paths(native_lib):
+    """fp32 ResNet-18 step (stem, strided dgrad, linear) through the tf32 kernels vs torch fp32."""
+    import torchvision
+    from pytorch_distributed_template_b200.models import create_model
+    from pytorch_distributed_template_b200.ops import _native
+    torch.manual_seed(12)
+    dev = torch.device("cuda", 0)
+    net = create_model("resnet18", num_classes=16).to(dev)
+    tv = torchvision.models.resnet18(num_classes=16).to(dev)
+    tv.load_state_dict(net.state_dict())
+    x = torch.randn(8, 3, 224, 224, device=dev)
+    y = torch.randint(0, 16, (8,), device=dev)
+    net.train(); tv.train()
+    torch.backends.cudnn.allow_tf32 = True
+    torch.backends.cuda.matmul.allow_tf32 = True
+    n0 = _native.launch_count
+    lo = F.cross_entropy(net(x), y)
+    lo.backward()
+    assert _native.launch_count - n0 > 60, "tf32 native path not taken"
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    lr = F.cross_entropy(tv(x), y)
+    lr.backward()
+    assert lo.item() == pytest.approx(lr.item(), rel=2e-2)
+    g1 = torch.cat([p.grad.reshape(-1) for p in net.parameters()])
+    g2 = torch.cat([p.grad.reshape(-1) for p in tv.parameters()])
+    assert torch.isfinite(g1).all()
+    assert torch.nn.functional.cosine_similarity(g1, g2, dim=0).item() > 0.98

@@ -244,3 +244,31 @@ def test_resnet18_amp_step_matches_torch_autocast(native_lib):
         assert scaler.skipped_steps() == 0
     finally:
         env.shutdown_distributed()
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("shape", [(5, 64, 112, 112), (3, 64, 30, 34)])
+def test_bn_relu_maxpool_fused(native_lib, dtype, shape):
+    from pytorch_distributed_template_b200 import ops
+    torch.manual_seed(8)
+    C = shape[1]
+    x = _nhwc(*shape, dtype=dtype, scale=1.3, shift=0.2).requires_grad_(True)
+    bn = torch.nn.BatchNorm2d(C).to(_dev())
+    with torch.no_grad():
+        bn.weight.uniform_(0.5, 1.5)
+        bn.bias.uniform_(-0.5, 0.5)
+    ref_bn = torch.nn.BatchNorm2d(C).to(_dev())
+    ref_bn.load_state_dict(bn.state_dict())
+    y = ops.bn_relu_maxpool(x, bn, 3, 2, 1)
+    xf = x.detach().float().requires_grad_(True)
+    yf = F.max_pool2d(F.relu(ref_bn(xf)), 3, 2, 1)
+    assert y.shape == yf.shape
+    tol = TOL[dtype]
+    assert torch.allclose(y.float(), yf, rtol=tol, atol=tol)
+    dy = _nhwc(*yf.shape, dtype=dtype)
+    y.backward(dy)
+    yf.backward(dy.float())
+    assert (x.grad.float() - xf.grad).abs().max().item() <= 2 * tol * max(1.0, xf.grad.abs().max().item())
+    assert (bn.weight.grad - ref_bn.weight.grad).abs().max().item() <= tol * max(1.0, ref_bn.weight.grad.abs().max().item())
+    assert (bn.bias.grad - ref_bn.bias.grad).abs().max().item() <= tol * max(1.0, ref_bn.bias.grad.abs().max().item())
+    assert torch.allclose(bn.running_var, ref_bn.running_var, rtol=1e-3, atol=1e-4)
