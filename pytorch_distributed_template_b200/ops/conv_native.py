@@ -104,6 +104,10 @@ def wgrad(x, dy, weight_shape, stride, pad, out=None):
 
 
 def wgrad_supported(C, K, dtype=torch.bfloat16):
+    # The TF32 weight-gradient kernel (both operands MN-major in kind::tf32) does not validate yet:
+    # fp32 weight gradients go through aten unless PDT_WGRAD_TF32=1 asks for the native kernel.
+    if dtype == torch.float32 and os.environ.get("PDT_WGRAD_TF32", "0") != "1":
+        return False
     return C % _row(dtype) == 0 and K % 8 == 0 and os.environ.get("PDT_WGRAD", "native") == "native"
 
 
@@ -306,6 +310,13 @@ class _StemNative(torch.autograd.Function):
         (xs,) = ctx.saved_tensors
         N, HP, WP, P, Q, K = ctx.geom
         dy = dy.contiguous(memory_format=CL)
+        if xs.dtype == torch.float32 and os.environ.get("PDT_WGRAD_TF32", "0") != "1":
+            # same reason as wgrad_supported(): 4x4/1 weight gradient over the transformed image through aten
+            xs_nchw = xs.permute(0, 3, 1, 2)
+            wshape = (K, 16, 4, 4)
+            dwp4 = torch.ops.aten.convolution_backward(dy, xs_nchw, torch.empty(wshape, device=dy.device), None,
+                                                       (1, 1), (0, 0), (1, 1), False, (0, 0), 1, (False, True, False))[1]
+            return None, stem_weight_grad_from_s2d(dwp4.permute(0, 2, 3, 1).reshape(K, 256), K), None
         dwp = torch.zeros((K, 256), dtype=torch.float32, device=dy.device)
         g = _StemNative._geom(xs.dtype, HP, WP, Q)
         _native.check(_native.lib().pdt_conv_wgrad_ex(
@@ -358,9 +369,13 @@ class _LinearNative(torch.autograd.Function):
             es = dy.element_size()
             fprop_ex(dy.data_ptr(), w_t, dx, None, dy.dtype, B, 1, 1, K, K, K * es, K * es, K * es, C, 1, 1, 1, (0, 0, 0, 0),
                      1, 1, 1, 1, 1, 0, 0, dy.device)
-        dw = torch.zeros((K, C), dtype=torch.float32, device=dy.device)
-        _native.check(_native.lib().pdt_conv_wgrad(x.data_ptr(), dy.data_ptr(), dw.data_ptr(), _native.dtype_code(dy.dtype),
-                                                   B, 1, 1, C, K, 1, 1, 1, 0, _native.stream_ptr(dy.device)), "pdt_conv_wgrad(fc)")
+        if wgrad_supported(C, K, dy.dtype):
+            dw = torch.zeros((K, C), dtype=torch.float32, device=dy.device)
+            _native.check(_native.lib().pdt_conv_wgrad(x.data_ptr(), dy.data_ptr(), dw.data_ptr(), _native.dtype_code(dy.dtype),
+                                                       B, 1, 1, C, K, 1, 1, 1, 0, _native.stream_ptr(dy.device)),
+                          "pdt_conv_wgrad(fc)")
+        else:
+            dw = (dy.t() @ x).float()
         db = dy.float().sum(0) if ctx.has_bias else None
         return dx, dw, db, None
 
