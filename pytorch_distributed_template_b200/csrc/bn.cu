@@ -197,8 +197,9 @@ __global__ void __launch_bounds__(kThreads) k_bn_fwd_apply(const T* __restrict__
   }
   __syncthreads();
   const int cg = C / V;
+  const bool pow2 = (cg & (cg - 1)) == 0;     // always true for the shapes the statistics kernels serve
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long)gridDim.x * blockDim.x) {
-    const int c0 = (int)(i % cg) * V;
+    const int c0 = (pow2 ? (int)(i & (cg - 1)) : (int)(i % cg)) * V;
     float f[V];
     load_vec<T>(x + i * V, f);
 #pragma unroll
@@ -309,8 +310,9 @@ __global__ void __launch_bounds__(kThreads) k_bn_bwd_apply(const T* __restrict__
   }
   __syncthreads();
   const int cg = C / V;
+  const bool pow2 = (cg & (cg - 1)) == 0;     // always true for the shapes the statistics kernels serve
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long)gridDim.x * blockDim.x) {
-    const int c0 = (int)(i % cg) * V;
+    const int c0 = (pow2 ? (int)(i & (cg - 1)) : (int)(i % cg)) * V;
     float g[V], xv[V];
     load_vec<T>(dy + i * V, g);
     load_vec<T>(x + i * V, xv);
@@ -353,13 +355,19 @@ __device__ __forceinline__ void gather_pool_grad(const T* __restrict__ dpool, co
       const int tap = kh * g.ks + (w + g.pd - wo * g.st);
       const size_t o = (((size_t)n * g.Ho + ho) * g.Wo + wo) * g.C + c0;
       const uint2 pk = *reinterpret_cast<const uint2*>(idx + o);
+      uint4 dv = *reinterpret_cast<const uint4*>(dpool + o);
+      // byte-wise compare of the 8 saved taps, widened to 16-bit lane masks; a masked-out 16-bit
+      // float becomes +0.0, so no per-channel branch is needed
+      const unsigned tap4 = (unsigned)tap * 0x01010101u;
+      const unsigned mlo = __vcmpeq4(pk.x, tap4), mhi = __vcmpeq4(pk.y, tap4);
+      dv.x &= __byte_perm(mlo, 0, 0x1100);
+      dv.y &= __byte_perm(mlo, 0, 0x3322);
+      dv.z &= __byte_perm(mhi, 0, 0x1100);
+      dv.w &= __byte_perm(mhi, 0, 0x3322);
       float d[8];
-      unpack8<T>(*reinterpret_cast<const uint4*>(dpool + o), d);
+      unpack8<T>(dv, d);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const int sel = ((j < 4 ? pk.x : pk.y) >> ((j & 3) * 8)) & 0xff;
-        if (sel == tap) acc[j] += d[j];
-      }
+      for (int j = 0; j < 8; ++j) acc[j] += d[j];
     }
   }
 }
@@ -440,10 +448,12 @@ __global__ void __launch_bounds__(kThreads) k_bn_pool_bwd_reduce(const T* __rest
   }
   if (r < rpi) {
     const int hw = g.H * g.W;
-    for (long row = row0 + r; row < row1; row += rpi) {
-      const int n = (int)(row / hw);
-      const int rem = (int)(row - (long)n * hw);
-      const int h = rem / g.W, w = rem - h * g.W;
+    long row = row0 + r;
+    int n = (int)(row / hw);
+    int h = (int)(row - (long)n * hw) / g.W;
+    int w = (int)(row - (long)n * hw) - h * g.W;
+    for (; row < row1; row += rpi, w += rpi) {
+      while (w >= g.W) { w -= g.W; if (++h == g.H) { h = 0; ++n; } }     // no division in the loop
       float gy[V], xv[V];
       gather_pool_grad<T>(dpool, idx, g, n, h, w, cgi * V, gy);
       load_vec<T>(x + row * C + cgi * V, xv);
@@ -498,23 +508,22 @@ __global__ void __launch_bounds__(256) k_bn_pool_bwd_apply(const T* __restrict__
     mu[c] = mean[c];
   }
   __syncthreads();
-  const int cg = C / 8;
-  const unsigned total = (unsigned)g.N * g.H * g.W * cg;
-  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
-    const int c0 = (int)(i % cg) * 8;
-    unsigned r = i / cg;
-    const int w = (int)(r % g.W); r /= g.W;
-    const int h = (int)(r % g.H);
-    const int n = (int)(r / g.H);
+  const int cg = C / 8;                       // power of two (checked by the launcher)
+  const int cg_shift = 31 - __clz(cg);
+  const int n = blockIdx.x / g.H, h = blockIdx.x - n * g.H;          // one image row per block
+  const size_t row_base = ((size_t)n * g.H + h) * g.W * cg;
+  for (int j = threadIdx.x; j < g.W * cg; j += blockDim.x) {
+    const int w = j >> cg_shift, c0 = (j & (cg - 1)) * 8;
+    const size_t i = row_base + j;
     float gy[8], xv[8];
     gather_pool_grad<T>(dpool, idx, g, n, h, w, c0, gy);
-    unpack8<T>(*reinterpret_cast<const uint4*>(x + (size_t)i * 8), xv);
+    unpack8<T>(*reinterpret_cast<const uint4*>(x + i * 8), xv);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const float gg = fmaf(xv[j], a[c0 + j], sh[c0 + j]) > 0.f ? gy[j] : 0.f;
       gy[j] = (gg - k1[c0 + j] - (xv[j] - mu[c0 + j]) * k2[c0 + j]) * a[c0 + j];
     }
-    *reinterpret_cast<uint4*>(dx + (size_t)i * 8) = pack8<T>(gy);
+    *reinterpret_cast<uint4*>(dx + i * 8) = pack8<T>(gy);
   }
 }
 
@@ -592,10 +601,9 @@ int pdt_bn_pool_bwd_apply(const void* dpool, const int8_t* idx, const void* x, v
                           const float* beta, const float* k, cudaStream_t stream) {
   PoolGeom g;
   if (!pool_geom(g, N, H, W, C, ks, st, pd)) return PDT_E_UNSUPPORTED;
-  const long total = (long)N * H * W * (C / 8);
-  long nb = (total + 255) / 256;
-  if (nb > 148 * 16) nb = 148 * 16;
-  BNP_DISPATCH(dtype, k_bn_pool_bwd_apply<T><<<(int)nb, 256, 5 * C * sizeof(float), stream>>>(
+  if (((C / 8) & (C / 8 - 1)) != 0) return PDT_E_UNSUPPORTED;
+  const long nb = (long)N * H;                 // one block per image row
+  BNP_DISPATCH(dtype, k_bn_pool_bwd_apply<T><<<(unsigned)nb, 256, 5 * C * sizeof(float), stream>>>(
       reinterpret_cast<const T*>(dpool), idx, reinterpret_cast<const T*>(x), reinterpret_cast<T*>(dx), g, mean, invstd,
       gamma, beta, k));
   return (int)cudaGetLastError();

@@ -445,8 +445,10 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
           mbar_wait(&full[stage], phase);
           tc_fence_after();
           // MN-major, 128B swizzle: 8-pixel groups 1024 B apart (SBO), 64-channel blocks kBlkBytes apart (LBO)
-          const uint64_t da = make_sw128_desc(smem_u32(smA + stage * C::kStageBytesA), 1024, kBlkBytes);
-          const uint64_t db = make_sw128_desc(smem_u32(smB + stage * C::kStageBytesB), 1024, kBlkBytes);
+          // 32-bit MN-major operands use the 32-byte-atom swizzle: 4-pixel groups 512 B apart
+          constexpr uint32_t kSbo = sizeof(T) == 4 ? 512 : 1024, kLayout = sizeof(T) == 4 ? 1 : 2;
+          const uint64_t da = make_sw128_desc(smem_u32(smA + stage * C::kStageBytesA), kSbo, kBlkBytes, kLayout);
+          const uint64_t db = make_sw128_desc(smem_u32(smB + stage * C::kStageBytesB), kSbo, kBlkBytes, kLayout);
 #pragma unroll
           for (int k = 0; k < 4; ++k)   // UMMA_K pixels = kUK * 128 bytes per step, in (addr >> 4) units
             umma<T>(tmem_d, da + (Elem<T>::kUK * 8) * k, db + (Elem<T>::kUK * 8) * k, idesc, (ks > ks0 || k > 0) ? 1u : 0u);
@@ -588,6 +590,8 @@ int launch_wgrad(const void* x, const void* dy, float* dw, int dtype, WgradGeom&
   const int es = esize_of(dtype);
   const int kRow = 128 / es, BKP = 4 * (32 / es);
   const int smem_bytes = (dtype == PDT_FP32) ? WCfg<BN, float>::kSmemBytes : WCfg<BN, __half>::kSmemBytes;
+  // MN-major 32-bit operands need the 32-byte-atom flavour of the 128-byte swizzle (see tc.cuh)
+  const CUtensorMapSwizzle swz = (dtype == PDT_FP32) ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
   CUtensorMap tmX, tmDY;
   {
     cuuint64_t dims[4] = {(cuuint64_t)g.Cx, (cuuint64_t)g.W, (cuuint64_t)g.H, (cuuint64_t)g.N};
@@ -596,7 +600,7 @@ int launch_wgrad(const void* x, const void* dy, float* dw, int dtype, WgradGeom&
     int upper[2] = {g.pad_hi_w - (g.S - 1) * g.dil_w, g.pad_hi_h - (g.R - 1)};
     cuuint32_t estr[4] = {1, (cuuint32_t)g.stride, (cuuint32_t)g.stride, 1};
     CUresult r = g_encode_im2col(&tmX, tm_dtype(dtype), 4, const_cast<void*>(x), dims, strides, lower, upper, kRow, BKP, estr,
-                                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                                 CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return 10000 + (int)r;
     int drv = 0;
@@ -610,7 +614,7 @@ int launch_wgrad(const void* x, const void* dy, float* dw, int dtype, WgradGeom&
     cuuint32_t box[2] = {(cuuint32_t)kRow, (cuuint32_t)BKP};
     cuuint32_t estr[2] = {1, 1};
     CUresult r = g_encode_tiled(&tmDY, tm_dtype(dtype), 2, const_cast<void*>(dy), dims, strides, box, estr,
-                                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                                CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                                 CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return 20000 + (int)r;
   }

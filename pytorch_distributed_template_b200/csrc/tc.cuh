@@ -112,13 +112,17 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 // Works for K-major tiles ([rows of M/N][64 x 16-bit along K]) and for MN-major tiles
 // ([rows of K][64 x 16-bit along M/N]); `lbo_bytes` is the distance between 64-element column
 // blocks of an MN-major tile (unused for K-major).
-__device__ __forceinline__ uint64_t make_sw128_desc(uint32_t smem_addr, uint32_t sbo_bytes, uint32_t lbo_bytes) {
+// layout_type: 2 = SWIZZLE_128B; 1 = SWIZZLE_128B_BASE32B (128-byte rows swizzled in 32-byte chunks with a
+// 4-row period) — the layout tcgen05 expects for MN-major 32-bit (tf32) operands, written by TMA with
+// CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B.
+__device__ __forceinline__ uint64_t make_sw128_desc(uint32_t smem_addr, uint32_t sbo_bytes, uint32_t lbo_bytes,
+                                                    uint32_t layout_type = 2) {
   uint64_t d = 0;
   d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);              // start address
   d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;          // leading dimension byte offset
   d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;          // stride dimension byte offset
   d |= (uint64_t)1 << 46;                                    // descriptor version (sm_100)
-  d |= (uint64_t)2 << 61;                                    // SWIZZLE_128B
+  d |= (uint64_t)layout_type << 61;
   return d;
 }
 // kind::f16 instruction descriptor: fp32 accumulate, A/B both `fmt` (0 = fp16, 1 = bf16).
