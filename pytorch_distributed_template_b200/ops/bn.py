@@ -26,6 +26,17 @@ def _bn_scratch(device, C):
     return buf
 
 
+def _param_grad_slots(params, C, device):
+    """Where the BN backward kernel writes dgamma / dbeta: straight into the gradient arena when the
+    parameters live in one and it is clean (ParamArena.direct_grad), else fresh tensors."""
+    out = []
+    for p in params:
+        arena = getattr(p, "_pdt_arena", None)
+        slot = arena.direct_grad(p) if arena is not None else None
+        out.append(slot if slot is not None else torch.empty(C, dtype=torch.float32, device=device))
+    return out
+
+
 def _native_ok(x, C):
     if not (x.is_cuda and x.dim() == 4 and _native.available()):
         return False
@@ -69,6 +80,7 @@ class _BNActNative(torch.autograd.Function):
         # the ReLU mask is recomputed from x in backward unless a residual entered the ReLU
         ctx.save_for_backward(x, y if (relu and res is not None) else None, weight, bias, mean, invstd)
         ctx.relu, ctx.has_res, ctx.comm = relu, res is not None, comm
+        ctx.params = (weight, bias)
         return y
 
     @staticmethod
@@ -83,8 +95,7 @@ class _BNActNative(torch.autograd.Function):
         M = N * H * W
         dy = dy.contiguous(memory_format=torch.channels_last)
         lib, s, dt = _native.lib(), _native.stream_ptr(x.device), _native.dtype_code(x.dtype)
-        dgamma = torch.empty(C, dtype=torch.float32, device=x.device)
-        dbeta = torch.empty_like(dgamma)
+        dgamma, dbeta = _param_grad_slots(ctx.params, C, x.device)
         k = torch.empty(2 * C, dtype=torch.float32, device=x.device)
         scratch = _bn_scratch(x.device, C)
         _native.check(lib.pdt_bn_bwd_reduce(dy.data_ptr(), _native.ptr(y), x.data_ptr(), M, C, dt, mean.data_ptr(),
@@ -126,6 +137,7 @@ class _BNReluPoolNative(torch.autograd.Function):
                       "pdt_bn_pool_fwd")
         ctx.save_for_backward(x, idx, weight, bias, mean, invstd)
         ctx.geom, ctx.comm = (ks, st, pd), comm
+        ctx.params = (weight, bias)
         return y
 
     @staticmethod
@@ -140,8 +152,7 @@ class _BNReluPoolNative(torch.autograd.Function):
         N, C, H, W = x.shape
         dpool = dpool.contiguous(memory_format=torch.channels_last)
         lib, s, dt = _native.lib(), _native.stream_ptr(x.device), _native.dtype_code(x.dtype)
-        dgamma = torch.empty(C, dtype=torch.float32, device=x.device)
-        dbeta = torch.empty_like(dgamma)
+        dgamma, dbeta = _param_grad_slots(ctx.params, C, x.device)
         k = torch.empty(2 * C, dtype=torch.float32, device=x.device)
         scratch = _bn_scratch(x.device, C)
         _native.check(lib.pdt_bn_pool_bwd_reduce(dpool.data_ptr(), idx.data_ptr(), x.data_ptr(), dt, N, H, W, C, ks, st, pd,

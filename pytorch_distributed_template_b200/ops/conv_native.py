@@ -90,13 +90,20 @@ def fprop_ex(x_ptr, w, y, bias, dtype, N, H, W, C, Cx, sw, sh, sn, K, R, S, stri
     return y
 
 
+def direct_grad(param):
+    """Slot of ``param`` in its gradient arena when backward may write there directly (see ParamArena)."""
+    arena = getattr(param, "_pdt_arena", None)
+    return None if arena is None else arena.direct_grad(param)
+
+
 def wgrad(x, dy, weight_shape, stride, pad, out=None):
-    """fp32 dW [K,C,R,S] (channels_last, i.e. KRSC) from x [N,C,H,W] and dy [N,K,P,Q], both channels_last."""
+    """fp32 dW [K,C,R,S] (channels_last, i.e. KRSC) from x [N,C,H,W] and dy [N,K,P,Q], both channels_last.
+    ``out``: an already-zeroed destination the kernel accumulates into (the gradient arena)."""
     N, C, H, W = x.shape
     K, _, R, S = weight_shape
     if out is None:
         out = torch.empty((K, C, R, S), dtype=torch.float32, device=x.device, memory_format=CL)
-    out.zero_()
+        out.zero_()
     _native.check(_native.lib().pdt_conv_wgrad(x.data_ptr(), dy.data_ptr(), out.data_ptr(), _native.dtype_code(x.dtype),
                                                N, H, W, C, K, R, S, stride, pad, _native.stream_ptr(x.device)),
                   "pdt_conv_wgrad")
@@ -104,9 +111,9 @@ def wgrad(x, dy, weight_shape, stride, pad, out=None):
 
 
 def wgrad_supported(C, K, dtype=torch.bfloat16):
-    # The TF32 weight-gradient kernel (both operands MN-major in kind::tf32) does not validate yet:
-    # fp32 weight gradients go through aten unless PDT_WGRAD_TF32=1 asks for the native kernel.
-    if dtype == torch.float32 and os.environ.get("PDT_WGRAD_TF32", "0") != "1":
+    # fp32: both operands are MN-major kind::tf32 tiles (32-byte-atom swizzle); PDT_WGRAD_TF32=0 routes
+    # fp32 weight gradients through aten instead.
+    if dtype == torch.float32 and os.environ.get("PDT_WGRAD_TF32", "1") != "1":
         return False
     return C % _row(dtype) == 0 and K % 8 == 0 and os.environ.get("PDT_WGRAD", "native") == "native"
 
@@ -182,6 +189,7 @@ class _ConvNative(torch.autograd.Function):
     def _forward_impl(ctx, x, weight, w_lp, stride, padding, bnpack=None):
         ctx.save_for_backward(x, w_lp)
         ctx.geom = (stride, padding)
+        ctx.weight = weight
         if bnpack is None:
             return fprop(x, w_lp, stride[0], padding[0])
         y, mean, invstd = fprop_bnstats(x, w_lp, stride[0], padding[0], *bnpack)
@@ -210,7 +218,7 @@ class _ConvNative(torch.autograd.Function):
                 dx = dgrad_stride2(dy, w_lp, x.shape, padding[0])
         native_dx = dx is not None
         native_dw = wgrad_supported(C, K, x.dtype)
-        dw = wgrad(x, dy, w_lp.shape, stride[0], padding[0]) if native_dw else None
+        dw = wgrad(x, dy, w_lp.shape, stride[0], padding[0], out=direct_grad(ctx.weight)) if native_dw else None
         if (need_dx and not native_dx) or not native_dw:
             dx2, dw2, _ = torch.ops.aten.convolution_backward(
                 dy, x, w_lp, None, stride, padding, (1, 1), False, (0, 0), 1,
@@ -310,7 +318,7 @@ class _StemNative(torch.autograd.Function):
         (xs,) = ctx.saved_tensors
         N, HP, WP, P, Q, K = ctx.geom
         dy = dy.contiguous(memory_format=CL)
-        if xs.dtype == torch.float32 and os.environ.get("PDT_WGRAD_TF32", "0") != "1":
+        if xs.dtype == torch.float32 and os.environ.get("PDT_WGRAD_TF32", "1") != "1":
             # same reason as wgrad_supported(): 4x4/1 weight gradient over the transformed image through aten
             xs_nchw = xs.permute(0, 3, 1, 2)
             wshape = (K, 16, 4, 4)
@@ -349,6 +357,7 @@ class _LinearNative(torch.autograd.Function):
                  1, 1, 1, 1, 1, 0, 0, x.device)
         ctx.save_for_backward(x, w_lp)
         ctx.has_bias = bias is not None
+        ctx.weight = weight
         return y
 
     @staticmethod
@@ -370,7 +379,9 @@ class _LinearNative(torch.autograd.Function):
             fprop_ex(dy.data_ptr(), w_t, dx, None, dy.dtype, B, 1, 1, K, K, K * es, K * es, K * es, C, 1, 1, 1, (0, 0, 0, 0),
                      1, 1, 1, 1, 1, 0, 0, dy.device)
         if wgrad_supported(C, K, dy.dtype):
-            dw = torch.zeros((K, C), dtype=torch.float32, device=dy.device)
+            dw = direct_grad(ctx.weight)
+            if dw is None:
+                dw = torch.zeros((K, C), dtype=torch.float32, device=dy.device)
             _native.check(_native.lib().pdt_conv_wgrad(x.data_ptr(), dy.data_ptr(), dw.data_ptr(), _native.dtype_code(dy.dtype),
                                                        B, 1, 1, C, K, 1, 1, 1, 0, _native.stream_ptr(dy.device)),
                           "pdt_conv_wgrad(fc)")

@@ -96,10 +96,12 @@ class SGD(torch.optim.Optimizer):
         return self._unit_state
 
     def zero_grad(self, set_to_none=True):
-        # Gradients are views into the arena; dropping the reference is enough, the
-        # next backward overwrites every element.
+        # Gradients are views into the arena: drop the references and clear the arena with ONE memset;
+        # backward kernels then write their results straight into it (ParamArena.direct_grad).
         for p in self.param_groups[0]["params"]:
             p.grad = None
+        if self.arena is not None and self.device.type == "cuda":
+            self.arena.zero_grads()
 
     @torch.no_grad()
     def step(self, closure=None):
@@ -113,6 +115,7 @@ class SGD(torch.optim.Optimizer):
         if not capturing:
             self.sync_hyper()
         a = self.arena
+        a.grads_zeroed = False          # the arena now holds this step's gradients
         if self.owner is not None and not hasattr(self.owner, "_launch_segment"):
             self.owner.fused_step(self)          # DataParallel: per-device reduce + SGD + push
         elif self.native:

@@ -74,6 +74,7 @@ class ParamArena:
         cur.end = pos
         self.segments.append(cur)
         self.total = pos
+        self.grads_zeroed = False
         self.segment_of = {id(p): s for s in self.segments for p in s.params}
 
         # ---- storage ---------------------------------------------------------------------
@@ -140,7 +141,18 @@ class ParamArena:
             torch._foreach_copy_(dst, src)
 
     def zero_grads(self):
+        """One memset for the whole gradient arena.  Afterwards (until the next optimizer step) the native
+        weight-gradient kernels accumulate straight into the arena views, so no per-parameter zero-fill and
+        no gradient -> bucket copy is ever launched."""
         self.flat_grads.zero_()
+        self.grads_zeroed = True
+
+    def direct_grad(self, p):
+        """A fresh view of ``p``'s slot in the gradient arena if a backward kernel may write (accumulate)
+        into it directly, else None."""
+        if not self.grads_zeroed or p.grad is not None or id(p) not in self.offset:
+            return None
+        return self.grad_view(p)
 
     def describe(self):
         return {"total_elems": self.total,

@@ -258,6 +258,7 @@ class DataParallel(nn.Module):
         for r, dev in enumerate(self.devices):
             with torch.cuda.device(dev):
                 self.arenas[r].gather_grads(drop=(r != 0))
+                self.arenas[r].grads_zeroed = False
                 ev = torch.cuda.Event()
                 ev.record(torch.cuda.current_stream(dev))
                 done.append(ev)
@@ -282,10 +283,13 @@ class DataParallel(nn.Module):
                 ev = torch.cuda.Event()
                 ev.record(s)
                 after.append(ev)
-        for dev in self.devices:      # new weights were written by peers: everybody waits for everybody
+        for r, dev in enumerate(self.devices):      # new weights were written by peers: everybody waits for everybody
             s = torch.cuda.current_stream(dev)
             for ev in after:
                 s.wait_event(ev)
+            if r > 0:      # replicas' gradients were dropped above: clear their arenas for direct writes
+                with torch.cuda.device(dev):
+                    self.arenas[r].zero_grads()
 
     def zero_replica_grads(self):
         for rep in self.replicas[1:]:

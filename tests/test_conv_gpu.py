@@ -143,7 +143,7 @@ TF32_TOL = 4e-3      # TF32 keeps 10 mantissa bits; cuDNN with allow_tf32 has th
 
 @pytest.mark.parametrize("cin,cout,hw,k,stride,pad", SHAPES)
 def test_tf32_conv_fprop_and_wgrad(native_lib, cin, cout, hw, k, stride, pad):
-    """fprop on kind::tf32 must match; the tf32 wgrad kernel is reported as xfail while it is being debugged."""
+    """fprop (K-major tiles) and wgrad (MN-major tiles, 32-byte-atom swizzle) on kind::tf32."""
     from pytorch_distributed_template_b200.ops import conv_native
     torch.backends.cudnn.allow_tf32 = False
     torch.manual_seed(10)
@@ -159,9 +159,7 @@ def test_tf32_conv_fprop_and_wgrad(native_lib, cin, cout, hw, k, stride, pad):
     F.conv2d(x, wf, None, stride, pad).backward(dy)
     dw = conv_native.wgrad(x, dy, (cout, cin, k, k), stride, pad)
     err = (dw - wf.grad).abs().max().item() / max(1.0, wf.grad.abs().max().item())
-    if err > TF32_TOL:
-        pytest.xfail("TF32 weight gradient (MN-major kind::tf32) not validated yet: rel err {:.3g}; fp32 training "
-                     "routes weight gradients through aten (ops/conv_native.py wgrad_supported)".format(err))
+    assert err <= TF32_TOL, err
 
 
 def test_tf32_model_paths(native_lib):
