@@ -42,6 +42,14 @@ __device__ __forceinline__ void load_vec(const T* p, float (&f)[Vec<T>::N]) {
   }
 }
 template <typename T>
+__device__ __forceinline__ void decode_vec(const uint4& u, float (&f)[Vec<T>::N]) {
+  if constexpr (sizeof(T) == 4) {
+    f[0] = __uint_as_float(u.x); f[1] = __uint_as_float(u.y); f[2] = __uint_as_float(u.z); f[3] = __uint_as_float(u.w);
+  } else {
+    unpack8<T>(u, f);
+  }
+}
+template <typename T>
 __device__ __forceinline__ void store_vec(T* p, const float (&f)[Vec<T>::N]) {
   uint4 u;
   if constexpr (sizeof(T) == 4) {
@@ -147,12 +155,23 @@ __global__ void __launch_bounds__(kThreads) k_bn_fwd_stats(const T* __restrict__
 #pragma unroll
   for (int j = 0; j < V; ++j) s[j] = q[j] = 0.f;
   if (r < rpi) {
-#pragma unroll 4
-    for (long row = row0 + r; row < row1; row += rpi) {
-      float f[V];
-      load_vec<T>(x + row * C + cgi * V, f);
+    // all loads of a batch of kBatch rows are issued before any is consumed: the kernel runs at one
+    // 512-thread block per SM, so memory-level parallelism has to come from each thread
+    constexpr int kBatch = 8;
+    for (long row = row0 + r; row < row1; row += (long)kBatch * rpi) {
+      uint4 u[kBatch];
 #pragma unroll
-      for (int j = 0; j < V; ++j) { s[j] += f[j]; q[j] = fmaf(f[j], f[j], q[j]); }
+      for (int b = 0; b < kBatch; ++b) {
+        const long rr = row + (long)b * rpi;
+        u[b] = rr < row1 ? ldg_stream(x + rr * C + cgi * V) : make_uint4(0, 0, 0, 0);
+      }
+#pragma unroll
+      for (int b = 0; b < kBatch; ++b) {
+        float f[V];
+        decode_vec<T>(u[b], f);
+#pragma unroll
+        for (int j = 0; j < V; ++j) { s[j] += f[j]; q[j] = fmaf(f[j], f[j], q[j]); }
+      }
     }
   }
   block_fold<V>(smem, s, q, C, cg, rpi, partial);
@@ -246,23 +265,36 @@ __global__ void __launch_bounds__(kThreads) k_bn_bwd_reduce(const T* __restrict_
     sh[j] = (r < rpi && remask) ? beta[c] - mean[c] * sc[j] : 0.f;
   }
   if (r < rpi) {
-#pragma unroll 2
-    for (long row = row0 + r; row < row1; row += rpi) {
-      const long o = row * C + cgi * V;
-      float g[V], xv[V];
-      load_vec<T>(dy + o, g);
-      load_vec<T>(x + o, xv);
-      if (remask) {
+    constexpr int kBatch = 4;              // loads of 4 rows in flight per thread (see k_bn_fwd_stats)
+    const bool need_y = relu && !remask;
+    for (long row = row0 + r; row < row1; row += (long)kBatch * rpi) {
+      uint4 ug[kBatch], ux[kBatch], uy[kBatch];
 #pragma unroll
-        for (int j = 0; j < V; ++j) g[j] = fmaf(xv[j], sc[j], sh[j]) > 0.f ? g[j] : 0.f;
-      } else if (relu) {
-        float yv[V];
-        load_vec<T>(y + o, yv);
-#pragma unroll
-        for (int j = 0; j < V; ++j) g[j] = yv[j] > 0.f ? g[j] : 0.f;
+      for (int b = 0; b < kBatch; ++b) {
+        const long rr = row + (long)b * rpi;
+        const bool ok = rr < row1;
+        const long o = rr * C + cgi * V;
+        ug[b] = ok ? ldg_stream(dy + o) : make_uint4(0, 0, 0, 0);
+        ux[b] = ok ? ldg_stream(x + o) : make_uint4(0, 0, 0, 0);
+        uy[b] = (ok && need_y) ? ldg_stream(y + o) : make_uint4(0, 0, 0, 0);
       }
 #pragma unroll
-      for (int j = 0; j < V; ++j) { s[j] += g[j]; q[j] = fmaf(g[j], xv[j] - mu[j], q[j]); }
+      for (int b = 0; b < kBatch; ++b) {
+        float g[V], xv[V];
+        decode_vec<T>(ug[b], g);
+        decode_vec<T>(ux[b], xv);
+        if (remask) {
+#pragma unroll
+          for (int j = 0; j < V; ++j) g[j] = fmaf(xv[j], sc[j], sh[j]) > 0.f ? g[j] : 0.f;
+        } else if (relu) {
+          float yv[V];
+          decode_vec<T>(uy[b], yv);
+#pragma unroll
+          for (int j = 0; j < V; ++j) g[j] = yv[j] > 0.f ? g[j] : 0.f;
+        }
+#pragma unroll
+        for (int j = 0; j < V; ++j) { s[j] += g[j]; q[j] = fmaf(g[j], xv[j] - mu[j], q[j]); }
+      }
     }
   }
   block_fold<V>(smem, s, q, C, cg, rpi, partial);
