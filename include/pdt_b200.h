@@ -184,6 +184,14 @@ int pdt_conv_fprop(const void* x, const void* w, void* y, int dtype, int N, int 
 int pdt_conv_fprop_bnstats(const void* x, const void* w, void* y, int dtype, int N, int H, int W, int C, int K, int R, int S,
                            int stride, int pad, void* scratch, float* running_mean, float* running_var, float momentum,
                            float eps, float* save_mean, float* save_invstd, cudaStream_t stream);
+/* 3x3 / stride 1 / pad 1 convolution with input-patch reuse for the large feature maps (W <= 56, K in {64, 128},
+ * C % 64 == 0): one tiled TMA load per (TR+2) x (W+2) patch serves all nine taps through row-shifted shared-memory
+ * descriptors; the 64x64 filter bank stays resident in shared memory.  scratch != NULL also yields the BatchNorm
+ * batch statistics of y (as pdt_conv_fprop_bnstats).  Same cuDNN calls replaced as pdt_conv_fprop. */
+int pdt_conv3x3_halo_supported(int dtype, int N, int H, int W, int C, int K);
+int pdt_conv3x3_halo(const void* x, const void* w, void* y, int dtype, int N, int H, int W, int C, int K, void* scratch,
+                     float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
+                     float* save_invstd, cudaStream_t stream);
 /* Weight gradient (cudnnConvolutionBackwardFilter): dw [K][R][S][C] fp32 += sum over pixels; split-K over
  * the pixel dimension with red.global.add, so zero dw first.  C % 64 == 0, K % 64 == 0. */
 int pdt_conv_wgrad(const void* x, const void* dy, float* dw, int dtype, int N, int H, int W, int C, int K, int R, int S,

@@ -374,11 +374,23 @@ __global__ void __launch_bounds__(kThreads) k_bn_bwd_apply(const T* __restrict__
 // Replaces batch_norm + relu_ + max_pool2d_with_indices and their three backward kernels.
 struct PoolGeom { int N, H, W, C, Ho, Wo, ks, st, pd; };
 
+template <typename T> struct Pair2;
+template <> struct Pair2<__nv_bfloat16> { using type = __nv_bfloat162; };
+template <> struct Pair2<__half> { using type = __half2; };
+template <typename T>
+__device__ __forceinline__ uint32_t add_packed(uint32_t a, uint32_t b) {
+  using P = typename Pair2<T>::type;
+  P r = __hadd2(*reinterpret_cast<P*>(&a), *reinterpret_cast<P*>(&b));
+  return *reinterpret_cast<uint32_t*>(&r);
+}
+
+// Gradient of the (virtual) BN+ReLU output at input pixel (n, h, w): sum of the pooled gradients of the <= 4
+// windows whose arg-max is this pixel.  Accumulated in the activation dtype with packed 2-wide adds, like the
+// reference's max_pool2d backward (atomic adds in the tensor dtype).
 template <typename T>
 __device__ __forceinline__ void gather_pool_grad(const T* __restrict__ dpool, const int8_t* __restrict__ idx, const PoolGeom& g,
                                                  int n, int h, int w, int c0, float (&acc)[8]) {
-#pragma unroll
-  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  uint4 sum = make_uint4(0, 0, 0, 0);
   const int ho_lo = max(0, (h + g.pd - g.ks + g.st) / g.st), ho_hi = min(g.Ho - 1, (h + g.pd) / g.st);
   const int wo_lo = max(0, (w + g.pd - g.ks + g.st) / g.st), wo_hi = min(g.Wo - 1, (w + g.pd) / g.st);
   for (int ho = ho_lo; ho <= ho_hi; ++ho) {
@@ -396,12 +408,13 @@ __device__ __forceinline__ void gather_pool_grad(const T* __restrict__ dpool, co
       dv.y &= __byte_perm(mlo, 0, 0x3322);
       dv.z &= __byte_perm(mhi, 0, 0x1100);
       dv.w &= __byte_perm(mhi, 0, 0x3322);
-      float d[8];
-      unpack8<T>(dv, d);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) acc[j] += d[j];
+      sum.x = add_packed<T>(sum.x, dv.x);
+      sum.y = add_packed<T>(sum.y, dv.y);
+      sum.z = add_packed<T>(sum.z, dv.z);
+      sum.w = add_packed<T>(sum.w, dv.w);
     }
   }
+  unpack8<T>(sum, acc);
 }
 
 template <typename T>

@@ -1,0 +1,388 @@
+// 3x3 / stride 1 / pad 1 convolution with input-patch reuse (SURVEY K-CONV-F/-D for the large feature maps).
+//
+// The generic implicit-GEMM kernel (conv.cu) fetches the activation once PER FILTER TAP (9 TMA im2col loads
+// per 64-channel block).  On the 56x56 and 28x28 layers that makes the L2 -> SM fabric (about 42 B/clk per
+// SM), not the tensor core, the limit: ncu shows 22 % tensor-pipe utilisation at 128x64 tiles.
+// Here a tile is TR whole rows of one image in PADDED coordinates (W + 2 wide, so TR*(W+2) <= 128 outputs,
+// the two border columns are junk).  ONE tiled TMA load brings the (TR+2) x (W+2) x 64-channel patch, with
+// the halo zero-filled by TMA's out-of-bounds handling, and all nine taps read it through shared-memory
+// descriptors whose start address is shifted by (r*(W+2) + s - 1) rows: tcgen05 derives the 128B swizzle
+// from the absolute address, so a row-shifted view of a swizzled tile is still a valid K-major operand
+// (verified by csrc/probe.cu).  The 64x64 filter bank of the first stage (72 KB for all taps) stays resident
+// in shared memory for the whole kernel; wider layers stream their taps through a second ring.
+// Activation traffic per output drops ~5x; the filter-tap loop issues 36 tcgen05.mma per patch.
+// Same warp roles, TMEM double buffering and BatchNorm-statistics epilogue as conv.cu.  The data gradient
+// of these layers is the same kernel on dy with the flipped/transposed filter.
+#include <type_traits>
+#include "tc.cuh"
+#include "../../include/pdt_b200.h"
+
+namespace {
+
+using namespace pdt;
+using namespace pdt::tc;
+
+constexpr int kThreads = 256;
+constexpr int kStatMaxK = 128;
+
+struct HaloGeom {
+  int N, H, W, C, K;
+  int Wp;                 // W + 2
+  int TR;                 // image rows per tile
+  int tiles_per_image;
+  int num_tiles;
+  int c_chunks;
+  uint32_t patch_bytes;   // (TR + 2) * Wp * 128
+};
+
+struct BnStats {
+  int enabled;
+  float* partial;
+  unsigned* counter;
+  float* running_mean;
+  float* running_var;
+  float* save_mean;
+  float* save_invstd;
+  float momentum, eps;
+  long long count;        // N*H*W
+};
+
+template <int BN, bool RES> struct HCfg {
+  static constexpr int kAStage = 32768;                       // 1 KB front slack + patch + tail slack (Wp <= 58)
+  static constexpr int kAStages = 3;
+  static constexpr int kBTile = BN * 128;
+  static constexpr int kBStages = RES ? 9 : 6;                // resident: all nine taps of the single 64-channel block
+  static constexpr int kTmemCols = 2 * BN;
+  static constexpr int kStatBytes = 4 * 2 * kStatMaxK * 4;
+  static constexpr int kSmemBytes = kAStages * kAStage + kBStages * kBTile + 1024 + 256 + kStatBytes;
+};
+
+__device__ __forceinline__ void tma_load_4d(void* smem, const CUtensorMap* m, uint64_t* bar, int c, int w, int h, int n) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(smem_u32(smem)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c), "r"(w), "r"(h), "r"(n) : "memory");
+}
+
+__device__ __forceinline__ void warp_transpose_reduce(float (&a)[32], int lane) {
+#pragma unroll
+  for (int s = 16; s >= 1; s >>= 1) {
+    const bool up = (lane & s) != 0;
+#pragma unroll
+    for (int i = 0; i < s; ++i) {
+      const float keep = up ? a[i + s] : a[i];
+      const float send = up ? a[i] : a[i + s];
+      a[i] = keep + __shfl_xor_sync(0xffffffffu, send, s);
+    }
+  }
+}
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+
+template <int BN, bool RES, typename T>
+__global__ void __launch_bounds__(kThreads, 1)
+k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW, T* __restrict__ out,
+               const HaloGeom g, const BnStats bs) {
+  using C = HCfg<BN, RES>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smA = smem;
+  uint8_t* smB = smem + C::kAStages * C::kAStage;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smB + C::kBStages * C::kBTile);
+  uint64_t* afull = bars;                        // [kAStages]
+  uint64_t* aempty = afull + C::kAStages;
+  uint64_t* bfull = aempty + C::kAStages;        // [kBStages] (RES: only bfull[0] is used, once)
+  uint64_t* bempty = bfull + C::kBStages;
+  uint64_t* tfull = bempty + C::kBStages;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  float* s_stat = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) { prefetch_tmap(&tmX); prefetch_tmap(&tmW); }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < C::kAStages; ++i) { mbar_init(&afull[i], 1); mbar_init(&aempty[i], 1); }
+    for (int i = 0; i < C::kBStages; ++i) { mbar_init(&bfull[i], 1); mbar_init(&bempty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 4); }
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, C::kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ================= TMA producer =================
+    if (lane == 0) {
+      if (RES) {     // the whole 3x3x64xBN filter bank, once
+        mbar_expect_tx(&bfull[0], 9 * C::kBTile);
+        for (int tap = 0; tap < 9; ++tap) tma_load_2d(smB + tap * C::kBTile, &tmW, &bfull[0], tap * g.C, 0);
+      }
+      int as = 0, bsg = 0;
+      uint32_t aph = 0, bph = 0;
+      for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x) {
+        const int n = tile / g.tiles_per_image;
+        const int h0 = (tile - n * g.tiles_per_image) * g.TR;
+        for (int cc = 0; cc < g.c_chunks; ++cc) {
+          mbar_wait(&aempty[as], aph ^ 1);
+          mbar_expect_tx(&afull[as], g.patch_bytes);
+          tma_load_4d(smA + as * C::kAStage + 1024, &tmX, &afull[as], cc * 64, -1, h0 - 1, n);
+          if (++as == C::kAStages) { as = 0; aph ^= 1; }
+          if (!RES) {
+            for (int tap = 0; tap < 9; ++tap) {
+              mbar_wait(&bempty[bsg], bph ^ 1);
+              mbar_expect_tx(&bfull[bsg], C::kBTile);
+              tma_load_2d(smB + bsg * C::kBTile, &tmW, &bfull[bsg], tap * g.C + cc * 64, 0);
+              if (++bsg == C::kBStages) { bsg = 0; bph ^= 1; }
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer =================
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(128, BN, std::is_same<T, __nv_bfloat16>::value ? 1 : 0, 0, 0);
+      if (RES) { mbar_wait(&bfull[0], 0); tc_fence_after(); }
+      int as = 0, bsg = 0, it = 0;
+      uint32_t aph = 0, bph = 0;
+      for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x, ++it) {
+        const int acc = it & 1;
+        const uint32_t acc_phase = (it >> 1) & 1;
+        mbar_wait(&tempty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + acc * BN;
+        for (int cc = 0; cc < g.c_chunks; ++cc) {
+          mbar_wait(&afull[as], aph);
+          tc_fence_after();
+          const uint32_t patch = smem_u32(smA + as * C::kAStage + 1024);
+#pragma unroll 1
+          for (int tap = 0; tap < 9; ++tap) {
+            const int r = tap / 3, s = tap - r * 3;
+            int bidx;
+            if (RES) bidx = tap;
+            else {
+              mbar_wait(&bfull[bsg], bph);
+              tc_fence_after();
+              bidx = bsg;
+            }
+            // the tap's operand = the patch shifted by whole 128-byte pixel rows
+            const uint64_t da = make_sw128_desc(patch + (uint32_t)((r * g.Wp + s - 1) * 128), 1024, 16);
+            const uint64_t db = make_sw128_desc(smem_u32(smB + bidx * C::kBTile), 1024, 16);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) umma_f16(tmem_d, da + 2 * k, db + 2 * k, idesc, (cc | tap | k) != 0);
+            if (!RES) {
+              umma_commit(&bempty[bsg]);
+              if (++bsg == C::kBStages) { bsg = 0; bph ^= 1; }
+            }
+          }
+          umma_commit(&aempty[as]);
+          if (++as == C::kAStages) { as = 0; aph ^= 1; }
+        }
+        umma_commit(&tfull[acc]);
+      }
+    }
+  } else if (warp >= 4) {
+    // ================= epilogue =================
+    const int quarter = warp & 3;
+    float* my_stat = s_stat + quarter * 2 * kStatMaxK;
+    if (bs.enabled) {
+      for (int i = lane; i < 2 * kStatMaxK; i += 32) my_stat[i] = 0.f;
+      __syncwarp();
+    }
+    const int m = quarter * 32 + lane;            // output slot inside the tile (padded coordinates)
+    const int ti = m / g.Wp, tj = m - ti * g.Wp;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x, ++it) {
+      const int n = tile / g.tiles_per_image;
+      const int h0 = (tile - n * g.tiles_per_image) * g.TR;
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1;
+      mbar_wait(&tfull[acc], acc_phase);
+      tc_fence_after();
+      const bool valid = ti < g.TR && tj >= 1 && tj <= g.W && (h0 + ti) < g.H;
+      T* orow = out + (((size_t)n * g.H + h0 + ti) * g.W + (tj - 1)) * g.K;
+      const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(quarter * 32) << 16);
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld32(taddr + c0, v);
+        tmem_ld_wait();
+        if (bs.enabled) {
+          float a[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) a[j] = valid ? __uint_as_float(v[j]) : 0.f;    // junk slots excluded
+          warp_transpose_reduce(a, lane);
+          const float colsum = a[0];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) { const float t = valid ? __uint_as_float(v[j]) : 0.f; a[j] = t * t; }
+          warp_transpose_reduce(a, lane);
+          my_stat[c0 + lane] += colsum;
+          my_stat[kStatMaxK + c0 + lane] += a[0];
+        }
+        if (valid) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            uint4 o;
+            o.x = Cvt<T>::pack2(__uint_as_float(v[j + 0]), __uint_as_float(v[j + 1]));
+            o.y = Cvt<T>::pack2(__uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
+            o.z = Cvt<T>::pack2(__uint_as_float(v[j + 4]), __uint_as_float(v[j + 5]));
+            o.w = Cvt<T>::pack2(__uint_as_float(v[j + 6]), __uint_as_float(v[j + 7]));
+            *reinterpret_cast<uint4*>(orow + c0 + j) = o;
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[acc]);
+    }
+    if (bs.enabled) {
+      __shared__ int s_last;
+      const int te = threadIdx.x - 128;
+      const int K = g.K;
+      epi_bar_sync();
+      for (int i = te; i < 2 * K; i += 128) {
+        const int which = i / K, c = i - which * K;
+        float t = 0.f;
+#pragma unroll
+        for (int q4 = 0; q4 < 4; ++q4) t += s_stat[(q4 * 2 + which) * kStatMaxK + c];
+        bs.partial[(size_t)blockIdx.x * 2 * K + i] = t;
+      }
+      __threadfence();
+      epi_bar_sync();
+      if (te == 0) s_last = (atomicAdd(bs.counter, 1u) == gridDim.x - 1);
+      epi_bar_sync();
+      if (s_last) {
+        __threadfence();
+        double* tot = reinterpret_cast<double*>(s_stat);
+        epi_bar_sync();
+        for (int i = te; i < 2 * K; i += 128) {
+          double t = 0.0;
+#pragma unroll 4
+          for (int b = 0; b < (int)gridDim.x; ++b) t += (double)__ldcg(bs.partial + (size_t)b * 2 * K + i);
+          tot[i] = t;
+        }
+        epi_bar_sync();
+        const double cnt = (double)bs.count;
+        for (int c = te; c < K; c += 128) {
+          const double mean = tot[c] / cnt;
+          double var = tot[K + c] / cnt - mean * mean;
+          var = var > 0.0 ? var : 0.0;
+          bs.save_mean[c] = (float)mean;
+          bs.save_invstd[c] = (float)(1.0 / sqrt(var + (double)bs.eps));
+          if (bs.running_mean != nullptr) {
+            const double unbiased = cnt > 1.0 ? var * cnt / (cnt - 1.0) : var;
+            bs.running_mean[c] = (float)((1.0 - bs.momentum) * bs.running_mean[c] + bs.momentum * mean);
+            bs.running_var[c] = (float)((1.0 - bs.momentum) * bs.running_var[c] + bs.momentum * unbiased);
+          }
+        }
+        if (te == 0) *bs.counter = 0;
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, C::kTmemCols);
+  }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn g_enc = nullptr;
+
+template <int BN, bool RES>
+int launch(const void* x, const void* w, void* y, int dtype, const HaloGeom& g, const BnStats& bs, const CUtensorMap& tmX,
+           const CUtensorMap& tmW, cudaStream_t stream) {
+  using C = HCfg<BN, RES>;
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int grid = g.num_tiles < sms ? g.num_tiles : sms;
+  if (dtype == PDT_FP16) {
+    auto kern = k_conv3x3_halo<BN, RES, __half>;
+    PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+    kern<<<grid, kThreads, C::kSmemBytes, stream>>>(tmX, tmW, reinterpret_cast<__half*>(y), g, bs);
+  } else {
+    auto kern = k_conv3x3_halo<BN, RES, __nv_bfloat16>;
+    PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+    kern<<<grid, kThreads, C::kSmemBytes, stream>>>(tmX, tmW, reinterpret_cast<__nv_bfloat16*>(y), g, bs);
+  }
+  return (int)cudaGetLastError();
+}
+
+}  // namespace
+
+extern "C" {
+
+// 1 if pdt_conv3x3_halo serves this shape (3x3, stride 1, pad 1 implied).
+int pdt_conv3x3_halo_supported(int dtype, int N, int H, int W, int C, int K) {
+  if (dtype != PDT_BF16 && dtype != PDT_FP16) return 0;
+  if (C % 64 || (K != 64 && K != 128) || W + 2 > 58 || W < 6 || H < 1 || N < 1) return 0;
+  return 1;
+}
+
+// x: [N][H][W][C], w: [K][3][3][C], y: [N][H][W][K] (bf16/fp16).  scratch/stat pointers as in
+// pdt_conv_fprop_bnstats; pass scratch == NULL for a plain convolution.
+int pdt_conv3x3_halo(const void* x, const void* w, void* y, int dtype, int N, int H, int W, int C, int K, void* scratch,
+                     float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
+                     float* save_invstd, cudaStream_t stream) {
+  if (!pdt_conv3x3_halo_supported(dtype, N, H, W, C, K)) return PDT_E_UNSUPPORTED;
+  if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(w) | reinterpret_cast<uintptr_t>(y)) & 15) return PDT_E_UNSUPPORTED;
+  if (g_enc == nullptr) {
+    cudaDriverEntryPointQueryResult q;
+    void* fn = nullptr;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q);
+    if (e != cudaSuccess || fn == nullptr) return (int)(e != cudaSuccess ? e : cudaErrorUnknown);
+    g_enc = reinterpret_cast<EncodeTiledFn>(fn);
+  }
+  HaloGeom g;
+  g.N = N; g.H = H; g.W = W; g.C = C; g.K = K;
+  g.Wp = W + 2;
+  g.TR = 128 / g.Wp;
+  if (g.TR > H) g.TR = H;
+  g.tiles_per_image = (H + g.TR - 1) / g.TR;
+  g.num_tiles = N * g.tiles_per_image;
+  g.c_chunks = C / 64;
+  g.patch_bytes = (uint32_t)((g.TR + 2) * g.Wp * 128);
+  if (1024 + (128 + 2 * g.Wp + 2) * 128 > 32768 || g.patch_bytes + 1024 > 32768) return PDT_E_UNSUPPORTED;
+  const bool resident = (C == 64 && K == 64);
+  const CUtensorMapDataType dt = dtype == PDT_FP16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  CUtensorMap tmX, tmW;
+  {
+    cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+    cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+    cuuint32_t box[4] = {64, (cuuint32_t)g.Wp, (cuuint32_t)(g.TR + 2), 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    if (g_enc(&tmX, dt, 4, const_cast<void*>(x), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return 10003;
+  }
+  {
+    cuuint64_t dims[2] = {(cuuint64_t)9 * C, (cuuint64_t)K};
+    cuuint64_t strides[1] = {(cuuint64_t)9 * C * 2};
+    cuuint32_t box[2] = {64, (cuuint32_t)K};
+    cuuint32_t estr[2] = {1, 1};
+    if (g_enc(&tmW, dt, 2, const_cast<void*>(w), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return 10004;
+  }
+  BnStats bs;
+  bs.enabled = scratch != nullptr;
+  bs.counter = reinterpret_cast<unsigned*>(scratch);
+  bs.partial = scratch ? reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + 256) : nullptr;
+  bs.running_mean = running_mean; bs.running_var = running_var;
+  bs.save_mean = save_mean; bs.save_invstd = save_invstd;
+  bs.momentum = momentum; bs.eps = eps;
+  bs.count = (long long)N * H * W;
+  if (K == 64) {
+    if (resident) return launch<64, true>(x, w, y, dtype, g, bs, tmX, tmW, stream);
+    return launch<64, false>(x, w, y, dtype, g, bs, tmX, tmW, stream);
+  }
+  return launch<128, false>(x, w, y, dtype, g, bs, tmX, tmW, stream);
+}
+
+}  // extern "C"

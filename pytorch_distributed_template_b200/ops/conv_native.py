@@ -29,7 +29,29 @@ _native.register("pdt_stem_s2d", [_vp, _vp, _i, _i, _i, _i, _i, _vp])
 _native.register("pdt_conv_fprop_bnstats", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp,
                                             _native._f, _native._f, _vp, _vp, _vp])
 
+_native.register("pdt_conv3x3_halo_supported", [_i, _i, _i, _i, _i, _i])
+_native.register("pdt_conv3x3_halo", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _native._f, _native._f, _vp, _vp, _vp])
+
 CL = torch.channels_last
+
+
+def _halo_ok(x, w_lp, stride, pad):
+    """Large-map 3x3/1/1 layers go to the patch-reuse kernel (csrc/conv_halo.cu); PDT_HALO=0 disables it."""
+    K, C, R, S = w_lp.shape
+    if R != 3 or S != 3 or stride != 1 or pad != 1 or x.dtype == torch.float32 or os.environ.get("PDT_HALO", "1") != "1":
+        return False
+    N, _, H, W = x.shape
+    return bool(_native.lib().pdt_conv3x3_halo_supported(_native.dtype_code(x.dtype), N, H, W, C, K))
+
+
+def _halo(x, w_lp, y, scratch=None, rm=None, rv=None, momentum=0.1, eps=1e-5, mean=None, invstd=None):
+    N, C, H, W = x.shape
+    K = w_lp.shape[0]
+    _native.check(_native.lib().pdt_conv3x3_halo(
+        x.data_ptr(), w_lp.data_ptr(), y.data_ptr(), _native.dtype_code(x.dtype), N, H, W, C, K, _native.ptr(scratch),
+        _native.ptr(rm), _native.ptr(rv), momentum, eps, _native.ptr(mean), _native.ptr(invstd),
+        _native.stream_ptr(x.device)), "pdt_conv3x3_halo")
+    return y
 
 
 def enabled():
@@ -59,6 +81,8 @@ def fprop(x, w_lp, stride, pad):
     K, _, R, S = w_lp.shape
     P, Q = (H + 2 * pad - R) // stride + 1, (W + 2 * pad - S) // stride + 1
     y = torch.empty((N, K, P, Q), dtype=x.dtype, device=x.device, memory_format=CL)
+    if _halo_ok(x, w_lp, stride, pad):
+        return _halo(x, w_lp, y)
     _native.check(_native.lib().pdt_conv_fprop(x.data_ptr(), w_lp.data_ptr(), y.data_ptr(), _native.dtype_code(x.dtype),
                                                N, H, W, C, K, R, S, stride, pad, _native.stream_ptr(x.device)),
                   "pdt_conv_fprop")
@@ -74,6 +98,9 @@ def fprop_bnstats(x, w_lp, stride, pad, running_mean, running_var, momentum, eps
     y = torch.empty((N, K, P, Q), dtype=x.dtype, device=x.device, memory_format=CL)
     mean = torch.empty(K, dtype=torch.float32, device=x.device)
     invstd = torch.empty_like(mean)
+    if _halo_ok(x, w_lp, stride, pad):
+        _halo(x, w_lp, y, _bn_scratch(x.device, K), running_mean, running_var, momentum, eps, mean, invstd)
+        return y, mean, invstd
     _native.check(_native.lib().pdt_conv_fprop_bnstats(
         x.data_ptr(), w_lp.data_ptr(), y.data_ptr(), _native.dtype_code(x.dtype), N, H, W, C, K, R, S, stride, pad,
         _bn_scratch(x.device, K).data_ptr(), _native.ptr(running_mean), _native.ptr(running_var), momentum, eps,

@@ -190,3 +190,27 @@ def test_tf32_model_paths(native_lib):
     g2 = torch.cat([p.grad.reshape(-1) for p in tv.parameters()])
     assert torch.isfinite(g1).all()
     assert torch.nn.functional.cosine_similarity(g1, g2, dim=0).item() > 0.98
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("cin,cout,hw,batch", [(64, 64, 56, 5), (128, 128, 28, 7), (64, 64, 56, 1), (128, 128, 28, 1),
+                                               (64, 128, 28, 3), (128, 64, 56, 2), (64, 64, 20, 3)])
+def test_conv3x3_halo_kernel(native_lib, dtype, cin, cout, hw, batch):
+    """Patch-reuse kernel (row-shifted smem descriptors) vs F.conv2d, with and without fused BN statistics."""
+    from pytorch_distributed_template_b200.ops import conv_native
+    torch.backends.cudnn.allow_tf32 = False
+    torch.manual_seed(20)
+    dev = torch.device("cuda", 0)
+    x = torch.randn(batch, cin, hw, hw, device=dev).to(dtype).contiguous(memory_format=torch.channels_last)
+    w = (torch.randn(cout, cin, 3, 3, device=dev) / (cin * 9) ** 0.5).to(dtype).contiguous(memory_format=torch.channels_last)
+    assert conv_native._halo_ok(x, w, 1, 1)
+    y = conv_native.fprop(x, w, 1, 1)
+    ref = F.conv2d(x.float(), w.float(), None, 1, 1)
+    tol = 2e-2 if dtype == torch.bfloat16 else 3e-3
+    assert (y.float() - ref).abs().max().item() <= tol * max(1.0, ref.abs().max().item())
+    rm, rv = torch.zeros(cout, device=dev), torch.ones(cout, device=dev)
+    y2, mean, invstd = conv_native.fprop_bnstats(x, w, 1, 1, rm, rv, 0.1, 1e-5)
+    assert torch.equal(y2, y)
+    assert torch.allclose(mean, ref.mean((0, 2, 3)), rtol=1e-2, atol=2e-3)
+    assert torch.allclose(invstd, torch.rsqrt(ref.var((0, 2, 3), unbiased=False) + 1e-5), rtol=1e-2, atol=1e-3)
+    assert torch.allclose(rm, 0.1 * ref.mean((0, 2, 3)), rtol=1e-2, atol=2e-3)
