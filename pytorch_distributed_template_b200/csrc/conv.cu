@@ -80,7 +80,8 @@ template <int BN> struct Cfg {
   static constexpr int kStageBytes = kStageBytesA + kStageBytesB;
   static constexpr int kStages = (BN >= 256) ? 4 : (BN >= 128 ? 6 : 8);
   static constexpr int kTmemCols = 2 * BN;     // double-buffered accumulator (power of two >= 32 for BN in {64,128,256})
-  static constexpr int kStatBytes = 4 * 2 * kStatMaxK * 4;   // [4 epilogue warps][sum, sumsq][K] floats
+  // per epilogue warp: [sum, sumsq][K] accumulators + a 32 x 33 float transpose tile
+  static constexpr int kStatBytes = 4 * (2 * kStatMaxK + 32 * 33) * 4;
   static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*alignment slack*/ + 256 /*barriers*/ + kStatBytes;
 };
 
@@ -139,8 +140,8 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    // ================= TMA producer =================
-    if (lane == 0) {
+    // ================= TMA producer (whole warp converged, one elected lane issues) =================
+    {
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -154,16 +155,19 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
           for (int s = 0; s < g.S; ++s)
             for (int cc = 0; cc < c_chunks; ++cc) {
               mbar_wait(&empty[stage], phase ^ 1);
-              mbar_expect_tx(&full[stage], C::kStageBytes);
-              tma_load_im2col_4d(smA + stage * C::kStageBytesA, &tmA, &full[stage], cc * BK, cw, ch, img, (uint16_t)(s * g.dil_w), (uint16_t)r);
-              tma_load_2d(smB + stage * C::kStageBytesB, &tmB, &full[stage], (r * g.S + s) * g.C + cc * BK, nt * BN);
+              if (elect_one_sync()) {
+                mbar_expect_tx(&full[stage], C::kStageBytes);
+                tma_load_im2col_4d(smA + stage * C::kStageBytesA, &tmA, &full[stage], cc * BK, cw, ch, img, (uint16_t)(s * g.dil_w), (uint16_t)r);
+                tma_load_2d(smB + stage * C::kStageBytesB, &tmB, &full[stage], (r * g.S + s) * g.C + cc * BK, nt * BN);
+              }
+              __syncwarp();
               if (++stage == C::kStages) { stage = 0; phase ^= 1; }
             }
       }
     }
   } else if (warp == 1) {
-    // ================= MMA issuer =================
-    if (lane == 0) {
+    // ================= MMA issuer (whole warp converged, one elected lane issues) =================
+    {
       constexpr uint32_t idesc = make_idesc(BM, BN, Elem<T>::kFmt, 0, 0);
       int stage = 0;
       uint32_t phase = 0;
@@ -179,19 +183,24 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
           tc_fence_after();
           const uint64_t da = make_sw128_desc(smem_u32(smA + stage * C::kStageBytesA), 1024, 16);
           const uint64_t db = make_sw128_desc(smem_u32(smB + stage * C::kStageBytesB), 1024, 16);
+          if (elect_one_sync()) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k)   // +32 bytes along K per UMMA_K step: +2 in the (addr >> 4) field
-            umma<T>(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
-          umma_commit(&empty[stage]);
+            for (int k = 0; k < 4; ++k)   // +32 bytes along K per UMMA_K step: +2 in the (addr >> 4) field
+              umma<T>(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+            umma_commit(&empty[stage]);
+          }
+          __syncwarp();
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&tfull[acc]);
+        if (elect_one_sync()) umma_commit(&tfull[acc]);
+        __syncwarp();
       }
     }
   } else if (warp >= 4) {
     // ================= epilogue: TMEM -> registers -> global =================
     const int quarter = warp & 3;                 // TMEM lanes [32*quarter, +32) are the ones this warp may read
-    float* my_stat = s_stat + quarter * 2 * kStatMaxK;
+    float* my_stat = s_stat + quarter * (2 * kStatMaxK + 32 * 33);
+    float* tp = my_stat + 2 * kStatMaxK;          // 32 x 33 transpose tile
     if (bs.enabled) {
       for (int i = lane; i < 2 * kStatMaxK; i += 32) my_stat[i] = 0.f;
       __syncwarp();
@@ -220,19 +229,19 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         tmem_ld32(taddr + c0, v);
         tmem_ld_wait();
         if (bs.enabled) {
-          // rows past M come from zero-filled (out-of-bounds) pixels: their accumulators are exactly 0
-          float a[32];
+          // rows past M come from zero-filled (out-of-bounds) pixels: their accumulators are exactly 0.
+          // Column sums over the warp's 32 rows via a padded shared-memory transpose (conflict-free both ways).
 #pragma unroll
-          for (int j = 0; j < 32; ++j) a[j] = __uint_as_float(v[j]);
-          warp_transpose_reduce(a, lane);
-          const float colsum = a[0];
+          for (int j = 0; j < 32; ++j) tp[lane * 33 + j] = __uint_as_float(v[j]);
+          __syncwarp();
+          float cs = 0.f, cq = 0.f;
 #pragma unroll
-          for (int j = 0; j < 32; ++j) { const float t = __uint_as_float(v[j]); a[j] = t * t; }
-          warp_transpose_reduce(a, lane);
+          for (int rr = 0; rr < 32; ++rr) { const float t = tp[rr * 33 + lane]; cs += t; cq = fmaf(t, t, cq); }
+          __syncwarp();
           const int col = nt * BN + c0 + lane;
           if (col < g.K) {
-            my_stat[col] += colsum;
-            my_stat[kStatMaxK + col] += a[0];
+            my_stat[col] += cs;
+            my_stat[kStatMaxK + col] += cq;
           }
         }
         if (row < g.M) {
@@ -277,7 +286,7 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         const int which = i / K, c = i - which * K;
         float t = 0.f;
 #pragma unroll
-        for (int q4 = 0; q4 < 4; ++q4) t += s_stat[(q4 * 2 + which) * kStatMaxK + c];
+        for (int q4 = 0; q4 < 4; ++q4) t += s_stat[q4 * (2 * kStatMaxK + 32 * 33) + which * kStatMaxK + c];
         bs.partial[(size_t)blockIdx.x * 2 * K + i] = t;
       }
       __threadfence();
@@ -390,7 +399,7 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
+    {
       int stage = 0;
       uint32_t phase = 0;
       for (int item = blockIdx.x; item < items; item += gridDim.x) {
@@ -416,18 +425,23 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
           const int p0 = rem / g.Q, q0 = rem - p0 * g.Q;
           const int cw = q0 * g.stride - g.pad_w, ch = p0 * g.stride - g.pad_h;
           mbar_wait(&empty[stage], phase ^ 1);
-          mbar_expect_tx(&full[stage], (uint32_t)(nA + nB) * kBlkBytes);
-          for (int b = 0; b < nA; ++b)
-            tma_load_im2col_4d(smA + stage * C::kStageBytesA + b * kBlkBytes, &tmX, &full[stage], cc[b] * kRow, cw, ch, img,
-                               (uint16_t)(taps[b] * g.dil_w), (uint16_t)tapr[b]);
-          for (int j = 0; j < nB; ++j)
-            tma_load_2d(smB + stage * C::kStageBytesB + j * kBlkBytes, &tmDY, &full[stage], nt * BN + j * kRow, m0);
+          if (elect_one_sync()) {
+            mbar_expect_tx(&full[stage], (uint32_t)(nA + nB) * kBlkBytes);
+#pragma unroll
+            for (int b = 0; b < kAB; ++b)
+              if (b < nA)
+                tma_load_im2col_4d(smA + stage * C::kStageBytesA + b * kBlkBytes, &tmX, &full[stage], cc[b] * kRow, cw, ch, img,
+                                   (uint16_t)(taps[b] * g.dil_w), (uint16_t)tapr[b]);
+            for (int j = 0; j < nB; ++j)
+              tma_load_2d(smB + stage * C::kStageBytesB + j * kBlkBytes, &tmDY, &full[stage], nt * BN + j * kRow, m0);
+          }
+          __syncwarp();
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    {
       constexpr uint32_t idesc = make_idesc(128, BN, Elem<T>::kFmt, 1, 1);
       int stage = 0;
       uint32_t phase = 0;
@@ -449,13 +463,17 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
           constexpr uint32_t kSbo = sizeof(T) == 4 ? 512 : 1024, kLayout = sizeof(T) == 4 ? 1 : 2;
           const uint64_t da = make_sw128_desc(smem_u32(smA + stage * C::kStageBytesA), kSbo, kBlkBytes, kLayout);
           const uint64_t db = make_sw128_desc(smem_u32(smB + stage * C::kStageBytesB), kSbo, kBlkBytes, kLayout);
+          if (elect_one_sync()) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k)   // UMMA_K pixels = kUK * 128 bytes per step, in (addr >> 4) units
-            umma<T>(tmem_d, da + (Elem<T>::kUK * 8) * k, db + (Elem<T>::kUK * 8) * k, idesc, (ks > ks0 || k > 0) ? 1u : 0u);
-          umma_commit(&empty[stage]);
+            for (int k = 0; k < 4; ++k)   // UMMA_K pixels = kUK * 128 bytes per step, in (addr >> 4) units
+              umma<T>(tmem_d, da + (Elem<T>::kUK * 8) * k, db + (Elem<T>::kUK * 8) * k, idesc, (ks > ks0 || k > 0) ? 1u : 0u);
+            umma_commit(&empty[stage]);
+          }
+          __syncwarp();
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&tfull[acc]);
+        if (elect_one_sync()) umma_commit(&tfull[acc]);
+        __syncwarp();
       }
     }
   } else if (warp >= 4) {

@@ -22,7 +22,8 @@ namespace {
 using namespace pdt;
 using namespace pdt::tc;
 
-constexpr int kThreads = 256;
+constexpr int kThreads = 384;       // warps: 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4..11 epilogue
+constexpr int kEpiWarps = 8;        // two warps per TMEM lane quarter, each draining half of the columns
 constexpr int kStatMaxK = 128;
 
 struct HaloGeom {
@@ -51,9 +52,10 @@ template <int BN, bool RES> struct HCfg {
   static constexpr int kAStage = 32768;                       // 1 KB front slack + patch + tail slack (Wp <= 58)
   static constexpr int kAStages = 3;
   static constexpr int kBTile = BN * 128;
-  static constexpr int kBStages = RES ? 9 : 6;                // resident: all nine taps of the single 64-channel block
+  static constexpr int kBStages = RES ? 9 : 4;                // resident: all nine taps of the single 64-channel block
   static constexpr int kTmemCols = 2 * BN;
-  static constexpr int kStatBytes = 4 * 2 * kStatMaxK * 4;
+  // per epilogue warp: column accumulators [2][kStatMaxK] + a 32 x 33 float transpose tile
+  static constexpr int kStatBytes = kEpiWarps * (2 * kStatMaxK + 32 * 33) * 4;
   static constexpr int kSmemBytes = kAStages * kAStage + kBStages * kBTile + 1024 + 256 + kStatBytes;
 };
 
@@ -75,7 +77,7 @@ __device__ __forceinline__ void warp_transpose_reduce(float (&a)[32], int lane) 
     }
   }
 }
-__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
 template <int BN, bool RES, typename T>
 __global__ void __launch_bounds__(kThreads, 1)
@@ -102,7 +104,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < C::kAStages; ++i) { mbar_init(&afull[i], 1); mbar_init(&aempty[i], 1); }
     for (int i = 0; i < C::kBStages; ++i) { mbar_init(&bfull[i], 1); mbar_init(&bempty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 4); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], kEpiWarps); }
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc(tmem_slot, C::kTmemCols);
@@ -112,11 +114,14 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    // ================= TMA producer =================
-    if (lane == 0) {
+    // ================= TMA producer (whole warp converged, one elected lane issues) =================
+    {
       if (RES) {     // the whole 3x3x64xBN filter bank, once
-        mbar_expect_tx(&bfull[0], 9 * C::kBTile);
-        for (int tap = 0; tap < 9; ++tap) tma_load_2d(smB + tap * C::kBTile, &tmW, &bfull[0], tap * g.C, 0);
+        if (elect_one_sync()) {
+          mbar_expect_tx(&bfull[0], 9 * C::kBTile);
+          for (int tap = 0; tap < 9; ++tap) tma_load_2d(smB + tap * C::kBTile, &tmW, &bfull[0], tap * g.C, 0);
+        }
+        __syncwarp();
       }
       int as = 0, bsg = 0;
       uint32_t aph = 0, bph = 0;
@@ -125,14 +130,20 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         const int h0 = (tile - n * g.tiles_per_image) * g.TR;
         for (int cc = 0; cc < g.c_chunks; ++cc) {
           mbar_wait(&aempty[as], aph ^ 1);
-          mbar_expect_tx(&afull[as], g.patch_bytes);
-          tma_load_4d(smA + as * C::kAStage + 1024, &tmX, &afull[as], cc * 64, -1, h0 - 1, n);
+          if (elect_one_sync()) {
+            mbar_expect_tx(&afull[as], g.patch_bytes);
+            tma_load_4d(smA + as * C::kAStage + 1024, &tmX, &afull[as], cc * 64, -1, h0 - 1, n);
+          }
+          __syncwarp();
           if (++as == C::kAStages) { as = 0; aph ^= 1; }
           if (!RES) {
             for (int tap = 0; tap < 9; ++tap) {
               mbar_wait(&bempty[bsg], bph ^ 1);
-              mbar_expect_tx(&bfull[bsg], C::kBTile);
-              tma_load_2d(smB + bsg * C::kBTile, &tmW, &bfull[bsg], tap * g.C + cc * 64, 0);
+              if (elect_one_sync()) {
+                mbar_expect_tx(&bfull[bsg], C::kBTile);
+                tma_load_2d(smB + bsg * C::kBTile, &tmW, &bfull[bsg], tap * g.C + cc * 64, 0);
+              }
+              __syncwarp();
               if (++bsg == C::kBStages) { bsg = 0; bph ^= 1; }
             }
           }
@@ -140,8 +151,8 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
       }
     }
   } else if (warp == 1) {
-    // ================= MMA issuer =================
-    if (lane == 0) {
+    // ================= MMA issuer (whole warp converged, one elected lane issues) =================
+    {
       constexpr uint32_t idesc = make_idesc(128, BN, std::is_same<T, __nv_bfloat16>::value ? 1 : 0, 0, 0);
       if (RES) { mbar_wait(&bfull[0], 0); tc_fence_after(); }
       int as = 0, bsg = 0, it = 0;
@@ -169,23 +180,31 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
             // the tap's operand = the patch shifted by whole 128-byte pixel rows
             const uint64_t da = make_sw128_desc(patch + (uint32_t)((r * g.Wp + s - 1) * 128), 1024, 16);
             const uint64_t db = make_sw128_desc(smem_u32(smB + bidx * C::kBTile), 1024, 16);
+            if (elect_one_sync()) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k) umma_f16(tmem_d, da + 2 * k, db + 2 * k, idesc, (cc | tap | k) != 0);
+              for (int k = 0; k < 4; ++k) umma_f16(tmem_d, da + 2 * k, db + 2 * k, idesc, (cc | tap | k) != 0);
+              if (!RES) umma_commit(&bempty[bsg]);
+            }
+            __syncwarp();
             if (!RES) {
-              umma_commit(&bempty[bsg]);
               if (++bsg == C::kBStages) { bsg = 0; bph ^= 1; }
             }
           }
-          umma_commit(&aempty[as]);
+          if (elect_one_sync()) umma_commit(&aempty[as]);
+          __syncwarp();
           if (++as == C::kAStages) { as = 0; aph ^= 1; }
         }
-        umma_commit(&tfull[acc]);
+        if (elect_one_sync()) umma_commit(&tfull[acc]);
+        __syncwarp();
       }
     }
   } else if (warp >= 4) {
     // ================= epilogue =================
-    const int quarter = warp & 3;
-    float* my_stat = s_stat + quarter * 2 * kStatMaxK;
+    const int quarter = warp & 3;                 // TMEM lane quarter this warp may read
+    const int half = (warp - 4) >> 2;             // which half of the BN columns it drains
+    const int ew = warp - 4;
+    float* my_stat = s_stat + ew * (2 * kStatMaxK + 32 * 33);
+    float* tp = my_stat + 2 * kStatMaxK;          // 32 x 33 transpose tile
     if (bs.enabled) {
       for (int i = lane; i < 2 * kStatMaxK; i += 32) my_stat[i] = 0.f;
       __syncwarp();
@@ -204,21 +223,22 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
       T* orow = out + (((size_t)n * g.H + h0 + ti) * g.W + (tj - 1)) * g.K;
       const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(quarter * 32) << 16);
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
+      for (int c0 = half * (BN / 2); c0 < (half + 1) * (BN / 2); c0 += 32) {
         uint32_t v[32];
         tmem_ld32(taddr + c0, v);
         tmem_ld_wait();
         if (bs.enabled) {
-          float a[32];
+          // column sums over this warp's 32 rows through a padded shared-memory transpose (conflict-free
+          // both ways): 32 STS + 32 LDS + 64 FMA per lane, cheaper than a shuffle butterfly
 #pragma unroll
-          for (int j = 0; j < 32; ++j) a[j] = valid ? __uint_as_float(v[j]) : 0.f;    // junk slots excluded
-          warp_transpose_reduce(a, lane);
-          const float colsum = a[0];
+          for (int j = 0; j < 32; ++j) tp[lane * 33 + j] = valid ? __uint_as_float(v[j]) : 0.f;   // junk slots excluded
+          __syncwarp();
+          float cs = 0.f, cq = 0.f;
 #pragma unroll
-          for (int j = 0; j < 32; ++j) { const float t = valid ? __uint_as_float(v[j]) : 0.f; a[j] = t * t; }
-          warp_transpose_reduce(a, lane);
-          my_stat[c0 + lane] += colsum;
-          my_stat[kStatMaxK + c0 + lane] += a[0];
+          for (int rr = 0; rr < 32; ++rr) { const float t = tp[rr * 33 + lane]; cs += t; cq = fmaf(t, t, cq); }
+          __syncwarp();
+          my_stat[c0 + lane] += cs;
+          my_stat[kStatMaxK + c0 + lane] += cq;
         }
         if (valid) {
 #pragma unroll
@@ -238,14 +258,14 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
     }
     if (bs.enabled) {
       __shared__ int s_last;
-      const int te = threadIdx.x - 128;
+      const int te = threadIdx.x - 128;            // 0..255 among the epilogue threads
       const int K = g.K;
       epi_bar_sync();
-      for (int i = te; i < 2 * K; i += 128) {
+      for (int i = te; i < 2 * K; i += 256) {
         const int which = i / K, c = i - which * K;
         float t = 0.f;
 #pragma unroll
-        for (int q4 = 0; q4 < 4; ++q4) t += s_stat[(q4 * 2 + which) * kStatMaxK + c];
+        for (int w8 = 0; w8 < kEpiWarps; ++w8) t += s_stat[w8 * (2 * kStatMaxK + 32 * 33) + which * kStatMaxK + c];
         bs.partial[(size_t)blockIdx.x * 2 * K + i] = t;
       }
       __threadfence();
@@ -256,7 +276,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         __threadfence();
         double* tot = reinterpret_cast<double*>(s_stat);
         epi_bar_sync();
-        for (int i = te; i < 2 * K; i += 128) {
+        for (int i = te; i < 2 * K; i += 256) {
           double t = 0.0;
 #pragma unroll 4
           for (int b = 0; b < (int)gridDim.x; ++b) t += (double)__ldcg(bs.partial + (size_t)b * 2 * K + i);
@@ -264,7 +284,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         }
         epi_bar_sync();
         const double cnt = (double)bs.count;
-        for (int c = te; c < K; c += 128) {
+        for (int c = te; c < K; c += 256) {
           const double mean = tot[c] / cnt;
           double var = tot[K + c] / cnt - mean * mean;
           var = var > 0.0 ? var : 0.0;

@@ -9,6 +9,20 @@ namespace tc {
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
+// One lane of a fully converged warp.  The role loops stay WARP-UNIFORM (all 32 lanes wait on the barriers and
+// compute the descriptors) and only the tcgen05 / TMA instruction itself is predicated on the elected lane:
+// a loop that runs under `if (lane == 0)` makes every operand thread-private, and ptxas then wraps each
+// UTCHMMA in an ELECT / R2UR / BRA.U.ANY uniformisation loop (~90 cycles of issue overhead per MMA, measured).
+__device__ __forceinline__ bool elect_one_sync() {
+  uint32_t pred = 0;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
+
 // ---- mbarrier ------------------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
