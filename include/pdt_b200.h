@@ -132,11 +132,15 @@ int pdt_bn_bwd_apply(const void* dy, const void* y, const void* x, void* dx, voi
 
 /* BatchNorm + ReLU + MaxPool fused (ResNet stem tail: batch_norm + relu_ + max_pool2d_with_indices and
  * their backward kernels).  The normalised tensor is never written: forward pools relu(bn(x)) straight
- * from the conv output x; backward gathers the pooled gradient through the saved arg-max taps and
- * recomputes the ReLU mask from x.  Statistics come from pdt_bn_fwd_stats on x. */
-int pdt_bn_pool_fwd(const void* x, void* y, int8_t* idx, int dtype, int N, int H, int W, int C, int ks, int st, int pd,
-                    const float* mean, const float* invstd, const float* gamma, const float* beta, cudaStream_t stream);
-int pdt_bn_pool_bwd_reduce(const void* dpool, const int8_t* idx, const void* x, int dtype, int N, int H, int W, int C,
+ * from the conv output x and also saves, per pooled element, the arg-max tap (`idx`) and the raw conv
+ * value at the arg-max (`xmax`).  Backward: the per-channel reductions are taken over the POOLED tensors
+ * (dpool masked by ypool > 0, times xmax - mean: every pooled gradient lands on exactly one input pixel),
+ * then the dx pass gathers the pooled gradient through `idx` and recomputes the ReLU mask from x.
+ * Statistics come from pdt_bn_fwd_stats on x. */
+int pdt_bn_pool_fwd(const void* x, void* y, int8_t* idx, void* xmax, int dtype, int N, int H, int W, int C, int ks, int st,
+                    int pd, const float* mean, const float* invstd, const float* gamma, const float* beta,
+                    cudaStream_t stream);
+int pdt_bn_pool_bwd_reduce(const void* dpool, const void* ypool, const void* xmax, int dtype, int N, int H, int W, int C,
                            int ks, int st, int pd, const float* mean, const float* invstd, const float* gamma,
                            const float* beta, void* scratch, const PdtCommDesc* comm, float* dgamma, float* dbeta,
                            float* out_k, cudaStream_t stream);

@@ -245,13 +245,15 @@ __global__ void __launch_bounds__(kThreads) k_bn_bwd_reduce(const T* __restrict_
                                                            const float* __restrict__ gamma, const float* __restrict__ beta,
                                                            int relu, float* __restrict__ partial, unsigned* counter, Comm comm,
                                                            float* __restrict__ dgamma, float* __restrict__ dbeta,
-                                                           float* __restrict__ out_k) {
+                                                           float* __restrict__ out_k, long count) {
   constexpr int V = Vec<T>::N;
   __shared__ __align__(16) float smem[kSmemFloats];
   __shared__ double s_count;
   const int tid = threadIdx.x, cg = C / V, rpi = kThreads / cg, cgi = tid % cg, r = tid / cg;
   const long chunk = (M + gridDim.x - 1) / gridDim.x;
   const long row0 = (long)blockIdx.x * chunk, row1 = min(M, row0 + chunk);
+  // `count` = elements per channel the BatchNorm normalised over on this rank; it differs from the M rows
+  // summed here when the caller feeds a compacted gradient (pdt_bn_pool_bwd_reduce).
   // y == nullptr with relu: no residual entered the ReLU, so its mask is recomputed from x with the
   // forward's own scale/shift instead of reading the output tensor (one pass of traffic less)
   const bool remask = relu && y == nullptr;
@@ -302,7 +304,7 @@ __global__ void __launch_bounds__(kThreads) k_bn_bwd_reduce(const T* __restrict_
 
   double* tot = reinterpret_cast<double*>(smem);
   fold_partials(tot, partial, gridDim.x, 2 * C);
-  if (tid == 0) { s_count = (double)M; *counter = 0; }
+  if (tid == 0) { s_count = (double)count; *counter = 0; }
   __syncthreads();
   for (int c = tid; c < C; c += blockDim.x) {   // parameter grads stay local: DDP averages them
     dbeta[c] = (float)tot[c];
@@ -418,7 +420,8 @@ __device__ __forceinline__ void gather_pool_grad(const T* __restrict__ dpool, co
 }
 
 template <typename T>
-__global__ void __launch_bounds__(256) k_bn_pool_fwd(const T* __restrict__ x, T* __restrict__ y, int8_t* __restrict__ idx, PoolGeom g,
+__global__ void __launch_bounds__(256) k_bn_pool_fwd(const T* __restrict__ x, T* __restrict__ y, int8_t* __restrict__ idx,
+                                                    T* __restrict__ xmax, PoolGeom g,
                                                     const float* __restrict__ mean, const float* __restrict__ invstd,
                                                     const float* __restrict__ gamma, const float* __restrict__ beta) {
   extern __shared__ float sm[];
@@ -438,10 +441,10 @@ __global__ void __launch_bounds__(256) k_bn_pool_fwd(const T* __restrict__ x, T*
     const int wo = (int)(r % g.Wo); r /= g.Wo;
     const int ho = (int)(r % g.Ho);
     const int n = (int)(r / g.Ho);
-    float best[8];
+    float best[8], bx[8];
     int bi[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) { best[j] = -INFINITY; bi[j] = 0; }
+    for (int j = 0; j < 8; ++j) { best[j] = -INFINITY; bi[j] = 0; bx[j] = 0.f; }
     for (int kh = 0; kh < g.ks; ++kh) {
       const int h = ho * g.st - g.pd + kh;
       if (h < 0 || h >= g.H) continue;
@@ -453,82 +456,17 @@ __global__ void __launch_bounds__(256) k_bn_pool_fwd(const T* __restrict__ x, T*
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           const float v = fmaxf(fmaf(f[j], scale[c0 + j], shift[c0 + j]), 0.f);
-          if (v > best[j]) { best[j] = v; bi[j] = kh * g.ks + kw; }
+          if (v > best[j]) { best[j] = v; bi[j] = kh * g.ks + kw; bx[j] = f[j]; }
         }
       }
     }
     const size_t o = (((size_t)n * g.Ho + ho) * g.Wo + wo) * g.C + c0;
     *reinterpret_cast<uint4*>(y + o) = pack8<T>(best);
+    *reinterpret_cast<uint4*>(xmax + o) = pack8<T>(bx);
     uint2 pk;
     pk.x = (bi[0] & 0xff) | ((bi[1] & 0xff) << 8) | ((bi[2] & 0xff) << 16) | ((bi[3] & 0xff) << 24);
     pk.y = (bi[4] & 0xff) | ((bi[5] & 0xff) << 8) | ((bi[6] & 0xff) << 16) | ((bi[7] & 0xff) << 24);
     *reinterpret_cast<uint2*>(idx + o) = pk;
-  }
-}
-
-template <typename T>
-__global__ void __launch_bounds__(kThreads) k_bn_pool_bwd_reduce(const T* __restrict__ dpool, const int8_t* __restrict__ idx,
-                                                                const T* __restrict__ x, PoolGeom g,
-                                                                const float* __restrict__ mean, const float* __restrict__ invstd,
-                                                                const float* __restrict__ gamma, const float* __restrict__ beta,
-                                                                float* __restrict__ partial, unsigned* counter, Comm comm,
-                                                                float* __restrict__ dgamma, float* __restrict__ dbeta,
-                                                                float* __restrict__ out_k) {
-  constexpr int V = 8;
-  __shared__ __align__(16) float smem[kSmemFloats];
-  __shared__ double s_count;
-  const int C = g.C;
-  const long M = (long)g.N * g.H * g.W;
-  const int tid = threadIdx.x, cg = C / V, rpi = kThreads / cg, cgi = tid % cg, r = tid / cg;
-  const long chunk = (M + gridDim.x - 1) / gridDim.x;
-  const long row0 = (long)blockIdx.x * chunk, row1 = min(M, row0 + chunk);
-  float s[V], q[V], mu[V], sc[V], sh[V];
-#pragma unroll
-  for (int j = 0; j < V; ++j) {
-    s[j] = q[j] = 0.f;
-    const int c = cgi * V + j;
-    mu[j] = (r < rpi) ? mean[c] : 0.f;
-    sc[j] = (r < rpi) ? gamma[c] * invstd[c] : 0.f;
-    sh[j] = (r < rpi) ? beta[c] - mean[c] * sc[j] : 0.f;
-  }
-  if (r < rpi) {
-    const int hw = g.H * g.W;
-    long row = row0 + r;
-    int n = (int)(row / hw);
-    int h = (int)(row - (long)n * hw) / g.W;
-    int w = (int)(row - (long)n * hw) - h * g.W;
-    for (; row < row1; row += rpi, w += rpi) {
-      while (w >= g.W) { w -= g.W; if (++h == g.H) { h = 0; ++n; } }     // no division in the loop
-      float gy[V], xv[V];
-      gather_pool_grad<T>(dpool, idx, g, n, h, w, cgi * V, gy);
-      load_vec<T>(x + row * C + cgi * V, xv);
-#pragma unroll
-      for (int j = 0; j < V; ++j) {
-        const float gg = fmaf(xv[j], sc[j], sh[j]) > 0.f ? gy[j] : 0.f;
-        s[j] += gg;
-        q[j] = fmaf(gg, xv[j] - mu[j], q[j]);
-      }
-    }
-  }
-  block_fold<V>(smem, s, q, C, cg, rpi, partial);
-  if (!take_last_ticket(counter)) return;
-
-  double* tot = reinterpret_cast<double*>(smem);
-  fold_partials(tot, partial, gridDim.x, 2 * C);
-  if (tid == 0) { s_count = (double)M; *counter = 0; }
-  __syncthreads();
-  for (int c = tid; c < C; c += blockDim.x) {
-    dbeta[c] = (float)tot[c];
-    dgamma[c] = (float)(tot[C + c] * (double)invstd[c]);
-  }
-  __syncthreads();
-  if (comm.world > 1) exchange_sum(comm, tot, 2 * C, &s_count);
-  __syncthreads();
-  const double Nn = s_count;
-  for (int c = tid; c < C; c += blockDim.x) {
-    const double is = (double)invstd[c];
-    out_k[c] = (float)(tot[c] / Nn);
-    out_k[C + c] = (float)(tot[C + c] * is * is / Nn);
   }
 }
 
@@ -572,6 +510,161 @@ __global__ void __launch_bounds__(256) k_bn_pool_bwd_apply(const T* __restrict__
   }
 }
 
+// ---- 3x3 / stride 2 / pad 1 specialisations (the torchvision stem; the generic kernels above keep every
+// other geometry working).  Both are bandwidth kernels whose generic form was latency bound: runtime loop
+// bounds kept ptxas from hoisting the loads, so each thread had ONE 16-byte load in flight (ncu: 1.8 TB/s).
+// Here every load of a work item is issued before the first is consumed.
+
+// One pooled output x 8 channels per thread: nine predicated loads in flight, then the scan.
+template <typename T>
+__global__ void __launch_bounds__(256) k_bn_pool_fwd_321(const T* __restrict__ x, T* __restrict__ y, int8_t* __restrict__ idx,
+                                                        T* __restrict__ xmax, PoolGeom g, const float* __restrict__ mean,
+                                                        const float* __restrict__ invstd, const float* __restrict__ gamma,
+                                                        const float* __restrict__ beta) {
+  extern __shared__ float sm[];
+  float* scale = sm;
+  float* shift = sm + g.C;
+  for (int c = threadIdx.x; c < g.C; c += blockDim.x) {
+    const float sc = gamma[c] * invstd[c];
+    scale[c] = sc;
+    shift[c] = beta[c] - mean[c] * sc;
+  }
+  __syncthreads();
+  const int cg = g.C / 8;
+  const unsigned total = (unsigned)g.N * g.Ho * g.Wo * cg;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int c0 = (int)(i % cg) * 8;
+    unsigned r = i / cg;
+    const int wo = (int)(r % g.Wo); r /= g.Wo;
+    const int ho = (int)(r % g.Ho);
+    const int n = (int)(r / g.Ho);
+    const int h0 = 2 * ho - 1, w0 = 2 * wo - 1;
+    uint4 u[9];
+    bool ok[9];
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh)
+#pragma unroll
+      for (int kw = 0; kw < 3; ++kw) {
+        const int h = h0 + kh, w = w0 + kw;
+        ok[kh * 3 + kw] = (unsigned)h < (unsigned)g.H && (unsigned)w < (unsigned)g.W;
+        u[kh * 3 + kw] = ok[kh * 3 + kw] ? __ldg(reinterpret_cast<const uint4*>(x + (((size_t)n * g.H + h) * g.W + w) * g.C + c0))
+                                         : make_uint4(0, 0, 0, 0);   // neighbours share pixels: keep them in L1
+      }
+    float sc[8], sh[8], best[8], bx[8];
+    int bi[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { sc[j] = scale[c0 + j]; sh[j] = shift[c0 + j]; best[j] = -INFINITY; bi[j] = 0; bx[j] = 0.f; }
+#pragma unroll
+    for (int t = 0; t < 9; ++t) {
+      if (!ok[t]) continue;
+      float f[8];
+      unpack8<T>(u[t], f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float v = fmaxf(fmaf(f[j], sc[j], sh[j]), 0.f);
+        if (v > best[j]) { best[j] = v; bi[j] = t; bx[j] = f[j]; }
+      }
+    }
+    const size_t o = (((size_t)n * g.Ho + ho) * g.Wo + wo) * g.C + c0;
+    *reinterpret_cast<uint4*>(y + o) = pack8<T>(best);
+    *reinterpret_cast<uint4*>(xmax + o) = pack8<T>(bx);
+    uint2 pk;
+    pk.x = (bi[0] & 0xff) | ((bi[1] & 0xff) << 8) | ((bi[2] & 0xff) << 16) | ((bi[3] & 0xff) << 24);
+    pk.y = (bi[4] & 0xff) | ((bi[5] & 0xff) << 8) | ((bi[6] & 0xff) << 16) | ((bi[7] & 0xff) << 24);
+    *reinterpret_cast<uint2*>(idx + o) = pk;
+  }
+}
+
+// dv with the channels whose saved arg-max is not `tap` zeroed (see gather_pool_grad).
+__device__ __forceinline__ uint4 keep_tap(uint4 dv, uint2 pk, unsigned tap) {
+  const unsigned tap4 = tap * 0x01010101u;
+  const unsigned mlo = __vcmpeq4(pk.x, tap4), mhi = __vcmpeq4(pk.y, tap4);
+  dv.x &= __byte_perm(mlo, 0, 0x1100);
+  dv.y &= __byte_perm(mlo, 0, 0x3322);
+  dv.z &= __byte_perm(mhi, 0, 0x1100);
+  dv.w &= __byte_perm(mhi, 0, 0x3322);
+  return dv;
+}
+template <typename T>
+__device__ __forceinline__ uint4 add_packed4(uint4 a, uint4 b) {
+  return make_uint4(add_packed<T>(a.x, b.x), add_packed<T>(a.y, b.y), add_packed<T>(a.z, b.z), add_packed<T>(a.w, b.w));
+}
+
+// A 2x2 block of input pixels (rows 2a, 2a+1; columns 2b, 2b+1) x 8 channels per thread.  Only the pooled
+// outputs (a..a+1, b..b+1) can have their arg-max inside the block, so four (tap, gradient) loads serve four
+// pixels (the per-pixel gather needed 2.25 on average, each behind a runtime loop), and with the four x
+// loads that is 160 bytes in flight per thread.  Accumulation order per pixel is the generic kernel's.
+template <typename T>
+__global__ void __launch_bounds__(256) k_bn_pool_bwd_apply_321(const T* __restrict__ dpool, const int8_t* __restrict__ idx,
+                                                              const T* __restrict__ x, T* __restrict__ dx, PoolGeom g,
+                                                              const float* __restrict__ mean, const float* __restrict__ invstd,
+                                                              const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                              const float* __restrict__ k) {
+  extern __shared__ float sm[];
+  const int C = g.C;
+  // dx = a*gg + b*x + c per channel: a = invstd*gamma, b = -k2*a, c = (mu*k2 - k1)*a; sh = forward shift
+  float* ca = sm;
+  float* cb = sm + C;
+  float* cc = sm + 2 * C;
+  float* sh = sm + 3 * C;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const float a = invstd[c] * gamma[c];
+    ca[c] = a;
+    cb[c] = -k[C + c] * a;
+    cc[c] = (mean[c] * k[C + c] - k[c]) * a;
+    sh[c] = beta[c] - mean[c] * a;
+  }
+  __syncthreads();
+  const int cg = C / 8, Hh = g.H / 2, Wh = g.W / 2;
+  const unsigned total = (unsigned)g.N * Hh * Wh * cg;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int c0 = (int)(i % cg) * 8;
+    unsigned r = i / cg;
+    const int b = (int)(r % Wh); r /= Wh;
+    const int a = (int)(r % Hh);
+    const int n = (int)(r / Hh);
+    const bool a1 = a + 1 < g.Ho, b1 = b + 1 < g.Wo;
+    const size_t p00 = (((size_t)n * g.Ho + a) * g.Wo + b) * C + c0;
+    const size_t p01 = p00 + C, p10 = p00 + (size_t)g.Wo * C, p11 = p10 + C;
+    const size_t x00 = (((size_t)n * g.H + 2 * a) * g.W + 2 * b) * C + c0;
+    const size_t x01 = x00 + C, x10 = x00 + (size_t)g.W * C, x11 = x10 + C;
+    const uint4 z4 = make_uint4(0, 0, 0, 0);
+    const uint2 z2 = make_uint2(0xffffffffu, 0xffffffffu);           // tap 255 never matches
+    const uint2 k00 = __ldg(reinterpret_cast<const uint2*>(idx + p00));
+    const uint2 k01 = b1 ? __ldg(reinterpret_cast<const uint2*>(idx + p01)) : z2;
+    const uint2 k10 = a1 ? __ldg(reinterpret_cast<const uint2*>(idx + p10)) : z2;
+    const uint2 k11 = (a1 && b1) ? __ldg(reinterpret_cast<const uint2*>(idx + p11)) : z2;
+    const uint4 d00 = __ldg(reinterpret_cast<const uint4*>(dpool + p00));   // each pooled output serves 4 blocks: L1
+    const uint4 d01 = b1 ? __ldg(reinterpret_cast<const uint4*>(dpool + p01)) : z4;
+    const uint4 d10 = a1 ? __ldg(reinterpret_cast<const uint4*>(dpool + p10)) : z4;
+    const uint4 d11 = (a1 && b1) ? __ldg(reinterpret_cast<const uint4*>(dpool + p11)) : z4;
+    uint4 xv[4];
+    xv[0] = ldg_stream(x + x00); xv[1] = ldg_stream(x + x01); xv[2] = ldg_stream(x + x10); xv[3] = ldg_stream(x + x11);
+    uint4 gsum[4];
+    gsum[0] = keep_tap(d00, k00, 4);
+    gsum[1] = add_packed4<T>(keep_tap(d00, k00, 5), keep_tap(d01, k01, 3));
+    gsum[2] = add_packed4<T>(keep_tap(d00, k00, 7), keep_tap(d10, k10, 1));
+    gsum[3] = add_packed4<T>(add_packed4<T>(add_packed4<T>(keep_tap(d00, k00, 8), keep_tap(d01, k01, 6)), keep_tap(d10, k10, 2)),
+                             keep_tap(d11, k11, 0));
+    float fa[8], fb[8], fc[8], fs[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { fa[j] = ca[c0 + j]; fb[j] = cb[c0 + j]; fc[j] = cc[c0 + j]; fs[j] = sh[c0 + j]; }
+    const size_t xo[4] = {x00, x01, x10, x11};
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      float gy[8], xf[8];
+      unpack8<T>(gsum[q], gy);
+      unpack8<T>(xv[q], xf);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float gg = fmaf(xf[j], fa[j], fs[j]) > 0.f ? gy[j] : 0.f;
+        gy[j] = fmaf(gg, fa[j], fmaf(xf[j], fb[j], fc[j]));
+      }
+      *reinterpret_cast<uint4*>(dx + xo[q]) = pack8<T>(gy);
+    }
+  }
+}
+
 template <typename T> bool shape_ok(int C) {
   const int V = Vec<T>::N;
   if (C % V) return false;
@@ -612,19 +705,30 @@ static bool pool_geom(PoolGeom& g, int N, int H, int W, int C, int ks, int st, i
   return C % 8 == 0 && ks * ks <= 127 && g.Ho > 0 && g.Wo > 0 && (double)N * H * W * (C / 8) < 4.0e9;
 }
 
-int pdt_bn_pool_fwd(const void* x, void* y, int8_t* idx, int dtype, int N, int H, int W, int C, int ks, int st, int pd,
-                    const float* mean, const float* invstd, const float* gamma, const float* beta, cudaStream_t stream) {
+int pdt_bn_pool_fwd(const void* x, void* y, int8_t* idx, void* xmax, int dtype, int N, int H, int W, int C, int ks, int st,
+                    int pd, const float* mean, const float* invstd, const float* gamma, const float* beta, cudaStream_t stream) {
   PoolGeom g;
   if (!pool_geom(g, N, H, W, C, ks, st, pd)) return PDT_E_UNSUPPORTED;
   const long total = (long)N * g.Ho * g.Wo * (C / 8);
   long nb = (total + 255) / 256;
   if (nb > 148 * 16) nb = 148 * 16;
-  BNP_DISPATCH(dtype, k_bn_pool_fwd<T><<<(int)nb, 256, 2 * C * sizeof(float), stream>>>(
-      reinterpret_cast<const T*>(x), reinterpret_cast<T*>(y), idx, g, mean, invstd, gamma, beta));
+  if (ks == 3 && st == 2 && pd == 1) {
+    BNP_DISPATCH(dtype, k_bn_pool_fwd_321<T><<<(int)nb, 256, 2 * C * sizeof(float), stream>>>(
+        reinterpret_cast<const T*>(x), reinterpret_cast<T*>(y), idx, reinterpret_cast<T*>(xmax), g, mean, invstd, gamma, beta));
+  } else {
+    BNP_DISPATCH(dtype, k_bn_pool_fwd<T><<<(int)nb, 256, 2 * C * sizeof(float), stream>>>(
+        reinterpret_cast<const T*>(x), reinterpret_cast<T*>(y), idx, reinterpret_cast<T*>(xmax), g, mean, invstd, gamma, beta));
+  }
   return (int)cudaGetLastError();
 }
 
-int pdt_bn_pool_bwd_reduce(const void* dpool, const int8_t* idx, const void* x, int dtype, int N, int H, int W, int C,
+// Reduction half of the backward, taken from the POOLED side: with g = dpool where ypool > 0 (the ReLU mask
+// of the arg-max element is exactly "the pooled value is positive"),
+//   sum over input pixels of dy            = sum over pooled outputs of g
+//   sum over input pixels of dy * (x - mu) = sum over pooled outputs of g * (x[arg-max] - mu)
+// because every pooled gradient lands on exactly one input pixel.  x[arg-max] is what the forward saved as
+// `xmax`, so this pass reads two pooled-size tensors + xmax instead of gathering over the 4x larger input.
+int pdt_bn_pool_bwd_reduce(const void* dpool, const void* ypool, const void* xmax, int dtype, int N, int H, int W, int C,
                            int ks, int st, int pd, const float* mean, const float* invstd, const float* gamma,
                            const float* beta, void* scratch, const PdtCommDesc* comm, float* dgamma, float* dbeta,
                            float* out_k, cudaStream_t stream) {
@@ -632,11 +736,12 @@ int pdt_bn_pool_bwd_reduce(const void* dpool, const int8_t* idx, const void* x, 
   if (!pool_geom(g, N, H, W, C, ks, st, pd)) return PDT_E_UNSUPPORTED;
   unsigned* counter = reinterpret_cast<unsigned*>(scratch);
   float* partial = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + 256);
+  const long Mp = (long)N * g.Ho * g.Wo;
   BNP_DISPATCH(dtype, {
     if (!shape_ok<T>(C)) return PDT_E_UNSUPPORTED;
-    k_bn_pool_bwd_reduce<T><<<stats_blocks((long)N * H * W, C, 8), kThreads, 0, stream>>>(
-        reinterpret_cast<const T*>(dpool), idx, reinterpret_cast<const T*>(x), g, mean, invstd, gamma, beta, partial,
-        counter, make_comm(comm), dgamma, dbeta, out_k);
+    k_bn_bwd_reduce<T><<<stats_blocks(Mp, C, 8), kThreads, 0, stream>>>(
+        reinterpret_cast<const T*>(dpool), reinterpret_cast<const T*>(ypool), reinterpret_cast<const T*>(xmax), Mp, C, mean,
+        invstd, gamma, beta, 1, partial, counter, make_comm(comm), dgamma, dbeta, out_k, (long)N * H * W);
   });
   return (int)cudaGetLastError();
 }
@@ -647,6 +752,15 @@ int pdt_bn_pool_bwd_apply(const void* dpool, const int8_t* idx, const void* x, v
   PoolGeom g;
   if (!pool_geom(g, N, H, W, C, ks, st, pd)) return PDT_E_UNSUPPORTED;
   if (((C / 8) & (C / 8 - 1)) != 0) return PDT_E_UNSUPPORTED;
+  if (ks == 3 && st == 2 && pd == 1 && H % 2 == 0 && W % 2 == 0) {
+    const long total = (long)N * (H / 2) * (W / 2) * (C / 8);
+    long nb = (total + 255) / 256;
+    if (nb > 148 * 32) nb = 148 * 32;
+    BNP_DISPATCH(dtype, k_bn_pool_bwd_apply_321<T><<<(unsigned)nb, 256, 4 * C * sizeof(float), stream>>>(
+        reinterpret_cast<const T*>(dpool), idx, reinterpret_cast<const T*>(x), reinterpret_cast<T*>(dx), g, mean, invstd,
+        gamma, beta, k));
+    return (int)cudaGetLastError();
+  }
   const long nb = (long)N * H;                 // one block per image row
   BNP_DISPATCH(dtype, k_bn_pool_bwd_apply<T><<<(unsigned)nb, 256, 5 * C * sizeof(float), stream>>>(
       reinterpret_cast<const T*>(dpool), idx, reinterpret_cast<const T*>(x), reinterpret_cast<T*>(dx), g, mean, invstd,
@@ -747,7 +861,7 @@ int pdt_bn_bwd_reduce(const void* dy, const void* y, const void* x, long M, int 
     if (!shape_ok<T>(C)) return PDT_E_UNSUPPORTED;
     k_bn_bwd_reduce<T><<<stats_blocks(M, C, Vec<T>::N), kThreads, 0, stream>>>(
         reinterpret_cast<const T*>(dy), reinterpret_cast<const T*>(y), reinterpret_cast<const T*>(x), M, C, mean, invstd,
-        gamma, beta, relu, partial, counter, make_comm(comm), dgamma, dbeta, out_k);
+        gamma, beta, relu, partial, counter, make_comm(comm), dgamma, dbeta, out_k, M);
   });
   return (int)cudaGetLastError();
 }

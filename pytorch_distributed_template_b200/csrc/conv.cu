@@ -200,7 +200,8 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     // ================= epilogue: TMEM -> registers -> global =================
     const int quarter = warp & 3;                 // TMEM lanes [32*quarter, +32) are the ones this warp may read
     float* my_stat = s_stat + quarter * (2 * kStatMaxK + 32 * 33);
-    float* tp = my_stat + 2 * kStatMaxK;          // 32 x 33 transpose tile
+    const uint32_t stat_a = smem_u32(my_stat);
+    const uint32_t tp_a = stat_a + 2 * kStatMaxK * 4u;   // 32 x 33 transpose tile
     if (bs.enabled) {
       for (int i = lane; i < 2 * kStatMaxK; i += 32) my_stat[i] = 0.f;
       __syncwarp();
@@ -232,16 +233,17 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
           // rows past M come from zero-filled (out-of-bounds) pixels: their accumulators are exactly 0.
           // Column sums over the warp's 32 rows via a padded shared-memory transpose (conflict-free both ways).
 #pragma unroll
-          for (int j = 0; j < 32; ++j) tp[lane * 33 + j] = __uint_as_float(v[j]);
+          for (int j = 0; j < 32; ++j) sts_f32(tp_a + (uint32_t)(lane * 33 + j) * 4u, __uint_as_float(v[j]));
           __syncwarp();
           float cs = 0.f, cq = 0.f;
 #pragma unroll
-          for (int rr = 0; rr < 32; ++rr) { const float t = tp[rr * 33 + lane]; cs += t; cq = fmaf(t, t, cq); }
+          for (int rr = 0; rr < 32; ++rr) { const float t = lds_f32(tp_a + (uint32_t)(rr * 33 + lane) * 4u); cs += t; cq = fmaf(t, t, cq); }
           __syncwarp();
           const int col = nt * BN + c0 + lane;
           if (col < g.K) {
-            my_stat[col] += cs;
-            my_stat[kStatMaxK + col] += cq;
+            const uint32_t a = stat_a + (uint32_t)col * 4u;
+            sts_f32(a, lds_f32(a) + cs);
+            sts_f32(a + kStatMaxK * 4u, lds_f32(a + kStatMaxK * 4u) + cq);
           }
         }
         if (row < g.M) {

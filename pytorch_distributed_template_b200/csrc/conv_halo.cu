@@ -53,7 +53,13 @@ template <int BN, bool RES> struct HCfg {
   static constexpr int kAStages = 3;
   static constexpr int kBTile = BN * 128;
   static constexpr int kBStages = RES ? 9 : 4;                // resident: all nine taps of the single 64-channel block
-  static constexpr int kTmemCols = 2 * BN;
+  // Several accumulator chains per tile, each double-buffered: consecutive tcgen05.mma that accumulate into
+  // the SAME TMEM columns serialise on the accumulate latency (~96 clk measured, i.e. 3x the 32-clk rate of
+  // an N=64 MMA and 1.5x the 64-clk rate of an N=128 one); rotating the 36 MMAs of a patch over 3 (N=64) or
+  // 2 (N=128) independent chains hides it.  The epilogue adds the chains.
+  static constexpr int kChains = BN == 64 ? 3 : 2;
+  static constexpr int kAccCols = BN == 64 ? 256 : 2 * BN;      // columns reserved per accumulator buffer (chains * BN, padded)
+  static constexpr int kTmemCols = 2 * kAccCols;                // 512
   // per epilogue warp: column accumulators [2][kStatMaxK] + a 32 x 33 float transpose tile
   static constexpr int kStatBytes = kEpiWarps * (2 * kStatMaxK + 32 * 33) * 4;
   static constexpr int kSmemBytes = kAStages * kAStage + kBStages * kBTile + 1024 + 256 + kStatBytes;
@@ -63,6 +69,13 @@ __device__ __forceinline__ void tma_load_4d(void* smem, const CUtensorMap* m, ui
   asm volatile(
       "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
       ::"r"(smem_u32(smem)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c), "r"(w), "r"(h), "r"(n) : "memory");
+}
+
+// Pull a future patch into L2 (no shared-memory destination, no barrier): the 3-deep shared-memory ring alone
+// cannot hide DRAM latency for 30 KB patches, an L2 hit can be.
+__device__ __forceinline__ void tma_prefetch_4d(const CUtensorMap* m, int c, int w, int h, int n) {
+  asm volatile("cp.async.bulk.prefetch.tensor.4d.L2.global [%0, {%1, %2, %3, %4}];"
+               ::"l"(reinterpret_cast<uint64_t>(m)), "r"(c), "r"(w), "r"(h), "r"(n) : "memory");
 }
 
 __device__ __forceinline__ void warp_transpose_reduce(float (&a)[32], int lane) {
@@ -128,6 +141,16 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
       for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x) {
         const int n = tile / g.tiles_per_image;
         const int h0 = (tile - n * g.tiles_per_image) * g.TR;
+        {   // L2 prefetch of the patch this CTA will want kPrefetchAhead tiles from now
+          constexpr int kPrefetchAhead = 6;
+          const int ft = tile + kPrefetchAhead * (int)gridDim.x;
+          if (ft < g.num_tiles && elect_one_sync()) {
+            const int fn = ft / g.tiles_per_image;
+            const int fh = (ft - fn * g.tiles_per_image) * g.TR;
+            for (int cc = 0; cc < g.c_chunks; ++cc) tma_prefetch_4d(&tmX, cc * 64, -1, fh - 1, fn);
+          }
+          __syncwarp();
+        }
         for (int cc = 0; cc < g.c_chunks; ++cc) {
           mbar_wait(&aempty[as], aph ^ 1);
           if (elect_one_sync()) {
@@ -154,6 +177,16 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
     // ================= MMA issuer (whole warp converged, one elected lane issues) =================
     {
       constexpr uint32_t idesc = make_idesc(128, BN, std::is_same<T, __nv_bfloat16>::value ? 1 : 0, 0, 0);
+      constexpr int NCH = C::kChains;
+      // Everything the 36 MMAs of a patch need is loop-invariant except the ring slot: the tap's operand is
+      // the patch shifted by whole 128-byte pixel rows, i.e. a constant added to the descriptor's
+      // (address >> 4) field.  Keeping those constants in registers and unrolling the tap loop matters: the
+      // single issuing warp was the bottleneck when it recomputed them (ncu: 70 % of its samples in
+      // descriptor arithmetic, 264 clk per tap for 4 MMAs worth 128-192 clk of tensor-pipe time).
+      int64_t tapoff[9];
+#pragma unroll
+      for (int tap = 0; tap < 9; ++tap) tapoff[tap] = (int64_t)(((tap / 3) * g.Wp + (tap % 3) - 1) * 8);
+      const uint64_t db_base = make_sw128_desc(smem_u32(smB), 1024, 16);
       if (RES) { mbar_wait(&bfull[0], 0); tc_fence_after(); }
       int as = 0, bsg = 0, it = 0;
       uint32_t aph = 0, bph = 0;
@@ -162,36 +195,47 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         const uint32_t acc_phase = (it >> 1) & 1;
         mbar_wait(&tempty[acc], acc_phase ^ 1);
         tc_fence_after();
-        const uint32_t tmem_d = tmem_base + acc * BN;
+        const uint32_t tmem_d = tmem_base + acc * C::kAccCols;
         for (int cc = 0; cc < g.c_chunks; ++cc) {
           mbar_wait(&afull[as], aph);
           tc_fence_after();
-          const uint32_t patch = smem_u32(smA + as * C::kAStage + 1024);
-#pragma unroll 1
-          for (int tap = 0; tap < 9; ++tap) {
-            const int r = tap / 3, s = tap - r * 3;
-            int bidx;
-            if (RES) bidx = tap;
-            else {
-              mbar_wait(&bfull[bsg], bph);
-              tc_fence_after();
-              bidx = bsg;
-            }
-            // the tap's operand = the patch shifted by whole 128-byte pixel rows
-            const uint64_t da = make_sw128_desc(patch + (uint32_t)((r * g.Wp + s - 1) * 128), 1024, 16);
-            const uint64_t db = make_sw128_desc(smem_u32(smB + bidx * C::kBTile), 1024, 16);
+          const uint64_t da_base = make_sw128_desc(smem_u32(smA + as * C::kAStage + 1024), 1024, 16);
+          const uint32_t later = cc != 0;
+          if (RES) {
             if (elect_one_sync()) {
 #pragma unroll
-              for (int k = 0; k < 4; ++k) umma_f16(tmem_d, da + 2 * k, db + 2 * k, idesc, (cc | tap | k) != 0);
-              if (!RES) umma_commit(&bempty[bsg]);
+              for (int tap = 0; tap < 9; ++tap) {
+                const uint64_t da = da_base + (uint64_t)tapoff[tap];
+                const uint64_t db = db_base + (uint64_t)(tap * (C::kBTile >> 4));
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                  const int i = tap * 4 + k;
+                  umma_f16(tmem_d + (i % NCH) * BN, da + 2 * k, db + 2 * k, idesc, i >= NCH ? 1u : later);
+                }
+              }
+              umma_commit(&aempty[as]);
             }
             __syncwarp();
-            if (!RES) {
+          } else {
+#pragma unroll
+            for (int tap = 0; tap < 9; ++tap) {
+              mbar_wait(&bfull[bsg], bph);
+              tc_fence_after();
+              const uint64_t da = da_base + (uint64_t)tapoff[tap];
+              const uint64_t db = db_base + (uint64_t)(bsg * (C::kBTile >> 4));
+              if (elect_one_sync()) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                  const int i = tap * 4 + k;
+                  umma_f16(tmem_d + (i % NCH) * BN, da + 2 * k, db + 2 * k, idesc, i >= NCH ? 1u : later);
+                }
+                umma_commit(&bempty[bsg]);
+                if (tap == 8) umma_commit(&aempty[as]);
+              }
+              __syncwarp();
               if (++bsg == C::kBStages) { bsg = 0; bph ^= 1; }
             }
           }
-          if (elect_one_sync()) umma_commit(&aempty[as]);
-          __syncwarp();
           if (++as == C::kAStages) { as = 0; aph ^= 1; }
         }
         if (elect_one_sync()) umma_commit(&tfull[acc]);
@@ -203,12 +247,17 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
     const int quarter = warp & 3;                 // TMEM lane quarter this warp may read
     const int half = (warp - 4) >> 2;             // which half of the BN columns it drains
     const int ew = warp - 4;
+    constexpr int NCH = C::kChains;
+    constexpr int NIT = BN / 64;                  // 32-column groups per warp
     float* my_stat = s_stat + ew * (2 * kStatMaxK + 32 * 33);
-    float* tp = my_stat + 2 * kStatMaxK;          // 32 x 33 transpose tile
+    const uint32_t tp_a = smem_u32(my_stat + 2 * kStatMaxK);   // 32 x 33 transpose tile
     if (bs.enabled) {
       for (int i = lane; i < 2 * kStatMaxK; i += 32) my_stat[i] = 0.f;
       __syncwarp();
     }
+    float cs[NIT], cq[NIT];                       // this lane's column (c0 + lane): running sum / sum of squares
+#pragma unroll
+    for (int q = 0; q < NIT; ++q) cs[q] = cq[q] = 0.f;
     const int m = quarter * 32 + lane;            // output slot inside the tile (padded coordinates)
     const int ti = m / g.Wp, tj = m - ti * g.Wp;
     int it = 0;
@@ -217,28 +266,36 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
       const int h0 = (tile - n * g.tiles_per_image) * g.TR;
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1;
-      mbar_wait(&tfull[acc], acc_phase);
-      tc_fence_after();
       const bool valid = ti < g.TR && tj >= 1 && tj <= g.W && (h0 + ti) < g.H;
       T* orow = out + (((size_t)n * g.H + h0 + ti) * g.W + (tj - 1)) * g.K;
-      const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(quarter * 32) << 16);
-#pragma unroll 1
-      for (int c0 = half * (BN / 2); c0 < (half + 1) * (BN / 2); c0 += 32) {
+      const uint32_t taddr = tmem_base + acc * C::kAccCols + ((uint32_t)(quarter * 32) << 16);
+      mbar_wait(&tfull[acc], acc_phase);
+      tc_fence_after();
+#pragma unroll
+      for (int q = 0; q < NIT; ++q) {
+        const int c0 = half * (BN / 2) + q * 32;
         uint32_t v[32];
-        tmem_ld32(taddr + c0, v);
-        tmem_ld_wait();
-        if (bs.enabled) {
-          // column sums over this warp's 32 rows through a padded shared-memory transpose (conflict-free
-          // both ways): 32 STS + 32 LDS + 64 FMA per lane, cheaper than a shuffle butterfly
+        {
+          uint32_t v2[32];
+          tmem_ld32(taddr + c0, v);
+          tmem_ld32(taddr + BN + c0, v2);
+          if (NCH == 3) {
+            uint32_t v3[32];
+            tmem_ld32(taddr + 2 * BN + c0, v3);
+            tmem_ld_wait();
 #pragma unroll
-          for (int j = 0; j < 32; ++j) tp[lane * 33 + j] = valid ? __uint_as_float(v[j]) : 0.f;   // junk slots excluded
-          __syncwarp();
-          float cs = 0.f, cq = 0.f;
+            for (int j = 0; j < 32; ++j)
+              v[j] = __float_as_uint(__uint_as_float(v[j]) + __uint_as_float(v2[j]) + __uint_as_float(v3[j]));
+          } else {
+            tmem_ld_wait();
 #pragma unroll
-          for (int rr = 0; rr < 32; ++rr) { const float t = tp[rr * 33 + lane]; cs += t; cq = fmaf(t, t, cq); }
+            for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + __uint_as_float(v2[j]));
+          }
+        }
+        if (q == NIT - 1) {       // accumulators are in registers: hand the buffer back before the long tail
+          tc_fence_before();
           __syncwarp();
-          my_stat[c0 + lane] += cs;
-          my_stat[kStatMaxK + c0 + lane] += cq;
+          if (lane == 0) mbar_arrive(&tempty[acc]);
         }
         if (valid) {
 #pragma unroll
@@ -251,10 +308,33 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
             *reinterpret_cast<uint4*>(orow + c0 + j) = o;
           }
         }
+        if (bs.enabled) {
+          // column sums over this warp's 32 rows through a padded shared-memory transpose (conflict-free
+          // both ways): 32 STS + 32 LDS + 64 FMA per lane, cheaper than a shuffle butterfly
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            sts_f32(tp_a + (uint32_t)(lane * 33 + j) * 4u, valid ? __uint_as_float(v[j]) : 0.f);   // junk slots excluded
+          __syncwarp();
+          float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+#pragma unroll
+          for (int rr = 0; rr < 32; rr += 2) {
+            const float t0 = lds_f32(tp_a + (uint32_t)(rr * 33 + lane) * 4u);
+            const float t1 = lds_f32(tp_a + (uint32_t)((rr + 1) * 33 + lane) * 4u);
+            s0 += t0; q0 = fmaf(t0, t0, q0);
+            s1 += t1; q1 = fmaf(t1, t1, q1);
+          }
+          __syncwarp();
+          cs[q] += s0 + s1;
+          cq[q] += q0 + q1;
+        }
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty[acc]);
+    }
+    if (bs.enabled) {
+#pragma unroll
+      for (int q = 0; q < NIT; ++q) {
+        my_stat[half * (BN / 2) + q * 32 + lane] = cs[q];
+        my_stat[kStatMaxK + half * (BN / 2) + q * 32 + lane] = cq[q];
+      }
     }
     if (bs.enabled) {
       __shared__ int s_last;

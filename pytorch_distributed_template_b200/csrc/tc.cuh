@@ -121,6 +121,16 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+// Explicit shared-window accesses.  Pointers carved out of the dynamic shared buffer through integer
+// arithmetic lose their address space and ptxas emits generic LD.E/ST.E for them (seen in the ncu source
+// view as `lg` stalls inside the epilogue); these keep the fast LDS/STS path.
+__device__ __forceinline__ void sts_f32(uint32_t addr, float v) { asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory"); }
+__device__ __forceinline__ float lds_f32(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
+  return v;
+}
+
 // ---- descriptors -------------------------------------------------------------------------------------
 // Shared-memory matrix descriptor, 128-byte swizzle, rows of 128 bytes, 8-row groups 1024 B apart.
 // Works for K-major tiles ([rows of M/N][64 x 16-bit along K]) and for MN-major tiles

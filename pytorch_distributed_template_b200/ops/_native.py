@@ -67,7 +67,7 @@ _SIGNATURES = {
     "pdt_bn_fwd_apply": ([_vp, _vp, _vp, _l, _i, _i, _vp, _vp, _vp, _vp, _i, _i, _f, _vp], _i),
     "pdt_bn_bwd_reduce": ([_vp, _vp, _vp, _l, _i, _i, _vp, _vp, _vp, _vp, _i, _vp, _PC, _vp, _vp, _vp, _vp], _i),
     "pdt_bn_bwd_apply": ([_vp, _vp, _vp, _vp, _vp, _l, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp], _i),
-    "pdt_bn_pool_fwd": ([_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp], _i),
+    "pdt_bn_pool_fwd": ([_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp], _i),
     "pdt_bn_pool_bwd_reduce": ([_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _PC, _vp, _vp, _vp, _vp], _i),
     "pdt_bn_pool_bwd_apply": ([_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp], _i),
     "pdt_ce_scratch_bytes": ([_i], _sz),

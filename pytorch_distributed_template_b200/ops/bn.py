@@ -132,10 +132,11 @@ class _BNReluPoolNative(torch.autograd.Function):
         Ho, Wo = (H + 2 * pd - ks) // st + 1, (W + 2 * pd - ks) // st + 1
         y = torch.empty((N, C, Ho, Wo), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
         idx = torch.empty((N, Ho, Wo, C), dtype=torch.int8, device=x.device)
-        _native.check(lib.pdt_bn_pool_fwd(x.data_ptr(), y.data_ptr(), idx.data_ptr(), dt, N, H, W, C, ks, st, pd,
-                                          mean.data_ptr(), invstd.data_ptr(), weight.data_ptr(), bias.data_ptr(), s),
+        xmax = torch.empty_like(y)       # conv value at each window's arg-max: lets backward reduce over pooled tensors
+        _native.check(lib.pdt_bn_pool_fwd(x.data_ptr(), y.data_ptr(), idx.data_ptr(), xmax.data_ptr(), dt, N, H, W, C, ks, st,
+                                          pd, mean.data_ptr(), invstd.data_ptr(), weight.data_ptr(), bias.data_ptr(), s),
                       "pdt_bn_pool_fwd")
-        ctx.save_for_backward(x, idx, weight, bias, mean, invstd)
+        ctx.save_for_backward(x, idx, weight, bias, mean, invstd, y, xmax)
         ctx.geom, ctx.comm = (ks, st, pd), comm
         ctx.params = (weight, bias)
         return y
@@ -147,7 +148,7 @@ class _BNReluPoolNative(torch.autograd.Function):
 
     @staticmethod
     def _backward_impl(ctx, dpool):
-        x, idx, weight, bias, mean, invstd = ctx.saved_tensors
+        x, idx, weight, bias, mean, invstd, y, xmax = ctx.saved_tensors
         ks, st, pd = ctx.geom
         N, C, H, W = x.shape
         dpool = dpool.contiguous(memory_format=torch.channels_last)
@@ -155,7 +156,7 @@ class _BNReluPoolNative(torch.autograd.Function):
         dgamma, dbeta = _param_grad_slots(ctx.params, C, x.device)
         k = torch.empty(2 * C, dtype=torch.float32, device=x.device)
         scratch = _bn_scratch(x.device, C)
-        _native.check(lib.pdt_bn_pool_bwd_reduce(dpool.data_ptr(), idx.data_ptr(), x.data_ptr(), dt, N, H, W, C, ks, st, pd,
+        _native.check(lib.pdt_bn_pool_bwd_reduce(dpool.data_ptr(), y.data_ptr(), xmax.data_ptr(), dt, N, H, W, C, ks, st, pd,
                                                  mean.data_ptr(), invstd.data_ptr(), weight.data_ptr(), bias.data_ptr(),
                                                  scratch.data_ptr(), ctx.comm, dgamma.data_ptr(), dbeta.data_ptr(),
                                                  k.data_ptr(), s), "pdt_bn_pool_bwd_reduce")

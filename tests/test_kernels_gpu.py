@@ -247,8 +247,10 @@ def test_resnet18_amp_step_matches_torch_autocast(native_lib):
 
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
-@pytest.mark.parametrize("shape", [(5, 64, 112, 112), (3, 64, 30, 34)])
-def test_bn_relu_maxpool_fused(native_lib, dtype, shape):
+@pytest.mark.parametrize("shape,geom", [((5, 64, 112, 112), (3, 2, 1)), ((3, 64, 30, 34), (3, 2, 1)),
+                                        ((2, 64, 31, 33), (3, 2, 1)),      # odd extent: generic dx kernel
+                                        ((2, 32, 24, 20), (2, 2, 0))])     # other geometry: generic kernels
+def test_bn_relu_maxpool_fused(native_lib, dtype, shape, geom):
     from pytorch_distributed_template_b200 import ops
     torch.manual_seed(8)
     C = shape[1]
@@ -259,9 +261,9 @@ def test_bn_relu_maxpool_fused(native_lib, dtype, shape):
         bn.bias.uniform_(-0.5, 0.5)
     ref_bn = torch.nn.BatchNorm2d(C).to(_dev())
     ref_bn.load_state_dict(bn.state_dict())
-    y = ops.bn_relu_maxpool(x, bn, 3, 2, 1)
+    y = ops.bn_relu_maxpool(x, bn, *geom)
     xf = x.detach().float().requires_grad_(True)
-    yf = F.max_pool2d(F.relu(ref_bn(xf)), 3, 2, 1)
+    yf = F.max_pool2d(F.relu(ref_bn(xf)), *geom)
     assert y.shape == yf.shape
     tol = TOL[dtype]
     assert torch.allclose(y.float(), yf, rtol=tol, atol=tol)
