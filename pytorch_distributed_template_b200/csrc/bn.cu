@@ -21,7 +21,10 @@
 // (scratch, [blocks][2C] floats); the block that takes the last ticket of `counter`
 // (scratch, one word, self-resetting) folds the rows in a fixed order in fp64, so the
 // result is deterministic for a given grid.
+#include <cstdlib>
+#include <initializer_list>
 #include "fabric.cuh"
+#include "tc.cuh"
 
 namespace {
 
@@ -140,6 +143,62 @@ __device__ __forceinline__ void exchange_sum(const Comm& c, double* tot, int n, 
   block_barrier(c, ch, 0);
 }
 
+// After block_fold: the last block folds every block's row, exchanges with the peers (SyncBN) and writes
+// mean / invstd / running statistics.  `smem` >= 2C doubles + blockDim doubles.
+__device__ __forceinline__ void finish_fwd_stats(float* smem, const float* __restrict__ partial, unsigned* counter, const Comm& comm,
+                                                 int C, long count, float* running_mean, float* running_var, float momentum,
+                                                 float eps, float* __restrict__ save_mean, float* __restrict__ save_invstd) {
+  __shared__ double s_count;
+  const int tid = threadIdx.x;
+  if (!take_last_ticket(counter)) return;
+  double* tot = reinterpret_cast<double*>(smem);
+  fold_partials(tot, partial, gridDim.x, 2 * C);
+  if (tid == 0) { s_count = (double)count; *counter = 0; }
+  __syncthreads();
+  if (comm.world > 1) exchange_sum(comm, tot, 2 * C, &s_count);
+  __syncthreads();
+  const double N = s_count;
+  for (int c = tid; c < C; c += blockDim.x) {
+    const double mean = tot[c] / N;
+    double var = tot[C + c] / N - mean * mean;
+    var = var > 0.0 ? var : 0.0;
+    save_mean[c] = (float)mean;
+    save_invstd[c] = (float)(1.0 / sqrt(var + (double)eps));
+    if (running_mean) {
+      const double unbiased = N > 1.0 ? var * N / (N - 1.0) : var;
+      running_mean[c] = (float)((1.0 - momentum) * running_mean[c] + momentum * mean);
+      running_var[c] = (float)((1.0 - momentum) * running_var[c] + momentum * unbiased);
+    }
+  }
+}
+
+// Same for the backward reduction: local dgamma / dbeta, then the (optionally cross-rank) k1, k2 vectors.
+// out_k: [2C] floats consumed by the dx pass: k1 = sum_dy / N, k2 = sum_dy_xmu * invstd^2 / N (N global)
+__device__ __forceinline__ void finish_bwd_reduce(float* smem, const float* __restrict__ partial, unsigned* counter, const Comm& comm,
+                                                  int C, long count, const float* __restrict__ invstd, float* __restrict__ dgamma,
+                                                  float* __restrict__ dbeta, float* __restrict__ out_k) {
+  __shared__ double s_count;
+  const int tid = threadIdx.x;
+  if (!take_last_ticket(counter)) return;
+  double* tot = reinterpret_cast<double*>(smem);
+  fold_partials(tot, partial, gridDim.x, 2 * C);
+  if (tid == 0) { s_count = (double)count; *counter = 0; }
+  __syncthreads();
+  for (int c = tid; c < C; c += blockDim.x) {   // parameter grads stay local: DDP averages them
+    dbeta[c] = (float)tot[c];
+    dgamma[c] = (float)(tot[C + c] * (double)invstd[c]);
+  }
+  __syncthreads();
+  if (comm.world > 1) exchange_sum(comm, tot, 2 * C, &s_count);
+  __syncthreads();
+  const double N = s_count;
+  for (int c = tid; c < C; c += blockDim.x) {
+    const double is = (double)invstd[c];
+    out_k[c] = (float)(tot[c] / N);
+    out_k[C + c] = (float)(tot[C + c] * is * is / N);
+  }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(kThreads) k_bn_fwd_stats(const T* __restrict__ x, long M, int C, float* __restrict__ partial,
                                                           unsigned* counter, Comm comm, float* running_mean,
@@ -147,7 +206,6 @@ __global__ void __launch_bounds__(kThreads) k_bn_fwd_stats(const T* __restrict__
                                                           float* __restrict__ save_mean, float* __restrict__ save_invstd) {
   constexpr int V = Vec<T>::N;
   __shared__ __align__(16) float smem[kSmemFloats];
-  __shared__ double s_count;
   const int tid = threadIdx.x, cg = C / V, rpi = kThreads / cg, cgi = tid % cg, r = tid / cg;
   const long chunk = (M + gridDim.x - 1) / gridDim.x;
   const long row0 = (long)blockIdx.x * chunk, row1 = min(M, row0 + chunk);
@@ -175,27 +233,7 @@ __global__ void __launch_bounds__(kThreads) k_bn_fwd_stats(const T* __restrict__
     }
   }
   block_fold<V>(smem, s, q, C, cg, rpi, partial);
-  if (!take_last_ticket(counter)) return;
-
-  double* tot = reinterpret_cast<double*>(smem);
-  fold_partials(tot, partial, gridDim.x, 2 * C);
-  if (tid == 0) { s_count = (double)M; *counter = 0; }
-  __syncthreads();
-  if (comm.world > 1) exchange_sum(comm, tot, 2 * C, &s_count);
-  __syncthreads();
-  const double N = s_count;
-  for (int c = tid; c < C; c += blockDim.x) {
-    const double mean = tot[c] / N;
-    double var = tot[C + c] / N - mean * mean;
-    var = var > 0.0 ? var : 0.0;
-    save_mean[c] = (float)mean;
-    save_invstd[c] = (float)(1.0 / sqrt(var + (double)eps));
-    if (running_mean) {
-      const double unbiased = N > 1.0 ? var * N / (N - 1.0) : var;
-      running_mean[c] = (float)((1.0 - momentum) * running_mean[c] + momentum * mean);
-      running_var[c] = (float)((1.0 - momentum) * running_var[c] + momentum * unbiased);
-    }
-  }
+  finish_fwd_stats(smem, partial, counter, comm, C, M, running_mean, running_var, momentum, eps, save_mean, save_invstd);
 }
 
 // stat2 is invstd (training) or running_var (eval, eps applied here).
@@ -248,7 +286,6 @@ __global__ void __launch_bounds__(kThreads) k_bn_bwd_reduce(const T* __restrict_
                                                            float* __restrict__ out_k, long count) {
   constexpr int V = Vec<T>::N;
   __shared__ __align__(16) float smem[kSmemFloats];
-  __shared__ double s_count;
   const int tid = threadIdx.x, cg = C / V, rpi = kThreads / cg, cgi = tid % cg, r = tid / cg;
   const long chunk = (M + gridDim.x - 1) / gridDim.x;
   const long row0 = (long)blockIdx.x * chunk, row1 = min(M, row0 + chunk);
@@ -300,25 +337,7 @@ __global__ void __launch_bounds__(kThreads) k_bn_bwd_reduce(const T* __restrict_
     }
   }
   block_fold<V>(smem, s, q, C, cg, rpi, partial);
-  if (!take_last_ticket(counter)) return;
-
-  double* tot = reinterpret_cast<double*>(smem);
-  fold_partials(tot, partial, gridDim.x, 2 * C);
-  if (tid == 0) { s_count = (double)count; *counter = 0; }
-  __syncthreads();
-  for (int c = tid; c < C; c += blockDim.x) {   // parameter grads stay local: DDP averages them
-    dbeta[c] = (float)tot[c];
-    dgamma[c] = (float)(tot[C + c] * (double)invstd[c]);
-  }
-  __syncthreads();
-  if (comm.world > 1) exchange_sum(comm, tot, 2 * C, &s_count);
-  __syncthreads();
-  const double N = s_count;
-  for (int c = tid; c < C; c += blockDim.x) {
-    const double is = (double)invstd[c];
-    out_k[c] = (float)(tot[c] / N);
-    out_k[C + c] = (float)(tot[C + c] * is * is / N);
-  }
+  finish_bwd_reduce(smem, partial, counter, comm, C, count, invstd, dgamma, dbeta, out_k);
 }
 
 template <typename T>
@@ -365,6 +384,335 @@ __global__ void __launch_bounds__(kThreads) k_bn_bwd_apply(const T* __restrict__
     store_vec<T>(dx + i * V, g);
   }
 }
+
+// ---- bulk-copy streaming variants ------------------------------------------------------------------------
+// The kernels above keep their loads in registers, so bytes in flight per SM = threads x 16-32 B, and
+// register pressure caps the threads: ncu showed 3.3-4.3 TB/s of the 6.5 TB/s HBM3e delivers.  Here one
+// producer warp streams 8 KB chunks of every input into a shared-memory ring with cp.async.bulk (the TMA
+// engine's 1-D mode) and 8 consumer warps read them back with LDS.128: 96 KB in flight per CTA, two CTAs
+// per SM, independent of what the arithmetic needs in registers.  A chunk is 512 sixteen-byte vectors;
+// the channel group of vector i is i mod (C/V) and C/V divides 256, so each consumer thread keeps ONE
+// channel group for the whole kernel and its per-channel constants / accumulators live in registers.
+// Grid = min(2 x SMs, chunks), chunk c goes to CTA c mod grid: fixed order, deterministic sums.
+namespace sp {
+using namespace pdt::tc;
+constexpr int kCons = 256;                       // consumer threads
+constexpr int kThr = kCons + 32;                 // + the producer warp
+constexpr int kU = 2;                            // vectors per consumer thread and chunk
+constexpr int kChunkVecs = kCons * kU;
+constexpr int kChunkBytes = kChunkVecs * 16;
+constexpr int kRingBytes = 96 * 1024;
+constexpr int kSmemBytes = kRingBytes + 256;
+__host__ __device__ constexpr int stages_for(int nin) { return kRingBytes / (nin * kChunkBytes) > 8 ? 8 : kRingBytes / (nin * kChunkBytes); }
+
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(dst), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 r;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(addr) : "memory");
+  return r;
+}
+
+template <int NIN>
+struct Pipe {
+  static constexpr int S = stages_for(NIN);
+  uint32_t ring;
+  uint64_t* full;
+  uint64_t* empty;
+  int s;
+  uint32_t ph;
+  __device__ __forceinline__ void init(uint8_t* dsm) {
+    ring = smem_u32(dsm);
+    full = reinterpret_cast<uint64_t*>(dsm + kRingBytes);
+    empty = full + 8;
+    s = 0; ph = 0;
+    if (threadIdx.x == 0) {
+      for (int i = 0; i < S; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], kCons / 32); }
+      fence_barrier_init();
+    }
+    __syncthreads();
+  }
+  __device__ __forceinline__ void advance() { if (++s == S) { s = 0; ph ^= 1; } }
+  // whole producer warp
+  __device__ __forceinline__ void produce(const void* const (&src)[NIN], long nvec) {
+    const long nchunks = (nvec + kChunkVecs - 1) / kChunkVecs;
+    for (long ch = blockIdx.x; ch < nchunks; ch += gridDim.x) {
+      mbar_wait(&empty[s], ph ^ 1);
+      if (elect_one_sync()) {
+        const long v0 = ch * kChunkVecs;
+        const long left = nvec - v0;
+        const uint32_t bytes = (uint32_t)(left < kChunkVecs ? left : kChunkVecs) * 16u;
+        mbar_expect_tx(&full[s], bytes * NIN);
+#pragma unroll
+        for (int j = 0; j < NIN; ++j)
+          bulk_g2s(ring + (uint32_t)((s * NIN + j) * kChunkBytes), reinterpret_cast<const char*>(src[j]) + v0 * 16, bytes, &full[s]);
+      }
+      __syncwarp();
+      advance();
+    }
+  }
+  // consumer side: address of vector v of input j in the current stage
+  __device__ __forceinline__ uint32_t at(int j, int v) const { return ring + (uint32_t)((s * NIN + j) * kChunkBytes + v * 16); }
+  __device__ __forceinline__ void wait_full() { mbar_wait(&full[s], ph); }
+  __device__ __forceinline__ void release() {     // whole consumer warp
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) mbar_arrive(&empty[s]);
+    advance();
+  }
+};
+
+template <typename T> __device__ __forceinline__ void dec(const uint4& u, float (&f)[Vec<T>::N]) { decode_vec<T>(u, f); }
+template <typename T>
+__device__ __forceinline__ uint4 enc(const float (&f)[Vec<T>::N]) {
+  if constexpr (sizeof(T) == 4) return make_uint4(__float_as_uint(f[0]), __float_as_uint(f[1]), __float_as_uint(f[2]), __float_as_uint(f[3]));
+  else return pack8<T>(f);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kThr, 2) k_fwd_stats(const T* __restrict__ x, long M, int C, float* __restrict__ partial,
+                                                      unsigned* counter, Comm comm, float* running_mean, float* running_var,
+                                                      float momentum, float eps, float* __restrict__ save_mean,
+                                                      float* __restrict__ save_invstd) {
+  constexpr int V = Vec<T>::N;
+  extern __shared__ __align__(128) uint8_t dsm[];
+  Pipe<1> pipe;
+  pipe.init(dsm);
+  const long nvec = M * C / V;
+  const int tid = threadIdx.x, cg = C / V;
+  float s[V], q[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) s[j] = q[j] = 0.f;
+  if (tid >= kCons) {
+    const void* src[1] = {x};
+    pipe.produce(src, nvec);
+  } else {
+    const long nchunks = (nvec + kChunkVecs - 1) / kChunkVecs;
+    for (long ch = blockIdx.x; ch < nchunks; ch += gridDim.x) {
+      pipe.wait_full();
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const int v = tid + kCons * u;
+        if (ch * kChunkVecs + v < nvec) {
+          float f[V];
+          dec<T>(lds128(pipe.at(0, v)), f);
+#pragma unroll
+          for (int j = 0; j < V; ++j) { s[j] += f[j]; q[j] = fmaf(f[j], f[j], q[j]); }
+        }
+      }
+      pipe.release();
+    }
+  }
+  __syncthreads();                                   // every chunk consumed: the ring is free for the fold
+  float* smem = reinterpret_cast<float*>(dsm);
+  block_fold<V>(smem, s, q, C, cg, kCons / cg, partial);
+  finish_fwd_stats(smem, partial, counter, comm, C, M, running_mean, running_var, momentum, eps, save_mean, save_invstd);
+}
+
+template <typename T, bool HAS_RES>
+__global__ void __launch_bounds__(kThr, 2) k_fwd_apply(const T* __restrict__ x, const T* __restrict__ res, T* __restrict__ y,
+                                                      long nvec, int C, const float* __restrict__ mean,
+                                                      const float* __restrict__ stat2, const float* __restrict__ gamma,
+                                                      const float* __restrict__ beta, int relu, int eval, float eps) {
+  constexpr int V = Vec<T>::N;
+  constexpr int NIN = HAS_RES ? 2 : 1;
+  extern __shared__ __align__(128) uint8_t dsm[];
+  Pipe<NIN> pipe;
+  pipe.init(dsm);
+  const int tid = threadIdx.x, cg = C / V;
+  if (tid >= kCons) {
+    if constexpr (HAS_RES) { const void* src[2] = {x, res}; pipe.produce(src, nvec); }
+    else { const void* src[1] = {x}; pipe.produce(src, nvec); }
+    return;
+  }
+  float sc[V], sh[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) {
+    const int c = (tid % cg) * V + j;
+    const float inv = eval ? rsqrtf(stat2[c] + eps) : stat2[c];
+    sc[j] = gamma[c] * inv;
+    sh[j] = beta[c] - mean[c] * sc[j];
+  }
+  uint4* out = reinterpret_cast<uint4*>(y);
+  const long nchunks = (nvec + kChunkVecs - 1) / kChunkVecs;
+  for (long ch = blockIdx.x; ch < nchunks; ch += gridDim.x) {
+    pipe.wait_full();
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const int v = tid + kCons * u;
+      const long gi = ch * kChunkVecs + v;
+      if (gi < nvec) {
+        float f[V];
+        dec<T>(lds128(pipe.at(0, v)), f);
+#pragma unroll
+        for (int j = 0; j < V; ++j) f[j] = fmaf(f[j], sc[j], sh[j]);
+        if constexpr (HAS_RES) {
+          float r[V];
+          dec<T>(lds128(pipe.at(1, v)), r);
+#pragma unroll
+          for (int j = 0; j < V; ++j) f[j] += r[j];
+        }
+        if (relu) {
+#pragma unroll
+          for (int j = 0; j < V; ++j) f[j] = fmaxf(f[j], 0.f);
+        }
+        out[gi] = enc<T>(f);
+      }
+    }
+    pipe.release();
+  }
+}
+
+// HAS_Y: the ReLU mask comes from the forward output y (a residual entered the ReLU); otherwise, with relu,
+// it is recomputed from x.
+template <typename T, bool HAS_Y>
+__global__ void __launch_bounds__(kThr, 2) k_bwd_reduce(const T* __restrict__ dy, const T* __restrict__ y, const T* __restrict__ x,
+                                                       long M, int C, const float* __restrict__ mean,
+                                                       const float* __restrict__ invstd, const float* __restrict__ gamma,
+                                                       const float* __restrict__ beta, int relu, float* __restrict__ partial,
+                                                       unsigned* counter, Comm comm, float* __restrict__ dgamma,
+                                                       float* __restrict__ dbeta, float* __restrict__ out_k, long count) {
+  constexpr int V = Vec<T>::N;
+  constexpr int NIN = HAS_Y ? 3 : 2;
+  extern __shared__ __align__(128) uint8_t dsm[];
+  Pipe<NIN> pipe;
+  pipe.init(dsm);
+  const long nvec = M * C / V;
+  const int tid = threadIdx.x, cg = C / V;
+  float s[V], q[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) s[j] = q[j] = 0.f;
+  if (tid >= kCons) {
+    if constexpr (HAS_Y) { const void* src[3] = {dy, x, y}; pipe.produce(src, nvec); }
+    else { const void* src[2] = {dy, x}; pipe.produce(src, nvec); }
+  } else {
+    const bool remask = relu && !HAS_Y;
+    float mu[V], sc[V], sh[V];
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      const int c = (tid % cg) * V + j;
+      mu[j] = mean[c];
+      sc[j] = remask ? gamma[c] * invstd[c] : 0.f;
+      sh[j] = remask ? beta[c] - mean[c] * sc[j] : 0.f;
+    }
+    const long nchunks = (nvec + kChunkVecs - 1) / kChunkVecs;
+    for (long ch = blockIdx.x; ch < nchunks; ch += gridDim.x) {
+      pipe.wait_full();
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const int v = tid + kCons * u;
+        if (ch * kChunkVecs + v < nvec) {
+          float g[V], xv[V];
+          dec<T>(lds128(pipe.at(0, v)), g);
+          dec<T>(lds128(pipe.at(1, v)), xv);
+          if constexpr (HAS_Y) {
+            float yv[V];
+            dec<T>(lds128(pipe.at(2, v)), yv);
+#pragma unroll
+            for (int j = 0; j < V; ++j) g[j] = yv[j] > 0.f ? g[j] : 0.f;
+          } else if (remask) {
+#pragma unroll
+            for (int j = 0; j < V; ++j) g[j] = fmaf(xv[j], sc[j], sh[j]) > 0.f ? g[j] : 0.f;
+          }
+#pragma unroll
+          for (int j = 0; j < V; ++j) { s[j] += g[j]; q[j] = fmaf(g[j], xv[j] - mu[j], q[j]); }
+        }
+      }
+      pipe.release();
+    }
+  }
+  __syncthreads();
+  float* smem = reinterpret_cast<float*>(dsm);
+  block_fold<V>(smem, s, q, C, cg, kCons / cg, partial);
+  finish_bwd_reduce(smem, partial, counter, comm, C, count, invstd, dgamma, dbeta, out_k);
+}
+
+// dx = a*g + b*x + c per channel with a = invstd*gamma, b = -k2*a, c = (mean*k2 - k1)*a (the expanded form of
+// (g - k1 - (x - mean)*k2) * a: three constants and two FMAs per element).
+template <typename T, bool HAS_Y, bool HAS_DRES>
+__global__ void __launch_bounds__(kThr, 2) k_bwd_apply(const T* __restrict__ dy, const T* __restrict__ y, const T* __restrict__ x,
+                                                      T* __restrict__ dx, T* __restrict__ dres, long nvec, int C,
+                                                      const float* __restrict__ mean, const float* __restrict__ invstd,
+                                                      const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                      const float* __restrict__ k, int relu) {
+  constexpr int V = Vec<T>::N;
+  constexpr int NIN = HAS_Y ? 3 : 2;
+  extern __shared__ __align__(128) uint8_t dsm[];
+  Pipe<NIN> pipe;
+  pipe.init(dsm);
+  const int tid = threadIdx.x, cg = C / V;
+  if (tid >= kCons) {
+    if constexpr (HAS_Y) { const void* src[3] = {dy, x, y}; pipe.produce(src, nvec); }
+    else { const void* src[2] = {dy, x}; pipe.produce(src, nvec); }
+    return;
+  }
+  const bool remask = relu && !HAS_Y;
+  float fa[V], fb[V], fc[V], fs[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) {
+    const int c = (tid % cg) * V + j;
+    const float a = gamma[c] * invstd[c];
+    fa[j] = a;
+    fb[j] = -k[C + c] * a;
+    fc[j] = (mean[c] * k[C + c] - k[c]) * a;
+    fs[j] = beta[c] - mean[c] * a;
+  }
+  uint4* odx = reinterpret_cast<uint4*>(dx);
+  uint4* odr = reinterpret_cast<uint4*>(dres);
+  const long nchunks = (nvec + kChunkVecs - 1) / kChunkVecs;
+  for (long ch = blockIdx.x; ch < nchunks; ch += gridDim.x) {
+    pipe.wait_full();
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const int v = tid + kCons * u;
+      const long gi = ch * kChunkVecs + v;
+      if (gi < nvec) {
+        float g[V], xv[V];
+        dec<T>(lds128(pipe.at(0, v)), g);
+        dec<T>(lds128(pipe.at(1, v)), xv);
+        if constexpr (HAS_Y) {
+          float yv[V];
+          dec<T>(lds128(pipe.at(2, v)), yv);
+#pragma unroll
+          for (int j = 0; j < V; ++j) g[j] = yv[j] > 0.f ? g[j] : 0.f;
+        } else if (remask) {
+#pragma unroll
+          for (int j = 0; j < V; ++j) g[j] = fmaf(xv[j], fa[j], fs[j]) > 0.f ? g[j] : 0.f;
+        }
+        if constexpr (HAS_DRES) odr[gi] = enc<T>(g);
+#pragma unroll
+        for (int j = 0; j < V; ++j) g[j] = fmaf(g[j], fa[j], fmaf(xv[j], fb[j], fc[j]));
+        odx[gi] = enc<T>(g);
+      }
+    }
+    pipe.release();
+  }
+}
+
+// Shapes the streaming kernels take: every thread must keep one channel group (C/V divides 256) and the
+// bulk copies need 16-byte aligned sources.
+template <typename T> bool ok(int C, std::initializer_list<const void*> ptrs) {
+  const int V = Vec<T>::N;
+  if (C % V) return false;
+  const int cg = C / V;
+  if (cg < 1 || cg > kCons || (cg & (cg - 1)) != 0) return false;
+  if (2 * C * (kCons / cg) * (int)sizeof(float) > kRingBytes || 2 * C * 8 + kThr * 8 > kRingBytes) return false;
+  for (const void* p : ptrs) if (reinterpret_cast<uintptr_t>(p) & 15) return false;
+  return true;
+}
+int grid_for(long nvec) {
+  static int sms = 0;
+  if (sms == 0) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); if (sms <= 0) sms = 148; }
+  const long nchunks = (nvec + kChunkVecs - 1) / kChunkVecs;
+  long g = 2L * sms;
+  if (g > PDT_BN_MAX_BLOCKS) g = PDT_BN_MAX_BLOCKS;
+  return (int)(nchunks < g ? (nchunks < 1 ? 1 : nchunks) : g);
+}
+template <typename K> cudaError_t optin(K kern) {
+  return cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+}
+}  // namespace sp
 
 // ---- BatchNorm + ReLU + MaxPool fused (the ResNet stem tail) -----------------------------------------
 // The stem's BN output is the largest activation of the network (112 x 112 x 64 per image) and exists
@@ -687,6 +1035,51 @@ int apply_blocks(long nvec) {
   return (int)nb;
 }
 
+template <typename T>
+int bwd_reduce_stream(const void* dy, const void* y, const void* x, long M, int C, const float* mean, const float* invstd,
+                      const float* gamma, const float* beta, int relu, float* partial, unsigned* counter, const PdtCommDesc* comm,
+                      float* dgamma, float* dbeta, float* out_k, long count, cudaStream_t stream) {
+  const int grid = sp::grid_for(M * C / Vec<T>::N);
+  if (relu && y != nullptr) {
+    PDT_CHECK(sp::optin(sp::k_bwd_reduce<T, true>));
+    sp::k_bwd_reduce<T, true><<<grid, sp::kThr, sp::kSmemBytes, stream>>>(
+        reinterpret_cast<const T*>(dy), reinterpret_cast<const T*>(y), reinterpret_cast<const T*>(x), M, C, mean, invstd, gamma,
+        beta, relu, partial, counter, make_comm(comm), dgamma, dbeta, out_k, count);
+  } else {
+    PDT_CHECK(sp::optin(sp::k_bwd_reduce<T, false>));
+    sp::k_bwd_reduce<T, false><<<grid, sp::kThr, sp::kSmemBytes, stream>>>(
+        reinterpret_cast<const T*>(dy), nullptr, reinterpret_cast<const T*>(x), M, C, mean, invstd, gamma, beta, relu, partial,
+        counter, make_comm(comm), dgamma, dbeta, out_k, count);
+  }
+  return (int)cudaGetLastError();
+}
+
+template <typename T, bool HY, bool HD>
+int bwd_apply_launch(const void* dy, const void* y, const void* x, void* dx, void* dres, long nvec, int C, const float* mean,
+                     const float* invstd, const float* gamma, const float* beta, const float* k, int relu, cudaStream_t stream) {
+  PDT_CHECK(sp::optin(sp::k_bwd_apply<T, HY, HD>));
+  sp::k_bwd_apply<T, HY, HD><<<sp::grid_for(nvec), sp::kThr, sp::kSmemBytes, stream>>>(
+      reinterpret_cast<const T*>(dy), reinterpret_cast<const T*>(y), reinterpret_cast<const T*>(x), reinterpret_cast<T*>(dx),
+      reinterpret_cast<T*>(dres), nvec, C, mean, invstd, gamma, beta, k, relu);
+  return (int)cudaGetLastError();
+}
+template <typename T>
+int bwd_apply_stream(const void* dy, const void* y, const void* x, void* dx, void* dres, long nvec, int C, const float* mean,
+                     const float* invstd, const float* gamma, const float* beta, const float* k, int relu, cudaStream_t stream) {
+  const bool hy = relu && y != nullptr, hd = dres != nullptr;
+  if (hy && hd) return bwd_apply_launch<T, true, true>(dy, y, x, dx, dres, nvec, C, mean, invstd, gamma, beta, k, relu, stream);
+  if (hy) return bwd_apply_launch<T, true, false>(dy, y, x, dx, dres, nvec, C, mean, invstd, gamma, beta, k, relu, stream);
+  if (hd) return bwd_apply_launch<T, false, true>(dy, y, x, dx, dres, nvec, C, mean, invstd, gamma, beta, k, relu, stream);
+  return bwd_apply_launch<T, false, false>(dy, y, x, dx, dres, nvec, C, mean, invstd, gamma, beta, k, relu, stream);
+}
+
+// PDT_BN_STREAM=0 falls back to the register-staged kernels (A/B measurements, debugging).
+bool stream_enabled() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("PDT_BN_STREAM"); v = (e != nullptr && e[0] == '0') ? 0 : 1; }
+  return v == 1;
+}
+
 }  // namespace
 
 extern "C" {
@@ -739,6 +1132,9 @@ int pdt_bn_pool_bwd_reduce(const void* dpool, const void* ypool, const void* xma
   const long Mp = (long)N * g.Ho * g.Wo;
   BNP_DISPATCH(dtype, {
     if (!shape_ok<T>(C)) return PDT_E_UNSUPPORTED;
+    if (stream_enabled() && sp::ok<T>(C, {dpool, ypool, xmax})) return bwd_reduce_stream<T>(dpool, ypool, xmax, Mp, C, mean, invstd, gamma, beta, 1,
+                                                                                            partial, counter, comm, dgamma, dbeta, out_k,
+                                                                                            (long)N * H * W, stream);
     k_bn_bwd_reduce<T><<<stats_blocks(Mp, C, 8), kThreads, 0, stream>>>(
         reinterpret_cast<const T*>(dpool), reinterpret_cast<const T*>(ypool), reinterpret_cast<const T*>(xmax), Mp, C, mean,
         invstd, gamma, beta, 1, partial, counter, make_comm(comm), dgamma, dbeta, out_k, (long)N * H * W);
@@ -781,6 +1177,13 @@ int pdt_bn_fwd_stats(const void* x, long M, int C, int dtype, void* scratch, con
   float* partial = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + 256);
   BN_DISPATCH(dtype, {
     if (!shape_ok<T>(C)) return PDT_E_UNSUPPORTED;
+    if (stream_enabled() && sp::ok<T>(C, {x})) {
+      PDT_CHECK(sp::optin(sp::k_fwd_stats<T>));
+      sp::k_fwd_stats<T><<<sp::grid_for(M * C / Vec<T>::N), sp::kThr, sp::kSmemBytes, stream>>>(
+          reinterpret_cast<const T*>(x), M, C, partial, counter, make_comm(comm), running_mean, running_var, momentum, eps,
+          save_mean, save_invstd);
+      return (int)cudaGetLastError();
+    }
     k_bn_fwd_stats<T><<<stats_blocks(M, C, Vec<T>::N), kThreads, 0, stream>>>(
         reinterpret_cast<const T*>(x), M, C, partial, counter, make_comm(comm), running_mean, running_var, momentum, eps,
         save_mean, save_invstd);
@@ -845,6 +1248,19 @@ int pdt_bn_fwd_apply(const void* x, const void* res, void* y, long M, int C, int
   BN_DISPATCH(dtype, {
     if (C % Vec<T>::N) return PDT_E_UNSUPPORTED;
     const long nvec = M * C / Vec<T>::N;
+    if (stream_enabled() && sp::ok<T>(C, {x, res, y})) {
+      if (res != nullptr) {
+        PDT_CHECK(sp::optin(sp::k_fwd_apply<T, true>));
+        sp::k_fwd_apply<T, true><<<sp::grid_for(nvec), sp::kThr, sp::kSmemBytes, stream>>>(
+            reinterpret_cast<const T*>(x), reinterpret_cast<const T*>(res), reinterpret_cast<T*>(y), nvec, C, mean, stat2,
+            gamma, beta, relu, eval, eps);
+      } else {
+        PDT_CHECK(sp::optin(sp::k_fwd_apply<T, false>));
+        sp::k_fwd_apply<T, false><<<sp::grid_for(nvec), sp::kThr, sp::kSmemBytes, stream>>>(
+            reinterpret_cast<const T*>(x), nullptr, reinterpret_cast<T*>(y), nvec, C, mean, stat2, gamma, beta, relu, eval, eps);
+      }
+      return (int)cudaGetLastError();
+    }
     k_bn_fwd_apply<T><<<apply_blocks(nvec), kThreads, 2 * C * sizeof(float), stream>>>(
         reinterpret_cast<const T*>(x), reinterpret_cast<const T*>(res), reinterpret_cast<T*>(y), nvec, C, mean, stat2,
         gamma, beta, relu, eval, eps);
@@ -859,6 +1275,8 @@ int pdt_bn_bwd_reduce(const void* dy, const void* y, const void* x, long M, int 
   float* partial = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + 256);
   BN_DISPATCH(dtype, {
     if (!shape_ok<T>(C)) return PDT_E_UNSUPPORTED;
+    if (stream_enabled() && sp::ok<T>(C, {dy, y, x})) return bwd_reduce_stream<T>(dy, y, x, M, C, mean, invstd, gamma, beta, relu,
+                                                                                  partial, counter, comm, dgamma, dbeta, out_k, M, stream);
     k_bn_bwd_reduce<T><<<stats_blocks(M, C, Vec<T>::N), kThreads, 0, stream>>>(
         reinterpret_cast<const T*>(dy), reinterpret_cast<const T*>(y), reinterpret_cast<const T*>(x), M, C, mean, invstd,
         gamma, beta, relu, partial, counter, make_comm(comm), dgamma, dbeta, out_k, M);
@@ -872,6 +1290,8 @@ int pdt_bn_bwd_apply(const void* dy, const void* y, const void* x, void* dx, voi
   BN_DISPATCH(dtype, {
     if (C % Vec<T>::N) return PDT_E_UNSUPPORTED;
     const long nvec = M * C / Vec<T>::N;
+    if (stream_enabled() && sp::ok<T>(C, {dy, y, x, dx, dres}))
+      return bwd_apply_stream<T>(dy, y, x, dx, dres, nvec, C, mean, invstd, gamma, beta, k, relu, stream);
     k_bn_bwd_apply<T><<<apply_blocks(nvec), kThreads, 5 * C * sizeof(float), stream>>>(
         reinterpret_cast<const T*>(dy), reinterpret_cast<const T*>(y), reinterpret_cast<const T*>(x),
         reinterpret_cast<T*>(dx), reinterpret_cast<T*>(dres), nvec, C, mean, invstd, gamma, beta, k, relu);

@@ -61,8 +61,15 @@ template <int BN, bool RES> struct HCfg {
   static constexpr int kAccCols = BN == 64 ? 256 : 2 * BN;      // columns reserved per accumulator buffer (chains * BN, padded)
   static constexpr int kTmemCols = 2 * kAccCols;                // 512
   // per epilogue warp: column accumulators [2][kStatMaxK] + a 32 x 33 float transpose tile
-  static constexpr int kStatBytes = kEpiWarps * (2 * kStatMaxK + 32 * 33) * 4;
-  static constexpr int kSmemBytes = kAStages * kAStage + kBStages * kBTile + 1024 + 256 + kStatBytes;
+  // N=64: the output tile is staged in shared memory (dense rows, 128B-swizzled, double-buffered) and leaves
+  // through one TMA store, and the statistics stay in registers, so the transpose tiles are not used.
+  static constexpr bool kTmaStore = BN == 64;
+  static constexpr int kOutBuf = 128 * 128;
+  static constexpr int kOutBytes = kTmaStore ? 2 * kOutBuf : 0;
+  static constexpr int kStatStride = kTmaStore ? 2 * kStatMaxK : 2 * kStatMaxK + 32 * 33;   // floats per epilogue warp
+  static constexpr int kStatBytes = kEpiWarps * kStatStride * 4;
+  static constexpr int kSmemBytes = kAStages * kAStage + kBStages * kBTile + kOutBytes + 1024 + 256 + kStatBytes;
+  static_assert(kSmemBytes <= 232448, "over the 227 KB shared-memory limit of sm_100");
 };
 
 __device__ __forceinline__ void tma_load_4d(void* smem, const CUtensorMap* m, uint64_t* bar, int c, int w, int h, int n) {
@@ -76,6 +83,17 @@ __device__ __forceinline__ void tma_load_4d(void* smem, const CUtensorMap* m, ui
 __device__ __forceinline__ void tma_prefetch_4d(const CUtensorMap* m, int c, int w, int h, int n) {
   asm volatile("cp.async.bulk.prefetch.tensor.4d.L2.global [%0, {%1, %2, %3, %4}];"
                ::"l"(reinterpret_cast<uint64_t>(m)), "r"(c), "r"(w), "r"(h), "r"(n) : "memory");
+}
+
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* m, uint32_t smem_src, int c, int w, int h, int n) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(m)), "r"(smem_src), "r"(c), "r"(w), "r"(h), "r"(n) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+template <int N> __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void sts128(uint32_t addr, const uint4& v) {
+  asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
 __device__ __forceinline__ void warp_transpose_reduce(float (&a)[32], int lane) {
@@ -94,30 +112,32 @@ __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 256;"
 
 template <int BN, bool RES, typename T>
 __global__ void __launch_bounds__(kThreads, 1)
-k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW, T* __restrict__ out,
-               const HaloGeom g, const BnStats bs) {
+k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
+               const __grid_constant__ CUtensorMap tmY, T* __restrict__ out, const HaloGeom g, const BnStats bs) {
   using C = HCfg<BN, RES>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smA = smem;
   uint8_t* smB = smem + C::kAStages * C::kAStage;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smB + C::kBStages * C::kBTile);
+  uint8_t* smO = smB + C::kBStages * C::kBTile;          // output staging (1024-byte aligned: every ring above is n KB)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smO + C::kOutBytes);
   uint64_t* afull = bars;                        // [kAStages]
   uint64_t* aempty = afull + C::kAStages;
   uint64_t* bfull = aempty + C::kAStages;        // [kBStages] (RES: only bfull[0] is used, once)
   uint64_t* bempty = bfull + C::kBStages;
   uint64_t* tfull = bempty + C::kBStages;
   uint64_t* tempty = tfull + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  uint64_t* sfree = tempty + 2;                  // [2] output staging buffer has been read by its TMA store
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sfree + 2);
   float* s_stat = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-  if (warp == 0 && lane == 0) { prefetch_tmap(&tmX); prefetch_tmap(&tmW); }
+  if (warp == 0 && lane == 0) { prefetch_tmap(&tmX); prefetch_tmap(&tmW); if (C::kTmaStore) prefetch_tmap(&tmY); }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < C::kAStages; ++i) { mbar_init(&afull[i], 1); mbar_init(&aempty[i], 1); }
     for (int i = 0; i < C::kBStages; ++i) { mbar_init(&bfull[i], 1); mbar_init(&bempty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], kEpiWarps); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], kEpiWarps); mbar_init(&sfree[i], 1); }
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc(tmem_slot, C::kTmemCols);
@@ -248,8 +268,103 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
     const int half = (warp - 4) >> 2;             // which half of the BN columns it drains
     const int ew = warp - 4;
     constexpr int NCH = C::kChains;
+    float* my_stat = s_stat + ew * C::kStatStride;
+    const int m = quarter * 32 + lane;            // output slot inside the tile (padded coordinates)
+    const int ti = m / g.Wp, tj = m - ti * g.Wp;
+    // tile -> (image, first row) advanced incrementally: no division inside the loop
+    int n = (int)blockIdx.x / g.tiles_per_image, tr = (int)blockIdx.x - n * g.tiles_per_image;
+    const int dn = (int)gridDim.x / g.tiles_per_image, dr = (int)gridDim.x - dn * g.tiles_per_image;
+    if constexpr (C::kTmaStore) {
+      // ---- N = 64: statistics in registers, output through a swizzled staging tile + one TMA store ----
+      // Each lane owns one accumulator row, so it keeps its own partial sums for its 32 columns across all
+      // tiles (2 instructions per element, no transposes); lanes are combined once at the end of the kernel.
+      float cs[32], cq[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) cs[j] = cq[j] = 0.f;
+      const bool slot_ok = ti < g.TR && tj >= 1 && tj <= g.W;
+      const int drow = ti * g.W + (tj - 1);                      // row of this slot in the dense staging tile
+      const uint32_t so = smem_u32(smO);
+      const int c0 = half * 32;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x, ++it) {
+        const int h0 = tr * g.TR;
+        const int acc = it & 1;
+        const uint32_t acc_phase = (it >> 1) & 1;
+        const bool valid = slot_ok && (h0 + ti) < g.H;
+        const uint32_t taddr = tmem_base + acc * C::kAccCols + ((uint32_t)(quarter * 32) << 16);
+        mbar_wait(&tfull[acc], acc_phase);
+        tc_fence_after();
+        uint32_t v[32];
+        {
+          uint32_t v2[32], v3[32];
+          tmem_ld32(taddr + c0, v);
+          tmem_ld32(taddr + BN + c0, v2);
+          if (NCH == 3) tmem_ld32(taddr + 2 * BN + c0, v3);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            float t = __uint_as_float(v[j]) + __uint_as_float(v2[j]);
+            if (NCH == 3) t += __uint_as_float(v3[j]);
+            v[j] = __float_as_uint(t);
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty[acc]);                // accumulators are in registers: hand the buffer back
+        uint4 o[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          o[j].x = Cvt<T>::pack2(__uint_as_float(v[8 * j + 0]), __uint_as_float(v[8 * j + 1]));
+          o[j].y = Cvt<T>::pack2(__uint_as_float(v[8 * j + 2]), __uint_as_float(v[8 * j + 3]));
+          o[j].z = Cvt<T>::pack2(__uint_as_float(v[8 * j + 4]), __uint_as_float(v[8 * j + 5]));
+          o[j].w = Cvt<T>::pack2(__uint_as_float(v[8 * j + 6]), __uint_as_float(v[8 * j + 7]));
+        }
+        const int ob = it & 1;
+        mbar_wait(&sfree[ob], ((it >> 1) & 1) ^ 1);              // the store that last used this buffer has read it
+        if (slot_ok) {
+          const uint32_t row = so + (uint32_t)(ob * C::kOutBuf + drow * 128);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) sts128(row + (uint32_t)((((half * 4 + j) ^ (drow & 7))) << 4), o[j]);
+        }
+        fence_proxy_async();
+        epi_bar_sync();
+        if (threadIdx.x == 128) {
+          tma_store_4d(&tmY, so + (uint32_t)(ob * C::kOutBuf), 0, 0, h0, n);   // rows past H are clipped by TMA
+          bulk_commit();
+          bulk_wait_read<1>();                                   // the previous tile's store no longer needs its buffer
+          if (it >= 1) mbar_arrive(&sfree[ob ^ 1]);
+        }
+        if (bs.enabled && valid) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const float t = __uint_as_float(v[j]);
+            cs[j] += t;
+            cq[j] = fmaf(t, t, cq[j]);
+          }
+        }
+        tr += dr; n += dn;
+        if (tr >= g.tiles_per_image) { tr -= g.tiles_per_image; ++n; }
+      }
+      if (threadIdx.x == 128) bulk_wait_all<0>();
+      if (bs.enabled) {
+        for (int i = lane; i < 2 * kStatMaxK; i += 32) my_stat[i] = 0.f;
+        __syncwarp();
+        float ks = 0.f, kq = 0.f;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          float a = cs[j], b = cq[j];
+#pragma unroll
+          for (int sft = 16; sft >= 1; sft >>= 1) {
+            a += __shfl_xor_sync(0xffffffffu, a, sft);
+            b += __shfl_xor_sync(0xffffffffu, b, sft);
+          }
+          if (lane == j) { ks = a; kq = b; }
+        }
+        my_stat[c0 + lane] = ks;
+        my_stat[kStatMaxK + c0 + lane] = kq;
+      }
+    } else {
     constexpr int NIT = BN / 64;                  // 32-column groups per warp
-    float* my_stat = s_stat + ew * (2 * kStatMaxK + 32 * 33);
     const uint32_t tp_a = smem_u32(my_stat + 2 * kStatMaxK);   // 32 x 33 transpose tile
     if (bs.enabled) {
       for (int i = lane; i < 2 * kStatMaxK; i += 32) my_stat[i] = 0.f;
@@ -258,12 +373,9 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
     float cs[NIT], cq[NIT];                       // this lane's column (c0 + lane): running sum / sum of squares
 #pragma unroll
     for (int q = 0; q < NIT; ++q) cs[q] = cq[q] = 0.f;
-    const int m = quarter * 32 + lane;            // output slot inside the tile (padded coordinates)
-    const int ti = m / g.Wp, tj = m - ti * g.Wp;
     int it = 0;
     for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x, ++it) {
-      const int n = tile / g.tiles_per_image;
-      const int h0 = (tile - n * g.tiles_per_image) * g.TR;
+      const int h0 = tr * g.TR;
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1;
       const bool valid = ti < g.TR && tj >= 1 && tj <= g.W && (h0 + ti) < g.H;
@@ -328,6 +440,8 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
           cq[q] += q0 + q1;
         }
       }
+      tr += dr; n += dn;
+      if (tr >= g.tiles_per_image) { tr -= g.tiles_per_image; ++n; }
     }
     if (bs.enabled) {
 #pragma unroll
@@ -336,6 +450,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         my_stat[kStatMaxK + half * (BN / 2) + q * 32 + lane] = cq[q];
       }
     }
+    }   // !kTmaStore
     if (bs.enabled) {
       __shared__ int s_last;
       const int te = threadIdx.x - 128;            // 0..255 among the epilogue threads
@@ -345,7 +460,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         const int which = i / K, c = i - which * K;
         float t = 0.f;
 #pragma unroll
-        for (int w8 = 0; w8 < kEpiWarps; ++w8) t += s_stat[w8 * (2 * kStatMaxK + 32 * 33) + which * kStatMaxK + c];
+        for (int w8 = 0; w8 < kEpiWarps; ++w8) t += s_stat[w8 * C::kStatStride + which * kStatMaxK + c];
         bs.partial[(size_t)blockIdx.x * 2 * K + i] = t;
       }
       __threadfence();
@@ -396,7 +511,7 @@ EncodeTiledFn g_enc = nullptr;
 
 template <int BN, bool RES>
 int launch(const void* x, const void* w, void* y, int dtype, const HaloGeom& g, const BnStats& bs, const CUtensorMap& tmX,
-           const CUtensorMap& tmW, cudaStream_t stream) {
+           const CUtensorMap& tmW, const CUtensorMap& tmY, cudaStream_t stream) {
   using C = HCfg<BN, RES>;
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
@@ -405,11 +520,11 @@ int launch(const void* x, const void* w, void* y, int dtype, const HaloGeom& g, 
   if (dtype == PDT_FP16) {
     auto kern = k_conv3x3_halo<BN, RES, __half>;
     PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
-    kern<<<grid, kThreads, C::kSmemBytes, stream>>>(tmX, tmW, reinterpret_cast<__half*>(y), g, bs);
+    kern<<<grid, kThreads, C::kSmemBytes, stream>>>(tmX, tmW, tmY, reinterpret_cast<__half*>(y), g, bs);
   } else {
     auto kern = k_conv3x3_halo<BN, RES, __nv_bfloat16>;
     PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
-    kern<<<grid, kThreads, C::kSmemBytes, stream>>>(tmX, tmW, reinterpret_cast<__nv_bfloat16*>(y), g, bs);
+    kern<<<grid, kThreads, C::kSmemBytes, stream>>>(tmX, tmW, tmY, reinterpret_cast<__nv_bfloat16*>(y), g, bs);
   }
   return (int)cudaGetLastError();
 }
@@ -470,6 +585,16 @@ int pdt_conv3x3_halo(const void* x, const void* w, void* y, int dtype, int N, in
               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
       return 10004;
   }
+  CUtensorMap tmY;
+  {   // output as (K, W, H, N); one box = the TR x W x 64-channel tile the N=64 kernel stages in shared memory
+    cuuint64_t dims[4] = {(cuuint64_t)K, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+    cuuint64_t strides[3] = {(cuuint64_t)K * 2, (cuuint64_t)W * K * 2, (cuuint64_t)H * W * K * 2};
+    cuuint32_t box[4] = {64, (cuuint32_t)W, (cuuint32_t)g.TR, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    if (g_enc(&tmY, dt, 4, y, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return 10005;
+  }
   BnStats bs;
   bs.enabled = scratch != nullptr;
   bs.counter = reinterpret_cast<unsigned*>(scratch);
@@ -479,10 +604,10 @@ int pdt_conv3x3_halo(const void* x, const void* w, void* y, int dtype, int N, in
   bs.momentum = momentum; bs.eps = eps;
   bs.count = (long long)N * H * W;
   if (K == 64) {
-    if (resident) return launch<64, true>(x, w, y, dtype, g, bs, tmX, tmW, stream);
-    return launch<64, false>(x, w, y, dtype, g, bs, tmX, tmW, stream);
+    if (resident) return launch<64, true>(x, w, y, dtype, g, bs, tmX, tmW, tmY, stream);
+    return launch<64, false>(x, w, y, dtype, g, bs, tmX, tmW, tmY, stream);
   }
-  return launch<128, false>(x, w, y, dtype, g, bs, tmX, tmW, stream);
+  return launch<128, false>(x, w, y, dtype, g, bs, tmX, tmW, tmY, stream);
 }
 
 }  // extern "C"
