@@ -196,6 +196,12 @@ int pdt_conv3x3_halo_supported(int dtype, int N, int H, int W, int C, int K);
 int pdt_conv3x3_halo(const void* x, const void* w, void* y, int dtype, int N, int H, int W, int C, int K, void* scratch,
                      float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
                      float* save_invstd, cudaStream_t stream);
+/* 3x3 / stride 1 / pad 1 weight gradient for 64 -> 64 channels with the same patch reuse (one x patch + one
+ * dy tile per work item, nine row-shifted views, two taps per M=128 instruction); dw [64][3][3][64] fp32 is
+ * accumulated into.  pdt_conv_wgrad routes eligible shapes here (PDT_WGRAD_HALO=0 disables). */
+int pdt_conv3x3_wgrad_halo_supported(int dtype, int N, int H, int W, int C, int K);
+int pdt_conv3x3_wgrad_halo(const void* x, const void* dy, float* dw, int dtype, int N, int H, int W, int C, int K,
+                           cudaStream_t stream);
 /* Weight gradient (cudnnConvolutionBackwardFilter): dw [K][R][S][C] fp32 += sum over pixels; split-K over
  * the pixel dimension with red.global.add, so zero dw first.  C % 64 == 0, K % 64 == 0. */
 int pdt_conv_wgrad(const void* x, const void* dy, float* dw, int dtype, int N, int H, int W, int C, int K, int R, int S,

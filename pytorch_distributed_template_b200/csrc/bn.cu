@@ -96,34 +96,7 @@ __device__ __forceinline__ bool take_last_ticket(unsigned* counter) {
 
 // Last block: tot[i] = sum_b partial[b][i] in fp64, left in smem as double[n2].
 __device__ __forceinline__ void fold_partials(double* tot, const float* __restrict__ partial, int nb, int n2) {
-  const int tid = threadIdx.x;
-  __syncthreads();
-  if (n2 >= (int)blockDim.x) {
-    for (int i = tid; i < n2; i += blockDim.x) {
-      double s = 0.0;
-#pragma unroll 8
-      for (int b = 0; b < nb; ++b) s += (double)__ldcg(partial + (size_t)b * n2 + i);
-      tot[i] = s;
-    }
-    __syncthreads();
-  } else {
-    const int rg = blockDim.x / n2, col = tid % n2, g = tid / n2;
-    double s = 0.0;
-    if (g < rg) {
-#pragma unroll 8
-      for (int b = g; b < nb; b += rg) s += (double)__ldcg(partial + (size_t)b * n2 + col);
-    }
-    // stage [rg][n2] doubles: rg*n2 <= blockDim.x = 512 doubles
-    double* stage = tot + n2;
-    if (g < rg) stage[g * n2 + col] = s;
-    __syncthreads();
-    if (tid < n2) {
-      double t = 0.0;
-      for (int gg = 0; gg < rg; ++gg) t += stage[gg * n2 + tid];
-      tot[tid] = t;
-    }
-    __syncthreads();
-  }
+  fold_rows_f64(tot, partial, nb, n2, (int)threadIdx.x, (int)blockDim.x, [] { __syncthreads(); });
 }
 
 // Cross-rank sum of tot[0..n) (+ the count) through the peers' scratch slots; one block per rank.

@@ -102,4 +102,50 @@ __device__ __forceinline__ uint4 ldg_stream(const void* p) {   // read-once data
   return r;
 }
 
+// Last-block fold of per-block partial rows in fp64: tot[i] = sum_b partial[b * n2 + i], i < n2 (n2 % 4 == 0,
+// rows 16-byte aligned).  Run by threads tid = 0..nthr-1 that meet at sync(); `tot` needs n2 + 4*nthr doubles.
+// One thread owns FOUR adjacent columns (16-byte loads) and keeps 16 rows in flight: the rows were just
+// written by other SMs, so every load is an L2 round trip, and the scalar one-row-at-a-time version of this
+// loop cost 40-60 us per launch for 1024-column rows (more than the streaming part of small layers).
+template <class Sync>
+__device__ __forceinline__ void fold_rows_f64(double* tot, const float* __restrict__ partial, int nb, int n2, int tid, int nthr,
+                                              Sync sync) {
+  const int nc4 = n2 >> 2;
+  sync();
+  if (nc4 >= nthr) {
+    for (int c4 = tid; c4 < nc4; c4 += nthr) {
+      double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+#pragma unroll 16
+      for (int b = 0; b < nb; ++b) {
+        const float4 v = __ldcg(reinterpret_cast<const float4*>(partial + (size_t)b * n2) + c4);
+        a0 += (double)v.x; a1 += (double)v.y; a2 += (double)v.z; a3 += (double)v.w;
+      }
+      tot[4 * c4 + 0] = a0; tot[4 * c4 + 1] = a1; tot[4 * c4 + 2] = a2; tot[4 * c4 + 3] = a3;
+    }
+    sync();
+  } else {
+    const int rg = nthr / nc4, c4 = tid % nc4, g = tid / nc4;
+    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+    if (g < rg) {
+#pragma unroll 16
+      for (int b = g; b < nb; b += rg) {
+        const float4 v = __ldcg(reinterpret_cast<const float4*>(partial + (size_t)b * n2) + c4);
+        a0 += (double)v.x; a1 += (double)v.y; a2 += (double)v.z; a3 += (double)v.w;
+      }
+    }
+    double* stage = tot + n2;                 // [rg][n2], rg * n2 <= 4 * nthr
+    if (g < rg) {
+      double* sp = stage + (size_t)g * n2 + 4 * c4;
+      sp[0] = a0; sp[1] = a1; sp[2] = a2; sp[3] = a3;
+    }
+    sync();
+    for (int i = tid; i < n2; i += nthr) {
+      double t = 0.0;
+      for (int gg = 0; gg < rg; ++gg) t += stage[(size_t)gg * n2 + i];
+      tot[i] = t;
+    }
+    sync();
+  }
+}
+
 }  // namespace pdt

@@ -17,6 +17,7 @@
 // activation, the flipped/transposed filter as the weight, pad' = R-1-pad).
 // Replaces cudnnConvolutionForward / BackwardData (reference: every nn.Conv2d of
 // torchvision resnet18, /root/reference/distributed.py:137,246,262).
+#include <cstdlib>
 #include <type_traits>
 #include "tc.cuh"
 #include "../../include/pdt_b200.h"
@@ -298,14 +299,7 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
       if (s_last) {
         __threadfence();
         double* tot = reinterpret_cast<double*>(s_stat);      // 2K doubles <= 8 KB of the 16 KB region
-        epi_bar_sync();
-        for (int i = te; i < 2 * K; i += 128) {
-          double t = 0.0;
-#pragma unroll 4
-          for (int b = 0; b < (int)gridDim.x; ++b) t += (double)__ldcg(bs.partial + (size_t)b * 2 * K + i);
-          tot[i] = t;
-        }
-        epi_bar_sync();
+        fold_rows_f64(tot, bs.partial, (int)gridDim.x, 2 * K, te, 128, [] { epi_bar_sync(); });
         const double n = (double)g.M;
         for (int c = te; c < K; c += 128) {
           const double mean = tot[c] / n;
@@ -688,6 +682,12 @@ int dispatch_fprop(const void* x, const void* w, void* y, const float* bias, int
   return launch_fprop<256>(x, w, y, bias, dtype, g, bs, stream);
 }
 
+bool wgrad_halo_enabled() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("PDT_WGRAD_HALO"); v = (e != nullptr && e[0] == '0') ? 0 : 1; }
+  return v == 1;
+}
+
 }  // namespace
 
 extern "C" {
@@ -699,6 +699,8 @@ int pdt_conv_wgrad(const void* x, const void* dy, float* dw, int dtype, int N, i
   const int es = esize_of(dtype), BKP = 4 * (32 / es);
   if (C % (128 / es) || K % 8 || R < 1 || S < 1 || stride < 1 || pad < 0) return PDT_E_UNSUPPORTED;
   if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(dw)) & 15) return PDT_E_UNSUPPORTED;
+  if (R == 3 && S == 3 && stride == 1 && pad == 1 && wgrad_halo_enabled() && pdt_conv3x3_wgrad_halo_supported(dtype, N, H, W, C, K))
+    return pdt_conv3x3_wgrad_halo(x, dy, dw, dtype, N, H, W, C, K, stream);
   int e = load_driver_fns();
   if (e) return e;
   WgradGeom wg;

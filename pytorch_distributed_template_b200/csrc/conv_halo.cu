@@ -67,7 +67,7 @@ template <int BN, bool RES> struct HCfg {
   static constexpr int kOutBuf = 128 * 128;
   static constexpr int kOutBytes = kTmaStore ? 2 * kOutBuf : 0;
   static constexpr int kStatStride = kTmaStore ? 2 * kStatMaxK : 2 * kStatMaxK + 32 * 33;   // floats per epilogue warp
-  static constexpr int kStatBytes = kEpiWarps * kStatStride * 4;
+  static constexpr int kStatBytes = kTmaStore ? 16384 : kEpiWarps * kStatStride * 4;   // also the fp64 fold scratch of the last CTA
   static constexpr int kSmemBytes = kAStages * kAStage + kBStages * kBTile + kOutBytes + 1024 + 256 + kStatBytes;
   static_assert(kSmemBytes <= 232448, "over the 227 KB shared-memory limit of sm_100");
 };
@@ -470,14 +470,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
       if (s_last) {
         __threadfence();
         double* tot = reinterpret_cast<double*>(s_stat);
-        epi_bar_sync();
-        for (int i = te; i < 2 * K; i += 256) {
-          double t = 0.0;
-#pragma unroll 4
-          for (int b = 0; b < (int)gridDim.x; ++b) t += (double)__ldcg(bs.partial + (size_t)b * 2 * K + i);
-          tot[i] = t;
-        }
-        epi_bar_sync();
+        fold_rows_f64(tot, bs.partial, (int)gridDim.x, 2 * K, te, 256, [] { epi_bar_sync(); });
         const double cnt = (double)bs.count;
         for (int c = te; c < K; c += 256) {
           const double mean = tot[c] / cnt;
@@ -501,6 +494,144 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
   if (warp == 2) {
     tc_fence_after();
     tmem_dealloc(tmem_base, C::kTmemCols);
+  }
+}
+
+// ---- 3x3 / stride 1 / pad 1 weight gradient, 64 -> 64 channels, with the same patch reuse -------------
+// dW[k][r][s][c] = sum over pixels of dy[pixel][k] * x[pixel + (r-1, s-1)][c].  The generic split-K kernel
+// (conv.cu) fetches one im2col tile of x per tap and 64-pixel step, which makes it L2-bound by ~3x on the
+// 56x56 layers.  Here a work item is again TR image rows in padded coordinates: ONE x patch (with halo) and
+// ONE dy tile (its two border columns and out-of-image rows zero-filled by TMA) are loaded per item, and the
+// nine taps are nine row-shifted MN-major views of the patch.  Two taps share one M=128 instruction: the
+// descriptor's leading-dimension offset (distance between the two 64-channel halves of A) is set to the
+// distance between the two taps' views (one pixel = 128 B, or W+2-2 pixels across a filter-row boundary), so
+// D rows 0-63 / 64-127 are dW of tap a / tap b.  Five accumulators (taps 01 23 45 67 8x) live in TMEM for the
+// whole kernel; each CTA adds them into dw once at the end (red.global.add.f32, dw must start zeroed).
+struct WHCfg {
+  static constexpr int kStages = 4;
+  static constexpr int kAStage = 32768;          // 1 KB front slack + patch + tail (rows read past the patch are zero)
+  static constexpr int kBStage = 16384;          // 128 pixel slots x 64 channels
+  static constexpr int kSmemBytes = kStages * (kAStage + kBStage) + 1024 + 128;
+};
+
+template <typename T>
+__global__ void __launch_bounds__(128, 1)
+k_wgrad3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmDY, float* __restrict__ dw,
+                const HaloGeom g) {
+  using W = WHCfg;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smA = smem;
+  uint8_t* smB = smem + W::kStages * W::kAStage;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smB + W::kStages * W::kBStage);
+  uint64_t* empty = full + W::kStages;
+  uint64_t* done = empty + W::kStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done + 1);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) { prefetch_tmap(&tmX); prefetch_tmap(&tmDY); }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < W::kStages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    mbar_init(done, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, 512);
+  // Slots the TMA boxes never write (tail of every stage) are read by the last k-step / the largest shifts:
+  // they must hold zeros, not whatever the previous kernel left in shared memory (0 * NaN = NaN).
+  {
+    uint4* z = reinterpret_cast<uint4*>(smem);
+    const int n16 = W::kStages * (W::kAStage + W::kBStage) / 16;
+    for (int i = threadIdx.x; i < n16; i += blockDim.x) z[i] = make_uint4(0, 0, 0, 0);
+  }
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int slots = g.TR * g.Wp;
+  const int ksteps = (slots + 15) >> 4;
+  const uint32_t dy_bytes = (uint32_t)slots * 128u;
+
+  if (warp == 0) {
+    int stage = 0;
+    uint32_t phase = 0;
+    int n = (int)blockIdx.x / g.tiles_per_image, tr = (int)blockIdx.x - n * g.tiles_per_image;
+    const int dn = (int)gridDim.x / g.tiles_per_image, dr = (int)gridDim.x - dn * g.tiles_per_image;
+    for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x) {
+      const int h0 = tr * g.TR;
+      mbar_wait(&empty[stage], phase ^ 1);
+      if (elect_one_sync()) {
+        mbar_expect_tx(&full[stage], g.patch_bytes + dy_bytes);
+        tma_load_4d(smA + stage * W::kAStage + 1024, &tmX, &full[stage], 0, -1, h0 - 1, n);
+        tma_load_4d(smB + stage * W::kBStage, &tmDY, &full[stage], 0, -1, h0, n);
+      }
+      __syncwarp();
+      if (++stage == W::kStages) { stage = 0; phase ^= 1; }
+      tr += dr; n += dn;
+      if (tr >= g.tiles_per_image) { tr -= g.tiles_per_image; ++n; }
+    }
+  } else if (warp == 1) {
+    constexpr uint32_t idesc = make_idesc(128, 64, std::is_same<T, __nv_bfloat16>::value ? 1 : 0, 1, 1);
+    // pair j = taps (2j, 2j+1); view of tap t starts (t/3)*Wp + t%3 - 1 pixel rows into the patch
+    uint64_t tmpl[5];
+#pragma unroll
+    for (int j = 0; j < 5; ++j) {
+      const int ta = 2 * j, tb = 2 * j + 1;
+      const int sa = (ta / 3) * g.Wp + ta % 3 - 1, sb = (tb / 3) * g.Wp + tb % 3 - 1;
+      tmpl[j] = make_sw128_desc(0, 1024, (uint32_t)(sb - sa) * 128u) + (uint64_t)(int64_t)(sa * 8);
+    }
+    int stage = 0;
+    uint32_t phase = 0;
+    bool first = true;
+    for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x) {
+      mbar_wait(&full[stage], phase);
+      tc_fence_after();
+      const uint64_t a_addr = (uint64_t)((smem_u32(smA + stage * W::kAStage + 1024) & 0x3FFFF) >> 4);
+      const uint64_t db0 = make_sw128_desc(smem_u32(smB + stage * W::kBStage), 1024, 1024);
+      if (elect_one_sync()) {
+        for (int ks = 0; ks < ksteps; ++ks) {
+          const uint32_t accum = (first && ks == 0) ? 0u : 1u;
+#pragma unroll
+          for (int j = 0; j < 5; ++j)
+            umma_f16(tmem_base + j * 64, tmpl[j] + a_addr + (uint64_t)(ks * 128), db0 + (uint64_t)(ks * 128), idesc, accum);
+        }
+        umma_commit(&empty[stage]);
+      }
+      __syncwarp();
+      first = false;
+      if (++stage == W::kStages) { stage = 0; phase ^= 1; }
+    }
+    if (elect_one_sync()) umma_commit(done);
+    __syncwarp();
+  }
+  __syncwarp();
+  // ---- drain: every warp adds its 32 accumulator rows (lane = tap-half * 64 + input channel) into dw ----
+  if (blockIdx.x < g.num_tiles) {
+    mbar_wait(done, 0);
+    tc_fence_after();
+    const int m = warp * 32 + lane;
+    const int hi = m >> 6, c = m & 63;
+#pragma unroll 1
+    for (int j = 0; j < 5; ++j) {
+      const int tap = 2 * j + hi;
+#pragma unroll 1
+      for (int c0 = 0; c0 < 64; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + j * 64 + c0, v);
+        tmem_ld_wait();
+        if (tap < 9) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i)       // dw[k][tap][c], k = c0 + i: the 32 lanes of a warp cover 32 consecutive c
+            atomicAdd(dw + ((size_t)(c0 + i) * 9 + tap) * 64 + c, __uint_as_float(v[i]));
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
   }
 }
 
@@ -608,6 +739,69 @@ int pdt_conv3x3_halo(const void* x, const void* w, void* y, int dtype, int N, in
     return launch<64, false>(x, w, y, dtype, g, bs, tmX, tmW, tmY, stream);
   }
   return launch<128, false>(x, w, y, dtype, g, bs, tmX, tmW, tmY, stream);
+}
+
+// 1 if pdt_conv3x3_wgrad_halo serves this weight gradient (3x3, stride 1, pad 1 implied).
+int pdt_conv3x3_wgrad_halo_supported(int dtype, int N, int H, int W, int C, int K) {
+  if (dtype != PDT_BF16 && dtype != PDT_FP16) return 0;
+  if (C != 64 || K != 64 || W + 2 > 58 || W < 6 || H < 1 || N < 1) return 0;
+  return 1;
+}
+
+// x: [N][H][W][64], dy: [N][H][W][64] (bf16/fp16), dw: [64][3][3][64] fp32, ACCUMULATED into (zero it first).
+int pdt_conv3x3_wgrad_halo(const void* x, const void* dy, float* dw, int dtype, int N, int H, int W, int C, int K,
+                           cudaStream_t stream) {
+  if (!pdt_conv3x3_wgrad_halo_supported(dtype, N, H, W, C, K)) return PDT_E_UNSUPPORTED;
+  if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(dw)) & 15) return PDT_E_UNSUPPORTED;
+  if (g_enc == nullptr) {
+    cudaDriverEntryPointQueryResult q;
+    void* fn = nullptr;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q);
+    if (e != cudaSuccess || fn == nullptr) return (int)(e != cudaSuccess ? e : cudaErrorUnknown);
+    g_enc = reinterpret_cast<EncodeTiledFn>(fn);
+  }
+  HaloGeom g;
+  g.N = N; g.H = H; g.W = W; g.C = C; g.K = K;
+  g.Wp = W + 2;
+  g.TR = 128 / g.Wp;
+  if (g.TR > H) g.TR = H;
+  g.tiles_per_image = (H + g.TR - 1) / g.TR;
+  g.num_tiles = N * g.tiles_per_image;
+  g.c_chunks = 1;
+  g.patch_bytes = (uint32_t)((g.TR + 2) * g.Wp * 128);
+  // the largest view (phantom tap 9, paired with tap 8) starts 2*Wp + 2 rows in and is read for 128 rows
+  if (1024 + (2 * g.Wp + 2 + 128) * 128 > WHCfg::kAStage || g.patch_bytes + 1024 > (uint32_t)WHCfg::kAStage) return PDT_E_UNSUPPORTED;
+  const CUtensorMapDataType dt = dtype == PDT_FP16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  CUtensorMap tmX, tmDY;
+  cuuint64_t dims[4] = {64, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t strides[3] = {128, (cuuint64_t)W * 128, (cuuint64_t)H * W * 128};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  {
+    cuuint32_t box[4] = {64, (cuuint32_t)g.Wp, (cuuint32_t)(g.TR + 2), 1};
+    if (g_enc(&tmX, dt, 4, const_cast<void*>(x), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return 10006;
+  }
+  {
+    cuuint32_t box[4] = {64, (cuuint32_t)g.Wp, (cuuint32_t)g.TR, 1};
+    if (g_enc(&tmDY, dt, 4, const_cast<void*>(dy), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return 10007;
+  }
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int grid = g.num_tiles < sms ? g.num_tiles : sms;
+  if (dtype == PDT_FP16) {
+    auto kern = k_wgrad3x3_halo<__half>;
+    PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, WHCfg::kSmemBytes));
+    kern<<<grid, 128, WHCfg::kSmemBytes, stream>>>(tmX, tmDY, dw, g);
+  } else {
+    auto kern = k_wgrad3x3_halo<__nv_bfloat16>;
+    PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, WHCfg::kSmemBytes));
+    kern<<<grid, 128, WHCfg::kSmemBytes, stream>>>(tmX, tmDY, dw, g);
+  }
+  return (int)cudaGetLastError();
 }
 
 }  // extern "C"

@@ -20,6 +20,7 @@ from . import conv as _conv
 
 _vp, _i, _ll = _native._vp, _native._i, _native.ctypes.c_longlong
 _native.register("pdt_conv_fprop", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp])
+_native.register("pdt_conv3x3_wgrad_halo_supported", [_i, _i, _i, _i, _i, _i])
 _native.register("pdt_conv_wgrad", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp])
 _native.register("pdt_conv_fprop_ex", [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _ll, _ll, _ll, _i, _i, _i, _i,
                                        _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp])

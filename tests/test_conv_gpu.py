@@ -214,3 +214,26 @@ def test_conv3x3_halo_kernel(native_lib, dtype, cin, cout, hw, batch):
     assert torch.allclose(mean, ref.mean((0, 2, 3)), rtol=1e-2, atol=2e-3)
     assert torch.allclose(invstd, torch.rsqrt(ref.var((0, 2, 3), unbiased=False) + 1e-5), rtol=1e-2, atol=1e-3)
     assert torch.allclose(rm, 0.1 * ref.mean((0, 2, 3)), rtol=1e-2, atol=2e-3)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("hw,batch", [(56, 5), (20, 3), (31, 2), (8, 150), (55, 1)])
+def test_conv3x3_wgrad_halo_kernel(native_lib, dtype, hw, batch):
+    """64->64 3x3 weight gradient with patch reuse (row-shifted MN-major views, tap pairs through the
+    descriptor's leading-dimension offset) vs autograd; includes partial last tiles (31, 55 rows)."""
+    from pytorch_distributed_template_b200 import ops
+    from pytorch_distributed_template_b200.ops import conv_native, _native
+    torch.backends.cudnn.allow_tf32 = False
+    torch.manual_seed(21)
+    dev = torch.device("cuda", 0)
+    assert _native.lib().pdt_conv3x3_wgrad_halo_supported(_native.dtype_code(dtype), batch, hw, hw, 64, 64) == 1
+    x = torch.randn(batch, 64, hw, hw, device=dev).to(dtype).contiguous(memory_format=torch.channels_last)
+    dy = (torch.randn(batch, 64, hw, hw, device=dev) / 8).to(dtype).contiguous(memory_format=torch.channels_last)
+    dw = conv_native.wgrad(x, dy, (64, 64, 3, 3), 1, 1)
+    wf = torch.zeros(64, 64, 3, 3, device=dev, requires_grad=True)
+    F.conv2d(x.float(), wf, None, 1, 1).backward(dy.float())
+    err = (dw - wf.grad).abs().max().item()
+    assert err <= 2e-3 * max(1.0, wf.grad.abs().max().item()), (err, wf.grad.abs().max().item())
+    # accumulates into its destination
+    dw2 = conv_native.wgrad(x, dy, (64, 64, 3, 3), 1, 1, out=dw.clone())
+    assert (dw2 - 2 * wf.grad).abs().max().item() <= 4e-3 * max(1.0, wf.grad.abs().max().item())
