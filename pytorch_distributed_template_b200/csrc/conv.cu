@@ -102,7 +102,13 @@ __device__ __forceinline__ void warp_transpose_reduce(float (&a)[32], int lane) 
 }
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 
-template <int BN, typename T>
+// CL > 1: launched as clusters of CL CTAs that work on CL consecutive M tiles of the SAME N tile in lock
+// step.  The filter tile of a k-block is then fetched once per cluster: CTA r loads rows [r*BN/CL, (r+1)*BN/CL)
+// and TMA multicasts them into every CTA's ring slot.  The 256-wide layers were bound by the L2's total
+// delivery rate (~42 B/clk per SM when all SMs stream): per k-block a CTA pulled 16 KB of activations and
+// 32 KB of filter for 512 clk of MMA; with CL = 4 it is 16 + 8 KB.  A slot may be refilled only when every
+// CTA of the cluster has consumed it, so the MMA warp's commit arrives on the `empty` barrier of all CL CTAs.
+template <int BN, typename T, int CL>
 __global__ void __launch_bounds__(kThreads, 1)
 k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, T* __restrict__ out,
              const float* __restrict__ bias, const ConvGeom g, const BnStats bs) {
@@ -120,7 +126,12 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   float* s_stat = reinterpret_cast<float*>(smem + C::kStages * C::kStageBytes + 256);   // [4][2][kStatMaxK]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int num_tiles = g.m_tiles * g.n_tiles;
+  // work unit = CL consecutive M tiles x one N tile; this CTA takes M tile (unit / n_tiles) * CL + rank.
+  // M tiles past the end (last group) run on zero-filled activations and store nothing.
+  const int crank = CL > 1 ? (int)cluster_ctarank() : 0;
+  const int cluster_id = (int)blockIdx.x / CL, num_clusters = (int)gridDim.x / CL;
+  const int num_units = ((g.m_tiles + CL - 1) / CL) * g.n_tiles;
+  constexpr uint16_t kMask = (uint16_t)((1u << CL) - 1);
   constexpr int BK = Elem<T>::kRow;
   const int c_chunks = (g.C + BK - 1) / BK;
   const int k_blocks = g.R * g.S * c_chunks;
@@ -130,13 +141,14 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     prefetch_tmap(&tmB);
   }
   if (warp == 1 && lane == 0) {
-    for (int i = 0; i < C::kStages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    for (int i = 0; i < C::kStages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], CL); }
     for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 4); }
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc(tmem_slot, C::kTmemCols);
   tc_fence_before();
   __syncthreads();
+  if (CL > 1) cluster_sync_all();        // peers' barriers are initialised before anything is multicast at them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -145,8 +157,8 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int mt = tile / g.n_tiles, nt = tile % g.n_tiles;
+      for (int unit = cluster_id; unit < num_units; unit += num_clusters) {
+        const int mt = (unit / g.n_tiles) * CL + crank, nt = unit % g.n_tiles;
         const int m0 = mt * BM;
         const int img = m0 / (g.P * g.Q);
         const int rem = m0 - img * (g.P * g.Q);
@@ -159,7 +171,12 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
               if (elect_one_sync()) {
                 mbar_expect_tx(&full[stage], C::kStageBytes);
                 tma_load_im2col_4d(smA + stage * C::kStageBytesA, &tmA, &full[stage], cc * BK, cw, ch, img, (uint16_t)(s * g.dil_w), (uint16_t)r);
-                tma_load_2d(smB + stage * C::kStageBytesB, &tmB, &full[stage], (r * g.S + s) * g.C + cc * BK, nt * BN);
+                if (CL == 1) {
+                  tma_load_2d(smB + stage * C::kStageBytesB, &tmB, &full[stage], (r * g.S + s) * g.C + cc * BK, nt * BN);
+                } else {
+                  tma_load_2d_mc(smB + stage * C::kStageBytesB + crank * (C::kStageBytesB / CL), &tmB, &full[stage],
+                                 (r * g.S + s) * g.C + cc * BK, nt * BN + crank * (BN / CL), kMask);
+                }
               }
               __syncwarp();
               if (++stage == C::kStages) { stage = 0; phase ^= 1; }
@@ -173,7 +190,7 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      for (int unit = cluster_id; unit < num_units; unit += num_clusters, ++it) {
         const int acc = it & 1;
         const uint32_t acc_phase = (it >> 1) & 1;
         mbar_wait(&tempty[acc], acc_phase ^ 1);
@@ -188,7 +205,7 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
 #pragma unroll
             for (int k = 0; k < 4; ++k)   // +32 bytes along K per UMMA_K step: +2 in the (addr >> 4) field
               umma<T>(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
-            umma_commit(&empty[stage]);
+            if (CL == 1) umma_commit(&empty[stage]); else umma_commit_mc(&empty[stage], kMask);
           }
           __syncwarp();
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
@@ -208,8 +225,8 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
       __syncwarp();
     }
     int it = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-      const int mt = tile / g.n_tiles, nt = tile % g.n_tiles;
+    for (int unit = cluster_id; unit < num_units; unit += num_clusters, ++it) {
+      const int mt = (unit / g.n_tiles) * CL + crank, nt = unit % g.n_tiles;
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1;
       mbar_wait(&tfull[acc], acc_phase);
@@ -320,6 +337,7 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
 
   tc_fence_before();
   __syncthreads();
+  if (CL > 1) cluster_sync_all();        // no CTA leaves while a peer may still multicast into it or arrive on its barriers
   if (warp == 2) {
     tc_fence_after();
     tmem_dealloc(tmem_base, C::kTmemCols);
@@ -544,11 +562,71 @@ CUtensorMapDataType tm_dtype(int dtype) {
 }
 int esize_of(int dtype) { return dtype == PDT_FP32 ? 4 : 2; }
 
+// Cluster size for the forward / data-gradient kernel: multicast pays when the filter tile is at least as
+// large as the activation tile (BN >= 128) and there are enough M tiles to keep every cluster busy.
+// PDT_CONV_CLUSTER=1|2|4 overrides.
+int cluster_size_for(int BN, const ConvGeom& g) {
+  static int env = -1;
+  if (env < 0) { const char* e = getenv("PDT_CONV_CLUSTER"); env = e ? atoi(e) : 0; }
+  int cl = env > 0 ? env : 2;     // 4 measured the same per launch but only 33 clusters of 4 are co-resident (132 of 148 SMs)
+  if (BN < 128 || (cl != 2 && cl != 4)) return 1;
+  if (g.m_tiles < 148) return 1;                            // fewer M tiles than SMs: keep every SM on a tile of its own
+  return cl;
+}
+
+template <int BN, typename T, int CL>
+int launch_igemm_cl(const CUtensorMap& tmA, const CUtensorMap& tmB, void* y, const float* bias, const ConvGeom& g, const BnStats& bs,
+                    int sms, cudaStream_t stream) {
+  using C = Cfg<BN>;
+  auto kern = k_conv_igemm<BN, T, CL>;
+  PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+  const int units = ((g.m_tiles + CL - 1) / CL) * g.n_tiles;
+  cudaLaunchConfig_t cfg = {};
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = C::kSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  int nattr = 0;
+  int clusters = sms / CL;
+  if (CL > 1) {
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CL; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    nattr = 1;
+    // a persistent kernel must fit in ONE wave: ask how many clusters can be resident (GPC boundaries make
+    // this less than SMs / CL on some parts) instead of assuming
+    static int cached[3] = {-1, -1, -1};
+    int& mc = cached[CL == 2 ? 1 : 2];
+    if (mc < 0) {
+      cfg.gridDim = dim3(sms / CL * CL);
+      cfg.attrs = attr; cfg.numAttrs = nattr;
+      int n = 0;
+      if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess || n < 1) { cudaGetLastError(); n = sms / CL / 2; }
+      mc = n;
+    }
+    if (clusters > mc) clusters = mc;
+  }
+  if (clusters > units) clusters = units;
+  cfg.gridDim = dim3(clusters * CL);
+  cfg.attrs = attr; cfg.numAttrs = nattr;
+  PDT_CHECK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, reinterpret_cast<T*>(y), bias, g, bs));
+  return (int)cudaGetLastError();
+}
+
+template <int BN, typename T>
+int launch_igemm(const CUtensorMap& tmA, const CUtensorMap& tmB, void* y, const float* bias, const ConvGeom& g, const BnStats& bs, int cl,
+                 int sms, cudaStream_t stream) {
+  if constexpr (BN >= 128) {
+    if (cl == 4) return launch_igemm_cl<BN, T, 4>(tmA, tmB, y, bias, g, bs, sms, stream);
+    if (cl == 2) return launch_igemm_cl<BN, T, 2>(tmA, tmB, y, bias, g, bs, sms, stream);
+  }
+  return launch_igemm_cl<BN, T, 1>(tmA, tmB, y, bias, g, bs, sms, stream);
+}
+
 template <int BN>
 int launch_fprop(const void* x, const void* w, void* y, const float* bias, int dtype, const ConvGeom& g, const BnStats& bs,
                  cudaStream_t stream) {
-  using C = Cfg<BN>;
   CUtensorMap tmA, tmB;
+  const int cl = cluster_size_for(BN, g);
   {
     cuuint64_t dims[4] = {(cuuint64_t)g.Cx, (cuuint64_t)g.W, (cuuint64_t)g.H, (cuuint64_t)g.N};
     cuuint64_t strides[3] = {(cuuint64_t)g.x_sw, (cuuint64_t)g.x_sh, (cuuint64_t)g.x_sn};
@@ -570,7 +648,7 @@ int launch_fprop(const void* x, const void* w, void* y, const float* bias, int d
   {
     cuuint64_t dims[2] = {(cuuint64_t)g.R * g.S * g.C, (cuuint64_t)g.K};
     cuuint64_t strides[1] = {(cuuint64_t)g.R * g.S * g.C * esize_of(dtype)};
-    cuuint32_t box[2] = {(cuuint32_t)(128 / esize_of(dtype)), (cuuint32_t)BN};
+    cuuint32_t box[2] = {(cuuint32_t)(128 / esize_of(dtype)), (cuuint32_t)(BN / cl)};   // one CTA's slice of the filter tile
     cuuint32_t estr[2] = {1, 1};
     CUresult r = g_encode_tiled(&tmB, tm_dtype(dtype), 2, const_cast<void*>(w), dims, strides, box, estr,
                                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -580,22 +658,9 @@ int launch_fprop(const void* x, const void* w, void* y, const float* bias, int d
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  const int tiles = g.m_tiles * g.n_tiles;
-  const int grid = tiles < sms ? tiles : sms;
-  if (dtype == PDT_FP16) {
-    auto kern = k_conv_igemm<BN, __half>;
-    PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
-    kern<<<grid, kThreads, C::kSmemBytes, stream>>>(tmA, tmB, reinterpret_cast<__half*>(y), bias, g, bs);
-  } else if (dtype == PDT_FP32) {
-    auto kern = k_conv_igemm<BN, float>;
-    PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
-    kern<<<grid, kThreads, C::kSmemBytes, stream>>>(tmA, tmB, reinterpret_cast<float*>(y), bias, g, bs);
-  } else {
-    auto kern = k_conv_igemm<BN, __nv_bfloat16>;
-    PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
-    kern<<<grid, kThreads, C::kSmemBytes, stream>>>(tmA, tmB, reinterpret_cast<__nv_bfloat16*>(y), bias, g, bs);
-  }
-  return (int)cudaGetLastError();
+  if (dtype == PDT_FP16) return launch_igemm<BN, __half>(tmA, tmB, y, bias, g, bs, cl, sms, stream);
+  if (dtype == PDT_FP32) return launch_igemm<BN, float>(tmA, tmB, y, bias, g, bs, cl, sms, stream);
+  return launch_igemm<BN, __nv_bfloat16>(tmA, tmB, y, bias, g, bs, cl, sms, stream);
 }
 
 template <int BN>

@@ -13,6 +13,7 @@
 // Activation traffic per output drops ~5x; the filter-tap loop issues 36 tcgen05.mma per patch.
 // Same warp roles, TMEM double buffering and BatchNorm-statistics epilogue as conv.cu.  The data gradient
 // of these layers is the same kernel on dy with the flipped/transposed filter.
+#include <cstdlib>
 #include <type_traits>
 #include "tc.cuh"
 #include "../../include/pdt_b200.h"
@@ -110,7 +111,12 @@ __device__ __forceinline__ void warp_transpose_reduce(float (&a)[32], int lane) 
 }
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
-template <int BN, bool RES, typename T>
+// CL = 2: CTA pairs (a thread-block cluster) stream ONE copy of the filter taps between them: each CTA loads
+// half of a tap's rows and TMA multicasts it into both rings, which halves the L2 traffic of the layers whose
+// filter bank does not fit in shared memory (they were bound by it: 9 x 16 KB of taps per 23 KB patch).  A ring
+// slot is refilled only when both CTAs have consumed it, so the MMA commit arrives on both `bempty` barriers;
+// CTAs of a pair run the same number of tiles (the last one may be a phantom tile that stores nothing).
+template <int BN, bool RES, typename T, int CL>
 __global__ void __launch_bounds__(kThreads, 1)
 k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
                const __grid_constant__ CUtensorMap tmY, T* __restrict__ out, const HaloGeom g, const BnStats bs) {
@@ -132,17 +138,23 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
   float* s_stat = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  static_assert(CL == 1 || (!RES && !HCfg<BN, RES>::kTmaStore), "the multicast ring is for the streamed, direct-store variant");
+  const int crank = CL > 1 ? (int)cluster_ctarank() : 0;
+  constexpr uint16_t kMask = (uint16_t)((1u << CL) - 1);
+  // every CTA of a cluster runs the same number of iterations
+  const int tile_end = CL > 1 ? ((g.num_tiles + (int)gridDim.x - 1) / (int)gridDim.x) * (int)gridDim.x : g.num_tiles;
 
   if (warp == 0 && lane == 0) { prefetch_tmap(&tmX); prefetch_tmap(&tmW); if (C::kTmaStore) prefetch_tmap(&tmY); }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < C::kAStages; ++i) { mbar_init(&afull[i], 1); mbar_init(&aempty[i], 1); }
-    for (int i = 0; i < C::kBStages; ++i) { mbar_init(&bfull[i], 1); mbar_init(&bempty[i], 1); }
+    for (int i = 0; i < C::kBStages; ++i) { mbar_init(&bfull[i], 1); mbar_init(&bempty[i], CL); }
     for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], kEpiWarps); mbar_init(&sfree[i], 1); }
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc(tmem_slot, C::kTmemCols);
   tc_fence_before();
   __syncthreads();
+  if (CL > 1) cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -158,7 +170,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
       }
       int as = 0, bsg = 0;
       uint32_t aph = 0, bph = 0;
-      for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x) {
+      for (int tile = blockIdx.x; tile < tile_end; tile += gridDim.x) {
         const int n = tile / g.tiles_per_image;
         const int h0 = (tile - n * g.tiles_per_image) * g.TR;
         {   // L2 prefetch of the patch this CTA will want kPrefetchAhead tiles from now
@@ -184,7 +196,9 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
               mbar_wait(&bempty[bsg], bph ^ 1);
               if (elect_one_sync()) {
                 mbar_expect_tx(&bfull[bsg], C::kBTile);
-                tma_load_2d(smB + bsg * C::kBTile, &tmW, &bfull[bsg], tap * g.C + cc * 64, 0);
+                if (CL == 1) tma_load_2d(smB + bsg * C::kBTile, &tmW, &bfull[bsg], tap * g.C + cc * 64, 0);
+                else tma_load_2d_mc(smB + bsg * C::kBTile + crank * (C::kBTile / CL), &tmW, &bfull[bsg], tap * g.C + cc * 64,
+                                    crank * (BN / CL), kMask);
               }
               __syncwarp();
               if (++bsg == C::kBStages) { bsg = 0; bph ^= 1; }
@@ -210,7 +224,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
       if (RES) { mbar_wait(&bfull[0], 0); tc_fence_after(); }
       int as = 0, bsg = 0, it = 0;
       uint32_t aph = 0, bph = 0;
-      for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x, ++it) {
+      for (int tile = blockIdx.x; tile < tile_end; tile += gridDim.x, ++it) {
         const int acc = it & 1;
         const uint32_t acc_phase = (it >> 1) & 1;
         mbar_wait(&tempty[acc], acc_phase ^ 1);
@@ -249,7 +263,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
                   const int i = tap * 4 + k;
                   umma_f16(tmem_d + (i % NCH) * BN, da + 2 * k, db + 2 * k, idesc, i >= NCH ? 1u : later);
                 }
-                umma_commit(&bempty[bsg]);
+                if (CL == 1) umma_commit(&bempty[bsg]); else umma_commit_mc(&bempty[bsg], kMask);
                 if (tap == 8) umma_commit(&aempty[as]);
               }
               __syncwarp();
@@ -286,7 +300,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
       const uint32_t so = smem_u32(smO);
       const int c0 = half * 32;
       int it = 0;
-      for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x, ++it) {
+      for (int tile = blockIdx.x; tile < tile_end; tile += gridDim.x, ++it) {
         const int h0 = tr * g.TR;
         const int acc = it & 1;
         const uint32_t acc_phase = (it >> 1) & 1;
@@ -374,11 +388,11 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
 #pragma unroll
     for (int q = 0; q < NIT; ++q) cs[q] = cq[q] = 0.f;
     int it = 0;
-    for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x, ++it) {
+    for (int tile = blockIdx.x; tile < tile_end; tile += gridDim.x, ++it) {
       const int h0 = tr * g.TR;
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1;
-      const bool valid = ti < g.TR && tj >= 1 && tj <= g.W && (h0 + ti) < g.H;
+      const bool valid = ti < g.TR && tj >= 1 && tj <= g.W && (h0 + ti) < g.H && tile < g.num_tiles;
       T* orow = out + (((size_t)n * g.H + h0 + ti) * g.W + (tj - 1)) * g.K;
       const uint32_t taddr = tmem_base + acc * C::kAccCols + ((uint32_t)(quarter * 32) << 16);
       mbar_wait(&tfull[acc], acc_phase);
@@ -491,6 +505,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
 
   tc_fence_before();
   __syncthreads();
+  if (CL > 1) cluster_sync_all();
   if (warp == 2) {
     tc_fence_after();
     tmem_dealloc(tmem_base, C::kTmemCols);
@@ -640,24 +655,54 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 EncodeTiledFn g_enc = nullptr;
 
-template <int BN, bool RES>
-int launch(const void* x, const void* w, void* y, int dtype, const HaloGeom& g, const BnStats& bs, const CUtensorMap& tmX,
-           const CUtensorMap& tmW, const CUtensorMap& tmY, cudaStream_t stream) {
+template <int BN, bool RES, typename T, int CL>
+int launch_t(void* y, const HaloGeom& g, const BnStats& bs, const CUtensorMap& tmX, const CUtensorMap& tmW, const CUtensorMap& tmY,
+             cudaStream_t stream) {
   using C = HCfg<BN, RES>;
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  const int grid = g.num_tiles < sms ? g.num_tiles : sms;
-  if (dtype == PDT_FP16) {
-    auto kern = k_conv3x3_halo<BN, RES, __half>;
-    PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
-    kern<<<grid, kThreads, C::kSmemBytes, stream>>>(tmX, tmW, tmY, reinterpret_cast<__half*>(y), g, bs);
-  } else {
-    auto kern = k_conv3x3_halo<BN, RES, __nv_bfloat16>;
-    PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
-    kern<<<grid, kThreads, C::kSmemBytes, stream>>>(tmX, tmW, tmY, reinterpret_cast<__nv_bfloat16*>(y), g, bs);
+  auto kern = k_conv3x3_halo<BN, RES, T, CL>;
+  PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+  cudaLaunchConfig_t cfg = {};
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = C::kSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  int grid = g.num_tiles < sms ? g.num_tiles : sms;
+  if (CL > 1) {
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CL; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    static int max_clusters = -1;       // resident clusters of this kernel: the persistent grid must be one wave
+    if (max_clusters < 0) {
+      cfg.gridDim = dim3(sms / CL * CL);
+      int n = 0;
+      if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess || n < 1) { cudaGetLastError(); n = sms / CL / 2; }
+      max_clusters = n;
+    }
+    int clusters = sms / CL < max_clusters ? sms / CL : max_clusters;
+    grid = clusters * CL;
   }
+  cfg.gridDim = dim3(grid);
+  PDT_CHECK(cudaLaunchKernelEx(&cfg, kern, tmX, tmW, tmY, reinterpret_cast<T*>(y), g, bs));
   return (int)cudaGetLastError();
+}
+
+template <int BN, bool RES, int CL = 1>
+int launch(const void* x, const void* w, void* y, int dtype, const HaloGeom& g, const BnStats& bs, const CUtensorMap& tmX,
+           const CUtensorMap& tmW, const CUtensorMap& tmY, cudaStream_t stream) {
+  (void)x; (void)w;
+  if (dtype == PDT_FP16) return launch_t<BN, RES, __half, CL>(y, g, bs, tmX, tmW, tmY, stream);
+  return launch_t<BN, RES, __nv_bfloat16, CL>(y, g, bs, tmX, tmW, tmY, stream);
+}
+
+// Filter-tap multicast between CTA pairs for the streamed 128-wide variant (PDT_CONV_CLUSTER=1 disables).
+int halo_cluster(const HaloGeom& g, int sms) {
+  static int env = -1;
+  if (env < 0) { const char* e = getenv("PDT_CONV_CLUSTER"); env = e ? atoi(e) : 0; }
+  if (env == 1) return 1;
+  return g.num_tiles >= 2 * sms ? 2 : 1;
 }
 
 }  // namespace
@@ -696,6 +741,9 @@ int pdt_conv3x3_halo(const void* x, const void* w, void* y, int dtype, int N, in
   g.patch_bytes = (uint32_t)((g.TR + 2) * g.Wp * 128);
   if (1024 + (128 + 2 * g.Wp + 2) * 128 > 32768 || g.patch_bytes + 1024 > 32768) return PDT_E_UNSUPPORTED;
   const bool resident = (C == 64 && K == 64);
+  int sms_q = 148;
+  { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms_q, cudaDevAttrMultiProcessorCount, dev); }
+  const int cl = (K == 128) ? halo_cluster(g, sms_q) : 1;
   const CUtensorMapDataType dt = dtype == PDT_FP16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
   CUtensorMap tmX, tmW;
   {
@@ -710,7 +758,7 @@ int pdt_conv3x3_halo(const void* x, const void* w, void* y, int dtype, int N, in
   {
     cuuint64_t dims[2] = {(cuuint64_t)9 * C, (cuuint64_t)K};
     cuuint64_t strides[1] = {(cuuint64_t)9 * C * 2};
-    cuuint32_t box[2] = {64, (cuuint32_t)K};
+    cuuint32_t box[2] = {64, (cuuint32_t)(K / cl)};     // with CTA pairs each CTA loads (and multicasts) half of a tap's rows
     cuuint32_t estr[2] = {1, 1};
     if (g_enc(&tmW, dt, 2, const_cast<void*>(w), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
@@ -738,6 +786,7 @@ int pdt_conv3x3_halo(const void* x, const void* w, void* y, int dtype, int N, in
     if (resident) return launch<64, true>(x, w, y, dtype, g, bs, tmX, tmW, tmY, stream);
     return launch<64, false>(x, w, y, dtype, g, bs, tmX, tmW, tmY, stream);
   }
+  if (cl == 2) return launch<128, false, 2>(x, w, y, dtype, g, bs, tmX, tmW, tmY, stream);
   return launch<128, false>(x, w, y, dtype, g, bs, tmX, tmW, tmY, stream);
 }
 

@@ -194,7 +194,8 @@ def test_tf32_model_paths(native_lib):
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
 @pytest.mark.parametrize("cin,cout,hw,batch", [(64, 64, 56, 5), (128, 128, 28, 7), (64, 64, 56, 1), (128, 128, 28, 1),
-                                               (64, 128, 28, 3), (128, 64, 56, 2), (64, 64, 20, 3)])
+                                               (64, 128, 28, 3), (128, 64, 56, 2), (64, 64, 20, 3),
+                                               (128, 128, 28, 43), (64, 128, 28, 44)])   # >= 2 tiles per SM: CTA-pair multicast
 def test_conv3x3_halo_kernel(native_lib, dtype, cin, cout, hw, batch):
     """Patch-reuse kernel (row-shifted smem descriptors) vs F.conv2d, with and without fused BN statistics."""
     from pytorch_distributed_template_b200.ops import conv_native
@@ -237,3 +238,27 @@ def test_conv3x3_wgrad_halo_kernel(native_lib, dtype, hw, batch):
     # accumulates into its destination
     dw2 = conv_native.wgrad(x, dy, (64, 64, 3, 3), 1, 1, out=dw.clone())
     assert (dw2 - 2 * wf.grad).abs().max().item() <= 4e-3 * max(1.0, wf.grad.abs().max().item())
+
+
+@pytest.mark.parametrize("cin,cout,hw,k,stride,pad,batch", [(256, 256, 14, 3, 1, 1, 100), (512, 512, 7, 3, 1, 1, 400),
+                                                             (128, 256, 28, 3, 2, 1, 101), (256, 512, 14, 1, 2, 0, 397)])
+def test_conv_cluster_multicast(native_lib, cin, cout, hw, k, stride, pad, batch):
+    """>= 148 M tiles: the 128/256-wide forward kernel runs as clusters of 4 CTAs that share one multicast
+    filter tile per k-block (includes M-tile counts that are not a multiple of 4: phantom tiles)."""
+    from pytorch_distributed_template_b200.ops import conv_native
+    torch.backends.cudnn.allow_tf32 = False
+    torch.manual_seed(31)
+    dev = torch.device("cuda", 0)
+    dtype = torch.bfloat16
+    x = torch.randn(batch, cin, hw, hw, device=dev).to(dtype).contiguous(memory_format=torch.channels_last)
+    w = (torch.randn(cout, cin, k, k, device=dev) / (cin * k * k) ** 0.5).to(dtype).contiguous(memory_format=torch.channels_last)
+    P = (hw + 2 * pad - k) // stride + 1
+    assert (batch * P * P + 127) // 128 >= 148
+    rm, rv = torch.zeros(cout, device=dev), torch.ones(cout, device=dev)
+    y, mean, invstd = conv_native.fprop_bnstats(x, w, stride, pad, rm, rv, 0.1, 1e-5)
+    ref = F.conv2d(x.float(), w.float(), None, stride, pad)
+    assert (y.float() - ref).abs().max().item() <= 2e-2 * max(1.0, ref.abs().max().item())
+    assert torch.allclose(mean, ref.mean((0, 2, 3)), rtol=1e-2, atol=2e-3)
+    assert torch.allclose(invstd, torch.rsqrt(ref.var((0, 2, 3), unbiased=False) + 1e-5), rtol=1e-2, atol=1e-3)
+    y2 = conv_native.fprop(x, w, stride, pad)
+    assert torch.equal(y2, y)
