@@ -220,6 +220,11 @@ int pdt_conv_wgrad_ex(const void* x, const void* dy, float* dw, int dtype, int N
 /* Stem input transform: NCHW fp32 -> 2x2 space-to-depth NHWC(16) low precision, zero padded by `pad`
  * (autocast input cast + layout change for the 7x7 stride-2 stem of torchvision resnet). */
 int pdt_stem_s2d(const float* x, void* y, int dtype, int N, int H, int W, int pad, cudaStream_t stream);
+/* Filter of the data-gradient convolution, 16-bit elements: out[c][i][j][k] = w[k][rs[i]][ss[j]][c], w = [K][R][S][C],
+ * out = [C][Th][Tw][K] (the flip / index_select / transpose / contiguous chain of the ATen formulation in one
+ * launch).  rs / ss are host arrays of Th / Tw tap indices (<= 8 each). */
+int pdt_dgrad_weight(const void* w, void* out, int K, int C, int R, int S, int Th, int Tw, const int* rs, const int* ss,
+                     cudaStream_t stream);
 
 #ifdef __cplusplus
 }

@@ -674,11 +674,19 @@ template <typename T> bool ok(int C, std::initializer_list<const void*> ptrs) {
   for (const void* p : ptrs) if (reinterpret_cast<uintptr_t>(p) & 15) return false;
   return true;
 }
-int grid_for(long nvec) {
+// per_sm: CTAs per SM.  The apply kernels run 2 (more warps to hide the LDS -> math -> STG chain); the reduction
+// kernels run 1: every CTA costs them a partial row that the last CTA folds serially, and one 96 KB ring per
+// SM already saturates HBM (measured 6.2 TB/s at 148 CTAs vs 5.9 at 296 on the 56x56 layers).
+int grid_for(long nvec, int per_sm = 2) {
   static int sms = 0;
   if (sms == 0) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); if (sms <= 0) sms = 148; }
   const long nchunks = (nvec + kChunkVecs - 1) / kChunkVecs;
-  long g = 2L * sms;
+  static int cap = -1;                       // PDT_BN_GRID_CAP: upper bound on the grid (experiments)
+  if (cap < 0) { const char* e = getenv("PDT_BN_GRID_CAP"); cap = e ? atoi(e) : 0; }
+  long g = (long)per_sm * sms;
+  if (cap > 0 && g > cap) g = cap;
+  // every CTA costs the reduction kernels one partial row to fold at the end: small tensors get fewer, fatter CTAs
+  if (nchunks / 8 < g) g = nchunks / 8 > sms / 4 ? nchunks / 8 : sms / 4;
   if (g > PDT_BN_MAX_BLOCKS) g = PDT_BN_MAX_BLOCKS;
   return (int)(nchunks < g ? (nchunks < 1 ? 1 : nchunks) : g);
 }
@@ -871,28 +879,82 @@ __global__ void __launch_bounds__(256) k_bn_pool_fwd_321(const T* __restrict__ x
         u[kh * 3 + kw] = ok[kh * 3 + kw] ? __ldg(reinterpret_cast<const uint4*>(x + (((size_t)n * g.H + h) * g.W + w) * g.C + c0))
                                          : make_uint4(0, 0, 0, 0);   // neighbours share pixels: keep them in L1
       }
-    float sc[8], sh[8], best[8], bx[8];
-    int bi[8];
+    float sc[8], sh[8];
+    bool any_zero = false;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) { sc[j] = scale[c0 + j]; sh[j] = shift[c0 + j]; best[j] = -INFINITY; bi[j] = 0; bx[j] = 0.f; }
-#pragma unroll
-    for (int t = 0; t < 9; ++t) {
-      if (!ok[t]) continue;
-      float f[8];
-      unpack8<T>(u[t], f);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const float v = fmaxf(fmaf(f[j], sc[j], sh[j]), 0.f);
-        if (v > best[j]) { best[j] = v; bi[j] = t; bx[j] = f[j]; }
-      }
-    }
+    for (int j = 0; j < 8; ++j) { sc[j] = scale[c0 + j]; sh[j] = shift[c0 + j]; any_zero |= (sc[j] == 0.f); }
     const size_t o = (((size_t)n * g.Ho + ho) * g.Wo + wo) * g.C + c0;
-    *reinterpret_cast<uint4*>(y + o) = pack8<T>(best);
-    *reinterpret_cast<uint4*>(xmax + o) = pack8<T>(bx);
-    uint2 pk;
-    pk.x = (bi[0] & 0xff) | ((bi[1] & 0xff) << 8) | ((bi[2] & 0xff) << 16) | ((bi[3] & 0xff) << 24);
-    pk.y = (bi[4] & 0xff) | ((bi[5] & 0xff) << 8) | ((bi[6] & 0xff) << 16) | ((bi[7] & 0xff) << 24);
-    *reinterpret_cast<uint2*>(idx + o) = pk;
+    if (!any_zero) {
+      // relu(sc*x + sh) is monotonic in x, so the window's arg-max is the arg-max of x (sc > 0) or of -x
+      // (sc < 0): the scan runs on the raw 16-bit pairs with packed compare / max / select (4 instructions per
+      // two elements and tap instead of 12 in fp32; the fp32 scan made this kernel issue-bound at 2.9 TB/s),
+      // and BN + ReLU are applied once, to the winner.  Ties and all-negative windows may pick a different tap
+      // than the fp32 scan only where the pooled value is identical.
+      using P = typename Pair2<T>::type;
+      P sgn[4], best[4];
+      uint32_t bi[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const uint32_t s2 = Cvt<T>::pack2(sc[2 * q] > 0.f ? 1.f : -1.f, sc[2 * q + 1] > 0.f ? 1.f : -1.f);
+        const uint32_t ninf = Cvt<T>::pack2(-INFINITY, -INFINITY);
+        sgn[q] = *reinterpret_cast<const P*>(&s2);
+        best[q] = *reinterpret_cast<const P*>(&ninf);
+        bi[q] = 0u;
+      }
+#pragma unroll
+      for (int t = 0; t < 9; ++t) {
+        if (!ok[t]) continue;
+        const uint32_t w4[4] = {u[t].x, u[t].y, u[t].z, u[t].w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const P key = __hmul2(*reinterpret_cast<const P*>(&w4[q]), sgn[q]);
+          const uint32_t gt = __hgt2_mask(key, best[q]);            // 0xffff per winning 16-bit lane
+          best[q] = __hmax2(key, best[q]);
+          bi[q] = (bi[q] & ~gt) | ((uint32_t)(t * 0x00010001u) & gt);
+        }
+      }
+      float bx[8], by[8];
+      uint4 xm;
+      uint32_t* xmw = reinterpret_cast<uint32_t*>(&xm);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const P xw = __hmul2(best[q], sgn[q]);                      // the winner's raw value back
+        xmw[q] = *reinterpret_cast<const uint32_t*>(&xw);
+        const float2 f2 = Cvt<T>::unpack2(xmw[q]);
+        bx[2 * q] = f2.x; bx[2 * q + 1] = f2.y;
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) by[j] = fmaxf(fmaf(bx[j], sc[j], sh[j]), 0.f);
+      *reinterpret_cast<uint4*>(y + o) = pack8<T>(by);
+      *reinterpret_cast<uint4*>(xmax + o) = xm;
+      uint2 pk;
+      pk.x = __byte_perm(bi[0], bi[1], 0x6420);
+      pk.y = __byte_perm(bi[2], bi[3], 0x6420);
+      *reinterpret_cast<uint2*>(idx + o) = pk;
+    } else {
+      // a zero scale makes every tap tie: keep the element-wise scan with first-tap-wins semantics
+      float best[8], bx[8];
+      int bi[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { best[j] = -INFINITY; bi[j] = 0; bx[j] = 0.f; }
+#pragma unroll
+      for (int t = 0; t < 9; ++t) {
+        if (!ok[t]) continue;
+        float f[8];
+        unpack8<T>(u[t], f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float v = fmaxf(fmaf(f[j], sc[j], sh[j]), 0.f);
+          if (v > best[j]) { best[j] = v; bi[j] = t; bx[j] = f[j]; }
+        }
+      }
+      *reinterpret_cast<uint4*>(y + o) = pack8<T>(best);
+      *reinterpret_cast<uint4*>(xmax + o) = pack8<T>(bx);
+      uint2 pk;
+      pk.x = (bi[0] & 0xff) | ((bi[1] & 0xff) << 8) | ((bi[2] & 0xff) << 16) | ((bi[3] & 0xff) << 24);
+      pk.y = (bi[4] & 0xff) | ((bi[5] & 0xff) << 8) | ((bi[6] & 0xff) << 16) | ((bi[7] & 0xff) << 24);
+      *reinterpret_cast<uint2*>(idx + o) = pk;
+    }
   }
 }
 
@@ -1012,7 +1074,7 @@ template <typename T>
 int bwd_reduce_stream(const void* dy, const void* y, const void* x, long M, int C, const float* mean, const float* invstd,
                       const float* gamma, const float* beta, int relu, float* partial, unsigned* counter, const PdtCommDesc* comm,
                       float* dgamma, float* dbeta, float* out_k, long count, cudaStream_t stream) {
-  const int grid = sp::grid_for(M * C / Vec<T>::N);
+  const int grid = sp::grid_for(M * C / Vec<T>::N, 1);
   if (relu && y != nullptr) {
     PDT_CHECK(sp::optin(sp::k_bwd_reduce<T, true>));
     sp::k_bwd_reduce<T, true><<<grid, sp::kThr, sp::kSmemBytes, stream>>>(
@@ -1152,7 +1214,7 @@ int pdt_bn_fwd_stats(const void* x, long M, int C, int dtype, void* scratch, con
     if (!shape_ok<T>(C)) return PDT_E_UNSUPPORTED;
     if (stream_enabled() && sp::ok<T>(C, {x})) {
       PDT_CHECK(sp::optin(sp::k_fwd_stats<T>));
-      sp::k_fwd_stats<T><<<sp::grid_for(M * C / Vec<T>::N), sp::kThr, sp::kSmemBytes, stream>>>(
+      sp::k_fwd_stats<T><<<sp::grid_for(M * C / Vec<T>::N, 1), sp::kThr, sp::kSmemBytes, stream>>>(
           reinterpret_cast<const T*>(x), M, C, partial, counter, make_comm(comm), running_mean, running_var, momentum, eps,
           save_mean, save_invstd);
       return (int)cudaGetLastError();

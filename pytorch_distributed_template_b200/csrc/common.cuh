@@ -107,6 +107,23 @@ __device__ __forceinline__ uint4 ldg_stream(const void* p) {   // read-once data
 // One thread owns FOUR adjacent columns (16-byte loads) and keeps 16 rows in flight: the rows were just
 // written by other SMs, so every load is an L2 round trip, and the scalar one-row-at-a-time version of this
 // loop cost 40-60 us per launch for 1024-column rows (more than the streaming part of small layers).
+// Sum rows b = b0, b0 + step, ... < nb of column quad c4 into a[4].  The loads of a batch are issued into an
+// array before any is consumed: left to itself ptxas reuses one register per row and the loop runs at one L2
+// round trip per row (measured: 0.25 us per row, 93 us for 296 rows).
+__device__ __forceinline__ void fold_quad(const float* __restrict__ partial, int nb, int n2, int c4, int b0, int step, double (&a)[4]) {
+  constexpr int kB = 8;
+  for (int b = b0; b < nb; b += kB * step) {
+    float4 v[kB];
+#pragma unroll
+    for (int u = 0; u < kB; ++u) {
+      const int bb = b + u * step;
+      v[u] = bb < nb ? __ldcg(reinterpret_cast<const float4*>(partial + (size_t)bb * n2) + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int u = 0; u < kB; ++u) { a[0] += (double)v[u].x; a[1] += (double)v[u].y; a[2] += (double)v[u].z; a[3] += (double)v[u].w; }
+  }
+}
+
 template <class Sync>
 __device__ __forceinline__ void fold_rows_f64(double* tot, const float* __restrict__ partial, int nb, int n2, int tid, int nthr,
                                               Sync sync) {
@@ -114,29 +131,19 @@ __device__ __forceinline__ void fold_rows_f64(double* tot, const float* __restri
   sync();
   if (nc4 >= nthr) {
     for (int c4 = tid; c4 < nc4; c4 += nthr) {
-      double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-#pragma unroll 16
-      for (int b = 0; b < nb; ++b) {
-        const float4 v = __ldcg(reinterpret_cast<const float4*>(partial + (size_t)b * n2) + c4);
-        a0 += (double)v.x; a1 += (double)v.y; a2 += (double)v.z; a3 += (double)v.w;
-      }
-      tot[4 * c4 + 0] = a0; tot[4 * c4 + 1] = a1; tot[4 * c4 + 2] = a2; tot[4 * c4 + 3] = a3;
+      double a[4] = {0.0, 0.0, 0.0, 0.0};
+      fold_quad(partial, nb, n2, c4, 0, 1, a);
+      tot[4 * c4 + 0] = a[0]; tot[4 * c4 + 1] = a[1]; tot[4 * c4 + 2] = a[2]; tot[4 * c4 + 3] = a[3];
     }
     sync();
   } else {
     const int rg = nthr / nc4, c4 = tid % nc4, g = tid / nc4;
-    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-    if (g < rg) {
-#pragma unroll 16
-      for (int b = g; b < nb; b += rg) {
-        const float4 v = __ldcg(reinterpret_cast<const float4*>(partial + (size_t)b * n2) + c4);
-        a0 += (double)v.x; a1 += (double)v.y; a2 += (double)v.z; a3 += (double)v.w;
-      }
-    }
+    double a[4] = {0.0, 0.0, 0.0, 0.0};
+    if (g < rg) fold_quad(partial, nb, n2, c4, g, rg, a);
     double* stage = tot + n2;                 // [rg][n2], rg * n2 <= 4 * nthr
     if (g < rg) {
       double* sp = stage + (size_t)g * n2 + 4 * c4;
-      sp[0] = a0; sp[1] = a1; sp[2] = a2; sp[3] = a3;
+      sp[0] = a[0]; sp[1] = a[1]; sp[2] = a[2]; sp[3] = a[3];
     }
     sync();
     for (int i = tid; i < n2; i += nthr) {

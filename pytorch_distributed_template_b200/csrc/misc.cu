@@ -405,3 +405,42 @@ extern "C" int pdt_peer_copy(const void* src, void* dst, size_t nbytes, cudaStre
                                            reinterpret_cast<unsigned char*>(dst) + n16 * 16, tail);
   return (int)cudaGetLastError();
 }
+
+// ---- filter re-layout for the data gradient --------------------------------------------------------
+// dx of a convolution is itself a convolution of dy with a filter whose channel roles are swapped and whose
+// taps are a (reversed) subset of the forward taps: out[c][i][j][k] = w[k][rs[i]][ss[j]][c] for 16-bit
+// elements, w = [K][R][S][C].  Stride 1 uses all taps reversed; one parity class of a stride-2 gradient uses
+// every second tap.  This replaces the flip / index_select x2 / transpose / contiguous chain (3-5 ATen launches
+// per convolution and step) by one tiled transpose through shared memory.
+namespace {
+struct TapSel { int rs[8], ss[8]; };
+__global__ void __launch_bounds__(256) k_dgrad_weight(const uint16_t* __restrict__ w, uint16_t* __restrict__ out, int K, int C, int R,
+                                                      int S, int Th, int Tw, TapSel sel) {
+  __shared__ uint16_t tile[32][34];
+  const int ij = blockIdx.z, i = ij / Tw, j = ij - i * Tw;
+  const int r = sel.rs[i], s = sel.ss[j];
+  const int k0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;      // 32 x 8
+  for (int kk = ty; kk < 32; kk += 8) {
+    const int k = k0 + kk, c = c0 + tx;
+    tile[kk][tx] = (k < K && c < C) ? w[(((size_t)k * R + r) * S + s) * C + c] : (uint16_t)0;
+  }
+  __syncthreads();
+  for (int cc = ty; cc < 32; cc += 8) {
+    const int c = c0 + cc, k = k0 + tx;
+    if (c < C && k < K) out[(((size_t)c * Th + i) * Tw + j) * K + k] = tile[tx][cc];
+  }
+}
+}  // namespace
+
+extern "C" int pdt_dgrad_weight(const void* w, void* out, int K, int C, int R, int S, int Th, int Tw, const int* rs, const int* ss,
+                                cudaStream_t stream) {
+  if (Th < 1 || Tw < 1 || Th > 8 || Tw > 8 || K < 1 || C < 1) return PDT_E_UNSUPPORTED;
+  TapSel sel;
+  for (int i = 0; i < 8; ++i) { sel.rs[i] = i < Th ? rs[i] : 0; sel.ss[i] = i < Tw ? ss[i] : 0; }
+  for (int i = 0; i < Th; ++i) if (sel.rs[i] < 0 || sel.rs[i] >= R) return PDT_E_UNSUPPORTED;
+  for (int j = 0; j < Tw; ++j) if (sel.ss[j] < 0 || sel.ss[j] >= S) return PDT_E_UNSUPPORTED;
+  dim3 grid((K + 31) / 32, (C + 31) / 32, Th * Tw);
+  k_dgrad_weight<<<grid, 256, 0, stream>>>(reinterpret_cast<const uint16_t*>(w), reinterpret_cast<uint16_t*>(out), K, C, R, S, Th, Tw, sel);
+  return (int)cudaGetLastError();
+}

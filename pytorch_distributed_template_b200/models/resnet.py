@@ -13,6 +13,7 @@ import torch
 import torch.nn as nn
 
 from .. import amp, ops
+from ..ops import bn as _bn_ops
 from ..parallel.syncbn import fused_bn, fused_bn_relu_maxpool, fused_conv_bn
 
 
@@ -106,8 +107,9 @@ class ResNet(nn.Module):
         if x.dim() == 4 and not (x.is_cuda and amp.active_dtype() is not None) \
                 and not x.is_contiguous(memory_format=torch.channels_last):
             x = x.contiguous(memory_format=torch.channels_last)
-        x = fused_bn_relu_maxpool(self.bn1, ops.conv2d(x, self.conv1), 3, 2, 1)
-        x = self.layer4(self.layer3(self.layer2(self.layer1(x))))
+        with _bn_ops.batched_counters():       # one launch for all num_batches_tracked increments
+            x = fused_bn_relu_maxpool(self.bn1, ops.conv2d(x, self.conv1), 3, 2, 1)
+            x = self.layer4(self.layer3(self.layer2(self.layer1(x))))
         x = ops.global_avg_pool(x)
         return ops.linear(x, self.fc)
 

@@ -27,6 +27,7 @@ _native.register("pdt_conv_fprop_ex", [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _
 _native.register("pdt_conv_wgrad_ex", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _ll, _ll, _ll, _i, _i, _i, _i,
                                        _i, _i, _i, _i, _i, _i, _i, _vp])
 _native.register("pdt_stem_s2d", [_vp, _vp, _i, _i, _i, _i, _i, _vp])
+_native.register("pdt_dgrad_weight", [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp])
 _native.register("pdt_conv_fprop_bnstats", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp,
                                             _native._f, _native._f, _vp, _vp, _vp])
 
@@ -157,6 +158,27 @@ def _parity_taps(size_in, ksize, pad, a):
 
 
 _index_cache = {}
+_tap_cache = {}
+
+
+def dgrad_weight(w_lp, rs, ss):
+    """[C, K, Th, Tw] channels_last (memory [C][Th][Tw][K]) filter of the data-gradient convolution:
+    out[c, k, i, j] = w_lp[k, c, rs[i], ss[j]] in one launch (w_lp: [K, C, R, S] channels_last, 16-bit)."""
+    K, C, R, S = w_lp.shape
+    Th, Tw = len(rs), len(ss)
+    if w_lp.element_size() != 2 or not w_lp.is_cuda or Th > 8 or Tw > 8:
+        ir, is_ = _index_tensor(rs, w_lp.device), _index_tensor(ss, w_lp.device)
+        return w_lp.index_select(2, ir).index_select(3, is_).transpose(0, 1).contiguous(memory_format=CL)
+    key = (tuple(rs), tuple(ss))
+    taps = _tap_cache.get(key)
+    if taps is None:
+        taps = ((_native.ctypes.c_int * Th)(*rs), (_native.ctypes.c_int * Tw)(*ss))
+        _tap_cache[key] = taps
+    out = torch.empty((C, K, Th, Tw), dtype=w_lp.dtype, device=w_lp.device, memory_format=CL)
+    _native.check(_native.lib().pdt_dgrad_weight(w_lp.data_ptr(), out.data_ptr(), K, C, R, S, Th, Tw,
+                                                 _native.ctypes.addressof(taps[0]), _native.ctypes.addressof(taps[1]),
+                                                 _native.stream_ptr(w_lp.device)), "pdt_dgrad_weight")
+    return out
 
 
 def _index_tensor(values, device):
@@ -194,9 +216,7 @@ def dgrad_stride2(dy, w_lp, x_shape, pad):
         Hs, Ws = (H - a + 1) // 2, (W - b + 1) // 2
         if Hs <= 0 or Ws <= 0:
             continue
-        idx_r = _index_tensor(rs, dy.device)
-        idx_s = _index_tensor(ss, dy.device)
-        w_sub = w_lp.index_select(2, idx_r).index_select(3, idx_s).transpose(0, 1).contiguous(memory_format=CL)
+        w_sub = dgrad_weight(w_lp, rs, ss)
         Th, Tw = len(rs), len(ss)
         pads = (-dh, -dw_, Hs + dh + Th - 1 - P, Ws + dw_ + Tw - 1 - Q)
         if pads[2] < 0 or pads[3] < 0:
@@ -240,7 +260,7 @@ class _ConvNative(torch.autograd.Function):
         if need_dx and K % 8 == 0 and C % 8 == 0:
             if stride[0] == 1 and R - 1 - padding[0] >= 0:
                 # dx = conv(dy, flip(w)^T, pad' = R-1-pad): the same kernel with the roles of C and K swapped
-                w_t = w_lp.flip(2, 3).transpose(0, 1).contiguous(memory_format=CL)
+                w_t = dgrad_weight(w_lp, list(range(R - 1, -1, -1)), list(range(S - 1, -1, -1)))
                 dx = fprop(dy, w_t, 1, R - 1 - padding[0])
             elif stride[0] == 2:
                 dx = dgrad_stride2(dy, w_lp, x.shape, padding[0])

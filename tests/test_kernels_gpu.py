@@ -259,6 +259,9 @@ def test_bn_relu_maxpool_fused(native_lib, dtype, shape, geom):
     with torch.no_grad():
         bn.weight.uniform_(0.5, 1.5)
         bn.bias.uniform_(-0.5, 0.5)
+        bn.weight[5] = -0.7          # negative scale: the window's winner is the SMALLEST conv value
+        bn.weight[11] = 0.0          # zero scale: every tap ties, first tap wins (element-wise fallback)
+        bn.bias[11] = 0.3
     ref_bn = torch.nn.BatchNorm2d(C).to(_dev())
     ref_bn.load_state_dict(bn.state_dict())
     y = ops.bn_relu_maxpool(x, bn, *geom)
