@@ -225,6 +225,17 @@ int pdt_stem_s2d(const float* x, void* y, int dtype, int N, int H, int W, int pa
  * launch).  rs / ss are host arrays of Th / Tw tap indices (<= 8 each). */
 int pdt_dgrad_weight(const void* w, void* out, int K, int C, int R, int S, int Th, int Tw, const int* rs, const int* ss,
                      cudaStream_t stream);
+/* The same for many filters in one launch.  `jobs_dev` is a DEVICE array of njobs descriptors; tile_begin is
+ * the running sum of ceil(K/32) * ceil(C/32) * Th * Tw over the preceding jobs, total_tiles the grand total. */
+typedef struct PdtDgradJob {
+  const void* src;
+  void* dst;
+  int K, C, R, S, Th, Tw;
+  int rs[8], ss[8];
+  int tile_begin;
+  int pad_;
+} PdtDgradJob;
+int pdt_dgrad_weight_batched(const PdtDgradJob* jobs_dev, int njobs, int total_tiles, cudaStream_t stream);
 
 #ifdef __cplusplus
 }

@@ -444,3 +444,47 @@ extern "C" int pdt_dgrad_weight(const void* w, void* out, int K, int C, int R, i
   k_dgrad_weight<<<grid, 256, 0, stream>>>(reinterpret_cast<const uint16_t*>(w), reinterpret_cast<uint16_t*>(out), K, C, R, S, Th, Tw, sel);
   return (int)cudaGetLastError();
 }
+
+// All filter re-layouts of a model in ONE launch: `jobs` is a device array (built once, the pointers are arena
+// slots and persistent buffers), a block finds its job from the running tile count.
+namespace {
+__global__ void __launch_bounds__(256) k_dgrad_weight_batched(const PdtDgradJob* __restrict__ jobs, int njobs) {
+  __shared__ uint16_t tile[32][34];
+  __shared__ PdtDgradJob jb;
+  if (threadIdx.x == 0) {
+    int lo = 0, hi = njobs - 1;                       // last job whose tile_begin <= blockIdx.x
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (jobs[mid].tile_begin <= (int)blockIdx.x) lo = mid; else hi = mid - 1;
+    }
+    jb = jobs[lo];
+  }
+  __syncthreads();
+  const int K = jb.K, C = jb.C, R = jb.R, S = jb.S, Th = jb.Th, Tw = jb.Tw;
+  const int kt = (K + 31) / 32, ct = (C + 31) / 32;
+  int t = (int)blockIdx.x - jb.tile_begin;
+  const int bx = t % kt; t /= kt;
+  const int by = t % ct; t /= ct;
+  const int i = t / Tw, j = t - i * Tw;
+  const int r = jb.rs[i], s = jb.ss[j];
+  const uint16_t* __restrict__ w = reinterpret_cast<const uint16_t*>(jb.src);
+  uint16_t* __restrict__ out = reinterpret_cast<uint16_t*>(jb.dst);
+  const int k0 = bx * 32, c0 = by * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int kk = ty; kk < 32; kk += 8) {
+    const int k = k0 + kk, c = c0 + tx;
+    tile[kk][tx] = (k < K && c < C) ? w[(((size_t)k * R + r) * S + s) * C + c] : (uint16_t)0;
+  }
+  __syncthreads();
+  for (int cc = ty; cc < 32; cc += 8) {
+    const int c = c0 + cc, k = k0 + tx;
+    if (c < C && k < K) out[(((size_t)c * Th + i) * Tw + j) * K + k] = tile[tx][cc];
+  }
+}
+}  // namespace
+
+extern "C" int pdt_dgrad_weight_batched(const PdtDgradJob* jobs_dev, int njobs, int total_tiles, cudaStream_t stream) {
+  if (njobs < 1 || total_tiles < 1) return 0;
+  k_dgrad_weight_batched<<<total_tiles, 256, 0, stream>>>(jobs_dev, njobs);
+  return (int)cudaGetLastError();
+}

@@ -107,6 +107,8 @@ class ResNet(nn.Module):
         if x.dim() == 4 and not (x.is_cuda and amp.active_dtype() is not None) \
                 and not x.is_contiguous(memory_format=torch.channels_last):
             x = x.contiguous(memory_format=torch.channels_last)
+        if self.training and torch.is_grad_enabled() and x.is_cuda:
+            ops.prepare_backward(self.conv1.weight)     # data-gradient filter layouts of every conv, one launch
         with _bn_ops.batched_counters():       # one launch for all num_batches_tracked increments
             x = fused_bn_relu_maxpool(self.bn1, ops.conv2d(x, self.conv1), 3, 2, 1)
             x = self.layer4(self.layer3(self.layer2(self.layer1(x))))

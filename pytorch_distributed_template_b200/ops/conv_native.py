@@ -28,6 +28,7 @@ _native.register("pdt_conv_wgrad_ex", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _l
                                        _i, _i, _i, _i, _i, _i, _i, _vp])
 _native.register("pdt_stem_s2d", [_vp, _vp, _i, _i, _i, _i, _i, _vp])
 _native.register("pdt_dgrad_weight", [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp])
+_native.register("pdt_dgrad_weight_batched", [_vp, _i, _i, _vp])
 _native.register("pdt_conv_fprop_bnstats", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp,
                                             _native._f, _native._f, _vp, _vp, _vp])
 
@@ -161,26 +162,6 @@ _index_cache = {}
 _tap_cache = {}
 
 
-def dgrad_weight(w_lp, rs, ss):
-    """[C, K, Th, Tw] channels_last (memory [C][Th][Tw][K]) filter of the data-gradient convolution:
-    out[c, k, i, j] = w_lp[k, c, rs[i], ss[j]] in one launch (w_lp: [K, C, R, S] channels_last, 16-bit)."""
-    K, C, R, S = w_lp.shape
-    Th, Tw = len(rs), len(ss)
-    if w_lp.element_size() != 2 or not w_lp.is_cuda or Th > 8 or Tw > 8:
-        ir, is_ = _index_tensor(rs, w_lp.device), _index_tensor(ss, w_lp.device)
-        return w_lp.index_select(2, ir).index_select(3, is_).transpose(0, 1).contiguous(memory_format=CL)
-    key = (tuple(rs), tuple(ss))
-    taps = _tap_cache.get(key)
-    if taps is None:
-        taps = ((_native.ctypes.c_int * Th)(*rs), (_native.ctypes.c_int * Tw)(*ss))
-        _tap_cache[key] = taps
-    out = torch.empty((C, K, Th, Tw), dtype=w_lp.dtype, device=w_lp.device, memory_format=CL)
-    _native.check(_native.lib().pdt_dgrad_weight(w_lp.data_ptr(), out.data_ptr(), K, C, R, S, Th, Tw,
-                                                 _native.ctypes.addressof(taps[0]), _native.ctypes.addressof(taps[1]),
-                                                 _native.stream_ptr(w_lp.device)), "pdt_dgrad_weight")
-    return out
-
-
 def _index_tensor(values, device):
     """Small index tensors are created once (an H2D copy is not allowed inside a graph capture)."""
     key = (tuple(values), device)
@@ -191,7 +172,105 @@ def _index_tensor(values, device):
     return t
 
 
-def dgrad_stride2(dy, w_lp, x_shape, pad):
+class _DgradJob(_native.ctypes.Structure):
+    _fields_ = [("src", _native.ctypes.c_void_p), ("dst", _native.ctypes.c_void_p),
+                ("K", _i), ("C", _i), ("R", _i), ("S", _i), ("Th", _i), ("Tw", _i),
+                ("rs", _i * 8), ("ss", _i * 8), ("tile_begin", _i), ("pad_", _i)]
+
+
+class _DgradPlan:
+    """Per device: every (filter, tap subset) the data-gradient kernels asked for, with a persistent output
+    buffer each.  ``prepare()`` (called at the start of a training forward, i.e. after the optimizer has
+    written the step's weights) re-lays all of them out in ONE launch; until the next ``prepare`` the
+    backward pass picks the buffers up without launching anything."""
+
+    def __init__(self, device):
+        self.device = device
+        self.jobs = {}            # (src_ptr, K, C, R, S, rs, ss) -> output tensor
+        self.order = []
+        self.table = None         # device copy of the descriptor array
+        self.table_jobs = 0
+        self.total_tiles = 0
+        self.fresh = False
+
+    def lookup(self, w_lp, rs, ss):
+        K, C, R, S = w_lp.shape
+        key = (w_lp.data_ptr(), K, C, R, S, tuple(rs), tuple(ss))
+        out = self.jobs.get(key)
+        if out is None:
+            out = torch.empty((C, K, len(rs), len(ss)), dtype=w_lp.dtype, device=w_lp.device, memory_format=CL)
+            self.jobs[key] = out
+            self.order.append(key)
+            return out, False
+        return out, self.fresh and self.table_jobs == len(self.order)
+
+    def prepare(self):
+        self.fresh = False
+        if not self.order or os.environ.get("PDT_DGRAD_BATCH", "1") != "1":
+            return
+        if self.table is None or self.table_jobs != len(self.order):
+            if torch.cuda.is_current_stream_capturing():
+                return                                   # the descriptor upload is a host-to-device copy
+            arr = (_DgradJob * len(self.order))()
+            tiles = 0
+            for n, key in enumerate(self.order):
+                ptr, K, C, R, S, rs, ss = key
+                j = arr[n]
+                j.src, j.dst = ptr, self.jobs[key].data_ptr()
+                j.K, j.C, j.R, j.S, j.Th, j.Tw = K, C, R, S, len(rs), len(ss)
+                for i, v in enumerate(rs):
+                    j.rs[i] = v
+                for i, v in enumerate(ss):
+                    j.ss[i] = v
+                j.tile_begin = tiles
+                tiles += ((K + 31) // 32) * ((C + 31) // 32) * len(rs) * len(ss)
+            host = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
+            self.table = host.to(self.device)
+            self.table_jobs = len(self.order)
+            self.total_tiles = tiles
+        with _native.guard(self.device):
+            _native.check(_native.lib().pdt_dgrad_weight_batched(self.table.data_ptr(), self.table_jobs, self.total_tiles,
+                                                                 _native.stream_ptr(self.device)), "pdt_dgrad_weight_batched")
+        self.fresh = True
+
+
+def prepare_dgrad_weights(arena):
+    """Call once per training forward (after the weights of the step are final).  The plan lives on the
+    parameter arena whose shadow weights it reads, and dies with it."""
+    plan = getattr(arena, "_dgrad_plan", None)
+    if plan is not None:
+        plan.prepare()
+
+
+def dgrad_weight(w_lp, rs, ss, stable=None):
+    """[C, K, Th, Tw] channels_last (memory [C][Th][Tw][K]) filter of the data-gradient convolution:
+    out[c, k, i, j] = w_lp[k, c, rs[i], ss[j]] in one launch (w_lp: [K, C, R, S] channels_last, 16-bit)."""
+    K, C, R, S = w_lp.shape
+    Th, Tw = len(rs), len(ss)
+    if w_lp.element_size() != 2 or not w_lp.is_cuda or Th > 8 or Tw > 8:
+        ir, is_ = _index_tensor(rs, w_lp.device), _index_tensor(ss, w_lp.device)
+        return w_lp.index_select(2, ir).index_select(3, is_).transpose(0, 1).contiguous(memory_format=CL)
+    if stable is not None and stable is not False:   # an arena: `w_lp` keeps its address across steps, cache the layout
+        plan = getattr(stable, "_dgrad_plan", None)
+        if plan is None:
+            plan = stable._dgrad_plan = _DgradPlan(w_lp.device)
+        out, ready = plan.lookup(w_lp, rs, ss)
+        if ready:
+            return out
+    else:
+        out = torch.empty((C, K, Th, Tw), dtype=w_lp.dtype, device=w_lp.device, memory_format=CL)
+    key = (tuple(rs), tuple(ss))
+    taps = _tap_cache.get(key)
+    if taps is None:
+        taps = ((_native.ctypes.c_int * Th)(*rs), (_native.ctypes.c_int * Tw)(*ss))
+        _tap_cache[key] = taps
+    _native.check(_native.lib().pdt_dgrad_weight(w_lp.data_ptr(), out.data_ptr(), K, C, R, S, Th, Tw,
+                                                 _native.ctypes.addressof(taps[0]), _native.ctypes.addressof(taps[1]),
+                                                 _native.stream_ptr(w_lp.device)), "pdt_dgrad_weight")
+    return out
+
+
+def dgrad_stride2(dy, w_lp, x_shape, pad, stable_w=None):
     """dx for a stride-2 convolution: one fprop launch per parity class of the input grid."""
     N, C, H, W = x_shape
     K, _, R, S = w_lp.shape
@@ -216,7 +295,7 @@ def dgrad_stride2(dy, w_lp, x_shape, pad):
         Hs, Ws = (H - a + 1) // 2, (W - b + 1) // 2
         if Hs <= 0 or Ws <= 0:
             continue
-        w_sub = dgrad_weight(w_lp, rs, ss)
+        w_sub = dgrad_weight(w_lp, rs, ss, stable_w)
         Th, Tw = len(rs), len(ss)
         pads = (-dh, -dw_, Hs + dh + Th - 1 - P, Ws + dw_ + Tw - 1 - Q)
         if pads[2] < 0 or pads[3] < 0:
@@ -238,6 +317,12 @@ class _ConvNative(torch.autograd.Function):
         ctx.save_for_backward(x, w_lp)
         ctx.geom = (stride, padding)
         ctx.weight = weight
+        ctx.set_materialize_grads(False)      # no zero tensors for the unused (mean, invstd) output gradients
+        # w_lp is the arena's shadow of `weight` (fixed address, rewritten in place by the optimizer kernel): its
+        # data-gradient layouts may be cached in the per-device plan.  Anything else is a temporary.
+        arena = getattr(weight, "_pdt_arena", None)
+        sv = arena.shadow_view(weight) if arena is not None and getattr(arena, "flat_shadow", None) is not None else None
+        ctx.stable_w = arena if (sv is not None and sv.data_ptr() == w_lp.data_ptr()) else None
         if bnpack is None:
             return fprop(x, w_lp, stride[0], padding[0])
         y, mean, invstd = fprop_bnstats(x, w_lp, stride[0], padding[0], *bnpack)
@@ -260,10 +345,10 @@ class _ConvNative(torch.autograd.Function):
         if need_dx and K % 8 == 0 and C % 8 == 0:
             if stride[0] == 1 and R - 1 - padding[0] >= 0:
                 # dx = conv(dy, flip(w)^T, pad' = R-1-pad): the same kernel with the roles of C and K swapped
-                w_t = dgrad_weight(w_lp, list(range(R - 1, -1, -1)), list(range(S - 1, -1, -1)))
+                w_t = dgrad_weight(w_lp, list(range(R - 1, -1, -1)), list(range(S - 1, -1, -1)), ctx.stable_w)
                 dx = fprop(dy, w_t, 1, R - 1 - padding[0])
             elif stride[0] == 2:
-                dx = dgrad_stride2(dy, w_lp, x.shape, padding[0])
+                dx = dgrad_stride2(dy, w_lp, x.shape, padding[0], ctx.stable_w)
         native_dx = dx is not None
         native_dw = wgrad_supported(C, K, x.dtype)
         dw = wgrad(x, dy, w_lp.shape, stride[0], padding[0], out=direct_grad(ctx.weight)) if native_dw else None
