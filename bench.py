@@ -46,6 +46,8 @@ def parse():
     p.add_argument("--amp-dtype", default=os.environ.get("PDT_AMP_DTYPE", "bf16"))
     p.add_argument("--no-graph", action="store_true")
     p.add_argument("--image-size", type=int, default=224)
+    p.add_argument("--input", default=os.environ.get("PDT_INPUT", "uint8"), choices=["uint8", "float"],
+                   help="ours: what the loader ships to the GPU (uint8 pixels normalised on the device, or host-normalised fp32)")
     return p.parse_args()
 
 
@@ -244,7 +246,14 @@ def run_ours(args, world):
 
     g = torch.Generator().manual_seed(1234 + rank)
     S = args.image_size
-    host_imgs = [torch.randn(per_rank, 3, S, S, generator=g).pin_memory() for _ in range(3)]
+    # what the framework's own loader hands over on a GPU (trainer.py / data.py): raw uint8 pixels, normalised on
+    # the device inside the stem's layout kernel (--input float: fp32 tensors normalised on the host, like the
+    # reference's pipeline)
+    u8 = args.input == "uint8"
+    if u8:
+        host_imgs = [torch.randint(0, 256, (per_rank, 3, S, S), generator=g, dtype=torch.uint8).pin_memory() for _ in range(3)]
+    else:
+        host_imgs = [torch.randn(per_rank, 3, S, S, generator=g).pin_memory() for _ in range(3)]
     host_tgts = [torch.randint(0, 1000, (per_rank,), generator=g).pin_memory() for _ in range(3)]
     dev_imgs = [t.to(device) for t in host_imgs]
     dev_tgts = [t.to(device) for t in host_tgts]
@@ -354,7 +363,7 @@ def run_ours(args, world):
 
     if rank == 0:
         value = args.batch / (ms / 1e3)
-        h2d = per_rank * 3 * S * S * 4 + per_rank * 8
+        h2d = per_rank * 3 * S * S * (1 if u8 else 4) + per_rank * 8
         launches = launches_per_step * args.steps if graph is not None else eager_launches
         fabric = getattr(model, "fabric", None)
         emit({"impl": "ours", "metric": "resnet18_train_images_per_sec", "value": value, "unit": "images/s",
@@ -368,6 +377,7 @@ def run_ours(args, world):
               "config": {"model": "resnet18", "global_batch": args.batch, "image": S, "mode": args.mode,
                          "parallelism": "{}{}".format("dp" if args.mode == "dp" else "ddp", args.gpus),
                          "cuda_graph": graph is not None, "final_loss": final_loss,
+                         "input": "uint8 NCHW, (x/255-mean)/std fused into the stem kernel" if u8 else "fp32 NCHW, host-normalised",
                          "fabric": fabric.describe() if fabric is not None else None,
                          "l2": "per-step working set >> 126 MB L2; 3 input batches rotate"}})
     if dist.is_initialized():

@@ -220,6 +220,11 @@ int pdt_conv_wgrad_ex(const void* x, const void* dy, float* dw, int dtype, int N
 /* Stem input transform: NCHW fp32 -> 2x2 space-to-depth NHWC(16) low precision, zero padded by `pad`
  * (autocast input cast + layout change for the 7x7 stride-2 stem of torchvision resnet). */
 int pdt_stem_s2d(const float* x, void* y, int dtype, int N, int H, int W, int pad, cudaStream_t stream);
+/* The same from raw uint8 NCHW pixels, with ToTensor + Normalize fused: value = x * scale[c] + bias[c]
+ * (scale = 1 / (255 * std), bias = -mean / std; host arrays of 3 floats).  The loader then ships one byte per
+ * value over PCIe instead of four. */
+int pdt_stem_s2d_u8(const unsigned char* x, void* y, int dtype, int N, int H, int W, int pad, const float* scale,
+                    const float* bias, cudaStream_t stream);
 /* Filter of the data-gradient convolution, 16-bit elements: out[c][i][j][k] = w[k][rs[i]][ss[j]][c], w = [K][R][S][C],
  * out = [C][Th][Tw][K] (the flip / index_select / transpose / contiguous chain of the ATen formulation in one
  * launch).  rs / ss are host arrays of Th / Tw tap indices (<= 8 each). */

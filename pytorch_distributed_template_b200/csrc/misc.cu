@@ -243,9 +243,13 @@ __global__ void __launch_bounds__(256) k_nchw_to_nhwc(const float* __restrict__ 
 // channels 12..15 zero (2x2 space-to-depth).  A 7x7 stride-2 pad-3 convolution over x becomes a
 // 4x4 stride-1 convolution over y whose four horizontal taps x 16 channels are 64 CONTIGUOUS
 // elements — exactly one 128-byte tensor-core K row (see ops/stem.py).
-template <typename T>
-__global__ void __launch_bounds__(256) k_stem_s2d(const float* __restrict__ x, T* __restrict__ y, int N, int H, int W, int HP, int WP,
-                                                 int pad) {
+// TI = float: the loader already normalised the image.  TI = uint8_t: raw 0..255 pixels; the per-channel
+// (x / 255 - mean) / std of torchvision's ToTensor + Normalize is applied here as x * sc[c] + bs[c], so the
+// host ships one byte per value instead of four (the H2D copy bounds the end-to-end step at 8 GPUs).
+struct StemNorm { float sc[3], bs[3]; };
+template <typename T, typename TI>
+__global__ void __launch_bounds__(256) k_stem_s2d(const TI* __restrict__ x, T* __restrict__ y, int N, int H, int W, int HP, int WP,
+                                                 int pad, StemNorm nm) {
   const long total = (long)N * HP * WP;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
     const int j = (int)(i % WP);
@@ -263,7 +267,11 @@ __global__ void __launch_bounds__(256) k_stem_s2d(const float* __restrict__ x, T
         const int xx = 2 * j + dx - pad;
         if (yy >= 0 && yy < H && xx >= 0 && xx < W) {
 #pragma unroll
-          for (int c = 0; c < 3; ++c) f[(dy * 2 + dx) * 3 + c] = __ldg(x + ((n * 3 + c) * H + yy) * (long)W + xx);
+          for (int c = 0; c < 3; ++c) {
+            const TI v = __ldg(x + ((n * 3 + c) * H + yy) * (long)W + xx);
+            if constexpr (sizeof(TI) == 1) f[(dy * 2 + dx) * 3 + c] = fmaf((float)v, nm.sc[c], nm.bs[c]);
+            else f[(dy * 2 + dx) * 3 + c] = (float)v;
+          }
         }
       }
     }
@@ -355,11 +363,29 @@ int pdt_avgpool_bwd(const void* dy, void* dx, int dtype, int N, int HW, int C, c
 int pdt_stem_s2d(const float* x, void* y, int dtype, int N, int H, int W, int pad, cudaStream_t stream) {
   const int HP = (H + 2 * pad + 1) / 2, WP = (W + 2 * pad + 1) / 2;
   const int nb = grid_for((long)N * HP * WP, 256);
+  StemNorm nm = {{1.f, 1.f, 1.f}, {0.f, 0.f, 0.f}};
   if (dtype == PDT_FP32) {
-    k_stem_s2d<float><<<nb, 256, 0, stream>>>(x, reinterpret_cast<float*>(y), N, H, W, HP, WP, pad);
+    k_stem_s2d<float, float><<<nb, 256, 0, stream>>>(x, reinterpret_cast<float*>(y), N, H, W, HP, WP, pad, nm);
     return (int)cudaGetLastError();
   }
-  LP_DISPATCH(dtype, k_stem_s2d<T><<<nb, 256, 0, stream>>>(x, reinterpret_cast<T*>(y), N, H, W, HP, WP, pad));
+  LP_DISPATCH(dtype, k_stem_s2d<T, float><<<nb, 256, 0, stream>>>(x, reinterpret_cast<T*>(y), N, H, W, HP, WP, pad, nm));
+  return (int)cudaGetLastError();
+}
+
+// Same transform from raw uint8 NCHW pixels with the normalisation fused: value = x * scale[c] + bias[c]
+// (scale = 1 / (255 std), bias = -mean / std; host arrays of 3 floats).
+int pdt_stem_s2d_u8(const unsigned char* x, void* y, int dtype, int N, int H, int W, int pad, const float* scale, const float* bias,
+                    cudaStream_t stream) {
+  if (pad < 0) return PDT_E_UNSUPPORTED;
+  const int HP = (H + 2 * pad + 1) / 2, WP = (W + 2 * pad + 1) / 2;
+  const int nb = grid_for((long)N * HP * WP, 256);
+  StemNorm nm;
+  for (int c = 0; c < 3; ++c) { nm.sc[c] = scale[c]; nm.bs[c] = bias[c]; }
+  if (dtype == PDT_FP32) {
+    k_stem_s2d<float, unsigned char><<<nb, 256, 0, stream>>>(x, reinterpret_cast<float*>(y), N, H, W, HP, WP, pad, nm);
+    return (int)cudaGetLastError();
+  }
+  LP_DISPATCH(dtype, k_stem_s2d<T, unsigned char><<<nb, 256, 0, stream>>>(x, reinterpret_cast<T*>(y), N, H, W, HP, WP, pad, nm));
   return (int)cudaGetLastError();
 }
 

@@ -22,7 +22,7 @@ from .env import env_int
 
 
 class SyntheticImageNet(Dataset):
-    def __init__(self, length, image_size=224, num_classes=1000, seed=0, cache=64):
+    def __init__(self, length, image_size=224, num_classes=1000, seed=0, cache=64, uint8=False):
         self.length = int(length)
         self.image_size = int(image_size)
         self.num_classes = int(num_classes)
@@ -30,7 +30,11 @@ class SyntheticImageNet(Dataset):
         # A small bank of distinct images; sample i is bank[i % cache] so a long
         # synthetic epoch does not spend its time in the host RNG.
         g = torch.Generator().manual_seed(self.seed)
-        self._bank = torch.randn(max(1, min(cache, self.length)), 3, self.image_size, self.image_size, generator=g)
+        n = max(1, min(cache, self.length))
+        if uint8:      # raw pixels, normalised on the device (ops/input_norm.py)
+            self._bank = torch.randint(0, 256, (n, 3, self.image_size, self.image_size), generator=g, dtype=torch.uint8)
+        else:
+            self._bank = torch.randn(n, 3, self.image_size, self.image_size, generator=g)
         self.classes = list(range(self.num_classes))
 
     def __len__(self):
@@ -42,27 +46,33 @@ class SyntheticImageNet(Dataset):
         return self._bank[i % self._bank.size(0)], (i * 2654435761) % self.num_classes
 
 
-def imagefolder_datasets(root):
+def imagefolder_datasets(root, uint8=False):
+    """The reference's two ImageFolder pipelines (distributed.py:112-131).  ``uint8``: stop at the cropped
+    uint8 CHW image (``PILToTensor``); ToTensor's /255 and Normalize then run on the device with the same
+    constants (ops/input_norm.py)."""
     import torchvision.datasets as datasets
     import torchvision.transforms as transforms
-    normalize = transforms.Normalize(mean=[0.485, 0.456, 0.406], std=[0.229, 0.224, 0.225])
+    from .ops.input_norm import IMAGENET_MEAN, IMAGENET_STD
+    if uint8:
+        tail = [transforms.PILToTensor()]
+    else:
+        tail = [transforms.ToTensor(), transforms.Normalize(mean=list(IMAGENET_MEAN), std=list(IMAGENET_STD))]
     train = datasets.ImageFolder(os.path.join(root, "train"), transforms.Compose([
-        transforms.RandomResizedCrop(224), transforms.RandomHorizontalFlip(),
-        transforms.ToTensor(), normalize]))
+        transforms.RandomResizedCrop(224), transforms.RandomHorizontalFlip()] + tail))
     val = datasets.ImageFolder(os.path.join(root, "val"), transforms.Compose([
-        transforms.Resize(256), transforms.CenterCrop(224), transforms.ToTensor(), normalize]))
+        transforms.Resize(256), transforms.CenterCrop(224)] + tail))
     return train, val
 
 
-def build_datasets(args):
+def build_datasets(args, uint8=False):
     """ImageFolder under ``args.data`` or, with ``PDT_SYNTHETIC=1``, synthetic sets."""
     from .env import env_flag
     if env_flag("PDT_SYNTHETIC"):
         size = env_int("PDT_IMAGE_SIZE", 224)
         ncls = env_int("PDT_NUM_CLASSES", 1000)
-        return (SyntheticImageNet(env_int("PDT_SYNTH_TRAIN_SIZE", 1281167), size, ncls, seed=1),
-                SyntheticImageNet(env_int("PDT_SYNTH_VAL_SIZE", 50000), size, ncls, seed=2))
-    return imagefolder_datasets(args.data)
+        return (SyntheticImageNet(env_int("PDT_SYNTH_TRAIN_SIZE", 1281167), size, ncls, seed=1, uint8=uint8),
+                SyntheticImageNet(env_int("PDT_SYNTH_VAL_SIZE", 50000), size, ncls, seed=2, uint8=uint8))
+    return imagefolder_datasets(args.data, uint8=uint8)
 
 
 class ShardSampler(Sampler):

@@ -101,10 +101,12 @@ class ResNet(nn.Module):
         layers += [block(self.inplanes, planes) for _ in range(1, blocks)]
         return nn.Sequential(*layers)
 
+    accepts_uint8 = True      # raw uint8 NCHW images are normalised on the device (ops/input_norm.py)
+
     def forward(self, x):
         # Weights live KRSC in the arena; keep activations channels_last to match.  (The native
         # amp stem consumes fp32 NCHW images directly and does the layout change itself.)
-        if x.dim() == 4 and not (x.is_cuda and amp.active_dtype() is not None) \
+        if x.dim() == 4 and not (x.is_cuda and amp.active_dtype() is not None) and x.dtype != torch.uint8 \
                 and not x.is_contiguous(memory_format=torch.channels_last):
             x = x.contiguous(memory_format=torch.channels_last)
         if self.training and torch.is_grad_enabled() and x.is_cuda:

@@ -58,6 +58,19 @@ def conv2d(x, conv, bnpack=None):
     lp = amp.active_dtype()
     plain = (not x.is_cuda or conv.groups != 1 or conv.dilation != (1, 1) or conv.bias is not None
              or conv.padding_mode != "zeros" or isinstance(conv.padding, str))
+    if x.dtype == torch.uint8:
+        # raw pixels (data.build_datasets(uint8=True)): the native stem normalises inside its layout kernel,
+        # every other path normalises here with the same arithmetic
+        if not plain and _stem_native is not None and _native.available() and _stem_native[0](x, conv) \
+                and (lp is not None or _tf32_on()):
+            w = (shadow_of(conv.weight, lp) if lp is not None else None)
+            if w is None:
+                w = conv.weight.detach() if lp is None else conv.weight.detach().to(dtype=lp, memory_format=torch.channels_last)
+            return _stem_native[1](x, conv, w)
+        from .input_norm import normalize_u8
+        x = normalize_u8(x)
+        if x.dim() == 4:
+            x = x.contiguous(memory_format=torch.channels_last)
     if lp is None and not plain and x.dtype == torch.float32 and _conv_native is not None and _native.available():
         # fp32 training (DataParallel / plain DDP): tcgen05 kind::tf32 where torch would allow TF32
         w = conv.weight.detach()

@@ -27,6 +27,7 @@ _native.register("pdt_conv_fprop_ex", [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _
 _native.register("pdt_conv_wgrad_ex", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _ll, _ll, _ll, _i, _i, _i, _i,
                                        _i, _i, _i, _i, _i, _i, _i, _vp])
 _native.register("pdt_stem_s2d", [_vp, _vp, _i, _i, _i, _i, _i, _vp])
+_native.register("pdt_stem_s2d_u8", [_vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _vp])
 _native.register("pdt_dgrad_weight", [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp])
 _native.register("pdt_dgrad_weight_batched", [_vp, _i, _i, _vp])
 _native.register("pdt_conv_fprop_bnstats", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp,
@@ -395,7 +396,7 @@ def stem_weight_grad_from_s2d(dwp, K):
 
 
 def stem_supported(x, conv):
-    return (enabled() and x.is_cuda and x.dtype == torch.float32 and x.dim() == 4 and x.shape[1] == 3
+    return (enabled() and x.is_cuda and x.dtype in (torch.float32, torch.uint8) and x.dim() == 4 and x.shape[1] == 3
             and conv.kernel_size == (7, 7) and conv.stride == (2, 2) and conv.padding == (3, 3)
             and conv.out_channels % 8 == 0 and x.shape[2] % 2 == 0 and x.shape[3] % 2 == 0
             and os.environ.get("PDT_STEM", "native") == "native")
@@ -430,8 +431,15 @@ class _StemNative(torch.autograd.Function):
         P, Q = HP - 3, WP - 3
         xs = torch.empty((N, HP, WP, 16), dtype=lp, device=x.device)
         x = x.contiguous()
-        _native.check(_native.lib().pdt_stem_s2d(x.data_ptr(), xs.data_ptr(), _native.dtype_code(lp), N, H, W, 3,
-                                                 _native.stream_ptr(x.device)), "pdt_stem_s2d")
+        if x.dtype == torch.uint8:      # raw pixels: ToTensor + Normalize are fused into the layout kernel
+            from . import input_norm
+            sc, bs = input_norm.scale_bias_ctypes()
+            _native.check(_native.lib().pdt_stem_s2d_u8(x.data_ptr(), xs.data_ptr(), _native.dtype_code(lp), N, H, W, 3,
+                                                        _native.ctypes.addressof(sc), _native.ctypes.addressof(bs),
+                                                        _native.stream_ptr(x.device)), "pdt_stem_s2d_u8")
+        else:
+            _native.check(_native.lib().pdt_stem_s2d(x.data_ptr(), xs.data_ptr(), _native.dtype_code(lp), N, H, W, 3,
+                                                     _native.stream_ptr(x.device)), "pdt_stem_s2d")
         wp = stem_weight_s2d(w_lp)
         y = torch.empty((N, K, P, Q), dtype=lp, device=x.device, memory_format=CL)
         g = _StemNative._geom(lp, HP, WP, Q)

@@ -14,6 +14,7 @@ Environment knobs (the CLI stays the reference's): PDT_SYNTHETIC, PDT_MAX_STEPS,
 PDT_MAX_VAL_STEPS, PDT_AMP_DTYPE, PDT_DEVICE, PDT_MODEL_IMPL, PDT_OUTPUT_EXISTS,
 PDT_SYNTH_TRAIN_SIZE, PDT_SYNTH_VAL_SIZE, PDT_IMAGE_SIZE, PDT_NUM_CLASSES.
 """
+import os
 import random
 import time
 import warnings
@@ -117,7 +118,13 @@ def setup(args, mode):
     if use_amp:
         ctx.scaler.bind(ctx.optimizer)
 
-    train_set, val_set = data.build_datasets(args)
+    # On a GPU the loader ships raw uint8 pixels and (x / 255 - mean) / std runs on the device (fused into the
+    # stem's layout kernel): a quarter of the H2D bytes of the reference's host-side ToTensor + Normalize.
+    # PDT_INPUT=float keeps the host-side pipeline; models that cannot take uint8 get it automatically.
+    inner = getattr(model, "module", model)
+    ctx.uint8_input = (ctx.device.type == "cuda" and os.environ.get("PDT_INPUT", "uint8") == "uint8"
+                       and getattr(inner, "accepts_uint8", False))
+    train_set, val_set = data.build_datasets(args, uint8=ctx.uint8_input)
     pin = ctx.device.type == "cuda"
     if distributed:
         ctx.train_sampler = data.ShardSampler(train_set)

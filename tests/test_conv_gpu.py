@@ -262,3 +262,34 @@ def test_conv_cluster_multicast(native_lib, cin, cout, hw, k, stride, pad, batch
     assert torch.allclose(invstd, torch.rsqrt(ref.var((0, 2, 3), unbiased=False) + 1e-5), rtol=1e-2, atol=1e-3)
     y2 = conv_native.fprop(x, w, stride, pad)
     assert torch.equal(y2, y)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_stem_uint8_input_fused_normalisation(native_lib, dtype):
+    """Raw uint8 images through the native stem (normalisation fused into the layout kernel) vs the same
+    stem on host-style normalised fp32 images; forward and weight gradient."""
+    from pytorch_distributed_template_b200 import amp, ops
+    from pytorch_distributed_template_b200.ops import input_norm
+    torch.backends.cudnn.allow_tf32 = False
+    torch.manual_seed(33)
+    dev = torch.device("cuda", 0)
+    conv = torch.nn.Conv2d(3, 64, 7, 2, 3, bias=False).to(dev)
+    x8 = torch.randint(0, 256, (6, 3, 64, 64), dtype=torch.uint8, device=dev)
+    xf = input_norm.normalize_u8(x8)
+    mean, std = input_norm.get_input_norm()
+    ref = (x8.float() / 255.0 - torch.tensor(mean, device=dev).view(1, 3, 1, 1)) / torch.tensor(std, device=dev).view(1, 3, 1, 1)
+    assert torch.allclose(xf, ref, rtol=1e-5, atol=1e-5)
+    with amp.autocast(dtype=dtype):
+        y8 = ops.conv2d(x8, conv)
+        y8.float().square().mean().backward()
+        g8 = conv.weight.grad.clone()
+        conv.weight.grad = None
+        yf = ops.conv2d(xf, conv)
+        yf.float().square().mean().backward()
+        gf = conv.weight.grad.clone()
+    assert y8.dtype == dtype and y8.shape == yf.shape
+    tol = 2e-2 if dtype == torch.bfloat16 else 3e-3
+    assert (y8.float() - yf.float()).abs().max().item() <= tol * max(1.0, yf.float().abs().max().item())
+    assert (g8 - gf).abs().max().item() <= tol * max(1e-3, gf.abs().max().item())
+    oracle = F.conv2d(ref, conv.weight.detach(), None, 2, 3)
+    assert (y8.float() - oracle).abs().max().item() <= 2 * tol * max(1.0, oracle.abs().max().item())

@@ -168,3 +168,30 @@ def test_synthetic_dataset_and_model_zoo():
         assert [(k, tuple(v.shape)) for k, v in ours.state_dict().items()] == \
                [(k, tuple(v.shape)) for k, v in tv.state_dict().items()]
     assert type(create_model("squeezenet1_0")).__module__.startswith("torchvision")
+
+
+def test_uint8_input_pipeline_cpu():
+    """Raw-pixel pipeline: synthetic uint8 dataset, device-side normalisation formula, model forward on
+    uint8 == forward on the normalised floats (CPU path)."""
+    import torch
+    from pytorch_distributed_template_b200 import data
+    from pytorch_distributed_template_b200.models import build_resnet
+    from pytorch_distributed_template_b200.ops import input_norm
+    ds = data.SyntheticImageNet(8, image_size=32, num_classes=10, uint8=True)
+    img, target = ds[3]
+    assert img.dtype == torch.uint8 and img.shape == (3, 32, 32) and 0 <= target < 10
+    x8 = torch.stack([ds[i][0] for i in range(4)])
+    xf = input_norm.normalize_u8(x8)
+    mean = torch.tensor(input_norm.IMAGENET_MEAN).view(1, 3, 1, 1)
+    std = torch.tensor(input_norm.IMAGENET_STD).view(1, 3, 1, 1)
+    assert torch.allclose(xf, (x8.float() / 255 - mean) / std, rtol=1e-5, atol=1e-5)
+    torch.manual_seed(0)
+    model = build_resnet("resnet18", num_classes=10).eval()
+    assert getattr(model, "accepts_uint8", False)
+    with torch.no_grad():
+        assert torch.allclose(model(x8), model(xf), rtol=1e-4, atol=1e-4)
+    input_norm.set_input_norm((0.5, 0.5, 0.5), (0.25, 0.25, 0.25))
+    try:
+        assert torch.allclose(input_norm.normalize_u8(x8), (x8.float() / 255 - 0.5) / 0.25, rtol=1e-5, atol=1e-5)
+    finally:
+        input_norm.set_input_norm(input_norm.IMAGENET_MEAN, input_norm.IMAGENET_STD)
