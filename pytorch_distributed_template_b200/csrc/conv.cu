@@ -224,6 +224,13 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
       for (int i = lane; i < 2 * kStatMaxK; i += 32) my_stat[i] = 0.f;
       __syncwarp();
     }
+    // N = 64 (the stem, 1x1 projections): each lane keeps its own per-column partial sums for the whole
+    // kernel (2 instructions per element, no shared-memory transposes; 128 registers, affordable at 256
+    // threads per CTA) and the lanes are combined once at the end.  Wider tiles keep the transpose scheme.
+    constexpr bool kRegStats = (BN == 64);
+    float rcs[kRegStats ? 64 : 1], rcq[kRegStats ? 64 : 1];
+#pragma unroll
+    for (int j = 0; j < (kRegStats ? 64 : 1); ++j) rcs[j] = rcq[j] = 0.f;
     int it = 0;
     for (int unit = cluster_id; unit < num_units; unit += num_clusters, ++it) {
       const int mt = (unit / g.n_tiles) * CL + crank, nt = unit % g.n_tiles;
@@ -242,12 +249,21 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         opix = (n * g.OH + (long)p * g.os + g.oa) * g.OW + (long)q * g.os + g.ob;
       }
       T* orow = out + opix * g.K + (long)nt * BN;
-#pragma unroll 1
+#pragma unroll (kRegStats ? 2 : 1)
       for (int c0 = 0; c0 < BN; c0 += 32) {
         uint32_t v[32];
         tmem_ld32(taddr + c0, v);
         tmem_ld_wait();
-        if (bs.enabled) {
+        if (kRegStats) {
+          if (bs.enabled) {       // rows past M are exactly 0 (zero-filled pixels): no mask needed
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const float t = __uint_as_float(v[j]);
+              rcs[(kRegStats ? c0 : 0) + j] += t;
+              rcq[(kRegStats ? c0 : 0) + j] = fmaf(t, t, rcq[(kRegStats ? c0 : 0) + j]);
+            }
+          }
+        } else if (bs.enabled) {
           // rows past M come from zero-filled (out-of-bounds) pixels: their accumulators are exactly 0.
           // Column sums over the warp's 32 rows via a padded shared-memory transpose (conflict-free both ways).
 #pragma unroll
@@ -295,6 +311,21 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty[acc]);
+    }
+    if (kRegStats && bs.enabled) {
+      float k0 = 0.f, k1 = 0.f, q0 = 0.f, q1 = 0.f;
+#pragma unroll
+      for (int j = 0; j < (kRegStats ? 64 : 1); ++j) {
+        float a = rcs[j], b = rcq[j];
+#pragma unroll
+        for (int sft = 16; sft >= 1; sft >>= 1) {
+          a += __shfl_xor_sync(0xffffffffu, a, sft);
+          b += __shfl_xor_sync(0xffffffffu, b, sft);
+        }
+        if (lane == (j & 31)) { if (j < 32) { k0 = a; q0 = b; } else { k1 = a; q1 = b; } }
+      }
+      my_stat[lane] = k0; my_stat[32 + lane] = k1;
+      my_stat[kStatMaxK + lane] = q0; my_stat[kStatMaxK + 32 + lane] = q1;
     }
     if (bs.enabled) {
       // ---- fold the 4 warps' column sums, publish this CTA's row, last CTA finalises ----
