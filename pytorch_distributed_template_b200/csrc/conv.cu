@@ -57,6 +57,10 @@ struct ConvGeom {
   // activation tensor as TMA sees it: Cx channels per pixel, byte strides of w / h / n
   int Cx;
   long long x_sw, x_sh, x_sn;
+  // 1: the whole filter (k_blocks tiles) is loaded ONCE into the B ring, slot kb = k-block kb, and stays there
+  // (one N tile, k_blocks <= ring depth, no cluster).  The stem (4 k-blocks) otherwise re-fetched 32 KB of
+  // filter per 128-pixel tile next to 64 KB of activations and ran at the L2 delivery limit.
+  int resident_b;
 };
 
 // Optional epilogue fusion: per-channel sum / sum of squares of the convolution output (the BatchNorm
@@ -122,7 +126,8 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   uint64_t* empty = bars + C::kStages;
   uint64_t* tfull = bars + 2 * C::kStages;
   uint64_t* tempty = tfull + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  uint64_t* bres = tempty + 2;                  // resident filter has landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bres + 1);
   float* s_stat = reinterpret_cast<float*>(smem + C::kStages * C::kStageBytes + 256);   // [4][2][kStatMaxK]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -143,6 +148,7 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < C::kStages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], CL); }
     for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 4); }
+    mbar_init(bres, 1);
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc(tmem_slot, C::kTmemCols);
@@ -157,6 +163,17 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     {
       int stage = 0;
       uint32_t phase = 0;
+      const bool resb = CL == 1 && g.resident_b != 0;
+      if (resb) {
+        if (elect_one_sync()) {
+          mbar_expect_tx(bres, (uint32_t)k_blocks * C::kStageBytesB);
+          for (int kb = 0; kb < k_blocks; ++kb) {
+            const int tap = kb / c_chunks, cc = kb - tap * c_chunks;
+            tma_load_2d(smB + kb * C::kStageBytesB, &tmB, bres, tap * g.C + cc * BK, 0);
+          }
+        }
+        __syncwarp();
+      }
       for (int unit = cluster_id; unit < num_units; unit += num_clusters) {
         const int mt = (unit / g.n_tiles) * CL + crank, nt = unit % g.n_tiles;
         const int m0 = mt * BM;
@@ -169,9 +186,10 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
             for (int cc = 0; cc < c_chunks; ++cc) {
               mbar_wait(&empty[stage], phase ^ 1);
               if (elect_one_sync()) {
-                mbar_expect_tx(&full[stage], C::kStageBytes);
+                mbar_expect_tx(&full[stage], resb ? C::kStageBytesA : C::kStageBytes);
                 tma_load_im2col_4d(smA + stage * C::kStageBytesA, &tmA, &full[stage], cc * BK, cw, ch, img, (uint16_t)(s * g.dil_w), (uint16_t)r);
-                if (CL == 1) {
+                if (resb) {
+                } else if (CL == 1) {
                   tma_load_2d(smB + stage * C::kStageBytesB, &tmB, &full[stage], (r * g.S + s) * g.C + cc * BK, nt * BN);
                 } else {
                   tma_load_2d_mc(smB + stage * C::kStageBytesB + crank * (C::kStageBytesB / CL), &tmB, &full[stage],
@@ -190,6 +208,8 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
+      const bool resb = CL == 1 && g.resident_b != 0;
+      if (resb) { mbar_wait(bres, 0); tc_fence_after(); }
       for (int unit = cluster_id; unit < num_units; unit += num_clusters, ++it) {
         const int acc = it & 1;
         const uint32_t acc_phase = (it >> 1) & 1;
@@ -200,7 +220,7 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
           mbar_wait(&full[stage], phase);
           tc_fence_after();
           const uint64_t da = make_sw128_desc(smem_u32(smA + stage * C::kStageBytesA), 1024, 16);
-          const uint64_t db = make_sw128_desc(smem_u32(smB + stage * C::kStageBytesB), 1024, 16);
+          const uint64_t db = make_sw128_desc(smem_u32(smB + (resb ? kb : stage) * C::kStageBytesB), 1024, 16);
           if (elect_one_sync()) {
 #pragma unroll
             for (int k = 0; k < 4; ++k)   // +32 bytes along K per UMMA_K step: +2 in the (addr >> 4) field
@@ -639,7 +659,15 @@ int launch_igemm_cl(const CUtensorMap& tmA, const CUtensorMap& tmB, void* y, con
   if (clusters > units) clusters = units;
   cfg.gridDim = dim3(clusters * CL);
   cfg.attrs = attr; cfg.numAttrs = nattr;
-  PDT_CHECK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, reinterpret_cast<T*>(y), bias, g, bs));
+  ConvGeom gg = g;
+  {
+    static int env = -1;                       // PDT_CONV_RESIDENT_B=0 keeps streaming the filter
+    if (env < 0) { const char* e = getenv("PDT_CONV_RESIDENT_B"); env = (e != nullptr && e[0] == '0') ? 0 : 1; }
+    const int bk = 128 / (int)sizeof(T);
+    const int k_blocks = g.R * g.S * ((g.C + bk - 1) / bk);
+    gg.resident_b = (env == 1 && CL == 1 && g.n_tiles == 1 && k_blocks <= C::kStages) ? 1 : 0;
+  }
+  PDT_CHECK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, reinterpret_cast<T*>(y), bias, gg, bs));
   return (int)cudaGetLastError();
 }
 
