@@ -202,6 +202,14 @@ int pdt_conv3x3_halo(const void* x, const void* w, void* y, int dtype, int N, in
 int pdt_conv3x3_wgrad_halo_supported(int dtype, int N, int H, int W, int C, int K);
 int pdt_conv3x3_wgrad_halo(const void* x, const void* dy, float* dw, int dtype, int N, int H, int W, int C, int K,
                            cudaStream_t stream);
+/* Stem: the 4x4 / stride 1 convolution over the space-to-depth image (pdt_stem_s2d), 16 channels per pixel,
+ * 64 output channels: one linear TMA load per 128-pixel tile, sixteen row-shifted K = 16 views (32-byte
+ * swizzle), resident filter, optional BatchNorm statistics in the epilogue (scratch != NULL).
+ * xs [N][HP][WP][16], wp [64][4][4][16], y [N][HP-3][WP-3][64]. */
+int pdt_stem_conv_supported(int dtype, int N, int HP, int WP, int K);
+int pdt_stem_conv(const void* xs, const void* wp, void* y, int dtype, int N, int HP, int WP, int K, void* scratch,
+                  float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
+                  float* save_invstd, cudaStream_t stream);
 /* Weight gradient (cudnnConvolutionBackwardFilter): dw [K][R][S][C] fp32 += sum over pixels; split-K over
  * the pixel dimension with red.global.add, so zero dw first.  C % 64 == 0, K % 64 == 0. */
 int pdt_conv_wgrad(const void* x, const void* dy, float* dw, int dtype, int N, int H, int W, int C, int K, int R, int S,

@@ -90,6 +90,10 @@ __device__ __forceinline__ void tma_store_4d(const CUtensorMap* m, uint32_t smem
   asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
                ::"l"(reinterpret_cast<uint64_t>(m)), "r"(smem_src), "r"(c), "r"(w), "r"(h), "r"(n) : "memory");
 }
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* m, uint32_t smem_src, int c, int w, int h) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(m)), "r"(smem_src), "r"(c), "r"(w), "r"(h) : "memory");
+}
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 template <int N> __device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
 template <int N> __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory"); }
@@ -650,6 +654,247 @@ k_wgrad3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
   }
 }
 
+// ---- stem: 4x4 / stride 1 convolution over the space-to-depth image, 16 channels per pixel -----------
+// (torchvision's 7x7 / stride 2 conv1 after pdt_stem_s2d).  The generic kernel builds each K row from four
+// neighbouring 32-byte pixels with an im2col load per filter row, i.e. it pulls every pixel 16 times from
+// L2 (ncu: 71 % L2 throughput, 21 % tensor pipe).  Here a tile is 128 consecutive pixel slots of the
+// row-major image; ONE linear TMA load brings the 512 pixels a tile can touch, stored as 32-byte rows with
+// the 32-byte swizzle, and each of the 16 taps is a K = 16 MMA whose A operand is that patch shifted by
+// r * WP + s rows (same absolute-address swizzle argument as the 3x3 kernels).  A tile is ONE output row
+// (Q <= 128; the slots past Q are junk and are neither stored nor counted), so the finished tile is a dense
+// Q x 64 block that leaves through one TMA store from a 128B-swizzled staging buffer, as in k_conv3x3_halo.
+// The 16 x 64 x 16 filter (32 KB) stays in shared memory; three TMEM accumulator chains hide the accumulate
+// latency; 8 epilogue warps keep the BatchNorm statistics in registers.
+struct StemGeom {
+  int N, HP, WP, P, Q, K;       // K = 64 output channels
+  long long slots;              // N * HP * WP
+  int num_tiles;                // N * P: one output row per tile (Q <= 128 slots of it are real)
+};
+struct SCfg {
+  static constexpr int kStages = 4;
+  static constexpr int kAStage = 512 * 32;                 // 16 KB patch
+  static constexpr int kBBytes = 16 * 64 * 32;             // resident filter
+  static constexpr int kAccCols = 256;                     // 3 chains x 64 columns, padded
+  static constexpr int kStatBytes = 16384;
+  static constexpr int kOutBuf = 128 * 128;                // staging tile, double-buffered
+  static constexpr int kSmemBytes = kStages * kAStage + kBBytes + 2 * kOutBuf + 1024 + 256 + kStatBytes;
+};
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads, 1)
+k_stem_conv(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
+            const __grid_constant__ CUtensorMap tmY, const StemGeom g, const BnStats bs) {
+  using C = SCfg;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smA = smem;
+  uint8_t* smB = smem + C::kStages * C::kAStage;
+  uint8_t* smO = smB + C::kBBytes;               // 1024-byte aligned (everything above is a multiple of 16 KB)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smO + 2 * C::kOutBuf);
+  uint64_t* afull = bars;
+  uint64_t* aempty = afull + C::kStages;
+  uint64_t* bfull = aempty + C::kStages;
+  uint64_t* tfull = bfull + 1;
+  uint64_t* tempty = tfull + 2;
+  uint64_t* sfree = tempty + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sfree + 2);
+  float* s_stat = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) { prefetch_tmap(&tmX); prefetch_tmap(&tmW); prefetch_tmap(&tmY); }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < C::kStages; ++i) { mbar_init(&afull[i], 1); mbar_init(&aempty[i], 1); }
+    mbar_init(bfull, 1);
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], kEpiWarps); mbar_init(&sfree[i], 1); }
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ================= TMA producer =================
+    if (elect_one_sync()) {
+      mbar_expect_tx(bfull, C::kBBytes);
+      for (int tap = 0; tap < 16; ++tap) tma_load_2d(smB + tap * 2048, &tmW, bfull, tap * 16, 0);
+    }
+    __syncwarp();
+    int as = 0;
+    uint32_t aph = 0;
+    for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x) {
+      const int n = tile / g.P, p = tile - n * g.P;
+      const int base = (n * g.HP + p) * g.WP;              // first pixel slot of output row (n, p)
+      mbar_wait(&aempty[as], aph ^ 1);
+      if (elect_one_sync()) {
+        mbar_expect_tx(&afull[as], C::kAStage);
+        tma_load_2d(smA + as * C::kAStage, &tmX, &afull[as], 0, base);
+        tma_load_2d(smA + as * C::kAStage + 8192, &tmX, &afull[as], 0, base + 256);
+      }
+      __syncwarp();
+      if (++as == C::kStages) { as = 0; aph ^= 1; }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer =================
+    constexpr uint32_t idesc = make_idesc(128, 64, std::is_same<T, __nv_bfloat16>::value ? 1 : 0, 0, 0);
+    int64_t tapoff[16];
+#pragma unroll
+    for (int tap = 0; tap < 16; ++tap) tapoff[tap] = (int64_t)(((tap >> 2) * g.WP + (tap & 3)) * 2);   // 32-byte rows, >> 4
+    // 32-byte swizzle (layout type 6): 8-row groups 256 B apart
+    const uint64_t db_base = make_sw128_desc(smem_u32(smB), 256, 16, 6);
+    mbar_wait(bfull, 0);
+    tc_fence_after();
+    int as = 0, it = 0;
+    uint32_t aph = 0;
+    for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x, ++it) {
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1;
+      mbar_wait(&tempty[acc], acc_phase ^ 1);
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_base + acc * C::kAccCols;
+      mbar_wait(&afull[as], aph);
+      tc_fence_after();
+      const uint64_t da_base = make_sw128_desc(smem_u32(smA + as * C::kAStage), 256, 16, 6);
+      if (elect_one_sync()) {
+#pragma unroll
+        for (int tap = 0; tap < 16; ++tap)
+          umma_f16(tmem_d + (tap % 3) * 64, da_base + (uint64_t)tapoff[tap], db_base + (uint64_t)(tap * 128), idesc, tap >= 3 ? 1u : 0u);
+        umma_commit(&aempty[as]);
+        umma_commit(&tfull[acc]);
+      }
+      __syncwarp();
+      if (++as == C::kStages) { as = 0; aph ^= 1; }
+    }
+  } else if (warp >= 4) {
+    // ================= epilogue: 8 warps, (lane quarter) x (column half) =================
+    const int quarter = warp & 3, half = (warp - 4) >> 2, ew = warp - 4;
+    const int c0 = half * 32;
+    float* my_stat = s_stat + ew * (2 * kStatMaxK);
+    float cs[32], cq[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) cs[j] = cq[j] = 0.f;
+    const int m = quarter * 32 + lane;                     // slot = output column q
+    const bool valid = m < g.Q;
+    const uint32_t so = smem_u32(smO);
+    int it = 0;
+    for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x, ++it) {
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1;
+      const uint32_t taddr = tmem_base + acc * C::kAccCols + ((uint32_t)(quarter * 32) << 16);
+      mbar_wait(&tfull[acc], acc_phase);
+      tc_fence_after();
+      uint32_t v[32];
+      {
+        uint32_t v2[32], v3[32];
+        tmem_ld32(taddr + c0, v);
+        tmem_ld32(taddr + 64 + c0, v2);
+        tmem_ld32(taddr + 128 + c0, v3);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          v[j] = __float_as_uint(__uint_as_float(v[j]) + __uint_as_float(v2[j]) + __uint_as_float(v3[j]));
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[acc]);
+      uint4 o[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        o[j].x = Cvt<T>::pack2(__uint_as_float(v[8 * j + 0]), __uint_as_float(v[8 * j + 1]));
+        o[j].y = Cvt<T>::pack2(__uint_as_float(v[8 * j + 2]), __uint_as_float(v[8 * j + 3]));
+        o[j].z = Cvt<T>::pack2(__uint_as_float(v[8 * j + 4]), __uint_as_float(v[8 * j + 5]));
+        o[j].w = Cvt<T>::pack2(__uint_as_float(v[8 * j + 6]), __uint_as_float(v[8 * j + 7]));
+      }
+      const int ob = it & 1;
+      mbar_wait(&sfree[ob], ((it >> 1) & 1) ^ 1);            // the store that last used this buffer has read it
+      if (valid) {
+        const uint32_t row = so + (uint32_t)(ob * C::kOutBuf + m * 128);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) sts128(row + (uint32_t)((((half * 4 + j) ^ (m & 7))) << 4), o[j]);
+      }
+      fence_proxy_async();
+      epi_bar_sync();
+      if (threadIdx.x == 128) {
+        tma_store_3d(&tmY, so + (uint32_t)(ob * C::kOutBuf), 0, 0, tile);     // (channel, q, n * P + p)
+        bulk_commit();
+        bulk_wait_read<1>();
+        if (it >= 1) mbar_arrive(&sfree[ob ^ 1]);
+      }
+      if (valid) {
+        if (bs.enabled) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const float t = __uint_as_float(v[j]);
+            cs[j] += t;
+            cq[j] = fmaf(t, t, cq[j]);
+          }
+        }
+      }
+    }
+    if (threadIdx.x == 128) bulk_wait_all<0>();
+    if (bs.enabled) {
+      for (int i = lane; i < 2 * kStatMaxK; i += 32) my_stat[i] = 0.f;
+      __syncwarp();
+      float ks = 0.f, kq = 0.f;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        float a = cs[j], b = cq[j];
+#pragma unroll
+        for (int sft = 16; sft >= 1; sft >>= 1) {
+          a += __shfl_xor_sync(0xffffffffu, a, sft);
+          b += __shfl_xor_sync(0xffffffffu, b, sft);
+        }
+        if (lane == j) { ks = a; kq = b; }
+      }
+      my_stat[c0 + lane] = ks;
+      my_stat[kStatMaxK + c0 + lane] = kq;
+      // ---- fold the 8 warps, publish this CTA's row, last CTA finalises (as in k_conv3x3_halo) ----
+      __shared__ int s_last;
+      const int te = threadIdx.x - 128;
+      const int K = 64;
+      epi_bar_sync();
+      for (int i = te; i < 2 * K; i += 256) {
+        const int which = i / K, c = i - which * K;
+        float t = 0.f;
+#pragma unroll
+        for (int w8 = 0; w8 < kEpiWarps; ++w8) t += s_stat[w8 * (2 * kStatMaxK) + which * kStatMaxK + c];
+        bs.partial[(size_t)blockIdx.x * 2 * K + i] = t;
+      }
+      __threadfence();
+      epi_bar_sync();
+      if (te == 0) s_last = (atomicAdd(bs.counter, 1u) == gridDim.x - 1);
+      epi_bar_sync();
+      if (s_last) {
+        __threadfence();
+        double* tot = reinterpret_cast<double*>(s_stat);
+        fold_rows_f64(tot, bs.partial, (int)gridDim.x, 2 * K, te, 256, [] { epi_bar_sync(); });
+        const double cnt = (double)bs.count;
+        for (int c = te; c < K; c += 256) {
+          const double mean = tot[c] / cnt;
+          double var = tot[K + c] / cnt - mean * mean;
+          var = var > 0.0 ? var : 0.0;
+          bs.save_mean[c] = (float)mean;
+          bs.save_invstd[c] = (float)(1.0 / sqrt(var + (double)bs.eps));
+          if (bs.running_mean != nullptr) {
+            const double unbiased = cnt > 1.0 ? var * cnt / (cnt - 1.0) : var;
+            bs.running_mean[c] = (float)((1.0 - bs.momentum) * bs.running_mean[c] + bs.momentum * mean);
+            bs.running_var[c] = (float)((1.0 - bs.momentum) * bs.running_var[c] + bs.momentum * unbiased);
+          }
+        }
+        if (te == 0) *bs.counter = 0;
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -849,6 +1094,84 @@ int pdt_conv3x3_wgrad_halo(const void* x, const void* dy, float* dw, int dtype, 
     auto kern = k_wgrad3x3_halo<__nv_bfloat16>;
     PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, WHCfg::kSmemBytes));
     kern<<<grid, 128, WHCfg::kSmemBytes, stream>>>(tmX, tmDY, dw, g);
+  }
+  return (int)cudaGetLastError();
+}
+
+// 1 if pdt_stem_conv serves this stem (space-to-depth image of WP pixels per row, K output channels).
+int pdt_stem_conv_supported(int dtype, int N, int HP, int WP, int K) {
+  if (dtype != PDT_BF16 && dtype != PDT_FP16) return 0;
+  if (K != 64 || WP < 4 || HP < 4 || WP > 127 || N < 1) return 0;      // WP <= 127: row fits a 128-slot tile and the 512-pixel patch
+  if ((long long)N * HP * WP > 2000000000ll) return 0;
+  return 1;
+}
+
+// xs: [N][HP][WP][16] space-to-depth image (pdt_stem_s2d), wp: [64][4][4][16] filter, y: [N][HP-3][WP-3][64].
+// scratch / statistics pointers as in pdt_conv_fprop_bnstats; scratch == NULL for a plain convolution.
+int pdt_stem_conv(const void* xs, const void* wp, void* y, int dtype, int N, int HP, int WP, int K, void* scratch,
+                  float* running_mean, float* running_var, float momentum, float eps, float* save_mean, float* save_invstd,
+                  cudaStream_t stream) {
+  if (!pdt_stem_conv_supported(dtype, N, HP, WP, K)) return PDT_E_UNSUPPORTED;
+  if ((reinterpret_cast<uintptr_t>(xs) | reinterpret_cast<uintptr_t>(wp) | reinterpret_cast<uintptr_t>(y)) & 15) return PDT_E_UNSUPPORTED;
+  if (g_enc == nullptr) {
+    cudaDriverEntryPointQueryResult q;
+    void* fn = nullptr;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q);
+    if (e != cudaSuccess || fn == nullptr) return (int)(e != cudaSuccess ? e : cudaErrorUnknown);
+    g_enc = reinterpret_cast<EncodeTiledFn>(fn);
+  }
+  StemGeom g;
+  g.N = N; g.HP = HP; g.WP = WP; g.P = HP - 3; g.Q = WP - 3; g.K = K;
+  g.slots = (long long)N * HP * WP;
+  g.num_tiles = N * g.P;
+  const CUtensorMapDataType dt = dtype == PDT_FP16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  CUtensorMap tmX, tmW, tmY;
+  cuuint32_t estr[2] = {1, 1};
+  {   // output rows: (channel, q, n * P + p); one box = one output row
+    cuuint64_t dims[3] = {64, (cuuint64_t)g.Q, (cuuint64_t)N * g.P};
+    cuuint64_t strides[2] = {128, (cuuint64_t)g.Q * 128};
+    cuuint32_t box[3] = {64, (cuuint32_t)g.Q, 1};
+    cuuint32_t estr3[3] = {1, 1, 1};
+    if (g_enc(&tmY, dt, 3, y, dims, strides, box, estr3, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return 10010;
+  }
+  {
+    cuuint64_t dims[2] = {16, (cuuint64_t)g.slots};
+    cuuint64_t strides[1] = {32};
+    cuuint32_t box[2] = {16, 256};
+    if (g_enc(&tmX, dt, 2, const_cast<void*>(xs), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return 10008;
+  }
+  {
+    cuuint64_t dims[2] = {256, 64};
+    cuuint64_t strides[1] = {512};
+    cuuint32_t box[2] = {16, 64};
+    if (g_enc(&tmW, dt, 2, const_cast<void*>(wp), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return 10009;
+  }
+  BnStats bs;
+  bs.enabled = scratch != nullptr;
+  bs.counter = reinterpret_cast<unsigned*>(scratch);
+  bs.partial = scratch ? reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + 256) : nullptr;
+  bs.running_mean = running_mean; bs.running_var = running_var;
+  bs.save_mean = save_mean; bs.save_invstd = save_invstd;
+  bs.momentum = momentum; bs.eps = eps;
+  bs.count = (long long)N * g.P * g.Q;
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int grid = g.num_tiles < sms ? g.num_tiles : sms;
+  if (dtype == PDT_FP16) {
+    auto kern = k_stem_conv<__half>;
+    PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SCfg::kSmemBytes));
+    kern<<<grid, kThreads, SCfg::kSmemBytes, stream>>>(tmX, tmW, tmY, g, bs);
+  } else {
+    auto kern = k_stem_conv<__nv_bfloat16>;
+    PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SCfg::kSmemBytes));
+    kern<<<grid, kThreads, SCfg::kSmemBytes, stream>>>(tmX, tmW, tmY, g, bs);
   }
   return (int)cudaGetLastError();
 }

@@ -14,7 +14,7 @@ import torch.nn as nn
 
 from .. import amp, ops
 from ..ops import bn as _bn_ops
-from ..parallel.syncbn import fused_bn, fused_bn_relu_maxpool, fused_conv_bn
+from ..parallel.syncbn import fused_bn, fused_bn_relu_maxpool, fused_conv_bn, fused_conv_bn_relu_maxpool
 
 
 def conv3x3(cin, cout, stride=1):
@@ -112,7 +112,7 @@ class ResNet(nn.Module):
         if self.training and torch.is_grad_enabled() and x.is_cuda:
             ops.prepare_backward(self.conv1.weight)     # data-gradient filter layouts of every conv, one launch
         with _bn_ops.batched_counters():       # one launch for all num_batches_tracked increments
-            x = fused_bn_relu_maxpool(self.bn1, ops.conv2d(x, self.conv1), 3, 2, 1)
+            x = fused_conv_bn_relu_maxpool(self.conv1, self.bn1, x, 3, 2, 1)
             x = self.layer4(self.layer3(self.layer2(self.layer1(x))))
         x = ops.global_avg_pool(x)
         return ops.linear(x, self.fc)

@@ -1,5 +1,5 @@
 """Functional ops: autograd.Functions over the sm_100a kernels, with torch oracles."""
-from .bn import bn_act, bn_relu_maxpool, conv_bn_act
+from .bn import bn_act, bn_relu_maxpool, conv_bn_act, conv_bn_relu_maxpool
 from .conv import conv2d, linear
 from . import conv_native  # noqa: F401  (registers the tcgen05 path with ops.conv)
 from .loss import CrossEntropyLoss, cross_entropy_with_accuracy
@@ -15,5 +15,5 @@ def prepare_backward(param):
         conv_native.prepare_dgrad_weights(arena)
 
 
-__all__ = ["bn_act", "bn_relu_maxpool", "conv_bn_act", "conv2d", "linear", "CrossEntropyLoss", "cross_entropy_with_accuracy",
+__all__ = ["bn_act", "bn_relu_maxpool", "conv_bn_act", "conv_bn_relu_maxpool", "conv2d", "linear", "CrossEntropyLoss", "cross_entropy_with_accuracy",
            "global_avg_pool", "max_pool2d"]

@@ -6,6 +6,8 @@ cross-rank exchange happens inside the statistics kernels).  Oracle / CPU path:
 Reference semantics: eps 1e-5, momentum 0.1, unbiased running variance
 (SURVEY §2.4 "Math that the fused kernels must match").
 """
+import os
+
 import torch
 import torch.distributed as dist
 import torch.nn.functional as F
@@ -148,21 +150,27 @@ class _BNReluPoolNative(torch.autograd.Function):
     """maxpool(relu(bn(x))) without ever writing the normalised tensor (ResNet stem tail)."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, running_mean, running_var, momentum, eps, ks, st, pd, comm):
+    def forward(ctx, x, weight, bias, running_mean, running_var, momentum, eps, ks, st, pd, comm, pre_mean=None,
+                pre_invstd=None):
         with _native.guard(x.device):
-            return _BNReluPoolNative._forward_impl(ctx, x, weight, bias, running_mean, running_var, momentum, eps, ks, st, pd, comm)
+            return _BNReluPoolNative._forward_impl(ctx, x, weight, bias, running_mean, running_var, momentum, eps, ks, st, pd,
+                                                   comm, pre_mean, pre_invstd)
 
     @staticmethod
-    def _forward_impl(ctx, x, weight, bias, running_mean, running_var, momentum, eps, ks, st, pd, comm):
+    def _forward_impl(ctx, x, weight, bias, running_mean, running_var, momentum, eps, ks, st, pd, comm, pre_mean=None,
+                      pre_invstd=None):
         N, C, H, W = x.shape
         x = x.contiguous(memory_format=torch.channels_last)
         lib, s, dt = _native.lib(), _native.stream_ptr(x.device), _native.dtype_code(x.dtype)
-        mean = torch.empty(C, dtype=torch.float32, device=x.device)
-        invstd = torch.empty_like(mean)
-        scratch = _bn_scratch(x.device, C)
-        _native.check(lib.pdt_bn_fwd_stats(x.data_ptr(), N * H * W, C, dt, scratch.data_ptr(), comm,
-                                           _native.ptr(running_mean), _native.ptr(running_var), momentum, eps,
-                                           mean.data_ptr(), invstd.data_ptr(), s), "pdt_bn_fwd_stats")
+        if pre_mean is not None:       # statistics (and running-stat update) came out of the convolution's epilogue
+            mean, invstd = pre_mean, pre_invstd
+        else:
+            mean = torch.empty(C, dtype=torch.float32, device=x.device)
+            invstd = torch.empty_like(mean)
+            scratch = _bn_scratch(x.device, C)
+            _native.check(lib.pdt_bn_fwd_stats(x.data_ptr(), N * H * W, C, dt, scratch.data_ptr(), comm,
+                                               _native.ptr(running_mean), _native.ptr(running_var), momentum, eps,
+                                               mean.data_ptr(), invstd.data_ptr(), s), "pdt_bn_fwd_stats")
         Ho, Wo = (H + 2 * pd - ks) // st + 1, (W + 2 * pd - ks) // st + 1
         y = torch.empty((N, C, Ho, Wo), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
         idx = torch.empty((N, Ho, Wo, C), dtype=torch.int8, device=x.device)
@@ -200,7 +208,7 @@ class _BNReluPoolNative(torch.autograd.Function):
             _native.check(lib.pdt_bn_pool_bwd_apply(dpool.data_ptr(), idx.data_ptr(), x.data_ptr(), dx.data_ptr(), dt, N, H, W,
                                                     C, ks, st, pd, mean.data_ptr(), invstd.data_ptr(), weight.data_ptr(),
                                                     bias.data_ptr(), k.data_ptr(), s), "pdt_bn_pool_bwd_apply")
-        return dx, dgamma, dbeta, None, None, None, None, None, None, None, None
+        return dx, dgamma, dbeta, None, None, None, None, None, None, None, None, None, None
 
 
 class _SyncStatsTorch(torch.autograd.Function):
@@ -297,6 +305,30 @@ def bn_relu_maxpool(x, bn, kernel_size=3, stride=2, padding=1, comm=None, group=
                                        kernel_size, stride, padding, comm if sync else None)
     from .pool import max_pool2d
     return max_pool2d(bn_act(x, bn, None, True, comm=comm, group=group), kernel_size, stride, padding)
+
+
+def conv_bn_relu_maxpool(x, conv, bn, kernel_size=3, stride=2, padding=1):
+    """``max_pool2d(relu(bn(conv(x))))`` (the ResNet stem).  On the native training path the convolution's
+    epilogue produces the BatchNorm statistics, so the 112x112x64 conv output is read once (by the fused
+    BN+ReLU+pool kernel) instead of twice."""
+    from .conv import conv2d
+    training = bn.training or bn.running_mean is None
+    fuse = (training and torch.is_grad_enabled() and x.is_cuda and _native.available() and bn.track_running_stats
+            and bn.affine and os.environ.get("PDT_BNSTATS_FUSION", "1") == "1")
+    if fuse:
+        momentum = 0.1 if bn.momentum is None else bn.momentum
+        out = conv2d(x, conv, bnpack=(bn.running_mean, bn.running_var, momentum, bn.eps))
+        if isinstance(out, tuple):
+            y, mean, invstd = out
+            C = y.shape[1]
+            if _native_ok(y, C) and y.dtype != torch.float32 and y.numel() // 8 < 4_000_000_000:
+                if bn.num_batches_tracked is not None:
+                    _bump(bn.num_batches_tracked)
+                return _BNReluPoolNative.apply(y, bn.weight, bn.bias, None, None, momentum, bn.eps, kernel_size, stride,
+                                               padding, None, mean, invstd)
+            raise RuntimeError("conv epilogue produced statistics for a shape the fused pool kernels do not serve")
+        return bn_relu_maxpool(out, bn, kernel_size, stride, padding)
+    return bn_relu_maxpool(conv2d(x, conv), bn, kernel_size, stride, padding)
 
 
 def conv_bn_act(x, conv, bn, residual=None, relu=False, comm=None, group=None):

@@ -66,7 +66,7 @@ def conv2d(x, conv, bnpack=None):
             w = (shadow_of(conv.weight, lp) if lp is not None else None)
             if w is None:
                 w = conv.weight.detach() if lp is None else conv.weight.detach().to(dtype=lp, memory_format=torch.channels_last)
-            return _stem_native[1](x, conv, w)
+            return _stem_native[1](x, conv, w, bnpack)
         from .input_norm import normalize_u8
         x = normalize_u8(x)
         if x.dim() == 4:
@@ -75,7 +75,7 @@ def conv2d(x, conv, bnpack=None):
         # fp32 training (DataParallel / plain DDP): tcgen05 kind::tf32 where torch would allow TF32
         w = conv.weight.detach()
         if _stem_native is not None and _stem_native[0](x, conv) and _tf32_on():
-            return _stem_native[1](x, conv, w)
+            return _stem_native[1](x, conv, w, bnpack)
         if _tf32_on() and x.dim() == 4:
             xc = x if x.is_contiguous(memory_format=torch.channels_last) else x.contiguous(memory_format=torch.channels_last)
             y = _conv_native(xc, conv.weight, w, conv.stride, conv.padding, bnpack)
@@ -87,7 +87,7 @@ def conv2d(x, conv, bnpack=None):
     if w_lp is None:
         w_lp = conv.weight.detach().to(dtype=lp, memory_format=torch.channels_last)
     if _stem_native is not None and _native.available() and _stem_native[0](x, conv):
-        return _stem_native[1](x, conv, w_lp)      # fp32 NCHW images: cast + layout change happen in the stem kernel
+        return _stem_native[1](x, conv, w_lp, bnpack)      # fp32 NCHW images: cast + layout change happen in the stem kernel
     if x.dtype != lp or not x.is_contiguous(memory_format=torch.channels_last):
         x = x.to(dtype=lp, memory_format=torch.channels_last)
     if _conv_native is not None and _native.available():

@@ -28,6 +28,8 @@ _native.register("pdt_conv_wgrad_ex", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _l
                                        _i, _i, _i, _i, _i, _i, _i, _vp])
 _native.register("pdt_stem_s2d", [_vp, _vp, _i, _i, _i, _i, _i, _vp])
 _native.register("pdt_stem_s2d_u8", [_vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _vp])
+_native.register("pdt_stem_conv_supported", [_i, _i, _i, _i, _i])
+_native.register("pdt_stem_conv", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _vp, _native._f, _native._f, _vp, _vp, _vp])
 _native.register("pdt_dgrad_weight", [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp])
 _native.register("pdt_dgrad_weight_batched", [_vp, _i, _i, _vp])
 _native.register("pdt_conv_fprop_bnstats", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp,
@@ -418,12 +420,13 @@ class _StemNative(torch.autograd.Function):
         return dict(C=32, S=2, dil=2, Wt=Q + 2, sw=px, sh=WP * px, sn=HP * WP * px)
 
     @staticmethod
-    def forward(ctx, x, weight, w_lp):
+    def forward(ctx, x, weight, w_lp, bnpack=None):
         with _native.guard(x.device):
-            return _StemNative._forward_impl(ctx, x, weight, w_lp)
+            return _StemNative._forward_impl(ctx, x, weight, w_lp, bnpack)
 
     @staticmethod
-    def _forward_impl(ctx, x, weight, w_lp):
+    def _forward_impl(ctx, x, weight, w_lp, bnpack=None):
+        ctx.set_materialize_grads(False)
         N, _, H, W = x.shape
         K = weight.shape[0]
         lp = w_lp.dtype
@@ -443,16 +446,42 @@ class _StemNative(torch.autograd.Function):
         wp = stem_weight_s2d(w_lp)
         y = torch.empty((N, K, P, Q), dtype=lp, device=x.device, memory_format=CL)
         g = _StemNative._geom(lp, HP, WP, Q)
-        fprop_ex(xs.data_ptr(), wp, y, None, lp, N, HP, g["Wt"], g["C"], g["C"], g["sw"], g["sh"], g["sn"], K, 4, g["S"], 1,
-                 (0, 0, 0, 0), P, Q, P, Q, 1, 0, 0, x.device, dil_w=g["dil"])
+        lib = _native.lib()
+        if (os.environ.get("PDT_STEM_CONV", "patch") == "patch"
+                and lib.pdt_stem_conv_supported(_native.dtype_code(lp), N, HP, WP, K) == 1):
+            # one linear TMA load per tile, sixteen row-shifted 32-byte-swizzled views (conv_halo.cu: k_stem_conv);
+            # with bnpack = (running_mean, running_var, momentum, eps) its epilogue also produces the batch statistics
+            stats = None
+            if bnpack is not None:
+                from .bn import _bn_scratch
+                rm, rv, momentum, eps = bnpack
+                mean = torch.empty(K, dtype=torch.float32, device=x.device)
+                invstd = torch.empty_like(mean)
+                stats = (mean, invstd)
+                _native.check(lib.pdt_stem_conv(xs.data_ptr(), wp.data_ptr(), y.data_ptr(), _native.dtype_code(lp), N, HP, WP, K,
+                                                _bn_scratch(x.device, K).data_ptr(), _native.ptr(rm), _native.ptr(rv),
+                                                momentum, eps, mean.data_ptr(), invstd.data_ptr(),
+                                                _native.stream_ptr(x.device)), "pdt_stem_conv")
+            else:
+                _native.check(lib.pdt_stem_conv(xs.data_ptr(), wp.data_ptr(), y.data_ptr(), _native.dtype_code(lp), N, HP, WP, K,
+                                                None, None, None, 0.1, 1e-5, None, None, _native.stream_ptr(x.device)),
+                              "pdt_stem_conv")
+            if stats is not None:
+                ctx.save_for_backward(xs)
+                ctx.geom = (N, HP, WP, P, Q, K)
+                ctx.mark_non_differentiable(*stats)
+                return y, stats[0], stats[1]
+        else:
+            fprop_ex(xs.data_ptr(), wp, y, None, lp, N, HP, g["Wt"], g["C"], g["C"], g["sw"], g["sh"], g["sn"], K, 4, g["S"], 1,
+                     (0, 0, 0, 0), P, Q, P, Q, 1, 0, 0, x.device, dil_w=g["dil"])
         ctx.save_for_backward(xs)
         ctx.geom = (N, HP, WP, P, Q, K)
         return y
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, *unused_stat_grads):
         with _native.guard(dy.device):
-            return _StemNative._backward_impl(ctx, dy)
+            return _StemNative._backward_impl(ctx, dy) + (None,)
 
     @staticmethod
     def _backward_impl(ctx, dy):
@@ -475,8 +504,9 @@ class _StemNative(torch.autograd.Function):
         return None, stem_weight_grad_from_s2d(dwp, K), None
 
 
-def stem_native(x, conv, w_lp):
-    return _StemNative.apply(x, conv.weight, w_lp)
+def stem_native(x, conv, w_lp, bnpack=None):
+    """bnpack as in conv_native(): returns (y, mean, invstd) when the patch kernel could fuse the statistics."""
+    return _StemNative.apply(x, conv.weight, w_lp, bnpack)
 
 
 # ------------------------------------------------------------------------------------------ linear

@@ -81,6 +81,14 @@ def fused_bn_relu_maxpool(bn, x, kernel_size=3, stride=2, padding=1):
     return ops.bn_relu_maxpool(x, bn, kernel_size, stride, padding)
 
 
+def fused_conv_bn_relu_maxpool(conv, bn, x, kernel_size=3, stride=2, padding=1):
+    """Stem ``maxpool(relu(bn(conv(x))))`` (SyncBN aware): plain BatchNorm takes its statistics from the stem
+    convolution's epilogue, SyncBatchNorm from its own exchanging statistics kernel."""
+    if isinstance(bn, SyncBatchNorm) and bn.training:
+        return fused_bn_relu_maxpool(bn, ops.conv2d(x, conv), kernel_size, stride, padding)
+    return ops.conv_bn_relu_maxpool(x, conv, bn, kernel_size, stride, padding)
+
+
 def fused_conv_bn(conv, bn, x, residual=None, relu=False):
     """``relu?(bn(conv(x)) + residual?)`` (SyncBN aware): plain BatchNorm gets its statistics from the
     convolution's epilogue, SyncBatchNorm from its own exchanging statistics kernel."""
