@@ -49,7 +49,9 @@ def _native_ok(x, C):
     return C % v == 0 and cg >= 1 and (cg & (cg - 1)) == 0 and cg <= 512 and 2 * C <= 4608
 
 
-_pending_counters = None
+import threading
+
+_tls = threading.local()     # DataParallel runs replicas in worker threads: the pending list is per thread
 
 
 class batched_counters:
@@ -57,14 +59,12 @@ class batched_counters:
     ONE multi-tensor launch on exit (20 one-element launches per ResNet-18 forward otherwise)."""
 
     def __enter__(self):
-        global _pending_counters
-        self._outer = _pending_counters
-        _pending_counters = []
+        self._outer = getattr(_tls, "pending", None)
+        _tls.pending = []
         return self
 
     def __exit__(self, *exc):
-        global _pending_counters
-        pending, _pending_counters = _pending_counters, self._outer
+        pending, _tls.pending = _tls.pending, self._outer
         if pending:
             if self._outer is not None:
                 self._outer.extend(pending)
@@ -77,10 +77,11 @@ class batched_counters:
 
 
 def _bump(counter):
-    if _pending_counters is None:
+    pending = getattr(_tls, "pending", None)
+    if pending is None:
         counter.add_(1)
     else:
-        _pending_counters.append(counter)
+        pending.append(counter)
 
 
 class _BNActNative(torch.autograd.Function):
