@@ -15,6 +15,8 @@ Conv weights are stored KRSC (channels_last of the logical OIHW tensor): that
 is what the implicit-GEMM kernels and TMA want, and ``state_dict`` IO is
 layout-agnostic.
 """
+import os
+
 import torch
 
 from .fabric import Fabric
@@ -35,6 +37,9 @@ class Segment:
     @property
     def length(self):
         return self.end - self.start
+
+
+_DIRECT = os.environ.get("PDT_DIRECT_GRAD", "1") == "1"     # 0: backward kernels never write into the arena themselves
 
 
 class ParamArena:
@@ -150,7 +155,7 @@ class ParamArena:
     def direct_grad(self, p):
         """A fresh view of ``p``'s slot in the gradient arena if a backward kernel may write (accumulate)
         into it directly, else None."""
-        if not self.grads_zeroed or p.grad is not None or id(p) not in self.offset:
+        if not self.grads_zeroed or p.grad is not None or id(p) not in self.offset or not _DIRECT:
             return None
         return self.grad_view(p)
 

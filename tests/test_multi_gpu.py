@@ -86,6 +86,13 @@ def test_dataparallel_matches_manual_replicas(native_lib):
     torch.manual_seed(21)
     net = create_model("resnet18", num_classes=10)
     manual = [copy.deepcopy(net).to("cuda:%d" % d) for d in range(n)]
+    # the parameter arena stores convolution weights KRSC (channels_last views); give the oracle replicas the
+    # same layout so aten picks the same convolution algorithms: with 8 images per replica the BatchNorm
+    # layers amplify algorithm-level rounding differences into percent-level gradient differences
+    for m in manual:
+        for p in m.parameters():
+            if p.dim() == 4:
+                p.data = p.data.contiguous(memory_format=torch.channels_last)
     tv = torchvision.models.resnet18(num_classes=10)
     tv.load_state_dict(net.state_dict())
     theirs = torch.nn.DataParallel(tv, device_ids=list(range(n))).cuda()
@@ -93,7 +100,17 @@ def test_dataparallel_matches_manual_replicas(native_lib):
     opt = optim.SGD(ours.parameters(), 0.01, momentum=0.9, weight_decay=1e-4)
     g = torch.Generator().manual_seed(3)
     mom = None
+    names = [k for k, _ in ours.module.named_parameters()]
     for it in range(2):
+        # The oracle replicas start EVERY iteration from our current parameters, bit for bit.  With 8 images per
+        # replica the weight gradients in front of a BatchNorm are small differences of large sums: a 1e-7
+        # difference in the weights (our fused SGD kernel vs the torch formula below) moved some of them by
+        # several percent in the second iteration, which says nothing about DataParallel.
+        with torch.no_grad():
+            for m in manual:
+                for q, p in zip(m.parameters(), ours.module.parameters()):
+                    q.copy_(p.detach().to(q.device))
+        prev = [p.detach().clone() for p in ours.module.parameters()]
         x = torch.randn(8 * n, 3, 64, 64, generator=g).cuda()
         y = torch.randint(0, 10, (8 * n,), generator=g).cuda()
         ours.train()
@@ -117,24 +134,26 @@ def test_dataparallel_matches_manual_replicas(native_lib):
         for d in range(n):
             torch.cuda.synchronize(d)
         gsum = [sum(p.grad.to("cuda:0") for p in ps) for ps in zip(*[m.parameters() for m in manual])]
+        # gradients as autograd left them on every replica, before the fused reduce + SGD kernels see them
+        gours = [sum(p.grad.to("cuda:0") for p in ps) for ps in zip(*[r.parameters() for r in ours.replicas])]
+        gerr = sorted(((rel(a, b), k) for k, a, b in zip(names, gours, gsum)), reverse=True)
+        assert gerr[0][0] < 1e-3, ("backward", it, gerr[:4])
         opt.step()
         for d in range(n):
             torch.cuda.synchronize(d)
-        # manual momentum SGD on every manual replica
-        if mom is None:
-            mom = [torch.zeros_like(gs) for gs in gsum]
+        # torch.optim.SGD(momentum=0.9, weight_decay=1e-4) by hand on the summed oracle gradients
+        expected = []
         with torch.no_grad():
+            if mom is None:
+                mom = [None] * len(gsum)
             for i, gs in enumerate(gsum):
-                p0 = manual[0].parameters().__iter__()
-            params0 = list(manual[0].parameters())
-            for i, gs in enumerate(gsum):
-                d_p = gs + 1e-4 * params0[i]
-                mom[i] = 0.9 * mom[i] + d_p if it > 0 else d_p.clone()
-                new = params0[i] - 0.01 * mom[i]
-                for m in manual:
-                    list(m.parameters())[i].copy_(new.to(list(m.parameters())[i].device))
-        worst = max(rel(p.detach(), q.detach()) for p, q in zip(ours.module.parameters(), manual[0].parameters()))
-        assert worst < 1e-4, (it, worst)
+                d_p = gs + 1e-4 * prev[i]
+                mom[i] = d_p.clone() if mom[i] is None else 0.9 * mom[i] + d_p
+                expected.append(prev[i] - 0.01 * mom[i])
+        # the UPDATE must agree: error relative to the size of the step, per tensor
+        errs = sorted((((p.detach() - e).abs().max() / ((e - q).abs().max() + 1e-12)).item(), k)
+                      for k, p, e, q in zip(names, ours.module.parameters(), expected, prev))
+        assert errs[-1][0] < 2e-3, (it, errs[-4:])
         for rep in ours.replicas[1:]:       # the optimizer kernel pushed the new weights into every replica
             for p, q in zip(rep.parameters(), ours.module.parameters()):
                 assert torch.equal(p.detach().cpu(), q.detach().cpu())
