@@ -17,6 +17,10 @@
 #include <stdint.h>
 #include <cuda_runtime_api.h>
 
+/* Bumped whenever an entry point is added or changes its signature; the Python binding refuses a library
+ * that reports a different number (a stale build of an older checkout). */
+#define PDT_ABI_VERSION 9
+
 #ifdef __cplusplus
 extern "C" {
 #endif
@@ -171,6 +175,7 @@ int pdt_nchw_to_nhwc(const float* x, void* y, int dtype, int N, int Cin, int H, 
 /* Destination-side pull of `nbytes` from a peer-mapped pointer (DataParallel scatter / gather /
  * buffer broadcast; torch.cuda.comm.scatter/gather/broadcast_coalesced, dataparallel.py:119). */
 int pdt_peer_copy(const void* src, void* dst, size_t nbytes, cudaStream_t stream);
+int pdt_abi_version(void);
 
 /* ---- implicit-GEMM convolution on tcgen05 / TMEM / TMA --------------------
  * x: [N][H][W][C], w: [K][R][S][C] (KRSC), y: [N][P][Q][K], all bf16, fp16 (kind::f16) or fp32

@@ -514,3 +514,5 @@ extern "C" int pdt_dgrad_weight_batched(const PdtDgradJob* jobs_dev, int njobs, 
   k_dgrad_weight_batched<<<total_tiles, 256, 0, stream>>>(jobs_dev, njobs);
   return (int)cudaGetLastError();
 }
+
+extern "C" int pdt_abi_version(void) { return PDT_ABI_VERSION; }

@@ -82,12 +82,55 @@ _SIGNATURES = {
 }
 
 
+def _header_abi():
+    import re
+    hdr = os.path.join(os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))), "include", "pdt_b200.h")
+    try:
+        m = re.search(r"#define\s+PDT_ABI_VERSION\s+(\d+)", open(hdr).read())
+        return int(m.group(1)) if m else None
+    except OSError:
+        return None
+
+
+def _rebuild_if_stale():
+    """Sources newer than the library (a fresh checkout, an edited kernel) and nvcc at hand: build before loading.
+    Ranks of one node serialise on a lock file; whoever comes second finds the library fresh."""
+    if os.environ.get("PDT_NO_AUTOBUILD", "0") == "1":
+        return
+    try:
+        from .. import build as _build
+        import fcntl
+        import glob
+        srcs = glob.glob(os.path.join(_build.CSRC, "*.cu")) + glob.glob(os.path.join(_build.CSRC, "*.cuh")) \
+            + glob.glob(os.path.join(_build.INCLUDE, "*.h"))
+        newest = max(os.path.getmtime(f) for f in srcs)
+        if os.path.exists(LIB_PATH) and os.path.getmtime(LIB_PATH) >= newest:
+            return
+        _build.nvcc_path()                       # raises when there is no compiler: keep whatever is there
+        os.makedirs(os.path.dirname(LIB_PATH), exist_ok=True)
+        with open(LIB_PATH + ".lock", "w") as lock:
+            fcntl.flock(lock, fcntl.LOCK_EX)
+            try:
+                if not (os.path.exists(LIB_PATH) and os.path.getmtime(LIB_PATH) >= newest):
+                    _build.build()
+            finally:
+                fcntl.flock(lock, fcntl.LOCK_UN)
+    except Exception:                            # no compiler / read-only tree: the load below reports what is wrong
+        pass
+
+
 def _load():
     global _lib, _load_error
     if _lib is not None or _load_error is not None:
         return _lib
+    _rebuild_if_stale()
     try:
         lib = ctypes.CDLL(LIB_PATH)
+        want = _header_abi()
+        have = lib.pdt_abi_version() if hasattr(lib, "pdt_abi_version") else None
+        if want is not None and have != want:
+            raise OSError("{} reports ABI {} but include/pdt_b200.h is at {}: stale build, run "
+                          "`python -m pytorch_distributed_template_b200.build`".format(LIB_PATH, have, want))
         for name, (argtypes, restype) in _SIGNATURES.items():
             fn = getattr(lib, name, None)
             if fn is None:

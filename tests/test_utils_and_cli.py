@@ -195,3 +195,18 @@ def test_uint8_input_pipeline_cpu():
         assert torch.allclose(input_norm.normalize_u8(x8), (x8.float() / 255 - 0.5) / 0.25, rtol=1e-5, atol=1e-5)
     finally:
         input_norm.set_input_norm(input_norm.IMAGENET_MEAN, input_norm.IMAGENET_STD)
+
+
+def test_native_library_abi_matches_header():
+    """The in-tree library (when built) reports the ABI number of include/pdt_b200.h; a stale build of an
+    older checkout is refused with a clear message instead of failing later on a missing symbol."""
+    import os
+    from pytorch_distributed_template_b200.ops import _native
+    want = _native._header_abi()
+    assert isinstance(want, int) and want >= 1
+    if not os.path.exists(_native.LIB_PATH):
+        import pytest
+        pytest.skip("library not built")
+    lib = _native._load()
+    assert lib is not None, _native._load_error
+    assert lib.pdt_abi_version() == want
