@@ -7,6 +7,7 @@ for all three scripts); this file only owns the parser and ``main()``.
 """
 from pytorch_distributed_template_b200 import trainer
 from pytorch_distributed_template_b200.config import build_parser
+from pytorch_distributed_template_b200.utils import reduce_mean  # noqa: F401  (module-level helper of the reference script)
 
 MODE = "ddp_amp"
 parser = build_parser(MODE)

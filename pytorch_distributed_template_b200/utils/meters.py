@@ -84,3 +84,15 @@ def accuracy(scores, targets, k=1):
     _, ind = scores.topk(k, 1, True, True)
     hit = ind.eq(targets.long().view(-1, 1).expand_as(ind))
     return hit.reshape(-1).float().sum() * (1.0 / batch_size)
+
+
+def reduce_mean(tensor, nprocs):
+    """Mean of ``tensor`` over the ranks: clone -> all_reduce(SUM) -> / nprocs, the reference's helper
+    (/root/reference/distributed.py:78-82).  The trainer itself packs loss and accuracy into one 8-byte
+    device all-reduce (``trainer._reduce_pair``); this is the same operation for user code."""
+    import torch.distributed as dist
+    rt = tensor.clone()
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+        dist.all_reduce(rt, op=dist.ReduceOp.SUM)
+    rt /= nprocs
+    return rt

@@ -210,3 +210,25 @@ def test_native_library_abi_matches_header():
     lib = _native._load()
     assert lib is not None, _native._load_error
     assert lib.pdt_abi_version() == want
+
+
+def test_start_sh_and_reduce_mean():
+    """start.sh: LF endings, the reference's three runs through torchrun on 127.0.0.1; reduce_mean is importable
+    from the scripts like in the reference and is the identity (divided by nprocs) without a process group."""
+    import os
+    import torch
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    raw = open(os.path.join(root, "start.sh"), "rb").read()
+    assert b"\r" not in raw
+    text = raw.decode()
+    for script in ("dataparallel.py", "distributed.py", "distributed_syncBN_amp.py"):
+        assert script in text
+    assert "torch.distributed.run" in text or "torchrun" in text
+    assert "127.0.0.1" in text
+    import distributed
+    import distributed_syncBN_amp
+    from pytorch_distributed_template_b200.utils import reduce_mean
+    assert distributed.reduce_mean is reduce_mean and distributed_syncBN_amp.reduce_mean is reduce_mean
+    t = torch.tensor([2.0, 4.0])
+    out = reduce_mean(t, 2)
+    assert torch.equal(out, torch.tensor([1.0, 2.0])) and torch.equal(t, torch.tensor([2.0, 4.0]))
