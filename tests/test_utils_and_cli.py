@@ -232,3 +232,32 @@ def test_start_sh_and_reduce_mean():
     t = torch.tensor([2.0, 4.0])
     out = reduce_mean(t, 2)
     assert torch.equal(out, torch.tensor([1.0, 2.0])) and torch.equal(t, torch.tensor([2.0, 4.0]))
+
+
+def test_imagefolder_uint8_pipeline_equals_host_normalisation(tmp_path):
+    """ImageFolder pipelines (the reference's transforms): the uint8 variant stops before ToTensor/Normalize and
+    device-side normalisation of its output equals the host-side float pipeline (deterministic val transform)."""
+    import numpy as np
+    import torch
+    PIL = pytest.importorskip("PIL.Image")
+    from pytorch_distributed_template_b200 import data
+    from pytorch_distributed_template_b200.ops import input_norm
+    rng = np.random.RandomState(0)
+    for split in ("train", "val"):
+        for cls in ("a", "b"):
+            d = tmp_path / split / cls
+            d.mkdir(parents=True)
+            for i in range(2):
+                PIL.fromarray(rng.randint(0, 256, (300, 260, 3), dtype=np.uint8)).save(str(d / ("%d.png" % i)))
+    tr8, va8 = data.imagefolder_datasets(str(tmp_path), uint8=True)
+    trf, vaf = data.imagefolder_datasets(str(tmp_path), uint8=False)
+    assert len(tr8) == len(trf) == 4 and len(va8) == 4
+    x8, y8 = va8[1]
+    xf, yf = vaf[1]
+    assert x8.dtype == torch.uint8 and x8.shape == (3, 224, 224) and xf.dtype == torch.float32 and y8 == yf
+    assert torch.allclose(input_norm.normalize_u8(x8[None])[0], xf, rtol=1e-5, atol=1e-5)
+    t8, _ = tr8[0]
+    assert t8.dtype == torch.uint8 and t8.shape == (3, 224, 224)
+    loader = data.build_loader(va8, 2, 0, shuffle=False, pin=False)
+    xb, yb = next(iter(loader))
+    assert xb.dtype == torch.uint8 and xb.shape == (2, 3, 224, 224) and yb.dtype == torch.int64
