@@ -78,3 +78,40 @@ def test_grad_scaler_state_machine():
     assert off.scale(t) is t and off.get_scale() == 1.0
     sd = sc.state_dict()
     assert set(sd) == {"scale", "growth_factor", "backoff_factor", "growth_interval", "_growth_tracker"}
+
+
+def test_batched_counters_are_per_thread():
+    """num_batches_tracked increments deferred by ops.bn.batched_counters: applied once on exit, nested contexts
+    hand their list to the outer one, and worker threads (DataParallel replicas) never see each other's list."""
+    import threading
+    import torch
+    from pytorch_distributed_template_b200.ops import bn as bnops
+
+    a, b, c = (torch.zeros((), dtype=torch.long) for _ in range(3))
+    with bnops.batched_counters():
+        bnops._bump(a)
+        with bnops.batched_counters():
+            bnops._bump(b)
+        assert a.item() == 0 and b.item() == 0          # deferred to the outermost exit
+    assert a.item() == 1 and b.item() == 1
+    bnops._bump(c)                                       # outside any context: immediate
+    assert c.item() == 1
+
+    counters = [torch.zeros((), dtype=torch.long) for _ in range(4)]
+    barrier = threading.Barrier(4)
+
+    def worker(t):
+        with bnops.batched_counters():
+            barrier.wait()                               # all four contexts are open at the same time
+            for _ in range(5):
+                bnops._bump(t)
+            barrier.wait()
+        # every thread applied exactly its own increments
+
+    threads = [threading.Thread(target=worker, args=(t,)) for t in counters]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join()
+    assert [int(t) for t in counters] == [5, 5, 5, 5]
+    assert getattr(bnops._tls, "pending", None) is None
