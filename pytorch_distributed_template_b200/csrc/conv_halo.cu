@@ -1,5 +1,11 @@
-// 3x3 / stride 1 / pad 1 convolution with input-patch reuse (SURVEY K-CONV-F/-D for the large feature maps).
+// Patch-reuse convolution kernels (SURVEY K-CONV-F / -D / -W for the large feature maps).  Three kernels share
+// one idea — load a contiguous input patch ONCE and form every filter tap as a row-shifted shared-memory
+// descriptor on it:
+//   k_conv3x3_halo   3x3 / 1 / 1 forward and data gradient, 64- and 128-channel layers   (pdt_conv3x3_halo)
+//   k_wgrad3x3_halo  3x3 / 1 / 1 weight gradient, 64 -> 64 channels, two taps per MMA     (pdt_conv3x3_wgrad_halo)
+//   k_stem_conv      the 7x7 / 2 stem as 4x4 / 1 over the space-to-depth image            (pdt_stem_conv)
 //
+// k_conv3x3_halo:
 // The generic implicit-GEMM kernel (conv.cu) fetches the activation once PER FILTER TAP (9 TMA im2col loads
 // per 64-channel block).  On the 56x56 and 28x28 layers that makes the L2 -> SM fabric (about 42 B/clk per
 // SM), not the tensor core, the limit: ncu shows 22 % tensor-pipe utilisation at 128x64 tiles.
