@@ -1109,6 +1109,7 @@ int pdt_stem_conv_supported(int dtype, int N, int HP, int WP, int K) {
   if (dtype != PDT_BF16 && dtype != PDT_FP16) return 0;
   if (K != 64 || WP < 4 || HP < 4 || WP > 127 || N < 1) return 0;      // WP <= 127: row fits a 128-slot tile and the 512-pixel patch
   if ((long long)N * HP * WP > 2000000000ll) return 0;
+  if ((long long)N * HP * WP < 512) return 0;      // the patch loads use 256-pixel boxes: tiny inputs take the generic kernel
   return 1;
 }
 
