@@ -127,11 +127,14 @@ class _FakeFolder:
         raise RuntimeError("synthetic batches are produced by the loader")
 
 
-def run_reference(mode, per_process_batch_total, steps, warmup, on_timed_region=None):
+def run_reference(mode, per_process_batch_total, steps, warmup, on_timed_region=None, extra_argv=None,
+                  model_factory=None, print_freq=1000000):
     """Run one reference script for ``warmup + steps`` training iterations.
 
     ``per_process_batch_total`` is the value for ``-b`` (TOTAL batch, the script divides it).
-    Returns the loader's timing dict.
+    Returns the loader's timing dict (+ ``outpath``, the directory the script logged into).
+    ``model_factory`` (parity tests): what ``models.__dict__[arch]()`` returns inside the script, so both arms
+    start from the same weights; ``extra_argv`` appends flags of the script's own CLI (e.g. ``--lr``).
     """
     module_name, extra = MODES[mode]
     if REF_DIR not in sys.path:
@@ -164,9 +167,12 @@ def run_reference(mode, per_process_batch_total, steps, warmup, on_timed_region=
     # names as the script itself sees them; torchvision / torch stay untouched
     ref.datasets = types.SimpleNamespace(ImageFolder=_FakeFolder)
     ref.DataLoader = fake_loader
+    if model_factory is not None:
+        ref.models = types.SimpleNamespace(resnet18=model_factory)
     out = tempfile.mkdtemp(prefix="pdt_ref_{}_".format(mode))
     argv = [module_name + ".py", "--epochs", "1", "-b", str(per_process_batch_total), "-j", "0",
-            "--outpath", os.path.join(out, "run"), "--data", "/nonexistent", "-p", "1000000"] + extra
+            "--outpath", os.path.join(out, "run"), "--data", "/nonexistent", "-p", str(print_freq)] + extra \
+        + list(extra_argv or [])
     if mode != "dp":
         argv.append("--local_rank={}".format(local_rank))
     old_argv = sys.argv
@@ -178,4 +184,5 @@ def run_reference(mode, per_process_batch_total, steps, warmup, on_timed_region=
     res = dict(holder["train"].result)
     res["per_loader_batch"] = per_loader_batch
     res["world"] = world
+    res["outpath"] = os.path.join(out, "run") + "_resnet18"
     return res

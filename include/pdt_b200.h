@@ -19,7 +19,7 @@
 
 /* Bumped whenever an entry point is added or changes its signature; the Python binding refuses a library
  * that reports a different number (a stale build of an older checkout). */
-#define PDT_ABI_VERSION 9
+#define PDT_ABI_VERSION 10
 
 #ifdef __cplusplus
 extern "C" {
@@ -47,9 +47,17 @@ typedef struct PdtPeers { void* p[PDT_MAX_RANKS]; } PdtPeers;   /* same VA range
 #endif
 
 typedef struct PdtCommDesc {
-  int rank, world;
+  int rank, world;            /* world: any value in 1..PDT_MAX_RANKS (the reference ships a 3-GPU launch, start.sh:2-4) */
   void* pad[PDT_MAX_RANKS];   /* PDT_PAD_BYTES each, zero-initialised once */
+  void* pad_mc;               /* the pad through an NVLS multicast mapping (all ranks at once), or NULL */
 } PdtCommDesc;
+
+/* Up to PDT_MAX_SEGMENTS ranges [off, off+len) of a flat fp32 arena, in elements (host struct). */
+#define PDT_MAX_SEGMENTS 8
+typedef struct PdtSegments {
+  int n;
+  size_t off[PDT_MAX_SEGMENTS], len[PDT_MAX_SEGMENTS];
+} PdtSegments;
 
 size_t pdt_comm_pad_bytes(void);
 
@@ -61,15 +69,19 @@ size_t pdt_comm_pad_bytes(void);
 /* Gradient bucket all-reduce, first half (c10d Reducer + ncclAllReduce at
  * distributed.py:262) fused with 1/world, AMP unscale and inf check
  * (_amp_foreach_non_finite_check_and_unscale_, distributed_syncBN_amp.py:276). */
-int pdt_reduce_scatter_f32(const PdtCommDesc* comm, const PdtPeers* grads, size_t seg_off, size_t seg_len,
-                           float* amp_state, int use_flags, int blocks, cudaStream_t stream);
+/* grads_mc: the gradient arena through its NVLS multicast mapping, or NULL.  With it the W-way sum of a
+ * 16-byte slot is ONE multimem.ld_reduce through the switch instead of W peer loads.  seg_len % (4 * world) == 0. */
+int pdt_reduce_scatter_f32(const PdtCommDesc* comm, const PdtPeers* grads, const void* grads_mc, size_t seg_off,
+                           size_t seg_len, float* amp_state, int use_flags, int blocks, cudaStream_t stream);
 
 /* Second half: inf consensus + momentum SGD (torch/optim/sgd.py:343-380) on the
  * owned shard + store of fp32 weights and low-precision shadow to every rank
- * (optimizer.step() at distributed.py:263; autocast weight casts). */
+ * (optimizer.step() at distributed.py:263; autocast weight casts).
+ * All segments of the arena are served by ONE launch.  params_mc / shadow_mc: multicast mappings of the two
+ * arenas (or NULL): each updated 16 bytes then leave this GPU once (multimem.st) instead of once per rank. */
 int pdt_sgd_allgather(const PdtCommDesc* comm, const PdtPeers* grads, const PdtPeers* params, const PdtPeers* shadow,
-                      int shadow_dtype, float* momentum, size_t seg_off, size_t seg_len, const float* hyper,
-                      float* amp_state, int use_flags, int blocks, cudaStream_t stream);
+                      void* params_mc, void* shadow_mc, int shadow_dtype, float* momentum, const PdtSegments* segments,
+                      const float* hyper, float* amp_state, int use_flags, int blocks, cudaStream_t stream);
 
 /* In-place two-shot all-reduce (dist.all_reduce, distributed.py:80). */
 int pdt_allreduce_f32(const PdtCommDesc* comm, const PdtPeers* bufs, size_t off, size_t len, float post_scale,
@@ -79,6 +91,11 @@ int pdt_allreduce_f32(const PdtCommDesc* comm, const PdtPeers* bufs, size_t off,
  * reduce_mean(acc1) and the barrier before them (distributed.py:253-255). */
 int pdt_allreduce_small_f32(const PdtCommDesc* comm, const float* in, float* out, int n, float post_scale,
                             int channel, cudaStream_t stream);
+/* The same exchange for n <= 1024 metrics, followed by AverageMeter.update on the device
+ * (losses.update / top1.update, distributed.py:257-258): meter[0..n) += out * weight, meter[n] += weight,
+ * meter[n+1 .. 2n+1) = out.  comm == NULL or world == 1: no exchange, just the meter update. */
+int pdt_metrics_update(const PdtCommDesc* comm, const float* in, float* out, int n, float post_scale, int channel,
+                       float* meter, float weight, cudaStream_t stream);
 
 /* Pull [off, off+len) of the root's arena into every rank's arena (DDP
  * constructor _sync_module_states and per-forward _sync_buffers,
@@ -91,6 +108,20 @@ int pdt_barrier(const PdtCommDesc* comm, int channel, cudaStream_t stream);
 
 /* GradScaler.update() (_amp_update_scale_, distributed_syncBN_amp.py:277). */
 int pdt_scale_update(float* amp_state, float growth, float backoff, int interval, cudaStream_t stream);
+
+/* Rank emulation for tests (no reference counterpart): the reduce-scatter, SGD/all-gather,
+ * small all-reduce and broadcast bodies run for ALL `world` ranks inside one cooperative launch on one GPU
+ * (rank = blockIdx.y), every rank's arena / pad / state a separate buffer of that GPU.  P2P data plane. */
+typedef struct PdtEmuRanks {
+  void* pad[PDT_MAX_RANKS];
+  float* amp_state[PDT_MAX_RANKS];
+  float* momentum[PDT_MAX_RANKS];
+  float* io[PDT_MAX_RANKS];
+} PdtEmuRanks;
+int pdt_emu_step(const PdtEmuRanks* ranks, int world, const PdtPeers* grads, const PdtPeers* params, const PdtPeers* shadow,
+                 const PdtSegments* segments, const float* hyper, int blocks, cudaStream_t stream);
+int pdt_emu_small(const PdtEmuRanks* ranks, int world, int n, float post_scale, const PdtPeers* bufs, size_t len_bytes,
+                  int root, cudaStream_t stream);
 
 /* foreach momentum SGD on one flat arena (torch/optim/sgd.py:383-477). */
 int pdt_sgd_flat(float* p, const float* g, float* m, void* shadow, int shadow_dtype, size_t n, const float* hyper,
@@ -117,7 +148,8 @@ int pdt_bn_fwd_stats(const void* x, long M, int C, int dtype, void* scratch, con
  *   limit   : C <= PDT_BN_STATIC_MAX_C, else PDT_E_TOO_LARGE; each GPU that loads the library keeps
  *             PDT_BN_STATIC_SCRATCH_BYTES resident until exit;
  *   sharing : all calls on a device use the same array; calls that may overlap on the GPU race;
- *   set-up  : the first call on each device looks the array's address up — do it before any stream capture.
+ *   set-up  : the first call on each device looks the array's address up (safe from several host threads at
+ *             once: the cached pointer is published atomically) — do it before any stream capture.
  * Calls no cudaMalloc / cudaFree / allocating routine. */
 #define PDT_BN_STATIC_MAX_C 512
 #define PDT_BN_STATIC_SCRATCH_BYTES (256 + PDT_BN_MAX_BLOCKS * 2 * PDT_BN_STATIC_MAX_C * 4)
@@ -219,6 +251,11 @@ int pdt_stem_conv(const void* xs, const void* wp, void* y, int dtype, int N, int
  * the pixel dimension with red.global.add, so zero dw first.  C % 64 == 0, K % 64 == 0. */
 int pdt_conv_wgrad(const void* x, const void* dy, float* dw, int dtype, int N, int H, int W, int C, int K, int R, int S,
                    int stride, int pad, cudaStream_t stream);
+/* Deterministic weight gradients on the CURRENT device (the reference's --seed turns on cudnn.deterministic,
+ * distributed.py:91-99): with a workspace registered, split-K partial tiles are stored into slabs of it and
+ * folded in a fixed order instead of red.global.add, and the atomics-based patch-reuse kernel is bypassed.
+ * ws == NULL restores the default.  Launches sharing the workspace must be stream-ordered. */
+int pdt_set_wgrad_workspace(void* ws, size_t bytes);
 /* General forms: fp32 bias [K] in the epilogue (nn.Linear as a 1x1 convolution, cuBLASLt GEMM + bias);
  * separate lower/upper padding with an explicit output size; placement of output pixel (p,q) at
  * (p*os + oa, q*os + ob) of an OH x OW image (one parity class of a strided data gradient, cuDNN strided

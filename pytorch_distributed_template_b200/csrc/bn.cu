@@ -21,6 +21,7 @@
 // (scratch, [blocks][2C] floats); the block that takes the last ticket of `counter`
 // (scratch, one word, self-resetting) folds the rows in a fixed order in fp64, so the
 // result is deterministic for a given grid.
+#include <atomic>
 #include <cstdlib>
 #include <initializer_list>
 #include "fabric.cuh"
@@ -100,11 +101,27 @@ __device__ __forceinline__ void fold_partials(double* tot, const float* __restri
 }
 
 // Cross-rank sum of tot[0..n) (+ the count) through the peers' scratch slots; one block per rank.
+// With an NVLS mapping of the pad, this rank's vector reaches every peer's slot through ONE 16-byte multimem.st
+// per four values (the switch replicates it) instead of `world` scalar peer stores per value.  Every rank then
+// sums the slots in rank order, so all ranks compute bit-identical statistics on either data plane.
 __device__ __forceinline__ void exchange_sum(const Comm& c, double* tot, int n, double* count) {
   const int ch = 1;
-  for (int i = threadIdx.x; i <= n; i += blockDim.x) {
-    const float v = (i < n) ? (float)tot[i] : (float)*count;
-    for (int q = 0; q < c.world; ++q) scratch_addr(c.pad[q], ch, c.rank)[i] = v;
+  if (c.pad_mc != nullptr) {
+    float* slot = scratch_addr(c.pad_mc, ch, c.rank);
+    for (int i4 = threadIdx.x * 4; i4 <= n; i4 += blockDim.x * 4) {
+      float v[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int i = i4 + j;
+        v[j] = (i < n) ? (float)tot[i] : (i == n ? (float)*count : 0.f);
+      }
+      mc_st_f4(slot + i4, make_float4(v[0], v[1], v[2], v[3]));
+    }
+  } else {
+    for (int i = threadIdx.x; i <= n; i += blockDim.x) {
+      const float v = (i < n) ? (float)tot[i] : (float)*count;
+      for (int q = 0; q < c.world; ++q) scratch_addr(c.pad[q], ch, c.rank)[i] = v;
+    }
   }
   __threadfence_system();
   block_barrier(c, ch, 0);
@@ -1242,24 +1259,25 @@ int pdt_bn_fwd_stats(const void* x, long M, int C, int dtype, void* scratch, con
 // Nothing here calls cudaMalloc, cudaFree or any allocating routine.
 static __device__ __align__(256) unsigned char g_bn_static_scratch[PDT_BN_STATIC_SCRATCH_BYTES];
 
-static void* g_bn_static_ptr[64];        // per device; filled once, with that device current
-static bool g_bn_static_ready[64];
+// Per device; filled once, with that device current.  The pointer is published with a release store and read
+// with an acquire load, so two host threads making the first call on one device at the same time both end up
+// with the same, fully written value (each may do the look-up; the result is identical).
+static std::atomic<void*> g_bn_static_ptr[64];
 
 static int bn_static_scratch_for_current_device(void** out) {
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return (int)e;
   if (dev < 0 || dev >= 64) return (int)cudaErrorInvalidDevice;
-  if (!g_bn_static_ready[dev]) {
+  void* p = g_bn_static_ptr[dev].load(std::memory_order_acquire);
+  if (p == nullptr) {
     // In host code the array's name is only a handle for the runtime, not a device address.
-    void* p = nullptr;
     e = cudaGetSymbolAddress(&p, g_bn_static_scratch);
     if (e != cudaSuccess) return (int)e;
     if (p == nullptr) return (int)cudaErrorInvalidSymbol;
-    g_bn_static_ptr[dev] = p;
-    g_bn_static_ready[dev] = true;
+    g_bn_static_ptr[dev].store(p, std::memory_order_release);
   }
-  *out = g_bn_static_ptr[dev];
+  *out = p;
   return 0;
 }
 

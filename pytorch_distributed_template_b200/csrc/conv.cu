@@ -431,7 +431,7 @@ template <int BN, typename T> struct WCfg {
 template <int BN, typename T>
 __global__ void __launch_bounds__(kThreads, 1)
 k_conv_wgrad(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmDY, float* __restrict__ dw,
-             const WgradGeom wg) {
+             float* __restrict__ part, const WgradGeom wg) {
   using C = WCfg<BN, T>;
   constexpr int kRow = C::kRow, BKP = C::kPix, kBlkBytes = C::kBlkBytes, kAB = C::kABlocks;
   const ConvGeom& g = wg.c;
@@ -561,10 +561,21 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
         tmem_ld32(taddr + c0, v);
         tmem_ld_wait();
         if (m < wg.rsc && nonempty) {
+          if (part != nullptr) {
+            // deterministic mode: every split stores its partial tile into its own slab; k_wgrad_fold adds the
+            // slabs in split order afterwards (no floating-point atomics anywhere)
+            float* slab = part + (size_t)sp * ((size_t)g.K * wg.rsc);
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            const int k = nt * BN + c0 + j;
-            if (k < g.K) atomicAdd(dw + (size_t)k * wg.rsc + m, __uint_as_float(v[j]));
+            for (int j = 0; j < 32; ++j) {
+              const int k = nt * BN + c0 + j;
+              if (k < g.K) slab[(size_t)k * wg.rsc + m] = __uint_as_float(v[j]);
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const int k = nt * BN + c0 + j;
+              if (k < g.K) atomicAdd(dw + (size_t)k * wg.rsc + m, __uint_as_float(v[j]));
+            }
           }
         }
       }
@@ -581,6 +592,19 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
     tmem_dealloc(tmem_base, C::kTmemCols);
   }
 }
+
+// Ordered fold of the split-K slabs of the deterministic weight gradient: dw[i] += part[0][i] + part[1][i] + ...
+__global__ void __launch_bounds__(256) k_wgrad_fold(float* __restrict__ dw, const float* __restrict__ part, size_t total, int splits) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    float a = 0.f;
+    for (int s = 0; s < splits; ++s) a += part[(size_t)s * total + i];
+    dw[i] += a;
+  }
+}
+
+// Per-device workspace for the deterministic weight gradient (pdt_set_wgrad_workspace); null = atomics.
+struct WgradWs { float* ptr; size_t floats; };
+WgradWs g_wgrad_ws[64];
 
 // ---- host side: tensor maps ---------------------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
@@ -765,20 +789,42 @@ int launch_wgrad(const void* x, const void* dy, float* dw, int dtype, WgradGeom&
   if (splits < 1) splits = 1;
   wg.steps_per_split = (wg.k_steps + splits - 1) / splits;
   wg.splits = (wg.k_steps + wg.steps_per_split - 1) / wg.steps_per_split;
+  // deterministic mode (a workspace is registered for this device): split-K partials go to slabs of the
+  // workspace and are folded in order; the split count shrinks to what the workspace holds
+  float* part = nullptr;
+  const size_t total = (size_t)wg.c.K * wg.rsc;
+  if (dev >= 0 && dev < 64 && g_wgrad_ws[dev].ptr != nullptr && wg.splits > 1) {
+    const size_t fit = g_wgrad_ws[dev].floats / total;
+    if (fit < 2) {
+      wg.steps_per_split = wg.k_steps;           // one writer per element: deterministic without slabs
+      wg.splits = 1;
+    } else {
+      if ((size_t)wg.splits > fit) {
+        wg.steps_per_split = (wg.k_steps + (int)fit - 1) / (int)fit;
+        wg.splits = (wg.k_steps + wg.steps_per_split - 1) / wg.steps_per_split;
+      }
+      if (wg.splits > 1) part = g_wgrad_ws[dev].ptr;
+    }
+  }
   const int items = tiles * wg.splits;
   const int grid = items < sms ? items : sms;
   if (dtype == PDT_FP16) {
     auto kern = k_conv_wgrad<BN, __half>;
     PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-    kern<<<grid, kThreads, smem_bytes, stream>>>(tmX, tmDY, dw, wg);
+    kern<<<grid, kThreads, smem_bytes, stream>>>(tmX, tmDY, dw, part, wg);
   } else if (dtype == PDT_FP32) {
     auto kern = k_conv_wgrad<BN, float>;
     PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-    kern<<<grid, kThreads, smem_bytes, stream>>>(tmX, tmDY, dw, wg);
+    kern<<<grid, kThreads, smem_bytes, stream>>>(tmX, tmDY, dw, part, wg);
   } else {
     auto kern = k_conv_wgrad<BN, __nv_bfloat16>;
     PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-    kern<<<grid, kThreads, smem_bytes, stream>>>(tmX, tmDY, dw, wg);
+    kern<<<grid, kThreads, smem_bytes, stream>>>(tmX, tmDY, dw, part, wg);
+  }
+  if (part != nullptr) {
+    PDT_CHECK(cudaGetLastError());
+    const int fb = (int)((total + 255) / 256 < 1184 ? (total + 255) / 256 : 1184);
+    k_wgrad_fold<<<fb, 256, 0, stream>>>(dw, part, total, wg.splits);
   }
   return (int)cudaGetLastError();
 }
@@ -809,12 +855,30 @@ int dispatch_fprop(const void* x, const void* w, void* y, const float* bias, int
 bool wgrad_halo_enabled() {
   static int v = -1;
   if (v < 0) { const char* e = getenv("PDT_WGRAD_HALO"); v = (e != nullptr && e[0] == '0') ? 0 : 1; }
-  return v == 1;
+  if (v != 1) return false;
+  int dev = 0;
+  cudaGetDevice(&dev);      // the patch-reuse kernel accumulates with red.add: not used in deterministic mode
+  return !(dev >= 0 && dev < 64 && g_wgrad_ws[dev].ptr != nullptr);
 }
 
 }  // namespace
 
 extern "C" {
+
+// Deterministic weight gradients for the CURRENT device: with a workspace registered, split-K partial tiles
+// are stored into slabs of it and folded in a fixed order (and the atomics-based patch-reuse kernel is not
+// used), so two runs produce bit-identical gradients (--seed, distributed.py:91-99: cudnn.deterministic).
+// ws == NULL switches back to the faster red.global.add accumulation.  Launches that share the workspace
+// must be stream-ordered.
+int pdt_set_wgrad_workspace(void* ws, size_t bytes) {
+  int dev = 0;
+  PDT_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return (int)cudaErrorInvalidDevice;
+  if ((reinterpret_cast<uintptr_t>(ws) & 15) != 0) return (int)cudaErrorInvalidValue;
+  g_wgrad_ws[dev].ptr = reinterpret_cast<float*>(ws);
+  g_wgrad_ws[dev].floats = ws ? bytes / sizeof(float) : 0;
+  return 0;
+}
 
 // x: [N][H][W][C], dy: [N][P][Q][K] (bf16/fp16), dw: [K][R][S][C] fp32, ACCUMULATED into (zero it first).
 int pdt_conv_wgrad(const void* x, const void* dy, float* dw, int dtype, int N, int H, int W, int C, int K, int R, int S,

@@ -1,6 +1,7 @@
 // Device-side fabric primitives shared by comm.cu and bn.cu: flag pads, the
 // block-level cross-GPU barrier and the scratch slots (layout in pdt_b200.h).
 #pragma once
+#include <cstdlib>
 #include "common.cuh"
 #include "../../include/pdt_b200.h"
 
@@ -11,7 +12,9 @@ constexpr int kChannels = PDT_COMM_CHANNELS;
 
 struct Comm {
   int rank, world;
+  uint64_t timeout_ns;            // spin budget of every cross-GPU wait (PDT_SPIN_TIMEOUT_S, default 600 s)
   uint32_t* pad[PDT_MAX_RANKS];   // each rank's pad base (flags, then inf slots, then scratch)
+  uint32_t* pad_mc;               // the same pad through the NVLS multicast mapping (one store reaches every rank), or null
 };
 
 __device__ __forceinline__ uint32_t* flag_addr(uint32_t* pad, int channel, int block, int src) {
@@ -25,21 +28,40 @@ __device__ __forceinline__ float* scratch_addr(uint32_t* pad, int channel, int s
          ((size_t)channel * PDT_MAX_RANKS + src) * PDT_SCRATCH_FLOATS;
 }
 
-__device__ __forceinline__ void signal_flag(uint32_t* addr) {
+// A rank may legitimately arrive late (rank 0 writing a checkpoint to a slow filesystem, a cold first batch),
+// so the budget is minutes, not the few seconds that would do for an intra-step skew; a dead peer still turns
+// into a trap (an error the host sees) instead of a hung box.
+__device__ __forceinline__ void signal_flag(uint32_t* addr, uint64_t timeout_ns) {
   uint32_t old;
   const uint64_t t0 = globaltimer_ns();
   do {
     asm volatile("atom.global.release.sys.cas.b32 %0, [%1], 0, 1;" : "=r"(old) : "l"(addr) : "memory");
-    if (old != 0 && globaltimer_ns() - t0 > kSpinTimeoutNs) __trap();
+    if (old != 0 && globaltimer_ns() - t0 > timeout_ns) __trap();
   } while (old != 0);
 }
-__device__ __forceinline__ void wait_flag(uint32_t* addr) {
+__device__ __forceinline__ void wait_flag(uint32_t* addr, uint64_t timeout_ns) {
   uint32_t old;
   const uint64_t t0 = globaltimer_ns();
   do {
     asm volatile("atom.global.acquire.sys.cas.b32 %0, [%1], 1, 0;" : "=r"(old) : "l"(addr) : "memory");
-    if (old != 1 && globaltimer_ns() - t0 > kSpinTimeoutNs) __trap();
+    if (old != 1 && globaltimer_ns() - t0 > timeout_ns) __trap();
   } while (old != 1);
+}
+
+// ---- NVLS: one instruction on the multicast mapping of a symmetric buffer ------------------------------------
+// ld_reduce: the switch reads the same offset on every rank and returns the sum (one NVLink transfer instead of W).
+// st:        one store that the switch replicates into every rank's copy (W-fold less egress).
+__device__ __forceinline__ float4 mc_ld_reduce_f4(const float* mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+  return v;
+}
+__device__ __forceinline__ void mc_st_f4(float* mc, const float4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ void mc_st_b64(void* mc, uint2 v) {   // 8 bytes of any type (four 16-bit shadow weights)
+  asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1,%2};" ::"l"(mc), "f"(__uint_as_float(v.x)), "f"(__uint_as_float(v.y)) : "memory");
 }
 
 // All threads of the block call this.  Everything the block wrote before is
@@ -49,17 +71,29 @@ __device__ __forceinline__ void block_barrier(const Comm& c, int channel, int ro
   __syncthreads();
   if ((int)threadIdx.x < c.world) {
     const int peer = threadIdx.x;
-    signal_flag(flag_addr(c.pad[peer], channel, row, c.rank));
-    wait_flag(flag_addr(c.pad[c.rank], channel, row, peer));
+    signal_flag(flag_addr(c.pad[peer], channel, row, c.rank), c.timeout_ns);
+    wait_flag(flag_addr(c.pad[c.rank], channel, row, peer), c.timeout_ns);
   }
   __syncthreads();
+}
+
+__host__ inline uint64_t spin_timeout_ns() {
+  static const uint64_t ns = [] {
+    const char* e = getenv("PDT_SPIN_TIMEOUT_S");
+    double s = e ? atof(e) : 600.0;
+    if (!(s > 0.0)) s = 600.0;
+    return (uint64_t)(s * 1e9);
+  }();
+  return ns;
 }
 
 __host__ inline Comm make_comm(const PdtCommDesc* d) {
   Comm c;
   c.rank = d ? d->rank : 0;
   c.world = d ? d->world : 1;
+  c.timeout_ns = spin_timeout_ns();
   for (int i = 0; i < PDT_MAX_RANKS; ++i) c.pad[i] = d ? reinterpret_cast<uint32_t*>(d->pad[i]) : nullptr;
+  c.pad_mc = d ? reinterpret_cast<uint32_t*>(d->pad_mc) : nullptr;
   return c;
 }
 

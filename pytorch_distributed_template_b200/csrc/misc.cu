@@ -30,7 +30,20 @@ __global__ void __launch_bounds__(128) k_ce_fwd(const T* __restrict__ logits, co
   __shared__ int s_last;
   const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const T* row = logits + (size_t)b * K;
-  const int tgt = (int)target[b];
+  // Labels: nn.CrossEntropyLoss semantics.  ignore_index = -100 rows contribute neither loss nor gradient and
+  // are left out of the mean; any other value outside [0, K) is a bug in the caller: trap (torch raises a
+  // device-side assert) instead of reading out of bounds.
+  const long long tgt_ll = target[b];
+  const bool ignored = tgt_ll == -100;
+  if (!ignored && (tgt_ll < 0 || tgt_ll >= K)) __trap();
+  const int tgt = ignored ? -1 : (int)tgt_ll;
+  int nvalid = 0;
+  for (int i = tid; i < B; i += 128) nvalid += target[i] != -100;
+  for (int o = 16; o > 0; o >>= 1) nvalid += __shfl_xor_sync(0xffffffffu, nvalid, o);
+  __shared__ int s_nv[4];
+  if (lane == 0) s_nv[wid] = nvalid;
+  __syncthreads();
+  nvalid = s_nv[0] + s_nv[1] + s_nv[2] + s_nv[3];
 
   float mx = -INFINITY;
   int arg = 0x7fffffff;
@@ -58,13 +71,13 @@ __global__ void __launch_bounds__(128) k_ce_fwd(const T* __restrict__ logits, co
   __syncthreads();
   se = s_red[0] + s_red[1] + s_red[2] + s_red[3];
   const float lse = mx + __logf(se);
-  const float inv = 1.f / se, invB = 1.f / (float)B;
+  const float inv = 1.f / se, invB = ignored ? 0.f : 1.f / (float)max(nvalid, 1);
   float* drow = dlogits_unit + (size_t)b * K;
   for (int i = tid; i < K; i += 128) {
     const float p = __expf(Cvt<T>::to_f(row[i]) - mx) * inv;
     drow[i] = (p - (i == tgt ? 1.f : 0.f)) * invB;
   }
-  if (tid == 0) row_out[b] = make_float2(lse - Cvt<T>::to_f(row[tgt]), arg == tgt ? 1.f : 0.f);
+  if (tid == 0) row_out[b] = ignored ? make_float2(0.f, 0.f) : make_float2(lse - Cvt<T>::to_f(row[tgt]), arg == tgt ? 1.f : 0.f);
 
   __threadfence();
   __syncthreads();
@@ -86,8 +99,8 @@ __global__ void __launch_bounds__(128) k_ce_fwd(const T* __restrict__ logits, co
     __syncthreads();
   }
   if (tid == 0) {
-    out[0] = (float)(s_l[0] / B);
-    out[1] = (float)(s_h[0] / B);
+    out[0] = (float)(s_l[0] / max(nvalid, 1));     // mean over the rows that are not ignored (torch: reduction='mean')
+    out[1] = (float)(s_h[0] / B);                  // utils.accuracy divides by the batch size
     *counter = 0;
   }
 }

@@ -27,7 +27,32 @@ class Peers(ctypes.Structure):
 
 
 class CommDesc(ctypes.Structure):
-    _fields_ = [("rank", ctypes.c_int), ("world", ctypes.c_int), ("pad", ctypes.c_void_p * MAX_RANKS)]
+    _fields_ = [("rank", ctypes.c_int), ("world", ctypes.c_int), ("pad", ctypes.c_void_p * MAX_RANKS),
+                ("pad_mc", ctypes.c_void_p)]
+
+
+MAX_SEGMENTS = 8
+
+
+class Segments(ctypes.Structure):
+    _fields_ = [("n", ctypes.c_int), ("off", ctypes.c_size_t * MAX_SEGMENTS), ("len", ctypes.c_size_t * MAX_SEGMENTS)]
+
+
+class EmuRanks(ctypes.Structure):
+    _fields_ = [("pad", ctypes.c_void_p * MAX_RANKS), ("amp_state", ctypes.c_void_p * MAX_RANKS),
+                ("momentum", ctypes.c_void_p * MAX_RANKS), ("io", ctypes.c_void_p * MAX_RANKS)]
+
+
+def make_segments(pairs):
+    """[(offset, length), ...] in elements -> PdtSegments (at most MAX_SEGMENTS)."""
+    pairs = list(pairs)
+    if not 1 <= len(pairs) <= MAX_SEGMENTS:
+        raise ValueError("1..{} segments per launch (got {})".format(MAX_SEGMENTS, len(pairs)))
+    s = Segments()
+    s.n = len(pairs)
+    for i, (o, l) in enumerate(pairs):
+        s.off[i], s.len[i] = int(o), int(l)
+    return s
 
 
 def dtype_code(dtype):
@@ -41,21 +66,27 @@ def make_peers(ptrs):
     return s
 
 
-def make_comm(rank, world, pad_ptrs):
+def make_comm(rank, world, pad_ptrs, pad_mc=0):
     d = CommDesc()
     d.rank, d.world = rank, world
     for i in range(MAX_RANKS):
         d.pad[i] = int(pad_ptrs[i]) if i < len(pad_ptrs) and pad_ptrs[i] else None
+    d.pad_mc = int(pad_mc) if pad_mc else None
     return d
 
 
 _vp, _i, _l, _f, _sz = ctypes.c_void_p, ctypes.c_int, ctypes.c_long, ctypes.c_float, ctypes.c_size_t
 _PC, _PP = ctypes.POINTER(CommDesc), ctypes.POINTER(Peers)
+_PS, _PE = ctypes.POINTER(Segments), ctypes.POINTER(EmuRanks)
 
 _SIGNATURES = {
     "pdt_comm_pad_bytes": ([], _sz),
-    "pdt_reduce_scatter_f32": ([_PC, _PP, _sz, _sz, _vp, _i, _i, _vp], _i),
-    "pdt_sgd_allgather": ([_PC, _PP, _PP, _PP, _i, _vp, _sz, _sz, _vp, _vp, _i, _i, _vp], _i),
+    "pdt_reduce_scatter_f32": ([_PC, _PP, _vp, _sz, _sz, _vp, _i, _i, _vp], _i),
+    "pdt_sgd_allgather": ([_PC, _PP, _PP, _PP, _vp, _vp, _i, _vp, _PS, _vp, _vp, _i, _i, _vp], _i),
+    "pdt_set_wgrad_workspace": ([_vp, _sz], _i),
+    "pdt_metrics_update": ([_PC, _vp, _vp, _i, _f, _i, _vp, _f, _vp], _i),
+    "pdt_emu_step": ([_PE, _i, _PP, _PP, _PP, _PS, _vp, _i, _vp], _i),
+    "pdt_emu_small": ([_PE, _i, _i, _f, _PP, _sz, _i, _vp], _i),
     "pdt_allreduce_f32": ([_PC, _PP, _sz, _sz, _f, _i, _vp], _i),
     "pdt_allreduce_small_f32": ([_PC, _vp, _vp, _i, _f, _i, _vp], _i),
     "pdt_bcast_pull": ([_PC, _PP, _sz, _sz, _i, _i, _i, _vp], _i),
@@ -93,51 +124,57 @@ def _header_abi():
 
 
 def _rebuild_if_stale():
-    """Sources newer than the library (a fresh checkout, an edited kernel) and nvcc at hand: build before loading.
-    Ranks of one node serialise on a lock file; whoever comes second finds the library fresh."""
-    if os.environ.get("PDT_NO_AUTOBUILD", "0") == "1":
-        return
+    """The library next to the package must have been built from the sources next to the package (content hash,
+    ``build.source_id()`` vs the id recorded by the build).  If it was not — a fresh checkout, an edited kernel —
+    build it now.  Ranks of one node serialise on a lock file; whoever comes second finds the library current.
+    A build error is raised, never swallowed: running a stale kernel is worse than not running."""
+    from .. import build as _build
     try:
-        from .. import build as _build
-        import fcntl
-        import glob
-        srcs = glob.glob(os.path.join(_build.CSRC, "*.cu")) + glob.glob(os.path.join(_build.CSRC, "*.cuh")) \
-            + glob.glob(os.path.join(_build.INCLUDE, "*.h"))
-        newest = max(os.path.getmtime(f) for f in srcs)
-        if os.path.exists(LIB_PATH) and os.path.getmtime(LIB_PATH) >= newest:
-            return
-        _build.nvcc_path()                       # raises when there is no compiler: keep whatever is there
-        os.makedirs(os.path.dirname(LIB_PATH), exist_ok=True)
-        with open(LIB_PATH + ".lock", "w") as lock:
-            fcntl.flock(lock, fcntl.LOCK_EX)
-            try:
-                if not (os.path.exists(LIB_PATH) and os.path.getmtime(LIB_PATH) >= newest):
-                    _build.build()
-            finally:
-                fcntl.flock(lock, fcntl.LOCK_UN)
-    except Exception:                            # no compiler / read-only tree: the load below reports what is wrong
-        pass
+        want = _build.source_id()
+    except OSError:
+        return None                      # sources not shipped (binary-only install): nothing to compare with
+    if _build.built_id() == want:
+        return want
+    if os.environ.get("PDT_NO_AUTOBUILD", "0") == "1":
+        raise OSError("{} was not built from the sources in {} (PDT_NO_AUTOBUILD=1): run "
+                      "`python -m pytorch_distributed_template_b200.build`".format(LIB_PATH, _build.CSRC))
+    import fcntl
+    os.makedirs(os.path.dirname(LIB_PATH), exist_ok=True)
+    with open(LIB_PATH + ".lock", "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if _build.built_id() != want:
+                _build.build()           # raises when nvcc is missing or fails
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+    return want
 
 
 def _load():
     global _lib, _load_error
     if _lib is not None or _load_error is not None:
         return _lib
-    _rebuild_if_stale()
     try:
+        want_id = _rebuild_if_stale()
         lib = ctypes.CDLL(LIB_PATH)
         want = _header_abi()
         have = lib.pdt_abi_version() if hasattr(lib, "pdt_abi_version") else None
         if want is not None and have != want:
             raise OSError("{} reports ABI {} but include/pdt_b200.h is at {}: stale build, run "
                           "`python -m pytorch_distributed_template_b200.build`".format(LIB_PATH, have, want))
+        if want_id is not None:
+            lib.pdt_build_id.restype = ctypes.c_char_p
+            have_id = lib.pdt_build_id().decode()
+            if have_id != want_id:
+                raise OSError("{} was built from other sources (id {} != {}): run "
+                              "`python -m pytorch_distributed_template_b200.build --force`".format(LIB_PATH, have_id, want_id))
         for name, (argtypes, restype) in _SIGNATURES.items():
             fn = getattr(lib, name, None)
             if fn is None:
                 continue
             fn.argtypes, fn.restype = argtypes, restype
         _lib = lib
-    except OSError as e:  # not built
+    except (OSError, RuntimeError) as e:  # not built / stale / build failed: require() reports it
         _load_error = e
     return _lib
 
@@ -166,6 +203,33 @@ def require():
 
 def lib():
     return require()
+
+
+_det_ws = {}
+
+
+def deterministic():
+    """PDT_DETERMINISTIC=1 (set by the trainer when --seed is given, like cudnn.deterministic in the reference,
+    distributed.py:91-99): weight gradients fold their split-K partials in a fixed order instead of using atomics."""
+    return os.environ.get("PDT_DETERMINISTIC", "0") == "1"
+
+
+def ensure_deterministic(device):
+    """Register (once per device) the workspace that switches the weight-gradient kernels to their
+    deterministic path; a no-op unless ``deterministic()``."""
+    if not deterministic() or device.type != "cuda":
+        return
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    if idx in _det_ws:
+        return
+    if torch.cuda.is_current_stream_capturing():
+        raise RuntimeError("deterministic mode must be set up before graph capture (run one eager step first)")
+    ws = torch.empty(int(os.environ.get("PDT_DETERMINISTIC_WS_MB", "256")) << 20, dtype=torch.uint8, device=device)
+    with torch.cuda.device(idx):
+        code = lib().pdt_set_wgrad_workspace(ws.data_ptr(), ws.numel())
+    if code != 0:
+        raise RuntimeError("pdt_set_wgrad_workspace failed ({})".format(code))
+    _det_ws[idx] = ws
 
 
 class _NoGuard:

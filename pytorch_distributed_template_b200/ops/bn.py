@@ -76,6 +76,17 @@ class batched_counters:
         return False
 
 
+def _ema_factor(bn):
+    """exponential_average_factor of nn.BatchNorm (torch/nn/modules/batchnorm.py): ``momentum``, or with
+    ``momentum=None`` the cumulative moving average 1 / num_batches_tracked (counted including this batch).
+    Call BEFORE ``_bump``; the cumulative form reads the counter on the host, like torch does."""
+    if bn.momentum is not None:
+        return bn.momentum
+    if bn.num_batches_tracked is None:
+        return 0.0
+    return 1.0 / float(int(bn.num_batches_tracked.item()) + 1)
+
+
 def _bump(counter):
     pending = getattr(_tls, "pending", None)
     if pending is None:
@@ -266,10 +277,11 @@ def bn_act(x, bn, residual=None, relu=False, comm=None, group=None, stats=None):
                                   stats[0], stats[1])
     training = bn.training or bn.running_mean is None
     sync = training and (comm is not None or group is not None)
+    momentum = _ema_factor(bn) if training else 0.0
     if training and bn.track_running_stats and bn.num_batches_tracked is not None:
         _bump(bn.num_batches_tracked)
-    momentum = 0.1 if bn.momentum is None else bn.momentum
-    if training and _native_ok(x, C) and torch.is_grad_enabled() and (not sync or comm is not None):
+    # (a SyncBatchNorm in train() under no_grad still synchronises its statistics: the native kernels need no autograd)
+    if training and _native_ok(x, C) and (torch.is_grad_enabled() or (sync and comm is not None)) and (not sync or comm is not None):
         return _BNActNative.apply(x, residual, bn.weight, bn.bias, bn.running_mean, bn.running_var, momentum, bn.eps,
                                   relu, comm if sync else None)
     if not training and _native_ok(x, C) and x.dtype != torch.float32 and not torch.is_grad_enabled():
@@ -299,9 +311,9 @@ def bn_relu_maxpool(x, bn, kernel_size=3, stride=2, padding=1, comm=None, group=
     sync = training and (comm is not None or group is not None)
     if (training and torch.is_grad_enabled() and _native_ok(x, C) and x.dtype != torch.float32
             and (not sync or comm is not None) and x.numel() // 8 < 4_000_000_000):
+        momentum = _ema_factor(bn)
         if bn.track_running_stats and bn.num_batches_tracked is not None:
             _bump(bn.num_batches_tracked)
-        momentum = 0.1 if bn.momentum is None else bn.momentum
         return _BNReluPoolNative.apply(x, bn.weight, bn.bias, bn.running_mean, bn.running_var, momentum, bn.eps,
                                        kernel_size, stride, padding, comm if sync else None)
     from .pool import max_pool2d
@@ -317,7 +329,7 @@ def conv_bn_relu_maxpool(x, conv, bn, kernel_size=3, stride=2, padding=1):
     fuse = (training and torch.is_grad_enabled() and x.is_cuda and _native.available() and bn.track_running_stats
             and bn.affine and os.environ.get("PDT_BNSTATS_FUSION", "1") == "1")
     if fuse:
-        momentum = 0.1 if bn.momentum is None else bn.momentum
+        momentum = _ema_factor(bn)
         out = conv2d(x, conv, bnpack=(bn.running_mean, bn.running_var, momentum, bn.eps))
         if isinstance(out, tuple):
             y, mean, invstd = out
@@ -341,7 +353,7 @@ def conv_bn_act(x, conv, bn, residual=None, relu=False, comm=None, group=None):
     fuse = (training and comm is None and group is None and torch.is_grad_enabled() and x.is_cuda
             and _native.available() and bn.track_running_stats and bn.affine)
     if fuse:
-        momentum = 0.1 if bn.momentum is None else bn.momentum
+        momentum = _ema_factor(bn)
         out = conv2d(x, conv, bnpack=(bn.running_mean, bn.running_var, momentum, bn.eps))
         if isinstance(out, tuple):
             y, mean, invstd = out

@@ -15,6 +15,23 @@ import torch.nn.functional as F
 from .. import amp
 from . import _native
 
+_seen_fallbacks = set()
+
+
+def note_fallback(kind, *key):
+    """Say ONCE per (kind, shape) that a layer is served by cuDNN / cuBLAS through aten instead of the package's
+    sm_100a kernels (groups, dilation, bias, channel counts the implicit-GEMM tiles do not take, non-ResNet
+    models), so nobody benchmarks the library path by accident.  PDT_QUIET_FALLBACK=1 silences it."""
+    k = (kind,) + tuple(key)
+    if k in _seen_fallbacks:
+        return
+    _seen_fallbacks.add(k)
+    import os
+    if os.environ.get("PDT_QUIET_FALLBACK", "0") != "1":
+        import logging
+        logging.getLogger("pdt_b200").warning("[pdt] %s falls back to the torch/cuDNN/cuBLAS path for %s", kind, key)
+
+
 _conv_native = None   # set by ops.conv_native when the tcgen05 kernels are importable
 _stem_native = None   # (supported(x, conv), run(x, conv, w_lp))
 _linear_native = None
@@ -82,6 +99,9 @@ def conv2d(x, conv, bnpack=None):
             if y is not None:
                 return y
     if lp is None or plain:
+        if x.is_cuda:
+            note_fallback("conv2d", tuple(conv.weight.shape), conv.stride, conv.padding, conv.groups, conv.dilation,
+                          conv.bias is not None, str(x.dtype))
         return conv._conv_forward(x, conv.weight, conv.bias)
     w_lp = shadow_of(conv.weight, lp)
     if w_lp is None:
@@ -94,6 +114,7 @@ def conv2d(x, conv, bnpack=None):
         y = _conv_native(x, conv.weight, w_lp, conv.stride, conv.padding, bnpack)
         if y is not None:
             return y
+    note_fallback("conv2d(amp)", tuple(conv.weight.shape), conv.stride, conv.padding, str(x.dtype))
     return _ConvLPTorch.apply(x, conv.weight, w_lp, conv.stride, conv.padding)
 
 
@@ -119,6 +140,8 @@ def linear(x, fc):
             and _linear_native[0](x, fc):
         return _linear_native[1](x, fc, fc.weight.detach())
     if lp is None or not x.is_cuda:
+        if x.is_cuda and torch.is_grad_enabled():
+            note_fallback("linear", tuple(fc.weight.shape), str(x.dtype))
         return F.linear(x, fc.weight, fc.bias)
     if x.dtype != lp:
         x = x.to(lp)
@@ -127,4 +150,5 @@ def linear(x, fc):
         w_lp = fc.weight.detach().to(lp)
     if _linear_native is not None and _native.available() and _linear_native[0](x, fc):
         return _linear_native[1](x, fc, w_lp)
+    note_fallback("linear(amp)", tuple(fc.weight.shape), str(x.dtype))
     return _LinearLP.apply(x, fc.weight, fc.bias, w_lp)

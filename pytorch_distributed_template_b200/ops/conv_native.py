@@ -134,6 +134,7 @@ def wgrad(x, dy, weight_shape, stride, pad, out=None):
     ``out``: an already-zeroed destination the kernel accumulates into (the gradient arena)."""
     N, C, H, W = x.shape
     K, _, R, S = weight_shape
+    _native.ensure_deterministic(x.device)
     if out is None:
         out = torch.empty((K, C, R, S), dtype=torch.float32, device=x.device, memory_format=CL)
         out.zero_()
@@ -195,8 +196,9 @@ class _DgradPlan:
         self.table_jobs = 0
         self.total_tiles = 0
         self.fresh = False
+        self.version = -1          # ParamArena.weights_version the buffers were made from
 
-    def lookup(self, w_lp, rs, ss):
+    def lookup(self, w_lp, rs, ss, version=None):
         K, C, R, S = w_lp.shape
         key = (w_lp.data_ptr(), K, C, R, S, tuple(rs), tuple(ss))
         out = self.jobs.get(key)
@@ -205,10 +207,11 @@ class _DgradPlan:
             self.jobs[key] = out
             self.order.append(key)
             return out, False
-        return out, self.fresh and self.table_jobs == len(self.order)
+        return out, self.fresh and self.table_jobs == len(self.order) and (version is None or version == self.version)
 
-    def prepare(self):
+    def prepare(self, version=None):
         self.fresh = False
+        self.version = version
         if not self.order or os.environ.get("PDT_DGRAD_BATCH", "1") != "1":
             return
         if self.table is None or self.table_jobs != len(self.order):
@@ -242,7 +245,7 @@ def prepare_dgrad_weights(arena):
     parameter arena whose shadow weights it reads, and dies with it."""
     plan = getattr(arena, "_dgrad_plan", None)
     if plan is not None:
-        plan.prepare()
+        plan.prepare(getattr(arena, "weights_version", None))
 
 
 def dgrad_weight(w_lp, rs, ss, stable=None):
@@ -257,7 +260,9 @@ def dgrad_weight(w_lp, rs, ss, stable=None):
         plan = getattr(stable, "_dgrad_plan", None)
         if plan is None:
             plan = stable._dgrad_plan = _DgradPlan(w_lp.device)
-        out, ready = plan.lookup(w_lp, rs, ss)
+        # a backward whose forward did not call prepare() after the last weight update (eval-mode forward with
+        # gradients, a retained graph) sees a version mismatch and re-makes the layout below
+        out, ready = plan.lookup(w_lp, rs, ss, getattr(stable, "weights_version", None))
         if ready:
             return out
     else:
@@ -496,6 +501,7 @@ class _StemNative(torch.autograd.Function):
                                                        (1, 1), (0, 0), (1, 1), False, (0, 0), 1, (False, True, False))[1]
             return None, stem_weight_grad_from_s2d(dwp4.permute(0, 2, 3, 1).reshape(K, 256), K), None
         dwp = torch.zeros((K, 256), dtype=torch.float32, device=dy.device)
+        _native.ensure_deterministic(dy.device)
         g = _StemNative._geom(xs.dtype, HP, WP, Q)
         _native.check(_native.lib().pdt_conv_wgrad_ex(
             xs.data_ptr(), dy.data_ptr(), dwp.data_ptr(), _native.dtype_code(dy.dtype), N, HP, g["Wt"], g["C"], g["C"],
@@ -553,6 +559,7 @@ class _LinearNative(torch.autograd.Function):
             dw = direct_grad(ctx.weight)
             if dw is None:
                 dw = torch.zeros((K, C), dtype=torch.float32, device=dy.device)
+            _native.ensure_deterministic(dy.device)
             _native.check(_native.lib().pdt_conv_wgrad(x.data_ptr(), dy.data_ptr(), dw.data_ptr(), _native.dtype_code(dy.dtype),
                                                        B, 1, 1, C, K, 1, 1, 1, 0, _native.stream_ptr(dy.device)),
                           "pdt_conv_wgrad(fc)")
@@ -563,8 +570,12 @@ class _LinearNative(torch.autograd.Function):
 
 
 def linear_supported(x, fc):
-    ok_dtype = x.dtype in (torch.bfloat16, torch.float16) or (x.dtype == torch.float32 and tf32_enabled()
-                                                                and torch.backends.cuda.matmul.allow_tf32)
+    # fp32 training: the classifier runs on tcgen05 kind::tf32 like the convolutions whenever TF32 convolutions
+    # are allowed (torch itself would keep cuBLAS fp32 unless matmul.allow_tf32 is also set; PDT_FC_TF32=0
+    # restores exactly that rule) — no cuBLAS call on the training path.
+    ok_dtype = x.dtype in (torch.bfloat16, torch.float16) or (
+        x.dtype == torch.float32 and tf32_enabled()
+        and (torch.backends.cuda.matmul.allow_tf32 or os.environ.get("PDT_FC_TF32", "1") == "1"))
     return (enabled() and x.is_cuda and x.dim() == 2 and ok_dtype
             and fc.in_features % 64 == 0 and fc.out_features % 8 == 0)
 

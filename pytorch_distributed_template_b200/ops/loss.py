@@ -24,6 +24,8 @@ def _ce_scratch(device, B):
 
 
 class _CENative(torch.autograd.Function):
+    last_pair = None
+
     @staticmethod
     def forward(ctx, logits, target):
         with _native.guard(logits.device):
@@ -42,6 +44,7 @@ class _CENative(torch.autograd.Function):
         ctx.dtype = logits.dtype
         loss, acc = out[0], out[1]
         ctx.mark_non_differentiable(acc)
+        _CENative.last_pair = out            # {loss, acc} as one 8-byte device vector (engine.StepRunner's meters)
         return loss, acc
 
     @staticmethod
@@ -77,8 +80,12 @@ class CrossEntropyLoss(nn.Module):
     def __init__(self):
         super().__init__()
         self.last_acc1 = None
+        self.last_pair = None       # float32[2] = {loss, top-1 fraction} of the last forward, one tensor
 
     def forward(self, logits, target):
+        _CENative.last_pair = None
         loss, acc = cross_entropy_with_accuracy(logits, target)
         self.last_acc1 = acc.detach()
+        pair = _CENative.last_pair
+        self.last_pair = pair if pair is not None else torch.stack([loss.detach().float(), acc.detach().float()])
         return loss

@@ -116,6 +116,7 @@ class SGD(torch.optim.Optimizer):
             self.sync_hyper()
         a = self.arena
         a.grads_zeroed = False          # the arena now holds this step's gradients
+        a.weights_changed()             # cached data-gradient filter layouts are stale after this step
         if self.owner is not None and not hasattr(self.owner, "_launch_segment"):
             self.owner.fused_step(self)          # DataParallel: per-device reduce + SGD + push
         elif self.native:
@@ -126,20 +127,25 @@ class SGD(torch.optim.Optimizer):
                 ddp = self.ddp
                 stream = ddp._comm_stream
                 stream.wait_stream(torch.cuda.current_stream(self.device))
+                nvls = ddp.fabric.use_nvls
                 with torch.cuda.stream(stream):
-                    for seg in a.segments:
+                    # every segment in ONE launch (one inf consensus, one pair of cross-GPU barriers); nothing else
+                    # runs at this point of the step, so the kernel may take most of the GPU
+                    for lo in range(0, len(a.segments), _native.MAX_SEGMENTS):
+                        segs = _native.make_segments((s.start, s.length) for s in a.segments[lo:lo + _native.MAX_SEGMENTS])
                         _native.check(lib.pdt_sgd_allgather(
                             ddp.fabric.comm, a.grad_buf.peers(), a.param_buf.peers(),
-                            a.shadow_buf.peers() if a.shadow_buf is not None else None, sh_dtype,
-                            a.momentum.data_ptr(), seg.start, seg.length, self._hyper.data_ptr(), st.data_ptr(),
-                            1 if ddp.world > 1 else 0, ddp.comm_blocks, stream.cuda_stream), "pdt_sgd_allgather")
+                            a.shadow_buf.peers() if a.shadow_buf is not None else None,
+                            a.param_buf.mc(nvls), a.shadow_buf.mc(nvls) if a.shadow_buf is not None else None, sh_dtype,
+                            a.momentum.data_ptr(), segs, self._hyper.data_ptr(), st.data_ptr(),
+                            1 if ddp.world > 1 else 0, ddp.step_blocks, stream.cuda_stream), "pdt_sgd_allgather")
                 ddp.join_comm()
             else:
                 a.gather_grads()
                 s = _native.stream_ptr(self.device)
                 if self.scaler is not None and self.scaler.is_enabled():
                     _native.check(lib.pdt_reduce_scatter_f32(
-                        a.fabric.comm, a.grad_buf.peers(), 0, a.total, st.data_ptr(), 0, 148, s),
+                        a.fabric.comm, a.grad_buf.peers(), None, 0, a.total, st.data_ptr(), 0, 148, s),
                         "pdt_reduce_scatter_f32(unscale)")
                 _native.check(lib.pdt_sgd_flat(
                     a.flat_params.data_ptr(), a.flat_grads.data_ptr(), a.momentum.data_ptr(),

@@ -43,7 +43,10 @@ _DIRECT = os.environ.get("PDT_DIRECT_GRAD", "1") == "1"     # 0: backward kernel
 
 
 class ParamArena:
-    def __init__(self, params, fabric, first_bucket_mb=1.0, bucket_cap_mb=25.0, shadow_dtype=None):
+    def __init__(self, params, fabric, first_bucket_mb=1.0, bucket_cap_mb=25.0, shadow_dtype=None, shard_world=None):
+        """``shard_world``: how many ways a segment is split between reducing ranks / devices (defaults to the
+        fabric's world; DataParallel passes its device count).  Any value 1..8 works: segments are padded to a
+        multiple of lcm(4 * shard_world, 64) elements, so every shard is a whole number of 16-byte vectors."""
         self.fabric = fabric
         self.device = fabric.device
         self.shadow_dtype = shadow_dtype
@@ -55,8 +58,10 @@ class ParamArena:
                 uniq.append(p)
         self.params = uniq
         order = list(reversed(uniq))
-        world = fabric.world
-        seg_align = _round_up(4 * world, _ALIGN)
+        import math
+        world = int(shard_world or fabric.world)
+        self.shard_world = world
+        seg_align = 4 * world * _ALIGN // math.gcd(4 * world, _ALIGN)
 
         # ---- layout: offsets (in elements) and segments --------------------------------
         self.offset = {}
@@ -80,6 +85,7 @@ class ParamArena:
         self.segments.append(cur)
         self.total = pos
         self.grads_zeroed = False
+        self.weights_version = 0      # bumped by every writer of the weights; cached re-layouts compare against it
         self.segment_of = {id(p): s for s in self.segments for p in s.params}
 
         # ---- storage ---------------------------------------------------------------------
@@ -125,10 +131,20 @@ class ParamArena:
     def shadow_view(self, p):
         return None if self.flat_shadow is None else self._view(self.flat_shadow, p)
 
+    def weights_changed(self):
+        """Every writer of the parameter arena calls this (optimizer kernels, load_state_dict, broadcasts): layouts
+        derived from the weights (the data-gradient filters cached by ops.conv_native) are stale until re-made."""
+        self.weights_version += 1
+
     def refresh_shadow(self):
         """Recompute the low-precision shadow from the fp32 master (init / load_state_dict)."""
         if self.flat_shadow is not None:
             self.flat_shadow.copy_(self.flat_params)
+        self.weights_changed()
+
+    def watch_state_dict(self, module):
+        """``module.load_state_dict`` writes the fp32 master weights in place; keep the shadow in step."""
+        module.register_load_state_dict_post_hook(lambda m, incompatible: self.refresh_shadow())
 
     def gather_grads(self, drop=False):
         """Copy every ``p.grad`` that is not already an arena view into the gradient arena."""

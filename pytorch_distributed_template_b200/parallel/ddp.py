@@ -61,7 +61,7 @@ class BufferArena:
 class DistributedDataParallel(nn.Module):
     def __init__(self, module, device_ids=None, output_device=None, dim=0, broadcast_buffers=True,
                  process_group=None, bucket_cap_mb=25, find_unused_parameters=False, check_reduction=False,
-                 gradient_as_bucket_view=True, static_graph=False, shadow_dtype=None, comm_blocks=32):
+                 gradient_as_bucket_view=True, static_graph=False, shadow_dtype=None, comm_blocks=32, step_blocks=128):
         super().__init__()
         self.module = module
         p0 = next(module.parameters())
@@ -75,10 +75,12 @@ class DistributedDataParallel(nn.Module):
         self.fabric = Fabric(self.device, self.process_group)
         self.world, self.rank = self.fabric.world, self.fabric.rank
         self.native = self.fabric.native
-        self.comm_blocks = comm_blocks
+        self.comm_blocks = comm_blocks      # reduce-scatter launches share the GPU with the rest of backward
+        self.step_blocks = step_blocks      # the SGD / all-gather launch at step end has it to itself
         self.arena = ParamArena(module.parameters(), self.fabric, first_bucket_mb=1.0,
                                 bucket_cap_mb=float(bucket_cap_mb), shadow_dtype=shadow_dtype)
         self.arena.owner = self
+        self.arena.watch_state_dict(module)
         from .syncbn import SyncBatchNorm
         for m in module.modules():
             if isinstance(m, SyncBatchNorm):
@@ -119,6 +121,7 @@ class DistributedDataParallel(nn.Module):
         ba = self.buffers_arena
         if ba.used == 0:
             return
+        self.fabric.check_stream(1)
         _native.check(_native.lib().pdt_bcast_pull(self.fabric.comm, ba.buf.peers(), 0, ba.total * 4, 0, 1, 4,
                                                   _native.stream_ptr(self.device)), "pdt_bcast_pull(buffers)")
 
@@ -183,8 +186,9 @@ class DistributedDataParallel(nn.Module):
                 lib = _native.lib()
                 if self.optimizer is not None:
                     _native.check(lib.pdt_reduce_scatter_f32(
-                        self.fabric.comm, self.arena.grad_buf.peers(), seg.start, seg.length, self._amp_ptr(),
-                        1 if self.world > 1 else 0, self.comm_blocks, s), "pdt_reduce_scatter_f32")
+                        self.fabric.comm, self.arena.grad_buf.peers(), self.arena.grad_buf.mc(self.fabric.use_nvls),
+                        seg.start, seg.length, self._amp_ptr(), 1 if self.world > 1 else 0, self.comm_blocks, s),
+                        "pdt_reduce_scatter_f32")
                 elif self.world > 1:
                     _native.check(lib.pdt_allreduce_f32(
                         self.fabric.comm, self.arena.grad_buf.peers(), seg.start, seg.length, 1.0 / self.world,

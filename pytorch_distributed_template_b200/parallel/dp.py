@@ -163,11 +163,14 @@ class DataParallel(nn.Module):
         if device_ids is None:
             device_ids = list(range(torch.cuda.device_count())) if torch.cuda.is_available() else []
         self.device_ids = [d if isinstance(d, int) else torch.device(d).index for d in device_ids]
+        if len(self.device_ids) > _native.MAX_RANKS:
+            raise ValueError("DataParallel drives at most {} devices (got {})".format(_native.MAX_RANKS, len(self.device_ids)))
         self.devices = [torch.device("cuda", d) for d in self.device_ids]
         self.output_device = self.device_ids[0] if self.device_ids else None
         self.shadow_dtype = shadow_dtype
         self.optimizer = None
         self._built = False
+        self._train_sig = None
         self.replicas, self.arenas, self.buffer_arenas, self._workers = [], [], [], []
         self._state = []
 
@@ -187,7 +190,7 @@ class DataParallel(nn.Module):
         for rep, dev in zip(self.replicas, self.devices):
             with torch.cuda.device(dev):
                 fab = Fabric(dev, group="solo")
-                arena = ParamArena(rep.parameters(), fab, shadow_dtype=self.shadow_dtype)
+                arena = ParamArena(rep.parameters(), fab, shadow_dtype=self.shadow_dtype, shard_world=len(self.devices))
                 arena.owner = self
                 self.arenas.append(arena)
                 self.buffer_arenas.append(BufferArena(rep, fab))
@@ -201,9 +204,25 @@ class DataParallel(nn.Module):
         self._shadow = _native.make_peers([a.shadow_buf.ptrs[0] for a in self.arenas]) if self.shadow_dtype else None
         self._comms = [_native.make_comm(r, W, []) for r in range(W)]
         self._hypers = [torch.zeros(4, dtype=torch.float32, device=d) for d in self.devices]
+        self._hyper_host = None
+        self._whole = _native.make_segments([(0, self.arenas[0].total)])
         for d in self.devices:
             torch.cuda.synchronize(d)
         self._built = True
+        self.module.register_load_state_dict_post_hook(lambda m, incompatible: self._push_master())
+
+    @torch.no_grad()
+    def _push_master(self):
+        """After ``load_state_dict`` on the real module: replicas and every shadow follow device 0's master weights."""
+        a0 = self.arenas[0]
+        torch.cuda.synchronize(self.devices[0])
+        for dev, a in zip(self.devices, self.arenas):
+            with torch.cuda.device(dev):
+                if a is not a0:
+                    a.flat_params.copy_(a0.flat_params)
+                a.refresh_shadow()
+        for d in self.devices:
+            torch.cuda.synchronize(d)
 
     @property
     def arena(self):
@@ -229,8 +248,14 @@ class DataParallel(nn.Module):
         x = inputs[0]
         if x.shape[0] < len(self.devices):
             return self.module(*inputs, **kwargs)
-        for rep in self.replicas[1:]:
-            rep.train(self.module.training)
+        # replicas mirror the training flag of EVERY sub-module (a BatchNorm the user froze with .eval() stays
+        # frozen on all devices, like torch's replicate()); 68 attribute reads, applied only on change
+        sig = tuple(m.training for m in self.module.modules())
+        if sig != self._train_sig:
+            for rep in self.replicas[1:]:
+                for m, flag in zip(rep.modules(), sig):
+                    m.training = flag
+            self._train_sig = sig
         self._bcast_buffers()
         xs = _Scatter.apply(self, x)
         grad_on = torch.is_grad_enabled()
@@ -252,7 +277,15 @@ class DataParallel(nn.Module):
         W = len(self.devices)
         lib = _native.lib()
         g = opt.param_groups[0]
-        host = torch.tensor([g["lr"], g["momentum"], g["weight_decay"], 0.0], dtype=torch.float32)
+        hyper = (float(g["lr"]), float(g["momentum"]), float(g["weight_decay"]), 0.0)
+        if hyper != self._hyper_host:      # device copies change only when the schedule does: no per-step H2D
+            host = torch.tensor(hyper, dtype=torch.float32).pin_memory()
+            for r, dev in enumerate(self.devices):
+                with torch.cuda.device(dev):
+                    self._hypers[r].copy_(host, non_blocking=True)
+            for dev in self.devices:
+                torch.cuda.synchronize(dev)          # `host` may go away; happens once per LR change
+            self._hyper_host = hyper
         # phase 1: every device moves its replica's gradients into its arena
         done = []
         for r, dev in enumerate(self.devices):
@@ -272,17 +305,18 @@ class DataParallel(nn.Module):
                 s = torch.cuda.current_stream(dev)
                 for ev in done:
                     s.wait_event(ev)
-                self._hypers[r].copy_(host, non_blocking=True)
-                _native.check(lib.pdt_reduce_scatter_f32(self._comms[r], self._grads, 0, a.total,
-                                                        self._state[r].data_ptr(), 0, 64, s.cuda_stream),
+                _native.check(lib.pdt_reduce_scatter_f32(self._comms[r], self._grads, None, 0, a.total,
+                                                        self._state[r].data_ptr(), 0, 128, s.cuda_stream),
                               "pdt_reduce_scatter_f32(dp)")
-                _native.check(lib.pdt_sgd_allgather(self._comms[r], self._grads, self._params, self._shadow, sh_dtype,
-                                                   a.momentum.data_ptr(), 0, a.total, self._hypers[r].data_ptr(),
-                                                   self._state[r].data_ptr(), 0, 64, s.cuda_stream),
+                _native.check(lib.pdt_sgd_allgather(self._comms[r], self._grads, self._params, self._shadow, None, None,
+                                                   sh_dtype, a.momentum.data_ptr(), self._whole, self._hypers[r].data_ptr(),
+                                                   self._state[r].data_ptr(), 0, 128, s.cuda_stream),
                               "pdt_sgd_allgather(dp)")
                 ev = torch.cuda.Event()
                 ev.record(s)
                 after.append(ev)
+        for a in self.arenas:
+            a.weights_changed()
         for r, dev in enumerate(self.devices):      # new weights were written by peers: everybody waits for everybody
             s = torch.cuda.current_stream(dev)
             for ev in after:

@@ -34,6 +34,10 @@ class SymBuffer:
     def peers(self, offset=0):
         return _native.make_peers([p + offset for p in self.ptrs])
 
+    def mc(self, use=True):
+        """The buffer through its NVLS multicast mapping (an int device pointer), or None."""
+        return self.multicast_ptr if (use and self.multicast_ptr) else None
+
 
 class Fabric:
     def __init__(self, device, group=None):
@@ -47,11 +51,15 @@ class Fabric:
         self._buffers = []
         self.pad = None
         self.comm = None
+        # NVLS data plane (multimem.ld_reduce / multimem.st on the multicast mapping) when the allocation got one;
+        # PDT_NVLS=0 forces the peer load/store plane.
+        self.use_nvls = os.environ.get("PDT_NVLS", "1") == "1"
+        self._channel_stream = {}
         if self.native:
-            if self.world > _native.MAX_RANKS or self.world not in (1, 2, 4, 8):
-                raise RuntimeError("native fabric supports world sizes 1, 2, 4, 8 (got {})".format(self.world))
+            if self.world > _native.MAX_RANKS:
+                raise RuntimeError("native fabric supports world sizes 1..{} (got {})".format(_native.MAX_RANKS, self.world))
             self.pad = self.alloc(_native.lib().pdt_comm_pad_bytes(), zero=True)
-            self.comm = _native.make_comm(self.rank, self.world, self.pad.ptrs)
+            self.comm = _native.make_comm(self.rank, self.world, self.pad.ptrs, self.pad.mc(self.use_nvls))
 
     # -- allocation ---------------------------------------------------------------------
     def alloc(self, nbytes, zero=True):
@@ -80,7 +88,21 @@ class Fabric:
         return SymBuffer(t, ptrs, mc, handle)
 
     # -- collectives used outside the gradient path ---------------------------------------
+    def check_stream(self, channel, stream_ptr=None):
+        """The flag protocol is self-resetting: every user of one channel must enqueue on ONE stream, in the same
+        order on every rank (SyncBN exchanges, metric reductions and buffer broadcasts share channel 1).  A second
+        stream on the same channel could interleave two exchanges on the same flag row and deadlock until the
+        spin budget traps; refuse it here instead."""
+        if self.world == 1:
+            return
+        s = _native.stream_ptr(self.device) if stream_ptr is None else stream_ptr
+        first = self._channel_stream.setdefault(channel, s)
+        if first != s:
+            raise RuntimeError("fabric channel {} is bound to stream {:#x} but was used from stream {:#x}: all users of a "
+                               "channel must share one stream (use another channel for a side stream)".format(channel, first, s))
+
     def barrier(self, channel=1):
+        self.check_stream(channel)
         if self.native and self.world > 1:
             _native.check(_native.lib().pdt_barrier(self.comm, channel, _native.stream_ptr(self.device)), "pdt_barrier")
         elif self.world > 1:
@@ -91,6 +113,7 @@ class Fabric:
         if self.world == 1:
             return t
         if self.native and t.is_cuda and t.dtype == torch.float32 and t.numel() <= 8192 and t.is_contiguous():
+            self.check_stream(channel)
             scale = 1.0 / self.world if mean else 1.0
             _native.check(_native.lib().pdt_allreduce_small_f32(
                 self.comm, t.data_ptr(), t.data_ptr(), t.numel(), scale, channel, _native.stream_ptr(self.device)),
@@ -102,5 +125,6 @@ class Fabric:
         return t
 
     def describe(self):
+        mc = bool(self.pad is not None and self.pad.multicast_ptr)
         return {"rank": self.rank, "world": self.world, "native": self.native, "symmetric": self.symmetric,
-                "multicast": bool(self.pad is not None and self.pad.multicast_ptr)}
+                "multicast": mc, "data_plane": "nvls" if (mc and self.use_nvls and self.world > 1) else "p2p"}

@@ -8,11 +8,15 @@ with the same log lines, TensorBoard scalars and checkpoint dict.
 Hot-loop differences: the reference drains the stream twice per
 iteration (``dist.barrier()`` + ``loss.item()``).  Here loss and accuracy are
 reduced across ranks by one 8-byte in-kernel all-reduce (which also IS the
-barrier) into device-resident meters that are read only when a line is printed.
+barrier) into device-resident meters that are read only when a line is printed,
+and the whole iteration is one ``engine.StepRunner.step`` — after a few eager
+iterations a single CUDA-graph replay fed by ``engine.DeviceFeed`` (the same
+objects ``bench.py`` times).
 
 Environment knobs (the CLI stays the reference's): PDT_SYNTHETIC, PDT_MAX_STEPS,
 PDT_MAX_VAL_STEPS, PDT_AMP_DTYPE, PDT_DEVICE, PDT_MODEL_IMPL, PDT_OUTPUT_EXISTS,
-PDT_SYNTH_TRAIN_SIZE, PDT_SYNTH_VAL_SIZE, PDT_IMAGE_SIZE, PDT_NUM_CLASSES.
+PDT_SYNTH_TRAIN_SIZE, PDT_SYNTH_VAL_SIZE, PDT_IMAGE_SIZE, PDT_NUM_CLASSES, PDT_GRAPH,
+PDT_GRAPH_WARMUP, PDT_NVTX, PDT_INPUT, PDT_NVLS, PDT_SPIN_TIMEOUT_S (INTEGRATION.md lists them all).
 """
 import os
 import random
@@ -24,12 +28,12 @@ import torch
 import torch.distributed as dist
 import torch.nn as nn
 
-from . import amp, data, env, optim
+from . import amp, data, engine, env, optim
 from .config import LOGGER_NAME, normalise_steps
 from .models import create_model
 from .ops import CrossEntropyLoss
 from .parallel import DataParallel, DistributedDataParallel, SyncBatchNorm
-from .utils import (AverageMeter, DeviceMeter, accuracy, ddp_print, get_learning_rate, get_logger,
+from .utils import (AverageMeter, ddp_print, get_learning_rate, get_logger,
                     make_summary_writer, output_process, save_checkpoint, write_settings)
 
 
@@ -42,6 +46,8 @@ def seed_everything(args):
             torch.cuda.manual_seed_all(args.seed)
         torch.backends.cudnn.deterministic = True
         torch.backends.cudnn.benchmark = False
+        # the native weight-gradient kernels honour the same promise: ordered split-K instead of atomics
+        os.environ.setdefault("PDT_DETERMINISTIC", "1")
         warnings.warn("You have chosen to seed training.This will turn on the cudnn deterministic setting,"
                       "which can slow down your training considerably!"
                       "You may see unexpected behavior when restarting from checkpoint.")
@@ -75,6 +81,7 @@ def setup(args, mode):
     else:
         ctx.device = torch.device("cuda", 0) if env.use_cuda() else torch.device("cpu")
         args.nprocs = max(1, torch.cuda.device_count()) if ctx.device.type == "cuda" else 1
+    engine.work_stream(ctx.device)      # everything from the first forward on runs on this stream (graph capture)
     if ctx.is_main:
         write_settings(args)
         ctx.logger.info(args)
@@ -138,57 +145,33 @@ def setup(args, mode):
     ctx.max_steps = env.env_int("PDT_MAX_STEPS", 0)
     ctx.max_val_steps = env.env_int("PDT_MAX_VAL_STEPS", ctx.max_steps)
     ctx.fabric = getattr(model, "fabric", None)
+    ctx.runner = engine.StepRunner(model, ctx.criterion, ctx.optimizer, ctx.scaler, ctx.device, use_amp=use_amp,
+                                   amp_dtype=ctx.amp_dtype)
     return ctx
 
 
-def _reduce_pair(ctx, loss, acc1):
-    """reduce_mean(loss), reduce_mean(acc1) and the barrier before them (distributed.py:253-255)
-    as one stream-ordered exchange; returns a 2-element device tensor."""
-    pair = torch.stack([loss.detach().float().reshape(()), acc1.detach().float().reshape(())])
-    if ctx.mode != "dp" and ctx.fabric is not None:
-        ctx.fabric.allreduce_small_(pair, mean=True)
-    return pair
-
-
-def _forward_loss(ctx, images, target, training):
-    """Forward + loss + top-1.  Validation never runs under autocast."""
-    with amp.autocast(enabled=ctx.use_amp and training, dtype=ctx.amp_dtype,
-                      device_type=ctx.device.type):
-        output = ctx.model(images)
-        loss = ctx.criterion(output, target)
-    acc1 = ctx.criterion.last_acc1 if ctx.criterion.last_acc1 is not None else accuracy(output, target, 1)
-    return loss, acc1
-
-
 def train(ctx, epoch):
-    args, lr, log = ctx.args, None, ctx.logger
+    args, log, runner = ctx.args, ctx.logger, ctx.runner
     batch_times, data_times = AverageMeter("Time", ":6.3f"), AverageMeter("Data", ":6.3f")
-    losses = DeviceMeter("Loss", ":.4e", ctx.device)
-    top1 = DeviceMeter("Acc@1", ":6.2f", ctx.device)
     ctx.model.train()
-    loader = data.PinnedPrefetcher(ctx.train_loader, ctx.device)
+    runner.meter.reset()
+    loader = engine.DeviceFeed(ctx.train_loader, runner)
     n_iter = len(loader)
     end = time.time()
     for i, (images, target) in enumerate(loader):
         data_times.update(time.time() - end)
-        loss, acc1 = _forward_loss(ctx, images, target, True)
-        pair = _reduce_pair(ctx, loss, acc1)
-        losses.update(pair[0], images.size(0))
-        top1.update(pair[1], images.size(0))
-        ctx.optimizer.zero_grad()
-        ctx.scaler.scale(loss).backward()
-        ctx.scaler.step(ctx.optimizer)
-        ctx.scaler.update()
+        runner.step(images, target)       # forward, metrics, zero_grad, backward (+ gradient exchange), SGD, scaler
         batch_times.update(time.time() - end)
         end = time.time()
         if i % args.print_freq == 0:
+            m = runner.meter.read()
             ddp_print("Train epoch: [{:d}/{:d}][{:d}/{:d}]\tlr={:.6f}\tce_loss={:.4f}\ttop1_acc={:.4f}\tdata_time={:6.3f}s"
                       "\tbatch_time={:6.3f}s".format(epoch, args.epochs, i, n_iter, get_learning_rate(ctx.optimizer),
-                                                    losses.read()["avg"], top1.read()["avg"], data_times.avg,
-                                                    batch_times.avg), log, ctx.local_rank)
+                                                    m["loss"], m["acc1"], data_times.avg, batch_times.avg), log, ctx.local_rank)
         if ctx.max_steps and i + 1 >= ctx.max_steps:
             break
-    l, a = losses.read()["avg"], top1.read()["avg"]
+    m = runner.meter.read()
+    l, a = m["loss"], m["acc1"]
     ddp_print("||==> Train epoch: [{:d}/{:d}]\tlr={:.6f}\tce_loss={:.4f}\ttop1_acc={:.4f}\tbatch_time={:6.3f}s"
               .format(epoch, args.epochs, get_learning_rate(ctx.optimizer), l, a, batch_times.avg), log, ctx.local_rank)
     if ctx.is_main:
@@ -199,29 +182,26 @@ def train(ctx, epoch):
 
 
 def validate(ctx, epoch):
-    args, log = ctx.args, ctx.logger
+    args, log, runner = ctx.args, ctx.logger, ctx.runner
     batch_times = AverageMeter("Time", ":6.3f")
-    losses = DeviceMeter("Loss", ":.4e", ctx.device)
-    top1 = DeviceMeter("Acc@1", ":6.2f", ctx.device)
+    meter = engine.Meter(ctx.device)
     ctx.model.eval()
     with torch.no_grad():
         loader = data.PinnedPrefetcher(ctx.val_loader, ctx.device)
         n_iter = len(loader)
         end = time.time()
         for i, (images, target) in enumerate(loader):
-            loss, acc1 = _forward_loss(ctx, images, target, False)
-            pair = _reduce_pair(ctx, loss, acc1)
-            losses.update(pair[0], images.size(0))
-            top1.update(pair[1], images.size(0))
+            runner.eval_step(images, target, meter)
             batch_times.update(time.time() - end)
             end = time.time()
             if i % args.print_freq == 0:
+                m = meter.read()
                 ddp_print("Val epoch: [{:d}/{:d}][{:d}/{:d}]\tce_loss={:.4f}\ttop1_acc={:.4f}\tbatch_time={:6.3f}s"
-                          .format(epoch, args.epochs, i, n_iter, losses.read()["avg"], top1.read()["avg"],
-                                  batch_times.avg), log, ctx.local_rank)
+                          .format(epoch, args.epochs, i, n_iter, m["loss"], m["acc1"], batch_times.avg), log, ctx.local_rank)
             if ctx.max_val_steps and i + 1 >= ctx.max_val_steps:
                 break
-        l, a = losses.read()["avg"], top1.read()["avg"]
+        m = meter.read()
+        l, a = m["loss"], m["acc1"]
         ddp_print("||==> Val epoch: [{:d}/{:d}]\tce_loss={:.4f}\ttop1_acc={:.4f}\tbatch_time={:6.3f}s"
                   .format(epoch, args.epochs, l, a, batch_times.avg), log, ctx.local_rank)
         if ctx.is_main:
@@ -259,7 +239,15 @@ def run(args, mode):
                 save_checkpoint({"epoch": epoch + 1, "arch": args.arch,
                                  "state_dict": ctx.model.module.state_dict(),
                                  "best_acc1": best_acc1}, is_best, args.outpath)
+            if mode != "dp" and dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+                # Rank 0 may spend a long time writing the checkpoint; the peers wait HERE on the host instead
+                # of inside the next epoch's first device-side exchange, whose spin budget is finite.
+                dist.barrier()
         ddp_print("||==> total_time_cost={:.4f}s".format(time.time() - total_start), ctx.logger, ctx.local_rank)
+        if env.env_flag("PDT_REPORT_GRAPHS") and ctx.is_main:      # not part of the reference's log format: opt-in
+            print("[pdt] training step: {} CUDA graphs, {} kernels per replay{}".format(
+                ctx.runner.graphs, ctx.runner.launches_per_step,
+                "" if ctx.runner.capture_error is None else " (capture failed: {})".format(ctx.runner.capture_error)), flush=True)
         if ctx.is_main:
             ctx.writer.close()
         return ctx

@@ -89,7 +89,7 @@ def accuracy(scores, targets, k=1):
 def reduce_mean(tensor, nprocs):
     """Mean of ``tensor`` over the ranks: clone -> all_reduce(SUM) -> / nprocs, the reference's helper
     (/root/reference/distributed.py:78-82).  The trainer itself packs loss and accuracy into one 8-byte
-    device all-reduce (``trainer._reduce_pair``); this is the same operation for user code."""
+    device all-reduce (``engine.StepRunner.update_metrics``); this is the same operation for user code."""
     import torch.distributed as dist
     rt = tensor.clone()
     if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:

@@ -17,42 +17,13 @@ from pytorch_distributed_template_b200.parallel import DistributedDataParallel, 
 
 
 def syncbn_layer_check(device, rank):
-    """One SyncBatchNorm layer, ours (in-kernel NVLink exchange) vs torch.nn.SyncBatchNorm, per rank."""
-    from pytorch_distributed_template_b200.parallel import Fabric
-    from pytorch_distributed_template_b200.parallel.syncbn import fused_bn
+    """One SyncBatchNorm layer, ours (in-kernel NVLink exchange) vs torch.nn.SyncBatchNorm, per rank
+    (the same function bench.py runs on the live job)."""
+    from pytorch_distributed_template_b200.parallel import Fabric, selfcheck
+    return selfcheck.syncbn_layer(Fabric(device))
 
-    def rel(a, b):
-        return ((a.float() - b.float()).abs().max() / (b.float().abs().max() + 1e-12)).item()
 
-    fab = Fabric(device)
-    worst = {}
-    for dtype in (torch.float32, torch.bfloat16):
-        for C, HW, relu in ((64, 16, False), (256, 7, True), (512, 4, True)):
-            torch.manual_seed(5 + rank)
-            x = (torch.randn(6, C, HW, HW, device=device) * (1 + rank) + rank).to(dtype).contiguous(memory_format=torch.channels_last)
-            dy = torch.randn(6, C, HW, HW, device=device).to(dtype).contiguous(memory_format=torch.channels_last)
-            ours = SyncBatchNorm(C).to(device)
-            ours._pdt_fabric = fab
-            ref = torch.nn.SyncBatchNorm(C).to(device)
-            with torch.no_grad():
-                ours.weight.uniform_(0.5, 1.5)
-                ours.bias.uniform_(-0.5, 0.5)
-                dist.broadcast(ours.weight, 0)
-                dist.broadcast(ours.bias, 0)
-            ref.load_state_dict(ours.state_dict())
-            xo = x.clone().requires_grad_(True)
-            xr = x.float().clone().requires_grad_(True)
-            yo = fused_bn(ours, xo, relu=relu)
-            yr = torch.relu(ref(xr)) if relu else ref(xr)
-            yo.backward(dy)
-            yr.backward(dy.float())
-            torch.cuda.synchronize()
-            key = "fp32" if dtype == torch.float32 else "bf16"
-            for name, a, b in (("y", yo, yr), ("dx", xo.grad, xr.grad), ("dgamma", ours.weight.grad, ref.weight.grad),
-                               ("dbeta", ours.bias.grad, ref.bias.grad), ("rmean", ours.running_mean, ref.running_mean),
-                               ("rvar", ours.running_var, ref.running_var)):
-                worst[key + "_" + name] = max(worst.get(key + "_" + name, 0.0), rel(a, b))
-    return worst
+PER_RANK = 64
 
 
 def main():
@@ -106,8 +77,10 @@ def main():
         worst_name = None
         first_loss = []
         for it in range(3):
-            x = torch.randn(8, 3, 64, 64, generator=g).to(device)
-            y = torch.randint(0, 10, (8,), generator=g).to(device)
+            # 64 images per rank: with 8, the 20 BatchNorm layers amplify rounding differences between two correct
+            # implementations into percent-level gradient differences and the bounds below would have to be useless
+            x = torch.randn(PER_RANK, 3, 64, 64, generator=g).to(device)
+            y = torch.randint(0, 10, (PER_RANK,), generator=g).to(device)
             for model, opt in ((ours, o_ours), (theirs, o_ref)):
                 model.train()
                 opt.zero_grad()

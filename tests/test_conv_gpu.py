@@ -163,7 +163,10 @@ def test_tf32_conv_fprop_and_wgrad(native_lib, cin, cout, hw, k, stride, pad):
 
 
 def test_tf32_model_paths(native_lib):
-    """fp32 ResNet-18 step (stem, strided dgrad, linear) through the tf32 kernels vs torch fp32."""
+    """fp32 ResNet-18 step (stem, strided dgrad, linear) through the kind::tf32 kernels against torch fp32 (TF32
+    off) on a well-conditioned batch (64 images).  Calibrated bound: cuDNN's own TF32 gradients are measured
+    against the same fp32 truth and ours may be at most 2x as far away (and within 2 % in the 2-norm)."""
+    import copy
     import torchvision
     from pytorch_distributed_template_b200.models import create_model
     from pytorch_distributed_template_b200.ops import _native
@@ -172,24 +175,30 @@ def test_tf32_model_paths(native_lib):
     net = create_model("resnet18", num_classes=16).to(dev)
     tv = torchvision.models.resnet18(num_classes=16).to(dev)
     tv.load_state_dict(net.state_dict())
-    x = torch.randn(8, 3, 224, 224, device=dev)
-    y = torch.randint(0, 16, (8,), device=dev)
-    net.train(); tv.train()
+    tv_tf32 = copy.deepcopy(tv)
+    x = torch.randn(64, 3, 128, 128, device=dev)
+    y = torch.randint(0, 16, (64,), device=dev)
+    net.train(); tv.train(); tv_tf32.train()
     torch.backends.cudnn.allow_tf32 = True
     torch.backends.cuda.matmul.allow_tf32 = True
     n0 = _native.launch_count
     lo = F.cross_entropy(net(x), y)
     lo.backward()
     assert _native.launch_count - n0 > 60, "tf32 native path not taken"
+    lt = F.cross_entropy(tv_tf32(x), y)
+    lt.backward()
     torch.backends.cudnn.allow_tf32 = False
     torch.backends.cuda.matmul.allow_tf32 = False
     lr = F.cross_entropy(tv(x), y)
     lr.backward()
-    assert lo.item() == pytest.approx(lr.item(), rel=2e-2)
-    g1 = torch.cat([p.grad.reshape(-1) for p in net.parameters()])
-    g2 = torch.cat([p.grad.reshape(-1) for p in tv.parameters()])
-    assert torch.isfinite(g1).all()
-    assert torch.nn.functional.cosine_similarity(g1, g2, dim=0).item() > 0.98
+    assert lo.item() == pytest.approx(lr.item(), rel=2e-3)
+    flat = lambda m: torch.cat([p.grad.reshape(-1) for p in m.parameters()])
+    g_ours, g_torch, g_true = flat(net), flat(tv_tf32), flat(tv)
+    assert torch.isfinite(g_ours).all()
+    e_ours = ((g_ours - g_true).norm() / g_true.norm()).item()
+    e_torch = ((g_torch - g_true).norm() / g_true.norm()).item()
+    assert e_ours <= 2.0 * e_torch + 1e-4, (e_ours, e_torch)
+    assert e_ours <= 2e-2, (e_ours, e_torch)
 
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])

@@ -35,31 +35,31 @@ def test_ddp_native_fabric_matches_torch_ddp(native_lib):
         assert o["fabric"]["native"] and o["fabric"]["symmetric"], json.dumps(o)
         assert o["init_synced"] and o["ranks_identical"], json.dumps(o)
         assert o["first_param_rel"] < 1e-4, json.dumps(o)
-        assert o["worst_param_rel"] < 5e-2, json.dumps(o)
+        assert o["worst_param_rel"] < 5e-3, json.dumps(o)       # three steps, 64 images per rank, fp32 both sides
         assert o["reduce_mean"] == pytest.approx([(n + 1) / 2, n + 1.0])
 
 
 @pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
 def test_syncbn_layer_matches_torch_syncbn(native_lib):
     """One layer, both dtypes, with and without ReLU: forward, dx, dgamma/dbeta, running stats per rank."""
+    from pytorch_distributed_template_b200.parallel import selfcheck
     outs = _launch(["--syncbn-layer"], 2, 29663)
     for o in outs:
         for k, v in o["layer"].items():
-            tol = 1e-5 if k.startswith("fp32") else 2e-2
-            assert v < tol, json.dumps(o)
+            assert v < selfcheck.syncbn_tolerance(k), json.dumps(o)
 
 
 @pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
 def test_syncbn_model_matches_torch_syncbn(native_lib):
-    """Whole ResNet-18 under DDP + SyncBN.  The first-step loss must agree with torch's DDP + SyncBatchNorm;
-    parameters are only loosely compared: tiny per-GPU batches through 20 normalisations amplify rounding
-    so much that torch's own result is tens of percent away from a single-GPU run on the global batch."""
+    """Whole ResNet-18 under DDP + SyncBN, 64 images per rank (a well-conditioned batch: with 8 per rank the 20
+    normalisations amplify rounding so much that torch's own result is tens of percent away from a single-GPU
+    run on the global batch).  Loss, first-step parameters and BN buffers must agree with torch's DDP + SyncBatchNorm."""
     outs = _launch(["--syncbn"], 2, 29662)
     for o in outs:
         assert o["ranks_identical"], json.dumps(o)
         assert o["first_loss_rel"] < 1e-3, json.dumps(o)
-        assert o["first_param_rel"] < 0.5, json.dumps(o)
-        assert o["bn_buffer_rel"] < 5e-2, json.dumps(o)
+        assert o["first_param_rel"] < 2e-2, json.dumps(o)
+        assert o["bn_buffer_rel"] < 1e-3, json.dumps(o)
 
 
 @pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
