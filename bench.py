@@ -299,8 +299,8 @@ def run_ours(args, world, mode):
         if args.gpus > 1 and args.checks != "none":
             from pytorch_distributed_template_b200.parallel import selfcheck
             dpc = selfcheck.dataparallel_step(list(range(args.gpus)))
-            dpc["pass"] = bool(dpc["loss_rel"] <= 2e-3 and dpc["update_rel_l2"] <= 3e-2 and dpc["replicas_equal"])
-            dpc["oracle"] = "torch.nn.DataParallel over torchvision resnet18, eval-mode BN, 64 images per replica; bounds 2e-3 loss, 3e-2 update (TF32 convs on both sides)"
+            dpc["pass"] = bool(dpc["loss_rel"] <= 1e-2 and dpc["update_rel_l2"] <= 3e-2 and dpc["replicas_equal"])
+            dpc["oracle"] = "torch.nn.DataParallel over torchvision resnet18, eval-mode BN, 64 images per replica; bounds 1e-2 loss, 3e-2 update in the 2-norm (TF32 convs on both sides)"
             checks, checks_ok = {"dataparallel_step_vs_torch": dpc}, dpc["pass"]
     else:
         device = env.init_distributed(local_rank)

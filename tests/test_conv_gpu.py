@@ -165,7 +165,8 @@ def test_tf32_conv_fprop_and_wgrad(native_lib, cin, cout, hw, k, stride, pad):
 def test_tf32_model_paths(native_lib):
     """fp32 ResNet-18 step (stem, strided dgrad, linear) through the kind::tf32 kernels against torch fp32 (TF32
     off) on a well-conditioned batch (64 images).  Calibrated bound: cuDNN's own TF32 gradients are measured
-    against the same fp32 truth and ours may be at most 2x as far away (and within 2 % in the 2-norm)."""
+    against the same fp32 truth (measured on B200: 10.4 % in the 2-norm after 20 BatchNorm layers — TF32 itself,
+    not an implementation, sets that scale) and ours may be at most 1.3x as far away."""
     import copy
     import torchvision
     from pytorch_distributed_template_b200.models import create_model
@@ -197,8 +198,8 @@ def test_tf32_model_paths(native_lib):
     assert torch.isfinite(g_ours).all()
     e_ours = ((g_ours - g_true).norm() / g_true.norm()).item()
     e_torch = ((g_torch - g_true).norm() / g_true.norm()).item()
-    assert e_ours <= 2.0 * e_torch + 1e-4, (e_ours, e_torch)
-    assert e_ours <= 2e-2, (e_ours, e_torch)
+    assert e_ours <= 1.3 * e_torch + 1e-3, (e_ours, e_torch)
+    assert e_ours <= 0.2, (e_ours, e_torch)
 
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])

@@ -206,8 +206,9 @@ def test_resnet18_amp_step_matches_torch_autocast(native_lib, lp):
     """Whole flagship step (native conv/BN/pool/CE kernels, shadow weights, fused SGD, GradScaler) against an fp32
     torchvision step on the same weights and a well-conditioned batch (64 images).  The bound is CALIBRATED, not
     guessed: torch's own autocast step in the same dtype is measured against the same fp32 truth, and our update
-    may be at most 1.5x as far from the truth as torch's (and in absolute terms within 5 % of the step for fp16,
-    15 % for bf16).  fp16 is the reference's dtype (/root/reference/distributed_syncBN_amp.py:259) and runs with
+    may be at most 1.2x as far from the truth as torch's.  (Measured on B200, relative to the size of the step:
+    torch 0.136 / ours 0.133 in fp16, torch 0.376 / ours 0.373 in bf16 — 16-bit activations through 20 BatchNorm
+    layers set that scale, for any implementation.)  fp16 is the reference's dtype (/root/reference/distributed_syncBN_amp.py:259) and runs with
     dynamic loss scaling end to end here."""
     import copy
     import os
@@ -257,8 +258,8 @@ def test_resnet18_amp_step_matches_torch_autocast(native_lib, lp):
         step = (truth - init).norm().item()
         e_ours, e_torch = (ours - truth).norm().item() / step, (theirs - truth).norm().item() / step
         assert loss.item() == pytest.approx(l32.item(), rel=5e-3 if lp == torch.float16 else 2e-2)
-        assert e_ours <= 1.5 * e_torch + 1e-3, (e_ours, e_torch)
-        assert e_ours <= (0.05 if lp == torch.float16 else 0.15), (e_ours, e_torch)
+        assert e_ours <= 1.2 * e_torch + 1e-3, (e_ours, e_torch)
+        assert e_ours <= (0.25 if lp == torch.float16 else 0.6), (e_ours, e_torch)
     finally:
         env.shutdown_distributed()
 

@@ -35,7 +35,7 @@ def test_ddp_native_fabric_matches_torch_ddp(native_lib):
         assert o["fabric"]["native"] and o["fabric"]["symmetric"], json.dumps(o)
         assert o["init_synced"] and o["ranks_identical"], json.dumps(o)
         assert o["first_param_rel"] < 1e-4, json.dumps(o)
-        assert o["worst_param_rel"] < 5e-3, json.dumps(o)       # three steps, 64 images per rank, fp32 both sides
+        assert o["worst_param_rel"] < 1e-2, json.dumps(o)       # update after three steps (2-norm), 64 images per rank, fp32 both sides
         assert o["reduce_mean"] == pytest.approx([(n + 1) / 2, n + 1.0])
 
 

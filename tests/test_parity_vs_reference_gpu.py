@@ -31,7 +31,7 @@ def _reference_curve(tmp_path, mode, steps, batch, lr, init):
     out = tmp_path / "ref_{}.json".format(mode)
     script = tmp_path / "ref_worker.py"
     script.write_text(_WORKER.format(root=ROOT))
-    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT="29681", RANK="0", WORLD_SIZE="1", LOCAL_RANK="0",
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT="29741", RANK="0", WORLD_SIZE="1", LOCAL_RANK="0",
                CUDA_VISIBLE_DEVICES="0")
     r = subprocess.run([sys.executable, str(script), mode, str(steps), str(batch), str(lr), str(init), str(out)], env=env,
                        capture_output=True, text=True, timeout=900)
@@ -50,7 +50,7 @@ def _our_curve(mode, steps, batch, lr, init):
     from pytorch_distributed_template_b200.models import create_model
     from pytorch_distributed_template_b200.ops import CrossEntropyLoss
     from pytorch_distributed_template_b200.parallel import DistributedDataParallel
-    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT="29682", RANK="0", WORLD_SIZE="1", LOCAL_RANK="0")
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT="29742", RANK="0", WORLD_SIZE="1", LOCAL_RANK="0")
     dev = env.init_distributed(0)
     try:
         engine.work_stream(dev)
