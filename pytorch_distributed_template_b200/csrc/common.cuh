@@ -4,6 +4,8 @@
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 #include <stdint.h>
+#include <mutex>
+#include <unordered_map>
 
 #ifndef PDT_MAX_RANKS
 #define PDT_MAX_RANKS 8
@@ -28,6 +30,30 @@ typedef struct PdtPeers { void* p[PDT_MAX_RANKS]; } PdtPeers;   // by-value kern
 #endif
 
 namespace pdt {
+
+// TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's
+// memory hung the GPU.  The launchers ask this before they pick a cluster size > 1 for a kernel whose tensor
+// map covers `p`; anything that is not known to live on the current device runs without multicast (each CTA
+// fetches the tile itself).  Answers are cached per (device, pointer); a pointer first seen during stream
+// capture is not queried and counts as "not local".
+inline bool memory_on_current_device(const void* p, cudaStream_t stream) {
+  static std::mutex mu;
+  static std::unordered_map<uint64_t, bool> cache;
+  int dev = -1;
+  if (p == nullptr || cudaGetDevice(&dev) != cudaSuccess) return false;
+  const uint64_t key = reinterpret_cast<uint64_t>(p) ^ ((uint64_t)(dev + 1) << 56);
+  std::lock_guard<std::mutex> lock(mu);
+  auto it = cache.find(key);
+  if (it != cache.end()) return it->second;
+  cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(stream, &st) != cudaSuccess || st != cudaStreamCaptureStatusNone) { cudaGetLastError(); return false; }
+  cudaPointerAttributes attr;
+  bool local = false;
+  if (cudaPointerGetAttributes(&attr, p) == cudaSuccess) local = attr.type == cudaMemoryTypeDevice && attr.device == dev;
+  else cudaGetLastError();
+  cache[key] = local;
+  return local;
+}
 
 __device__ __forceinline__ uint64_t globaltimer_ns() {
   uint64_t t;

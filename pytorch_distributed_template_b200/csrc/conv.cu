@@ -640,12 +640,13 @@ int esize_of(int dtype) { return dtype == PDT_FP32 ? 4 : 2; }
 // Cluster size for the forward / data-gradient kernel: multicast pays when the filter tile is at least as
 // large as the activation tile (BN >= 128) and there are enough M tiles to keep every cluster busy.
 // PDT_CONV_CLUSTER=1|2|4 overrides.
-int cluster_size_for(int BN, const ConvGeom& g) {
+int cluster_size_for(int BN, const ConvGeom& g, const void* filter, cudaStream_t stream) {
   static int env = -1;
   if (env < 0) { const char* e = getenv("PDT_CONV_CLUSTER"); env = e ? atoi(e) : 0; }
   int cl = env > 0 ? env : 2;     // 4 measured the same per launch but only 33 clusters of 4 are co-resident (132 of 148 SMs)
   if (BN < 128 || (cl != 2 && cl != 4)) return 1;
   if (g.m_tiles < 148) return 1;                            // fewer M tiles than SMs: keep every SM on a tile of its own
+  if (!memory_on_current_device(filter, stream)) return 1;  // the multicast tile (the filter) must be this GPU's memory
   return cl;
 }
 
@@ -709,7 +710,7 @@ template <int BN>
 int launch_fprop(const void* x, const void* w, void* y, const float* bias, int dtype, const ConvGeom& g, const BnStats& bs,
                  cudaStream_t stream) {
   CUtensorMap tmA, tmB;
-  const int cl = cluster_size_for(BN, g);
+  const int cl = cluster_size_for(BN, g, w, stream);
   {
     cuuint64_t dims[4] = {(cuuint64_t)g.Cx, (cuuint64_t)g.W, (cuuint64_t)g.H, (cuuint64_t)g.N};
     cuuint64_t strides[3] = {(cuuint64_t)g.x_sw, (cuuint64_t)g.x_sh, (cuuint64_t)g.x_sn};

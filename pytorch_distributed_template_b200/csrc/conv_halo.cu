@@ -949,11 +949,12 @@ int launch(const void* x, const void* w, void* y, int dtype, const HaloGeom& g, 
 }
 
 // Filter-tap multicast between CTA pairs for the streamed 128-wide variant (PDT_CONV_CLUSTER=1 disables).
-int halo_cluster(const HaloGeom& g, int sms) {
+int halo_cluster(const HaloGeom& g, int sms, const void* filter, cudaStream_t stream) {
   static int env = -1;
   if (env < 0) { const char* e = getenv("PDT_CONV_CLUSTER"); env = e ? atoi(e) : 0; }
   if (env == 1) return 1;
-  return g.num_tiles >= 2 * sms ? 2 : 1;
+  if (g.num_tiles < 2 * sms) return 1;
+  return memory_on_current_device(filter, stream) ? 2 : 1;   // the multicast tile (the filter) must be this GPU's memory
 }
 
 }  // namespace
@@ -994,7 +995,7 @@ int pdt_conv3x3_halo(const void* x, const void* w, void* y, int dtype, int N, in
   const bool resident = (C == 64 && K == 64);
   int sms_q = 148;
   { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms_q, cudaDevAttrMultiProcessorCount, dev); }
-  const int cl = (K == 128) ? halo_cluster(g, sms_q) : 1;
+  const int cl = (K == 128) ? halo_cluster(g, sms_q, w, stream) : 1;
   const CUtensorMapDataType dt = dtype == PDT_FP16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
   CUtensorMap tmX, tmW;
   {
