@@ -423,6 +423,7 @@ struct Pipe {
       fence_barrier_init();
     }
     __syncthreads();
+    pdl_enter();       // the ring is set up; nothing of the previous kernel's output has been touched yet
   }
   __device__ __forceinline__ void advance() { if (++s == S) { s = 0; ph ^= 1; } }
   // whole producer warp
@@ -867,6 +868,7 @@ __global__ void __launch_bounds__(256) k_bn_pool_fwd_321(const T* __restrict__ x
                                                         T* __restrict__ xmax, PoolGeom g, const float* __restrict__ mean,
                                                         const float* __restrict__ invstd, const float* __restrict__ gamma,
                                                         const float* __restrict__ beta) {
+  pdl_enter();
   extern __shared__ float sm[];
   float* scale = sm;
   float* shift = sm + g.C;
@@ -1000,6 +1002,7 @@ __global__ void __launch_bounds__(256) k_bn_pool_bwd_apply_321(const T* __restri
                                                               const float* __restrict__ mean, const float* __restrict__ invstd,
                                                               const float* __restrict__ gamma, const float* __restrict__ beta,
                                                               const float* __restrict__ k) {
+  pdl_enter();
   extern __shared__ float sm[];
   const int C = g.C;
   // dx = a*gg + b*x + c per channel: a = invstd*gamma, b = -k2*a, c = (mu*k2 - k1)*a; sh = forward shift
@@ -1094,12 +1097,12 @@ int bwd_reduce_stream(const void* dy, const void* y, const void* x, long M, int 
   const int grid = sp::grid_for(M * C / Vec<T>::N, 1);
   if (relu && y != nullptr) {
     PDT_CHECK(sp::optin(sp::k_bwd_reduce<T, true>));
-    sp::k_bwd_reduce<T, true><<<grid, sp::kThr, sp::kSmemBytes, stream>>>(
+    launch_pdl(sp::k_bwd_reduce<T, true>, dim3(grid), dim3(sp::kThr), sp::kSmemBytes, stream,
         reinterpret_cast<const T*>(dy), reinterpret_cast<const T*>(y), reinterpret_cast<const T*>(x), M, C, mean, invstd, gamma,
         beta, relu, partial, counter, make_comm(comm), dgamma, dbeta, out_k, count);
   } else {
     PDT_CHECK(sp::optin(sp::k_bwd_reduce<T, false>));
-    sp::k_bwd_reduce<T, false><<<grid, sp::kThr, sp::kSmemBytes, stream>>>(
+    launch_pdl(sp::k_bwd_reduce<T, false>, dim3(grid), dim3(sp::kThr), sp::kSmemBytes, stream,
         reinterpret_cast<const T*>(dy), nullptr, reinterpret_cast<const T*>(x), M, C, mean, invstd, gamma, beta, relu, partial,
         counter, make_comm(comm), dgamma, dbeta, out_k, count);
   }
@@ -1110,7 +1113,7 @@ template <typename T, bool HY, bool HD>
 int bwd_apply_launch(const void* dy, const void* y, const void* x, void* dx, void* dres, long nvec, int C, const float* mean,
                      const float* invstd, const float* gamma, const float* beta, const float* k, int relu, cudaStream_t stream) {
   PDT_CHECK(sp::optin(sp::k_bwd_apply<T, HY, HD>));
-  sp::k_bwd_apply<T, HY, HD><<<sp::grid_for(nvec), sp::kThr, sp::kSmemBytes, stream>>>(
+  launch_pdl(sp::k_bwd_apply<T, HY, HD>, dim3(sp::grid_for(nvec)), dim3(sp::kThr), sp::kSmemBytes, stream,
       reinterpret_cast<const T*>(dy), reinterpret_cast<const T*>(y), reinterpret_cast<const T*>(x), reinterpret_cast<T*>(dx),
       reinterpret_cast<T*>(dres), nvec, C, mean, invstd, gamma, beta, k, relu);
   return (int)cudaGetLastError();
@@ -1158,7 +1161,7 @@ int pdt_bn_pool_fwd(const void* x, void* y, int8_t* idx, void* xmax, int dtype, 
   long nb = (total + 255) / 256;
   if (nb > 148 * 16) nb = 148 * 16;
   if (ks == 3 && st == 2 && pd == 1) {
-    BNP_DISPATCH(dtype, k_bn_pool_fwd_321<T><<<(int)nb, 256, 2 * C * sizeof(float), stream>>>(
+    BNP_DISPATCH(dtype, launch_pdl(k_bn_pool_fwd_321<T>, dim3((unsigned)nb), dim3(256), 2 * C * sizeof(float), stream,
         reinterpret_cast<const T*>(x), reinterpret_cast<T*>(y), idx, reinterpret_cast<T*>(xmax), g, mean, invstd, gamma, beta));
   } else {
     BNP_DISPATCH(dtype, k_bn_pool_fwd<T><<<(int)nb, 256, 2 * C * sizeof(float), stream>>>(
@@ -1204,7 +1207,7 @@ int pdt_bn_pool_bwd_apply(const void* dpool, const int8_t* idx, const void* x, v
     const long total = (long)N * (H / 2) * (W / 2) * (C / 8);
     long nb = (total + 255) / 256;
     if (nb > 148 * 32) nb = 148 * 32;
-    BNP_DISPATCH(dtype, k_bn_pool_bwd_apply_321<T><<<(unsigned)nb, 256, 4 * C * sizeof(float), stream>>>(
+    BNP_DISPATCH(dtype, launch_pdl(k_bn_pool_bwd_apply_321<T>, dim3((unsigned)nb), dim3(256), 4 * C * sizeof(float), stream,
         reinterpret_cast<const T*>(dpool), idx, reinterpret_cast<const T*>(x), reinterpret_cast<T*>(dx), g, mean, invstd,
         gamma, beta, k));
     return (int)cudaGetLastError();
@@ -1231,7 +1234,7 @@ int pdt_bn_fwd_stats(const void* x, long M, int C, int dtype, void* scratch, con
     if (!shape_ok<T>(C)) return PDT_E_UNSUPPORTED;
     if (stream_enabled() && sp::ok<T>(C, {x})) {
       PDT_CHECK(sp::optin(sp::k_fwd_stats<T>));
-      sp::k_fwd_stats<T><<<sp::grid_for(M * C / Vec<T>::N, 1), sp::kThr, sp::kSmemBytes, stream>>>(
+      launch_pdl(sp::k_fwd_stats<T>, dim3(sp::grid_for(M * C / Vec<T>::N, 1)), dim3(sp::kThr), sp::kSmemBytes, stream,
           reinterpret_cast<const T*>(x), M, C, partial, counter, make_comm(comm), running_mean, running_var, momentum, eps,
           save_mean, save_invstd);
       return (int)cudaGetLastError();
@@ -1304,12 +1307,12 @@ int pdt_bn_fwd_apply(const void* x, const void* res, void* y, long M, int C, int
     if (stream_enabled() && sp::ok<T>(C, {x, res, y})) {
       if (res != nullptr) {
         PDT_CHECK(sp::optin(sp::k_fwd_apply<T, true>));
-        sp::k_fwd_apply<T, true><<<sp::grid_for(nvec), sp::kThr, sp::kSmemBytes, stream>>>(
+        launch_pdl(sp::k_fwd_apply<T, true>, dim3(sp::grid_for(nvec)), dim3(sp::kThr), sp::kSmemBytes, stream,
             reinterpret_cast<const T*>(x), reinterpret_cast<const T*>(res), reinterpret_cast<T*>(y), nvec, C, mean, stat2,
             gamma, beta, relu, eval, eps);
       } else {
         PDT_CHECK(sp::optin(sp::k_fwd_apply<T, false>));
-        sp::k_fwd_apply<T, false><<<sp::grid_for(nvec), sp::kThr, sp::kSmemBytes, stream>>>(
+        launch_pdl(sp::k_fwd_apply<T, false>, dim3(sp::grid_for(nvec)), dim3(sp::kThr), sp::kSmemBytes, stream,
             reinterpret_cast<const T*>(x), nullptr, reinterpret_cast<T*>(y), nvec, C, mean, stat2, gamma, beta, relu, eval, eps);
       }
       return (int)cudaGetLastError();

@@ -4,8 +4,10 @@
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 #include <stdint.h>
+#include <cstdlib>
 #include <mutex>
 #include <unordered_map>
+#include <utility>
 
 #ifndef PDT_MAX_RANKS
 #define PDT_MAX_RANKS 8
@@ -53,6 +55,40 @@ inline bool memory_on_current_device(const void* p, cudaStream_t stream) {
   else cudaGetLastError();
   cache[key] = local;
   return local;
+}
+
+// ---- programmatic dependent launch (PDL) -------------------------------------------------------------------
+// A kernel launched through launch_pdl() may START while its predecessor in the stream is still draining: its
+// CTAs are scheduled as the predecessor's retire and run their prologue (shared-memory carve-up, mbarrier init,
+// TMEM allocation, tensor-map prefetch).  pdl_wait() then blocks until the predecessor has COMPLETED and its
+// memory is visible, so every kernel calls it before its first access to global memory; pdl_trigger() lets the
+// NEXT kernel's CTAs start the same way.  At 150 images per GPU a step is ~170 kernels of 10-40 us each, and
+// the launch gap + tail + prologue between two of them is what this can hide.  Kernels launched without the
+// attribute (torch's own, <<<>>>) see both calls as no-ops.  Measured on B200 inside the captured step: 4.094 ->
+// 4.062 ms at 150 images (-0.8 %), within noise at 1200 images (the kernels are persistent one-wave grids, so
+// there is little tail to overlap and graph replay already has ~1 us gaps).  Hence opt-in: PDT_PDL=1.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_enter() { pdl_wait(); pdl_trigger(); }
+
+inline bool pdl_enabled() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("PDT_PDL"); v = (e != nullptr && e[0] == '1') ? 1 : 0; }
+  return v == 1;
+}
+inline int pdl_attr(cudaLaunchAttribute* a) {      // fills a[0]; returns the number of attributes to use (0 or 1)
+  a[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  a[0].val.programmaticStreamSerializationAllowed = 1;
+  return pdl_enabled() ? 1 : 0;
+}
+template <typename... P, typename... A>
+inline cudaError_t launch_pdl(void (*kern)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, A&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  cfg.numAttrs = pdl_attr(attr);
+  cfg.attrs = attr;
+  return cudaLaunchKernelEx(&cfg, kern, std::forward<A>(args)...);
 }
 
 __device__ __forceinline__ uint64_t globaltimer_ns() {

@@ -157,6 +157,7 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   if (CL > 1) cluster_sync_all();        // peers' barriers are initialised before anything is multicast at them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_enter();                           // everything above overlapped the previous kernel's tail
 
   if (warp == 0) {
     // ================= TMA producer (whole warp converged, one elected lane issues) =================
@@ -462,6 +463,7 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_enter();
 
   if (warp == 0) {
     {
@@ -595,6 +597,7 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
 
 // Ordered fold of the split-K slabs of the deterministic weight gradient: dw[i] += part[0][i] + part[1][i] + ...
 __global__ void __launch_bounds__(256) k_wgrad_fold(float* __restrict__ dw, const float* __restrict__ part, size_t total, int splits) {
+  pdl_enter();
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     float a = 0.f;
     for (int s = 0; s < splits; ++s) a += part[(size_t)s * total + i];
@@ -661,7 +664,7 @@ int launch_igemm_cl(const CUtensorMap& tmA, const CUtensorMap& tmB, void* y, con
   cfg.blockDim = dim3(kThreads);
   cfg.dynamicSmemBytes = C::kSmemBytes;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   int nattr = 0;
   int clusters = sms / CL;
   if (CL > 1) {
@@ -683,6 +686,7 @@ int launch_igemm_cl(const CUtensorMap& tmA, const CUtensorMap& tmB, void* y, con
   }
   if (clusters > units) clusters = units;
   cfg.gridDim = dim3(clusters * CL);
+  nattr += pdl_attr(attr + nattr);
   cfg.attrs = attr; cfg.numAttrs = nattr;
   ConvGeom gg = g;
   {
@@ -812,15 +816,15 @@ int launch_wgrad(const void* x, const void* dy, float* dw, int dtype, WgradGeom&
   if (dtype == PDT_FP16) {
     auto kern = k_conv_wgrad<BN, __half>;
     PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-    kern<<<grid, kThreads, smem_bytes, stream>>>(tmX, tmDY, dw, part, wg);
+    PDT_CHECK(launch_pdl(kern, dim3(grid), dim3(kThreads), smem_bytes, stream, tmX, tmDY, dw, part, wg));
   } else if (dtype == PDT_FP32) {
     auto kern = k_conv_wgrad<BN, float>;
     PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-    kern<<<grid, kThreads, smem_bytes, stream>>>(tmX, tmDY, dw, part, wg);
+    PDT_CHECK(launch_pdl(kern, dim3(grid), dim3(kThreads), smem_bytes, stream, tmX, tmDY, dw, part, wg));
   } else {
     auto kern = k_conv_wgrad<BN, __nv_bfloat16>;
     PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-    kern<<<grid, kThreads, smem_bytes, stream>>>(tmX, tmDY, dw, part, wg);
+    PDT_CHECK(launch_pdl(kern, dim3(grid), dim3(kThreads), smem_bytes, stream, tmX, tmDY, dw, part, wg));
   }
   if (part != nullptr) {
     PDT_CHECK(cudaGetLastError());

@@ -167,6 +167,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
   if (CL > 1) cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_enter();
 
   if (warp == 0) {
     // ================= TMA producer (whole warp converged, one elected lane issues) =================
@@ -573,6 +574,7 @@ k_wgrad3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_enter();
   const int slots = g.TR * g.Wp;
   const int ksteps = (slots + 15) >> 4;
   const uint32_t dy_bytes = (uint32_t)slots * 128u;
@@ -719,6 +721,7 @@ k_stem_conv(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUt
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_enter();
 
   if (warp == 0) {
     // ================= TMA producer =================
@@ -919,11 +922,13 @@ int launch_t(void* y, const HaloGeom& g, const BnStats& bs, const CUtensorMap& t
   cfg.blockDim = dim3(kThreads);
   cfg.dynamicSmemBytes = C::kSmemBytes;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
+  int nattr = 0;
   int grid = g.num_tiles < sms ? g.num_tiles : sms;
   if (CL > 1) {
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = CL; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    nattr = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
     static int max_clusters = -1;       // resident clusters of this kernel: the persistent grid must be one wave
     if (max_clusters < 0) {
@@ -936,6 +941,8 @@ int launch_t(void* y, const HaloGeom& g, const BnStats& bs, const CUtensorMap& t
     grid = clusters * CL;
   }
   cfg.gridDim = dim3(grid);
+  nattr += pdl_attr(attr + nattr);
+  cfg.attrs = attr; cfg.numAttrs = nattr;
   PDT_CHECK(cudaLaunchKernelEx(&cfg, kern, tmX, tmW, tmY, reinterpret_cast<T*>(y), g, bs));
   return (int)cudaGetLastError();
 }
@@ -1096,11 +1103,11 @@ int pdt_conv3x3_wgrad_halo(const void* x, const void* dy, float* dw, int dtype, 
   if (dtype == PDT_FP16) {
     auto kern = k_wgrad3x3_halo<__half>;
     PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, WHCfg::kSmemBytes));
-    kern<<<grid, 128, WHCfg::kSmemBytes, stream>>>(tmX, tmDY, dw, g);
+    PDT_CHECK(launch_pdl(kern, dim3(grid), dim3(128), WHCfg::kSmemBytes, stream, tmX, tmDY, dw, g));
   } else {
     auto kern = k_wgrad3x3_halo<__nv_bfloat16>;
     PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, WHCfg::kSmemBytes));
-    kern<<<grid, 128, WHCfg::kSmemBytes, stream>>>(tmX, tmDY, dw, g);
+    PDT_CHECK(launch_pdl(kern, dim3(grid), dim3(128), WHCfg::kSmemBytes, stream, tmX, tmDY, dw, g));
   }
   return (int)cudaGetLastError();
 }
@@ -1175,11 +1182,11 @@ int pdt_stem_conv(const void* xs, const void* wp, void* y, int dtype, int N, int
   if (dtype == PDT_FP16) {
     auto kern = k_stem_conv<__half>;
     PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SCfg::kSmemBytes));
-    kern<<<grid, kThreads, SCfg::kSmemBytes, stream>>>(tmX, tmW, tmY, g, bs);
+    PDT_CHECK(launch_pdl(kern, dim3(grid), dim3(kThreads), SCfg::kSmemBytes, stream, tmX, tmW, tmY, g, bs));
   } else {
     auto kern = k_stem_conv<__nv_bfloat16>;
     PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SCfg::kSmemBytes));
-    kern<<<grid, kThreads, SCfg::kSmemBytes, stream>>>(tmX, tmW, tmY, g, bs);
+    PDT_CHECK(launch_pdl(kern, dim3(grid), dim3(kThreads), SCfg::kSmemBytes, stream, tmX, tmW, tmY, g, bs));
   }
   return (int)cudaGetLastError();
 }

@@ -25,6 +25,7 @@ template <typename T>
 __global__ void __launch_bounds__(128) k_ce_fwd(const T* __restrict__ logits, const long long* __restrict__ target, int B, int K,
                                                float* __restrict__ dlogits_unit, float2* __restrict__ row_out,
                                                unsigned* counter, float* __restrict__ out) {
+  pdl_enter();
   __shared__ float s_red[4];
   __shared__ int s_idx[4];
   __shared__ int s_last;
@@ -108,6 +109,7 @@ __global__ void __launch_bounds__(128) k_ce_fwd(const T* __restrict__ logits, co
 template <typename T>
 __global__ void __launch_bounds__(256) k_scale_cast(const float* __restrict__ in, const float* __restrict__ scale, T* __restrict__ out,
                                                    size_t n) {
+  pdl_enter();
   const float s = *scale;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
     out[i] = Cvt<T>::from_f(in[i] * s);
@@ -191,6 +193,7 @@ __global__ void __launch_bounds__(256) k_maxpool_bwd(const T* __restrict__ dy, c
 
 template <typename T>
 __global__ void __launch_bounds__(256) k_avgpool_fwd(const T* __restrict__ x, T* __restrict__ y, int N, int HW, int C) {
+  pdl_enter();
   const int cg = C / 8;
   const long total = (long)N * cg;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
@@ -214,6 +217,7 @@ __global__ void __launch_bounds__(256) k_avgpool_fwd(const T* __restrict__ x, T*
 
 template <typename T>
 __global__ void __launch_bounds__(256) k_avgpool_bwd(const T* __restrict__ dy, T* __restrict__ dx, int N, int HW, int C) {
+  pdl_enter();
   const int cg = C / 8;
   const long total = (long)N * HW * cg;
   const float inv = 1.f / (float)HW;
@@ -263,6 +267,7 @@ struct StemNorm { float sc[3], bs[3]; };
 template <typename T, typename TI>
 __global__ void __launch_bounds__(256) k_stem_s2d(const TI* __restrict__ x, T* __restrict__ y, int N, int H, int W, int HP, int WP,
                                                  int pad, StemNorm nm) {
+  pdl_enter();
   const long total = (long)N * HP * WP;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
     const int j = (int)(i % WP);
@@ -326,18 +331,18 @@ int pdt_ce_fwd(const void* logits, int dtype, const long long* target, int B, in
   unsigned* counter = reinterpret_cast<unsigned*>(scratch);
   float2* rows = reinterpret_cast<float2*>(reinterpret_cast<char*>(scratch) + 256);
   if (dtype == PDT_FP32)
-    k_ce_fwd<float><<<B, 128, 0, stream>>>(reinterpret_cast<const float*>(logits), target, B, K, dlogits_unit, rows, counter, out);
+    launch_pdl(k_ce_fwd<float>, dim3(B), dim3(128), 0, stream, reinterpret_cast<const float*>(logits), target, B, K, dlogits_unit, rows, counter, out);
   else
-    LP_DISPATCH(dtype, k_ce_fwd<T><<<B, 128, 0, stream>>>(reinterpret_cast<const T*>(logits), target, B, K, dlogits_unit, rows, counter, out));
+    LP_DISPATCH(dtype, launch_pdl(k_ce_fwd<T>, dim3(B), dim3(128), 0, stream, reinterpret_cast<const T*>(logits), target, B, K, dlogits_unit, rows, counter, out));
   return (int)cudaGetLastError();
 }
 
 int pdt_scale_cast(const float* in, const float* scale, void* out, int dtype, size_t n, cudaStream_t stream) {
   const int nb = grid_for((long)n, 256 * 4);
   if (dtype == PDT_FP32)
-    k_scale_cast<float><<<nb, 256, 0, stream>>>(in, scale, reinterpret_cast<float*>(out), n);
+    launch_pdl(k_scale_cast<float>, dim3(nb), dim3(256), 0, stream, in, scale, reinterpret_cast<float*>(out), n);
   else
-    LP_DISPATCH(dtype, k_scale_cast<T><<<nb, 256, 0, stream>>>(in, scale, reinterpret_cast<T*>(out), n));
+    LP_DISPATCH(dtype, launch_pdl(k_scale_cast<T>, dim3(nb), dim3(256), 0, stream, in, scale, reinterpret_cast<T*>(out), n));
   return (int)cudaGetLastError();
 }
 
@@ -361,14 +366,14 @@ int pdt_maxpool_bwd(const void* dy, const int8_t* idx, void* dx, int dtype, int 
 
 int pdt_avgpool_fwd(const void* x, void* y, int dtype, int N, int HW, int C, cudaStream_t stream) {
   if (C % 8) return PDT_E_UNSUPPORTED;
-  LP_DISPATCH(dtype, k_avgpool_fwd<T><<<grid_for((long)N * (C / 8), 256), 256, 0, stream>>>(
+  LP_DISPATCH(dtype, launch_pdl(k_avgpool_fwd<T>, dim3(grid_for((long)N * (C / 8), 256)), dim3(256), 0, stream, 
       reinterpret_cast<const T*>(x), reinterpret_cast<T*>(y), N, HW, C));
   return (int)cudaGetLastError();
 }
 
 int pdt_avgpool_bwd(const void* dy, void* dx, int dtype, int N, int HW, int C, cudaStream_t stream) {
   if (C % 8) return PDT_E_UNSUPPORTED;
-  LP_DISPATCH(dtype, k_avgpool_bwd<T><<<grid_for((long)N * HW * (C / 8), 256), 256, 0, stream>>>(
+  LP_DISPATCH(dtype, launch_pdl(k_avgpool_bwd<T>, dim3(grid_for((long)N * HW * (C / 8), 256)), dim3(256), 0, stream, 
       reinterpret_cast<const T*>(dy), reinterpret_cast<T*>(dx), N, HW, C));
   return (int)cudaGetLastError();
 }
@@ -378,10 +383,10 @@ int pdt_stem_s2d(const float* x, void* y, int dtype, int N, int H, int W, int pa
   const int nb = grid_for((long)N * HP * WP, 256);
   StemNorm nm = {{1.f, 1.f, 1.f}, {0.f, 0.f, 0.f}};
   if (dtype == PDT_FP32) {
-    k_stem_s2d<float, float><<<nb, 256, 0, stream>>>(x, reinterpret_cast<float*>(y), N, H, W, HP, WP, pad, nm);
+    launch_pdl(k_stem_s2d<float, float>, dim3(nb), dim3(256), 0, stream, x, reinterpret_cast<float*>(y), N, H, W, HP, WP, pad, nm);
     return (int)cudaGetLastError();
   }
-  LP_DISPATCH(dtype, k_stem_s2d<T, float><<<nb, 256, 0, stream>>>(x, reinterpret_cast<T*>(y), N, H, W, HP, WP, pad, nm));
+  LP_DISPATCH(dtype, launch_pdl(k_stem_s2d<T, float>, dim3(nb), dim3(256), 0, stream, x, reinterpret_cast<T*>(y), N, H, W, HP, WP, pad, nm));
   return (int)cudaGetLastError();
 }
 
@@ -395,10 +400,10 @@ int pdt_stem_s2d_u8(const unsigned char* x, void* y, int dtype, int N, int H, in
   StemNorm nm;
   for (int c = 0; c < 3; ++c) { nm.sc[c] = scale[c]; nm.bs[c] = bias[c]; }
   if (dtype == PDT_FP32) {
-    k_stem_s2d<float, unsigned char><<<nb, 256, 0, stream>>>(x, reinterpret_cast<float*>(y), N, H, W, HP, WP, pad, nm);
+    launch_pdl(k_stem_s2d<float, unsigned char>, dim3(nb), dim3(256), 0, stream, x, reinterpret_cast<float*>(y), N, H, W, HP, WP, pad, nm);
     return (int)cudaGetLastError();
   }
-  LP_DISPATCH(dtype, k_stem_s2d<T, unsigned char><<<nb, 256, 0, stream>>>(x, reinterpret_cast<T*>(y), N, H, W, HP, WP, pad, nm));
+  LP_DISPATCH(dtype, launch_pdl(k_stem_s2d<T, unsigned char>, dim3(nb), dim3(256), 0, stream, x, reinterpret_cast<T*>(y), N, H, W, HP, WP, pad, nm));
   return (int)cudaGetLastError();
 }
 
@@ -488,6 +493,7 @@ extern "C" int pdt_dgrad_weight(const void* w, void* out, int K, int C, int R, i
 // slots and persistent buffers), a block finds its job from the running tile count.
 namespace {
 __global__ void __launch_bounds__(256) k_dgrad_weight_batched(const PdtDgradJob* __restrict__ jobs, int njobs) {
+  pdl_enter();
   __shared__ uint16_t tile[32][34];
   __shared__ PdtDgradJob jb;
   if (threadIdx.x == 0) {
@@ -524,7 +530,7 @@ __global__ void __launch_bounds__(256) k_dgrad_weight_batched(const PdtDgradJob*
 
 extern "C" int pdt_dgrad_weight_batched(const PdtDgradJob* jobs_dev, int njobs, int total_tiles, cudaStream_t stream) {
   if (njobs < 1 || total_tiles < 1) return 0;
-  k_dgrad_weight_batched<<<total_tiles, 256, 0, stream>>>(jobs_dev, njobs);
+  launch_pdl(k_dgrad_weight_batched, dim3(total_tiles), dim3(256), 0, stream, jobs_dev, njobs);
   return (int)cudaGetLastError();
 }
 
