@@ -19,7 +19,7 @@
 
 /* Bumped whenever an entry point is added or changes its signature; the Python binding refuses a library
  * that reports a different number (a stale build of an older checkout). */
-#define PDT_ABI_VERSION 10
+#define PDT_ABI_VERSION 11
 
 #ifdef __cplusplus
 extern "C" {
@@ -218,6 +218,9 @@ int pdt_abi_version(void);
  * stride-1 convolutions (cudnnConvolutionBackwardData, distributed.py:262). */
 int pdt_conv_fprop(const void* x, const void* w, void* y, int dtype, int N, int H, int W, int C, int K, int R, int S,
                    int stride, int pad, cudaStream_t stream);
+/* y = conv(x, w) + addend, addend laid out like y (same residual-gradient use as pdt_conv3x3_halo_add). */
+int pdt_conv_fprop_add(const void* x, const void* w, void* y, const void* addend, int dtype, int N, int H, int W, int C, int K,
+                       int R, int S, int stride, int pad, cudaStream_t stream);
 /* Convolution + BatchNorm batch statistics in one kernel: the epilogue also produces the per-channel
  * mean / invstd of y (and updates the running statistics), so BatchNorm needs no statistics pass of its
  * own (cudnnConvolutionForward + batch_norm statistics kernel).  Dense NHWC output, K <= 512.
@@ -230,6 +233,12 @@ int pdt_conv_fprop_bnstats(const void* x, const void* w, void* y, int dtype, int
  * descriptors; the 64x64 filter bank stays resident in shared memory.  scratch != NULL also yields the BatchNorm
  * batch statistics of y (as pdt_conv_fprop_bnstats).  Same cuDNN calls replaced as pdt_conv_fprop. */
 int pdt_conv3x3_halo_supported(int dtype, int N, int H, int W, int C, int K);
+/* pdt_conv3x3_halo with an optional addend [N][H][W][K] summed into the output in the epilogue (y = conv + addend;
+ * requires scratch == NULL).  As the data gradient of a residual block's first convolution it takes the shortcut
+ * gradient, replacing the ATen add that autograd issues per block in the reference's backward (distributed.py:262). */
+int pdt_conv3x3_halo_add(const void* x, const void* w, void* y, const void* addend, int dtype, int N, int H, int W, int C, int K,
+                         void* scratch, float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
+                         float* save_invstd, cudaStream_t stream);
 int pdt_conv3x3_halo(const void* x, const void* w, void* y, int dtype, int N, int H, int W, int C, int K, void* scratch,
                      float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
                      float* save_invstd, cudaStream_t stream);
@@ -263,7 +272,8 @@ int pdt_set_wgrad_workspace(void* ws, size_t bytes);
 int pdt_conv_fprop_ex(const void* x, const void* w, void* y, const float* bias, int dtype, int N, int H, int W, int C,
                       int Cx, long long x_sw, long long x_sh, long long x_sn, int K, int R, int S, int stride,
                       int pad_lo_h, int pad_lo_w, int pad_hi_h, int pad_hi_w, int P, int Q, int OH, int OW, int os,
-                      int oa, int ob, int dil_w, cudaStream_t stream);
+                      int oa, int ob, int dil_w, const void* addend /* laid out like the OH x OW output, or NULL */,
+                      cudaStream_t stream);
 int pdt_conv_wgrad_ex(const void* x, const void* dy, float* dw, int dtype, int N, int H, int W, int C, int Cx,
                       long long x_sw, long long x_sh, long long x_sn, int K, int R, int S, int stride, int pad_lo_h,
                       int pad_lo_w, int pad_hi_h, int pad_hi_w, int P, int Q, int dil_w, cudaStream_t stream);

@@ -61,6 +61,10 @@ struct ConvGeom {
   // (one N tile, k_blocks <= ring depth, no cluster).  The stem (4 k-blocks) otherwise re-fetched 32 KB of
   // filter per 128-pixel tile next to 64 KB of activations and ran at the L2 delivery limit.
   int resident_b;
+  // optional epilogue addend, same layout / dtype as the output: out = conv(...) + addend.  The data gradient
+  // of a residual block's first convolution adds the block's shortcut gradient here instead of leaving the sum
+  // to a separate elementwise pass (3 tensor passes saved per block).
+  const void* addend;
 };
 
 // Optional epilogue fusion: per-channel sum / sum of squares of the convolution output (the BatchNorm
@@ -270,6 +274,7 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         opix = (n * g.OH + (long)p * g.os + g.oa) * g.OW + (long)q * g.os + g.ob;
       }
       T* orow = out + opix * g.K + (long)nt * BN;
+      const T* arow = g.addend != nullptr ? reinterpret_cast<const T*>(g.addend) + opix * g.K + (long)nt * BN : nullptr;
 #pragma unroll (kRegStats ? 2 : 1)
       for (int c0 = 0; c0 < BN; c0 += 32) {
         uint32_t v[32];
@@ -313,6 +318,19 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                 const float4 b1 = *reinterpret_cast<const float4*>(bias + nt * BN + c0 + j + 4);
                 f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w;
                 f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
+              }
+              if (arow != nullptr) {
+                if constexpr (sizeof(T) == 4) {
+                  const float4 a0 = *reinterpret_cast<const float4*>(arow + c0 + j);
+                  const float4 a1 = *reinterpret_cast<const float4*>(arow + c0 + j + 4);
+                  f[0] += a0.x; f[1] += a0.y; f[2] += a0.z; f[3] += a0.w;
+                  f[4] += a1.x; f[5] += a1.y; f[6] += a1.z; f[7] += a1.w;
+                } else {
+                  float a[8];
+                  unpack8<T>(ldg_stream(arow + c0 + j), a);
+#pragma unroll
+                  for (int e = 0; e < 8; ++e) f[e] += a[e];
+                }
               }
               if constexpr (sizeof(T) == 4) {
                 *reinterpret_cast<float4*>(orow + c0 + j) = make_float4(f[0], f[1], f[2], f[3]);
@@ -845,6 +863,7 @@ void fill_dense(ConvGeom& g, int N, int H, int W, int C, int K, int R, int S, in
   g.OH = g.P; g.OW = g.Q; g.os = 1; g.oa = g.ob = 0;
   g.Cx = C;
   g.x_sw = (long long)C * es; g.x_sh = (long long)W * C * es; g.x_sn = (long long)H * W * C * es;
+  g.addend = nullptr;
 }
 
 int dispatch_fprop(const void* x, const void* w, void* y, const float* bias, int dtype, ConvGeom& g, cudaStream_t stream,
@@ -928,6 +947,7 @@ int pdt_conv_wgrad_ex(const void* x, const void* dy, float* dw, int dtype, int N
   g.m_tiles = g.n_tiles = 0;
   g.OH = P; g.OW = Q; g.os = 1; g.oa = g.ob = 0;
   g.Cx = Cx; g.x_sw = x_sw; g.x_sh = x_sh; g.x_sn = x_sn;
+  g.addend = nullptr;
   wg.rsc = R * S * C;
   wg.m_tiles = (wg.rsc + 127) / 128;
   wg.k_steps = (g.M + BKP - 1) / BKP;
@@ -949,6 +969,25 @@ int pdt_conv_fprop(const void* x, const void* w, void* y, int dtype, int N, int 
   ConvGeom g;
   fill_dense(g, N, H, W, C, K, R, S, stride, pad, es);
   if (g.P < 1 || g.Q < 1) return PDT_E_UNSUPPORTED;
+  return dispatch_fprop(x, w, y, nullptr, dtype, g, stream);
+}
+
+// y = conv(x, w) + addend (addend: [N][P][Q][K] like y).  Used as the data gradient of the first convolution of
+// a residual block with the block's shortcut gradient as addend (autograd's AccumulateGrad add, an ATen
+// elementwise kernel per block in the reference's backward, distributed.py:262).
+int pdt_conv_fprop_add(const void* x, const void* w, void* y, const void* addend, int dtype, int N, int H, int W, int C, int K,
+                       int R, int S, int stride, int pad, cudaStream_t stream) {
+  if (dtype != PDT_BF16 && dtype != PDT_FP16 && dtype != PDT_FP32) return PDT_E_UNSUPPORTED;
+  const int es = esize_of(dtype);
+  if (C % (16 / es) || K % 8 || R < 1 || S < 1 || stride < 1 || pad < 0) return PDT_E_UNSUPPORTED;
+  if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(w) | reinterpret_cast<uintptr_t>(y) |
+       reinterpret_cast<uintptr_t>(addend)) & 15) return PDT_E_UNSUPPORTED;
+  int e = load_driver_fns();
+  if (e) return e;
+  ConvGeom g;
+  fill_dense(g, N, H, W, C, K, R, S, stride, pad, es);
+  if (g.P < 1 || g.Q < 1) return PDT_E_UNSUPPORTED;
+  g.addend = addend;
   return dispatch_fprop(x, w, y, nullptr, dtype, g, stream);
 }
 
@@ -984,8 +1023,9 @@ int pdt_conv_fprop_bnstats(const void* x, const void* w, void* y, int dtype, int
 int pdt_conv_fprop_ex(const void* x, const void* w, void* y, const float* bias, int dtype, int N, int H, int W, int C,
                       int Cx, long long x_sw, long long x_sh, long long x_sn, int K, int R, int S, int stride,
                       int pad_lo_h, int pad_lo_w, int pad_hi_h, int pad_hi_w, int P, int Q, int OH, int OW, int os,
-                      int oa, int ob, int dil_w, cudaStream_t stream) {
+                      int oa, int ob, int dil_w, const void* addend, cudaStream_t stream) {
   if (dtype != PDT_BF16 && dtype != PDT_FP16 && dtype != PDT_FP32) return PDT_E_UNSUPPORTED;
+  if (reinterpret_cast<uintptr_t>(addend) & 15) return PDT_E_UNSUPPORTED;
   if (K % 8 || R < 1 || S < 1 || stride < 1 || P < 1 || Q < 1 || dil_w < 1 || (x_sw | x_sh | x_sn) % 16) return PDT_E_UNSUPPORTED;
   if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(w) | reinterpret_cast<uintptr_t>(y)) & 15) return PDT_E_UNSUPPORTED;
   int e = load_driver_fns();
@@ -998,6 +1038,7 @@ int pdt_conv_fprop_ex(const void* x, const void* w, void* y, const float* bias, 
   g.m_tiles = (g.M + BM - 1) / BM;
   g.OH = OH; g.OW = OW; g.os = os; g.oa = oa; g.ob = ob;
   g.Cx = Cx; g.x_sw = x_sw; g.x_sh = x_sh; g.x_sn = x_sn;
+  g.addend = addend;
   return dispatch_fprop(x, w, y, bias, dtype, g, stream);
 }
 

@@ -41,6 +41,7 @@ struct HaloGeom {
   int num_tiles;
   int c_chunks;
   uint32_t patch_bytes;   // (TR + 2) * Wp * 128
+  const void* addend;     // optional [N][H][W][K] tensor added to the output in the epilogue (residual-gradient sum), or null
 };
 
 struct BnStats {
@@ -317,6 +318,13 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         const uint32_t acc_phase = (it >> 1) & 1;
         const bool valid = slot_ok && (h0 + ti) < g.H;
         const uint32_t taddr = tmem_base + acc * C::kAccCols + ((uint32_t)(quarter * 32) << 16);
+        uint4 ad[4];
+        const bool has_add = g.addend != nullptr && valid;
+        if (has_add) {            // issued before the accumulator wait: the loads fly while the MMAs finish
+          const T* arow = reinterpret_cast<const T*>(g.addend) + (((size_t)n * g.H + h0 + ti) * g.W + (tj - 1)) * g.K + c0;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) ad[j] = ldg_stream(arow + 8 * j);
+        }
         mbar_wait(&tfull[acc], acc_phase);
         tc_fence_after();
         uint32_t v[32];
@@ -336,6 +344,15 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&tempty[acc]);                // accumulators are in registers: hand the buffer back
+        if (has_add) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            float a[8];
+            unpack8<T>(ad[j], a);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[8 * j + e] = __float_as_uint(__uint_as_float(v[8 * j + e]) + a[e]);
+          }
+        }
         uint4 o[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -433,6 +450,19 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&tempty[acc]);
+        }
+        if (valid && g.addend != nullptr) {
+          const T* arow = reinterpret_cast<const T*>(g.addend) + (orow - out) + c0;
+          uint4 ad[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) ad[j] = ldg_stream(arow + 8 * j);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            float a[8];
+            unpack8<T>(ad[j], a);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[8 * j + e] = __float_as_uint(__uint_as_float(v[8 * j + e]) + a[e]);
+          }
         }
         if (valid) {
 #pragma unroll
@@ -980,8 +1010,20 @@ int pdt_conv3x3_halo_supported(int dtype, int N, int H, int W, int C, int K) {
 int pdt_conv3x3_halo(const void* x, const void* w, void* y, int dtype, int N, int H, int W, int C, int K, void* scratch,
                      float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
                      float* save_invstd, cudaStream_t stream) {
+  return pdt_conv3x3_halo_add(x, w, y, nullptr, dtype, N, H, W, C, K, scratch, running_mean, running_var, momentum, eps,
+                              save_mean, save_invstd, stream);
+}
+
+// The same with an optional addend [N][H][W][K] summed into the output in the epilogue (y = conv + addend): the
+// data gradient of a residual block's first 3x3 convolution takes the shortcut gradient here.  Not combined
+// with the statistics epilogue (addend != NULL requires scratch == NULL).
+int pdt_conv3x3_halo_add(const void* x, const void* w, void* y, const void* addend, int dtype, int N, int H, int W, int C, int K,
+                         void* scratch, float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
+                         float* save_invstd, cudaStream_t stream) {
   if (!pdt_conv3x3_halo_supported(dtype, N, H, W, C, K)) return PDT_E_UNSUPPORTED;
-  if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(w) | reinterpret_cast<uintptr_t>(y)) & 15) return PDT_E_UNSUPPORTED;
+  if (addend != nullptr && scratch != nullptr) return PDT_E_UNSUPPORTED;
+  if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(w) | reinterpret_cast<uintptr_t>(y) |
+       reinterpret_cast<uintptr_t>(addend)) & 15) return PDT_E_UNSUPPORTED;
   if (g_enc == nullptr) {
     cudaDriverEntryPointQueryResult q;
     void* fn = nullptr;
@@ -990,6 +1032,7 @@ int pdt_conv3x3_halo(const void* x, const void* w, void* y, int dtype, int N, in
     g_enc = reinterpret_cast<EncodeTiledFn>(fn);
   }
   HaloGeom g;
+  g.addend = addend;
   g.N = N; g.H = H; g.W = W; g.C = C; g.K = K;
   g.Wp = W + 2;
   g.TR = 128 / g.Wp;
@@ -1069,6 +1112,7 @@ int pdt_conv3x3_wgrad_halo(const void* x, const void* dy, float* dw, int dtype, 
     g_enc = reinterpret_cast<EncodeTiledFn>(fn);
   }
   HaloGeom g;
+  g.addend = nullptr;
   g.N = N; g.H = H; g.W = W; g.C = C; g.K = K;
   g.Wp = W + 2;
   g.TR = 128 / g.Wp;

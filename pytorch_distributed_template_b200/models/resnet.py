@@ -14,6 +14,7 @@ import torch.nn as nn
 
 from .. import amp, ops
 from ..ops import bn as _bn_ops
+from ..ops.conv_native import GradLink, link_enabled
 from ..parallel.syncbn import fused_bn, fused_bn_relu_maxpool, fused_conv_bn, fused_conv_bn_relu_maxpool
 
 
@@ -40,10 +41,16 @@ class BasicBlock(nn.Module):
 
     def forward(self, x):
         identity = x
-        out = fused_conv_bn(self.conv1, self.bn1, x, relu=True)
+        # The gradient of x is conv1's data gradient plus the shortcut's gradient: the link lets conv1's backward
+        # kernel add the latter in its epilogue (ops.conv_native.GradLink) instead of a separate elementwise pass.
+        link = GradLink() if link_enabled(x) else None
+        out = fused_conv_bn(self.conv1, self.bn1, x, relu=True, consume=link)
+        if link is not None and not link.claimed:
+            link = None
         if self.downsample is not None:
-            identity = fused_conv_bn(self.downsample[0], self.downsample[1], x)
-        return fused_conv_bn(self.conv2, self.bn2, out, residual=identity, relu=True)
+            identity = fused_conv_bn(self.downsample[0], self.downsample[1], x, produce=link)
+            link = None
+        return fused_conv_bn(self.conv2, self.bn2, out, residual=identity, relu=True, res_link=link)
 
 
 class Bottleneck(nn.Module):
@@ -63,11 +70,15 @@ class Bottleneck(nn.Module):
 
     def forward(self, x):
         identity = x
-        out = fused_conv_bn(self.conv1, self.bn1, x, relu=True)
+        link = GradLink() if link_enabled(x) else None       # see BasicBlock.forward
+        out = fused_conv_bn(self.conv1, self.bn1, x, relu=True, consume=link)
+        if link is not None and not link.claimed:
+            link = None
         out = fused_conv_bn(self.conv2, self.bn2, out, relu=True)
         if self.downsample is not None:
-            identity = fused_conv_bn(self.downsample[0], self.downsample[1], x)
-        return fused_conv_bn(self.conv3, self.bn3, out, residual=identity, relu=True)
+            identity = fused_conv_bn(self.downsample[0], self.downsample[1], x, produce=link)
+            link = None
+        return fused_conv_bn(self.conv3, self.bn3, out, residual=identity, relu=True, res_link=link)
 
 
 class ResNet(nn.Module):

@@ -98,7 +98,11 @@ def _bump(counter):
 class _BNActNative(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, res, weight, bias, running_mean, running_var, momentum, eps, relu, comm, pre_mean=None,
-                pre_invstd=None):
+                pre_invstd=None, res_link=None):
+        # res_link: conv_native.GradLink whose consumer (the block's first convolution, fed by the same tensor as
+        # ``res``) adds the shortcut gradient in its data-gradient epilogue; backward then deposits it there
+        # instead of returning it.
+        ctx.res_link = res_link if (res is not None and res_link is not None and res_link.claimed) else None
         with _native.guard(x.device):
             return _BNActNative._forward_impl(ctx, x, res, weight, bias, running_mean, running_var, momentum, eps, relu,
                                               comm, pre_mean, pre_invstd)
@@ -155,7 +159,9 @@ class _BNActNative(torch.autograd.Function):
         _native.check(lib.pdt_bn_bwd_apply(dy.data_ptr(), _native.ptr(y), x.data_ptr(), dx.data_ptr(), _native.ptr(dres),
                                            M, C, dt, mean.data_ptr(), invstd.data_ptr(), weight.data_ptr(), bias.data_ptr(),
                                            k.data_ptr(), int(ctx.relu), s), "pdt_bn_bwd_apply")
-        return dx, dres, dgamma, dbeta, None, None, None, None, None, None, None, None
+        if ctx.res_link is not None and dres is not None and ctx.needs_input_grad[1]:
+            ctx.res_link.grad, dres = dres, None
+        return dx, dres, dgamma, dbeta, None, None, None, None, None, None, None, None, None
 
 
 class _BNReluPoolNative(torch.autograd.Function):
@@ -262,7 +268,7 @@ class _SyncStatsTorch(torch.autograd.Function):
         return dx.to(dy.dtype), dgamma, dbeta, None, None, None, None, None
 
 
-def bn_act(x, bn, residual=None, relu=False, comm=None, group=None, stats=None):
+def bn_act(x, bn, residual=None, relu=False, comm=None, group=None, stats=None, res_link=None):
     """``relu?(bn(x) + residual?)`` for an ``nn.BatchNorm2d``-like module ``bn``.
 
     ``comm`` (native CommDesc) or ``group`` (process group) turn it into SyncBatchNorm.
@@ -274,7 +280,7 @@ def bn_act(x, bn, residual=None, relu=False, comm=None, group=None, stats=None):
         if bn.track_running_stats and bn.num_batches_tracked is not None:
             _bump(bn.num_batches_tracked)
         return _BNActNative.apply(x, residual, bn.weight, bn.bias, None, None, 0.1, bn.eps, relu, None,
-                                  stats[0], stats[1])
+                                  stats[0], stats[1], res_link)
     training = bn.training or bn.running_mean is None
     sync = training and (comm is not None or group is not None)
     momentum = _ema_factor(bn) if training else 0.0
@@ -283,7 +289,7 @@ def bn_act(x, bn, residual=None, relu=False, comm=None, group=None, stats=None):
     # (a SyncBatchNorm in train() under no_grad still synchronises its statistics: the native kernels need no autograd)
     if training and _native_ok(x, C) and (torch.is_grad_enabled() or (sync and comm is not None)) and (not sync or comm is not None):
         return _BNActNative.apply(x, residual, bn.weight, bn.bias, bn.running_mean, bn.running_var, momentum, bn.eps,
-                                  relu, comm if sync else None)
+                                  relu, comm if sync else None, None, None, res_link)
     if not training and _native_ok(x, C) and x.dtype != torch.float32 and not torch.is_grad_enabled():
         xc = x.contiguous(memory_format=torch.channels_last)
         rc = residual.contiguous(memory_format=torch.channels_last) if residual is not None else None
@@ -344,7 +350,7 @@ def conv_bn_relu_maxpool(x, conv, bn, kernel_size=3, stride=2, padding=1):
     return bn_relu_maxpool(conv2d(x, conv), bn, kernel_size, stride, padding)
 
 
-def conv_bn_act(x, conv, bn, residual=None, relu=False, comm=None, group=None):
+def conv_bn_act(x, conv, bn, residual=None, relu=False, comm=None, group=None, consume=None, produce=None, res_link=None):
     """``relu?(bn(conv(x)) + residual?)``.  On the native training path the convolution's epilogue
     produces the BatchNorm statistics (no separate pass over the activation); SyncBatchNorm keeps its
     own statistics kernel because the cross-rank exchange lives there."""
@@ -354,11 +360,11 @@ def conv_bn_act(x, conv, bn, residual=None, relu=False, comm=None, group=None):
             and _native.available() and bn.track_running_stats and bn.affine)
     if fuse:
         momentum = _ema_factor(bn)
-        out = conv2d(x, conv, bnpack=(bn.running_mean, bn.running_var, momentum, bn.eps))
+        out = conv2d(x, conv, bnpack=(bn.running_mean, bn.running_var, momentum, bn.eps), consume=consume, produce=produce)
         if isinstance(out, tuple):
             y, mean, invstd = out
             if _native_ok(y, y.shape[1]):
-                return bn_act(y, bn, residual, relu, stats=(mean, invstd))
+                return bn_act(y, bn, residual, relu, stats=(mean, invstd), res_link=res_link)
             raise RuntimeError("conv epilogue produced statistics for a shape the BN kernels do not serve")
-        return bn_act(out, bn, residual, relu, comm=comm, group=group)
-    return bn_act(conv2d(x, conv), bn, residual, relu, comm=comm, group=group)
+        return bn_act(out, bn, residual, relu, comm=comm, group=group, res_link=res_link)
+    return bn_act(conv2d(x, conv, consume=consume, produce=produce), bn, residual, relu, comm=comm, group=group, res_link=res_link)

@@ -69,9 +69,11 @@ class _ConvLPTorch(torch.autograd.Function):
         return dx, dw.float(), None, None, None
 
 
-def conv2d(x, conv, bnpack=None):
+def conv2d(x, conv, bnpack=None, consume=None, produce=None):
     """``conv(x)``.  With ``bnpack`` (see conv_native.conv_native) the native kernel may return
-    ``(y, mean, invstd)`` — batch statistics of y for the BatchNorm that follows."""
+    ``(y, mean, invstd)`` — batch statistics of y for the BatchNorm that follows.  ``consume`` / ``produce``:
+    roles of this convolution in a residual block's gradient link (conv_native.GradLink); only the native
+    kernels take them, every other path ignores them (the link then stays unclaimed / unfilled)."""
     lp = amp.active_dtype()
     plain = (not x.is_cuda or conv.groups != 1 or conv.dilation != (1, 1) or conv.bias is not None
              or conv.padding_mode != "zeros" or isinstance(conv.padding, str))
@@ -95,7 +97,7 @@ def conv2d(x, conv, bnpack=None):
             return _stem_native[1](x, conv, w, bnpack)
         if _tf32_on() and x.dim() == 4:
             xc = x if x.is_contiguous(memory_format=torch.channels_last) else x.contiguous(memory_format=torch.channels_last)
-            y = _conv_native(xc, conv.weight, w, conv.stride, conv.padding, bnpack)
+            y = _conv_native(xc, conv.weight, w, conv.stride, conv.padding, bnpack, consume, produce)
             if y is not None:
                 return y
     if lp is None or plain:
@@ -111,7 +113,7 @@ def conv2d(x, conv, bnpack=None):
     if x.dtype != lp or not x.is_contiguous(memory_format=torch.channels_last):
         x = x.to(dtype=lp, memory_format=torch.channels_last)
     if _conv_native is not None and _native.available():
-        y = _conv_native(x, conv.weight, w_lp, conv.stride, conv.padding, bnpack)
+        y = _conv_native(x, conv.weight, w_lp, conv.stride, conv.padding, bnpack, consume, produce)
         if y is not None:
             return y
     note_fallback("conv2d(amp)", tuple(conv.weight.shape), conv.stride, conv.padding, str(x.dtype))

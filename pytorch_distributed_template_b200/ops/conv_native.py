@@ -23,7 +23,9 @@ _native.register("pdt_conv_fprop", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _
 _native.register("pdt_conv3x3_wgrad_halo_supported", [_i, _i, _i, _i, _i, _i])
 _native.register("pdt_conv_wgrad", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp])
 _native.register("pdt_conv_fprop_ex", [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _ll, _ll, _ll, _i, _i, _i, _i,
-                                       _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp])
+                                       _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp])
+_native.register("pdt_conv_fprop_add", [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp])
+_native.register("pdt_conv3x3_halo_add", [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _native._f, _native._f, _vp, _vp, _vp])
 _native.register("pdt_conv_wgrad_ex", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _ll, _ll, _ll, _i, _i, _i, _i,
                                        _i, _i, _i, _i, _i, _i, _i, _vp])
 _native.register("pdt_stem_s2d", [_vp, _vp, _i, _i, _i, _i, _i, _vp])
@@ -50,12 +52,12 @@ def _halo_ok(x, w_lp, stride, pad):
     return bool(_native.lib().pdt_conv3x3_halo_supported(_native.dtype_code(x.dtype), N, H, W, C, K))
 
 
-def _halo(x, w_lp, y, scratch=None, rm=None, rv=None, momentum=0.1, eps=1e-5, mean=None, invstd=None):
+def _halo(x, w_lp, y, scratch=None, rm=None, rv=None, momentum=0.1, eps=1e-5, mean=None, invstd=None, addend=None):
     N, C, H, W = x.shape
     K = w_lp.shape[0]
-    _native.check(_native.lib().pdt_conv3x3_halo(
-        x.data_ptr(), w_lp.data_ptr(), y.data_ptr(), _native.dtype_code(x.dtype), N, H, W, C, K, _native.ptr(scratch),
-        _native.ptr(rm), _native.ptr(rv), momentum, eps, _native.ptr(mean), _native.ptr(invstd),
+    _native.check(_native.lib().pdt_conv3x3_halo_add(
+        x.data_ptr(), w_lp.data_ptr(), y.data_ptr(), _native.ptr(addend), _native.dtype_code(x.dtype), N, H, W, C, K,
+        _native.ptr(scratch), _native.ptr(rm), _native.ptr(rv), momentum, eps, _native.ptr(mean), _native.ptr(invstd),
         _native.stream_ptr(x.device)), "pdt_conv3x3_halo")
     return y
 
@@ -81,14 +83,20 @@ def supported(x, weight, stride, padding):
 
 
 # ------------------------------------------------------------------------------------------ kernels
-def fprop(x, w_lp, stride, pad):
-    """x: [N,C,H,W] channels_last, w_lp: [K,C,R,S] channels_last -> y [N,K,P,Q] channels_last."""
+def fprop(x, w_lp, stride, pad, addend=None):
+    """x: [N,C,H,W] channels_last, w_lp: [K,C,R,S] channels_last -> y [N,K,P,Q] channels_last.
+    ``addend`` (shaped and laid out like y) is summed into the result in the kernel's epilogue."""
     N, C, H, W = x.shape
     K, _, R, S = w_lp.shape
     P, Q = (H + 2 * pad - R) // stride + 1, (W + 2 * pad - S) // stride + 1
     y = torch.empty((N, K, P, Q), dtype=x.dtype, device=x.device, memory_format=CL)
     if _halo_ok(x, w_lp, stride, pad):
-        return _halo(x, w_lp, y)
+        return _halo(x, w_lp, y, addend=addend)
+    if addend is not None:
+        _native.check(_native.lib().pdt_conv_fprop_add(x.data_ptr(), w_lp.data_ptr(), y.data_ptr(), addend.data_ptr(),
+                                                       _native.dtype_code(x.dtype), N, H, W, C, K, R, S, stride, pad,
+                                                       _native.stream_ptr(x.device)), "pdt_conv_fprop_add")
+        return y
     _native.check(_native.lib().pdt_conv_fprop(x.data_ptr(), w_lp.data_ptr(), y.data_ptr(), _native.dtype_code(x.dtype),
                                                N, H, W, C, K, R, S, stride, pad, _native.stream_ptr(x.device)),
                   "pdt_conv_fprop")
@@ -115,10 +123,10 @@ def fprop_bnstats(x, w_lp, stride, pad, running_mean, running_var, momentum, eps
 
 
 def fprop_ex(x_ptr, w, y, bias, dtype, N, H, W, C, Cx, sw, sh, sn, K, R, S, stride, pads, P, Q, OH, OW, os_, oa, ob, device,
-             dil_w=1):
+             dil_w=1, addend=None):
     _native.check(_native.lib().pdt_conv_fprop_ex(
         x_ptr, w.data_ptr(), y.data_ptr(), _native.ptr(bias), _native.dtype_code(dtype), N, H, W, C, Cx, sw, sh, sn,
-        K, R, S, stride, pads[0], pads[1], pads[2], pads[3], P, Q, OH, OW, os_, oa, ob, dil_w,
+        K, R, S, stride, pads[0], pads[1], pads[2], pads[3], P, Q, OH, OW, os_, oa, ob, dil_w, _native.ptr(addend),
         _native.stream_ptr(device)), "pdt_conv_fprop_ex")
     return y
 
@@ -278,8 +286,9 @@ def dgrad_weight(w_lp, rs, ss, stable=None):
     return out
 
 
-def dgrad_stride2(dy, w_lp, x_shape, pad, stable_w=None):
-    """dx for a stride-2 convolution: one fprop launch per parity class of the input grid."""
+def dgrad_stride2(dy, w_lp, x_shape, pad, stable_w=None, addend=None):
+    """dx for a stride-2 convolution: one fprop launch per parity class of the input grid.  ``addend`` (like dx)
+    is summed in by the launches' epilogues when the four classes cover every pixel, else by one add afterwards."""
     N, C, H, W = x_shape
     K, _, R, S = w_lp.shape
     _, _, P, Q = dy.shape
@@ -309,16 +318,51 @@ def dgrad_stride2(dy, w_lp, x_shape, pad, stable_w=None):
         if pads[2] < 0 or pads[3] < 0:
             return None
         fprop_ex(dy.data_ptr(), w_sub, dx, None, dy.dtype, N, P, Q, K, K, sw, sh, sn, C, Th, Tw, 1, pads, Hs, Ws,
-                 H, W, 2, a, b, dy.device)
+                 H, W, 2, a, b, dy.device, addend=addend if full else None)
+    if addend is not None and not full:
+        dx += addend
     return dx
 
 
 # ------------------------------------------------------------------------------------------ autograd
+class GradLink:
+    """Hands the shortcut gradient of a residual block to the data-gradient kernel of the block's first convolution.
+
+    In ``out = relu(bn2(conv2(relu(bn1(conv1(x))))) + shortcut(x))`` the gradient of x is the sum of conv1's data
+    gradient and the shortcut's gradient; autograd would add the two with an elementwise kernel (three passes over
+    the block's largest tensor, eight times per ResNet-18 backward).  Instead the PRODUCER of the shortcut gradient
+    (the block's last BatchNorm when the shortcut is the identity, the projection convolution otherwise) deposits
+    its result here and reports "no gradient" for x, and the CONSUMER (conv1's backward) passes the deposit to its
+    kernel as an epilogue addend.  Ordering: with an identity shortcut the producer precedes the consumer by data
+    dependency; a projection convolution additionally takes the consumer's ``token`` output as an input, which
+    makes the autograd engine run it first.
+
+    Measured on B200 (ResNet-18, fp16, 1200 images): the eight ATen adds cost 0.92 ms, but the epilogue addend —
+    each lane pulling its own 64-byte row pieces next to the accumulator read-out — slows the data-gradient kernels
+    by 2.2 ms (k_conv3x3_halo<64> +0.70, k_conv_igemm<64> parity launches +0.65, <128> +0.34, <256> +0.31,
+    halo<128> +0.14): step 25.1 -> 25.9 ms.  The link is therefore OFF unless PDT_RESADD_FUSION=1; making it pay
+    needs the addend tile staged through shared memory by TMA like the output tile is."""
+    __slots__ = ("grad", "claimed", "token")
+
+    def __init__(self):
+        self.grad, self.claimed, self.token = None, False, None
+
+
+def link_enabled(x):
+    return (x.is_cuda and x.requires_grad and torch.is_grad_enabled() and enabled()
+            and os.environ.get("PDT_RESADD_FUSION", "0") == "1")
+
+
 class _ConvNative(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, w_lp, stride, padding, bnpack=None):
+    def forward(ctx, x, weight, w_lp, stride, padding, bnpack=None, consume=None, produce=None, token=None):
         with _native.guard(x.device):
-            return _ConvNative._forward_impl(ctx, x, weight, w_lp, stride, padding, bnpack)
+            outs = _ConvNative._forward_impl(ctx, x, weight, w_lp, stride, padding, bnpack)
+        ctx.consume, ctx.produce = consume, produce
+        if consume is None:
+            return outs
+        tok = x.new_empty(0)           # differentiable dummy output: a producer that takes it runs before this node
+        return (outs + (tok,)) if isinstance(outs, tuple) else (outs, tok)
 
     @staticmethod
     def _forward_impl(ctx, x, weight, w_lp, stride, padding, bnpack=None):
@@ -340,7 +384,7 @@ class _ConvNative(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dy, *unused_stat_grads):
         with _native.guard(dy.device):
-            return _ConvNative._backward_impl(ctx, dy)
+            return _ConvNative._backward_impl(ctx, dy) + (None, None, None)
 
     @staticmethod
     def _backward_impl(ctx, dy):
@@ -350,13 +394,23 @@ class _ConvNative(torch.autograd.Function):
         K, C, R, S = w_lp.shape
         need_dx = ctx.needs_input_grad[0]
         dx = None
+        add = None
+        if ctx.consume is not None:        # the shortcut gradient deposited by this block's producer (GradLink)
+            add, ctx.consume.grad = ctx.consume.grad, None
+            if add is not None and (not need_dx or add.shape != x.shape or add.dtype != dy.dtype):
+                raise RuntimeError("GradLink: deposited shortcut gradient does not match the consumer's input")
+            if add is not None and not add.is_contiguous(memory_format=CL):
+                add = add.contiguous(memory_format=CL)
         if need_dx and K % 8 == 0 and C % 8 == 0:
             if stride[0] == 1 and R - 1 - padding[0] >= 0:
                 # dx = conv(dy, flip(w)^T, pad' = R-1-pad): the same kernel with the roles of C and K swapped
                 w_t = dgrad_weight(w_lp, list(range(R - 1, -1, -1)), list(range(S - 1, -1, -1)), ctx.stable_w)
-                dx = fprop(dy, w_t, 1, R - 1 - padding[0])
+                dx = fprop(dy, w_t, 1, R - 1 - padding[0], addend=add)
+                add = None
             elif stride[0] == 2:
-                dx = dgrad_stride2(dy, w_lp, x.shape, padding[0], ctx.stable_w)
+                dx = dgrad_stride2(dy, w_lp, x.shape, padding[0], ctx.stable_w, addend=add)
+                if dx is not None:
+                    add = None
         native_dx = dx is not None
         native_dw = wgrad_supported(C, K, x.dtype)
         dw = wgrad(x, dy, w_lp.shape, stride[0], padding[0], out=direct_grad(ctx.weight)) if native_dw else None
@@ -368,22 +422,37 @@ class _ConvNative(torch.autograd.Function):
                 dx = dx2
             if not native_dw:
                 dw = dw2.float()
+        if add is not None:                 # a data-gradient path without the epilogue addend: add here
+            dx = dx + add
+        if ctx.produce is not None and dx is not None:
+            ctx.produce.grad, dx = dx, None     # the consumer (same input x) returns the sum
         return dx, dw, None, None, None, None
 
 
-def conv_native(x, weight, w_lp, stride, padding, bnpack=None):
+def conv_native(x, weight, w_lp, stride, padding, bnpack=None, consume=None, produce=None):
     """bnpack = (running_mean, running_var, momentum, eps): also return the batch statistics of the
-    output, computed in the convolution's epilogue -> (y, mean, invstd)."""
+    output, computed in the convolution's epilogue -> (y, mean, invstd).
+    consume / produce: ``GradLink`` roles of this convolution in a residual block (see GradLink)."""
     if not supported(x, weight, stride, padding):
         return None
     if not w_lp.is_contiguous(memory_format=CL):
         w_lp = w_lp.contiguous(memory_format=CL)
     if bnpack is not None and (weight.shape[0] > 512 or os.environ.get("PDT_BNSTATS_FUSION", "1") != "1"):
         bnpack = None
-    out = _ConvNative.apply(x, weight, w_lp, tuple(stride), tuple(padding), bnpack)
-    if bnpack is None:
-        return out
-    return out      # (y, mean, invstd)
+    token = None
+    if produce is not None:
+        token = produce.token if (produce.claimed and produce.token is not None and x.requires_grad) else None
+        if token is None:
+            produce = None               # no consumer behind this link: behave like an ordinary convolution
+    if consume is not None and not x.requires_grad:
+        consume = None
+    out = _ConvNative.apply(x, weight, w_lp, tuple(stride), tuple(padding), bnpack, consume, produce, token)
+    if consume is not None:
+        consume.claimed, consume.token = True, out[-1]
+        out = out[:-1]
+        if len(out) == 1:
+            out = out[0]
+    return out      # y or (y, mean, invstd)
 
 
 # ------------------------------------------------------------------------------------------ stem (7x7/2, C_in = 3)

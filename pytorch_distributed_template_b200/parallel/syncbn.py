@@ -51,12 +51,12 @@ class SyncBatchNorm(nn.BatchNorm2d):
         return out
 
 
-def fused_bn(bn, x, residual=None, relu=False):
+def fused_bn(bn, x, residual=None, relu=False, res_link=None):
     """Dispatch one BatchNorm-like module through the fused op (SyncBN aware)."""
     if isinstance(bn, SyncBatchNorm) and bn.training:
         fabric = bn._pdt_fabric
         if fabric is not None and fabric.native and fabric.world > 1 and x.is_cuda:
-            return ops.bn_act(x, bn, residual, relu, comm=fabric.comm)
+            return ops.bn_act(x, bn, residual, relu, comm=fabric.comm, res_link=res_link)
         group = bn.process_group if bn.process_group is not None else (dist.group.WORLD if dist.is_initialized() else None)
         if group is not None and dist.get_world_size(group) > 1:
             return ops.bn_act(x, bn, residual, relu, group=group)
@@ -66,7 +66,7 @@ def fused_bn(bn, x, residual=None, relu=False):
         if residual is not None:
             y = y + residual
         return torch.relu(y) if relu else y
-    return ops.bn_act(x, bn, residual, relu)
+    return ops.bn_act(x, bn, residual, relu, res_link=res_link)
 
 
 def fused_bn_relu_maxpool(bn, x, kernel_size=3, stride=2, padding=1):
@@ -89,9 +89,10 @@ def fused_conv_bn_relu_maxpool(conv, bn, x, kernel_size=3, stride=2, padding=1):
     return ops.conv_bn_relu_maxpool(x, conv, bn, kernel_size, stride, padding)
 
 
-def fused_conv_bn(conv, bn, x, residual=None, relu=False):
+def fused_conv_bn(conv, bn, x, residual=None, relu=False, consume=None, produce=None, res_link=None):
     """``relu?(bn(conv(x)) + residual?)`` (SyncBN aware): plain BatchNorm gets its statistics from the
-    convolution's epilogue, SyncBatchNorm from its own exchanging statistics kernel."""
+    convolution's epilogue, SyncBatchNorm from its own exchanging statistics kernel.
+    consume / produce / res_link: the block's shortcut-gradient link (ops.conv_native.GradLink)."""
     if isinstance(bn, SyncBatchNorm) and bn.training:
-        return fused_bn(bn, ops.conv2d(x, conv), residual, relu)
-    return ops.conv_bn_act(x, conv, bn, residual, relu)
+        return fused_bn(bn, ops.conv2d(x, conv, consume=consume, produce=produce), residual, relu, res_link=res_link)
+    return ops.conv_bn_act(x, conv, bn, residual, relu, consume=consume, produce=produce, res_link=res_link)

@@ -303,3 +303,85 @@ def test_stem_uint8_input_fused_normalisation(native_lib, dtype):
     assert (g8 - gf).abs().max().item() <= tol * max(1e-3, gf.abs().max().item())
     oracle = F.conv2d(ref, conv.weight.detach(), None, 2, 3)
     assert (y8.float() - oracle).abs().max().item() <= 2 * tol * max(1.0, oracle.abs().max().item())
+
+
+def _dev():
+    return torch.device("cuda", 0)
+
+
+def _nhwc(*shape, dtype=torch.bfloat16):
+    return torch.randn(*shape, device=_dev()).to(dtype).contiguous(memory_format=torch.channels_last)
+
+
+TOL = {torch.bfloat16: 2e-2, torch.float16: 4e-3}
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("N,C,H,K,R,pad", [(6, 64, 56, 64, 3, 1),      # patch-reuse kernel, TMA-store epilogue
+                                           (5, 128, 28, 128, 3, 1),    # patch-reuse kernel, direct-store epilogue
+                                           (44, 128, 28, 128, 3, 1),   # ... with CTA pairs
+                                           (7, 256, 14, 256, 3, 1),    # implicit-GEMM kernel
+                                           (9, 512, 7, 512, 3, 1), (4, 256, 14, 64, 1, 0)])
+def test_conv_epilogue_addend(native_lib, dtype, N, C, H, K, R, pad):
+    """y = conv(x, w) + addend in the kernels' epilogues (the residual-gradient sum of a block's backward) vs
+    F.conv2d + add in fp32."""
+    from pytorch_distributed_template_b200.ops import conv_native
+    torch.manual_seed(3)
+    x = _nhwc(N, C, H, H, dtype=dtype)
+    w = (torch.randn(K, C, R, R, device=_dev()) / (C * R * R) ** 0.5).to(dtype).contiguous(memory_format=torch.channels_last)
+    add = _nhwc(N, K, H, H, dtype=dtype)
+    y = conv_native.fprop(x, w, 1, pad, addend=add)
+    y0 = conv_native.fprop(x, w, 1, pad)
+    ref = F.conv2d(x.float(), w.float(), padding=pad) + add.float()
+    tol = TOL[dtype]
+    assert (y.float() - ref).abs().max().item() <= tol * max(1.0, ref.abs().max().item())
+    # and it is the plain result plus the addend up to one rounding of the sum
+    assert (y.float() - (y0.float() + add.float())).abs().max().item() <= tol * max(1.0, ref.abs().max().item())
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+def test_strided_dgrad_with_addend(native_lib, dtype):
+    from pytorch_distributed_template_b200.ops import conv_native
+    torch.manual_seed(5)
+    N, C, H, K = 6, 64, 56, 128
+    row = 32 if dtype == torch.float32 else 64
+    assert C % row == 0
+    w = (torch.randn(K, C, 3, 3, device=_dev()) / (C * 9) ** 0.5).to(dtype).contiguous(memory_format=torch.channels_last)
+    dy = _nhwc(N, K, H // 2, H // 2, dtype=dtype)
+    add = _nhwc(N, C, H, H, dtype=dtype)
+    dx = conv_native.dgrad_stride2(dy, w, (N, C, H, H), 1, None, addend=add)
+    assert dx is not None
+    ref = torch.ops.aten.convolution_backward(dy.float(), torch.empty(N, C, H, H, device=_dev()), w.float(), None, (2, 2), (1, 1),
+                                              (1, 1), False, (0, 0), 1, (True, False, False))[0] + add.float()
+    tol = TOL[dtype] if dtype != torch.float32 else TF32_TOL
+    assert (dx.float() - ref).abs().max().item() <= tol * max(1.0, ref.abs().max().item())
+
+
+def test_residual_gradient_link_matches_unfused_backward(native_lib, monkeypatch):
+    """Whole ResNet-18 backward with the shortcut gradients added in the data-gradient epilogues (GradLink) against
+    the same network with autograd's separate adds: same gradients up to one 16-bit rounding per block, and no
+    elementwise add kernel left for the eight blocks."""
+    from pytorch_distributed_template_b200 import amp
+    from pytorch_distributed_template_b200.models import create_model
+    torch.manual_seed(21)
+    dev = _dev()
+    net = create_model("resnet18", num_classes=32).to(dev)
+    net.train()
+    x = torch.randn(32, 3, 96, 96, device=dev)
+    y = torch.randint(0, 32, (32,), device=dev)
+    grads = {}
+    for mode in ("1", "0"):
+        monkeypatch.setenv("PDT_RESADD_FUSION", mode)
+        net.zero_grad()
+        torch.manual_seed(0)
+        for m in net.modules():
+            if isinstance(m, torch.nn.BatchNorm2d):
+                m.reset_running_stats()
+        with amp.autocast(True, torch.float16):
+            loss = F.cross_entropy(net(x).float(), y)
+        loss.backward()
+        torch.cuda.synchronize()
+        grads[mode] = torch.cat([p.grad.reshape(-1).clone() for p in net.parameters()])
+    rel = ((grads["1"] - grads["0"]).norm() / grads["0"].norm()).item()
+    assert rel < 2e-2, rel
+    assert torch.isfinite(grads["1"]).all()
