@@ -97,9 +97,11 @@ class StepRunner:
         self.native = cuda and _native.available()
         if graph is None:
             graph = os.environ.get("PDT_GRAPH", "1") == "1"
-        # DataParallel drives several devices from one process: its step stays eager (one capture per device
-        # would be needed); everything else is captured.
-        self.graph_enabled = bool(graph) and self.native and not self.is_dp
+        # DataParallel drives several devices from one process: its step is captured as per-device pieces
+        # (parallel.dp.GraphStep) when no loss scaling is involved; with one device it is the wrapped module's step.
+        dp_ok = (not self.is_dp) or (os.environ.get("PDT_DP_GRAPH", "1") == "1" and len(getattr(model, "device_ids", [])) > 1
+                                     and (scaler is None or not scaler.is_enabled()))
+        self.graph_enabled = bool(graph) and self.native and dp_ok
         self.eager_left = int(os.environ.get("PDT_GRAPH_WARMUP", "3")) if eager_steps is None else int(eager_steps)
         self.stream = work_stream(self.device) if cuda else None
         self.nbuf = nbuf
@@ -185,7 +187,39 @@ class StepRunner:
                 self.optimizer.step()
         return self.result
 
+    def _capture_dp(self, slot):
+        """DataParallel: 3 W + 1 graphs (forward / loss / backward / optimizer pieces per device)."""
+        img, tgt = self._static[slot]
+
+        def loss_fn(logits, target):
+            loss = self.criterion(logits, target)
+            pair = getattr(self.criterion, "last_pair", None)
+            if pair is None:
+                with torch.no_grad():
+                    pair = torch.stack([loss.detach().float(), (logits.argmax(1) == target).float().mean()])
+            return loss, pair
+
+        try:
+            for d in self.model.devices:
+                torch.cuda.synchronize(d)
+            g = self.model.graph_step(img, tgt, loss_fn, self.update_metrics, self.amp_dtype if self.use_amp else None)
+        except Exception as e:
+            self.capture_error = repr(e)
+            self.graph_enabled = False
+            for d in self.model.devices:
+                try:
+                    torch.cuda.synchronize(d)
+                except Exception:
+                    pass
+            print("[pdt] CUDA-graph capture of the DataParallel step failed, continuing eagerly: {!r}".format(e), file=sys.stderr)
+            return None
+        self.launches_per_step = g.launches
+        self._graphs[slot] = g
+        return g
+
     def _capture(self, slot):
+        if self.is_dp:
+            return self._capture_dp(slot)
         img, tgt = self._static[slot]
         g = torch.cuda.CUDAGraph()
         n0 = _native.launch_count
@@ -229,7 +263,10 @@ class StepRunner:
                 self._body(img, tgt)
             else:
                 with nvtx_range("step(graph)"):
-                    g.replay()
+                    if self.is_dp:
+                        g.replay(self.optimizer)
+                    else:
+                        g.replay()
                 self._weights_changed()      # the replayed optimizer kernels rewrote the weights behind Python's back
         self.consumed[slot].record(torch.cuda.current_stream(self.device))
         return self.result

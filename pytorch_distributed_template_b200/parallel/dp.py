@@ -114,9 +114,10 @@ class _Gather(torch.autograd.Function):
 class _Worker(threading.Thread):
     """One persistent launch thread per device (the reference spawns W threads per forward)."""
 
-    def __init__(self, device):
+    def __init__(self, device, stream=None):
         super().__init__(daemon=True)
         self.device = device
+        self.stream = stream
         self.job = None
         self.result = None
         self.cv = threading.Condition()
@@ -124,6 +125,8 @@ class _Worker(threading.Thread):
 
     def run(self):
         torch.cuda.set_device(self.device)
+        if self.stream is not None:      # the device's one work stream (see DataParallel._build)
+            torch.cuda.set_stream(self.stream)
         while True:
             with self.cv:
                 while self.job is None:
@@ -151,6 +154,153 @@ class _Worker(threading.Thread):
         if not ok:
             raise val
         return val
+
+
+class GraphStep:
+    """One DataParallel training step as 3 W + 1 CUDA graphs replayed from ONE thread.
+
+    The reference drives W replicas with W Python threads per forward and autograd's device threads per
+    backward, all serialised by the GIL (torch/nn/parallel/parallel_apply.py:123-136); at 150 images per GPU
+    the launches, not the GPUs, set the pace.  Here the step is cut where data crosses devices and each piece
+    is captured once on its device's stream:
+
+      F[d]  (device d)  pull rank 0's BN buffers and slice d of the input batch over NVLink, replica forward
+      L     (device 0)  pull every replica's logits, loss + top-1 + meters, gradient of the loss w.r.t. the logits
+      B[d]  (device d)  pull slice d of that gradient, clear the gradient arena, replica backward
+      S[d]  (device d)  sum shard d of all W gradient arenas, momentum SGD on it, push the new weights to all
+
+    Between the pieces only events order the devices (F[*] -> L -> B[*] -> S[*] -> next F[*]); a replay is
+    3 W + 1 graph launches and the same number of event records from the calling thread, no worker threads,
+    no host synchronisation.  ``images`` / ``target`` are static device-0 tensors the caller refills."""
+
+    def __init__(self, dp, images, target, loss_fn, metrics_fn, amp_dtype=None):
+        from .. import amp
+        self.dp, self.images, self.target = dp, images, target
+        W = len(dp.devices)
+        devs, streams = dp.devices, dp._streams
+        n = images.shape[0]
+        bounds = [0]
+        for c in images.chunk(W, 0):
+            bounds.append(bounds[-1] + c.shape[0])
+        self.bounds = bounds
+        self.gF, self.gB, self.gS = [None] * W, [None] * W, [None] * W
+        self.evF = [torch.cuda.Event() for _ in range(W)]
+        self.evB = [torch.cuda.Event() for _ in range(W)]
+        self.evS = [torch.cuda.Event() for _ in range(W)]
+        self.evL = torch.cuda.Event()
+        self.evIn = torch.cuda.Event()
+        outs = [None] * W
+        sig = tuple(m.training for m in dp.module.modules())
+        for rep in dp.replicas[1:]:
+            for m, flag in zip(rep.modules(), sig):
+                m.training = flag
+        dp._train_sig = sig
+        n0 = _native.launch_count
+        # ---- F[d]
+        for d, dev in enumerate(devs):
+            with torch.cuda.device(dev):
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=streams[d]):
+                    if d > 0 and dp.buffer_arenas[0].used:
+                        _peer_copy(dp.buffer_arenas[0].flat, dp.buffer_arenas[d].flat)
+                    xs = images[bounds[d]:bounds[d + 1]]
+                    if d > 0:
+                        xd = torch.empty(xs.shape, dtype=xs.dtype, device=dev)
+                        _peer_copy(xs, xd)
+                    else:
+                        xd = xs
+                    with torch.enable_grad(), amp.autocast(enabled=amp_dtype is not None, dtype=amp_dtype):
+                        outs[d] = dp.replicas[d](xd)
+                self.gF[d] = g
+        # ---- L
+        dev0 = devs[0]
+        with torch.cuda.device(dev0):
+            full = torch.empty((n,) + tuple(outs[0].shape[1:]), dtype=outs[0].dtype, device=dev0)
+            self.gL = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.gL, stream=streams[0], pool=self.gF[0].pool()):
+                for d in range(W):
+                    _peer_copy(outs[d].detach(), full[bounds[d]:bounds[d + 1]])
+                leaf = full.detach().requires_grad_(True)
+                with torch.enable_grad():
+                    loss, pair = loss_fn(leaf, target)
+                metrics_fn(pair, n)
+                (dfull,) = torch.autograd.grad(loss, leaf)
+        self.full, self.dfull = full, dfull
+        # ---- B[d]
+        for d, dev in enumerate(devs):
+            with torch.cuda.device(dev):
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=streams[d], pool=self.gF[d].pool()):
+                    piece = dfull[bounds[d]:bounds[d + 1]]
+                    if d > 0:
+                        dl = torch.empty(piece.shape, dtype=piece.dtype, device=dev)
+                        _peer_copy(piece, dl)
+                    else:
+                        dl = piece
+                    for p in dp.replicas[d].parameters():
+                        p.grad = None
+                    dp.arenas[d].zero_grads()
+                    torch.autograd.backward([outs[d]], [dl.to(outs[d].dtype)])
+                    dp.arenas[d].gather_grads(drop=False)
+                    dp.arenas[d].grads_zeroed = False
+                self.gB[d] = g
+        outs = None
+        # ---- S[d]
+        lib = _native.lib()
+        sh_dtype = _native.dtype_code(dp.shadow_dtype) if dp.shadow_dtype is not None else _native.BF16
+        for d, dev in enumerate(devs):
+            a = dp.arenas[d]
+            with torch.cuda.device(dev):
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=streams[d], pool=self.gF[d].pool()):
+                    s_ = streams[d].cuda_stream
+                    _native.check(lib.pdt_reduce_scatter_f32(dp._comms[d], dp._grads, None, 0, a.total, dp._state[d].data_ptr(), 0,
+                                                            128, s_), "pdt_reduce_scatter_f32(dp)")
+                    _native.check(lib.pdt_sgd_allgather(dp._comms[d], dp._grads, dp._params, dp._shadow, None, None, sh_dtype,
+                                                       a.momentum.data_ptr(), dp._whole, dp._hypers[d].data_ptr(),
+                                                       dp._state[d].data_ptr(), 0, 128, s_), "pdt_sgd_allgather(dp)")
+                self.gS[d] = g
+        self.launches = _native.launch_count - n0
+
+    def replay(self, opt):
+        dp = self.dp
+        devs, streams = dp.devices, dp._streams
+        W = len(devs)
+        dp.sync_hyper(opt)
+        self.evIn.record(streams[0])                      # the caller filled the input buffers on device 0's stream
+        for d in range(W):
+            s = streams[d]
+            if d > 0:
+                s.wait_event(self.evIn)
+            for e in self.evS:                            # last step's weight pushes (and gradient reads) are done
+                s.wait_event(e)
+            with torch.cuda.device(devs[d]), torch.cuda.stream(s):
+                self.gF[d].replay()
+            self.evF[d].record(s)
+        s0 = streams[0]
+        for e in self.evF[1:]:
+            s0.wait_event(e)
+        with torch.cuda.device(devs[0]), torch.cuda.stream(s0):
+            self.gL.replay()
+        self.evL.record(s0)
+        for d in range(W):
+            s = streams[d]
+            if d > 0:
+                s.wait_event(self.evL)
+            with torch.cuda.device(devs[d]), torch.cuda.stream(s):
+                self.gB[d].replay()
+            self.evB[d].record(s)
+        for d in range(W):
+            s = streams[d]
+            for e in self.evB:
+                s.wait_event(e)
+            with torch.cuda.device(devs[d]), torch.cuda.stream(s):
+                self.gS[d].replay()
+            self.evS[d].record(s)
+        for e in self.evS[1:]:                            # device 0's stream ends the step: it has seen every push
+            s0.wait_event(e)
+        for a in dp.arenas:
+            a.weights_changed()
 
 
 class DataParallel(nn.Module):
@@ -197,7 +347,14 @@ class DataParallel(nn.Module):
                 st = torch.zeros(8, dtype=torch.float32, device=dev)
                 st[0] = 1.0 / len(self.devices)      # k_reduce_scatter multiplies by 1/(W*scale): DP grads are sums
                 self._state.append(st)
-        self._workers = [None] + [_Worker(d) for d in self.devices[1:]]
+        # ONE work stream per device for everything this wrapper does there (forward in the launch threads,
+        # backward in autograd's device threads, which follow the forward's stream, the optimizer kernels, and
+        # the captured graphs): autograd remembers the stream of the first forward, and a graph capture must not
+        # have to synchronise with the legacy default stream.
+        self._streams = [torch.cuda.current_stream(dev0)] + [torch.cuda.Stream(d) for d in self.devices[1:]]
+        for st_ in self._streams[1:]:
+            torch.cuda.set_stream(st_)           # per-device current stream of THIS thread
+        self._workers = [None] + [_Worker(d, st_) for d, st_ in zip(self.devices[1:], self._streams[1:])]
         W = len(self.devices)
         self._grads = _native.make_peers([a.grad_buf.ptrs[0] for a in self.arenas])
         self._params = _native.make_peers([a.param_buf.ptrs[0] for a in self.arenas])
@@ -271,14 +428,12 @@ class DataParallel(nn.Module):
         outs = [run(self.replicas[0], xs[0])] + [w.wait() for w in self._workers[1:]]
         return _Gather.apply(self, *outs)
 
-    # ------------------------------------------------------------------ fused optimizer step
-    def fused_step(self, opt):
-        """D7 + D8 + D3 in one pair of kernels per device (see module docstring)."""
-        W = len(self.devices)
-        lib = _native.lib()
+    def sync_hyper(self, opt):
+        """lr / momentum / weight decay live in device memory the optimizer kernels read (also from replayed
+        graphs); copies happen only when the schedule changes them."""
         g = opt.param_groups[0]
         hyper = (float(g["lr"]), float(g["momentum"]), float(g["weight_decay"]), 0.0)
-        if hyper != self._hyper_host:      # device copies change only when the schedule does: no per-step H2D
+        if hyper != self._hyper_host:
             host = torch.tensor(hyper, dtype=torch.float32).pin_memory()
             for r, dev in enumerate(self.devices):
                 with torch.cuda.device(dev):
@@ -286,6 +441,19 @@ class DataParallel(nn.Module):
             for dev in self.devices:
                 torch.cuda.synchronize(dev)          # `host` may go away; happens once per LR change
             self._hyper_host = hyper
+
+    def graph_step(self, images, target, loss_fn, metrics_fn, amp_dtype=None):
+        """Capture this wrapper's training step for the static device-0 batch (images, target): see GraphStep."""
+        if not self._built:
+            raise RuntimeError("run at least one eager step before capturing (replicas are built at the first forward)")
+        return GraphStep(self, images, target, loss_fn, metrics_fn, amp_dtype)
+
+    # ------------------------------------------------------------------ fused optimizer step
+    def fused_step(self, opt):
+        """D7 + D8 + D3 in one pair of kernels per device (see module docstring)."""
+        W = len(self.devices)
+        lib = _native.lib()
+        self.sync_hyper(opt)
         # phase 1: every device moves its replica's gradients into its arena
         done = []
         for r, dev in enumerate(self.devices):

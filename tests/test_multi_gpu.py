@@ -161,3 +161,48 @@ def test_dataparallel_matches_manual_replicas(native_lib):
     ours.eval()
     with torch.no_grad():
         assert ours(torch.randn(4 * n, 3, 64, 64).cuda()).shape == (4 * n, 10)
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
+def test_dataparallel_graph_step_equals_eager(native_lib, monkeypatch):
+    """The DataParallel step replayed from per-device CUDA graphs (parallel.dp.GraphStep: forward / loss / backward /
+    optimizer pieces, ordered by events, launched from one thread) leaves exactly the parameters the eager,
+    thread-driven step leaves (deterministic weight gradients), on every replica."""
+    monkeypatch.setenv("PDT_DETERMINISTIC", "1")
+    from pytorch_distributed_template_b200 import amp, engine, optim
+    from pytorch_distributed_template_b200.models import create_model
+    from pytorch_distributed_template_b200.ops import CrossEntropyLoss
+    from pytorch_distributed_template_b200.parallel import DataParallel
+    n = min(4, _ngpu())
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(0)
+    engine.work_stream(dev)
+
+    def run(graph):
+        torch.manual_seed(5)
+        model = DataParallel(create_model("resnet18", num_classes=20), device_ids=list(range(n))).to(dev)
+        crit = CrossEntropyLoss().to(dev)
+        opt = optim.SGD(model.parameters(), 0.05, momentum=0.9, weight_decay=1e-4)
+        scaler = amp.GradScaler(enabled=False, device=dev)
+        runner = engine.StepRunner(model, crit, opt, scaler, dev, graph=graph, eager_steps=2)
+        g = torch.Generator().manual_seed(17)
+        batches = [(torch.randint(0, 256, (16 * n, 3, 64, 64), generator=g, dtype=torch.uint8).pin_memory(),
+                    torch.randint(0, 20, (16 * n,), generator=g).pin_memory()) for _ in range(6)]
+        model.train()
+        res = []
+        for img, tgt in engine.DeviceFeed(batches, runner):
+            res.append(runner.step(img, tgt).clone())
+        for d in range(n):
+            torch.cuda.synchronize(d)
+        reps = [torch.cat([p.detach().reshape(-1) for p in r.parameters()]).cpu() for r in model.replicas]
+        return reps, torch.stack(res).cpu(), runner
+
+    eager, l_eager, r_eager = run(False)
+    graph, l_graph, r_graph = run(True)
+    assert r_eager.graphs == 0 and r_graph.graphs == 2, (r_graph.graphs, r_graph.capture_error)
+    assert torch.equal(l_eager, l_graph), (l_eager, l_graph)
+    for a, b in zip(eager, graph):
+        assert torch.equal(a, b)
+    for b in graph[1:]:
+        assert torch.equal(graph[0], b)            # every replica holds the pushed weights
+    assert torch.isfinite(l_graph).all()
