@@ -41,9 +41,16 @@ def scale_bias_ctypes():
     return _c_cache
 
 
+_t_cache = {}
+
+
 def normalize_u8(x):
-    """uint8 [N,3,H,W] -> fp32, the torch formulation (CPU / non-native paths and the test oracle)."""
+    """uint8 [N,3,H,W] -> fp32, the torch formulation (CPU / non-native paths and the test oracle).
+    The constants are cached per device: creating them is a host-to-device copy, which a graph capture forbids."""
     sc, bs = scale_bias()
-    sc = torch.tensor(sc, dtype=torch.float32, device=x.device).view(1, 3, 1, 1)
-    bs = torch.tensor(bs, dtype=torch.float32, device=x.device).view(1, 3, 1, 1)
-    return x.float() * sc + bs
+    key = (x.device, sc, bs)
+    t = _t_cache.get(key)
+    if t is None:
+        t = _t_cache[key] = (torch.tensor(sc, dtype=torch.float32, device=x.device).view(1, 3, 1, 1),
+                             torch.tensor(bs, dtype=torch.float32, device=x.device).view(1, 3, 1, 1))
+    return x.float() * t[0] + t[1]

@@ -57,7 +57,7 @@ class _Scatter(torch.autograd.Function):
             if dev == x.device:
                 outs.append(c)
                 continue
-            with torch.cuda.device(dev):
+            with torch.cuda.device(dev), torch.cuda.stream(dp.stream_of(dev)):
                 torch.cuda.current_stream(dev).wait_event(ev)
                 o = torch.empty(c.shape, dtype=c.dtype, device=dev)
                 _peer_copy(c.contiguous(), o)
@@ -84,7 +84,7 @@ class _Gather(torch.autograd.Function):
             for o in outs:
                 if o.device != dev0:
                     ev = torch.cuda.Event()
-                    ev.record(torch.cuda.current_stream(o.device))
+                    ev.record(dp.stream_of(o.device))
                     s0.wait_event(ev)
                 _peer_copy(o.contiguous(), full[pos:pos + o.shape[0]])
                 pos += o.shape[0]
@@ -103,7 +103,7 @@ class _Gather(torch.autograd.Function):
             if dev == g.device:
                 outs.append(piece)
                 continue
-            with torch.cuda.device(dev):
+            with torch.cuda.device(dev), torch.cuda.stream(dp.stream_of(dev)):
                 torch.cuda.current_stream(dev).wait_event(ev)
                 o = torch.empty(piece.shape, dtype=piece.dtype, device=dev)
                 _peer_copy(piece, o)
@@ -352,8 +352,10 @@ class DataParallel(nn.Module):
         # the captured graphs): autograd remembers the stream of the first forward, and a graph capture must not
         # have to synchronise with the legacy default stream.
         self._streams = [torch.cuda.current_stream(dev0)] + [torch.cuda.Stream(d) for d in self.devices[1:]]
+        keep_dev = torch.cuda.current_device()
         for st_ in self._streams[1:]:
-            torch.cuda.set_stream(st_)           # per-device current stream of THIS thread
+            torch.cuda.set_stream(st_)           # per-device current stream of THIS thread (also switches device)
+        torch.cuda.set_device(keep_dev)
         self._workers = [None] + [_Worker(d, st_) for d, st_ in zip(self.devices[1:], self._streams[1:])]
         W = len(self.devices)
         self._grads = _native.make_peers([a.grad_buf.ptrs[0] for a in self.arenas])
@@ -392,7 +394,7 @@ class DataParallel(nn.Module):
         ev = torch.cuda.Event()
         ev.record(torch.cuda.current_stream(self.devices[0]))
         for dev, ba in zip(self.devices[1:], self.buffer_arenas[1:]):
-            with torch.cuda.device(dev):
+            with torch.cuda.device(dev), torch.cuda.stream(self.stream_of(dev)):
                 torch.cuda.current_stream(dev).wait_event(ev)
                 _peer_copy(ba0.flat, ba.flat)
 
@@ -428,6 +430,10 @@ class DataParallel(nn.Module):
         outs = [run(self.replicas[0], xs[0])] + [w.wait() for w in self._workers[1:]]
         return _Gather.apply(self, *outs)
 
+    def stream_of(self, device):
+        """The work stream of one of this wrapper's devices (see _build)."""
+        return self._streams[self.devices.index(torch.device(device))]
+
     def sync_hyper(self, opt):
         """lr / momentum / weight decay live in device memory the optimizer kernels read (also from replayed
         graphs); copies happen only when the schedule changes them."""
@@ -457,7 +463,7 @@ class DataParallel(nn.Module):
         # phase 1: every device moves its replica's gradients into its arena
         done = []
         for r, dev in enumerate(self.devices):
-            with torch.cuda.device(dev):
+            with torch.cuda.device(dev), torch.cuda.stream(self._streams[r]):
                 self.arenas[r].gather_grads(drop=(r != 0))
                 self.arenas[r].grads_zeroed = False
                 ev = torch.cuda.Event()
@@ -469,8 +475,8 @@ class DataParallel(nn.Module):
         # applies SGD to it and stores the new weights into every replica
         for r, dev in enumerate(self.devices):
             a = self.arenas[r]
-            with torch.cuda.device(dev):
-                s = torch.cuda.current_stream(dev)
+            with torch.cuda.device(dev), torch.cuda.stream(self._streams[r]):
+                s = self._streams[r]
                 for ev in done:
                     s.wait_event(ev)
                 _native.check(lib.pdt_reduce_scatter_f32(self._comms[r], self._grads, None, 0, a.total,
@@ -486,11 +492,11 @@ class DataParallel(nn.Module):
         for a in self.arenas:
             a.weights_changed()
         for r, dev in enumerate(self.devices):      # new weights were written by peers: everybody waits for everybody
-            s = torch.cuda.current_stream(dev)
+            s = self._streams[r]
             for ev in after:
                 s.wait_event(ev)
             if r > 0:      # replicas' gradients were dropped above: clear their arenas for direct writes
-                with torch.cuda.device(dev):
+                with torch.cuda.device(dev), torch.cuda.stream(s):
                     self.arenas[r].zero_grads()
 
     def zero_replica_grads(self):
