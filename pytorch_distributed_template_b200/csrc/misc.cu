@@ -191,6 +191,101 @@ __global__ void __launch_bounds__(256) k_maxpool_bwd(const T* __restrict__ dy, c
   }
 }
 
+// fp32 variants (the reference's fp32 modes, distributed.py / dataparallel.py): 4 channels per 16-byte vector.
+__global__ void __launch_bounds__(256) k_maxpool_fwd_f32(const float* __restrict__ x, float* __restrict__ y, int8_t* __restrict__ idx,
+                                                        int N, int H, int W, int C, int Ho, int Wo, int ks, int st, int pd) {
+  pdl_enter();
+  const int cg = C / 4;
+  const long total = (long)N * Ho * Wo * cg;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int c4 = (int)(i % cg);
+    long r = i / cg;
+    const int wo = (int)(r % Wo); r /= Wo;
+    const int ho = (int)(r % Ho);
+    const int n = (int)(r / Ho);
+    float best[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+    int bi[4] = {0, 0, 0, 0};
+    for (int kh = 0; kh < ks; ++kh) {
+      const int hi = ho * st - pd + kh;
+      if (hi < 0 || hi >= H) continue;
+      for (int kw = 0; kw < ks; ++kw) {
+        const int wi = wo * st - pd + kw;
+        if (wi < 0 || wi >= W) continue;
+        const float4 v = *reinterpret_cast<const float4*>(x + (((long)n * H + hi) * W + wi) * C + c4 * 4);
+        const float f[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (f[j] > best[j]) { best[j] = f[j]; bi[j] = kh * ks + kw; }
+      }
+    }
+    const long o = (((long)n * Ho + ho) * Wo + wo) * C + c4 * 4;
+    *reinterpret_cast<float4*>(y + o) = make_float4(best[0], best[1], best[2], best[3]);
+    *reinterpret_cast<uint32_t*>(idx + o) = (bi[0] & 0xff) | ((bi[1] & 0xff) << 8) | ((bi[2] & 0xff) << 16) | ((bi[3] & 0xff) << 24);
+  }
+}
+
+__global__ void __launch_bounds__(256) k_maxpool_bwd_f32(const float* __restrict__ dy, const int8_t* __restrict__ idx, float* __restrict__ dx,
+                                                        int N, int H, int W, int C, int Ho, int Wo, int ks, int st, int pd) {
+  pdl_enter();
+  const int cg = C / 4;
+  const long total = (long)N * H * W * cg;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int c4 = (int)(i % cg);
+    long r = i / cg;
+    const int wi = (int)(r % W); r /= W;
+    const int hi = (int)(r % H);
+    const int n = (int)(r / H);
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    const int ho_lo = max(0, (hi + pd - ks + st) / st), ho_hi = min(Ho - 1, (hi + pd) / st);
+    const int wo_lo = max(0, (wi + pd - ks + st) / st), wo_hi = min(Wo - 1, (wi + pd) / st);
+    for (int ho = ho_lo; ho <= ho_hi; ++ho) {
+      const int kh = hi + pd - ho * st;
+      for (int wo = wo_lo; wo <= wo_hi; ++wo) {
+        const int kw = wi + pd - wo * st;
+        const long o = (((long)n * Ho + ho) * Wo + wo) * C + c4 * 4;
+        const uint32_t pk = *reinterpret_cast<const uint32_t*>(idx + o);
+        const float4 g = *reinterpret_cast<const float4*>(dy + o);
+        const float gf[4] = {g.x, g.y, g.z, g.w};
+        const int tap = kh * ks + kw;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if ((int)((pk >> (j * 8)) & 0xff) == tap) acc[j] += gf[j];
+      }
+    }
+    *reinterpret_cast<float4*>(dx + (((long)n * H + hi) * W + wi) * C + c4 * 4) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+  }
+}
+
+__global__ void __launch_bounds__(256) k_avgpool_fwd_f32(const float* __restrict__ x, float* __restrict__ y, int N, int HW, int C) {
+  pdl_enter();
+  const int cg = C / 4;
+  const long total = (long)N * cg;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int c4 = (int)(i % cg);
+    const long n = i / cg;
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int p = 0; p < HW; ++p) {
+      const float4 v = *reinterpret_cast<const float4*>(x + (n * HW + p) * C + c4 * 4);
+      a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+    }
+    const float inv = 1.f / (float)HW;
+    *reinterpret_cast<float4*>(y + n * C + c4 * 4) = make_float4(a.x * inv, a.y * inv, a.z * inv, a.w * inv);
+  }
+}
+
+__global__ void __launch_bounds__(256) k_avgpool_bwd_f32(const float* __restrict__ dy, float* __restrict__ dx, int N, int HW, int C) {
+  pdl_enter();
+  const int cg = C / 4;
+  const long total = (long)N * HW * cg;
+  const float inv = 1.f / (float)HW;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int c4 = (int)(i % cg);
+    const long n = i / cg / HW;
+    const float4 v = *reinterpret_cast<const float4*>(dy + n * C + c4 * 4);
+    *reinterpret_cast<float4*>(dx + i * 4) = make_float4(v.x * inv, v.y * inv, v.z * inv, v.w * inv);
+  }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256) k_avgpool_fwd(const T* __restrict__ x, T* __restrict__ y, int N, int HW, int C) {
   pdl_enter();
@@ -350,6 +445,11 @@ int pdt_maxpool_fwd(const void* x, void* y, int8_t* idx, int dtype, int N, int H
                     cudaStream_t stream) {
   if (C % 8 || ks * ks > 127) return PDT_E_UNSUPPORTED;
   const int Ho = (H + 2 * pd - ks) / st + 1, Wo = (W + 2 * pd - ks) / st + 1;
+  if (dtype == PDT_FP32) {
+    launch_pdl(k_maxpool_fwd_f32, dim3(grid_for((long)N * Ho * Wo * (C / 4), 256)), dim3(256), 0, stream,
+               reinterpret_cast<const float*>(x), reinterpret_cast<float*>(y), idx, N, H, W, C, Ho, Wo, ks, st, pd);
+    return (int)cudaGetLastError();
+  }
   LP_DISPATCH(dtype, k_maxpool_fwd<T><<<grid_for((long)N * Ho * Wo * (C / 8), 256), 256, 0, stream>>>(
       reinterpret_cast<const T*>(x), reinterpret_cast<T*>(y), idx, N, H, W, C, Ho, Wo, ks, st, pd));
   return (int)cudaGetLastError();
@@ -359,6 +459,11 @@ int pdt_maxpool_bwd(const void* dy, const int8_t* idx, void* dx, int dtype, int 
                     int pd, cudaStream_t stream) {
   if (C % 8) return PDT_E_UNSUPPORTED;
   const int Ho = (H + 2 * pd - ks) / st + 1, Wo = (W + 2 * pd - ks) / st + 1;
+  if (dtype == PDT_FP32) {
+    launch_pdl(k_maxpool_bwd_f32, dim3(grid_for((long)N * H * W * (C / 4), 256)), dim3(256), 0, stream,
+               reinterpret_cast<const float*>(dy), idx, reinterpret_cast<float*>(dx), N, H, W, C, Ho, Wo, ks, st, pd);
+    return (int)cudaGetLastError();
+  }
   LP_DISPATCH(dtype, k_maxpool_bwd<T><<<grid_for((long)N * H * W * (C / 8), 256), 256, 0, stream>>>(
       reinterpret_cast<const T*>(dy), idx, reinterpret_cast<T*>(dx), N, H, W, C, Ho, Wo, ks, st, pd));
   return (int)cudaGetLastError();
@@ -366,6 +471,11 @@ int pdt_maxpool_bwd(const void* dy, const int8_t* idx, void* dx, int dtype, int 
 
 int pdt_avgpool_fwd(const void* x, void* y, int dtype, int N, int HW, int C, cudaStream_t stream) {
   if (C % 8) return PDT_E_UNSUPPORTED;
+  if (dtype == PDT_FP32) {
+    launch_pdl(k_avgpool_fwd_f32, dim3(grid_for((long)N * (C / 4), 256)), dim3(256), 0, stream,
+               reinterpret_cast<const float*>(x), reinterpret_cast<float*>(y), N, HW, C);
+    return (int)cudaGetLastError();
+  }
   LP_DISPATCH(dtype, launch_pdl(k_avgpool_fwd<T>, dim3(grid_for((long)N * (C / 8), 256)), dim3(256), 0, stream, 
       reinterpret_cast<const T*>(x), reinterpret_cast<T*>(y), N, HW, C));
   return (int)cudaGetLastError();
@@ -373,6 +483,11 @@ int pdt_avgpool_fwd(const void* x, void* y, int dtype, int N, int HW, int C, cud
 
 int pdt_avgpool_bwd(const void* dy, void* dx, int dtype, int N, int HW, int C, cudaStream_t stream) {
   if (C % 8) return PDT_E_UNSUPPORTED;
+  if (dtype == PDT_FP32) {
+    launch_pdl(k_avgpool_bwd_f32, dim3(grid_for((long)N * HW * (C / 4), 256)), dim3(256), 0, stream,
+               reinterpret_cast<const float*>(dy), reinterpret_cast<float*>(dx), N, HW, C);
+    return (int)cudaGetLastError();
+  }
   LP_DISPATCH(dtype, launch_pdl(k_avgpool_bwd<T>, dim3(grid_for((long)N * HW * (C / 8), 256)), dim3(256), 0, stream, 
       reinterpret_cast<const T*>(dy), reinterpret_cast<T*>(dx), N, HW, C));
   return (int)cudaGetLastError();

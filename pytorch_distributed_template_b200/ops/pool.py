@@ -1,5 +1,6 @@
-"""MaxPool2d / AdaptiveAvgPool2d(1) on channels_last low-precision activations (SURVEY K-MAXPOOL,
-K-AVGPOOL); torch ops elsewhere."""
+"""MaxPool2d / AdaptiveAvgPool2d(1) on channels_last activations — bf16 / fp16 under amp, fp32 in the reference's
+fp32 modes — (SURVEY K-MAXPOOL, K-AVGPOOL); torch ops elsewhere.  (ATen's NHWC fp32 max-pool pair cost 13 ms of a
+68 ms fp32 step at 1200 images on B200.)"""
 import torch
 import torch.nn.functional as F
 
@@ -7,7 +8,7 @@ from . import _native
 
 
 def _lp_native(x):
-    return (x.is_cuda and x.dim() == 4 and x.dtype in (torch.bfloat16, torch.float16) and x.shape[1] % 8 == 0
+    return (x.is_cuda and x.dim() == 4 and x.dtype in (torch.bfloat16, torch.float16, torch.float32) and x.shape[1] % 8 == 0
             and _native.available())
 
 

@@ -100,9 +100,11 @@ def test_cross_entropy_fused(native_lib, dtype, B, K):
     assert (logits.grad.float() - lf.grad).abs().max().item() <= tol * lf.grad.abs().max().item() + 1e-7
 
 
-@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
 def test_pools(native_lib, dtype):
     from pytorch_distributed_template_b200 import ops
+    from pytorch_distributed_template_b200.ops import _native
+    n0 = _native.launch_count
     x = _nhwc(5, 64, 112, 112, dtype=dtype).requires_grad_(True)
     y = ops.max_pool2d(x, 3, 2, 1)
     xf = x.detach().float().requires_grad_(True)
@@ -119,6 +121,7 @@ def test_pools(native_lib, dtype):
     da = torch.randn(7, 512, device=_dev()).to(dtype)
     a.backward(da); af.backward(da.float())
     assert torch.allclose(z.grad.float(), zf.grad, rtol=1e-2, atol=1e-3)
+    assert _native.launch_count - n0 == 4, "pool kernels of the package were not used"
 
 
 def test_layout_cast_and_peer_copy(native_lib):
