@@ -113,6 +113,10 @@ class StepRunner:
         self.result = torch.zeros(2, dtype=torch.float32, device=self.device)   # cross-rank mean (loss, acc1), last step
         self.consumed = [torch.cuda.Event() for _ in range(nbuf)] if cuda else None
         self.capture_error = None
+        # (loss, acc1) of the last step in pinned HOST memory, written by a device-to-host copy that is part of
+        # the step itself (also of the captured graph): reading ``result_host`` after a stream / event
+        # synchronisation costs the training loop no extra launch between two replays.
+        self.result_host = torch.zeros(2, dtype=torch.float32).pin_memory() if cuda else torch.zeros(2)
 
     # ------------------------------------------------------------------ static input buffers
     def ensure_static(self, images, target):
@@ -185,6 +189,7 @@ class StepRunner:
                 self.scaler.update()
             else:
                 self.optimizer.step()
+        self.result_host.copy_(self.result, non_blocking=True)
         return self.result
 
     def _capture_dp(self, slot):
@@ -202,7 +207,11 @@ class StepRunner:
         try:
             for d in self.model.devices:
                 torch.cuda.synchronize(d)
-            g = self.model.graph_step(img, tgt, loss_fn, self.update_metrics, self.amp_dtype if self.use_amp else None)
+            def metrics_fn(pair, n):
+                self.update_metrics(pair, n)
+                self.result_host.copy_(self.result, non_blocking=True)
+
+            g = self.model.graph_step(img, tgt, loss_fn, metrics_fn, self.amp_dtype if self.use_amp else None)
         except Exception as e:
             self.capture_error = repr(e)
             self.graph_enabled = False

@@ -223,7 +223,7 @@ class GraphStep:
                 leaf = full.detach().requires_grad_(True)
                 with torch.enable_grad():
                     loss, pair = loss_fn(leaf, target)
-                metrics_fn(pair, n)
+                metrics_fn(pair, n)                 # also copies the reduced (loss, acc1) to the runner's pinned host slot
                 (dfull,) = torch.autograd.grad(loss, leaf)
         self.full, self.dfull = full, dfull
         # ---- B[d]
