@@ -34,6 +34,12 @@ from .ops import _native
 
 _streams = {}
 
+# Graph captures run in "thread_local" error mode: a training process has other threads that legitimately call the
+# CUDA runtime while a capture is open (the DataLoader's pin-memory thread allocates pinned buffers), which the
+# default "global" mode turns into an invalidated capture.  Kernels that autograd's device threads launch into the
+# capturing stream are captured in every mode.
+CAPTURE_MODE = "thread_local"
+
 
 def work_stream(device):
     """The one non-default stream everything of a training process runs on, made current on first use.
@@ -233,7 +239,7 @@ class StepRunner:
         g = torch.cuda.CUDAGraph()
         n0 = _native.launch_count
         try:
-            with torch.cuda.graph(g, stream=self.stream, pool=self._pool):
+            with torch.cuda.graph(g, stream=self.stream, pool=self._pool, capture_error_mode=CAPTURE_MODE):
                 self._body(img, tgt)
         except Exception as e:        # keep training: report once, continue eagerly
             self.capture_error = repr(e)

@@ -175,6 +175,7 @@ class GraphStep:
 
     def __init__(self, dp, images, target, loss_fn, metrics_fn, amp_dtype=None):
         from .. import amp
+        from ..engine import CAPTURE_MODE
         self.dp, self.images, self.target = dp, images, target
         W = len(dp.devices)
         devs, streams = dp.devices, dp._streams
@@ -200,7 +201,7 @@ class GraphStep:
         for d, dev in enumerate(devs):
             with torch.cuda.device(dev):
                 g = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(g, stream=streams[d]):
+                with torch.cuda.graph(g, stream=streams[d], capture_error_mode=CAPTURE_MODE):
                     if d > 0 and dp.buffer_arenas[0].used:
                         _peer_copy(dp.buffer_arenas[0].flat, dp.buffer_arenas[d].flat)
                     xs = images[bounds[d]:bounds[d + 1]]
@@ -217,7 +218,7 @@ class GraphStep:
         with torch.cuda.device(dev0):
             full = torch.empty((n,) + tuple(outs[0].shape[1:]), dtype=outs[0].dtype, device=dev0)
             self.gL = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(self.gL, stream=streams[0], pool=self.gF[0].pool()):
+            with torch.cuda.graph(self.gL, stream=streams[0], pool=self.gF[0].pool(), capture_error_mode=CAPTURE_MODE):
                 for d in range(W):
                     _peer_copy(outs[d].detach(), full[bounds[d]:bounds[d + 1]])
                 leaf = full.detach().requires_grad_(True)
@@ -230,7 +231,7 @@ class GraphStep:
         for d, dev in enumerate(devs):
             with torch.cuda.device(dev):
                 g = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(g, stream=streams[d], pool=self.gF[d].pool()):
+                with torch.cuda.graph(g, stream=streams[d], pool=self.gF[d].pool(), capture_error_mode=CAPTURE_MODE):
                     piece = dfull[bounds[d]:bounds[d + 1]]
                     if d > 0:
                         dl = torch.empty(piece.shape, dtype=piece.dtype, device=dev)
@@ -252,7 +253,7 @@ class GraphStep:
             a = dp.arenas[d]
             with torch.cuda.device(dev):
                 g = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(g, stream=streams[d], pool=self.gF[d].pool()):
+                with torch.cuda.graph(g, stream=streams[d], pool=self.gF[d].pool(), capture_error_mode=CAPTURE_MODE):
                     s_ = streams[d].cuda_stream
                     _native.check(lib.pdt_reduce_scatter_f32(dp._comms[d], dp._grads, None, 0, a.total, dp._state[d].data_ptr(), 0,
                                                             128, s_), "pdt_reduce_scatter_f32(dp)")

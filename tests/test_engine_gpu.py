@@ -60,9 +60,10 @@ def test_training_script_replays_the_step_from_a_graph(native_lib, tmp_path):
     env = dict(os.environ, PDT_SYNTHETIC="1", PDT_SYNTH_TRAIN_SIZE="512", PDT_SYNTH_VAL_SIZE="64", PDT_IMAGE_SIZE="64",
                PDT_NUM_CLASSES="10", PDT_OUTPUT_EXISTS="delete", MASTER_ADDR="127.0.0.1", MASTER_PORT="29743", RANK="0",
                WORLD_SIZE="1", LOCAL_RANK="0", PDT_REPORT_GRAPHS="1")
-    r = subprocess.run([sys.executable, os.path.join(ROOT, "distributed_syncBN_amp.py"), "--epochs", "1", "-b", "64", "-j", "0",
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "distributed_syncBN_amp.py"), "--epochs", "1", "-b", "64", "-j", "2",
                         "-p", "2", "--outpath", str(tmp_path / "out")], cwd=ROOT, env=env, capture_output=True, text=True,
                        timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert "||==> Train epoch: [0/1]" in r.stdout
+    # (-j 2: the DataLoader's pin-memory thread allocates pinned memory while the step is being captured)
     assert "[pdt] training step: 2 CUDA graphs" in r.stdout + r.stderr, r.stdout[-1500:] + r.stderr[-1500:]
