@@ -173,7 +173,10 @@ __device__ __forceinline__ uint4 ldg_stream(const void* p) {   // read-once data
 // array before any is consumed: left to itself ptxas reuses one register per row and the loop runs at one L2
 // round trip per row (measured: 0.25 us per row, 93 us for 296 rows).
 __device__ __forceinline__ void fold_quad(const float* __restrict__ partial, int nb, int n2, int c4, int b0, int step, double (&a)[4]) {
-  constexpr int kB = 8;
+  // 16 rows (16-byte loads) in flight per thread: with 128 folding threads that is 32 KB outstanding, about what one
+  // SM needs to cover the L2 round trip.  (At 8 in flight the fold of 116-148 rows x 1024 columns took 15-38 serial
+  // round trips: ~20 us of a ~33 us layer-4 convolution at 150 images per GPU.)
+  constexpr int kB = 16;
   for (int b = b0; b < nb; b += kB * step) {
     float4 v[kB];
 #pragma unroll
