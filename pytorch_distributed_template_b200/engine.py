@@ -93,7 +93,7 @@ class Meter:
 
 class StepRunner:
     def __init__(self, model, criterion, optimizer, scaler=None, device=None, use_amp=False, amp_dtype=None,
-                 graph=None, eager_steps=None, nbuf=2):
+                 graph=None, eager_steps=None, nbuf=None):
         self.model, self.criterion, self.optimizer, self.scaler = model, criterion, optimizer, scaler
         self.device = torch.device(device) if device is not None else next(model.parameters()).device
         self.use_amp, self.amp_dtype = bool(use_amp), amp_dtype
@@ -110,7 +110,7 @@ class StepRunner:
         self.graph_enabled = bool(graph) and self.native and dp_ok
         self.eager_left = int(os.environ.get("PDT_GRAPH_WARMUP", "3")) if eager_steps is None else int(eager_steps)
         self.stream = work_stream(self.device) if cuda else None
-        self.nbuf = nbuf
+        self.nbuf = nbuf = int(os.environ.get("PDT_FEED_BUFFERS", "2")) if nbuf is None else int(nbuf)
         self._static = None            # [(images, target)] * nbuf, owned here, written by DeviceFeed
         self._graphs = {}
         self._pool = None
@@ -306,8 +306,8 @@ class StepRunner:
 class DeviceFeed:
     """Iterate ``(images, target)`` on the device, staged for a ``StepRunner``.
 
-    Batch i+1 is copied host -> device on a side stream into the runner's staging buffer (i+1) % nbuf while
-    batch i computes; the copy waits for the step that last read that buffer (``runner.consumed``), the step
+    Batches i+1 .. i+nbuf-1 are copied host -> device on a side stream into the runner's staging buffers while
+    batch i computes; a copy waits for the step that last read that buffer (``runner.consumed``), the step
     waits for the copy.  Pinned host batches (``DataLoader(pin_memory=True)``) make the copy asynchronous.
     Batches of another shape than the first (the tail of an epoch) are moved with ordinary tensors."""
 
@@ -343,18 +343,24 @@ class DeviceFeed:
         return di, dt, ready, (images, target)      # the host tensors stay referenced until the copy is consumed
 
     def __iter__(self):
+        """Up to nbuf - 1 batches are staged ahead of the one being consumed (nbuf = 2: the classic double buffer;
+        nbuf = 3 gives every copy two step times to land, which matters when eight ranks pull from the same host)."""
+        import collections
         it = iter(self.loader)
-        try:
-            nxt = self._stage(next(it))
-        except StopIteration:
-            return
-        while nxt is not None:
-            cur = nxt
-            try:
-                nxt = self._stage(next(it))
-            except StopIteration:
-                nxt = None
-            di, dt, ready, _keep = cur
+        depth = max(1, self.runner.nbuf - 1)
+        queue = collections.deque()
+
+        def fill():
+            while len(queue) < depth + 1:
+                try:
+                    queue.append(self._stage(next(it)))
+                except StopIteration:
+                    return
+
+        fill()
+        while queue:
+            di, dt, ready, _keep = queue.popleft()
+            fill()
             if ready is not None:
                 main = torch.cuda.current_stream(self.device)
                 main.wait_event(ready)
