@@ -40,6 +40,11 @@ __device__ __forceinline__ void umma(uint32_t tmem_d, uint64_t da, uint64_t db, 
   if constexpr (sizeof(T) == 4) umma_tf32(tmem_d, da, db, idesc, acc);
   else umma_f16(tmem_d, da, db, idesc, acc);
 }
+template <typename T>
+__device__ __forceinline__ void umma_pair(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t acc) {
+  if constexpr (sizeof(T) == 4) umma_tf32_pair(tmem_d, da, db, idesc, acc);
+  else umma_f16_pair(tmem_d, da, db, idesc, acc);
+}
 constexpr int kThreads = 256;
 
 struct ConvGeom {
@@ -116,7 +121,12 @@ __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;"
 // delivery rate (~42 B/clk per SM when all SMs stream): per k-block a CTA pulled 16 KB of activations and
 // 32 KB of filter for 512 clk of MMA; with CL = 4 it is 16 + 8 KB.  A slot may be refilled only when every
 // CTA of the cluster has consumed it, so the MMA warp's commit arrives on the `empty` barrier of all CL CTAs.
-template <int BN, typename T, int CL>
+// PAIR (requires CL == 2): the two CTAs of a cluster run ONE M = 256 tcgen05.mma.cta_group::2 per k-step instead of two
+// M = 128 ones.  Each CTA still loads its own 128-pixel activation tile, but only HALF of the filter tile (rows
+// [rank*BN/2, +BN/2), no multicast); both CTAs' loads complete on the leader's `full` barrier, the leader's MMA
+// thread issues for the pair, its commits arrive on the `empty` / `tfull` barriers of both CTAs, and every
+// epilogue warp of either CTA hands the accumulator back on the leader's `tempty`.
+template <int BN, typename T, int CL, bool PAIR = false>
 __global__ void __launch_bounds__(kThreads, 1)
 k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, T* __restrict__ out,
              const float* __restrict__ bias, const ConvGeom g, const BnStats bs) {
@@ -149,13 +159,14 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     prefetch_tmap(&tmA);
     prefetch_tmap(&tmB);
   }
+  static_assert(!PAIR || CL == 2, "a CTA pair is a cluster of two");
   if (warp == 1 && lane == 0) {
-    for (int i = 0; i < C::kStages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], CL); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 4); }
+    for (int i = 0; i < C::kStages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], PAIR ? 1 : CL); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], PAIR ? 8 : 4); }
     mbar_init(bres, 1);
     fence_barrier_init();
   }
-  if (warp == 2) tmem_alloc(tmem_slot, C::kTmemCols);
+  if (warp == 2) { if constexpr (PAIR) tmem_alloc_pair(tmem_slot, C::kTmemCols); else tmem_alloc(tmem_slot, C::kTmemCols); }
   tc_fence_before();
   __syncthreads();
   if (CL > 1) cluster_sync_all();        // peers' barriers are initialised before anything is multicast at them
@@ -190,7 +201,17 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
           for (int s = 0; s < g.S; ++s)
             for (int cc = 0; cc < c_chunks; ++cc) {
               mbar_wait(&empty[stage], phase ^ 1);
-              if (elect_one_sync()) {
+              if constexpr (PAIR) {
+                if (elect_one_sync()) {
+                  // both CTAs' bytes (2 x A tile + the two halves of the B tile) complete on the LEADER's barrier
+                  const uint32_t lead_full = mapa_cluster(smem_u32(&full[stage]), 0);
+                  if (crank == 0) mbar_expect_tx(&full[stage], 2 * C::kStageBytesA + C::kStageBytesB);
+                  tma_load_im2col_4d_pair(smA + stage * C::kStageBytesA, &tmA, lead_full, cc * BK, cw, ch, img,
+                                          (uint16_t)(s * g.dil_w), (uint16_t)r);
+                  tma_load_2d_pair(smB + stage * C::kStageBytesB, &tmB, lead_full, (r * g.S + s) * g.C + cc * BK,
+                                   nt * BN + crank * (BN / 2));
+                }
+              } else if (elect_one_sync()) {
                 mbar_expect_tx(&full[stage], resb ? C::kStageBytesA : C::kStageBytes);
                 tma_load_im2col_4d(smA + stage * C::kStageBytesA, &tmA, &full[stage], cc * BK, cw, ch, img, (uint16_t)(s * g.dil_w), (uint16_t)r);
                 if (resb) {
@@ -206,10 +227,10 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
             }
       }
     }
-  } else if (warp == 1) {
-    // ================= MMA issuer (whole warp converged, one elected lane issues) =================
+  } else if (warp == 1 && (!PAIR || crank == 0)) {
+    // ================= MMA issuer (whole warp converged, one elected lane issues; the leader CTA of a pair) =================
     {
-      constexpr uint32_t idesc = make_idesc(BM, BN, Elem<T>::kFmt, 0, 0);
+      constexpr uint32_t idesc = make_idesc(PAIR ? 2 * BM : BM, BN, Elem<T>::kFmt, 0, 0);
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
@@ -228,14 +249,18 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
           const uint64_t db = make_sw128_desc(smem_u32(smB + (resb ? kb : stage) * C::kStageBytesB), 1024, 16);
           if (elect_one_sync()) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k)   // +32 bytes along K per UMMA_K step: +2 in the (addr >> 4) field
-              umma<T>(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
-            if (CL == 1) umma_commit(&empty[stage]); else umma_commit_mc(&empty[stage], kMask);
+            for (int k = 0; k < 4; ++k) {  // +32 bytes along K per UMMA_K step: +2 in the (addr >> 4) field
+              if constexpr (PAIR) umma_pair<T>(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+              else umma<T>(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+            }
+            if constexpr (PAIR) umma_commit_pair(&empty[stage], kMask);
+            else if (CL == 1) umma_commit(&empty[stage]);
+            else umma_commit_mc(&empty[stage], kMask);
           }
           __syncwarp();
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
         }
-        if (elect_one_sync()) umma_commit(&tfull[acc]);
+        if (elect_one_sync()) { if constexpr (PAIR) umma_commit_pair(&tfull[acc], kMask); else umma_commit(&tfull[acc]); }
         __syncwarp();
       }
     }
@@ -349,7 +374,10 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty[acc]);
+      if (lane == 0) {
+        if constexpr (PAIR) mbar_arrive_cluster(mapa_cluster(smem_u32(&tempty[acc]), 0));   // the leader's MMA thread waits for both CTAs
+        else mbar_arrive(&tempty[acc]);
+      }
     }
     if (kRegStats && bs.enabled) {
       float k0 = 0.f, k1 = 0.f, q0 = 0.f, q1 = 0.f;
@@ -410,7 +438,7 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   if (CL > 1) cluster_sync_all();        // no CTA leaves while a peer may still multicast into it or arrive on its barriers
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, C::kTmemCols);
+    if constexpr (PAIR) tmem_dealloc_pair(tmem_base, C::kTmemCols); else tmem_dealloc(tmem_base, C::kTmemCols);
   }
 }
 
@@ -671,11 +699,11 @@ int cluster_size_for(int BN, const ConvGeom& g, const void* filter, cudaStream_t
   return cl;
 }
 
-template <int BN, typename T, int CL>
+template <int BN, typename T, int CL, bool PAIR = false>
 int launch_igemm_cl(const CUtensorMap& tmA, const CUtensorMap& tmB, void* y, const float* bias, const ConvGeom& g, const BnStats& bs,
                     int sms, cudaStream_t stream) {
   using C = Cfg<BN>;
-  auto kern = k_conv_igemm<BN, T, CL>;
+  auto kern = k_conv_igemm<BN, T, CL, PAIR>;
   PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
   const int units = ((g.m_tiles + CL - 1) / CL) * g.n_tiles;
   cudaLaunchConfig_t cfg = {};
@@ -691,7 +719,7 @@ int launch_igemm_cl(const CUtensorMap& tmA, const CUtensorMap& tmB, void* y, con
     nattr = 1;
     // a persistent kernel must fit in ONE wave: ask how many clusters can be resident (GPC boundaries make
     // this less than SMs / CL on some parts) instead of assuming
-    static int cached[3] = {-1, -1, -1};
+    static int cached[3] = {-1, -1, -1};      // (static per template instance: PAIR and multicast variants each keep their own)
     int& mc = cached[CL == 2 ? 1 : 2];
     if (mc < 0) {
       cfg.gridDim = dim3(sms / CL * CL);
@@ -723,7 +751,12 @@ int launch_igemm(const CUtensorMap& tmA, const CUtensorMap& tmB, void* y, const 
                  int sms, cudaStream_t stream) {
   if constexpr (BN >= 128) {
     if (cl == 4) return launch_igemm_cl<BN, T, 4>(tmA, tmB, y, bias, g, bs, sms, stream);
-    if (cl == 2) return launch_igemm_cl<BN, T, 2>(tmA, tmB, y, bias, g, bs, sms, stream);
+    if (cl == 2) {
+      static int pair = -1;                 // PDT_CONV_PAIR=1: CTA pairs run one M = 256 cta_group::2 MMA (see k_conv_igemm)
+      if (pair < 0) { const char* e = getenv("PDT_CONV_PAIR"); pair = (e != nullptr && e[0] == '1') ? 1 : 0; }
+      if (pair == 1) return launch_igemm_cl<BN, T, 2, true>(tmA, tmB, y, bias, g, bs, sms, stream);
+      return launch_igemm_cl<BN, T, 2>(tmA, tmB, y, bias, g, bs, sms, stream);
+    }
   }
   return launch_igemm_cl<BN, T, 1>(tmA, tmB, y, bias, g, bs, sms, stream);
 }
