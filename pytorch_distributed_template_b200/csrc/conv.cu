@@ -88,11 +88,11 @@ struct BnStats {
   float momentum, eps;
 };
 
-template <int BN> struct Cfg {
+template <int BN, bool PAIR = false> struct Cfg {
   static constexpr int kStageBytesA = BM * 128;
-  static constexpr int kStageBytesB = BN * 128;
+  static constexpr int kStageBytesB = (PAIR ? BN / 2 : BN) * 128;       // a CTA of a pair holds half of the filter tile
   static constexpr int kStageBytes = kStageBytesA + kStageBytesB;
-  static constexpr int kStages = (BN >= 256) ? 4 : (BN >= 128 ? 6 : 8);
+  static constexpr int kStages = PAIR ? (BN >= 256 ? 6 : 8) : ((BN >= 256) ? 4 : (BN >= 128 ? 6 : 8));
   static constexpr int kTmemCols = 2 * BN;     // double-buffered accumulator (power of two >= 32 for BN in {64,128,256})
   // per epilogue warp: [sum, sumsq][K] accumulators + a 32 x 33 float transpose tile
   static constexpr int kStatBytes = 4 * (2 * kStatMaxK + 32 * 33) * 4;
@@ -130,7 +130,7 @@ template <int BN, typename T, int CL, bool PAIR = false>
 __global__ void __launch_bounds__(kThreads, 1)
 k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, T* __restrict__ out,
              const float* __restrict__ bias, const ConvGeom g, const BnStats bs) {
-  using C = Cfg<BN>;
+  using C = Cfg<BN, PAIR>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smA = smem;
@@ -205,7 +205,7 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                 if (elect_one_sync()) {
                   // both CTAs' bytes (2 x A tile + the two halves of the B tile) complete on the LEADER's barrier
                   const uint32_t lead_full = mapa_cluster(smem_u32(&full[stage]), 0);
-                  if (crank == 0) mbar_expect_tx(&full[stage], 2 * C::kStageBytesA + C::kStageBytesB);
+                  if (crank == 0) mbar_expect_tx(&full[stage], 2 * C::kStageBytes);
                   tma_load_im2col_4d_pair(smA + stage * C::kStageBytesA, &tmA, lead_full, cc * BK, cw, ch, img,
                                           (uint16_t)(s * g.dil_w), (uint16_t)r);
                   tma_load_2d_pair(smB + stage * C::kStageBytesB, &tmB, lead_full, (r * g.S + s) * g.C + cc * BK,
@@ -702,7 +702,7 @@ int cluster_size_for(int BN, const ConvGeom& g, const void* filter, cudaStream_t
 template <int BN, typename T, int CL, bool PAIR = false>
 int launch_igemm_cl(const CUtensorMap& tmA, const CUtensorMap& tmB, void* y, const float* bias, const ConvGeom& g, const BnStats& bs,
                     int sms, cudaStream_t stream) {
-  using C = Cfg<BN>;
+  using C = Cfg<BN, PAIR>;
   auto kern = k_conv_igemm<BN, T, CL, PAIR>;
   PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
   const int units = ((g.m_tiles + CL - 1) / CL) * g.n_tiles;
@@ -754,7 +754,10 @@ int launch_igemm(const CUtensorMap& tmA, const CUtensorMap& tmB, void* y, const 
     if (cl == 2) {
       static int pair = -1;                 // PDT_CONV_PAIR=1: CTA pairs run one M = 256 cta_group::2 MMA (see k_conv_igemm)
       if (pair < 0) { const char* e = getenv("PDT_CONV_PAIR"); pair = (e != nullptr && e[0] == '1') ? 1 : 0; }
-      if (pair == 1) return launch_igemm_cl<BN, T, 2, true>(tmA, tmB, y, bias, g, bs, sms, stream);
+      // pairs pay when the k loop is long enough to amortise the pair's hand-shakes (3x3 layers: 18-72 k-blocks;
+      // measured slower on 1x1 projections with 2-4 k-blocks)
+      const int kb = g.R * g.S * ((g.C + (128 / (int)sizeof(T)) - 1) / (128 / (int)sizeof(T)));
+      if (pair == 1 && kb >= 9) return launch_igemm_cl<BN, T, 2, true>(tmA, tmB, y, bias, g, bs, sms, stream);
       return launch_igemm_cl<BN, T, 2>(tmA, tmB, y, bias, g, bs, sms, stream);
     }
   }
