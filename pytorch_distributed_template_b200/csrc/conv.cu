@@ -121,6 +121,9 @@ __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;"
 // delivery rate (~42 B/clk per SM when all SMs stream): per k-block a CTA pulled 16 KB of activations and
 // 32 KB of filter for 512 clk of MMA; with CL = 4 it is 16 + 8 KB.  A slot may be refilled only when every
 // CTA of the cluster has consumed it, so the MMA warp's commit arrives on the `empty` barrier of all CL CTAs.
+// Measured on B200 (fp16, 1200 images, in isolation): 256->256 3x3 at 14x14 209.2 -> 196.1 us (1.33 -> 1.42 PFLOP/s),
+// 512->512 3x3 at 7x7 197.0 -> 189.1 us (1.47 PFLOP/s), 128->256 3x3/2 125.7 -> 121.4 us; slower for 2-4 k-block 1x1
+// projections, which keep the multicast form.  Whole step 25.00 -> 24.82 ms.
 // PAIR (requires CL == 2): the two CTAs of a cluster run ONE M = 256 tcgen05.mma.cta_group::2 per k-step instead of two
 // M = 128 ones.  Each CTA still loads its own 128-pixel activation tile, but only HALF of the filter tile (rows
 // [rank*BN/2, +BN/2), no multicast); both CTAs' loads complete on the leader's `full` barrier, the leader's MMA
@@ -752,8 +755,8 @@ int launch_igemm(const CUtensorMap& tmA, const CUtensorMap& tmB, void* y, const 
   if constexpr (BN >= 128) {
     if (cl == 4) return launch_igemm_cl<BN, T, 4>(tmA, tmB, y, bias, g, bs, sms, stream);
     if (cl == 2) {
-      static int pair = -1;                 // PDT_CONV_PAIR=1: CTA pairs run one M = 256 cta_group::2 MMA (see k_conv_igemm)
-      if (pair < 0) { const char* e = getenv("PDT_CONV_PAIR"); pair = (e != nullptr && e[0] == '1') ? 1 : 0; }
+      static int pair = -1;                 // CTA pairs run one M = 256 cta_group::2 MMA (see k_conv_igemm); PDT_CONV_PAIR=0: multicast pairs
+      if (pair < 0) { const char* e = getenv("PDT_CONV_PAIR"); pair = (e != nullptr && e[0] == '0') ? 0 : 1; }
       // pairs pay when the k loop is long enough to amortise the pair's hand-shakes (3x3 layers: 18-72 k-blocks;
       // measured slower on 1x1 projections with 2-4 k-blocks)
       const int kb = g.R * g.S * ((g.C + (128 / (int)sizeof(T)) - 1) / (128 / (int)sizeof(T)));
