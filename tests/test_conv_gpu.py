@@ -385,3 +385,29 @@ def test_residual_gradient_link_matches_unfused_backward(native_lib, monkeypatch
     rel = ((grads["1"] - grads["0"]).norm() / grads["0"].norm()).item()
     assert rel < 2e-2, rel
     assert torch.isfinite(grads["1"]).all()
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("N,C,H,K,R,stride,pad", [(101, 256, 14, 256, 3, 1, 1),    # 155 M tiles: odd, the last pair has one empty half
+                                                  (100, 128, 28, 256, 3, 2, 1),    # strided, 128 -> 256
+                                                  (400, 512, 7, 512, 3, 1, 1),     # two N tiles per M tile
+                                                  (160, 256, 14, 128, 3, 1, 1)])   # BN = 128 pairs
+def test_conv_cta_pair_tiles(native_lib, dtype, N, C, H, K, R, stride, pad):
+    """Shapes large enough (>= 148 M tiles, >= 9 k-blocks, N tile >= 128) to run as CTA pairs: one M = 256
+    tcgen05.mma.cta_group::2 per k-step, each CTA holding half of the filter tile (k_conv_igemm<.., PAIR>)."""
+    from pytorch_distributed_template_b200.ops import conv_native
+    torch.manual_seed(7)
+    x = _nhwc(N, C, H, H, dtype=dtype)
+    w = (torch.randn(K, C, R, R, device=_dev()) / (C * R * R) ** 0.5).to(dtype).contiguous(memory_format=torch.channels_last)
+    y = conv_native.fprop(x, w, stride, pad)
+    tol = TOL[dtype]
+    for sl in (slice(0, 24), slice(N - 24, N)):               # first and last images (the tail tiles)
+        ref = F.conv2d(x[sl].float(), w.float(), None, stride, pad)
+        assert (y[sl].float() - ref).abs().max().item() <= tol * max(1.0, ref.abs().max().item())
+    # with the BatchNorm statistics epilogue
+    bn = torch.nn.BatchNorm2d(K).to(_dev())
+    y2, mean, invstd = conv_native.fprop_bnstats(x, w, stride, pad, bn.running_mean, bn.running_var, 0.1, 1e-5)
+    yf = y2.float()
+    assert torch.equal(y2, y)
+    assert torch.allclose(mean, yf.mean((0, 2, 3)), rtol=2e-3, atol=2e-3)
+    assert torch.allclose(invstd, torch.rsqrt(yf.var((0, 2, 3), unbiased=False) + 1e-5), rtol=5e-3, atol=5e-3)
