@@ -19,7 +19,7 @@
 
 /* Bumped whenever an entry point is added or changes its signature; the Python binding refuses a library
  * that reports a different number (a stale build of an older checkout). */
-#define PDT_ABI_VERSION 11
+#define PDT_ABI_VERSION 12
 
 #ifdef __cplusplus
 extern "C" {
@@ -224,10 +224,14 @@ int pdt_conv_fprop_add(const void* x, const void* w, void* y, const void* addend
 /* Convolution + BatchNorm batch statistics in one kernel: the epilogue also produces the per-channel
  * mean / invstd of y (and updates the running statistics), so BatchNorm needs no statistics pass of its
  * own (cudnnConvolutionForward + batch_norm statistics kernel).  Dense NHWC output, K <= 512.
- * scratch: pdt_bn_scratch_bytes(K) bytes, first word zero before the first call. */
+ * scratch: pdt_bn_scratch_bytes(K) bytes, first word zero before the first call.
+ * comm != NULL with world > 1: SyncBatchNorm — the CTA that finalises the statistics exchanges the raw moments
+ * with its peers over NVLink before it writes mean / invstd (the all_gather of torch's sync_batch_norm,
+ * torch/nn/modules/_functions.py:74-76, inside the convolution kernel).  Same for the two kernels below. */
 int pdt_conv_fprop_bnstats(const void* x, const void* w, void* y, int dtype, int N, int H, int W, int C, int K, int R, int S,
-                           int stride, int pad, void* scratch, float* running_mean, float* running_var, float momentum,
-                           float eps, float* save_mean, float* save_invstd, cudaStream_t stream);
+                           int stride, int pad, void* scratch, const PdtCommDesc* comm, float* running_mean,
+                           float* running_var, float momentum, float eps, float* save_mean, float* save_invstd,
+                           cudaStream_t stream);
 /* 3x3 / stride 1 / pad 1 convolution with input-patch reuse for the large feature maps (W <= 56, K in {64, 128},
  * C % 64 == 0): one tiled TMA load per (TR+2) x (W+2) patch serves all nine taps through row-shifted shared-memory
  * descriptors; the 64x64 filter bank stays resident in shared memory.  scratch != NULL also yields the BatchNorm
@@ -237,8 +241,8 @@ int pdt_conv3x3_halo_supported(int dtype, int N, int H, int W, int C, int K);
  * requires scratch == NULL).  As the data gradient of a residual block's first convolution it takes the shortcut
  * gradient, replacing the ATen add that autograd issues per block in the reference's backward (distributed.py:262). */
 int pdt_conv3x3_halo_add(const void* x, const void* w, void* y, const void* addend, int dtype, int N, int H, int W, int C, int K,
-                         void* scratch, float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
-                         float* save_invstd, cudaStream_t stream);
+                         void* scratch, const PdtCommDesc* comm, float* running_mean, float* running_var, float momentum,
+                         float eps, float* save_mean, float* save_invstd, cudaStream_t stream);
 int pdt_conv3x3_halo(const void* x, const void* w, void* y, int dtype, int N, int H, int W, int C, int K, void* scratch,
                      float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
                      float* save_invstd, cudaStream_t stream);
@@ -254,8 +258,8 @@ int pdt_conv3x3_wgrad_halo(const void* x, const void* dy, float* dw, int dtype, 
  * xs [N][HP][WP][16], wp [64][4][4][16], y [N][HP-3][WP-3][64]. */
 int pdt_stem_conv_supported(int dtype, int N, int HP, int WP, int K);
 int pdt_stem_conv(const void* xs, const void* wp, void* y, int dtype, int N, int HP, int WP, int K, void* scratch,
-                  float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
-                  float* save_invstd, cudaStream_t stream);
+                  const PdtCommDesc* comm, float* running_mean, float* running_var, float momentum, float eps,
+                  float* save_mean, float* save_invstd, cudaStream_t stream);
 /* Weight gradient (cudnnConvolutionBackwardFilter): dw [K][R][S][C] fp32 += sum over pixels; split-K over
  * the pixel dimension with red.global.add, so zero dw first.  C % 64 == 0, K % 64 == 0. */
 int pdt_conv_wgrad(const void* x, const void* dy, float* dw, int dtype, int N, int H, int W, int C, int K, int R, int S,

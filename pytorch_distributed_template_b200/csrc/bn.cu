@@ -100,37 +100,9 @@ __device__ __forceinline__ void fold_partials(double* tot, const float* __restri
   fold_rows_f64(tot, partial, nb, n2, (int)threadIdx.x, (int)blockDim.x, [] { __syncthreads(); });
 }
 
-// Cross-rank sum of tot[0..n) (+ the count) through the peers' scratch slots; one block per rank.
-// With an NVLS mapping of the pad, this rank's vector reaches every peer's slot through ONE 16-byte multimem.st
-// per four values (the switch replicates it) instead of `world` scalar peer stores per value.  Every rank then
-// sums the slots in rank order, so all ranks compute bit-identical statistics on either data plane.
+// Cross-rank sum of tot[0..n) (+ the count): the whole block takes part (fabric.cuh: exchange_sum_t).
 __device__ __forceinline__ void exchange_sum(const Comm& c, double* tot, int n, double* count) {
-  const int ch = 1;
-  if (c.pad_mc != nullptr) {
-    float* slot = scratch_addr(c.pad_mc, ch, c.rank);
-    for (int i4 = threadIdx.x * 4; i4 <= n; i4 += blockDim.x * 4) {
-      float v[4];
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int i = i4 + j;
-        v[j] = (i < n) ? (float)tot[i] : (i == n ? (float)*count : 0.f);
-      }
-      mc_st_f4(slot + i4, make_float4(v[0], v[1], v[2], v[3]));
-    }
-  } else {
-    for (int i = threadIdx.x; i <= n; i += blockDim.x) {
-      const float v = (i < n) ? (float)tot[i] : (float)*count;
-      for (int q = 0; q < c.world; ++q) scratch_addr(c.pad[q], ch, c.rank)[i] = v;
-    }
-  }
-  __threadfence_system();
-  block_barrier(c, ch, 0);
-  for (int i = threadIdx.x; i <= n; i += blockDim.x) {
-    double a = 0.0;
-    for (int p = 0; p < c.world; ++p) a += (double)*reinterpret_cast<volatile float*>(scratch_addr(c.pad[c.rank], ch, p) + i);
-    if (i < n) tot[i] = a; else *count = a;
-  }
-  block_barrier(c, ch, 0);
+  exchange_sum_t(c, tot, n, count, (int)threadIdx.x, (int)blockDim.x, [] { __syncthreads(); });
 }
 
 // After block_fold: the last block folds every block's row, exchanges with the peers (SyncBN) and writes

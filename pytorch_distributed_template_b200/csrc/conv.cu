@@ -20,7 +20,7 @@
 #include <cstdlib>
 #include <type_traits>
 #include "tc.cuh"
-#include "../../include/pdt_b200.h"
+#include "fabric.cuh"
 
 namespace {
 
@@ -86,6 +86,7 @@ struct BnStats {
   float* save_mean;
   float* save_invstd;
   float momentum, eps;
+  Comm comm;               // world > 1: SyncBatchNorm — the last CTA exchanges the raw moments with its peers (fabric.cuh)
 };
 
 template <int BN, bool PAIR = false> struct Cfg {
@@ -418,7 +419,11 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         __threadfence();
         double* tot = reinterpret_cast<double*>(s_stat);      // 2K doubles <= 8 KB of the 16 KB region
         fold_rows_f64(tot, bs.partial, (int)gridDim.x, 2 * K, te, 128, [] { epi_bar_sync(); });
-        const double n = (double)g.M;
+        __shared__ double s_cnt;
+        if (te == 0) s_cnt = (double)g.M;
+        epi_bar_sync();
+        if (bs.comm.world > 1) exchange_sum_t(bs.comm, tot, 2 * K, &s_cnt, te, 128, [] { epi_bar_sync(); });
+        const double n = s_cnt;
         for (int c = te; c < K; c += 128) {
           const double mean = tot[c] / n;
           double var = tot[K + c] / n - mean * mean;
@@ -1033,8 +1038,8 @@ int pdt_conv_fprop_add(const void* x, const void* w, void* y, const void* addend
 // Convolution + BatchNorm batch statistics in one kernel (dense NHWC output, K <= 512).  scratch: at
 // least 256 + 148 * 2 * K * 4 bytes, first word zero before the first call (pdt_bn_scratch_bytes fits).
 int pdt_conv_fprop_bnstats(const void* x, const void* w, void* y, int dtype, int N, int H, int W, int C, int K, int R, int S,
-                           int stride, int pad, void* scratch, float* running_mean, float* running_var, float momentum,
-                           float eps, float* save_mean, float* save_invstd, cudaStream_t stream) {
+                           int stride, int pad, void* scratch, const PdtCommDesc* comm, float* running_mean, float* running_var,
+                           float momentum, float eps, float* save_mean, float* save_invstd, cudaStream_t stream) {
   if (dtype != PDT_BF16 && dtype != PDT_FP16 && dtype != PDT_FP32) return PDT_E_UNSUPPORTED;
   const int es = esize_of(dtype);
   if (C % (16 / es) || K % 8 || K > kStatMaxK || R < 1 || S < 1 || stride < 1 || pad < 0) return PDT_E_UNSUPPORTED;
@@ -1051,6 +1056,7 @@ int pdt_conv_fprop_bnstats(const void* x, const void* w, void* y, int dtype, int
   bs.running_mean = running_mean; bs.running_var = running_var;
   bs.save_mean = save_mean; bs.save_invstd = save_invstd;
   bs.momentum = momentum; bs.eps = eps;
+  bs.comm = make_comm(comm);
   return dispatch_fprop(x, w, y, nullptr, dtype, g, stream, &bs);
 }
 

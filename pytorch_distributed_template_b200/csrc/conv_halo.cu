@@ -22,7 +22,7 @@
 #include <cstdlib>
 #include <type_traits>
 #include "tc.cuh"
-#include "../../include/pdt_b200.h"
+#include "fabric.cuh"
 
 namespace {
 
@@ -54,6 +54,7 @@ struct BnStats {
   float* save_invstd;
   float momentum, eps;
   long long count;        // N*H*W
+  Comm comm;              // world > 1: SyncBatchNorm — the last CTA exchanges the raw moments with its peers (fabric.cuh)
 };
 
 template <int BN, bool RES> struct HCfg {
@@ -526,7 +527,11 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         __threadfence();
         double* tot = reinterpret_cast<double*>(s_stat);
         fold_rows_f64(tot, bs.partial, (int)gridDim.x, 2 * K, te, 256, [] { epi_bar_sync(); });
-        const double cnt = (double)bs.count;
+        __shared__ double s_cnt;
+        if (te == 0) s_cnt = (double)bs.count;
+        epi_bar_sync();
+        if (bs.comm.world > 1) exchange_sum_t(bs.comm, tot, 2 * K, &s_cnt, te, 256, [] { epi_bar_sync(); });
+        const double cnt = s_cnt;
         for (int c = te; c < K; c += 256) {
           const double mean = tot[c] / cnt;
           double var = tot[K + c] / cnt - mean * mean;
@@ -908,7 +913,11 @@ k_stem_conv(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUt
         __threadfence();
         double* tot = reinterpret_cast<double*>(s_stat);
         fold_rows_f64(tot, bs.partial, (int)gridDim.x, 2 * K, te, 256, [] { epi_bar_sync(); });
-        const double cnt = (double)bs.count;
+        __shared__ double s_cnt;
+        if (te == 0) s_cnt = (double)bs.count;
+        epi_bar_sync();
+        if (bs.comm.world > 1) exchange_sum_t(bs.comm, tot, 2 * K, &s_cnt, te, 256, [] { epi_bar_sync(); });
+        const double cnt = s_cnt;
         for (int c = te; c < K; c += 256) {
           const double mean = tot[c] / cnt;
           double var = tot[K + c] / cnt - mean * mean;
@@ -1010,7 +1019,7 @@ int pdt_conv3x3_halo_supported(int dtype, int N, int H, int W, int C, int K) {
 int pdt_conv3x3_halo(const void* x, const void* w, void* y, int dtype, int N, int H, int W, int C, int K, void* scratch,
                      float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
                      float* save_invstd, cudaStream_t stream) {
-  return pdt_conv3x3_halo_add(x, w, y, nullptr, dtype, N, H, W, C, K, scratch, running_mean, running_var, momentum, eps,
+  return pdt_conv3x3_halo_add(x, w, y, nullptr, dtype, N, H, W, C, K, scratch, nullptr, running_mean, running_var, momentum, eps,
                               save_mean, save_invstd, stream);
 }
 
@@ -1018,8 +1027,8 @@ int pdt_conv3x3_halo(const void* x, const void* w, void* y, int dtype, int N, in
 // data gradient of a residual block's first 3x3 convolution takes the shortcut gradient here.  Not combined
 // with the statistics epilogue (addend != NULL requires scratch == NULL).
 int pdt_conv3x3_halo_add(const void* x, const void* w, void* y, const void* addend, int dtype, int N, int H, int W, int C, int K,
-                         void* scratch, float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
-                         float* save_invstd, cudaStream_t stream) {
+                         void* scratch, const PdtCommDesc* comm, float* running_mean, float* running_var, float momentum, float eps,
+                         float* save_mean, float* save_invstd, cudaStream_t stream) {
   if (!pdt_conv3x3_halo_supported(dtype, N, H, W, C, K)) return PDT_E_UNSUPPORTED;
   if (addend != nullptr && scratch != nullptr) return PDT_E_UNSUPPORTED;
   if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(w) | reinterpret_cast<uintptr_t>(y) |
@@ -1084,6 +1093,7 @@ int pdt_conv3x3_halo_add(const void* x, const void* w, void* y, const void* adde
   bs.save_mean = save_mean; bs.save_invstd = save_invstd;
   bs.momentum = momentum; bs.eps = eps;
   bs.count = (long long)N * H * W;
+  bs.comm = make_comm(comm);
   if (K == 64) {
     if (resident) return launch<64, true>(x, w, y, dtype, g, bs, tmX, tmW, tmY, stream);
     return launch<64, false>(x, w, y, dtype, g, bs, tmX, tmW, tmY, stream);
@@ -1168,7 +1178,7 @@ int pdt_stem_conv_supported(int dtype, int N, int HP, int WP, int K) {
 // xs: [N][HP][WP][16] space-to-depth image (pdt_stem_s2d), wp: [64][4][4][16] filter, y: [N][HP-3][WP-3][64].
 // scratch / statistics pointers as in pdt_conv_fprop_bnstats; scratch == NULL for a plain convolution.
 int pdt_stem_conv(const void* xs, const void* wp, void* y, int dtype, int N, int HP, int WP, int K, void* scratch,
-                  float* running_mean, float* running_var, float momentum, float eps, float* save_mean, float* save_invstd,
+                  const PdtCommDesc* comm, float* running_mean, float* running_var, float momentum, float eps, float* save_mean, float* save_invstd,
                   cudaStream_t stream) {
   if (!pdt_stem_conv_supported(dtype, N, HP, WP, K)) return PDT_E_UNSUPPORTED;
   if ((reinterpret_cast<uintptr_t>(xs) | reinterpret_cast<uintptr_t>(wp) | reinterpret_cast<uintptr_t>(y)) & 15) return PDT_E_UNSUPPORTED;
@@ -1219,6 +1229,7 @@ int pdt_stem_conv(const void* xs, const void* wp, void* y, int dtype, int N, int
   bs.save_mean = save_mean; bs.save_invstd = save_invstd;
   bs.momentum = momentum; bs.eps = eps;
   bs.count = (long long)N * g.P * g.Q;
+  bs.comm = make_comm(comm);
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);

@@ -77,6 +77,54 @@ __device__ __forceinline__ void block_barrier(const Comm& c, int channel, int ro
   __syncthreads();
 }
 
+// The same for a SUBSET of the block's threads (the epilogue warps of a convolution kernel): `tid` numbers the
+// participating threads from 0, `sync` synchronises exactly them (a named barrier).
+template <class Sync>
+__device__ __forceinline__ void block_barrier_t(const Comm& c, int channel, int row, int tid, Sync sync) {
+  sync();
+  if (tid < c.world) {
+    signal_flag(flag_addr(c.pad[tid], channel, row, c.rank), c.timeout_ns);
+    wait_flag(flag_addr(c.pad[c.rank], channel, row, tid), c.timeout_ns);
+  }
+  sync();
+}
+
+// Cross-rank sum of tot[0..n) (+ the count) through the peers' scratch slots; called by ONE block per rank (the
+// one that finalises a statistics reduction) with `nthr` threads numbered `tid`.  With an NVLS mapping of the pad,
+// this rank's vector reaches every peer's slot through ONE 16-byte multimem.st per four values (the switch
+// replicates it) instead of `world` scalar peer stores per value.  Every rank then sums the slots in rank order,
+// so all ranks compute bit-identical statistics on either data plane.  SyncBatchNorm's all_gather / all_reduce
+// (torch/nn/modules/_functions.py:74-76, 159-164) as an in-kernel exchange.
+template <class Sync>
+__device__ __forceinline__ void exchange_sum_t(const Comm& c, double* tot, int n, double* count, int tid, int nthr, Sync sync) {
+  const int ch = 1;
+  if (c.pad_mc != nullptr) {
+    float* slot = scratch_addr(c.pad_mc, ch, c.rank);
+    for (int i4 = tid * 4; i4 <= n; i4 += nthr * 4) {
+      float v[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int i = i4 + j;
+        v[j] = (i < n) ? (float)tot[i] : (i == n ? (float)*count : 0.f);
+      }
+      mc_st_f4(slot + i4, make_float4(v[0], v[1], v[2], v[3]));
+    }
+  } else {
+    for (int i = tid; i <= n; i += nthr) {
+      const float v = (i < n) ? (float)tot[i] : (float)*count;
+      for (int q = 0; q < c.world; ++q) scratch_addr(c.pad[q], ch, c.rank)[i] = v;
+    }
+  }
+  __threadfence_system();
+  block_barrier_t(c, ch, 0, tid, sync);
+  for (int i = tid; i <= n; i += nthr) {
+    double a = 0.0;
+    for (int p = 0; p < c.world; ++p) a += (double)*reinterpret_cast<volatile float*>(scratch_addr(c.pad[c.rank], ch, p) + i);
+    if (i < n) tot[i] = a; else *count = a;
+  }
+  block_barrier_t(c, ch, 0, tid, sync);
+}
+
 __host__ inline uint64_t spin_timeout_ns() {
   static const uint64_t ns = [] {
     const char* e = getenv("PDT_SPIN_TIMEOUT_S");

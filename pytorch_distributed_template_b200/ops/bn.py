@@ -279,7 +279,8 @@ def bn_act(x, bn, residual=None, relu=False, comm=None, group=None, stats=None, 
     if stats is not None:
         if bn.track_running_stats and bn.num_batches_tracked is not None:
             _bump(bn.num_batches_tracked)
-        return _BNActNative.apply(x, residual, bn.weight, bn.bias, None, None, 0.1, bn.eps, relu, None,
+        # (comm: the statistics were already exchanged inside the convolution; backward still has to sum dy moments)
+        return _BNActNative.apply(x, residual, bn.weight, bn.bias, None, None, 0.1, bn.eps, relu, comm,
                                   stats[0], stats[1], res_link)
     training = bn.training or bn.running_mean is None
     sync = training and (comm is not None or group is not None)
@@ -326,7 +327,7 @@ def bn_relu_maxpool(x, bn, kernel_size=3, stride=2, padding=1, comm=None, group=
     return max_pool2d(bn_act(x, bn, None, True, comm=comm, group=group), kernel_size, stride, padding)
 
 
-def conv_bn_relu_maxpool(x, conv, bn, kernel_size=3, stride=2, padding=1):
+def conv_bn_relu_maxpool(x, conv, bn, kernel_size=3, stride=2, padding=1, comm=None):
     """``max_pool2d(relu(bn(conv(x))))`` (the ResNet stem).  On the native training path the convolution's
     epilogue produces the BatchNorm statistics, so the 112x112x64 conv output is read once (by the fused
     BN+ReLU+pool kernel) instead of twice."""
@@ -336,7 +337,7 @@ def conv_bn_relu_maxpool(x, conv, bn, kernel_size=3, stride=2, padding=1):
             and bn.affine and os.environ.get("PDT_BNSTATS_FUSION", "1") == "1")
     if fuse:
         momentum = _ema_factor(bn)
-        out = conv2d(x, conv, bnpack=(bn.running_mean, bn.running_var, momentum, bn.eps))
+        out = conv2d(x, conv, bnpack=(bn.running_mean, bn.running_var, momentum, bn.eps, comm))
         if isinstance(out, tuple):
             y, mean, invstd = out
             C = y.shape[1]
@@ -344,10 +345,16 @@ def conv_bn_relu_maxpool(x, conv, bn, kernel_size=3, stride=2, padding=1):
                 if bn.num_batches_tracked is not None:
                     _bump(bn.num_batches_tracked)
                 return _BNReluPoolNative.apply(y, bn.weight, bn.bias, None, None, momentum, bn.eps, kernel_size, stride,
-                                               padding, None, mean, invstd)
-            raise RuntimeError("conv epilogue produced statistics for a shape the fused pool kernels do not serve")
-        return bn_relu_maxpool(out, bn, kernel_size, stride, padding)
-    return bn_relu_maxpool(conv2d(x, conv), bn, kernel_size, stride, padding)
+                                               padding, comm, mean, invstd)
+            if comm is None:
+                raise RuntimeError("conv epilogue produced statistics for a shape the fused pool kernels do not serve")
+            from .pool import max_pool2d        # fp32 SyncBatchNorm stem: statistics are done, normalise + pool separately
+            if bn.num_batches_tracked is not None:
+                _bump(bn.num_batches_tracked)
+            return max_pool2d(_BNActNative.apply(y, None, bn.weight, bn.bias, None, None, momentum, bn.eps, True, comm,
+                                                 mean, invstd, None), kernel_size, stride, padding)
+        return bn_relu_maxpool(out, bn, kernel_size, stride, padding, comm=comm)
+    return bn_relu_maxpool(conv2d(x, conv), bn, kernel_size, stride, padding, comm=comm)
 
 
 def conv_bn_act(x, conv, bn, residual=None, relu=False, comm=None, group=None, consume=None, produce=None, res_link=None):
@@ -356,15 +363,16 @@ def conv_bn_act(x, conv, bn, residual=None, relu=False, comm=None, group=None, c
     own statistics kernel because the cross-rank exchange lives there."""
     from .conv import conv2d
     training = bn.training or bn.running_mean is None
-    fuse = (training and comm is None and group is None and torch.is_grad_enabled() and x.is_cuda
+    # (comm: SyncBatchNorm on the native fabric — the exchange of the moments happens in the convolution's last CTA)
+    fuse = (training and group is None and torch.is_grad_enabled() and x.is_cuda
             and _native.available() and bn.track_running_stats and bn.affine)
     if fuse:
         momentum = _ema_factor(bn)
-        out = conv2d(x, conv, bnpack=(bn.running_mean, bn.running_var, momentum, bn.eps), consume=consume, produce=produce)
+        out = conv2d(x, conv, bnpack=(bn.running_mean, bn.running_var, momentum, bn.eps, comm), consume=consume, produce=produce)
         if isinstance(out, tuple):
             y, mean, invstd = out
             if _native_ok(y, y.shape[1]):
-                return bn_act(y, bn, residual, relu, stats=(mean, invstd), res_link=res_link)
+                return bn_act(y, bn, residual, relu, comm=comm, stats=(mean, invstd), res_link=res_link)
             raise RuntimeError("conv epilogue produced statistics for a shape the BN kernels do not serve")
         return bn_act(out, bn, residual, relu, comm=comm, group=group, res_link=res_link)
     return bn_act(conv2d(x, conv, consume=consume, produce=produce), bn, residual, relu, comm=comm, group=group, res_link=res_link)

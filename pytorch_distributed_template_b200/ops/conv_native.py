@@ -25,16 +25,16 @@ _native.register("pdt_conv_wgrad", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _
 _native.register("pdt_conv_fprop_ex", [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _ll, _ll, _ll, _i, _i, _i, _i,
                                        _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp])
 _native.register("pdt_conv_fprop_add", [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp])
-_native.register("pdt_conv3x3_halo_add", [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _native._f, _native._f, _vp, _vp, _vp])
+_native.register("pdt_conv3x3_halo_add", [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _native._PC, _vp, _vp, _native._f, _native._f, _vp, _vp, _vp])
 _native.register("pdt_conv_wgrad_ex", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _ll, _ll, _ll, _i, _i, _i, _i,
                                        _i, _i, _i, _i, _i, _i, _i, _vp])
 _native.register("pdt_stem_s2d", [_vp, _vp, _i, _i, _i, _i, _i, _vp])
 _native.register("pdt_stem_s2d_u8", [_vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _vp])
 _native.register("pdt_stem_conv_supported", [_i, _i, _i, _i, _i])
-_native.register("pdt_stem_conv", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _vp, _native._f, _native._f, _vp, _vp, _vp])
+_native.register("pdt_stem_conv", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, _native._PC, _vp, _vp, _native._f, _native._f, _vp, _vp, _vp])
 _native.register("pdt_dgrad_weight", [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp])
 _native.register("pdt_dgrad_weight_batched", [_vp, _i, _i, _vp])
-_native.register("pdt_conv_fprop_bnstats", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp,
+_native.register("pdt_conv_fprop_bnstats", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _native._PC, _vp, _vp,
                                             _native._f, _native._f, _vp, _vp, _vp])
 
 _native.register("pdt_conv3x3_halo_supported", [_i, _i, _i, _i, _i, _i])
@@ -52,12 +52,12 @@ def _halo_ok(x, w_lp, stride, pad):
     return bool(_native.lib().pdt_conv3x3_halo_supported(_native.dtype_code(x.dtype), N, H, W, C, K))
 
 
-def _halo(x, w_lp, y, scratch=None, rm=None, rv=None, momentum=0.1, eps=1e-5, mean=None, invstd=None, addend=None):
+def _halo(x, w_lp, y, scratch=None, rm=None, rv=None, momentum=0.1, eps=1e-5, mean=None, invstd=None, addend=None, comm=None):
     N, C, H, W = x.shape
     K = w_lp.shape[0]
     _native.check(_native.lib().pdt_conv3x3_halo_add(
         x.data_ptr(), w_lp.data_ptr(), y.data_ptr(), _native.ptr(addend), _native.dtype_code(x.dtype), N, H, W, C, K,
-        _native.ptr(scratch), _native.ptr(rm), _native.ptr(rv), momentum, eps, _native.ptr(mean), _native.ptr(invstd),
+        _native.ptr(scratch), comm, _native.ptr(rm), _native.ptr(rv), momentum, eps, _native.ptr(mean), _native.ptr(invstd),
         _native.stream_ptr(x.device)), "pdt_conv3x3_halo")
     return y
 
@@ -103,8 +103,9 @@ def fprop(x, w_lp, stride, pad, addend=None):
     return y
 
 
-def fprop_bnstats(x, w_lp, stride, pad, running_mean, running_var, momentum, eps):
-    """Convolution whose epilogue also yields the BatchNorm batch statistics of its output."""
+def fprop_bnstats(x, w_lp, stride, pad, running_mean, running_var, momentum, eps, comm=None):
+    """Convolution whose epilogue also yields the BatchNorm batch statistics of its output; with ``comm`` (a native
+    CommDesc, world > 1) the statistics are SyncBatchNorm's: exchanged with the peers inside the kernel."""
     from .bn import _bn_scratch
     N, C, H, W = x.shape
     K, _, R, S = w_lp.shape
@@ -113,11 +114,11 @@ def fprop_bnstats(x, w_lp, stride, pad, running_mean, running_var, momentum, eps
     mean = torch.empty(K, dtype=torch.float32, device=x.device)
     invstd = torch.empty_like(mean)
     if _halo_ok(x, w_lp, stride, pad):
-        _halo(x, w_lp, y, _bn_scratch(x.device, K), running_mean, running_var, momentum, eps, mean, invstd)
+        _halo(x, w_lp, y, _bn_scratch(x.device, K), running_mean, running_var, momentum, eps, mean, invstd, comm=comm)
         return y, mean, invstd
     _native.check(_native.lib().pdt_conv_fprop_bnstats(
         x.data_ptr(), w_lp.data_ptr(), y.data_ptr(), _native.dtype_code(x.dtype), N, H, W, C, K, R, S, stride, pad,
-        _bn_scratch(x.device, K).data_ptr(), _native.ptr(running_mean), _native.ptr(running_var), momentum, eps,
+        _bn_scratch(x.device, K).data_ptr(), comm, _native.ptr(running_mean), _native.ptr(running_var), momentum, eps,
         mean.data_ptr(), invstd.data_ptr(), _native.stream_ptr(x.device)), "pdt_conv_fprop_bnstats")
     return y, mean, invstd
 
@@ -377,7 +378,7 @@ class _ConvNative(torch.autograd.Function):
         ctx.stable_w = arena if (sv is not None and sv.data_ptr() == w_lp.data_ptr()) else None
         if bnpack is None:
             return fprop(x, w_lp, stride[0], padding[0])
-        y, mean, invstd = fprop_bnstats(x, w_lp, stride[0], padding[0], *bnpack)
+        y, mean, invstd = fprop_bnstats(x, w_lp, stride[0], padding[0], *bnpack)      # bnpack may carry a 5th item: comm
         ctx.mark_non_differentiable(mean, invstd)
         return y, mean, invstd
 
@@ -528,17 +529,18 @@ class _StemNative(torch.autograd.Function):
             stats = None
             if bnpack is not None:
                 from .bn import _bn_scratch
-                rm, rv, momentum, eps = bnpack
+                rm, rv, momentum, eps = bnpack[:4]
+                comm = bnpack[4] if len(bnpack) > 4 else None
                 mean = torch.empty(K, dtype=torch.float32, device=x.device)
                 invstd = torch.empty_like(mean)
                 stats = (mean, invstd)
                 _native.check(lib.pdt_stem_conv(xs.data_ptr(), wp.data_ptr(), y.data_ptr(), _native.dtype_code(lp), N, HP, WP, K,
-                                                _bn_scratch(x.device, K).data_ptr(), _native.ptr(rm), _native.ptr(rv),
+                                                _bn_scratch(x.device, K).data_ptr(), comm, _native.ptr(rm), _native.ptr(rv),
                                                 momentum, eps, mean.data_ptr(), invstd.data_ptr(),
                                                 _native.stream_ptr(x.device)), "pdt_stem_conv")
             else:
                 _native.check(lib.pdt_stem_conv(xs.data_ptr(), wp.data_ptr(), y.data_ptr(), _native.dtype_code(lp), N, HP, WP, K,
-                                                None, None, None, 0.1, 1e-5, None, None, _native.stream_ptr(x.device)),
+                                                None, None, None, None, 0.1, 1e-5, None, None, _native.stream_ptr(x.device)),
                               "pdt_stem_conv")
             if stats is not None:
                 ctx.save_for_backward(xs)

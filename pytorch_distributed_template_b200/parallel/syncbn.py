@@ -8,6 +8,8 @@ with all peers over NVLink from inside the kernel (``csrc/bn.cu``) — the
 reference's 20 all_gathers + 20 all_reduces + 20 host syncs per step are gone.
 In eval it is plain BatchNorm on running statistics, like torch.
 """
+import os
+
 import torch
 import torch.distributed as dist
 import torch.nn as nn
@@ -81,18 +83,35 @@ def fused_bn_relu_maxpool(bn, x, kernel_size=3, stride=2, padding=1):
     return ops.bn_relu_maxpool(x, bn, kernel_size, stride, padding)
 
 
-def fused_conv_bn_relu_maxpool(conv, bn, x, kernel_size=3, stride=2, padding=1):
-    """Stem ``maxpool(relu(bn(conv(x))))`` (SyncBN aware): plain BatchNorm takes its statistics from the stem
-    convolution's epilogue, SyncBatchNorm from its own exchanging statistics kernel."""
+def _native_comm(bn, x):
+    """The fabric descriptor for a training SyncBatchNorm on the native NVLink path, else None."""
     if isinstance(bn, SyncBatchNorm) and bn.training:
-        return fused_bn_relu_maxpool(bn, ops.conv2d(x, conv), kernel_size, stride, padding)
+        fabric = bn._pdt_fabric
+        if fabric is not None and fabric.native and fabric.world > 1 and x.is_cuda:
+            return fabric.comm
+    return None
+
+
+def fused_conv_bn_relu_maxpool(conv, bn, x, kernel_size=3, stride=2, padding=1):
+    """Stem ``maxpool(relu(bn(conv(x))))`` (SyncBN aware).  The batch statistics come out of the stem convolution's
+    epilogue; for a SyncBatchNorm on the native fabric the kernel's last CTA also exchanges them with the peers.
+    (A SyncBatchNorm over a torch process group keeps its own statistics pass.)"""
+    if isinstance(bn, SyncBatchNorm) and bn.training:
+        comm = _native_comm(bn, x)
+        if comm is None or os.environ.get("PDT_SYNCBN_EPILOGUE", "1") != "1":
+            return fused_bn_relu_maxpool(bn, ops.conv2d(x, conv), kernel_size, stride, padding)
+        return ops.conv_bn_relu_maxpool(x, conv, bn, kernel_size, stride, padding, comm=comm)
     return ops.conv_bn_relu_maxpool(x, conv, bn, kernel_size, stride, padding)
 
 
 def fused_conv_bn(conv, bn, x, residual=None, relu=False, consume=None, produce=None, res_link=None):
     """``relu?(bn(conv(x)) + residual?)`` (SyncBN aware): plain BatchNorm gets its statistics from the
-    convolution's epilogue, SyncBatchNorm from its own exchanging statistics kernel.
+    convolution's epilogue, a SyncBatchNorm on the native fabric too — the convolution's last CTA exchanges the
+    moments with the peers (PDT_SYNCBN_EPILOGUE=0: its own exchanging statistics kernel).
     consume / produce / res_link: the block's shortcut-gradient link (ops.conv_native.GradLink)."""
     if isinstance(bn, SyncBatchNorm) and bn.training:
-        return fused_bn(bn, ops.conv2d(x, conv, consume=consume, produce=produce), residual, relu, res_link=res_link)
+        comm = _native_comm(bn, x)
+        if comm is None or os.environ.get("PDT_SYNCBN_EPILOGUE", "1") != "1":
+            return fused_bn(bn, ops.conv2d(x, conv, consume=consume, produce=produce), residual, relu, res_link=res_link)
+        return ops.conv_bn_act(x, conv, bn, residual, relu, comm=comm, consume=consume, produce=produce, res_link=res_link)
     return ops.conv_bn_act(x, conv, bn, residual, relu, consume=consume, produce=produce, res_link=res_link)
