@@ -120,16 +120,13 @@ class ResNet(nn.Module):
         if x.dim() == 4 and not (x.is_cuda and amp.active_dtype() is not None) and x.dtype != torch.uint8 \
                 and not x.is_contiguous(memory_format=torch.channels_last):
             x = x.contiguous(memory_format=torch.channels_last)
-        prep = None
         if self.training and torch.is_grad_enabled() and x.is_cuda:
-            prep = ops.prepare_backward(self.conv1.weight)     # data-gradient filter layouts of every conv: one launch, side stream
+            ops.prepare_backward(self.conv1.weight)     # data-gradient filter layouts of every conv, one launch
         with _bn_ops.batched_counters():       # one launch for all num_batches_tracked increments
             x = fused_conv_bn_relu_maxpool(self.conv1, self.bn1, x, 3, 2, 1)
             x = self.layer4(self.layer3(self.layer2(self.layer1(x))))
         x = ops.global_avg_pool(x)
-        x = ops.linear(x, self.fc)
-        ops.join_backward_preparation(prep)             # backward may start after this point
-        return x
+        return ops.linear(x, self.fc)
 
 
 _CFG = {"resnet18": (BasicBlock, [2, 2, 2, 2]), "resnet34": (BasicBlock, [3, 4, 6, 3]),

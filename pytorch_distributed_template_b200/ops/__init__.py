@@ -12,13 +12,7 @@ def prepare_backward(param):
     from . import _native
     arena = getattr(param, "_pdt_arena", None)
     if arena is not None and _native.available():
-        return conv_native.prepare_dgrad_weights(arena)
-    return None
-
-
-def join_backward_preparation(handle):
-    """Make the current stream wait for what ``prepare_backward`` started on its side stream (end of the forward)."""
-    conv_native.join_dgrad_weights(handle)
+        conv_native.prepare_dgrad_weights(arena)
 
 
 __all__ = ["bn_act", "bn_relu_maxpool", "conv_bn_act", "conv_bn_relu_maxpool", "conv2d", "linear", "CrossEntropyLoss", "cross_entropy_with_accuracy",

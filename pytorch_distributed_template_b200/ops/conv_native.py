@@ -206,8 +206,6 @@ class _DgradPlan:
         self.total_tiles = 0
         self.fresh = False
         self.version = -1          # ParamArena.weights_version the buffers were made from
-        self.side = None           # stream the per-step re-layout runs on
-        self.event = None
 
     def lookup(self, w_lp, rs, ss, version=None):
         K, C, R, S = w_lp.shape
@@ -245,23 +243,10 @@ class _DgradPlan:
             self.table = host.to(self.device)
             self.table_jobs = len(self.order)
             self.total_tiles = tiles
-        # The layouts are needed by backward only: the launch goes to a side stream and overlaps the forward pass
-        # (54 us per step otherwise in front of the stem); `join()` at the end of the forward makes the main stream wait.
-        main = torch.cuda.current_stream(self.device)
-        if self.side is None:
-            self.side = torch.cuda.Stream(self.device)
-        self.side.wait_stream(main)                  # the optimizer's weights are final on the main stream
-        with _native.guard(self.device), torch.cuda.stream(self.side):
+        with _native.guard(self.device):
             _native.check(_native.lib().pdt_dgrad_weight_batched(self.table.data_ptr(), self.table_jobs, self.total_tiles,
-                                                                 self.side.cuda_stream), "pdt_dgrad_weight_batched")
-            self.event = torch.cuda.Event()
-            self.event.record(self.side)
+                                                                 _native.stream_ptr(self.device)), "pdt_dgrad_weight_batched")
         self.fresh = True
-
-    def join(self):
-        if self.event is not None:
-            torch.cuda.current_stream(self.device).wait_event(self.event)
-            self.event = None
 
 
 def prepare_dgrad_weights(arena):
@@ -270,13 +255,6 @@ def prepare_dgrad_weights(arena):
     plan = getattr(arena, "_dgrad_plan", None)
     if plan is not None:
         plan.prepare(getattr(arena, "weights_version", None))
-    return plan
-
-
-def join_dgrad_weights(plan):
-    """The current stream waits for the re-layout started by ``prepare_dgrad_weights`` (call before backward can start)."""
-    if plan is not None:
-        plan.join()
 
 
 def dgrad_weight(w_lp, rs, ss, stable=None):
