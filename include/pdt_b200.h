@@ -34,7 +34,7 @@ extern "C" {
 #define PDT_E_TOO_LARGE (-3)     /* size beyond a documented fixed limit */
 
 /* ---- fabric pad layout (one pad per rank, peer-mapped) ------------------- */
-#define PDT_COMM_CHANNELS 4            /* 0: gradient stream, 1: main stream, 2-3: spare */
+#define PDT_COMM_CHANNELS 4            /* 0: gradient stream, 1: main stream (metrics, broadcasts), 2: SyncBatchNorm exchanges, 3: spare */
 #define PDT_COMM_MAX_BLOCKS 256
 #define PDT_SCRATCH_FLOATS 8192        /* per (channel, source rank) */
 #define PDT_PAD_INF_OFFSET_WORDS (PDT_COMM_CHANNELS * PDT_COMM_MAX_BLOCKS * PDT_MAX_RANKS)

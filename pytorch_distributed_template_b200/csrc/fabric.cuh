@@ -97,9 +97,24 @@ __device__ __forceinline__ void block_barrier_t(const Comm& c, int channel, int 
 // (torch/nn/modules/_functions.py:74-76, 159-164) as an in-kernel exchange.
 template <class Sync>
 __device__ __forceinline__ void exchange_sum_t(const Comm& c, double* tot, int n, double* count, int tid, int nthr, Sync sync) {
-  const int ch = 1;
+  // Channel 2 belongs to these exchanges alone (flags and scratch).  Two alternating slot sets make ONE cross-GPU
+  // barrier per exchange enough: a rank can write exchange k+1 into the other set as soon as it has passed barrier
+  // k, and it can only reach exchange k+2 (the same set again) after every peer has signalled barrier k+1, i.e.
+  // after every peer has finished reading set k.  The parity comes from a per-rank call counter in this rank's own
+  // pad (last word of its slot), which survives graph replays; all ranks run the same sequence of exchanges.
+  constexpr int ch = 2;
+  constexpr int kHalf = PDT_SCRATCH_FLOATS / 2;
+  __shared__ int s_parity;
+  if (tid == 0) {
+    uint32_t* ctr = reinterpret_cast<uint32_t*>(scratch_addr(c.pad[c.rank], ch, c.rank)) + (PDT_SCRATCH_FLOATS - 1);
+    const uint32_t k = *ctr;
+    *ctr = k + 1;
+    s_parity = (int)(k & 1u);
+  }
+  sync();
+  const int off = s_parity * kHalf;
   if (c.pad_mc != nullptr) {
-    float* slot = scratch_addr(c.pad_mc, ch, c.rank);
+    float* slot = scratch_addr(c.pad_mc, ch, c.rank) + off;
     for (int i4 = tid * 4; i4 <= n; i4 += nthr * 4) {
       float v[4];
 #pragma unroll
@@ -112,17 +127,17 @@ __device__ __forceinline__ void exchange_sum_t(const Comm& c, double* tot, int n
   } else {
     for (int i = tid; i <= n; i += nthr) {
       const float v = (i < n) ? (float)tot[i] : (float)*count;
-      for (int q = 0; q < c.world; ++q) scratch_addr(c.pad[q], ch, c.rank)[i] = v;
+      for (int q = 0; q < c.world; ++q) (scratch_addr(c.pad[q], ch, c.rank) + off)[i] = v;
     }
   }
   __threadfence_system();
   block_barrier_t(c, ch, 0, tid, sync);
   for (int i = tid; i <= n; i += nthr) {
     double a = 0.0;
-    for (int p = 0; p < c.world; ++p) a += (double)*reinterpret_cast<volatile float*>(scratch_addr(c.pad[c.rank], ch, p) + i);
+    for (int p = 0; p < c.world; ++p) a += (double)*reinterpret_cast<volatile float*>(scratch_addr(c.pad[c.rank], ch, p) + off + i);
     if (i < n) tot[i] = a; else *count = a;
   }
-  block_barrier_t(c, ch, 0, tid, sync);
+  sync();
 }
 
 __host__ inline uint64_t spin_timeout_ns() {
