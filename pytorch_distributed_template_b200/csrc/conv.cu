@@ -469,25 +469,30 @@ struct WgradGeom {
   int splits, steps_per_split;
 };
 
-template <int BN, typename T> struct WCfg {
+template <int BN, typename T, bool PAIR = false> struct WCfg {
   static constexpr int kRow = Elem<T>::kRow;             // channels per 128-byte block row: 64 (16 bit) / 32 (tf32)
   static constexpr int kPix = 4 * Elem<T>::kUK;          // pixels per k-step (4 MMAs): 64 / 32
   static constexpr int kBlkBytes = kPix * 128;           // one [kPix pixel][128 byte] block
   static constexpr int kABlocks = 128 / kRow;            // blocks forming the M = 128 side
   static constexpr int kBBlocks = BN / kRow;
+  static constexpr int kBLocal = PAIR ? kBBlocks / 2 : kBBlocks;     // dy blocks held by ONE CTA (a pair splits the N side)
   static constexpr int kStageBytesA = kABlocks * kBlkBytes;
-  static constexpr int kStageBytesB = kBBlocks * kBlkBytes;
+  static constexpr int kStageBytesB = kBLocal * kBlkBytes;
   static constexpr int kStageBytes = kStageBytesA + kStageBytesB;
-  static constexpr int kStages = (BN >= 256) ? 4 : (BN >= 128 ? 6 : 8);
+  static constexpr int kStages = PAIR ? (BN >= 256 ? 6 : 8) : ((BN >= 256) ? 4 : (BN >= 128 ? 6 : 8));
   static constexpr int kTmemCols = 2 * BN;
   static constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256;
 };
 
-template <int BN, typename T>
+// PAIR: clusters of two CTAs run ONE M = 256 tcgen05.mma.cta_group::2 per k-step: the pair takes two adjacent
+// (r,s,c) tiles of the same output-channel tile and pixel split; each CTA loads its own x blocks and HALF of the
+// dy blocks (the N side), completing on the leader's barrier — the same scheme as k_conv_igemm<.., PAIR>.
+template <int BN, typename T, bool PAIR = false>
 __global__ void __launch_bounds__(kThreads, 1)
 k_conv_wgrad(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmDY, float* __restrict__ dw,
              float* __restrict__ part, const WgradGeom wg) {
-  using C = WCfg<BN, T>;
+  using C = WCfg<BN, T, PAIR>;
+  static_assert(!PAIR || WCfg<BN, T, false>::kBBlocks % 2 == 0, "a pair splits the dy blocks in halves");
   constexpr int kRow = C::kRow, BKP = C::kPix, kBlkBytes = C::kBlkBytes, kAB = C::kABlocks;
   const ConvGeom& g = wg.c;
   extern __shared__ uint8_t smem_raw[];
@@ -502,19 +507,26 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int items = wg.m_tiles * wg.n_tiles * wg.splits;
+  // PAIR: a work item is (pair of adjacent M tiles, N tile, pixel split) and belongs to a cluster of two CTAs;
+  // CTA `crank` of the cluster owns M tile 2 * pair + crank (past the end for the last odd one: computed, never stored).
+  const int crank = PAIR ? (int)cluster_ctarank() : 0;
+  const int first_item = PAIR ? (int)blockIdx.x / 2 : (int)blockIdx.x;
+  const int item_step = PAIR ? (int)gridDim.x / 2 : (int)gridDim.x;
+  const int m_groups = PAIR ? (wg.m_tiles + 1) / 2 : wg.m_tiles;
+  const int items = m_groups * wg.n_tiles * wg.splits;
   const int c_chunks = g.C / kRow;
   const int m_blocks = wg.rsc / kRow;   // wgrad needs C % kRow == 0: an (r,s,c) block never straddles two taps
 
   if (warp == 0 && lane == 0) { prefetch_tmap(&tmX); prefetch_tmap(&tmDY); }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < C::kStages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 4); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], PAIR ? 8 : 4); }
     fence_barrier_init();
   }
-  if (warp == 2) tmem_alloc(tmem_slot, C::kTmemCols);
+  if (warp == 2) { if constexpr (PAIR) tmem_alloc_pair(tmem_slot, C::kTmemCols); else tmem_alloc(tmem_slot, C::kTmemCols); }
   tc_fence_before();
   __syncthreads();
+  if constexpr (PAIR) cluster_sync_all();      // the peer's barriers exist before anything is signalled at them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   pdl_enter();
@@ -523,14 +535,19 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
     {
       int stage = 0;
       uint32_t phase = 0;
-      for (int item = blockIdx.x; item < items; item += gridDim.x) {
+      for (int item = first_item; item < items; item += item_step) {
         const int sp = item % wg.splits;
         const int tile = item / wg.splits;
-        const int mt = tile / wg.n_tiles, nt = tile % wg.n_tiles;
+        const int mt = PAIR ? (tile / wg.n_tiles) * 2 + crank : tile / wg.n_tiles, nt = tile % wg.n_tiles;
         const int ks0 = sp * wg.steps_per_split;
         const int ks1 = min(wg.k_steps, ks0 + wg.steps_per_split);
-        const int nA = min(kAB, m_blocks - mt * kAB);
+        const int nA = max(0, min(kAB, m_blocks - mt * kAB));
         const int nB = min(C::kBBlocks, (g.K - nt * BN + kRow - 1) / kRow);
+        // PAIR: this CTA loads dy blocks [jb0, jb1) of the N tile into its own ring slot; the leader expects the
+        // bytes of both CTAs (its peer's M tile may be short or absent)
+        const int jb0 = PAIR ? min(nB, crank * C::kBLocal) : 0;
+        const int jb1 = PAIR ? min(nB, (crank + 1) * C::kBLocal) : nB;
+        const int nA_peer = PAIR ? max(0, min(kAB, m_blocks - (mt ^ 1) * kAB)) : 0;
         int tapr[kAB], taps[kAB], cc[kAB];
         for (int b = 0; b < kAB; ++b) {
           const int gb = min(mt * kAB + b, m_blocks - 1);
@@ -546,7 +563,19 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
           const int p0 = rem / g.Q, q0 = rem - p0 * g.Q;
           const int cw = q0 * g.stride - g.pad_w, ch = p0 * g.stride - g.pad_h;
           mbar_wait(&empty[stage], phase ^ 1);
-          if (elect_one_sync()) {
+          if constexpr (PAIR) {
+            if (elect_one_sync()) {
+              const uint32_t lead_full = mapa_cluster(smem_u32(&full[stage]), 0);
+              if (crank == 0) mbar_expect_tx(&full[stage], (uint32_t)(nA + nA_peer + nB) * kBlkBytes);
+#pragma unroll
+              for (int b = 0; b < kAB; ++b)
+                if (b < nA)
+                  tma_load_im2col_4d_pair(smA + stage * C::kStageBytesA + b * kBlkBytes, &tmX, lead_full, cc[b] * kRow, cw, ch, img,
+                                          (uint16_t)(taps[b] * g.dil_w), (uint16_t)tapr[b]);
+              for (int j = jb0; j < jb1; ++j)
+                tma_load_2d_pair(smB + stage * C::kStageBytesB + (j - jb0) * kBlkBytes, &tmDY, lead_full, nt * BN + j * kRow, m0);
+            }
+          } else if (elect_one_sync()) {
             mbar_expect_tx(&full[stage], (uint32_t)(nA + nB) * kBlkBytes);
 #pragma unroll
             for (int b = 0; b < kAB; ++b)
@@ -561,13 +590,13 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
         }
       }
     }
-  } else if (warp == 1) {
+  } else if (warp == 1 && (!PAIR || crank == 0)) {
     {
-      constexpr uint32_t idesc = make_idesc(128, BN, Elem<T>::kFmt, 1, 1);
+      constexpr uint32_t idesc = make_idesc(PAIR ? 256 : 128, BN, Elem<T>::kFmt, 1, 1);
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
-      for (int item = blockIdx.x; item < items; item += gridDim.x, ++it) {
+      for (int item = first_item; item < items; item += item_step, ++it) {
         const int sp = item % wg.splits;
         const int ks0 = sp * wg.steps_per_split;
         const int ks1 = min(wg.k_steps, ks0 + wg.steps_per_split);
@@ -586,23 +615,27 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
           const uint64_t db = make_sw128_desc(smem_u32(smB + stage * C::kStageBytesB), kSbo, kBlkBytes, kLayout);
           if (elect_one_sync()) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k)   // UMMA_K pixels = kUK * 128 bytes per step, in (addr >> 4) units
-              umma<T>(tmem_d, da + (Elem<T>::kUK * 8) * k, db + (Elem<T>::kUK * 8) * k, idesc, (ks > ks0 || k > 0) ? 1u : 0u);
-            umma_commit(&empty[stage]);
+            for (int k = 0; k < 4; ++k) {  // UMMA_K pixels = kUK * 128 bytes per step, in (addr >> 4) units
+              if constexpr (PAIR)
+                umma_pair<T>(tmem_d, da + (Elem<T>::kUK * 8) * k, db + (Elem<T>::kUK * 8) * k, idesc, (ks > ks0 || k > 0) ? 1u : 0u);
+              else
+                umma<T>(tmem_d, da + (Elem<T>::kUK * 8) * k, db + (Elem<T>::kUK * 8) * k, idesc, (ks > ks0 || k > 0) ? 1u : 0u);
+            }
+            if constexpr (PAIR) umma_commit_pair(&empty[stage], (uint16_t)3); else umma_commit(&empty[stage]);
           }
           __syncwarp();
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
         }
-        if (elect_one_sync()) umma_commit(&tfull[acc]);
+        if (elect_one_sync()) { if constexpr (PAIR) umma_commit_pair(&tfull[acc], (uint16_t)3); else umma_commit(&tfull[acc]); }
         __syncwarp();
       }
     }
   } else if (warp >= 4) {
     const int quarter = warp & 3;
     int it = 0;
-    for (int item = blockIdx.x; item < items; item += gridDim.x, ++it) {
+    for (int item = first_item; item < items; item += item_step, ++it) {
       const int tile = item / wg.splits;
-      const int mt = tile / wg.n_tiles, nt = tile % wg.n_tiles;
+      const int mt = PAIR ? (tile / wg.n_tiles) * 2 + crank : tile / wg.n_tiles, nt = tile % wg.n_tiles;
       const int sp = item % wg.splits;
       const bool nonempty = sp * wg.steps_per_split < wg.k_steps;
       const int acc = it & 1;
@@ -637,15 +670,19 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty[acc]);
+      if (lane == 0) {
+        if constexpr (PAIR) mbar_arrive_cluster(mapa_cluster(smem_u32(&tempty[acc]), 0));
+        else mbar_arrive(&tempty[acc]);
+      }
     }
   }
 
   tc_fence_before();
   __syncthreads();
+  if constexpr (PAIR) cluster_sync_all();      // no CTA leaves while its peer may still signal its barriers / write its TMEM
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, C::kTmemCols);
+    if constexpr (PAIR) tmem_dealloc_pair(tmem_base, C::kTmemCols); else tmem_dealloc(tmem_base, C::kTmemCols);
   }
 }
 
@@ -850,8 +887,36 @@ int launch_wgrad(const void* x, const void* dy, float* dw, int dtype, WgradGeom&
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  const int tiles = wg.m_tiles * wg.n_tiles;
-  int splits = sms / tiles;                                   // one wave: never more work items than SMs
+  // CTA pairs (one M = 256 cta_group::2 MMA over two adjacent (r,s,c) tiles): PDT_WGRAD_PAIR=0 keeps single CTAs
+  // (measured per launch at 1200 images: BN = 256 tiles +12 %, BN = 128 tiles -2.5 %: only the wide tiles pair up)
+  bool pair = false;
+  if constexpr (BN >= 256) {
+    static int env = -1;
+    if (env < 0) { const char* e = getenv("PDT_WGRAD_PAIR"); env = (e != nullptr && e[0] == '0') ? 0 : 1; }
+    pair = env == 1 && wg.m_tiles >= 2;
+  }
+  int units = sms;                                            // co-resident work units: CTAs, or clusters of two
+  if (pair) {
+    static int cached = -1;                                   // clusters of 2 that fit at once (GPC boundaries decide)
+    if (cached < 0) {
+      int n = 0;
+      if constexpr (BN >= 256) {
+        auto kern = k_conv_wgrad<BN, __half, true>;
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, WCfg<BN, __half, true>::kSmemBytes);
+        cudaLaunchConfig_t q = {};
+        cudaLaunchAttribute qa[1];
+        qa[0].id = cudaLaunchAttributeClusterDimension;
+        qa[0].val.clusterDim.x = 2; qa[0].val.clusterDim.y = 1; qa[0].val.clusterDim.z = 1;
+        q.gridDim = dim3(sms / 2 * 2); q.blockDim = dim3(kThreads);
+        q.dynamicSmemBytes = WCfg<BN, __half, true>::kSmemBytes; q.attrs = qa; q.numAttrs = 1;
+        if (cudaOccupancyMaxActiveClusters(&n, kern, &q) != cudaSuccess || n < 1) { cudaGetLastError(); n = sms / 4; }
+      }
+      cached = n < sms / 2 ? n : sms / 2;
+    }
+    units = cached;
+  }
+  const int tiles = (pair ? (wg.m_tiles + 1) / 2 : wg.m_tiles) * wg.n_tiles;
+  int splits = units / tiles;                                 // one wave: never more work items than resident units
   if (splits > wg.k_steps) splits = wg.k_steps;
   if (splits < 1) splits = 1;
   wg.steps_per_split = (wg.k_steps + splits - 1) / splits;
@@ -874,20 +939,37 @@ int launch_wgrad(const void* x, const void* dy, float* dw, int dtype, WgradGeom&
     }
   }
   const int items = tiles * wg.splits;
-  const int grid = items < sms ? items : sms;
-  if (dtype == PDT_FP16) {
-    auto kern = k_conv_wgrad<BN, __half>;
-    PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-    PDT_CHECK(launch_pdl(kern, dim3(grid), dim3(kThreads), smem_bytes, stream, tmX, tmDY, dw, part, wg));
-  } else if (dtype == PDT_FP32) {
-    auto kern = k_conv_wgrad<BN, float>;
-    PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-    PDT_CHECK(launch_pdl(kern, dim3(grid), dim3(kThreads), smem_bytes, stream, tmX, tmDY, dw, part, wg));
-  } else {
-    auto kern = k_conv_wgrad<BN, __nv_bfloat16>;
-    PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-    PDT_CHECK(launch_pdl(kern, dim3(grid), dim3(kThreads), smem_bytes, stream, tmX, tmDY, dw, part, wg));
+  const int grid = (items < units ? items : units) * (pair ? 2 : 1);
+  auto go = [&](auto kern, int smem) -> int {
+    PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    if (!pair) {
+      PDT_CHECK(launch_pdl(kern, dim3(grid), dim3(kThreads), smem, stream, tmX, tmDY, dw, part, wg));
+      return 0;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    int nattr = 1 + pdl_attr(attr + 1);
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(kThreads); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+    cfg.attrs = attr; cfg.numAttrs = nattr;
+    PDT_CHECK(cudaLaunchKernelEx(&cfg, kern, tmX, tmDY, dw, part, wg));
+    return 0;
+  };
+  int rc = 0;
+  if constexpr (BN >= 256) {
+    if (pair) {
+      if (dtype == PDT_FP16) rc = go(k_conv_wgrad<BN, __half, true>, WCfg<BN, __half, true>::kSmemBytes);
+      else if (dtype == PDT_FP32) rc = go(k_conv_wgrad<BN, float, true>, WCfg<BN, float, true>::kSmemBytes);
+      else rc = go(k_conv_wgrad<BN, __nv_bfloat16, true>, WCfg<BN, __nv_bfloat16, true>::kSmemBytes);
+    }
   }
+  if (!pair) {
+    if (dtype == PDT_FP16) rc = go(k_conv_wgrad<BN, __half>, smem_bytes);
+    else if (dtype == PDT_FP32) rc = go(k_conv_wgrad<BN, float>, smem_bytes);
+    else rc = go(k_conv_wgrad<BN, __nv_bfloat16>, smem_bytes);
+  }
+  if (rc != 0) return rc;
   if (part != nullptr) {
     PDT_CHECK(cudaGetLastError());
     const int fb = (int)((total + 255) / 256 < 1184 ? (total + 255) / 256 : 1184);
