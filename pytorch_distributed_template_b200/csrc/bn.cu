@@ -84,20 +84,12 @@ __device__ __forceinline__ void block_fold(float* smem, const float (&a)[V], con
   }
 }
 
-// Returns true in exactly one block per launch: the one that arrives last.
-__device__ __forceinline__ bool take_last_ticket(unsigned* counter) {
+// Every block calls this after block_fold; true in exactly one block per launch, whose tot[0..n2) (fp64, shared
+// memory) then holds the column sums of all blocks' rows (common.cuh: tree_fold).
+__device__ __forceinline__ bool fold_partials(double* tot, float* partial, unsigned* counter, int n2) {
   __shared__ int s_last;
-  __threadfence();
-  __syncthreads();
-  if (threadIdx.x == 0) s_last = (atomicAdd(counter, 1u) == gridDim.x - 1);
-  __syncthreads();
-  if (s_last) __threadfence();
-  return s_last != 0;
-}
-
-// Last block: tot[i] = sum_b partial[b][i] in fp64, left in smem as double[n2].
-__device__ __forceinline__ void fold_partials(double* tot, const float* __restrict__ partial, int nb, int n2) {
-  fold_rows_f64(tot, partial, nb, n2, (int)threadIdx.x, (int)blockDim.x, [] { __syncthreads(); });
+  return tree_fold(tot, partial, counter, (int)gridDim.x, n2, PDT_BN_MAX_BLOCKS, (int)threadIdx.x, (int)blockDim.x,
+                   [] { __syncthreads(); }, &s_last);
 }
 
 // Cross-rank sum of tot[0..n) (+ the count): the whole block takes part (fabric.cuh: exchange_sum_t).
@@ -107,57 +99,44 @@ __device__ __forceinline__ void exchange_sum(const Comm& c, double* tot, int n, 
 
 // After block_fold: the last block folds every block's row, exchanges with the peers (SyncBN) and writes
 // mean / invstd / running statistics.  `smem` >= 2C doubles + blockDim doubles.
-__device__ __forceinline__ void finish_fwd_stats(float* smem, const float* __restrict__ partial, unsigned* counter, const Comm& comm,
+__device__ __forceinline__ void finish_fwd_stats(float* smem, float* partial, unsigned* counter, const Comm& comm,
                                                  int C, long count, float* running_mean, float* running_var, float momentum,
                                                  float eps, float* __restrict__ save_mean, float* __restrict__ save_invstd) {
   __shared__ double s_count;
   const int tid = threadIdx.x;
-  if (!take_last_ticket(counter)) return;
   double* tot = reinterpret_cast<double*>(smem);
-  fold_partials(tot, partial, gridDim.x, 2 * C);
+  if (!fold_partials(tot, partial, counter, 2 * C)) return;
   if (tid == 0) { s_count = (double)count; *counter = 0; }
   __syncthreads();
   if (comm.world > 1) exchange_sum(comm, tot, 2 * C, &s_count);
   __syncthreads();
-  const double N = s_count;
-  for (int c = tid; c < C; c += blockDim.x) {
-    const double mean = tot[c] / N;
-    double var = tot[C + c] / N - mean * mean;
-    var = var > 0.0 ? var : 0.0;
-    save_mean[c] = (float)mean;
-    save_invstd[c] = (float)(1.0 / sqrt(var + (double)eps));
-    if (running_mean) {
-      const double unbiased = N > 1.0 ? var * N / (N - 1.0) : var;
-      running_mean[c] = (float)((1.0 - momentum) * running_mean[c] + momentum * mean);
-      running_var[c] = (float)((1.0 - momentum) * running_var[c] + momentum * unbiased);
-    }
-  }
+  bn_stats_finalize(tot, C, s_count, eps, momentum, save_mean, save_invstd, running_mean, running_var, tid, (int)blockDim.x);
 }
 
 // Same for the backward reduction: local dgamma / dbeta, then the (optionally cross-rank) k1, k2 vectors.
 // out_k: [2C] floats consumed by the dx pass: k1 = sum_dy / N, k2 = sum_dy_xmu * invstd^2 / N (N global)
-__device__ __forceinline__ void finish_bwd_reduce(float* smem, const float* __restrict__ partial, unsigned* counter, const Comm& comm,
+__device__ __forceinline__ void finish_bwd_reduce(float* smem, float* partial, unsigned* counter, const Comm& comm,
                                                   int C, long count, const float* __restrict__ invstd, float* __restrict__ dgamma,
                                                   float* __restrict__ dbeta, float* __restrict__ out_k) {
   __shared__ double s_count;
   const int tid = threadIdx.x;
-  if (!take_last_ticket(counter)) return;
   double* tot = reinterpret_cast<double*>(smem);
-  fold_partials(tot, partial, gridDim.x, 2 * C);
+  if (!fold_partials(tot, partial, counter, 2 * C)) return;
   if (tid == 0) { s_count = (double)count; *counter = 0; }
   __syncthreads();
   for (int c = tid; c < C; c += blockDim.x) {   // parameter grads stay local: DDP averages them
     dbeta[c] = (float)tot[c];
-    dgamma[c] = (float)(tot[C + c] * (double)invstd[c]);
+    dgamma[c] = (float)tot[C + c] * invstd[c];
   }
   __syncthreads();
   if (comm.world > 1) exchange_sum(comm, tot, 2 * C, &s_count);
   __syncthreads();
-  const double N = s_count;
+  double inv_n = (double)(1.0f / (float)s_count);
+  inv_n = inv_n * (2.0 - s_count * inv_n);                  // fp32 reciprocal + one fp64 Newton step (no fp64 divide sequence)
   for (int c = tid; c < C; c += blockDim.x) {
-    const double is = (double)invstd[c];
-    out_k[c] = (float)(tot[c] / N);
-    out_k[C + c] = (float)(tot[C + c] * is * is / N);
+    const float is = invstd[c];
+    out_k[c] = (float)(tot[c] * inv_n);
+    out_k[C + c] = (float)(tot[C + c] * inv_n) * is * is;
   }
 }
 

@@ -184,8 +184,12 @@ __device__ __forceinline__ void fold_quad(const float* __restrict__ partial, int
       const int bb = b + u * step;
       v[u] = bb < nb ? __ldcg(reinterpret_cast<const float4*>(partial + (size_t)bb * n2) + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
+    // the batch is summed in fp32 (fixed order) and enters the fp64 total once: an F2F + DADD per element ran at
+    // ~21 cycles per warp instruction on B200 and dominated the fold
+    float4 f = v[0];
 #pragma unroll
-    for (int u = 0; u < kB; ++u) { a[0] += (double)v[u].x; a[1] += (double)v[u].y; a[2] += (double)v[u].z; a[3] += (double)v[u].w; }
+    for (int u = 1; u < kB; ++u) { f.x += v[u].x; f.y += v[u].y; f.z += v[u].z; f.w += v[u].w; }
+    a[0] += (double)f.x; a[1] += (double)f.y; a[2] += (double)f.z; a[3] += (double)f.w;
   }
 }
 
@@ -217,6 +221,106 @@ __device__ __forceinline__ void fold_rows_f64(double* tot, const float* __restri
       tot[i] = t;
     }
     sync();
+  }
+}
+
+// ---- two-level fold ------------------------------------------------------------------------------------
+// One SM reads other SMs' rows out of L2 at ~50 GB/s (measured: 148 rows x 2 KB in 6.5 us, 116 x 4 KB in 9.1 us,
+// at the tail of EVERY statistics-producing kernel), so the last CTA must not read them all.  CTAs form groups of
+// ~sqrt(nb) by block index; the last CTA to arrive in a group adds the group's rows (fp32, row order) into a group
+// row, and the last group to finish adds the ~sqrt(nb) group rows in fp64: ~2 sqrt(nb) rows on the critical path
+// instead of nb, still a fixed summation order (deterministic, independent of arrival order).
+//   counters: word 0 = top-level ticket (the CALLER resets it when it is done), words 1.. = group tickets (reset
+//             here); all zero between launches.  The scratch header has 64 words.
+//   partial:  [nb] CTA rows, then room for the group rows: nb + groups <= max_rows, else one level.
+// Every CTA calls this with all `nthr` threads after writing its row; true in exactly one CTA, whose `tot` then
+// holds the column sums (fp64, needs n2 + 4 * nthr doubles like fold_rows_f64).
+template <class Sync>
+__device__ __forceinline__ bool tree_fold(double* tot, float* partial, unsigned* counters, int nb, int n2, int max_rows, int tid,
+                                          int nthr, Sync sync, int* s_flag) {
+  int G = 8;
+  while (G * G < nb) ++G;
+  const int groups = (nb + G - 1) / G;
+  const bool two = nb > 24 && groups <= 62 && nb + groups <= max_rows;
+  __threadfence();                                           // this CTA's row
+  sync();
+  if (!two) {
+    if (tid == 0) *s_flag = (atomicAdd(counters, 1u) == (unsigned)nb - 1u);
+    sync();
+    if (!*s_flag) return false;
+    __threadfence();
+    fold_rows_f64(tot, partial, nb, n2, tid, nthr, sync);
+    return true;
+  }
+  const int grp = (int)blockIdx.x / G, r0 = grp * G, members = min(G, nb - r0);
+  if (tid == 0) {
+    const bool last = atomicAdd(counters + 1 + grp, 1u) == (unsigned)members - 1u;
+    if (last) counters[1 + grp] = 0;                         // nobody else touches it in this launch
+    *s_flag = last;
+  }
+  sync();
+  if (!*s_flag) return false;
+  __threadfence();
+  {
+    const int nc4 = n2 >> 2;
+    float* grow = partial + (size_t)(nb + grp) * n2;
+    for (int c4 = tid; c4 < nc4; c4 += nthr) {
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int b = 0; b < members; b += 16) {
+        float4 v[16];
+#pragma unroll
+        for (int u = 0; u < 16; ++u)
+          v[u] = b + u < members ? __ldcg(reinterpret_cast<const float4*>(partial + (size_t)(r0 + b + u) * n2) + c4)
+                                 : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int u = 0; u < 16; ++u) { a.x += v[u].x; a.y += v[u].y; a.z += v[u].z; a.w += v[u].w; }
+      }
+      reinterpret_cast<float4*>(grow)[c4] = a;
+    }
+  }
+  __threadfence();
+  sync();
+  if (tid == 0) *s_flag = (atomicAdd(counters, 1u) == (unsigned)groups - 1u);
+  sync();
+  if (!*s_flag) return false;
+  __threadfence();
+  fold_rows_f64(tot, partial + (size_t)nb * n2, groups, n2, tid, nthr, sync);
+  return true;
+}
+
+// mean / invstd / running statistics of channels [0, K) from tot = {sums[K], sums of squares[K]} over `cnt` values,
+// by threads tid < nthr of the finalising CTA.  The cancellation E[x^2] - mean^2 stays in fp64 (two multiplies and
+// one FMA per channel; 1 / cnt is an fp32 reciprocal refined by one fp64 Newton step); square root, reciprocal
+// and the running-statistics update are fp32, and the running statistics of a thread's channels are loaded before
+// any is stored (fp64 divide / sqrt sequences and four dependent L2 round trips cost this CTA 2-4 us per launch).
+__device__ __forceinline__ void bn_stats_finalize(const double* tot, int K, double cnt, float eps, float momentum,
+                                                  float* __restrict__ save_mean, float* __restrict__ save_invstd,
+                                                  float* running_mean, float* running_var, int tid, int nthr) {
+  double inv_n = (double)(1.0f / (float)cnt);
+  inv_n = inv_n * (2.0 - cnt * inv_n);
+  const float unbias = cnt > 1.0 ? (float)cnt / ((float)cnt - 1.f) : 1.f;
+  for (int c0 = tid; c0 < K; c0 += 4 * nthr) {
+    float rm[4], rv[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int c = c0 + u * nthr;
+      rm[u] = rv[u] = 0.f;
+      if (running_mean != nullptr && c < K) { rm[u] = running_mean[c]; rv[u] = running_var[c]; }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int c = c0 + u * nthr;
+      if (c < K) {
+        const double mean = tot[c] * inv_n;
+        const float var = fmaxf((float)fma(-mean, mean, tot[K + c] * inv_n), 0.f);
+        save_mean[c] = (float)mean;
+        save_invstd[c] = 1.0f / sqrtf(var + eps);
+        if (running_mean != nullptr) {
+          running_mean[c] = fmaf(momentum, (float)mean - rm[u], rm[u]);
+          running_var[c] = fmaf(momentum, var * unbias - rv[u], rv[u]);
+        }
+      }
+    }
   }
 }
 

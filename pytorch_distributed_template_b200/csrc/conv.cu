@@ -411,31 +411,13 @@ k_conv_igemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         for (int q4 = 0; q4 < 4; ++q4) t += s_stat[q4 * (2 * kStatMaxK + 32 * 33) + which * kStatMaxK + c];
         bs.partial[(size_t)blockIdx.x * 2 * K + i] = t;
       }
-      __threadfence();
-      epi_bar_sync();
-      if (te == 0) s_last = (atomicAdd(bs.counter, 1u) == gridDim.x - 1);
-      epi_bar_sync();
-      if (s_last) {
-        __threadfence();
-        double* tot = reinterpret_cast<double*>(s_stat);      // 2K doubles <= 8 KB of the 16 KB region
-        fold_rows_f64(tot, bs.partial, (int)gridDim.x, 2 * K, te, 128, [] { epi_bar_sync(); });
+      double* tot = reinterpret_cast<double*>(s_stat);        // 2K + 512 doubles <= 12 KB of the 16 KB region
+      if (tree_fold(tot, bs.partial, bs.counter, (int)gridDim.x, 2 * K, PDT_BN_MAX_BLOCKS, te, 128, [] { epi_bar_sync(); }, &s_last)) {
         __shared__ double s_cnt;
         if (te == 0) s_cnt = (double)g.M;
         epi_bar_sync();
         if (bs.comm.world > 1) exchange_sum_t(bs.comm, tot, 2 * K, &s_cnt, te, 128, [] { epi_bar_sync(); });
-        const double n = s_cnt;
-        for (int c = te; c < K; c += 128) {
-          const double mean = tot[c] / n;
-          double var = tot[K + c] / n - mean * mean;
-          var = var > 0.0 ? var : 0.0;
-          bs.save_mean[c] = (float)mean;
-          bs.save_invstd[c] = (float)(1.0 / sqrt(var + (double)bs.eps));
-          if (bs.running_mean != nullptr) {
-            const double unbiased = n > 1.0 ? var * n / (n - 1.0) : var;
-            bs.running_mean[c] = (float)((1.0 - bs.momentum) * bs.running_mean[c] + bs.momentum * mean);
-            bs.running_var[c] = (float)((1.0 - bs.momentum) * bs.running_var[c] + bs.momentum * unbiased);
-          }
-        }
+        bn_stats_finalize(tot, K, s_cnt, bs.eps, bs.momentum, bs.save_mean, bs.save_invstd, bs.running_mean, bs.running_var, te, 128);
         if (te == 0) *bs.counter = 0;
       }
     }

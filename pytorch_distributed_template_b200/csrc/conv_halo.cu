@@ -519,31 +519,13 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         for (int w8 = 0; w8 < kEpiWarps; ++w8) t += s_stat[w8 * C::kStatStride + which * kStatMaxK + c];
         bs.partial[(size_t)blockIdx.x * 2 * K + i] = t;
       }
-      __threadfence();
-      epi_bar_sync();
-      if (te == 0) s_last = (atomicAdd(bs.counter, 1u) == gridDim.x - 1);
-      epi_bar_sync();
-      if (s_last) {
-        __threadfence();
-        double* tot = reinterpret_cast<double*>(s_stat);
-        fold_rows_f64(tot, bs.partial, (int)gridDim.x, 2 * K, te, 256, [] { epi_bar_sync(); });
+      double* tot = reinterpret_cast<double*>(s_stat);
+      if (tree_fold(tot, bs.partial, bs.counter, (int)gridDim.x, 2 * K, PDT_BN_MAX_BLOCKS, te, 256, [] { epi_bar_sync(); }, &s_last)) {
         __shared__ double s_cnt;
         if (te == 0) s_cnt = (double)bs.count;
         epi_bar_sync();
         if (bs.comm.world > 1) exchange_sum_t(bs.comm, tot, 2 * K, &s_cnt, te, 256, [] { epi_bar_sync(); });
-        const double cnt = s_cnt;
-        for (int c = te; c < K; c += 256) {
-          const double mean = tot[c] / cnt;
-          double var = tot[K + c] / cnt - mean * mean;
-          var = var > 0.0 ? var : 0.0;
-          bs.save_mean[c] = (float)mean;
-          bs.save_invstd[c] = (float)(1.0 / sqrt(var + (double)bs.eps));
-          if (bs.running_mean != nullptr) {
-            const double unbiased = cnt > 1.0 ? var * cnt / (cnt - 1.0) : var;
-            bs.running_mean[c] = (float)((1.0 - bs.momentum) * bs.running_mean[c] + bs.momentum * mean);
-            bs.running_var[c] = (float)((1.0 - bs.momentum) * bs.running_var[c] + bs.momentum * unbiased);
-          }
-        }
+        bn_stats_finalize(tot, K, s_cnt, bs.eps, bs.momentum, bs.save_mean, bs.save_invstd, bs.running_mean, bs.running_var, te, 256);
         if (te == 0) *bs.counter = 0;
       }
     }
@@ -905,31 +887,13 @@ k_stem_conv(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUt
         for (int w8 = 0; w8 < kEpiWarps; ++w8) t += s_stat[w8 * (2 * kStatMaxK) + which * kStatMaxK + c];
         bs.partial[(size_t)blockIdx.x * 2 * K + i] = t;
       }
-      __threadfence();
-      epi_bar_sync();
-      if (te == 0) s_last = (atomicAdd(bs.counter, 1u) == gridDim.x - 1);
-      epi_bar_sync();
-      if (s_last) {
-        __threadfence();
-        double* tot = reinterpret_cast<double*>(s_stat);
-        fold_rows_f64(tot, bs.partial, (int)gridDim.x, 2 * K, te, 256, [] { epi_bar_sync(); });
+      double* tot = reinterpret_cast<double*>(s_stat);
+      if (tree_fold(tot, bs.partial, bs.counter, (int)gridDim.x, 2 * K, PDT_BN_MAX_BLOCKS, te, 256, [] { epi_bar_sync(); }, &s_last)) {
         __shared__ double s_cnt;
         if (te == 0) s_cnt = (double)bs.count;
         epi_bar_sync();
         if (bs.comm.world > 1) exchange_sum_t(bs.comm, tot, 2 * K, &s_cnt, te, 256, [] { epi_bar_sync(); });
-        const double cnt = s_cnt;
-        for (int c = te; c < K; c += 256) {
-          const double mean = tot[c] / cnt;
-          double var = tot[K + c] / cnt - mean * mean;
-          var = var > 0.0 ? var : 0.0;
-          bs.save_mean[c] = (float)mean;
-          bs.save_invstd[c] = (float)(1.0 / sqrt(var + (double)bs.eps));
-          if (bs.running_mean != nullptr) {
-            const double unbiased = cnt > 1.0 ? var * cnt / (cnt - 1.0) : var;
-            bs.running_mean[c] = (float)((1.0 - bs.momentum) * bs.running_mean[c] + bs.momentum * mean);
-            bs.running_var[c] = (float)((1.0 - bs.momentum) * bs.running_var[c] + bs.momentum * unbiased);
-          }
-        }
+        bn_stats_finalize(tot, K, s_cnt, bs.eps, bs.momentum, bs.save_mean, bs.save_invstd, bs.running_mean, bs.running_var, te, 256);
         if (te == 0) *bs.counter = 0;
       }
     }

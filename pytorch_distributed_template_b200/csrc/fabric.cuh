@@ -132,10 +132,17 @@ __device__ __forceinline__ void exchange_sum_t(const Comm& c, double* tot, int n
   }
   __threadfence_system();
   block_barrier_t(c, ch, 0, tid, sync);
+  // (the per-rank values are fp32 already: summed in fp32 in rank order; only the count, which may pass 2^24, in fp64)
   for (int i = tid; i <= n; i += nthr) {
-    double a = 0.0;
-    for (int p = 0; p < c.world; ++p) a += (double)*reinterpret_cast<volatile float*>(scratch_addr(c.pad[c.rank], ch, p) + off + i);
-    if (i < n) tot[i] = a; else *count = a;
+    if (i < n) {
+      float a = 0.f;
+      for (int p = 0; p < c.world; ++p) a += *reinterpret_cast<volatile float*>(scratch_addr(c.pad[c.rank], ch, p) + off + i);
+      tot[i] = (double)a;
+    } else {
+      double a = 0.0;
+      for (int p = 0; p < c.world; ++p) a += (double)*reinterpret_cast<volatile float*>(scratch_addr(c.pad[c.rank], ch, p) + off + i);
+      *count = a;
+    }
   }
   sync();
 }

@@ -26,5 +26,22 @@ def main(path, top=40):
         print("{:9.1f} us {:5.1f}% x{:<4d} {}".format(us, 100 * us / total, n, name))
 
 
+def listing(path):
+    """Every launch in order: time, grid, kernel (for finding the launches that scale badly with batch size)."""
+    with open(path, newline="") as f:
+        lines = [l for l in f if l.startswith('"')]
+    for r in csv.DictReader(lines):
+        if r.get("Metric Name") != "gpu__time_duration.sum":
+            continue
+        val = float(r["Metric Value"].replace(",", ""))
+        unit = r.get("Metric Unit", "ns")
+        us = val / 1e3 if unit in ("ns", "nsecond") else (val if unit in ("us", "usecond") else val * 1e3)
+        print("{:4s} {:8.1f} us  grid {:>16s}  {}".format(r["ID"], us, r.get("Grid Size", "").replace(" ", ""),
+                                                       re.sub(r"\(.*", "", r["Kernel Name"])[:80]))
+
+
 if __name__ == "__main__":
-    main(sys.argv[1], int(sys.argv[2]) if len(sys.argv) > 2 else 40)
+    if len(sys.argv) > 2 and sys.argv[2] == "list":
+        listing(sys.argv[1])
+    else:
+        main(sys.argv[1], int(sys.argv[2]) if len(sys.argv) > 2 else 40)
