@@ -32,6 +32,9 @@ using namespace pdt::tc;
 constexpr int kThreads = 384;       // warps: 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4..11 epilogue
 constexpr int kEpiWarps = 8;        // two warps per TMEM lane quarter, each draining half of the columns
 constexpr int kStatMaxK = 128;
+#ifndef PDT_HALO64_CHAINS
+#define PDT_HALO64_CHAINS 3      // (4 measured 3 % slower: the chains are not the limit)
+#endif
 
 struct HaloGeom {
   int N, H, W, C, K;
@@ -66,7 +69,7 @@ template <int BN, bool RES> struct HCfg {
   // the SAME TMEM columns serialise on the accumulate latency (~96 clk measured, i.e. 3x the 32-clk rate of
   // an N=64 MMA and 1.5x the 64-clk rate of an N=128 one); rotating the 36 MMAs of a patch over 3 (N=64) or
   // 2 (N=128) independent chains hides it.  The epilogue adds the chains.
-  static constexpr int kChains = BN == 64 ? 3 : 2;
+  static constexpr int kChains = BN == 64 ? PDT_HALO64_CHAINS : 2;
   static constexpr int kAccCols = BN == 64 ? 256 : 2 * BN;      // columns reserved per accumulator buffer (chains * BN, padded)
   static constexpr int kTmemCols = 2 * kAccCols;                // 512
   // per epilogue warp: column accumulators [2][kStatMaxK] + a 32 x 33 float transpose tile
@@ -330,15 +333,17 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         tc_fence_after();
         uint32_t v[32];
         {
-          uint32_t v2[32], v3[32];
+          uint32_t v2[32], v3[32], v4[NCH >= 4 ? 32 : 1];
           tmem_ld32(taddr + c0, v);
           tmem_ld32(taddr + BN + c0, v2);
-          if (NCH == 3) tmem_ld32(taddr + 2 * BN + c0, v3);
+          if (NCH >= 3) tmem_ld32(taddr + 2 * BN + c0, v3);
+          if constexpr (NCH >= 4) tmem_ld32(taddr + 3 * BN + c0, v4);
           tmem_ld_wait();
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
             float t = __uint_as_float(v[j]) + __uint_as_float(v2[j]);
-            if (NCH == 3) t += __uint_as_float(v3[j]);
+            if (NCH >= 3) t += __uint_as_float(v3[j]);
+            if constexpr (NCH >= 4) t += __uint_as_float(v4[j]);
             v[j] = __float_as_uint(t);
           }
         }
@@ -667,6 +672,141 @@ k_wgrad3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
 #pragma unroll
           for (int i = 0; i < 32; ++i)       // dw[k][tap][c], k = c0 + i: the 32 lanes of a warp cover 32 consecutive c
             atomicAdd(dw + ((size_t)(c0 + i) * 9 + tap) * 64 + c, __uint_as_float(v[i]));
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+// fp32 (kind::tf32) form of k_wgrad3x3_halo.  A pixel's 64 fp32 channels are two 128-byte rows, so the patch and
+// the dy tile are kept as two PLANES of 32 channels each (two TMA loads, 32-byte-atom swizzle: the MN-major layout
+// tcgen05 reads for 32-bit operands, as in k_conv_wgrad<float>).  One M = 128 instruction takes the FOUR views
+// (r, s = 0..3) of one plane — leading-dimension offset = one pixel slot, the fourth view is a phantom tap whose rows
+// are never stored — against all 64 output channels (two planes of dy, N = 64): six accumulator chains
+// (3 filter rows x 2 planes, 384 TMEM columns) per 8-pixel k-step, 192 tensor clocks per 8 pixels, and every
+// activation byte leaves L2 once instead of once per tap (k_conv_wgrad<64, float>: 1.73 ms per layer-1
+// convolution at 1200 images, bound by L2 -> SM traffic).
+struct WHCfg32 {
+  static constexpr int kStages = 2;
+  static constexpr int kAPlane = 32768;          // 1 KB front slack + patch plane + tail
+  static constexpr int kBPlane = 16384;          // 128 pixel slots x 32 channels
+  static constexpr int kAStage = 2 * kAPlane, kBStage = 2 * kBPlane;
+  static constexpr int kSmemBytes = kStages * (kAStage + kBStage) + 1024 + 128;
+  static_assert(kSmemBytes <= 232448, "over the 227 KB shared-memory limit of sm_100");
+};
+
+__global__ void __launch_bounds__(128, 1)
+k_wgrad3x3_halo_tf32(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmDY, float* __restrict__ dw,
+                     const HaloGeom g) {
+  using W = WHCfg32;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smA = smem;
+  uint8_t* smB = smem + W::kStages * W::kAStage;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smB + W::kStages * W::kBStage);
+  uint64_t* empty = full + W::kStages;
+  uint64_t* done = empty + W::kStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done + 1);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) { prefetch_tmap(&tmX); prefetch_tmap(&tmDY); }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < W::kStages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    mbar_init(done, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, 512);
+  {   // slots no TMA box writes are read by the last k-step / the largest shifts: zeros, not stale shared memory
+    uint4* z = reinterpret_cast<uint4*>(smem);
+    const int n16 = W::kStages * (W::kAStage + W::kBStage) / 16;
+    for (int i = threadIdx.x; i < n16; i += blockDim.x) z[i] = make_uint4(0, 0, 0, 0);
+  }
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_enter();
+  const int slots = g.TR * g.Wp;
+  const int ksteps = (slots + 7) >> 3;
+  const uint32_t dy_bytes = (uint32_t)slots * 128u;          // per plane
+
+  if (warp == 0) {
+    int stage = 0;
+    uint32_t phase = 0;
+    int n = (int)blockIdx.x / g.tiles_per_image, tr = (int)blockIdx.x - n * g.tiles_per_image;
+    const int dn = (int)gridDim.x / g.tiles_per_image, dr = (int)gridDim.x - dn * g.tiles_per_image;
+    for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x) {
+      const int h0 = tr * g.TR;
+      mbar_wait(&empty[stage], phase ^ 1);
+      if (elect_one_sync()) {
+        mbar_expect_tx(&full[stage], 2 * (g.patch_bytes + dy_bytes));
+#pragma unroll
+        for (int p = 0; p < 2; ++p) {
+          tma_load_4d(smA + stage * W::kAStage + p * W::kAPlane + 1024, &tmX, &full[stage], 32 * p, -1, h0 - 1, n);
+          tma_load_4d(smB + stage * W::kBStage + p * W::kBPlane, &tmDY, &full[stage], 32 * p, -1, h0, n);
+        }
+      }
+      __syncwarp();
+      if (++stage == W::kStages) { stage = 0; phase ^= 1; }
+      tr += dr; n += dn;
+      if (tr >= g.tiles_per_image) { tr -= g.tiles_per_image; ++n; }
+    }
+  } else if (warp == 1) {
+    constexpr uint32_t idesc = make_idesc(128, 64, 2, 1, 1);            // kind::tf32, both operands MN-major
+    // filter row r: the views of taps (r, 0..3) start (r * Wp - 1), +1, +2, +3 slots into the plane
+    uint64_t tmpl[3];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) tmpl[r] = make_sw128_desc(0, 512, 128, 1) + (uint64_t)(int64_t)((r * g.Wp - 1) * 8);
+    int stage = 0;
+    uint32_t phase = 0;
+    bool first = true;
+    for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x) {
+      mbar_wait(&full[stage], phase);
+      tc_fence_after();
+      const uint64_t a_addr = (uint64_t)((smem_u32(smA + stage * W::kAStage + 1024) & 0x3FFFF) >> 4);
+      const uint64_t db0 = make_sw128_desc(smem_u32(smB + stage * W::kBStage), 512, W::kBPlane, 1);
+      if (elect_one_sync()) {
+        for (int ks = 0; ks < ksteps; ++ks) {
+          const uint32_t accum = (first && ks == 0) ? 0u : 1u;
+#pragma unroll
+          for (int j = 0; j < 6; ++j)      // chain j = (filter row j / 2, channel plane j % 2)
+            umma_tf32(tmem_base + j * 64, tmpl[j >> 1] + a_addr + (uint64_t)((j & 1) * (W::kAPlane >> 4) + ks * 64),
+                      db0 + (uint64_t)(ks * 64), idesc, accum);
+        }
+        umma_commit(&empty[stage]);
+      }
+      __syncwarp();
+      first = false;
+      if (++stage == W::kStages) { stage = 0; phase ^= 1; }
+    }
+    if (elect_one_sync()) umma_commit(done);
+    __syncwarp();
+  }
+  __syncwarp();
+  // ---- drain: accumulator row = (tap column s) * 32 + input channel of the plane; warp 3 holds the phantom tap ----
+  if (blockIdx.x < g.num_tiles) {
+    mbar_wait(done, 0);
+    tc_fence_after();
+    const int sx = warp, c = lane;
+#pragma unroll 1
+    for (int j = 0; j < 6; ++j) {
+      const int tap = (j >> 1) * 3 + sx, ch = (j & 1) * 32 + c;
+#pragma unroll 1
+      for (int c0 = 0; c0 < 64; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + j * 64 + c0, v);
+        tmem_ld_wait();
+        if (sx < 3) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i)       // dw[k][tap][ch], k = c0 + i: a warp's lanes cover 32 consecutive channels
+            atomicAdd(dw + ((size_t)(c0 + i) * 9 + tap) * 64 + ch, __uint_as_float(v[i]));
         }
       }
     }
@@ -1068,12 +1208,12 @@ int pdt_conv3x3_halo_add(const void* x, const void* w, void* y, const void* adde
 
 // 1 if pdt_conv3x3_wgrad_halo serves this weight gradient (3x3, stride 1, pad 1 implied).
 int pdt_conv3x3_wgrad_halo_supported(int dtype, int N, int H, int W, int C, int K) {
-  if (dtype != PDT_BF16 && dtype != PDT_FP16) return 0;
+  if (dtype != PDT_BF16 && dtype != PDT_FP16 && dtype != PDT_FP32) return 0;
   if (C != 64 || K != 64 || W + 2 > 58 || W < 6 || H < 1 || N < 1) return 0;
   return 1;
 }
 
-// x: [N][H][W][64], dy: [N][H][W][64] (bf16/fp16), dw: [64][3][3][64] fp32, ACCUMULATED into (zero it first).
+// x: [N][H][W][64], dy: [N][H][W][64] (bf16 / fp16 / fp32 as tf32), dw: [64][3][3][64] fp32, ACCUMULATED into (zero it first).
 int pdt_conv3x3_wgrad_halo(const void* x, const void* dy, float* dw, int dtype, int N, int H, int W, int C, int K,
                            cudaStream_t stream) {
   if (!pdt_conv3x3_wgrad_halo_supported(dtype, N, H, W, C, K)) return PDT_E_UNSUPPORTED;
@@ -1095,30 +1235,42 @@ int pdt_conv3x3_wgrad_halo(const void* x, const void* dy, float* dw, int dtype, 
   g.num_tiles = N * g.tiles_per_image;
   g.c_chunks = 1;
   g.patch_bytes = (uint32_t)((g.TR + 2) * g.Wp * 128);
-  // the largest view (phantom tap 9, paired with tap 8) starts 2*Wp + 2 rows in and is read for 128 rows
+  const bool f32 = dtype == PDT_FP32;
+  // the largest view starts 2*Wp + 2 rows in and is read for up to 128 rows (16 bit: phantom tap 9, paired with tap 8;
+  // fp32: phantom tap (2, 3) of the four-view instruction of the last filter row)
   if (1024 + (2 * g.Wp + 2 + 128) * 128 > WHCfg::kAStage || g.patch_bytes + 1024 > (uint32_t)WHCfg::kAStage) return PDT_E_UNSUPPORTED;
-  const CUtensorMapDataType dt = dtype == PDT_FP16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  const CUtensorMapDataType dt = f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
+                                     : (dtype == PDT_FP16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16);
+  // fp32: a pixel is two 128-byte rows; the box takes 32 channels (one plane), MN-major 32-bit operands use the
+  // 32-byte-atom flavour of the 128-byte swizzle
+  const CUtensorMapSwizzle swz = f32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
+  const cuuint64_t px = f32 ? 256 : 128;
+  const cuuint32_t bc = f32 ? 32 : 64;
   CUtensorMap tmX, tmDY;
   cuuint64_t dims[4] = {64, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
-  cuuint64_t strides[3] = {128, (cuuint64_t)W * 128, (cuuint64_t)H * W * 128};
+  cuuint64_t strides[3] = {px, (cuuint64_t)W * px, (cuuint64_t)H * W * px};
   cuuint32_t estr[4] = {1, 1, 1, 1};
   {
-    cuuint32_t box[4] = {64, (cuuint32_t)g.Wp, (cuuint32_t)(g.TR + 2), 1};
+    cuuint32_t box[4] = {bc, (cuuint32_t)g.Wp, (cuuint32_t)(g.TR + 2), 1};
     if (g_enc(&tmX, dt, 4, const_cast<void*>(x), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+              swz, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
       return 10006;
   }
   {
-    cuuint32_t box[4] = {64, (cuuint32_t)g.Wp, (cuuint32_t)g.TR, 1};
+    cuuint32_t box[4] = {bc, (cuuint32_t)g.Wp, (cuuint32_t)g.TR, 1};
     if (g_enc(&tmDY, dt, 4, const_cast<void*>(dy), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+              swz, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
       return 10007;
   }
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   const int grid = g.num_tiles < sms ? g.num_tiles : sms;
-  if (dtype == PDT_FP16) {
+  if (f32) {
+    auto kern = k_wgrad3x3_halo_tf32;
+    PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, WHCfg32::kSmemBytes));
+    PDT_CHECK(launch_pdl(kern, dim3(grid), dim3(128), WHCfg32::kSmemBytes, stream, tmX, tmDY, dw, g));
+  } else if (dtype == PDT_FP16) {
     auto kern = k_wgrad3x3_halo<__half>;
     PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, WHCfg::kSmemBytes));
     PDT_CHECK(launch_pdl(kern, dim3(grid), dim3(128), WHCfg::kSmemBytes, stream, tmX, tmDY, dw, g));

@@ -227,11 +227,12 @@ def test_conv3x3_halo_kernel(native_lib, dtype, cin, cout, hw, batch):
     assert torch.allclose(rm, 0.1 * ref.mean((0, 2, 3)), rtol=1e-2, atol=2e-3)
 
 
-@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
 @pytest.mark.parametrize("hw,batch", [(56, 5), (20, 3), (31, 2), (8, 150), (55, 1)])
 def test_conv3x3_wgrad_halo_kernel(native_lib, dtype, hw, batch):
     """64->64 3x3 weight gradient with patch reuse (row-shifted MN-major views, tap pairs through the
-    descriptor's leading-dimension offset) vs autograd; includes partial last tiles (31, 55 rows)."""
+    descriptor's leading-dimension offset; fp32: kind::tf32, four views per instruction over two channel planes)
+    vs autograd; includes partial last tiles (31, 55 rows)."""
     from pytorch_distributed_template_b200 import ops
     from pytorch_distributed_template_b200.ops import conv_native, _native
     torch.backends.cudnn.allow_tf32 = False
@@ -244,10 +245,11 @@ def test_conv3x3_wgrad_halo_kernel(native_lib, dtype, hw, batch):
     wf = torch.zeros(64, 64, 3, 3, device=dev, requires_grad=True)
     F.conv2d(x.float(), wf, None, 1, 1).backward(dy.float())
     err = (dw - wf.grad).abs().max().item()
-    assert err <= 2e-3 * max(1.0, wf.grad.abs().max().item()), (err, wf.grad.abs().max().item())
+    tol = 3e-3 if dtype == torch.float32 else 2e-3          # tf32 keeps 10 mantissa bits of fp32 inputs
+    assert err <= tol * max(1.0, wf.grad.abs().max().item()), (err, wf.grad.abs().max().item())
     # accumulates into its destination
     dw2 = conv_native.wgrad(x, dy, (64, 64, 3, 3), 1, 1, out=dw.clone())
-    assert (dw2 - 2 * wf.grad).abs().max().item() <= 4e-3 * max(1.0, wf.grad.abs().max().item())
+    assert (dw2 - 2 * wf.grad).abs().max().item() <= 2 * tol * max(1.0, wf.grad.abs().max().item())
 
 
 @pytest.mark.parametrize("cin,cout,hw,k,stride,pad,batch", [(256, 256, 14, 3, 1, 1, 100), (512, 512, 7, 3, 1, 1, 400),

@@ -11,13 +11,23 @@ def main():
     top = int(sys.argv[2]) if len(sys.argv) > 2 else 20
     out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(out.splitlines()))
-    hi = next(i for i, r in enumerate(rows) if "# Samples" in r)
-    h = rows[hi]
+    # one table per profiled launch, each starting with its own header row
+    heads = [i for i, r in enumerate(rows) if "# Samples" in r]
+    for t, hi in enumerate(heads):
+        end = heads[t + 1] if t + 1 < len(heads) else len(rows)
+        title = next((" ".join(r) for r in rows[max(0, hi - 3):hi] if r and "Kernel" in " ".join(r)), "")
+        print("=== launch {} of {} in the report {}".format(t + 1, len(heads), title[:100]))
+        table(rows[hi], [r for r in rows[hi + 1:end]], top)
+
+
+def table(h, body, top):
     si, so = h.index("# Samples"), h.index("Source")
     st = [i for i, x in enumerate(h) if x.startswith("stall_") and "Not Issued" not in x]
-    data = [r for r in rows[hi + 1:] if len(r) > si]
+    data = [r for r in body if len(r) > si and (r[si] or "0").isdigit()]
     tot = sum(int(r[si] or 0) for r in data)
     print("total samples", tot, "instructions", len(data))
+    if tot == 0:
+        return
     b = collections.Counter()
     for i, r in enumerate(data):
         b[i // 100] += int(r[si] or 0)
