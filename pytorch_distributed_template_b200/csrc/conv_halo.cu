@@ -60,7 +60,7 @@ struct BnStats {
   Comm comm;              // world > 1: SyncBatchNorm — the last CTA exchanges the raw moments with its peers (fabric.cuh)
 };
 
-template <int BN, bool RES> struct HCfg {
+template <int BN, bool RES, bool F32 = false> struct HCfg {
   static constexpr int kAStage = 32768;                       // 1 KB front slack + patch + tail slack (Wp <= 58)
   static constexpr int kAStages = 3;
   static constexpr int kBTile = BN * 128;
@@ -75,7 +75,7 @@ template <int BN, bool RES> struct HCfg {
   // per epilogue warp: column accumulators [2][kStatMaxK] + a 32 x 33 float transpose tile
   // N=64: the output tile is staged in shared memory (dense rows, 128B-swizzled, double-buffered) and leaves
   // through one TMA store, and the statistics stay in registers, so the transpose tiles are not used.
-  static constexpr bool kTmaStore = BN == 64;
+  static constexpr bool kTmaStore = BN == 64 && !F32;           // (fp32 rows are 256 B: they leave through direct 16-byte stores)
   static constexpr int kOutBuf = 128 * 128;
   static constexpr int kOutBytes = kTmaStore ? 2 * kOutBuf : 0;
   static constexpr int kStatStride = kTmaStore ? 2 * kStatMaxK : 2 * kStatMaxK + 32 * 33;   // floats per epilogue warp
@@ -135,7 +135,10 @@ template <int BN, bool RES, typename T, int CL>
 __global__ void __launch_bounds__(kThreads, 1)
 k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
                const __grid_constant__ CUtensorMap tmY, T* __restrict__ out, const HaloGeom g, const BnStats bs) {
-  using C = HCfg<BN, RES>;
+  using C = HCfg<BN, RES, sizeof(T) == 4>;
+  // one 128-byte K row of a patch pixel / filter row: 64 channels in 16 bit, 32 as fp32 (kind::tf32); a layer's
+  // channels are g.c_chunks such chunks, each with its own patch load and nine tap tiles
+  constexpr int kCh = 128 / (int)sizeof(T);
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smA = smem;
@@ -153,7 +156,8 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
   float* s_stat = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  static_assert(CL == 1 || (!RES && !HCfg<BN, RES>::kTmaStore), "the multicast ring is for the streamed, direct-store variant");
+  static_assert(CL == 1 || (!RES && !C::kTmaStore), "the multicast ring is for the streamed, direct-store variant");
+  static_assert(sizeof(T) == 2 || !RES, "the fp32 filter bank (144 KB for 64 x 64 x 9) is streamed, never resident");
   const int crank = CL > 1 ? (int)cluster_ctarank() : 0;
   constexpr uint16_t kMask = (uint16_t)((1u << CL) - 1);
   // every CTA of a cluster runs the same number of iterations
@@ -195,7 +199,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
           if (ft < g.num_tiles && elect_one_sync()) {
             const int fn = ft / g.tiles_per_image;
             const int fh = (ft - fn * g.tiles_per_image) * g.TR;
-            for (int cc = 0; cc < g.c_chunks; ++cc) tma_prefetch_4d(&tmX, cc * 64, -1, fh - 1, fn);
+            for (int cc = 0; cc < g.c_chunks; ++cc) tma_prefetch_4d(&tmX, cc * kCh, -1, fh - 1, fn);
           }
           __syncwarp();
         }
@@ -203,7 +207,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
           mbar_wait(&aempty[as], aph ^ 1);
           if (elect_one_sync()) {
             mbar_expect_tx(&afull[as], g.patch_bytes);
-            tma_load_4d(smA + as * C::kAStage + 1024, &tmX, &afull[as], cc * 64, -1, h0 - 1, n);
+            tma_load_4d(smA + as * C::kAStage + 1024, &tmX, &afull[as], cc * kCh, -1, h0 - 1, n);
           }
           __syncwarp();
           if (++as == C::kAStages) { as = 0; aph ^= 1; }
@@ -212,8 +216,8 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
               mbar_wait(&bempty[bsg], bph ^ 1);
               if (elect_one_sync()) {
                 mbar_expect_tx(&bfull[bsg], C::kBTile);
-                if (CL == 1) tma_load_2d(smB + bsg * C::kBTile, &tmW, &bfull[bsg], tap * g.C + cc * 64, 0);
-                else tma_load_2d_mc(smB + bsg * C::kBTile + crank * (C::kBTile / CL), &tmW, &bfull[bsg], tap * g.C + cc * 64,
+                if (CL == 1) tma_load_2d(smB + bsg * C::kBTile, &tmW, &bfull[bsg], tap * g.C + cc * kCh, 0);
+                else tma_load_2d_mc(smB + bsg * C::kBTile + crank * (C::kBTile / CL), &tmW, &bfull[bsg], tap * g.C + cc * kCh,
                                     crank * (BN / CL), kMask);
               }
               __syncwarp();
@@ -226,8 +230,11 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
   } else if (warp == 1) {
     // ================= MMA issuer (whole warp converged, one elected lane issues) =================
     {
-      constexpr uint32_t idesc = make_idesc(128, BN, std::is_same<T, __nv_bfloat16>::value ? 1 : 0, 0, 0);
+      constexpr uint32_t idesc = make_idesc(128, BN, sizeof(T) == 4 ? 2 : (std::is_same<T, __nv_bfloat16>::value ? 1 : 0), 0, 0);
       constexpr int NCH = C::kChains;
+      auto mma = [](uint32_t d, uint64_t a, uint64_t b, uint32_t id, uint32_t acc) {      // 32 bytes of K per instruction either way
+        if constexpr (sizeof(T) == 4) umma_tf32(d, a, b, id, acc); else umma_f16(d, a, b, id, acc);
+      };
       // Everything the 36 MMAs of a patch need is loop-invariant except the ring slot: the tap's operand is
       // the patch shifted by whole 128-byte pixel rows, i.e. a constant added to the descriptor's
       // (address >> 4) field.  Keeping those constants in registers and unrolling the tap loop matters: the
@@ -260,7 +267,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
                   const int i = tap * 4 + k;
-                  umma_f16(tmem_d + (i % NCH) * BN, da + 2 * k, db + 2 * k, idesc, i >= NCH ? 1u : later);
+                  mma(tmem_d + (i % NCH) * BN, da + 2 * k, db + 2 * k, idesc, i >= NCH ? 1u : later);
                 }
               }
               umma_commit(&aempty[as]);
@@ -277,7 +284,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
                   const int i = tap * 4 + k;
-                  umma_f16(tmem_d + (i % NCH) * BN, da + 2 * k, db + 2 * k, idesc, i >= NCH ? 1u : later);
+                  mma(tmem_d + (i % NCH) * BN, da + 2 * k, db + 2 * k, idesc, i >= NCH ? 1u : later);
                 }
                 if (CL == 1) umma_commit(&bempty[bsg]); else umma_commit_mc(&bempty[bsg], kMask);
                 if (tap == 8) umma_commit(&aempty[as]);
@@ -459,26 +466,45 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         }
         if (valid && g.addend != nullptr) {
           const T* arow = reinterpret_cast<const T*>(g.addend) + (orow - out) + c0;
-          uint4 ad[4];
+          if constexpr (sizeof(T) == 4) {
+            uint4 ad[8];
 #pragma unroll
-          for (int j = 0; j < 4; ++j) ad[j] = ldg_stream(arow + 8 * j);
+            for (int j = 0; j < 8; ++j) ad[j] = ldg_stream(arow + 4 * j);
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            float a[8];
-            unpack8<T>(ad[j], a);
+            for (int j = 0; j < 8; ++j) {
+              v[4 * j + 0] = __float_as_uint(__uint_as_float(v[4 * j + 0]) + __uint_as_float(ad[j].x));
+              v[4 * j + 1] = __float_as_uint(__uint_as_float(v[4 * j + 1]) + __uint_as_float(ad[j].y));
+              v[4 * j + 2] = __float_as_uint(__uint_as_float(v[4 * j + 2]) + __uint_as_float(ad[j].z));
+              v[4 * j + 3] = __float_as_uint(__uint_as_float(v[4 * j + 3]) + __uint_as_float(ad[j].w));
+            }
+          } else {
+            uint4 ad[4];
 #pragma unroll
-            for (int e = 0; e < 8; ++e) v[8 * j + e] = __float_as_uint(__uint_as_float(v[8 * j + e]) + a[e]);
+            for (int j = 0; j < 4; ++j) ad[j] = ldg_stream(arow + 8 * j);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              float a[8];
+              unpack8<T>(ad[j], a);
+#pragma unroll
+              for (int e = 0; e < 8; ++e) v[8 * j + e] = __float_as_uint(__uint_as_float(v[8 * j + e]) + a[e]);
+            }
           }
         }
         if (valid) {
+          if constexpr (sizeof(T) == 4) {
 #pragma unroll
-          for (int j = 0; j < 32; j += 8) {
-            uint4 o;
-            o.x = Cvt<T>::pack2(__uint_as_float(v[j + 0]), __uint_as_float(v[j + 1]));
-            o.y = Cvt<T>::pack2(__uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
-            o.z = Cvt<T>::pack2(__uint_as_float(v[j + 4]), __uint_as_float(v[j + 5]));
-            o.w = Cvt<T>::pack2(__uint_as_float(v[j + 6]), __uint_as_float(v[j + 7]));
-            *reinterpret_cast<uint4*>(orow + c0 + j) = o;
+            for (int j = 0; j < 32; j += 4)
+              *reinterpret_cast<uint4*>(orow + c0 + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              uint4 o;
+              o.x = Cvt<T>::pack2(__uint_as_float(v[j + 0]), __uint_as_float(v[j + 1]));
+              o.y = Cvt<T>::pack2(__uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
+              o.z = Cvt<T>::pack2(__uint_as_float(v[j + 4]), __uint_as_float(v[j + 5]));
+              o.w = Cvt<T>::pack2(__uint_as_float(v[j + 6]), __uint_as_float(v[j + 7]));
+              *reinterpret_cast<uint4*>(orow + c0 + j) = o;
+            }
           }
         }
         if (bs.enabled) {
@@ -1055,7 +1081,7 @@ EncodeTiledFn g_enc = nullptr;
 template <int BN, bool RES, typename T, int CL>
 int launch_t(void* y, const HaloGeom& g, const BnStats& bs, const CUtensorMap& tmX, const CUtensorMap& tmW, const CUtensorMap& tmY,
              cudaStream_t stream) {
-  using C = HCfg<BN, RES>;
+  using C = HCfg<BN, RES, sizeof(T) == 4>;
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -1094,8 +1120,15 @@ template <int BN, bool RES, int CL = 1>
 int launch(const void* x, const void* w, void* y, int dtype, const HaloGeom& g, const BnStats& bs, const CUtensorMap& tmX,
            const CUtensorMap& tmW, const CUtensorMap& tmY, cudaStream_t stream) {
   (void)x; (void)w;
-  if (dtype == PDT_FP16) return launch_t<BN, RES, __half, CL>(y, g, bs, tmX, tmW, tmY, stream);
-  return launch_t<BN, RES, __nv_bfloat16, CL>(y, g, bs, tmX, tmW, tmY, stream);
+  if constexpr (!RES) {
+    if (dtype == PDT_FP32) return launch_t<BN, RES, float, CL>(y, g, bs, tmX, tmW, tmY, stream);
+  }
+  if constexpr (BN == 64 && CL > 1) {
+    return PDT_E_UNSUPPORTED;                   // the 16-bit N = 64 kernel stores through TMA: no cluster form
+  } else {
+    if (dtype == PDT_FP16) return launch_t<BN, RES, __half, CL>(y, g, bs, tmX, tmW, tmY, stream);
+    return launch_t<BN, RES, __nv_bfloat16, CL>(y, g, bs, tmX, tmW, tmY, stream);
+  }
 }
 
 // Filter-tap multicast between CTA pairs for the streamed 128-wide variant (PDT_CONV_CLUSTER=1 disables).
@@ -1113,12 +1146,12 @@ extern "C" {
 
 // 1 if pdt_conv3x3_halo serves this shape (3x3, stride 1, pad 1 implied).
 int pdt_conv3x3_halo_supported(int dtype, int N, int H, int W, int C, int K) {
-  if (dtype != PDT_BF16 && dtype != PDT_FP16) return 0;
+  if (dtype != PDT_BF16 && dtype != PDT_FP16 && dtype != PDT_FP32) return 0;
   if (C % 64 || (K != 64 && K != 128) || W + 2 > 58 || W < 6 || H < 1 || N < 1) return 0;
   return 1;
 }
 
-// x: [N][H][W][C], w: [K][3][3][C], y: [N][H][W][K] (bf16/fp16).  scratch/stat pointers as in
+// x: [N][H][W][C], w: [K][3][3][C], y: [N][H][W][K] (bf16 / fp16 / fp32 as tf32).  scratch/stat pointers as in
 // pdt_conv_fprop_bnstats; pass scratch == NULL for a plain convolution.
 int pdt_conv3x3_halo(const void* x, const void* w, void* y, int dtype, int N, int H, int W, int C, int K, void* scratch,
                      float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
@@ -1152,19 +1185,23 @@ int pdt_conv3x3_halo_add(const void* x, const void* w, void* y, const void* adde
   if (g.TR > H) g.TR = H;
   g.tiles_per_image = (H + g.TR - 1) / g.TR;
   g.num_tiles = N * g.tiles_per_image;
-  g.c_chunks = C / 64;
+  const bool f32 = dtype == PDT_FP32;
+  const cuuint64_t es = f32 ? 4 : 2;
+  const cuuint32_t kch = f32 ? 32 : 64;          // channels per 128-byte K row
+  g.c_chunks = C / (int)kch;
   g.patch_bytes = (uint32_t)((g.TR + 2) * g.Wp * 128);
   if (1024 + (128 + 2 * g.Wp + 2) * 128 > 32768 || g.patch_bytes + 1024 > 32768) return PDT_E_UNSUPPORTED;
-  const bool resident = (C == 64 && K == 64);
+  const bool resident = (C == 64 && K == 64 && !f32);
   int sms_q = 148;
   { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms_q, cudaDevAttrMultiProcessorCount, dev); }
-  const int cl = (K == 128) ? halo_cluster(g, sms_q, w, stream) : 1;
-  const CUtensorMapDataType dt = dtype == PDT_FP16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  const int cl = (K == 128 || f32) ? halo_cluster(g, sms_q, w, stream) : 1;
+  const CUtensorMapDataType dt = f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
+                                     : (dtype == PDT_FP16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16);
   CUtensorMap tmX, tmW;
   {
     cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
-    cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
-    cuuint32_t box[4] = {64, (cuuint32_t)g.Wp, (cuuint32_t)(g.TR + 2), 1};
+    cuuint64_t strides[3] = {(cuuint64_t)C * es, (cuuint64_t)W * C * es, (cuuint64_t)H * W * C * es};
+    cuuint32_t box[4] = {kch, (cuuint32_t)g.Wp, (cuuint32_t)(g.TR + 2), 1};
     cuuint32_t estr[4] = {1, 1, 1, 1};
     if (g_enc(&tmX, dt, 4, const_cast<void*>(x), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
@@ -1172,8 +1209,8 @@ int pdt_conv3x3_halo_add(const void* x, const void* w, void* y, const void* adde
   }
   {
     cuuint64_t dims[2] = {(cuuint64_t)9 * C, (cuuint64_t)K};
-    cuuint64_t strides[1] = {(cuuint64_t)9 * C * 2};
-    cuuint32_t box[2] = {64, (cuuint32_t)(K / cl)};     // with CTA pairs each CTA loads (and multicasts) half of a tap's rows
+    cuuint64_t strides[1] = {(cuuint64_t)9 * C * es};
+    cuuint32_t box[2] = {kch, (cuuint32_t)(K / cl)};    // with CTA pairs each CTA loads (and multicasts) half of a tap's rows
     cuuint32_t estr[2] = {1, 1};
     if (g_enc(&tmW, dt, 2, const_cast<void*>(w), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
@@ -1182,8 +1219,8 @@ int pdt_conv3x3_halo_add(const void* x, const void* w, void* y, const void* adde
   CUtensorMap tmY;
   {   // output as (K, W, H, N); one box = the TR x W x 64-channel tile the N=64 kernel stages in shared memory
     cuuint64_t dims[4] = {(cuuint64_t)K, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
-    cuuint64_t strides[3] = {(cuuint64_t)K * 2, (cuuint64_t)W * K * 2, (cuuint64_t)H * W * K * 2};
-    cuuint32_t box[4] = {64, (cuuint32_t)W, (cuuint32_t)g.TR, 1};
+    cuuint64_t strides[3] = {(cuuint64_t)K * es, (cuuint64_t)W * K * es, (cuuint64_t)H * W * K * es};
+    cuuint32_t box[4] = {kch, (cuuint32_t)W, (cuuint32_t)g.TR, 1};      // (only the 16-bit N = 64 kernel stores through it)
     cuuint32_t estr[4] = {1, 1, 1, 1};
     if (g_enc(&tmY, dt, 4, y, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
               CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
@@ -1200,6 +1237,7 @@ int pdt_conv3x3_halo_add(const void* x, const void* w, void* y, const void* adde
   bs.comm = make_comm(comm);
   if (K == 64) {
     if (resident) return launch<64, true>(x, w, y, dtype, g, bs, tmX, tmW, tmY, stream);
+    if (f32 && cl == 2) return launch<64, false, 2>(x, w, y, dtype, g, bs, tmX, tmW, tmY, stream);
     return launch<64, false>(x, w, y, dtype, g, bs, tmX, tmW, tmY, stream);
   }
   if (cl == 2) return launch<128, false, 2>(x, w, y, dtype, g, bs, tmX, tmW, tmY, stream);

@@ -46,7 +46,9 @@ CL = torch.channels_last
 def _halo_ok(x, w_lp, stride, pad):
     """Large-map 3x3/1/1 layers go to the patch-reuse kernel (csrc/conv_halo.cu); PDT_HALO=0 disables it."""
     K, C, R, S = w_lp.shape
-    if R != 3 or S != 3 or stride != 1 or pad != 1 or x.dtype == torch.float32 or os.environ.get("PDT_HALO", "1") != "1":
+    if R != 3 or S != 3 or stride != 1 or pad != 1 or os.environ.get("PDT_HALO", "1") != "1":
+        return False
+    if x.dtype == torch.float32 and os.environ.get("PDT_HALO_TF32", "1") != "1":      # fp32 runs as kind::tf32, streamed filter taps
         return False
     N, _, H, W = x.shape
     return bool(_native.lib().pdt_conv3x3_halo_supported(_native.dtype_code(x.dtype), N, H, W, C, K))

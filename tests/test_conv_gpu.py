@@ -202,12 +202,14 @@ def test_tf32_model_paths(native_lib):
     assert e_ours <= 0.2, (e_ours, e_torch)
 
 
-@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
 @pytest.mark.parametrize("cin,cout,hw,batch", [(64, 64, 56, 5), (128, 128, 28, 7), (64, 64, 56, 1), (128, 128, 28, 1),
                                                (64, 128, 28, 3), (128, 64, 56, 2), (64, 64, 20, 3),
-                                               (128, 128, 28, 43), (64, 128, 28, 44)])   # >= 2 tiles per SM: CTA-pair multicast
+                                               (128, 128, 28, 43), (64, 128, 28, 44),    # >= 2 tiles per SM: CTA-pair multicast
+                                               (64, 64, 56, 11)])                        # the same for the fp32 N = 64 form
 def test_conv3x3_halo_kernel(native_lib, dtype, cin, cout, hw, batch):
-    """Patch-reuse kernel (row-shifted smem descriptors) vs F.conv2d, with and without fused BN statistics."""
+    """Patch-reuse kernel (row-shifted smem descriptors) vs F.conv2d, with and without fused BN statistics
+    (fp32: kind::tf32 over 32-channel chunks, streamed filter taps)."""
     from pytorch_distributed_template_b200.ops import conv_native
     torch.backends.cudnn.allow_tf32 = False
     torch.manual_seed(20)
@@ -217,7 +219,7 @@ def test_conv3x3_halo_kernel(native_lib, dtype, cin, cout, hw, batch):
     assert conv_native._halo_ok(x, w, 1, 1)
     y = conv_native.fprop(x, w, 1, 1)
     ref = F.conv2d(x.float(), w.float(), None, 1, 1)
-    tol = 2e-2 if dtype == torch.bfloat16 else 3e-3
+    tol = 2e-2 if dtype == torch.bfloat16 else 3e-3          # (tf32 keeps 10 mantissa bits, like fp16)
     assert (y.float() - ref).abs().max().item() <= tol * max(1.0, ref.abs().max().item())
     rm, rv = torch.zeros(cout, device=dev), torch.ones(cout, device=dev)
     y2, mean, invstd = conv_native.fprop_bnstats(x, w, 1, 1, rm, rv, 0.1, 1e-5)
