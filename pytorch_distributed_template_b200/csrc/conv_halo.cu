@@ -60,11 +60,15 @@ struct BnStats {
   Comm comm;              // world > 1: SyncBatchNorm — the last CTA exchanges the raw moments with its peers (fabric.cuh)
 };
 
-template <int BN, bool RES, bool F32 = false> struct HCfg {
+// PAIR: two CTAs of a cluster run ONE M = 256 tcgen05.mma.cta_group::2 per tap and k-step over their two patches; each
+// holds HALF of every filter tile (BN / 2 output channels), so the 64 -> 64 filter banks stay resident in fp32 too
+// (72 KB per CTA) and a CTA reads A + B/2 from shared memory per instruction (see tc.cuh, k_conv_igemm<.., PAIR>).
+template <int BN, bool RES, bool F32 = false, bool PAIR = false> struct HCfg {
   static constexpr int kAStage = 32768;                       // 1 KB front slack + patch + tail slack (Wp <= 58)
   static constexpr int kAStages = 3;
-  static constexpr int kBTile = BN * 128;
-  static constexpr int kBStages = RES ? 9 : 4;                // resident: all nine taps of the single 64-channel block
+  static constexpr int kBTile = (PAIR ? BN / 2 : BN) * 128;   // rows of one (tap, channel chunk) filter tile held by this CTA
+  static constexpr int kChunks = F32 ? 2 : 1;                 // resident form: C = 64 is one 16-bit chunk or two fp32 chunks
+  static constexpr int kBStages = RES ? 9 * kChunks : (PAIR ? 8 : 4);   // resident: every tap of every chunk
   // Several accumulator chains per tile, each double-buffered: consecutive tcgen05.mma that accumulate into
   // the SAME TMEM columns serialise on the accumulate latency (~96 clk measured, i.e. 3x the 32-clk rate of
   // an N=64 MMA and 1.5x the 64-clk rate of an N=128 one); rotating the 36 MMAs of a patch over 3 (N=64) or
@@ -88,6 +92,13 @@ __device__ __forceinline__ void tma_load_4d(void* smem, const CUtensorMap* m, ui
   asm volatile(
       "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
       ::"r"(smem_u32(smem)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c), "r"(w), "r"(h), "r"(n) : "memory");
+}
+
+// The same for a CTA pair: the data lands in THIS CTA's shared memory, the bytes are signalled on the leader's barrier.
+__device__ __forceinline__ void tma_load_4d_pair(void* smem, const CUtensorMap* m, uint32_t bar_cluster_addr, int c, int w, int h, int n) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(smem_u32(smem)), "l"(reinterpret_cast<uint64_t>(m)), "r"(bar_cluster_addr), "r"(c), "r"(w), "r"(h), "r"(n) : "memory");
 }
 
 // Pull a future patch into L2 (no shared-memory destination, no barrier): the 3-deep shared-memory ring alone
@@ -131,11 +142,12 @@ __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 256;"
 // filter bank does not fit in shared memory (they were bound by it: 9 x 16 KB of taps per 23 KB patch).  A ring
 // slot is refilled only when both CTAs have consumed it, so the MMA commit arrives on both `bempty` barriers;
 // CTAs of a pair run the same number of tiles (the last one may be a phantom tile that stores nothing).
-template <int BN, bool RES, typename T, int CL>
+template <int BN, bool RES, typename T, int CL, bool PAIR = false>
 __global__ void __launch_bounds__(kThreads, 1)
 k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
                const __grid_constant__ CUtensorMap tmY, T* __restrict__ out, const HaloGeom g, const BnStats bs) {
-  using C = HCfg<BN, RES, sizeof(T) == 4>;
+  using C = HCfg<BN, RES, sizeof(T) == 4, PAIR>;
+  static_assert(!PAIR || CL == 2, "a CTA pair is a cluster of two");
   // one 128-byte K row of a patch pixel / filter row: 64 channels in 16 bit, 32 as fp32 (kind::tf32); a layer's
   // channels are g.c_chunks such chunks, each with its own patch load and nine tap tiles
   constexpr int kCh = 128 / (int)sizeof(T);
@@ -156,8 +168,8 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
   float* s_stat = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  static_assert(CL == 1 || (!RES && !C::kTmaStore), "the multicast ring is for the streamed, direct-store variant");
-  static_assert(sizeof(T) == 2 || !RES, "the fp32 filter bank (144 KB for 64 x 64 x 9) is streamed, never resident");
+  static_assert(CL == 1 || PAIR || (!RES && !C::kTmaStore), "the multicast ring is for the streamed, direct-store variant");
+  static_assert(sizeof(T) == 2 || !RES || PAIR, "the fp32 filter bank (144 KB for 64 x 64 x 9) is resident only as the halves of a CTA pair");
   const int crank = CL > 1 ? (int)cluster_ctarank() : 0;
   constexpr uint16_t kMask = (uint16_t)((1u << CL) - 1);
   // every CTA of a cluster runs the same number of iterations
@@ -166,11 +178,13 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
   if (warp == 0 && lane == 0) { prefetch_tmap(&tmX); prefetch_tmap(&tmW); if (C::kTmaStore) prefetch_tmap(&tmY); }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < C::kAStages; ++i) { mbar_init(&afull[i], 1); mbar_init(&aempty[i], 1); }
-    for (int i = 0; i < C::kBStages; ++i) { mbar_init(&bfull[i], 1); mbar_init(&bempty[i], CL); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], kEpiWarps); mbar_init(&sfree[i], 1); }
+    // PAIR: the `full` barriers that count are the leader's (both CTAs' loads complete on them); one MMA commit
+    // reaches both CTAs' `empty` / tfull barriers; both CTAs' epilogue warps arrive on the leader's tempty
+    for (int i = 0; i < C::kBStages; ++i) { mbar_init(&bfull[i], 1); mbar_init(&bempty[i], PAIR ? 1 : CL); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], PAIR ? 2 * kEpiWarps : kEpiWarps); mbar_init(&sfree[i], 1); }
     fence_barrier_init();
   }
-  if (warp == 2) tmem_alloc(tmem_slot, C::kTmemCols);
+  if (warp == 2) { if constexpr (PAIR) tmem_alloc_pair(tmem_slot, C::kTmemCols); else tmem_alloc(tmem_slot, C::kTmemCols); }
   tc_fence_before();
   __syncthreads();
   if (CL > 1) cluster_sync_all();
@@ -181,10 +195,18 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
   if (warp == 0) {
     // ================= TMA producer (whole warp converged, one elected lane issues) =================
     {
-      if (RES) {     // the whole 3x3x64xBN filter bank, once
+      if (RES) {     // the whole 3x3x64xBN filter bank, once (PAIR: this CTA's BN / 2 rows of every tile)
         if (elect_one_sync()) {
-          mbar_expect_tx(&bfull[0], 9 * C::kBTile);
-          for (int tap = 0; tap < 9; ++tap) tma_load_2d(smB + tap * C::kBTile, &tmW, &bfull[0], tap * g.C, 0);
+          if constexpr (PAIR) {
+            const uint32_t lead = mapa_cluster(smem_u32(&bfull[0]), 0);
+            if (crank == 0) mbar_expect_tx(&bfull[0], 2 * C::kBStages * C::kBTile);
+            for (int cc = 0; cc < C::kChunks; ++cc)
+              for (int tap = 0; tap < 9; ++tap)
+                tma_load_2d_pair(smB + (cc * 9 + tap) * C::kBTile, &tmW, lead, tap * g.C + cc * kCh, crank * (BN / 2));
+          } else {
+            mbar_expect_tx(&bfull[0], 9 * C::kBTile);
+            for (int tap = 0; tap < 9; ++tap) tma_load_2d(smB + tap * C::kBTile, &tmW, &bfull[0], tap * g.C, 0);
+          }
         }
         __syncwarp();
       }
@@ -206,8 +228,13 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         for (int cc = 0; cc < g.c_chunks; ++cc) {
           mbar_wait(&aempty[as], aph ^ 1);
           if (elect_one_sync()) {
-            mbar_expect_tx(&afull[as], g.patch_bytes);
-            tma_load_4d(smA + as * C::kAStage + 1024, &tmX, &afull[as], cc * kCh, -1, h0 - 1, n);
+            if constexpr (PAIR) {
+              if (crank == 0) mbar_expect_tx(&afull[as], 2 * g.patch_bytes);
+              tma_load_4d_pair(smA + as * C::kAStage + 1024, &tmX, mapa_cluster(smem_u32(&afull[as]), 0), cc * kCh, -1, h0 - 1, n);
+            } else {
+              mbar_expect_tx(&afull[as], g.patch_bytes);
+              tma_load_4d(smA + as * C::kAStage + 1024, &tmX, &afull[as], cc * kCh, -1, h0 - 1, n);
+            }
           }
           __syncwarp();
           if (++as == C::kAStages) { as = 0; aph ^= 1; }
@@ -215,10 +242,16 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
             for (int tap = 0; tap < 9; ++tap) {
               mbar_wait(&bempty[bsg], bph ^ 1);
               if (elect_one_sync()) {
+                if constexpr (PAIR) {
+                  if (crank == 0) mbar_expect_tx(&bfull[bsg], 2 * C::kBTile);
+                  tma_load_2d_pair(smB + bsg * C::kBTile, &tmW, mapa_cluster(smem_u32(&bfull[bsg]), 0), tap * g.C + cc * kCh,
+                                   crank * (BN / 2));
+                } else {
                 mbar_expect_tx(&bfull[bsg], C::kBTile);
                 if (CL == 1) tma_load_2d(smB + bsg * C::kBTile, &tmW, &bfull[bsg], tap * g.C + cc * kCh, 0);
                 else tma_load_2d_mc(smB + bsg * C::kBTile + crank * (C::kBTile / CL), &tmW, &bfull[bsg], tap * g.C + cc * kCh,
                                     crank * (BN / CL), kMask);
+                }
               }
               __syncwarp();
               if (++bsg == C::kBStages) { bsg = 0; bph ^= 1; }
@@ -227,14 +260,16 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         }
       }
     }
-  } else if (warp == 1) {
-    // ================= MMA issuer (whole warp converged, one elected lane issues) =================
+  } else if (warp == 1 && (!PAIR || crank == 0)) {
+    // ================= MMA issuer (whole warp converged, one elected lane issues; the leader CTA of a pair) =================
     {
-      constexpr uint32_t idesc = make_idesc(128, BN, sizeof(T) == 4 ? 2 : (std::is_same<T, __nv_bfloat16>::value ? 1 : 0), 0, 0);
+      constexpr uint32_t idesc = make_idesc(PAIR ? 256 : 128, BN, sizeof(T) == 4 ? 2 : (std::is_same<T, __nv_bfloat16>::value ? 1 : 0), 0, 0);
       constexpr int NCH = C::kChains;
       auto mma = [](uint32_t d, uint64_t a, uint64_t b, uint32_t id, uint32_t acc) {      // 32 bytes of K per instruction either way
-        if constexpr (sizeof(T) == 4) umma_tf32(d, a, b, id, acc); else umma_f16(d, a, b, id, acc);
+        if constexpr (PAIR) { if constexpr (sizeof(T) == 4) umma_tf32_pair(d, a, b, id, acc); else umma_f16_pair(d, a, b, id, acc); }
+        else { if constexpr (sizeof(T) == 4) umma_tf32(d, a, b, id, acc); else umma_f16(d, a, b, id, acc); }
       };
+      auto commit = [](uint64_t* bar) { if constexpr (PAIR) umma_commit_pair(bar, (uint16_t)3); else umma_commit(bar); };
       // Everything the 36 MMAs of a patch need is loop-invariant except the ring slot: the tap's operand is
       // the patch shifted by whole 128-byte pixel rows, i.e. a constant added to the descriptor's
       // (address >> 4) field.  Keeping those constants in registers and unrolling the tap loop matters: the
@@ -263,14 +298,14 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
 #pragma unroll
               for (int tap = 0; tap < 9; ++tap) {
                 const uint64_t da = da_base + (uint64_t)tapoff[tap];
-                const uint64_t db = db_base + (uint64_t)(tap * (C::kBTile >> 4));
+                const uint64_t db = db_base + (uint64_t)((cc * 9 + tap) * (C::kBTile >> 4));
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
                   const int i = tap * 4 + k;
                   mma(tmem_d + (i % NCH) * BN, da + 2 * k, db + 2 * k, idesc, i >= NCH ? 1u : later);
                 }
               }
-              umma_commit(&aempty[as]);
+              commit(&aempty[as]);
             }
             __syncwarp();
           } else {
@@ -286,8 +321,9 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
                   const int i = tap * 4 + k;
                   mma(tmem_d + (i % NCH) * BN, da + 2 * k, db + 2 * k, idesc, i >= NCH ? 1u : later);
                 }
-                if (CL == 1) umma_commit(&bempty[bsg]); else umma_commit_mc(&bempty[bsg], kMask);
-                if (tap == 8) umma_commit(&aempty[as]);
+                if constexpr (PAIR) commit(&bempty[bsg]);
+                else if (CL == 1) umma_commit(&bempty[bsg]); else umma_commit_mc(&bempty[bsg], kMask);
+                if (tap == 8) commit(&aempty[as]);
               }
               __syncwarp();
               if (++bsg == C::kBStages) { bsg = 0; bph ^= 1; }
@@ -295,12 +331,15 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
           }
           if (++as == C::kAStages) { as = 0; aph ^= 1; }
         }
-        if (elect_one_sync()) umma_commit(&tfull[acc]);
+        if (elect_one_sync()) commit(&tfull[acc]);
         __syncwarp();
       }
     }
   } else if (warp >= 4) {
     // ================= epilogue =================
+    auto release_acc = [&](int acc) {        // one arrival per epilogue warp; a pair's accumulators are released at the leader
+      if constexpr (PAIR) mbar_arrive_cluster(mapa_cluster(smem_u32(&tempty[acc]), 0)); else mbar_arrive(&tempty[acc]);
+    };
     const int quarter = warp & 3;                 // TMEM lane quarter this warp may read
     const int half = (warp - 4) >> 2;             // which half of the BN columns it drains
     const int ew = warp - 4;
@@ -356,7 +395,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         }
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&tempty[acc]);                // accumulators are in registers: hand the buffer back
+        if (lane == 0) release_acc(acc);                // accumulators are in registers: hand the buffer back
         if (has_add) {
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
@@ -462,7 +501,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         if (q == NIT - 1) {       // accumulators are in registers: hand the buffer back before the long tail
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(&tempty[acc]);
+          if (lane == 0) release_acc(acc);
         }
         if (valid && g.addend != nullptr) {
           const T* arow = reinterpret_cast<const T*>(g.addend) + (orow - out) + c0;
@@ -567,7 +606,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
   if (CL > 1) cluster_sync_all();
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, C::kTmemCols);
+    if constexpr (PAIR) tmem_dealloc_pair(tmem_base, C::kTmemCols); else tmem_dealloc(tmem_base, C::kTmemCols);
   }
 }
 
@@ -1078,14 +1117,14 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 EncodeTiledFn g_enc = nullptr;
 
-template <int BN, bool RES, typename T, int CL>
+template <int BN, bool RES, typename T, int CL, bool PAIR = false>
 int launch_t(void* y, const HaloGeom& g, const BnStats& bs, const CUtensorMap& tmX, const CUtensorMap& tmW, const CUtensorMap& tmY,
              cudaStream_t stream) {
-  using C = HCfg<BN, RES, sizeof(T) == 4>;
+  using C = HCfg<BN, RES, sizeof(T) == 4, PAIR>;
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  auto kern = k_conv3x3_halo<BN, RES, T, CL>;
+  auto kern = k_conv3x3_halo<BN, RES, T, CL, PAIR>;
   PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
   cudaLaunchConfig_t cfg = {};
   cfg.blockDim = dim3(kThreads);
@@ -1116,18 +1155,18 @@ int launch_t(void* y, const HaloGeom& g, const BnStats& bs, const CUtensorMap& t
   return (int)cudaGetLastError();
 }
 
-template <int BN, bool RES, int CL = 1>
+template <int BN, bool RES, int CL = 1, bool PAIR = false>
 int launch(const void* x, const void* w, void* y, int dtype, const HaloGeom& g, const BnStats& bs, const CUtensorMap& tmX,
            const CUtensorMap& tmW, const CUtensorMap& tmY, cudaStream_t stream) {
   (void)x; (void)w;
-  if constexpr (!RES) {
-    if (dtype == PDT_FP32) return launch_t<BN, RES, float, CL>(y, g, bs, tmX, tmW, tmY, stream);
+  if constexpr (!RES || PAIR) {
+    if (dtype == PDT_FP32) return launch_t<BN, RES, float, CL, PAIR>(y, g, bs, tmX, tmW, tmY, stream);
   }
-  if constexpr (BN == 64 && CL > 1) {
-    return PDT_E_UNSUPPORTED;                   // the 16-bit N = 64 kernel stores through TMA: no cluster form
+  if constexpr (BN == 64 && CL > 1 && !PAIR) {
+    return PDT_E_UNSUPPORTED;                   // the 16-bit N = 64 kernel stores through TMA: no multicast-cluster form
   } else {
-    if (dtype == PDT_FP16) return launch_t<BN, RES, __half, CL>(y, g, bs, tmX, tmW, tmY, stream);
-    return launch_t<BN, RES, __nv_bfloat16, CL>(y, g, bs, tmX, tmW, tmY, stream);
+    if (dtype == PDT_FP16) return launch_t<BN, RES, __half, CL, PAIR>(y, g, bs, tmX, tmW, tmY, stream);
+    return launch_t<BN, RES, __nv_bfloat16, CL, PAIR>(y, g, bs, tmX, tmW, tmY, stream);
   }
 }
 
@@ -1191,10 +1230,17 @@ int pdt_conv3x3_halo_add(const void* x, const void* w, void* y, const void* adde
   g.c_chunks = C / (int)kch;
   g.patch_bytes = (uint32_t)((g.TR + 2) * g.Wp * 128);
   if (1024 + (128 + 2 * g.Wp + 2) * 128 > 32768 || g.patch_bytes + 1024 > 32768) return PDT_E_UNSUPPORTED;
-  const bool resident = (C == 64 && K == 64 && !f32);
   int sms_q = 148;
   { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms_q, cudaDevAttrMultiProcessorCount, dev); }
-  const int cl = (K == 128 || f32) ? halo_cluster(g, sms_q, w, stream) : 1;
+  // CTA pairs (cta_group::2, no multicast load involved): when every pair has at least two tiles each; PDT_HALO_PAIR=0 disables
+  static int pair_env = -1;
+  if (pair_env < 0) { const char* e = getenv("PDT_HALO_PAIR"); pair_env = (e != nullptr && e[0] == '0') ? 0 : 1; }
+  // (measured per launch at 1200 images: 128-wide fp16 274 -> 245 us, fp32 550 -> 465 us; 64-wide fp32 846 -> 648 us with the
+  // filter bank resident as two halves; the 16-bit 64-wide kernel got SLOWER, 322 -> 386 us: its M = 256 x N = 64
+  // instructions are too short for one issuing thread, so it keeps single CTAs)
+  const bool pair = pair_env == 1 && g.num_tiles >= 2 * sms_q && (K == 128 || f32);
+  const bool resident = (C == 64 && K == 64 && (!f32 || pair));
+  const int cl = pair ? 2 : ((K == 128 || f32) ? halo_cluster(g, sms_q, w, stream) : 1);
   const CUtensorMapDataType dt = f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
                                      : (dtype == PDT_FP16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16);
   CUtensorMap tmX, tmW;
@@ -1236,10 +1282,13 @@ int pdt_conv3x3_halo_add(const void* x, const void* w, void* y, const void* adde
   bs.count = (long long)N * H * W;
   bs.comm = make_comm(comm);
   if (K == 64) {
+    if (resident && pair) return launch<64, true, 2, true>(x, w, y, dtype, g, bs, tmX, tmW, tmY, stream);
+    if (pair) return launch<64, false, 2, true>(x, w, y, dtype, g, bs, tmX, tmW, tmY, stream);
     if (resident) return launch<64, true>(x, w, y, dtype, g, bs, tmX, tmW, tmY, stream);
     if (f32 && cl == 2) return launch<64, false, 2>(x, w, y, dtype, g, bs, tmX, tmW, tmY, stream);
     return launch<64, false>(x, w, y, dtype, g, bs, tmX, tmW, tmY, stream);
   }
+  if (pair) return launch<128, false, 2, true>(x, w, y, dtype, g, bs, tmX, tmW, tmY, stream);
   if (cl == 2) return launch<128, false, 2>(x, w, y, dtype, g, bs, tmX, tmW, tmY, stream);
   return launch<128, false>(x, w, y, dtype, g, bs, tmX, tmW, tmY, stream);
 }
