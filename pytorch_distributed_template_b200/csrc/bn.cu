@@ -378,9 +378,12 @@ struct Pipe {
   }
   __device__ __forceinline__ void advance() { if (++s == S) { s = 0; ph ^= 1; } }
   // whole producer warp
-  __device__ __forceinline__ void produce(const void* const (&src)[NIN], long nvec) {
+  // rev: walk the chunks from the END of the tensor.  The kernel that wrote (or last read) these tensors went
+  // through them front to back, so what is still in the 126 MB L2 is their tail: start there.
+  __device__ __forceinline__ void produce(const void* const (&src)[NIN], long nvec, bool rev = false) {
     const long nchunks = (nvec + kChunkVecs - 1) / kChunkVecs;
-    for (long ch = blockIdx.x; ch < nchunks; ch += gridDim.x) {
+    for (long ci = blockIdx.x; ci < nchunks; ci += gridDim.x) {
+      const long ch = rev ? nchunks - 1 - ci : ci;
       mbar_wait(&empty[s], ph ^ 1);
       if (elect_one_sync()) {
         const long v0 = ch * kChunkVecs;
@@ -464,8 +467,8 @@ __global__ void __launch_bounds__(kThr, 2) k_fwd_apply(const T* __restrict__ x, 
   pipe.init(dsm);
   const int tid = threadIdx.x, cg = C / V;
   if (tid >= kCons) {
-    if constexpr (HAS_RES) { const void* src[2] = {x, res}; pipe.produce(src, nvec); }
-    else { const void* src[1] = {x}; pipe.produce(src, nvec); }
+    if constexpr (HAS_RES) { const void* src[2] = {x, res}; pipe.produce(src, nvec, true); }
+    else { const void* src[1] = {x}; pipe.produce(src, nvec, true); }
     return;
   }
   float sc[V], sh[V];
@@ -478,7 +481,8 @@ __global__ void __launch_bounds__(kThr, 2) k_fwd_apply(const T* __restrict__ x, 
   }
   uint4* out = reinterpret_cast<uint4*>(y);
   const long nchunks = (nvec + kChunkVecs - 1) / kChunkVecs;
-  for (long ch = blockIdx.x; ch < nchunks; ch += gridDim.x) {
+  for (long ci = blockIdx.x; ci < nchunks; ci += gridDim.x) {
+    const long ch = nchunks - 1 - ci;            // the producer's order (see Pipe::produce)
     pipe.wait_full();
 #pragma unroll
     for (int u = 0; u < kU; ++u) {
@@ -526,8 +530,8 @@ __global__ void __launch_bounds__(kThr, 2) k_bwd_reduce(const T* __restrict__ dy
 #pragma unroll
   for (int j = 0; j < V; ++j) s[j] = q[j] = 0.f;
   if (tid >= kCons) {
-    if constexpr (HAS_Y) { const void* src[3] = {dy, x, y}; pipe.produce(src, nvec); }
-    else { const void* src[2] = {dy, x}; pipe.produce(src, nvec); }
+    if constexpr (HAS_Y) { const void* src[3] = {dy, x, y}; pipe.produce(src, nvec, true); }
+    else { const void* src[2] = {dy, x}; pipe.produce(src, nvec, true); }
   } else {
     const bool remask = relu && !HAS_Y;
     float mu[V], sc[V], sh[V];
@@ -539,7 +543,8 @@ __global__ void __launch_bounds__(kThr, 2) k_bwd_reduce(const T* __restrict__ dy
       sh[j] = remask ? beta[c] - mean[c] * sc[j] : 0.f;
     }
     const long nchunks = (nvec + kChunkVecs - 1) / kChunkVecs;
-    for (long ch = blockIdx.x; ch < nchunks; ch += gridDim.x) {
+    for (long ci = blockIdx.x; ci < nchunks; ci += gridDim.x) {
+      const long ch = nchunks - 1 - ci;          // the producer's order (see Pipe::produce)
       pipe.wait_full();
 #pragma unroll
       for (int u = 0; u < kU; ++u) {
