@@ -1024,6 +1024,166 @@ __global__ void __launch_bounds__(256) k_bn_pool_bwd_apply_321(const T* __restri
   }
 }
 
+// ---- the same two kernels for fp32 activations (the fp32 training modes): FOUR channels per thread, so every access
+// is still one 16-byte vector and the same number of loads is in flight.  Without them the fp32 stem tail ran as
+// BN-apply + max-pool forward (2.7 ms at 1200 images) and max-pool backward + BN reduce + BN apply (6.9 ms),
+// i.e. it wrote and re-read the 112 x 112 x 64 normalised tensor and its gradient (3.85 GB each).
+__global__ void __launch_bounds__(256) k_bn_pool_fwd_321_f32(const float* __restrict__ x, float* __restrict__ y, int8_t* __restrict__ idx,
+                                                            float* __restrict__ xmax, PoolGeom g, const float* __restrict__ mean,
+                                                            const float* __restrict__ invstd, const float* __restrict__ gamma,
+                                                            const float* __restrict__ beta) {
+  pdl_enter();
+  extern __shared__ float sm[];
+  float* scale = sm;
+  float* shift = sm + g.C;
+  for (int c = threadIdx.x; c < g.C; c += blockDim.x) {
+    const float sc = gamma[c] * invstd[c];
+    scale[c] = sc;
+    shift[c] = beta[c] - mean[c] * sc;
+  }
+  __syncthreads();
+  const int cg = g.C / 4;
+  const unsigned total = (unsigned)g.N * g.Ho * g.Wo * cg;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int c0 = (int)(i % cg) * 4;
+    unsigned r = i / cg;
+    const int wo = (int)(r % g.Wo); r /= g.Wo;
+    const int ho = (int)(r % g.Ho);
+    const int n = (int)(r / g.Ho);
+    const int h0 = 2 * ho - 1, w0 = 2 * wo - 1;
+    float4 u[9];
+    bool ok[9];
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh)
+#pragma unroll
+      for (int kw = 0; kw < 3; ++kw) {
+        const int h = h0 + kh, w = w0 + kw;
+        ok[kh * 3 + kw] = (unsigned)h < (unsigned)g.H && (unsigned)w < (unsigned)g.W;
+        u[kh * 3 + kw] = ok[kh * 3 + kw] ? __ldg(reinterpret_cast<const float4*>(x + (((size_t)n * g.H + h) * g.W + w) * g.C + c0))
+                                         : make_float4(0.f, 0.f, 0.f, 0.f);   // neighbours share pixels: keep them in L1
+      }
+    float sc[4], sh[4];
+    bool any_zero = false;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { sc[j] = scale[c0 + j]; sh[j] = shift[c0 + j]; any_zero |= (sc[j] == 0.f); }
+    float best[4], bx[4], by[4];
+    int bi[4];
+    if (!any_zero) {
+      // relu(sc*x + sh) is monotonic in x: the window's arg-max is the arg-max of x (sc > 0) or of -x (sc < 0)
+      float sg[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { sg[j] = sc[j] > 0.f ? 1.f : -1.f; best[j] = -INFINITY; bi[j] = 0; }
+#pragma unroll
+      for (int t = 0; t < 9; ++t) {
+        if (!ok[t]) continue;
+        const float f[4] = {u[t].x, u[t].y, u[t].z, u[t].w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float key = f[j] * sg[j];
+          if (key > best[j]) { best[j] = key; bi[j] = t; }
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { bx[j] = best[j] * sg[j]; by[j] = fmaxf(fmaf(bx[j], sc[j], sh[j]), 0.f); }
+    } else {
+      // a zero scale makes every tap tie: element-wise scan with first-tap-wins semantics
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { by[j] = -INFINITY; bi[j] = 0; bx[j] = 0.f; }
+#pragma unroll
+      for (int t = 0; t < 9; ++t) {
+        if (!ok[t]) continue;
+        const float f[4] = {u[t].x, u[t].y, u[t].z, u[t].w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float v = fmaxf(fmaf(f[j], sc[j], sh[j]), 0.f);
+          if (v > by[j]) { by[j] = v; bi[j] = t; bx[j] = f[j]; }
+        }
+      }
+    }
+    const size_t o = (((size_t)n * g.Ho + ho) * g.Wo + wo) * g.C + c0;
+    *reinterpret_cast<float4*>(y + o) = make_float4(by[0], by[1], by[2], by[3]);
+    *reinterpret_cast<float4*>(xmax + o) = make_float4(bx[0], bx[1], bx[2], bx[3]);
+    *reinterpret_cast<uint32_t*>(idx + o) = (uint32_t)(bi[0] & 0xff) | ((uint32_t)(bi[1] & 0xff) << 8) | ((uint32_t)(bi[2] & 0xff) << 16) |
+                                            ((uint32_t)(bi[3] & 0xff) << 24);
+  }
+}
+
+// d with the channels whose saved arg-max (one byte each in k) is not `tap` zeroed.
+__device__ __forceinline__ float4 keep_tap_f32(const float4& d, uint32_t k, uint32_t tap) {
+  return make_float4((k & 0xffu) == tap ? d.x : 0.f, ((k >> 8) & 0xffu) == tap ? d.y : 0.f, ((k >> 16) & 0xffu) == tap ? d.z : 0.f,
+                     (k >> 24) == tap ? d.w : 0.f);
+}
+__device__ __forceinline__ float4 add4(const float4& a, const float4& b) { return make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w); }
+
+__global__ void __launch_bounds__(256) k_bn_pool_bwd_apply_321_f32(const float* __restrict__ dpool, const int8_t* __restrict__ idx,
+                                                                  const float* __restrict__ x, float* __restrict__ dx, PoolGeom g,
+                                                                  const float* __restrict__ mean, const float* __restrict__ invstd,
+                                                                  const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                                  const float* __restrict__ k) {
+  pdl_enter();
+  extern __shared__ float sm[];
+  const int C = g.C;
+  float* ca = sm;            // dx = a*gg + b*x + c per channel (see k_bn_pool_bwd_apply_321); sh = forward shift
+  float* cb = sm + C;
+  float* cc = sm + 2 * C;
+  float* sh = sm + 3 * C;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const float a = invstd[c] * gamma[c];
+    ca[c] = a;
+    cb[c] = -k[C + c] * a;
+    cc[c] = (mean[c] * k[C + c] - k[c]) * a;
+    sh[c] = beta[c] - mean[c] * a;
+  }
+  __syncthreads();
+  const int cg = C / 4, Hh = g.H / 2, Wh = g.W / 2;
+  const unsigned total = (unsigned)g.N * Hh * Wh * cg;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int c0 = (int)(i % cg) * 4;
+    unsigned r = i / cg;
+    const int b = (int)(r % Wh); r /= Wh;
+    const int a = (int)(r % Hh);
+    const int n = (int)(r / Hh);
+    const bool a1 = a + 1 < g.Ho, b1 = b + 1 < g.Wo;
+    const size_t p00 = (((size_t)n * g.Ho + a) * g.Wo + b) * C + c0;
+    const size_t p01 = p00 + C, p10 = p00 + (size_t)g.Wo * C, p11 = p10 + C;
+    const size_t x00 = (((size_t)n * g.H + 2 * a) * g.W + 2 * b) * C + c0;
+    const size_t x01 = x00 + C, x10 = x00 + (size_t)g.W * C, x11 = x10 + C;
+    const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    const uint32_t zk = 0xffffffffu;                                       // tap 255 never matches
+    const uint32_t k00 = __ldg(reinterpret_cast<const uint32_t*>(idx + p00));
+    const uint32_t k01 = b1 ? __ldg(reinterpret_cast<const uint32_t*>(idx + p01)) : zk;
+    const uint32_t k10 = a1 ? __ldg(reinterpret_cast<const uint32_t*>(idx + p10)) : zk;
+    const uint32_t k11 = (a1 && b1) ? __ldg(reinterpret_cast<const uint32_t*>(idx + p11)) : zk;
+    const float4 d00 = __ldg(reinterpret_cast<const float4*>(dpool + p00));   // each pooled output serves 4 blocks: L1
+    const float4 d01 = b1 ? __ldg(reinterpret_cast<const float4*>(dpool + p01)) : z4;
+    const float4 d10 = a1 ? __ldg(reinterpret_cast<const float4*>(dpool + p10)) : z4;
+    const float4 d11 = (a1 && b1) ? __ldg(reinterpret_cast<const float4*>(dpool + p11)) : z4;
+    uint4 xr[4];
+    xr[0] = ldg_stream(x + x00); xr[1] = ldg_stream(x + x01); xr[2] = ldg_stream(x + x10); xr[3] = ldg_stream(x + x11);
+    float4 gsum[4];
+    gsum[0] = keep_tap_f32(d00, k00, 4);
+    gsum[1] = add4(keep_tap_f32(d00, k00, 5), keep_tap_f32(d01, k01, 3));
+    gsum[2] = add4(keep_tap_f32(d00, k00, 7), keep_tap_f32(d10, k10, 1));
+    gsum[3] = add4(add4(add4(keep_tap_f32(d00, k00, 8), keep_tap_f32(d01, k01, 6)), keep_tap_f32(d10, k10, 2)), keep_tap_f32(d11, k11, 0));
+    float fa[4], fb[4], fc[4], fs[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { fa[j] = ca[c0 + j]; fb[j] = cb[c0 + j]; fc[j] = cc[c0 + j]; fs[j] = sh[c0 + j]; }
+    const size_t xo[4] = {x00, x01, x10, x11};
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float gy[4] = {gsum[q].x, gsum[q].y, gsum[q].z, gsum[q].w};
+      const float xf[4] = {__uint_as_float(xr[q].x), __uint_as_float(xr[q].y), __uint_as_float(xr[q].z), __uint_as_float(xr[q].w)};
+      float o[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float gg = fmaf(xf[j], fa[j], fs[j]) > 0.f ? gy[j] : 0.f;
+        o[j] = fmaf(gg, fa[j], fmaf(xf[j], fb[j], fc[j]));
+      }
+      *reinterpret_cast<float4*>(dx + xo[q]) = make_float4(o[0], o[1], o[2], o[3]);
+    }
+  }
+}
+
 template <typename T> bool shape_ok(int C) {
   const int V = Vec<T>::N;
   if (C % V) return false;
@@ -1097,6 +1257,12 @@ extern "C" {
 
 size_t pdt_bn_scratch_bytes(int C) { return (size_t)PDT_BN_MAX_BLOCKS * 2 * C * sizeof(float) + 256; }
 
+#define BN_DISPATCH(dtype, ...)                                                      \
+  if (dtype == PDT_BF16) { using T = __nv_bfloat16; __VA_ARGS__; }                   \
+  else if (dtype == PDT_FP16) { using T = __half; __VA_ARGS__; }                     \
+  else if (dtype == PDT_FP32) { using T = float; __VA_ARGS__; }                      \
+  else return PDT_E_UNSUPPORTED;
+
 #define BNP_DISPATCH(dtype, ...)                                      \
   if (dtype == PDT_BF16) { using T = __nv_bfloat16; __VA_ARGS__; }    \
   else if (dtype == PDT_FP16) { using T = __half; __VA_ARGS__; }      \
@@ -1113,6 +1279,15 @@ int pdt_bn_pool_fwd(const void* x, void* y, int8_t* idx, void* xmax, int dtype, 
                     int pd, const float* mean, const float* invstd, const float* gamma, const float* beta, cudaStream_t stream) {
   PoolGeom g;
   if (!pool_geom(g, N, H, W, C, ks, st, pd)) return PDT_E_UNSUPPORTED;
+  if (dtype == PDT_FP32) {         // fp32: the 3x3 / 2 / 1 window (the ResNet stem) only, four channels per thread
+    if (!(ks == 3 && st == 2 && pd == 1) || (reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) |
+                                             reinterpret_cast<uintptr_t>(xmax)) % 16 != 0) return PDT_E_UNSUPPORTED;
+    long nb4 = ((long)N * g.Ho * g.Wo * (C / 4) + 255) / 256;
+    if (nb4 > 148 * 16) nb4 = 148 * 16;
+    launch_pdl(k_bn_pool_fwd_321_f32, dim3((unsigned)nb4), dim3(256), 2 * C * sizeof(float), stream, reinterpret_cast<const float*>(x),
+               reinterpret_cast<float*>(y), idx, reinterpret_cast<float*>(xmax), g, mean, invstd, gamma, beta);
+    return (int)cudaGetLastError();
+  }
   const long total = (long)N * g.Ho * g.Wo * (C / 8);
   long nb = (total + 255) / 256;
   if (nb > 148 * 16) nb = 148 * 16;
@@ -1141,12 +1316,12 @@ int pdt_bn_pool_bwd_reduce(const void* dpool, const void* ypool, const void* xma
   unsigned* counter = reinterpret_cast<unsigned*>(scratch);
   float* partial = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + 256);
   const long Mp = (long)N * g.Ho * g.Wo;
-  BNP_DISPATCH(dtype, {
+  BN_DISPATCH(dtype, {
     if (!shape_ok<T>(C)) return PDT_E_UNSUPPORTED;
     if (stream_enabled() && sp::ok<T>(C, {dpool, ypool, xmax})) return bwd_reduce_stream<T>(dpool, ypool, xmax, Mp, C, mean, invstd, gamma, beta, 1,
                                                                                             partial, counter, comm, dgamma, dbeta, out_k,
                                                                                             (long)N * H * W, stream);
-    k_bn_bwd_reduce<T><<<stats_blocks(Mp, C, 8), kThreads, 0, stream>>>(
+    k_bn_bwd_reduce<T><<<stats_blocks(Mp, C, Vec<T>::N), kThreads, 0, stream>>>(
         reinterpret_cast<const T*>(dpool), reinterpret_cast<const T*>(ypool), reinterpret_cast<const T*>(xmax), Mp, C, mean,
         invstd, gamma, beta, 1, partial, counter, make_comm(comm), dgamma, dbeta, out_k, (long)N * H * W);
   });
@@ -1159,6 +1334,16 @@ int pdt_bn_pool_bwd_apply(const void* dpool, const int8_t* idx, const void* x, v
   PoolGeom g;
   if (!pool_geom(g, N, H, W, C, ks, st, pd)) return PDT_E_UNSUPPORTED;
   if (((C / 8) & (C / 8 - 1)) != 0) return PDT_E_UNSUPPORTED;
+  if (dtype == PDT_FP32) {
+    if (!(ks == 3 && st == 2 && pd == 1 && H % 2 == 0 && W % 2 == 0) ||
+        (reinterpret_cast<uintptr_t>(dpool) | reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(dx)) % 16 != 0) return PDT_E_UNSUPPORTED;
+    long nb4 = ((long)N * (H / 2) * (W / 2) * (C / 4) + 255) / 256;
+    if (nb4 > 148 * 32) nb4 = 148 * 32;
+    launch_pdl(k_bn_pool_bwd_apply_321_f32, dim3((unsigned)nb4), dim3(256), 4 * C * sizeof(float), stream,
+               reinterpret_cast<const float*>(dpool), idx, reinterpret_cast<const float*>(x), reinterpret_cast<float*>(dx), g, mean, invstd,
+               gamma, beta, k);
+    return (int)cudaGetLastError();
+  }
   if (ks == 3 && st == 2 && pd == 1 && H % 2 == 0 && W % 2 == 0) {
     const long total = (long)N * (H / 2) * (W / 2) * (C / 8);
     long nb = (total + 255) / 256;
@@ -1175,11 +1360,6 @@ int pdt_bn_pool_bwd_apply(const void* dpool, const int8_t* idx, const void* x, v
   return (int)cudaGetLastError();
 }
 
-#define BN_DISPATCH(dtype, ...)                                                      \
-  if (dtype == PDT_BF16) { using T = __nv_bfloat16; __VA_ARGS__; }                   \
-  else if (dtype == PDT_FP16) { using T = __half; __VA_ARGS__; }                     \
-  else if (dtype == PDT_FP32) { using T = float; __VA_ARGS__; }                      \
-  else return PDT_E_UNSUPPORTED;
 
 int pdt_bn_fwd_stats(const void* x, long M, int C, int dtype, void* scratch, const PdtCommDesc* comm,
                      float* running_mean, float* running_var, float momentum, float eps, float* save_mean,

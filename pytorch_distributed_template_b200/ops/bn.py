@@ -311,13 +311,22 @@ def bn_act(x, bn, residual=None, relu=False, comm=None, group=None, stats=None, 
     return F.relu(y) if relu else y
 
 
+def _pool_fusable(x, ks, st, pd):
+    """Shapes the fused BN + ReLU + max-pool kernels serve: any window in 16 bit; fp32 has the 3x3 / 2 / 1 form (the
+    ResNet stem) over even maps only.  PDT_BN_POOL_F32=0 sends fp32 through the separate kernels."""
+    if x.dtype != torch.float32:
+        return True
+    return ((ks, st, pd) == (3, 2, 1) and x.shape[2] % 2 == 0 and x.shape[3] % 2 == 0
+            and os.environ.get("PDT_BN_POOL_F32", "1") == "1")
+
+
 def bn_relu_maxpool(x, bn, kernel_size=3, stride=2, padding=1, comm=None, group=None):
     """``max_pool2d(relu(bn(x)))``; one fused kernel set on the native training path."""
     C = x.shape[1]
     training = bn.training or bn.running_mean is None
     sync = training and (comm is not None or group is not None)
-    if (training and torch.is_grad_enabled() and _native_ok(x, C) and x.dtype != torch.float32
-            and (not sync or comm is not None) and x.numel() // 8 < 4_000_000_000):
+    if (training and torch.is_grad_enabled() and _native_ok(x, C) and _pool_fusable(x, kernel_size, stride, padding)
+            and (not sync or comm is not None) and x.numel() // 4 < 4_000_000_000):
         momentum = _ema_factor(bn)
         if bn.track_running_stats and bn.num_batches_tracked is not None:
             _bump(bn.num_batches_tracked)
@@ -341,7 +350,7 @@ def conv_bn_relu_maxpool(x, conv, bn, kernel_size=3, stride=2, padding=1, comm=N
         if isinstance(out, tuple):
             y, mean, invstd = out
             C = y.shape[1]
-            if _native_ok(y, C) and y.dtype != torch.float32 and y.numel() // 8 < 4_000_000_000:
+            if _native_ok(y, C) and _pool_fusable(y, kernel_size, stride, padding) and y.numel() // 4 < 4_000_000_000:
                 if bn.num_batches_tracked is not None:
                     _bump(bn.num_batches_tracked)
                 return _BNReluPoolNative.apply(y, bn.weight, bn.bias, None, None, momentum, bn.eps, kernel_size, stride,

@@ -267,7 +267,7 @@ def test_resnet18_amp_step_matches_torch_autocast(native_lib, lp):
         env.shutdown_distributed()
 
 
-@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
 @pytest.mark.parametrize("shape,geom", [((5, 64, 112, 112), (3, 2, 1)), ((3, 64, 30, 34), (3, 2, 1)),
                                         ((2, 64, 31, 33), (3, 2, 1)),      # odd extent: generic dx kernel
                                         ((2, 32, 24, 20), (2, 2, 0))])     # other geometry: generic kernels
