@@ -19,7 +19,7 @@
 
 /* Bumped whenever an entry point is added or changes its signature; the Python binding refuses a library
  * that reports a different number (a stale build of an older checkout). */
-#define PDT_ABI_VERSION 12
+#define PDT_ABI_VERSION 13
 
 #ifdef __cplusplus
 extern "C" {
@@ -260,6 +260,11 @@ int pdt_stem_conv_supported(int dtype, int N, int HP, int WP, int K);
 int pdt_stem_conv(const void* xs, const void* wp, void* y, int dtype, int N, int HP, int WP, int K, void* scratch,
                   const PdtCommDesc* comm, float* running_mean, float* running_var, float momentum, float eps,
                   float* save_mean, float* save_invstd, cudaStream_t stream);
+/* Stem weight gradient with the same patch reuse (16-bit, 64 output channels, output rows of 16..128 pixels in
+ * 16-pixel steps): dwp [64][4][4][16] fp32 += sum over output pixels (zero it first; accumulates with red.add,
+ * so the deterministic mode keeps pdt_conv_wgrad_ex).  xs [N][HP][WP][16], dy [N][HP-3][WP-3][64]. */
+int pdt_stem_wgrad_supported(int dtype, int N, int HP, int WP, int K);
+int pdt_stem_wgrad(const void* xs, const void* dy, float* dwp, int dtype, int N, int HP, int WP, int K, cudaStream_t stream);
 /* Weight gradient (cudnnConvolutionBackwardFilter): dw [K][R][S][C] fp32 += sum over pixels; split-K over
  * the pixel dimension with red.global.add, so zero dw first.  C % 64 == 0, K % 64 == 0. */
 int pdt_conv_wgrad(const void* x, const void* dy, float* dw, int dtype, int N, int H, int W, int C, int K, int R, int S,

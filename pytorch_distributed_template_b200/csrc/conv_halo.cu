@@ -94,6 +94,11 @@ __device__ __forceinline__ void tma_load_4d(void* smem, const CUtensorMap* m, ui
       ::"r"(smem_u32(smem)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c), "r"(w), "r"(h), "r"(n) : "memory");
 }
 
+__device__ __forceinline__ void tma_load_3d(void* smem, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(smem_u32(smem)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
 // The same for a CTA pair: the data lands in THIS CTA's shared memory, the bytes are signalled on the leader's barrier.
 __device__ __forceinline__ void tma_load_4d_pair(void* smem, const CUtensorMap* m, uint32_t bar_cluster_addr, int c, int w, int h, int n) {
   asm volatile(
@@ -884,6 +889,142 @@ k_wgrad3x3_halo_tf32(const __grid_constant__ CUtensorMap tmX, const __grid_const
   }
 }
 
+// ---- stem weight gradient: dW'[k][r][s][c] = sum over output pixels of dy[n,p,q,k] * xs[n, p+r, q+s, c] (4x4 taps over the
+// space-to-depth image, 16 channels per pixel).  The generic split-K kernel builds each 128-byte operand row (four
+// neighbouring pixels) with an im2col load per filter row and M tile, pulling every pixel 16 times and every dy
+// element twice out of L2 (1.0 ms at 1200 images, bound by L2 -> SM traffic).  Here a tile is TR output rows of one
+// image: the TR + 3 image rows it touches arrive ONCE as linear 32-byte pixel rows (32-byte swizzle), and the A
+// operand of filter row r is that patch read MN-major: 16 channels of a pixel are one 32-byte atom along M, the
+// NEXT atom (leading-dimension offset 32 B) is the next pixel, i.e. the next horizontal tap, and the reduction index
+// (the output pixel q) also advances one pixel per row: M = 128 rows are taps s = 0..7 x 16 channels of which
+// s < 4 are real (an M = 64 instruction costs the same tensor time), against dy's 64 channels (N = 64).  Four
+// accumulators (r = 0..3) stay in TMEM for the whole kernel and are added into dW' once per CTA.
+struct SWCfg {
+  static constexpr int kStages = 2;
+  static constexpr int kTR = 4;                        // output rows per tile
+  static constexpr int kAStage = 1024 * 32;            // 1024 linear pixel slots (>= (kTR + 3) * WP + 8)
+  static constexpr int kBStage = kTR * 128 * 128;      // kTR rows of up to 128 pixels x 64 channels
+  static constexpr int kSmemBytes = kStages * (kAStage + kBStage) + 1024 + 128;
+  static_assert(kSmemBytes <= 232448, "over the 227 KB shared-memory limit of sm_100");
+};
+struct StemWGeom {
+  int N, HP, WP, P, Q;
+  int tiles_per_image, num_tiles;
+};
+
+template <typename T>
+__global__ void __launch_bounds__(128, 1)
+k_stem_wgrad(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmDY, float* __restrict__ dw, const StemWGeom g) {
+  using W = SWCfg;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smA = smem;
+  uint8_t* smB = smem + W::kStages * W::kAStage;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smB + W::kStages * W::kBStage);
+  uint64_t* empty = full + W::kStages;
+  uint64_t* done = empty + W::kStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done + 1);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) { prefetch_tmap(&tmX); prefetch_tmap(&tmDY); }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < W::kStages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    mbar_init(done, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, 256);
+  {   // dy rows shorter than 128 pixels leave gaps no TMA box writes: zeros, not stale shared memory (0 * NaN = NaN)
+    uint4* z = reinterpret_cast<uint4*>(smem);
+    const int n16 = W::kStages * (W::kAStage + W::kBStage) / 16;
+    for (int i = threadIdx.x; i < n16; i += blockDim.x) z[i] = make_uint4(0, 0, 0, 0);
+  }
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_enter();
+  const int qsteps = g.Q >> 4;                               // 16-pixel k-steps per output row
+  const uint32_t dy_half_bytes = (uint32_t)(2 * g.Q) * 128u; // one dy load: two output rows
+
+  if (warp == 0) {
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x) {
+      const int n = tile / g.tiles_per_image;
+      const int p0 = (tile - n * g.tiles_per_image) * W::kTR;
+      mbar_wait(&empty[stage], phase ^ 1);
+      if (elect_one_sync()) {
+        mbar_expect_tx(&full[stage], (uint32_t)W::kAStage + 2 * dy_half_bytes);
+        const long long slot0 = ((long long)n * g.HP + p0) * g.WP;
+#pragma unroll
+        for (int i = 0; i < 4; ++i)          // 4 x 256 pixel slots; slots past the image array are zero-filled
+          tma_load_2d(smA + stage * W::kAStage + i * 8192, &tmX, &full[stage], 0, (int)(slot0 + 256 * i));
+#pragma unroll
+        for (int i = 0; i < 2; ++i)          // rows p0 + 2i, p0 + 2i + 1 of dy; rows past P are zero-filled
+          tma_load_3d(smB + stage * W::kBStage + i * dy_half_bytes, &tmDY, &full[stage], 0, (p0 + 2 * i) * g.Q, n);
+      }
+      __syncwarp();
+      if (++stage == W::kStages) { stage = 0; phase ^= 1; }
+    }
+  } else if (warp == 1) {
+    constexpr uint32_t idesc = make_idesc(128, 64, std::is_same<T, __nv_bfloat16>::value ? 1 : 0, 1, 1);
+    int stage = 0;
+    uint32_t phase = 0;
+    bool first = true;
+    for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x) {
+      mbar_wait(&full[stage], phase);
+      tc_fence_after();
+      // A: 32-byte swizzle (layout type 6), 8-pixel groups 256 B apart along the reduction, atoms 32 B apart along M
+      const uint64_t da0 = make_sw128_desc(smem_u32(smA + stage * W::kAStage), 256, 32, 6);
+      const uint64_t db0 = make_sw128_desc(smem_u32(smB + stage * W::kBStage), 1024, 1024);
+      if (elect_one_sync()) {
+        for (int j = 0; j < W::kTR; ++j)
+          for (int ks = 0; ks < qsteps; ++ks) {
+            const uint32_t accum = (first && j == 0 && ks == 0) ? 0u : 1u;
+            const uint64_t db = db0 + (uint64_t)((j * g.Q + ks * 16) * 8);
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+              umma_f16(tmem_base + r * 64, da0 + (uint64_t)(((j + r) * g.WP + ks * 16) * 2), db, idesc, accum);
+          }
+        umma_commit(&empty[stage]);
+      }
+      __syncwarp();
+      first = false;
+      if (++stage == W::kStages) { stage = 0; phase ^= 1; }
+    }
+    if (elect_one_sync()) umma_commit(done);
+    __syncwarp();
+  }
+  __syncwarp();
+  // ---- drain: accumulator row m = s * 16 + c; rows 64..127 (warps 2, 3) are the phantom taps s = 4..7 ----
+  if (blockIdx.x < g.num_tiles) {
+    mbar_wait(done, 0);
+    tc_fence_after();
+    const int m = warp * 32 + lane;
+#pragma unroll 1
+    for (int r = 0; r < 4; ++r) {
+#pragma unroll 1
+      for (int c0 = 0; c0 < 64; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + r * 64 + c0, v);
+        tmem_ld_wait();
+        if (warp < 2) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i)       // dw'[k][r][s][c], k = c0 + i: a warp's lanes cover 32 consecutive (s, c)
+            atomicAdd(dw + (size_t)(c0 + i) * 256 + r * 64 + m, __uint_as_float(v[i]));
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 256);
+  }
+}
+
 // ---- stem: 4x4 / stride 1 convolution over the space-to-depth image, 16 channels per pixel -----------
 // (torchvision's 7x7 / stride 2 conv1 after pdt_stem_s2d).  The generic kernel builds each K row from four
 // neighbouring 32-byte pixels with an im2col load per filter row, i.e. it pulls every pixel 16 times from
@@ -1365,6 +1506,68 @@ int pdt_conv3x3_wgrad_halo(const void* x, const void* dy, float* dw, int dtype, 
     auto kern = k_wgrad3x3_halo<__nv_bfloat16>;
     PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, WHCfg::kSmemBytes));
     PDT_CHECK(launch_pdl(kern, dim3(grid), dim3(128), WHCfg::kSmemBytes, stream, tmX, tmDY, dw, g));
+  }
+  return (int)cudaGetLastError();
+}
+
+// 1 if pdt_stem_wgrad serves this stem weight gradient (16-bit, 64 output channels, output rows of 16..128 pixels in
+// whole 16-pixel steps).  Not used in deterministic mode (it accumulates with red.add).
+int pdt_stem_wgrad_supported(int dtype, int N, int HP, int WP, int K) {
+  if (dtype != PDT_BF16 && dtype != PDT_FP16) return 0;
+  const int P = HP - 3, Q = WP - 3;
+  if (K != 64 || N < 1 || P < 1 || Q < 16 || Q > 128 || Q % 16) return 0;
+  if ((SWCfg::kTR + 3) * WP + 8 > 1024) return 0;
+  if ((long long)N * HP * WP > 2000000000ll || (long long)N * HP * WP < 256) return 0;
+  return 1;
+}
+
+// xs: [N][HP][WP][16] space-to-depth image, dy: [N][HP-3][WP-3][64], dwp: [64][4][4][16] fp32, ACCUMULATED into.
+int pdt_stem_wgrad(const void* xs, const void* dy, float* dwp, int dtype, int N, int HP, int WP, int K, cudaStream_t stream) {
+  if (!pdt_stem_wgrad_supported(dtype, N, HP, WP, K)) return PDT_E_UNSUPPORTED;
+  if ((reinterpret_cast<uintptr_t>(xs) | reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(dwp)) & 15) return PDT_E_UNSUPPORTED;
+  if (g_enc == nullptr) {
+    cudaDriverEntryPointQueryResult q;
+    void* fn = nullptr;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q);
+    if (e != cudaSuccess || fn == nullptr) return (int)(e != cudaSuccess ? e : cudaErrorUnknown);
+    g_enc = reinterpret_cast<EncodeTiledFn>(fn);
+  }
+  StemWGeom g;
+  g.N = N; g.HP = HP; g.WP = WP; g.P = HP - 3; g.Q = WP - 3;
+  g.tiles_per_image = (g.P + SWCfg::kTR - 1) / SWCfg::kTR;
+  g.num_tiles = N * g.tiles_per_image;
+  const CUtensorMapDataType dt = dtype == PDT_FP16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  CUtensorMap tmX, tmDY;
+  {
+    cuuint64_t dims[2] = {16, (cuuint64_t)N * HP * WP};
+    cuuint64_t strides[1] = {32};
+    cuuint32_t box[2] = {16, 256};
+    cuuint32_t estr[2] = {1, 1};
+    if (g_enc(&tmX, dt, 2, const_cast<void*>(xs), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return 10011;
+  }
+  {
+    cuuint64_t dims[3] = {64, (cuuint64_t)g.P * g.Q, (cuuint64_t)N};
+    cuuint64_t strides[2] = {128, (cuuint64_t)g.P * g.Q * 128};
+    cuuint32_t box[3] = {64, (cuuint32_t)(2 * g.Q), 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    if (g_enc(&tmDY, dt, 3, const_cast<void*>(dy), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return 10012;
+  }
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int grid = g.num_tiles < sms ? g.num_tiles : sms;
+  if (dtype == PDT_FP16) {
+    auto kern = k_stem_wgrad<__half>;
+    PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SWCfg::kSmemBytes));
+    PDT_CHECK(launch_pdl(kern, dim3(grid), dim3(128), SWCfg::kSmemBytes, stream, tmX, tmDY, dwp, g));
+  } else {
+    auto kern = k_stem_wgrad<__nv_bfloat16>;
+    PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SWCfg::kSmemBytes));
+    PDT_CHECK(launch_pdl(kern, dim3(grid), dim3(128), SWCfg::kSmemBytes, stream, tmX, tmDY, dwp, g));
   }
   return (int)cudaGetLastError();
 }

@@ -31,6 +31,8 @@ _native.register("pdt_conv_wgrad_ex", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _l
 _native.register("pdt_stem_s2d", [_vp, _vp, _i, _i, _i, _i, _i, _vp])
 _native.register("pdt_stem_s2d_u8", [_vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _vp])
 _native.register("pdt_stem_conv_supported", [_i, _i, _i, _i, _i])
+_native.register("pdt_stem_wgrad_supported", [_i, _i, _i, _i, _i])
+_native.register("pdt_stem_wgrad", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp])
 _native.register("pdt_stem_conv", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, _native._PC, _vp, _vp, _native._f, _native._f, _vp, _vp, _vp])
 _native.register("pdt_dgrad_weight", [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp])
 _native.register("pdt_dgrad_weight_batched", [_vp, _i, _i, _vp])
@@ -575,6 +577,13 @@ class _StemNative(torch.autograd.Function):
             return None, stem_weight_grad_from_s2d(dwp4.permute(0, 2, 3, 1).reshape(K, 256), K), None
         dwp = torch.zeros((K, 256), dtype=torch.float32, device=dy.device)
         _native.ensure_deterministic(dy.device)
+        lib = _native.lib()
+        if (os.environ.get("PDT_STEM_WGRAD", "patch") == "patch" and not _native.deterministic()
+                and lib.pdt_stem_wgrad_supported(_native.dtype_code(dy.dtype), N, HP, WP, K) == 1):
+            # the image rows of a tile arrive once; every tap is a shifted MN-major view of them (conv_halo.cu: k_stem_wgrad)
+            _native.check(lib.pdt_stem_wgrad(xs.data_ptr(), dy.data_ptr(), dwp.data_ptr(), _native.dtype_code(dy.dtype), N, HP, WP, K,
+                                             _native.stream_ptr(dy.device)), "pdt_stem_wgrad")
+            return None, stem_weight_grad_from_s2d(dwp, K), None
         g = _StemNative._geom(xs.dtype, HP, WP, Q)
         _native.check(_native.lib().pdt_conv_wgrad_ex(
             xs.data_ptr(), dy.data_ptr(), dwp.data_ptr(), _native.dtype_code(dy.dtype), N, HP, g["Wt"], g["C"], g["C"],

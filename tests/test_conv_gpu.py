@@ -113,6 +113,26 @@ def test_stem_space_to_depth(native_lib, dtype, batch, hw):
     assert (conv.weight.grad - wf.grad).abs().max().item() <= 3e-3 * max(1.0, wf.grad.abs().max().item())
 
 
+@pytest.mark.parametrize("shape", [(5, 68, 64), (2, 224, 160), (150, 32, 32)])
+def test_stem_weight_gradient_patch_kernel(native_lib, shape):
+    """k_stem_wgrad (shifted MN-major views of the space-to-depth rows) vs autograd; 68 rows: a partial last tile."""
+    from pytorch_distributed_template_b200.ops import conv_native, _native
+    torch.backends.cudnn.allow_tf32 = False
+    torch.manual_seed(15)
+    dev = torch.device("cuda", 0)
+    n, h, w = shape
+    assert _native.lib().pdt_stem_wgrad_supported(_native.dtype_code(torch.float16), n, (h + 6) // 2, (w + 6) // 2, 64) == 1
+    conv = torch.nn.Conv2d(3, 64, 7, 2, 3, bias=False).to(dev)
+    x = torch.randn(n, 3, h, w, device=dev)
+    w_lp = conv.weight.detach().to(torch.float16)
+    y = conv_native.stem_native(x, conv, w_lp)
+    dy = (torch.randn_like(y.float()) / 16).to(torch.float16).contiguous(memory_format=torch.channels_last)
+    y.backward(dy)
+    wf = w_lp.float().requires_grad_(True)
+    F.conv2d(x.half().float(), wf, None, 2, 3).backward(dy.float())
+    assert (conv.weight.grad - wf.grad).abs().max().item() <= 3e-3 * max(1.0, wf.grad.abs().max().item())
+
+
 @pytest.mark.parametrize("B", [150, 37])
 def test_linear_native(native_lib, B):
     from pytorch_distributed_template_b200.ops import conv_native
