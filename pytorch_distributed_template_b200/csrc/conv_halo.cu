@@ -45,6 +45,8 @@ struct HaloGeom {
   int c_chunks;
   uint32_t patch_bytes;   // (TR + 2) * Wp * 128
   const void* addend;     // optional [N][H][W][K] tensor added to the output in the epilogue (residual-gradient sum), or null
+  int dw_ct;              // weight-gradient kernels: input channels of the WHOLE layer (the row length of dw); a launch
+                          // handles one 64 x 64 (input, output) channel slice of it
 };
 
 struct BnStats {
@@ -741,7 +743,7 @@ k_wgrad3x3_halo(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
         if (tap < 9) {
 #pragma unroll
           for (int i = 0; i < 32; ++i)       // dw[k][tap][c], k = c0 + i: the 32 lanes of a warp cover 32 consecutive c
-            atomicAdd(dw + ((size_t)(c0 + i) * 9 + tap) * 64 + c, __uint_as_float(v[i]));
+            atomicAdd(dw + ((size_t)(c0 + i) * 9 + tap) * g.dw_ct + c, __uint_as_float(v[i]));
         }
       }
     }
@@ -876,7 +878,7 @@ k_wgrad3x3_halo_tf32(const __grid_constant__ CUtensorMap tmX, const __grid_const
         if (sx < 3) {
 #pragma unroll
           for (int i = 0; i < 32; ++i)       // dw[k][tap][ch], k = c0 + i: a warp's lanes cover 32 consecutive channels
-            atomicAdd(dw + ((size_t)(c0 + i) * 9 + tap) * 64 + ch, __uint_as_float(v[i]));
+            atomicAdd(dw + ((size_t)(c0 + i) * 9 + tap) * g.dw_ct + ch, __uint_as_float(v[i]));
         }
       }
     }
@@ -1437,8 +1439,16 @@ int pdt_conv3x3_halo_add(const void* x, const void* w, void* y, const void* adde
 // 1 if pdt_conv3x3_wgrad_halo serves this weight gradient (3x3, stride 1, pad 1 implied).
 int pdt_conv3x3_wgrad_halo_supported(int dtype, int N, int H, int W, int C, int K) {
   if (dtype != PDT_BF16 && dtype != PDT_FP16 && dtype != PDT_FP32) return 0;
-  if (C != 64 || K != 64 || W + 2 > 58 || W < 6 || H < 1 || N < 1) return 0;
-  return 1;
+  if (W + 2 > 58 || W < 6 || H < 1 || N < 1) return 0;
+  if (C == 64 && K == 64) return 1;
+  // 128 -> 128 as four 64 x 64 channel slices, one launch each: pays in fp32, where the generic kernel is bound by
+  // its per-tap im2col traffic (993 us at 1200 images against 4 x 160); in 16 bit the generic kernel is as fast
+  if (C == 128 && K == 128 && dtype == PDT_FP32) {
+    static int env = -1;
+    if (env < 0) { const char* e = getenv("PDT_WGRAD_HALO_SLICES"); env = (e != nullptr && e[0] == '0') ? 0 : 1; }
+    return env;
+  }
+  return 0;
 }
 
 // x: [N][H][W][64], dy: [N][H][W][64] (bf16 / fp16 / fp32 as tf32), dw: [64][3][3][64] fp32, ACCUMULATED into (zero it first).
@@ -1455,7 +1465,8 @@ int pdt_conv3x3_wgrad_halo(const void* x, const void* dy, float* dw, int dtype, 
   }
   HaloGeom g;
   g.addend = nullptr;
-  g.N = N; g.H = H; g.W = W; g.C = C; g.K = K;
+  g.N = N; g.H = H; g.W = W; g.C = 64; g.K = 64;
+  g.dw_ct = C;
   g.Wp = W + 2;
   g.TR = 128 / g.Wp;
   if (g.TR > H) g.TR = H;
@@ -1472,28 +1483,39 @@ int pdt_conv3x3_wgrad_halo(const void* x, const void* dy, float* dw, int dtype, 
   // fp32: a pixel is two 128-byte rows; the box takes 32 channels (one plane), MN-major 32-bit operands use the
   // 32-byte-atom flavour of the 128-byte swizzle
   const CUtensorMapSwizzle swz = f32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
-  const cuuint64_t px = f32 ? 256 : 128;
+  const cuuint64_t es = f32 ? 4 : 2;
   const cuuint32_t bc = f32 ? 32 : 64;
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int grid = g.num_tiles < sms ? g.num_tiles : sms;
+  const void* x_all = x;
+  const void* dy_all = dy;
+  float* dw_all = dw;
+  for (int k0 = 0; k0 < K; k0 += 64)
+  for (int c0 = 0; c0 < C; c0 += 64) {
+  // one 64 x 64 channel slice: the tensor maps see 64 of the layer's channels (pixel stride = the whole pixel)
+  x = reinterpret_cast<const char*>(x_all) + (size_t)c0 * es;
+  dy = reinterpret_cast<const char*>(dy_all) + (size_t)k0 * es;
+  dw = dw_all + (size_t)k0 * 9 * C + c0;
   CUtensorMap tmX, tmDY;
-  cuuint64_t dims[4] = {64, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
-  cuuint64_t strides[3] = {px, (cuuint64_t)W * px, (cuuint64_t)H * W * px};
   cuuint32_t estr[4] = {1, 1, 1, 1};
   {
+    cuuint64_t dims[4] = {64, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+    cuuint64_t strides[3] = {(cuuint64_t)C * es, (cuuint64_t)W * C * es, (cuuint64_t)H * W * C * es};
     cuuint32_t box[4] = {bc, (cuuint32_t)g.Wp, (cuuint32_t)(g.TR + 2), 1};
     if (g_enc(&tmX, dt, 4, const_cast<void*>(x), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
               swz, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
       return 10006;
   }
   {
+    cuuint64_t dims[4] = {64, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+    cuuint64_t strides[3] = {(cuuint64_t)K * es, (cuuint64_t)W * K * es, (cuuint64_t)H * W * K * es};
     cuuint32_t box[4] = {bc, (cuuint32_t)g.Wp, (cuuint32_t)g.TR, 1};
     if (g_enc(&tmDY, dt, 4, const_cast<void*>(dy), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
               swz, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
       return 10007;
   }
-  int dev = 0, sms = 148;
-  cudaGetDevice(&dev);
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  const int grid = g.num_tiles < sms ? g.num_tiles : sms;
   if (f32) {
     auto kern = k_wgrad3x3_halo_tf32;
     PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, WHCfg32::kSmemBytes));
@@ -1507,6 +1529,7 @@ int pdt_conv3x3_wgrad_halo(const void* x, const void* dy, float* dw, int dtype, 
     PDT_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, WHCfg::kSmemBytes));
     PDT_CHECK(launch_pdl(kern, dim3(grid), dim3(128), WHCfg::kSmemBytes, stream, tmX, tmDY, dw, g));
   }
+  }   // channel slices
   return (int)cudaGetLastError();
 }
 

@@ -13,11 +13,17 @@ def main():
     rows = list(csv.reader(out.splitlines()))
     # one table per profiled launch, each starting with its own header row
     heads = [i for i, r in enumerate(rows) if "# Samples" in r]
+    seen = set()
     for t, hi in enumerate(heads):
         end = heads[t + 1] if t + 1 < len(heads) else len(rows)
+        body = rows[hi + 1:end]
+        sig = (len(body), tuple(tuple(r) for r in body[:50]))
+        if sig in seen:                      # the page repeats a launch once per source view
+            continue
+        seen.add(sig)
         title = next((" ".join(r) for r in rows[max(0, hi - 3):hi] if r and "Kernel" in " ".join(r)), "")
-        print("=== launch {} of {} in the report {}".format(t + 1, len(heads), title[:100]))
-        table(rows[hi], [r for r in rows[hi + 1:end]], top)
+        print("=== launch table {} of the report {}".format(len(seen), title[:110]))
+        table(rows[hi], body, top)
 
 
 def table(h, body, top):

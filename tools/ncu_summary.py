@@ -17,12 +17,25 @@ WANT = [
 ]
 
 
+SCALE = {"ns": 1e-3, "nsecond": 1e-3, "us": 1.0, "usecond": 1.0, "ms": 1e3, "msecond": 1e3, "s": 1e6, "second": 1e6,
+         "byte": 1e-6, "Kbyte": 1e-3, "Mbyte": 1.0, "Gbyte": 1e3, "Tbyte": 1e6}
+
+
 def rows_of(path):
+    """One dict per profiled launch; times in us and byte counts in MB whatever unit ncu picked for the report."""
     out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(out.splitlines()))
-    hdr = rows[0]
+    hdr, units = rows[0], rows[1]
     for r in rows[2:]:
-        yield {h: v for h, v in zip(hdr, r)}
+        d = {}
+        for h, u, v in zip(hdr, units, r):
+            if u in SCALE and (h.endswith(".sum") and ("bytes" in h or "time_duration" in h)):
+                try:
+                    v = str(float(v.replace(",", "")) * SCALE[u])
+                except ValueError:
+                    pass
+            d[h] = v
+        yield d
 
 
 def main(paths):
