@@ -129,9 +129,9 @@ int pdt_sgd_flat(float* p, const float* g, float* m, void* shadow, int shadow_dt
 
 /* ---- BatchNorm / SyncBatchNorm on NHWC activations ------------------------
  * x, y, dy, dx, res: [M][C] in `dtype`; statistics and affine parameters fp32.
- * scratch: pdt_bn_scratch_bytes(C) bytes, first word zero before the first
- * call (self-resetting afterwards); do not share one scratch between kernels
- * that may overlap.  comm == NULL or world == 1: plain BatchNorm (cuDNN/ATen
+ * scratch: pdt_bn_scratch_bytes(C) bytes, the first 256 bytes (ticket words of the
+ * two-level cross-CTA fold) zero before the first call (self-resetting
+ * afterwards); do not share one scratch between kernels that may overlap.  comm == NULL or world == 1: plain BatchNorm (cuDNN/ATen
  * batch_norm, 20 layers of torchvision resnet18).  world > 1: SyncBatchNorm
  * with the cross-rank exchange inside the kernel (replaces
  * torch/nn/modules/_functions.py:39-209; distributed_syncBN_amp.py:143-145). */
@@ -224,7 +224,7 @@ int pdt_conv_fprop_add(const void* x, const void* w, void* y, const void* addend
 /* Convolution + BatchNorm batch statistics in one kernel: the epilogue also produces the per-channel
  * mean / invstd of y (and updates the running statistics), so BatchNorm needs no statistics pass of its
  * own (cudnnConvolutionForward + batch_norm statistics kernel).  Dense NHWC output, K <= 512.
- * scratch: pdt_bn_scratch_bytes(K) bytes, first word zero before the first call.
+ * scratch: pdt_bn_scratch_bytes(K) bytes, first 256 bytes zero before the first call.
  * comm != NULL with world > 1: SyncBatchNorm — the CTA that finalises the statistics exchanges the raw moments
  * with its peers over NVLink before it writes mean / invstd (the all_gather of torch's sync_batch_norm,
  * torch/nn/modules/_functions.py:74-76, inside the convolution kernel).  Same for the two kernels below. */

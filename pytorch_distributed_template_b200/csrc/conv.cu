@@ -1099,8 +1099,8 @@ int pdt_conv_fprop_add(const void* x, const void* w, void* y, const void* addend
   return dispatch_fprop(x, w, y, nullptr, dtype, g, stream);
 }
 
-// Convolution + BatchNorm batch statistics in one kernel (dense NHWC output, K <= 512).  scratch: at
-// least 256 + 148 * 2 * K * 4 bytes, first word zero before the first call (pdt_bn_scratch_bytes fits).
+// Convolution + BatchNorm batch statistics in one kernel (dense NHWC output, K <= 512).  scratch:
+// pdt_bn_scratch_bytes(K) bytes (CTA rows + group rows of the two-level fold), first 256 bytes zero before the first call.
 int pdt_conv_fprop_bnstats(const void* x, const void* w, void* y, int dtype, int N, int H, int W, int C, int K, int R, int S,
                            int stride, int pad, void* scratch, const PdtCommDesc* comm, float* running_mean, float* running_var,
                            float momentum, float eps, float* save_mean, float* save_invstd, cudaStream_t stream) {
