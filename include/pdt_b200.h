@@ -19,7 +19,7 @@
 
 /* Bumped whenever an entry point is added or changes its signature; the Python binding refuses a library
  * that reports a different number (a stale build of an older checkout). */
-#define PDT_ABI_VERSION 13
+#define PDT_ABI_VERSION 14
 
 #ifdef __cplusplus
 extern "C" {
@@ -283,6 +283,13 @@ int pdt_conv_fprop_ex(const void* x, const void* w, void* y, const float* bias, 
                       int pad_lo_h, int pad_lo_w, int pad_hi_h, int pad_hi_w, int P, int Q, int OH, int OW, int os,
                       int oa, int ob, int dil_w, const void* addend /* laid out like the OH x OW output, or NULL */,
                       cudaStream_t stream);
+/* The general form with the BatchNorm-statistics epilogue of pdt_conv_fprop_bnstats (dense P x Q output, no bias, no
+ * addend, K <= 512): the fp32 stem uses it. */
+int pdt_conv_fprop_ex_bnstats(const void* x, const void* w, void* y, int dtype, int N, int H, int W, int C, int Cx, long long x_sw,
+                              long long x_sh, long long x_sn, int K, int R, int S, int stride, int pad_lo_h, int pad_lo_w,
+                              int pad_hi_h, int pad_hi_w, int P, int Q, int dil_w, void* scratch, const PdtCommDesc* comm,
+                              float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
+                              float* save_invstd, cudaStream_t stream);
 int pdt_conv_wgrad_ex(const void* x, const void* dy, float* dw, int dtype, int N, int H, int W, int C, int Cx,
                       long long x_sw, long long x_sh, long long x_sn, int K, int R, int S, int stride, int pad_lo_h,
                       int pad_lo_w, int pad_hi_h, int pad_hi_w, int P, int Q, int dil_w, cudaStream_t stream);

@@ -1151,4 +1151,38 @@ int pdt_conv_fprop_ex(const void* x, const void* w, void* y, const float* bias, 
   return dispatch_fprop(x, w, y, bias, dtype, g, stream);
 }
 
+// The general form with the BatchNorm-statistics epilogue (dense output only: os == 1, OH x OW == P x Q, no addend, no bias;
+// K <= 512).  The fp32 stem (a 4x4 convolution over a strided view of the space-to-depth image) uses it so that its
+// BatchNorm needs no statistics pass over the 112 x 112 x 64 output.  scratch / statistics as in pdt_conv_fprop_bnstats.
+int pdt_conv_fprop_ex_bnstats(const void* x, const void* w, void* y, int dtype, int N, int H, int W, int C, int Cx, long long x_sw,
+                              long long x_sh, long long x_sn, int K, int R, int S, int stride, int pad_lo_h, int pad_lo_w,
+                              int pad_hi_h, int pad_hi_w, int P, int Q, int dil_w, void* scratch, const PdtCommDesc* comm,
+                              float* running_mean, float* running_var, float momentum, float eps, float* save_mean,
+                              float* save_invstd, cudaStream_t stream) {
+  if (dtype != PDT_BF16 && dtype != PDT_FP16 && dtype != PDT_FP32) return PDT_E_UNSUPPORTED;
+  if (scratch == nullptr || save_mean == nullptr || save_invstd == nullptr) return PDT_E_UNSUPPORTED;
+  if (K % 8 || K > kStatMaxK || R < 1 || S < 1 || stride < 1 || P < 1 || Q < 1 || dil_w < 1 || (x_sw | x_sh | x_sn) % 16) return PDT_E_UNSUPPORTED;
+  if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(w) | reinterpret_cast<uintptr_t>(y)) & 15) return PDT_E_UNSUPPORTED;
+  int e = load_driver_fns();
+  if (e) return e;
+  ConvGeom g;
+  g.N = N; g.H = H; g.W = W; g.C = C; g.K = K; g.R = R; g.S = S; g.stride = stride; g.dil_w = dil_w;
+  g.pad_h = pad_lo_h; g.pad_w = pad_lo_w; g.pad_hi_h = pad_hi_h; g.pad_hi_w = pad_hi_w;
+  g.P = P; g.Q = Q;
+  g.M = N * P * Q;
+  g.m_tiles = (g.M + BM - 1) / BM;
+  g.OH = P; g.OW = Q; g.os = 1; g.oa = g.ob = 0;
+  g.Cx = Cx; g.x_sw = x_sw; g.x_sh = x_sh; g.x_sn = x_sn;
+  g.addend = nullptr;
+  BnStats bs;
+  bs.enabled = 1;
+  bs.counter = reinterpret_cast<unsigned*>(scratch);
+  bs.partial = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + 256);
+  bs.running_mean = running_mean; bs.running_var = running_var;
+  bs.save_mean = save_mean; bs.save_invstd = save_invstd;
+  bs.momentum = momentum; bs.eps = eps;
+  bs.comm = make_comm(comm);
+  return dispatch_fprop(x, w, y, nullptr, dtype, g, stream, &bs);
+}
+
 }  // extern "C"

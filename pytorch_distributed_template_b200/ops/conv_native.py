@@ -24,6 +24,8 @@ _native.register("pdt_conv3x3_wgrad_halo_supported", [_i, _i, _i, _i, _i, _i])
 _native.register("pdt_conv_wgrad", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp])
 _native.register("pdt_conv_fprop_ex", [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _ll, _ll, _ll, _i, _i, _i, _i,
                                        _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp])
+_native.register("pdt_conv_fprop_ex_bnstats", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _ll, _ll, _ll, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i,
+                                               _i, _vp, _native._PC, _vp, _vp, _native._f, _native._f, _vp, _vp, _vp])
 _native.register("pdt_conv_fprop_add", [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp])
 _native.register("pdt_conv3x3_halo_add", [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _native._PC, _vp, _vp, _native._f, _native._f, _vp, _vp, _vp])
 _native.register("pdt_conv_wgrad_ex", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _ll, _ll, _ll, _i, _i, _i, _i,
@@ -551,6 +553,22 @@ class _StemNative(torch.autograd.Function):
                 ctx.geom = (N, HP, WP, P, Q, K)
                 ctx.mark_non_differentiable(*stats)
                 return y, stats[0], stats[1]
+        elif bnpack is not None and K <= 512 and os.environ.get("PDT_BNSTATS_FUSION", "1") == "1":
+            # generic im2col kernel (fp32 / shapes the patch kernel declines) with the statistics epilogue
+            from .bn import _bn_scratch
+            rm, rv, momentum, eps = bnpack[:4]
+            comm = bnpack[4] if len(bnpack) > 4 else None
+            mean = torch.empty(K, dtype=torch.float32, device=x.device)
+            invstd = torch.empty_like(mean)
+            _native.check(lib.pdt_conv_fprop_ex_bnstats(
+                xs.data_ptr(), wp.data_ptr(), y.data_ptr(), _native.dtype_code(lp), N, HP, g["Wt"], g["C"], g["C"], g["sw"], g["sh"],
+                g["sn"], K, 4, g["S"], 1, 0, 0, 0, 0, P, Q, g["dil"], _bn_scratch(x.device, K).data_ptr(), comm, _native.ptr(rm),
+                _native.ptr(rv), momentum, eps, mean.data_ptr(), invstd.data_ptr(), _native.stream_ptr(x.device)),
+                "pdt_conv_fprop_ex_bnstats")
+            ctx.save_for_backward(xs)
+            ctx.geom = (N, HP, WP, P, Q, K)
+            ctx.mark_non_differentiable(mean, invstd)
+            return y, mean, invstd
         else:
             fprop_ex(xs.data_ptr(), wp, y, None, lp, N, HP, g["Wt"], g["C"], g["C"], g["sw"], g["sh"], g["sn"], K, 4, g["S"], 1,
                      (0, 0, 0, 0), P, Q, P, Q, 1, 0, 0, x.device, dil_w=g["dil"])
