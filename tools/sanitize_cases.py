@@ -6,9 +6,11 @@
 
 Each case also checks its result against torch, so a run without the sanitizer doubles as a smoke test.
 Covered: k_conv_igemm (fprop, stride-1 and stride-2 data gradient), k_conv_wgrad, k_conv3x3_halo<64/128>,
-k_wgrad3x3_halo, k_stem_conv (+ k_stem_s2d), sp::k_fwd_stats / k_fwd_apply / k_bwd_reduce / k_bwd_apply,
-k_bn_pool_*_321, k_maxpool / k_avgpool (16-bit and fp32), k_ce_fwd / k_scale_cast, k_sgd_flat / k_reduce_scatter<1>,
+k_wgrad3x3_halo, k_stem_conv (+ k_stem_s2d), k_stem_wgrad, sp::k_fwd_stats / k_fwd_apply / k_bwd_reduce / k_bwd_apply,
+k_bn_pool_*_321 (16-bit and, in the fp32 step of model_case, the _f32 pair together with k_conv3x3_halo<.., float> and
+k_wgrad3x3_halo_tf32), k_maxpool / k_avgpool, k_ce_fwd / k_scale_cast, k_sgd_flat / k_reduce_scatter<1>,
 the rank-emulation launch (k_reduce_scatter / k_sgd_allgather / k_allreduce_small / k_bcast_pull bodies + flag protocol).
+(The CTA-pair forms need >= 2 tiles per SM and are exercised by tests/test_conv_gpu.py instead.)
 """
 import os
 import sys
