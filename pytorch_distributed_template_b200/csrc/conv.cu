@@ -721,9 +721,18 @@ int cluster_size_for(int BN, const ConvGeom& g, const void* filter, cudaStream_t
   if (env < 0) { const char* e = getenv("PDT_CONV_CLUSTER"); env = e ? atoi(e) : 0; }
   int cl = env > 0 ? env : 2;     // 4 measured the same per launch but only 33 clusters of 4 are co-resident (132 of 148 SMs)
   if (BN < 128 || (cl != 2 && cl != 4)) return 1;
-  if (g.m_tiles < 148) return 1;                            // fewer M tiles than SMs: keep every SM on a tile of its own
-  if (!memory_on_current_device(filter, stream)) return 1;  // the multicast tile (the filter) must be this GPU's memory
+  // fewer M tiles than SMs: a multicast cluster would leave SMs idle, but a CTA PAIR (cta_group::2, no multicast load) keeps
+  // the same number of SMs busy as single CTAs and runs the wider instruction: -2 = "pairs only" (layer 4 at 150 images
+  // per GPU: 58 M tiles)
+  if (g.m_tiles < 148) return (cl == 2 && g.m_tiles >= 2) ? -2 : 1;
+  if (!memory_on_current_device(filter, stream)) return cl == 2 ? -2 : 1;  // a multicast tile (the filter) must be this GPU's memory
   return cl;
+}
+
+int conv_pair_enabled() {
+  static int pair = -1;
+  if (pair < 0) { const char* e = getenv("PDT_CONV_PAIR"); pair = (e != nullptr && e[0] == '0') ? 0 : 1; }
+  return pair;
 }
 
 template <int BN, typename T, int CL, bool PAIR = false>
@@ -779,8 +788,7 @@ int launch_igemm(const CUtensorMap& tmA, const CUtensorMap& tmB, void* y, const 
   if constexpr (BN >= 128) {
     if (cl == 4) return launch_igemm_cl<BN, T, 4>(tmA, tmB, y, bias, g, bs, sms, stream);
     if (cl == 2) {
-      static int pair = -1;                 // CTA pairs run one M = 256 cta_group::2 MMA (see k_conv_igemm); PDT_CONV_PAIR=0: multicast pairs
-      if (pair < 0) { const char* e = getenv("PDT_CONV_PAIR"); pair = (e != nullptr && e[0] == '0') ? 0 : 1; }
+      const int pair = conv_pair_enabled();  // CTA pairs run one M = 256 cta_group::2 MMA (see k_conv_igemm); PDT_CONV_PAIR=0: multicast pairs
       // pairs pay when the k loop is long enough to amortise the pair's hand-shakes (3x3 layers: 18-72 k-blocks;
       // measured slower on 1x1 projections with 2-4 k-blocks)
       const int kb = g.R * g.S * ((g.C + (128 / (int)sizeof(T)) - 1) / (128 / (int)sizeof(T)));
@@ -795,7 +803,12 @@ template <int BN>
 int launch_fprop(const void* x, const void* w, void* y, const float* bias, int dtype, const ConvGeom& g, const BnStats& bs,
                  cudaStream_t stream) {
   CUtensorMap tmA, tmB;
-  const int cl = cluster_size_for(BN, g, w, stream);
+  int cl = cluster_size_for(BN, g, w, stream);
+  if (cl == -2) {                        // "pairs only": the same condition launch_igemm uses to pick the pair form
+    const int bk = 128 / esize_of(dtype);
+    const int kb = g.R * g.S * ((g.C + bk - 1) / bk);
+    cl = (conv_pair_enabled() == 1 && kb >= 9) ? 2 : 1;
+  }
   {
     cuuint64_t dims[4] = {(cuuint64_t)g.Cx, (cuuint64_t)g.W, (cuuint64_t)g.H, (cuuint64_t)g.N};
     cuuint64_t strides[3] = {(cuuint64_t)g.x_sw, (cuuint64_t)g.x_sh, (cuuint64_t)g.x_sn};
