@@ -19,7 +19,7 @@
 
 /* Bumped whenever an entry point is added or changes its signature; the Python binding refuses a library
  * that reports a different number (a stale build of an older checkout). */
-#define PDT_ABI_VERSION 14
+#define PDT_ABI_VERSION 15
 
 #ifdef __cplusplus
 extern "C" {
@@ -307,7 +307,8 @@ int pdt_stem_s2d_u8(const unsigned char* x, void* y, int dtype, int N, int H, in
 int pdt_dgrad_weight(const void* w, void* out, int K, int C, int R, int S, int Th, int Tw, const int* rs, const int* ss,
                      cudaStream_t stream);
 /* The same for many filters in one launch.  `jobs_dev` is a DEVICE array of njobs descriptors; tile_begin is
- * the running sum of ceil(K/32) * ceil(C/32) * Th * Tw over the preceding jobs, total_tiles the grand total. */
+ * the running sum of ceil(K/t) * ceil(C/t) * Th * Tw over the preceding jobs with t = pdt_dgrad_tile() (64),
+ * total_tiles the grand total. */
 typedef struct PdtDgradJob {
   const void* src;
   void* dst;
@@ -317,6 +318,7 @@ typedef struct PdtDgradJob {
   int pad_;
 } PdtDgradJob;
 int pdt_dgrad_weight_batched(const PdtDgradJob* jobs_dev, int njobs, int total_tiles, cudaStream_t stream);
+int pdt_dgrad_tile(void);
 
 #ifdef __cplusplus
 }

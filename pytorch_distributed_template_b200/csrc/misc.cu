@@ -607,9 +607,10 @@ extern "C" int pdt_dgrad_weight(const void* w, void* out, int K, int C, int R, i
 // All filter re-layouts of a model in ONE launch: `jobs` is a device array (built once, the pointers are arena
 // slots and persistent buffers), a block finds its job from the running tile count.
 namespace {
+constexpr int kDT = 64;      // tile edge: 64 output channels x 64 input channels (128-byte rows on both sides)
 __global__ void __launch_bounds__(256) k_dgrad_weight_batched(const PdtDgradJob* __restrict__ jobs, int njobs) {
   pdl_enter();
-  __shared__ uint16_t tile[32][34];
+  __shared__ __align__(16) uint16_t tile[kDT][kDT + 2];
   __shared__ PdtDgradJob jb;
   if (threadIdx.x == 0) {
     int lo = 0, hi = njobs - 1;                       // last job whose tile_begin <= blockIdx.x
@@ -621,7 +622,7 @@ __global__ void __launch_bounds__(256) k_dgrad_weight_batched(const PdtDgradJob*
   }
   __syncthreads();
   const int K = jb.K, C = jb.C, R = jb.R, S = jb.S, Th = jb.Th, Tw = jb.Tw;
-  const int kt = (K + 31) / 32, ct = (C + 31) / 32;
+  const int kt = (K + kDT - 1) / kDT, ct = (C + kDT - 1) / kDT;
   int t = (int)blockIdx.x - jb.tile_begin;
   const int bx = t % kt; t /= kt;
   const int by = t % ct; t /= ct;
@@ -629,16 +630,35 @@ __global__ void __launch_bounds__(256) k_dgrad_weight_batched(const PdtDgradJob*
   const int r = jb.rs[i], s = jb.ss[j];
   const uint16_t* __restrict__ w = reinterpret_cast<const uint16_t*>(jb.src);
   uint16_t* __restrict__ out = reinterpret_cast<uint16_t*>(jb.dst);
-  const int k0 = bx * 32, c0 = by * 32;
-  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  for (int kk = ty; kk < 32; kk += 8) {
-    const int k = k0 + kk, c = c0 + tx;
-    tile[kk][tx] = (k < K && c < C) ? w[(((size_t)k * R + r) * S + s) * C + c] : (uint16_t)0;
+  const int k0 = bx * kDT, c0 = by * kDT;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;     // 32 lanes x 8 rows; a lane moves two adjacent elements
+  // The 32 x 32 version of this kernel moved 64-byte row pieces with one load in flight per thread (53 us for the 22 MB
+  // of ResNet-18 filters, 0.8 TB/s).  Here a warp reads / writes whole 128-byte rows and has eight loads in flight.
+  const bool vec = ((C | K) & 1) == 0 && ((reinterpret_cast<uintptr_t>(w) | reinterpret_cast<uintptr_t>(out)) & 3) == 0;
+  uint32_t v[8];
+#pragma unroll
+  for (int m = 0; m < 8; ++m) {
+    const int k = k0 + ty + 8 * m, c = c0 + 2 * tx;
+    const size_t at = (((size_t)k * R + r) * S + s) * C + c;
+    uint32_t x = 0;
+    if (k < K && c < C) {
+      if (vec) x = *reinterpret_cast<const uint32_t*>(w + at);        // c + 1 < C because C is even
+      else x = (uint32_t)w[at] | (c + 1 < C ? (uint32_t)w[at + 1] << 16 : 0u);
+    }
+    v[m] = x;
   }
+#pragma unroll
+  for (int m = 0; m < 8; ++m) *reinterpret_cast<uint32_t*>(&tile[ty + 8 * m][2 * tx]) = v[m];
   __syncthreads();
-  for (int cc = ty; cc < 32; cc += 8) {
-    const int c = c0 + cc, k = k0 + tx;
-    if (c < C && k < K) out[(((size_t)c * Th + i) * Tw + j) * K + k] = tile[tx][cc];
+#pragma unroll
+  for (int m = 0; m < 8; ++m) {
+    const int cc = ty + 8 * m, c = c0 + cc, k = k0 + 2 * tx;
+    if (c < C && k < K) {
+      const size_t at = (((size_t)c * Th + i) * Tw + j) * K + k;
+      const uint32_t lo = tile[2 * tx][cc], hi = tile[2 * tx + 1][cc];
+      if (vec) *reinterpret_cast<uint32_t*>(out + at) = lo | (hi << 16);
+      else { out[at] = (uint16_t)lo; if (k + 1 < K) out[at + 1] = (uint16_t)hi; }
+    }
   }
 }
 }  // namespace
@@ -648,5 +668,8 @@ extern "C" int pdt_dgrad_weight_batched(const PdtDgradJob* jobs_dev, int njobs, 
   launch_pdl(k_dgrad_weight_batched, dim3(total_tiles), dim3(256), 0, stream, jobs_dev, njobs);
   return (int)cudaGetLastError();
 }
+
+// Tile edge of pdt_dgrad_weight_batched: a job covers ceil(K / t) * ceil(C / t) * Th * Tw tiles (PdtDgradJob.tile_begin).
+extern "C" int pdt_dgrad_tile(void) { return kDT; }
 
 extern "C" int pdt_abi_version(void) { return PDT_ABI_VERSION; }

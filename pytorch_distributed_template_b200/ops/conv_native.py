@@ -38,6 +38,7 @@ _native.register("pdt_stem_wgrad", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp])
 _native.register("pdt_stem_conv", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, _native._PC, _vp, _vp, _native._f, _native._f, _vp, _vp, _vp])
 _native.register("pdt_dgrad_weight", [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp])
 _native.register("pdt_dgrad_weight_batched", [_vp, _i, _i, _vp])
+_native.register("pdt_dgrad_tile", [])
 _native.register("pdt_conv_fprop_bnstats", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _native._PC, _vp, _vp,
                                             _native._f, _native._f, _vp, _vp, _vp])
 
@@ -234,6 +235,7 @@ class _DgradPlan:
                 return                                   # the descriptor upload is a host-to-device copy
             arr = (_DgradJob * len(self.order))()
             tiles = 0
+            te = int(_native.lib().pdt_dgrad_tile())        # tile edge of the batched re-layout kernel
             for n, key in enumerate(self.order):
                 ptr, K, C, R, S, rs, ss = key
                 j = arr[n]
@@ -244,7 +246,7 @@ class _DgradPlan:
                 for i, v in enumerate(ss):
                     j.ss[i] = v
                 j.tile_begin = tiles
-                tiles += ((K + 31) // 32) * ((C + 31) // 32) * len(rs) * len(ss)
+                tiles += ((K + te - 1) // te) * ((C + te - 1) // te) * len(rs) * len(ss)
             host = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
             self.table = host.to(self.device)
             self.table_jobs = len(self.order)

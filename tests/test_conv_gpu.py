@@ -435,3 +435,35 @@ def test_conv_cta_pair_tiles(native_lib, dtype, N, C, H, K, R, stride, pad):
     assert torch.equal(y2, y)
     assert torch.allclose(mean, yf.mean((0, 2, 3)), rtol=2e-3, atol=2e-3)
     assert torch.allclose(invstd, torch.rsqrt(yf.var((0, 2, 3), unbiased=False) + 1e-5), rtol=5e-3, atol=5e-3)
+
+
+def test_batched_dgrad_filter_layouts(native_lib):
+    """One launch re-lays out every data-gradient filter of a model (64 x 64 tiles): against index_select / transpose,
+    with channel counts that are not multiples of the tile and tap subsets of a stride-2 gradient."""
+    import types
+    from pytorch_distributed_template_b200.ops import conv_native
+    torch.manual_seed(40)
+    dev = torch.device("cuda", 0)
+    st = types.SimpleNamespace(weights_version=0)
+    cases = [(64, 64, 3, [2, 1, 0], [2, 1, 0]), (128, 64, 3, [1], [2, 0]), (72, 40, 3, [2, 0], [1]), (512, 256, 1, [0], [0]),
+             (200, 136, 3, [2, 1, 0], [2, 1, 0]), (8, 8, 3, [0, 2], [0, 2])]
+    ws = []
+    for (K, C, R, rs, ss) in cases:
+        w = torch.randn(K, C, R, R, device=dev).to(torch.float16).contiguous(memory_format=torch.channels_last)
+        ws.append(w)
+        conv_native.dgrad_weight(w, rs, ss, st)            # registers the job (and lays it out once on its own)
+    conv_native.prepare_dgrad_weights(st)                    # all of them in one launch
+    for w, (K, C, R, rs, ss) in zip(ws, cases):
+        out = conv_native.dgrad_weight(w, rs, ss, st)
+        ir, is_ = torch.tensor(rs, device=dev), torch.tensor(ss, device=dev)
+        ref = w.index_select(2, ir).index_select(3, is_).transpose(0, 1)
+        assert out.shape == ref.shape and torch.equal(out, ref.contiguous(memory_format=torch.channels_last)), (K, C, R)
+    # a weight update followed by prepare() refreshes every buffer
+    for w in ws:
+        w.mul_(2)
+    st.weights_version = 1
+    conv_native.prepare_dgrad_weights(st)
+    for w, (K, C, R, rs, ss) in zip(ws, cases):
+        out = conv_native.dgrad_weight(w, rs, ss, st)
+        ref = w.index_select(2, torch.tensor(rs, device=dev)).index_select(3, torch.tensor(ss, device=dev)).transpose(0, 1)
+        assert torch.equal(out, ref.contiguous(memory_format=torch.channels_last))
