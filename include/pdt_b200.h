@@ -19,7 +19,7 @@
 
 /* Bumped whenever an entry point is added or changes its signature; the Python binding refuses a library
  * that reports a different number (a stale build of an older checkout). */
-#define PDT_ABI_VERSION 15
+#define PDT_ABI_VERSION 16
 
 #ifdef __cplusplus
 extern "C" {
@@ -319,6 +319,12 @@ typedef struct PdtDgradJob {
 } PdtDgradJob;
 int pdt_dgrad_weight_batched(const PdtDgradJob* jobs_dev, int njobs, int total_tiles, cudaStream_t stream);
 int pdt_dgrad_tile(void);
+/* Stem filter [K][3][7][7] (any element strides) -> [K][4][4][16], the filter of the 4x4 / 1 convolution over the
+ * space-to-depth image, and the inverse for its fp32 gradient (writes every element of dw). */
+int pdt_stem_weight_s2d(const void* w, void* wp, int dtype, int K, long long sk, long long sc, long long sr, long long ss,
+                        cudaStream_t stream);
+int pdt_stem_weight_grad_unpack(const float* dwp, float* dw, int K, long long sk, long long sc, long long sr, long long ss,
+                                cudaStream_t stream);
 
 #ifdef __cplusplus
 }

@@ -33,6 +33,8 @@ _native.register("pdt_conv_wgrad_ex", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _l
 _native.register("pdt_stem_s2d", [_vp, _vp, _i, _i, _i, _i, _i, _vp])
 _native.register("pdt_stem_s2d_u8", [_vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _vp])
 _native.register("pdt_stem_conv_supported", [_i, _i, _i, _i, _i])
+_native.register("pdt_stem_weight_s2d", [_vp, _vp, _i, _i, _ll, _ll, _ll, _ll, _vp])
+_native.register("pdt_stem_weight_grad_unpack", [_vp, _vp, _i, _ll, _ll, _ll, _ll, _vp])
 _native.register("pdt_stem_wgrad_supported", [_i, _i, _i, _i, _i])
 _native.register("pdt_stem_wgrad", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp])
 _native.register("pdt_stem_conv", [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, _native._PC, _vp, _vp, _native._f, _native._f, _vp, _vp, _vp])
@@ -465,9 +467,20 @@ def conv_native(x, weight, w_lp, stride, padding, bnpack=None, consume=None, pro
 
 
 # ------------------------------------------------------------------------------------------ stem (7x7/2, C_in = 3)
+def _stem_weight_native(t):
+    return (t.is_cuda and _native.available() and t.dtype in (torch.float16, torch.bfloat16, torch.float32)
+            and os.environ.get("PDT_STEM_WEIGHT", "native") == "native")
+
+
 def stem_weight_s2d(w_lp):
     """[K,3,7,7] -> [K,4,4,16] (k, r', s', (dy,dx,c) padded to 16): filter of the equivalent 4x4/1 conv."""
     K = w_lp.shape[0]
+    if _stem_weight_native(w_lp) and tuple(w_lp.shape[1:]) == (3, 7, 7):       # one launch (csrc/misc.cu: k_stem_weight_s2d)
+        out = torch.empty((K, 4, 4, 16), dtype=w_lp.dtype, device=w_lp.device)
+        sk, sc, sr, ss = w_lp.stride()
+        _native.check(_native.lib().pdt_stem_weight_s2d(w_lp.data_ptr(), out.data_ptr(), _native.dtype_code(w_lp.dtype), K, sk, sc, sr, ss,
+                                                        _native.stream_ptr(w_lp.device)), "pdt_stem_weight_s2d")
+        return out
     wp = F.pad(w_lp, (0, 1, 0, 1))                                   # 8x8, zero last row/col
     wp = wp.reshape(K, 3, 4, 2, 4, 2).permute(0, 2, 4, 3, 5, 1)       # k, r', s', dy, dx, c
     wp = wp.reshape(K, 4, 4, 12)
@@ -476,6 +489,12 @@ def stem_weight_s2d(w_lp):
 
 def stem_weight_grad_from_s2d(dwp, K):
     """inverse of stem_weight_s2d for the fp32 gradient: [K,4,4,16] -> [K,3,7,7]."""
+    if _stem_weight_native(dwp) and dwp.dtype == torch.float32 and dwp.is_contiguous() and dwp.numel() == K * 256:
+        dw = torch.empty((K, 3, 7, 7), dtype=torch.float32, device=dwp.device, memory_format=CL)
+        sk, sc, sr, ss = dw.stride()
+        _native.check(_native.lib().pdt_stem_weight_grad_unpack(dwp.data_ptr(), dw.data_ptr(), K, sk, sc, sr, ss,
+                                                                _native.stream_ptr(dwp.device)), "pdt_stem_weight_grad_unpack")
+        return dw
     g = dwp.reshape(K, 4, 4, 16)[..., :12].reshape(K, 4, 4, 2, 2, 3).permute(0, 5, 1, 3, 2, 4)   # k,c,r',dy,s',dx
     return g.reshape(K, 3, 8, 8)[:, :, :7, :7]
 

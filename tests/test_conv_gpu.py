@@ -467,3 +467,24 @@ def test_batched_dgrad_filter_layouts(native_lib):
         out = conv_native.dgrad_weight(w, rs, ss, st)
         ref = w.index_select(2, torch.tensor(rs, device=dev)).index_select(3, torch.tensor(ss, device=dev)).transpose(0, 1)
         assert torch.equal(out, ref.contiguous(memory_format=torch.channels_last))
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16, torch.float32])
+def test_stem_filter_space_to_depth_kernels(native_lib, dtype, monkeypatch):
+    """k_stem_weight_s2d / k_stem_weight_grad_unpack against the pad / reshape / permute formulation, for a
+    channels_last and a plain-contiguous filter."""
+    from pytorch_distributed_template_b200.ops import conv_native
+    torch.manual_seed(41)
+    dev = torch.device("cuda", 0)
+    for fmt in (torch.channels_last, torch.contiguous_format):
+        w = torch.randn(64, 3, 7, 7, device=dev).to(dtype).contiguous(memory_format=fmt)
+        got = conv_native.stem_weight_s2d(w)
+        monkeypatch.setenv("PDT_STEM_WEIGHT", "torch")
+        want = conv_native.stem_weight_s2d(w)
+        monkeypatch.setenv("PDT_STEM_WEIGHT", "native")
+        assert got.shape == want.shape and torch.equal(got, want)
+    dwp = torch.randn(64, 256, device=dev)
+    got = conv_native.stem_weight_grad_from_s2d(dwp, 64)
+    monkeypatch.setenv("PDT_STEM_WEIGHT", "torch")
+    want = conv_native.stem_weight_grad_from_s2d(dwp, 64)
+    assert got.shape == (64, 3, 7, 7) and torch.equal(got, want.contiguous())
