@@ -14,8 +14,8 @@ for fam in k_conv_igemm k_conv_wgrad k_conv3x3_halo k_wgrad3x3_halo k_stem_conv 
   ncu --set full --clock-control none --import-source on --profile-from-start off -k regex:$fam -c ${COUNT:-2} \
       -o $OUT/prof_r2_$fam -f python tools/step_profile.py --batch $BATCH > $OUT/ncu_r2_$fam.log 2>&1
   rc=$?
-  python tools/ncu_summary.py $OUT/prof_r2_$fam.ncu-rep >> $OUT/ncu_r2_summary.md 2>/dev/null
-  python tools/ncu_hot.py $OUT/prof_r2_$fam.ncu-rep 10 > $OUT/ncu_r2_hot_$fam.txt 2>/dev/null
+  python tools/ncu_summary.py $OUT/prof_r2_$fam.ncu-rep >> $OUT/ncu_r2_summary.md 2>>$OUT/ncu_r2_errors.txt
+  python tools/ncu_hot.py $OUT/prof_r2_$fam.ncu-rep 10 > $OUT/ncu_r2_hot_$fam.txt 2>>$OUT/ncu_r2_errors.txt
   case " $KEEP " in *" $fam "*) ;; *) rm -f $OUT/prof_r2_$fam.ncu-rep ;; esac
   tail -c 400 $OUT/ncu_r2_$fam.log > $OUT/ncu_r2_$fam.tail; rm -f $OUT/ncu_r2_$fam.log
   echo "$fam exit $rc"
